@@ -1,0 +1,61 @@
+/*
+ * Minimal, ABI-faithful <jni.h> for building the JNI entry points on a machine
+ * without a JDK (this image has none).  Only what the Smith-Waterman binding
+ * touches is declared: the primitive typedefs and JNIEnv::GetDirectBufferAddress.
+ *
+ * The JNIEnv layout follows the JNI specification's "Interface Function Table":
+ * JNIEnv points to a table of function pointers in which slots 0-3 are reserved
+ * and GetDirectBufferAddress is slot 230.  A library compiled against this
+ * header therefore calls the right slot of a real JVM's table.  When a JDK is
+ * available, build with -I$JAVA_HOME/include -I$JAVA_HOME/include/linux instead
+ * (mgl_b200/csrc/Makefile picks that up from JAVA_HOME).
+ */
+#ifndef MGL_B200_JNI_MIN_H
+#define MGL_B200_JNI_MIN_H
+
+#include <stdint.h>
+
+#define JNIEXPORT __attribute__((visibility("default")))
+#define JNIIMPORT
+#define JNICALL
+
+typedef int32_t jint;
+typedef int64_t jlong;
+typedef int8_t  jbyte;
+
+#ifdef __cplusplus
+class _jobject {};
+class _jclass : public _jobject {};
+typedef _jobject *jobject;
+typedef _jclass  *jclass;
+#else
+struct _jobject;
+typedef struct _jobject *jobject;
+typedef jobject jclass;
+#endif
+
+#define MGL_JNI_SLOT_GetDirectBufferAddress 230
+#define MGL_JNI_TABLE_SLOTS 235
+
+struct JNINativeInterface_;
+struct JNIEnv_;
+#ifdef __cplusplus
+typedef JNIEnv_ JNIEnv;
+#else
+typedef const struct JNINativeInterface_ *JNIEnv;
+#endif
+
+struct JNINativeInterface_ {
+    void *slots_0_229[MGL_JNI_SLOT_GetDirectBufferAddress];
+    void *(JNICALL *GetDirectBufferAddress)(JNIEnv *env, jobject buf);
+    void *slots_231_234[MGL_JNI_TABLE_SLOTS - MGL_JNI_SLOT_GetDirectBufferAddress - 1];
+};
+
+#ifdef __cplusplus
+struct JNIEnv_ {
+    const struct JNINativeInterface_ *functions;
+    void *GetDirectBufferAddress(jobject buf) { return functions->GetDirectBufferAddress(this, buf); }
+};
+#endif
+
+#endif /* MGL_B200_JNI_MIN_H */
