@@ -1,0 +1,24 @@
+/*
+ * sw_config.h -- which fill kernels exist.  One kernel per (arithmetic, lane
+ * group width G, registers per lane K); the planner only emits launches whose
+ * (kind, G, K) is in this table, and sw_fill_dispatch.cu fails loudly otherwise.
+ */
+#ifndef MGL_B200_SW_CONFIG_H
+#define MGL_B200_SW_CONFIG_H
+
+#define MGLSW_KMAX 24            /* registers (alt columns) per lane, upper bound */
+#define MGLSW_G_SHORT 8          /* lane group for alt length <= 8 * KMAX         */
+#define MGLSW_G_LONG 32          /* whole warp per pair, strip-mined              */
+#define MGLSW_FILL_THREADS 128   /* 4 warps per block                             */
+
+/* X(kind_type, G, K) for every instantiated kernel */
+#define MGLSW_FOR_K_1_24(X, T, G) \
+    X(T, G, 1) X(T, G, 2) X(T, G, 3) X(T, G, 4) X(T, G, 5) X(T, G, 6) X(T, G, 7) X(T, G, 8) \
+    X(T, G, 9) X(T, G, 10) X(T, G, 11) X(T, G, 12) X(T, G, 13) X(T, G, 14) X(T, G, 15) X(T, G, 16) \
+    X(T, G, 17) X(T, G, 18) X(T, G, 19) X(T, G, 20) X(T, G, 21) X(T, G, 22) X(T, G, 23) X(T, G, 24)
+#define MGLSW_FOR_K_7_24(X, T, G) \
+    X(T, G, 7) X(T, G, 8) \
+    X(T, G, 9) X(T, G, 10) X(T, G, 11) X(T, G, 12) X(T, G, 13) X(T, G, 14) X(T, G, 15) X(T, G, 16) \
+    X(T, G, 17) X(T, G, 18) X(T, G, 19) X(T, G, 20) X(T, G, 21) X(T, G, 22) X(T, G, 23) X(T, G, 24)
+
+#endif

@@ -1,0 +1,241 @@
+/*
+ * sw_fill.h -- the matrix fill, one lane's view.
+ *
+ * Replaces the reference's fill loops (calculateMatrix sw.cpp:5-146 and its
+ * AVX2 twin calculateMatrix_avx sw_avx.cpp:110-322) with a strip-mined
+ * wavefront: a group of G lanes sweeps the ref rows, each lane holding K
+ * adjacent alt columns in registers (H of the previous row, E, the alt bytes
+ * and a 4-bit-per-cell trace accumulator).  Lane l is one row behind lane
+ * l - 1; the two values that cross a lane boundary (H and F of the lane's last
+ * real column) travel by warp shuffle.  Alt lengths beyond G * K columns are
+ * processed as several strips; the last lane of a strip parks (H, F) per row
+ * in a carry column in HBM which lane 0 of the next strip reads back -- the
+ * GPU analogue of the score[]/step[] band carry in sw_avx.cpp:36-49,193-198.
+ * The same carry column of the LAST strip is H[.][ql], which the traceback
+ * kernel scans for the reference's last-column maximum (sw.cpp:100-104);
+ * the registers of row tl are captured for the last-row scan (sw.cpp:116-127).
+ *
+ * FillLane is SW_HD: the CUDA kernel (sw_fill_kernel.cuh) drives 32 of them in
+ * a warp with __shfl_up_sync; tests/emu drives 32 of them in a loop on the CPU.
+ */
+#ifndef MGL_B200_SW_FILL_H
+#define MGL_B200_SW_FILL_H
+#include "sw_cell.h"
+#include "sw_layout.h"
+
+namespace mglsw {
+
+#if SW_ON_DEVICE
+#define SW_LDG(p) __ldg(p)
+#else
+#define SW_LDG(p) (*(p))
+#endif
+
+struct Carry { u32 h, f; };   /* 8 bytes: H[i][last col] + match, F[i][last col + 1] (both + bias) */
+
+/* device buffers of one fill launch */
+struct FillArgs {
+    const uint8_t *arena;     /* raw sequence bytes                                   */
+    const UnitDesc *units;    /* units of this launch, (32 / G) per warp              */
+    u32 *trace;               /* trace buffer (word offsets in UnitDesc)              */
+    Carry *carry;             /* strip carry columns                                  */
+    u32 *lastrow;             /* captured last rows                                   */
+    u32 n_warps;
+    CellConsts c;
+};
+
+template <class T, int G, int K>
+struct FillLane {
+    static constexpr int Q = (K + 3) / 4;
+    u32 e[K], hm[K], bq[K], acc[K];
+    u32 hleft;                /* H[i-1][first col - 1] + match: diagonal input of register 0 */
+    u32 h_out, f_out;         /* this step's values for the right-hand neighbour      */
+    u32 ra_next;              /* ref bytes of the next step's row (prefetched)        */
+    Carry cin_next;           /* carry-in of the next step's row (strips > 0, lane 0) */
+
+    /* lane constants */
+    const uint8_t *ref0, *ref1, *alt0, *alt1;
+    u32 tl0, tl1, tlmax, own_rows, ql;
+    u32 lane;                 /* lane inside the group                                */
+    u32 wlane;                /* lane inside the warp                                 */
+    u32 n;                    /* real columns of this lane in the current strip       */
+    u32 j0;                   /* 1-based first column of this lane                    */
+    u32 slot, nslots;
+    u32 indel, active, strip, nstrips, rb_count;
+    u32 col_base, col_rem;
+    u32 *trace_base;          /* trace words of the warp region                       */
+    u32 *trace_cur;           /* ... of the current strip                             */
+    Carry *carry_cols;        /* two columns of carry_rows entries                    */
+    u32 carry_rows;
+    u32 *lastrow;             /* PAIRS regions of nslots * K words                    */
+
+    SW_HD void setup(const FillArgs &a, const UnitDesc &u, u32 warp_lane)
+    {
+        wlane = warp_lane;
+        lane = warp_lane % G;
+        ref0 = a.arena + u.ref_off[0];
+        alt0 = a.arena + u.alt_off[0];
+        const int two = (T::PAIRS == 2 && u.pair[1] != NO_PAIR);
+        ref1 = two ? a.arena + u.ref_off[1] : ref0;
+        alt1 = two ? a.arena + u.alt_off[1] : alt0;
+        tl0 = u.tl[0];
+        tl1 = two ? u.tl[1] : u.tl[0];
+        tlmax = u.tlmax;
+        own_rows = u.carry_rows - 1;
+        ql = u.ql;
+        nstrips = u.nstrips;
+        nslots = u.nstrips * G;
+        col_base = u.col_base;
+        col_rem = u.col_rem;
+        rb_count = u.rb_count;
+        indel = (u.flags & UNIT_INDEL) ? 1u : 0u;
+        active = (u.flags & UNIT_ACTIVE) ? 1u : 0u;
+        trace_base = a.trace + u.trace_off;
+        trace_cur = trace_base;
+        carry_cols = a.carry + u.carry_off;
+        carry_rows = u.carry_rows;
+        lastrow = a.lastrow + u.lastrow_off;
+        h_out = f_out = 0;
+    }
+
+    SW_HD int bnd(const CellConsts &c, int x) const { return boundary_score(x, (int)indel, c.s_go, c.s_ge); }
+
+    SW_HD u32 fetch_ref(int i) const
+    {
+        int i0 = i < 1 ? 1 : (i > (int)tl0 ? (int)tl0 : i);
+        u32 r = SW_LDG(ref0 + (i0 - 1));
+        if (T::PAIRS == 2) {
+            int i1 = i < 1 ? 1 : (i > (int)tl1 ? (int)tl1 : i);
+            r |= (u32)SW_LDG(ref1 + (i1 - 1)) << 16;
+        }
+        return r;
+    }
+    SW_HD Carry fetch_carry(int i) const
+    {
+        Carry z; z.h = 0; z.f = 0;
+        if (strip == 0 || lane != 0) return z;
+        int ii = i < 1 ? 1 : (i > (int)own_rows ? (int)own_rows : i);
+        const Carry *col = carry_cols + (size_t)((strip - 1) & 1u) * carry_rows;
+#if SW_ON_DEVICE
+        const uint2 v = __ldcg(reinterpret_cast<const uint2 *>(col + ii));
+        z.h = v.x; z.f = v.y;
+        return z;
+#else
+        return col[ii];
+#endif
+    }
+
+    /* state of the row above row 1 (sw.cpp:10-40): E seeds, H[0][j], and the diagonal of register 0 */
+    SW_HD void reset_rows(const CellConsts &c)
+    {
+#pragma unroll
+        for (int k = 0; k < K; k++) {
+            const int b = bnd(c, (int)j0 + k);
+            e[k] = T::rep(c.bias + b - c.s_go);
+            hm[k] = T::rep(c.bias + b + c.s_match);
+        }
+        hleft = T::rep(c.bias + c.s_match + bnd(c, (int)j0 - 1));
+    }
+
+    SW_HD void strip_begin(const CellConsts &c, u32 s)
+    {
+        strip = s;
+        trace_cur = trace_base + (size_t)s * strip_trace_words(rb_count, K);
+        slot = s * G + lane;
+        n = col_base + (slot < col_rem ? 1u : 0u);
+        j0 = 1u + (slot < col_rem ? slot * (col_base + 1) : col_rem * (col_base + 1) + (slot - col_rem) * col_base);
+#pragma unroll
+        for (int k = 0; k < K; k++) {
+            u32 j = j0 + (u32)k;                      /* 1-based column */
+            if (j > ql) j = ql;                       /* virtual register: any byte will do */
+            u32 b = SW_LDG(alt0 + (j - 1));
+            if (T::PAIRS == 2) b |= (u32)SW_LDG(alt1 + (j - 1)) << 16;
+            bq[k] = b;
+            acc[k] = 0;
+        }
+        reset_rows(c);
+        h_out = T::rep(c.bias);
+        f_out = T::rep(c.bias);
+        ra_next = fetch_ref(-(int)lane);
+        cin_next = fetch_carry(-(int)lane);
+    }
+
+    /*
+     * One wavefront step: this lane computes ref row i = t - lane over its K
+     * registers.  h_sh / f_sh are the neighbour's previous-step outputs.
+     */
+    SW_HD void step(const CellConsts &c, u32 t, u32 h_sh, u32 f_sh)
+    {
+        const int i = (int)t - (int)lane;
+        const u32 ra = ra_next;
+        const Carry cin = cin_next;
+        ra_next = fetch_ref(i + 1);
+        cin_next = fetch_carry(i + 1);
+
+        u32 h_in = h_sh, f_in = f_sh;
+        if (lane == 0) {
+            if (strip == 0) {                       /* column 0: sw.cpp:47-49 and the f[] seeds :22-26,38 */
+                const int b = bnd(c, i);
+                h_in = T::rep(c.bias + c.s_match + b);
+                f_in = T::rep(c.bias + b - c.s_go);
+            } else {
+                h_in = cin.h;
+                f_in = cin.f;
+            }
+        }
+
+        u32 diag = hleft;
+        hleft = h_in;
+        u32 f = f_in;
+        u32 f_km2 = f_in;
+#pragma unroll
+        for (int k = 0; k < K; k++) {
+            const u32 old = hm[k];
+            sw_cell<T>(c, ra, bq[k], diag, e[k], f, hm[k], acc[k]);
+            diag = old;
+            if (k == K - 2) f_km2 = f;
+        }
+        if (n == (u32)K) { h_out = hm[K - 1]; f_out = f; }
+        else             { h_out = K >= 2 ? hm[K >= 2 ? K - 2 : 0] : h_in; f_out = f_km2; }
+
+        if (active) {
+            if (lane == G - 1 && i >= 1 && i <= (int)own_rows) {
+                Carry *col = carry_cols + (size_t)(strip & 1u) * carry_rows;
+#if SW_ON_DEVICE
+                __stcg(reinterpret_cast<uint2 *>(col + i), make_uint2(h_out, f_out));
+#else
+                col[i].h = h_out; col[i].f = f_out;
+#endif
+            }
+            if (i == (int)tl0) {
+#pragma unroll
+                for (int k = 0; k < K; k++) lastrow[(size_t)slot * K + k] = hm[k];
+            }
+            if (T::PAIRS == 2 && i == (int)tl1) {
+#pragma unroll
+                for (int k = 0; k < K; k++) lastrow[(size_t)(nslots + slot) * K + k] = hm[k];
+            }
+        }
+        if (i == 0) reset_rows(c);
+
+        if ((t % T::SPW) == T::SPW - 1) {
+            u32 *dst = trace_cur + ((size_t)(t / T::SPW) * Q * 32u + wlane) * 4u;
+#pragma unroll
+            for (int q = 0; q < Q; q++) {
+                const u32 w0 = acc[4 * q];
+                const u32 w1 = 4 * q + 1 < K ? acc[4 * q + 1 < K ? 4 * q + 1 : 0] : 0u;
+                const u32 w2 = 4 * q + 2 < K ? acc[4 * q + 2 < K ? 4 * q + 2 : 0] : 0u;
+                const u32 w3 = 4 * q + 3 < K ? acc[4 * q + 3 < K ? 4 * q + 3 : 0] : 0u;
+#if SW_ON_DEVICE
+                __stcs(reinterpret_cast<uint4 *>(dst + (size_t)q * 128u), make_uint4(w0, w1, w2, w3));
+#else
+                u32 *p = dst + (size_t)q * 128u;
+                p[0] = w0; p[1] = w1; p[2] = w2; p[3] = w3;
+#endif
+            }
+        }
+    }
+};
+
+}  // namespace mglsw
+#endif
