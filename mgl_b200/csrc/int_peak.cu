@@ -1,0 +1,117 @@
+/*
+ * int_peak.cu -- measures the integer issue rates the roofline is quoted against
+ * (P_int is not in MEASURED_PEAKS.json and must be measured
+ * on the box).  Each kernel runs a long dependency-light stream of ONE
+ * instruction kind (8 interleaved chains per thread, inline PTX so ptxas keeps
+ * them), on every SM at full occupancy; ops/s = threads * ops per thread / time.
+ */
+#include <cuda_runtime.h>
+#include "sw_kernels.h"
+
+namespace mglsw {
+
+enum { PK_IADD3 = 0, PK_IMNMX, PK_VIMNMX3, PK_VIADDMNMX, PK_VIMNMX3_16, PK_VIADDMNMX_16, PK_LOP3, PK_SHF, PK_IMAD,
+       PK_MIX_ALU_IMAD, PK_PRMT, PK_COUNT };
+
+static const char *const kNames[PK_COUNT] = {
+    "iadd3_s32", "imnmx_s32", "vimnmx3_s32", "viaddmnmx_s32", "vimnmx3_u16x2", "viaddmnmx_u16x2", "lop3", "shf",
+    "imad_s32", "mix_iadd3+imad", "prmt"};
+
+template <int WHICH>
+__device__ __forceinline__ void op(unsigned &x, unsigned a, unsigned b)
+{
+    if (WHICH == PK_IADD3) asm volatile("add.u32 %0, %0, %1;" : "+r"(x) : "r"(a));
+    else if (WHICH == PK_IMNMX) asm volatile("max.s32 %0, %0, %1;" : "+r"(x) : "r"(a));
+    else if (WHICH == PK_VIMNMX3) x = (unsigned)__vimax3_s32((int)x, (int)a, (int)b);
+    else if (WHICH == PK_VIADDMNMX) x = (unsigned)__viaddmax_s32((int)x, (int)a, (int)b);
+    else if (WHICH == PK_VIMNMX3_16) x = __vimax3_u16x2(x, a, b);
+    else if (WHICH == PK_VIADDMNMX_16) x = __viaddmax_u16x2(x, a, b);
+    else if (WHICH == PK_LOP3) asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x) : "r"(a), "r"(b));
+    else if (WHICH == PK_SHF) asm volatile("shf.l.wrap.b32 %0, %0, %1, %2;" : "+r"(x) : "r"(a), "r"(b));
+    else if (WHICH == PK_IMAD) asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(x) : "r"(a), "r"(b));
+    else if (WHICH == PK_PRMT) asm volatile("prmt.b32 %0, %0, %1, %2;" : "+r"(x) : "r"(a), "r"(b));
+}
+
+template <int WHICH>
+__global__ void __launch_bounds__(256) peak_kernel(unsigned *out, unsigned a, unsigned b, int iters)
+{
+    unsigned x[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) x[k] = threadIdx.x * 8 + k + a;
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int r = 0; r < 8; r++) {
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                /* operands come from the other chains so ptxas cannot fold the stream */
+                if (WHICH == PK_MIX_ALU_IMAD) {
+                    if (k & 1) op<PK_IMAD>(x[k], x[(k + 2) & 7], x[(k + 4) & 7]);
+                    else op<PK_IADD3>(x[k], x[(k + 2) & 7], x[(k + 4) & 7]);
+                } else op<WHICH>(x[k], x[(k + 1) & 7], x[(k + 3) & 7]);
+            }
+        }
+    }
+    unsigned s = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) s ^= x[k];
+    if (s == 0x12345678u) out[0] = s;         /* keep the chains alive */
+}
+
+template <int WHICH>
+static cudaError_t time_one(int sms, double *ops_per_s)
+{
+    unsigned *out = nullptr;
+    cudaError_t e = cudaMalloc(&out, 64);
+    if (e != cudaSuccess) return e;
+    const int iters = 4096, blocks = sms * 8, threads = 256;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    peak_kernel<WHICH><<<blocks, threads>>>(out, 3u, 5u, 64);      /* warm-up */
+    float best = 1e30f;
+    for (int rep = 0; rep < 5; rep++) {
+        cudaEventRecord(e0);
+        peak_kernel<WHICH><<<blocks, threads>>>(out, 3u, 5u, iters);
+        cudaEventRecord(e1);
+        e = cudaEventSynchronize(e1);
+        if (e != cudaSuccess) break;
+        float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+        if (ms < best) best = ms;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    cudaFree(out);
+    if (e != cudaSuccess) return e;
+    *ops_per_s = (double)blocks * threads * (double)iters * 64.0 / (best * 1e-3);
+    return cudaGetLastError();
+}
+
+int int_peak_count() { return PK_COUNT; }
+const char *int_peak_name(int which) { return which >= 0 && which < PK_COUNT ? kNames[which] : "?"; }
+
+cudaError_t run_int_peak(int which, int device, double *ops_per_s, double *sm_mhz)
+{
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return e;
+    cudaDeviceProp prop;
+    e = cudaGetDeviceProperties(&prop, device);
+    if (e != cudaSuccess) return e;
+    int khz = 0;
+    cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, device);
+    if (sm_mhz) *sm_mhz = khz / 1000.0;
+    const int sms = prop.multiProcessorCount;
+    switch (which) {
+    case PK_IADD3: return time_one<PK_IADD3>(sms, ops_per_s);
+    case PK_IMNMX: return time_one<PK_IMNMX>(sms, ops_per_s);
+    case PK_VIMNMX3: return time_one<PK_VIMNMX3>(sms, ops_per_s);
+    case PK_VIADDMNMX: return time_one<PK_VIADDMNMX>(sms, ops_per_s);
+    case PK_VIMNMX3_16: return time_one<PK_VIMNMX3_16>(sms, ops_per_s);
+    case PK_VIADDMNMX_16: return time_one<PK_VIADDMNMX_16>(sms, ops_per_s);
+    case PK_LOP3: return time_one<PK_LOP3>(sms, ops_per_s);
+    case PK_SHF: return time_one<PK_SHF>(sms, ops_per_s);
+    case PK_IMAD: return time_one<PK_IMAD>(sms, ops_per_s);
+    case PK_MIX_ALU_IMAD: return time_one<PK_MIX_ALU_IMAD>(sms, ops_per_s);
+    case PK_PRMT: return time_one<PK_PRMT>(sms, ops_per_s);
+    }
+    return cudaErrorInvalidValue;
+}
+
+}  // namespace mglsw

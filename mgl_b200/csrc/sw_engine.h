@@ -1,0 +1,122 @@
+/*
+ * sw_engine.h -- host batcher, execution half: device buffers, streams and the
+ * chunk pipeline of one GPU.  (The planning half is sw_plan.h.)
+ *
+ * A batch is cut into chunks of consecutive pairs.  Each chunk is planned on
+ * the host while the previous one runs, its descriptors and the arena bytes it
+ * touches go up on the chunk's stream, then: fill launches (one per bucket) ->
+ * traceback -> scan -> compact -> results down.  Two work slots (trace, carry,
+ * scratch, result buffers) alternate so copies of one chunk overlap kernels of
+ * the other.  There is no CPU fallback: every error is returned to the caller.
+ */
+#ifndef MGL_B200_SW_ENGINE_H
+#define MGL_B200_SW_ENGINE_H
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "sw_plan.h"
+
+namespace mglsw {
+
+struct BatchIn {
+    int64_t n;
+    const uint8_t *arena;
+    uint64_t arena_bytes;
+    const uint64_t *ref_off, *alt_off;
+    const uint32_t *ref_len, *alt_len;
+    const int32_t *strategies;   /* per pair, or NULL */
+    int strategy;                /* used when strategies == NULL */
+    Scores scores;
+};
+
+struct BatchOut {
+    int32_t *offsets;            /* n */
+    uint64_t *cigar_start;       /* n + 1 */
+    uint32_t *ops;               /* ops_cap packed elements */
+    uint64_t ops_cap;
+    uint64_t ops_total;          /* out */
+};
+
+struct BatchStats {              /* filled by every run */
+    uint64_t cells, pairs, pairs_s16, pairs_s32;
+    uint64_t fill_launches, other_launches, chunks;
+    uint64_t trace_bytes;        /* trace words written * 4 */
+    uint64_t h2d_bytes, d2h_bytes;
+    double fill_ms, trace_ms, post_ms, device_ms;   /* device_ms etc. only from run_resident */
+};
+
+/* growable device / pinned buffers */
+struct DevBuf {
+    void *p = nullptr; size_t cap = 0;
+    cudaError_t reserve(size_t bytes);
+    void release();
+};
+struct PinBuf {
+    void *p = nullptr; size_t cap = 0;
+    cudaError_t reserve(size_t bytes);
+    void release();
+};
+
+/* a planned chunk with its descriptors on the device */
+struct ChunkDev {
+    ChunkPlan plan;
+    int64_t first = 0; u32 n = 0;
+    DevBuf units, pair_unit, ops_end, strategy;
+    PinBuf h_units, h_pair_unit, h_ops_end, h_strategy;
+    void release();
+};
+
+struct WorkSlot {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev_counts = nullptr, ev_done = nullptr;
+    DevBuf trace, carry, lastrow, scratch, offsets, n_ops, starts, ops;
+    PinBuf h_n_ops, h_total;
+    ChunkDev chunk;              /* descriptors of the chunk in flight (streaming mode) */
+    void release();
+};
+
+class Engine {
+public:
+    explicit Engine(int device);
+    ~Engine();
+    int device() const { return device_; }
+    const std::string &last_error() const { return err_; }
+
+    /* host buffers in, host buffers out; returns 0 or an MGL_SW_E_* code */
+    int align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats);
+
+    /* device-resident mode (bench `value`): upload + plan once, then time kernels only */
+    int prepare_resident(const BatchIn &in);
+    int run_resident(BatchStats *stats);
+    /* results of the last run_resident, brought down for checking */
+    int fetch_resident(BatchOut &out);
+    void drop_resident();
+
+    bool allow_s16 = true;
+    u32 chunk_pairs = 1u << 17;
+    u64 trace_budget_bytes = 0;  /* 0: derived from free memory */
+
+private:
+    int fail(int code, const std::string &msg);
+    int cuda_fail(cudaError_t e, const char *what);
+    int plan_next(const BatchIn &in, int64_t first, ChunkDev &cd);
+    int upload_chunk(const BatchIn &in, ChunkDev &cd, cudaStream_t st, bool upload_arena, BatchStats &bs);
+    int run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed);
+    int ensure_slot(WorkSlot &ws, const ChunkPlan &plan, u32 n);
+    u64 budget();
+
+    int device_;
+    std::string err_;
+    DevBuf arena_;
+    WorkSlot slots_[2];
+    std::vector<ChunkDev *> resident_;
+    std::vector<DevBuf> resident_results_;   /* per chunk: offsets | starts | ops kept on device */
+    Scores resident_scores_{};
+    cudaEvent_t tev_[4] = {nullptr, nullptr, nullptr, nullptr};
+};
+
+}  // namespace mglsw
+#endif

@@ -1,0 +1,49 @@
+/*
+ * sw_fill_kernel.cuh -- the CUDA fill kernel: one warp drives 32 FillLanes
+ * (sw_fill.h), 32 / G lane groups per warp, neighbours exchange (H, F) with
+ * __shfl_up_sync.  sm_100a only.
+ */
+#ifndef MGL_B200_SW_FILL_KERNEL_CUH
+#define MGL_B200_SW_FILL_KERNEL_CUH
+#include <cuda_runtime.h>
+#include "sw_config.h"
+#include "sw_fill.h"
+
+namespace mglsw {
+
+template <class T, int G, int K>
+__global__ void __launch_bounds__(MGLSW_FILL_THREADS)
+sw_fill_kernel(const __grid_constant__ FillArgs a, const u32 first_unit)
+{
+    const u32 warp = blockIdx.x * (MGLSW_FILL_THREADS / 32) + (threadIdx.x >> 5);
+    if (warp >= a.n_warps) return;
+    const u32 wl = threadIdx.x & 31u;
+    const UnitDesc &u = a.units[first_unit + warp * (32 / G) + wl / G];
+
+    FillLane<T, G, K> L;
+    L.setup(a, u, wl);
+    const u32 steps = u.rb_count * T::SPW;       /* same for every lane of the warp */
+    const u32 nstrips = u.nstrips;
+    for (u32 s = 0; s < nstrips; s++) {
+        L.strip_begin(a.c, s);
+        for (u32 t = 0; t < steps; t++) {
+            const u32 h = __shfl_up_sync(0xffffffffu, L.h_out, 1, G);
+            const u32 f = __shfl_up_sync(0xffffffffu, L.f_out, 1, G);
+            L.step(a.c, t, h, f);
+        }
+        __syncwarp();                            /* carry column of strip s is read by lane 0 in strip s + 1 */
+    }
+}
+
+template <class T, int G, int K>
+cudaError_t launch_fill(const FillArgs &a, u32 first_unit, cudaStream_t stream)
+{
+    const u32 wpb = MGLSW_FILL_THREADS / 32;
+    const u32 blocks = (a.n_warps + wpb - 1) / wpb;
+    if (blocks == 0) return cudaSuccess;
+    sw_fill_kernel<T, G, K><<<blocks, MGLSW_FILL_THREADS, 0, stream>>>(a, first_unit);
+    return cudaGetLastError();
+}
+
+}  // namespace mglsw
+#endif

@@ -1,0 +1,44 @@
+/*
+ * sw_kernels.h -- host-callable launchers of every CUDA kernel on the path.
+ * Implemented in sw_fill_inst_*.cu / sw_fill_dispatch.cu / sw_trace_kernel.cu /
+ * int_peak.cu; called by the engine (sw_engine.cu).
+ */
+#ifndef MGL_B200_SW_KERNELS_H
+#define MGL_B200_SW_KERNELS_H
+#include <cuda_runtime.h>
+#include "sw_fill.h"
+
+namespace mglsw {
+
+/* fill: fails with cudaErrorInvalidValue when no kernel was built for (kind, G, K) */
+cudaError_t launch_fill_any(int kind, int G, int K, const FillArgs &a, u32 first_unit, cudaStream_t stream);
+
+struct TraceArgs {
+    const UnitDesc *units;
+    const u32 *pair_unit;     /* per pair: unit * 2 + half                      */
+    const u64 *ops_end;       /* per pair: end of its scratch region (words)    */
+    const int *strategy;      /* per pair                                       */
+    const u32 *trace;
+    const Carry *carry;
+    const u32 *lastrow;
+    u32 *scratch;             /* CIGAR elements, written downwards from ops_end */
+    int *offsets;             /* out, per pair                                  */
+    u32 *n_ops;               /* out, per pair                                  */
+    u32 n_pairs;
+};
+cudaError_t launch_traceback(const TraceArgs &a, cudaStream_t stream);
+
+/* exclusive scan of n_ops -> starts[0..n], starts[n] = total (n <= 2^24) */
+cudaError_t launch_scan_counts(const u32 *n_ops, u32 *starts, u32 n, cudaStream_t stream);
+
+/* ops_out[starts[p] ..] = scratch[ops_end[p] - n_ops[p] .. ops_end[p]) */
+cudaError_t launch_compact(const u32 *scratch, const u64 *ops_end, const u32 *n_ops, const u32 *starts,
+                           u32 *ops_out, u32 n, cudaStream_t stream);
+
+/* integer-pipe microbenchmarks (int_peak.cu): ops per second of one instruction mix */
+cudaError_t run_int_peak(int which, int device, double *ops_per_s, double *sm_mhz);
+int int_peak_count();
+const char *int_peak_name(int which);
+
+}  // namespace mglsw
+#endif

@@ -1,0 +1,84 @@
+/*
+ * sw_trace_kernel.cu -- endpoint scan + traceback (one thread per pair), and
+ * the two small kernels that turn per-pair CIGAR scratch into one dense array.
+ * Replaces calculateCigar / calculateCigar_avx (sw.cpp:149-255, sw_avx.cpp:324-430).
+ */
+#include "sw_kernels.h"
+#include "sw_trace.h"
+#include "sw_config.h"
+
+namespace mglsw {
+
+__global__ void __launch_bounds__(128) sw_traceback_kernel(const __grid_constant__ TraceArgs a)
+{
+    const u32 p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= a.n_pairs) return;
+    const u32 pu = a.pair_unit[p];
+    const UnitDesc &u = a.units[pu >> 1];
+    const u32 half = pu & 1u;
+    const u32 G = (u.flags & UNIT_G32) ? MGLSW_G_LONG : MGLSW_G_SHORT;
+    u32 *end = a.scratch + a.ops_end[p];
+    PairResult r;
+    if (u.flags & UNIT_S32) r = traceback_pair<S32>(u, half, G, u.regs, a.trace, a.carry, a.lastrow, a.strategy[p], end);
+    else                    r = traceback_pair<S16x2>(u, half, G, u.regs, a.trace, a.carry, a.lastrow, a.strategy[p], end);
+    a.offsets[p] = r.offset;
+    a.n_ops[p] = r.n_ops;
+}
+
+cudaError_t launch_traceback(const TraceArgs &a, cudaStream_t stream)
+{
+    if (a.n_pairs == 0) return cudaSuccess;
+    sw_traceback_kernel<<<(a.n_pairs + 127) / 128, 128, 0, stream>>>(a);
+    return cudaGetLastError();
+}
+
+/* single-block exclusive scan: each thread owns a contiguous slice */
+__global__ void __launch_bounds__(1024) sw_scan_kernel(const u32 *__restrict__ n_ops, u32 *__restrict__ starts, u32 n)
+{
+    __shared__ u32 part[1024];
+    const u32 tid = threadIdx.x;
+    const u32 per = (n + 1023u) / 1024u;
+    const u32 lo = tid * per < n ? tid * per : n;
+    const u32 hi = lo + per < n ? lo + per : n;
+    u32 sum = 0;
+    for (u32 k = lo; k < hi; k++) sum += n_ops[k];
+    part[tid] = sum;
+    __syncthreads();
+    for (u32 d = 1; d < 1024; d <<= 1) {
+        const u32 v = tid >= d ? part[tid - d] : 0u;
+        __syncthreads();
+        part[tid] += v;
+        __syncthreads();
+    }
+    u32 run = part[tid] - sum;
+    for (u32 k = lo; k < hi; k++) { starts[k] = run; run += n_ops[k]; }
+    if (tid == 1023) starts[n] = part[1023];
+}
+
+cudaError_t launch_scan_counts(const u32 *n_ops, u32 *starts, u32 n, cudaStream_t stream)
+{
+    sw_scan_kernel<<<1, 1024, 0, stream>>>(n_ops, starts, n);
+    return cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(256) sw_compact_kernel(const u32 *__restrict__ scratch, const u64 *__restrict__ ops_end,
+                                                         const u32 *__restrict__ n_ops, const u32 *__restrict__ starts,
+                                                         u32 *__restrict__ ops_out, u32 n)
+{
+    const u32 p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    const u32 cnt = n_ops[p];
+    const u32 *src = scratch + (ops_end[p] - cnt);
+    u32 *dst = ops_out + starts[p];
+    for (u32 k = 0; k < cnt; k++) dst[k] = src[k];
+}
+
+cudaError_t launch_compact(const u32 *scratch, const u64 *ops_end, const u32 *n_ops, const u32 *starts,
+                           u32 *ops_out, u32 n, cudaStream_t stream)
+{
+    if (n == 0) return cudaSuccess;
+    sw_compact_kernel<<<(n + 255) / 256, 256, 0, stream>>>(scratch, ops_end, n_ops, starts, ops_out, n);
+    return cudaGetLastError();
+}
+
+}  // namespace mglsw
