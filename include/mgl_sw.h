@@ -1,0 +1,128 @@
+/*
+ * mgl_sw.h -- C ABI of libmgl_sw.so, the B200 Smith-Waterman affine-gap aligner.
+ *
+ * Drop-in boundary.  The library exports the three JNI symbols the reference's
+ * libmgl_sw.so exports (src/main/native/mgl_sw/
+ * com_microsoft_mgl_smithwaterman_MicrosoftSmithWaterman.h:15,23,31), unchanged
+ * in name, signature and behaviour, and adds underneath them the batched entry
+ * points below, which are what reaches the GPU.  Nothing here takes or returns
+ * a torch / CUDA type: plain pointers and sizes only.
+ *
+ * Semantics of one alignment are the reference's (sw.cpp:5-272): scores are
+ * sign-normalised the way alignNative does (...SmithWaterman.cpp:52-55),
+ * strategy is one of 1 SOFTCLIP, 2 INDEL, 4 LEADING_INDEL, 8 IGNORE
+ * (sw_common.h:22-25), the result is the alignment offset and the CIGAR.
+ * There is NO CPU fallback: without a usable B200 every call returns an error.
+ */
+#ifndef MGL_SW_H
+#define MGL_SW_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MGL_SW_API __attribute__((visibility("default")))
+
+/* status codes */
+#define MGL_SW_OK               0
+#define MGL_SW_E_INVALID       -1   /* NULL / negative / inconsistent argument                 */
+#define MGL_SW_E_SCORES        -2   /* score set outside what 32-bit cells can represent       */
+#define MGL_SW_E_PAIR          -3   /* empty or over-long sequence (the reference leaves empty
+                                       inputs undefined, ...SmithWaterman.cpp:48-49)           */
+#define MGL_SW_E_CUDA          -4   /* CUDA runtime error; see mgl_sw_last_error               */
+#define MGL_SW_E_OPS_CAPACITY  -5   /* ops_out too small; *ops_total holds the needed count    */
+#define MGL_SW_E_NO_DEVICE     -6   /* no CUDA device / extension unusable                     */
+
+/* overhang strategies, sw_common.h:22-25 */
+#define MGL_SW_SOFTCLIP       1
+#define MGL_SW_INDEL          2
+#define MGL_SW_LEADING_INDEL  4
+#define MGL_SW_IGNORE         8
+
+/* packed CIGAR element: (length << 4) | op, op in BAM numbering */
+#define MGL_SW_OP_M 0
+#define MGL_SW_OP_I 1
+#define MGL_SW_OP_D 2
+#define MGL_SW_OP_S 4
+
+typedef struct mgl_sw_handle mgl_sw_handle;
+
+/* One batch.  Sequences are raw bytes (compared for equality as bytes, sw.cpp:55) in one arena. */
+typedef struct mgl_sw_batch {
+    int64_t n;                    /* pairs                                                   */
+    const uint8_t *arena;         /* sequence bytes (pinned memory makes the copy asynchronous) */
+    uint64_t arena_bytes;
+    const uint64_t *ref_off;      /* n: byte offset of each ref (target)                     */
+    const uint32_t *ref_len;      /* n                                                       */
+    const uint64_t *alt_off;      /* n: byte offset of each alt (query)                      */
+    const uint32_t *alt_len;      /* n                                                       */
+    const int32_t *strategies;    /* n, or NULL: `strategy` applies to every pair            */
+    int32_t strategy;
+    int32_t match, mismatch, gap_open, gap_extend;   /* as GATK passes them, any sign         */
+} mgl_sw_batch;
+
+typedef struct mgl_sw_result {
+    int32_t *offsets;             /* n: alignment offsets (alignNative's return value)        */
+    uint64_t *cigar_start;        /* n + 1: pair p's elements are ops[cigar_start[p] .. cigar_start[p+1]) */
+    uint32_t *ops;                /* ops_cap packed elements, left to right                   */
+    uint64_t ops_cap;
+    uint64_t ops_total;           /* out: elements produced (needed, on MGL_SW_E_OPS_CAPACITY) */
+} mgl_sw_result;
+
+typedef struct mgl_sw_stats {
+    uint64_t cells, pairs, pairs_s16, pairs_s32;
+    uint64_t fill_launches, other_launches, chunks;
+    uint64_t trace_bytes, h2d_bytes, d2h_bytes;
+    double fill_ms, trace_ms, post_ms, device_ms;
+} mgl_sw_stats;
+
+/* lifecycle: one handle drives one GPU; calls on one handle are serialised internally */
+MGL_SW_API int mgl_sw_create(int device, mgl_sw_handle **out);
+MGL_SW_API void mgl_sw_destroy(mgl_sw_handle *h);
+MGL_SW_API const char *mgl_sw_last_error(mgl_sw_handle *h);
+MGL_SW_API int mgl_sw_device_count(void);
+MGL_SW_API const char *mgl_sw_version(void);
+
+/* tuning knobs: "allow_s16" 0/1, "chunk_pairs", "trace_budget_mb" */
+MGL_SW_API int mgl_sw_set_option(mgl_sw_handle *h, const char *name, int64_t value);
+
+/* the batched aligner: host buffers in, host buffers out */
+MGL_SW_API int mgl_sw_align_batch(mgl_sw_handle *h, const mgl_sw_batch *batch, mgl_sw_result *result, mgl_sw_stats *stats);
+
+/* device-resident variant for kernel timing: inputs uploaded once, kernels timed with CUDA events */
+MGL_SW_API int mgl_sw_resident_prepare(mgl_sw_handle *h, const mgl_sw_batch *batch);
+MGL_SW_API int mgl_sw_resident_run(mgl_sw_handle *h, mgl_sw_stats *stats);
+MGL_SW_API int mgl_sw_resident_fetch(mgl_sw_handle *h, mgl_sw_result *result);
+MGL_SW_API void mgl_sw_resident_drop(mgl_sw_handle *h);
+
+/* one pair, text CIGAR, exactly what alignNative produces (batch of one on a process-wide handle) */
+MGL_SW_API int mgl_sw_align_one(const uint8_t *ref, int32_t ref_len, const uint8_t *alt, int32_t alt_len,
+                                int32_t match, int32_t mismatch, int32_t gap_open, int32_t gap_extend,
+                                int32_t strategy, char *cigar_out, int32_t cigar_cap, int32_t *cigar_len,
+                                int32_t *offset);
+
+/* packed elements -> "3M2D5M" (sw.cpp:251-252); returns characters written or -1 */
+MGL_SW_API int mgl_sw_format_cigar(const uint32_t *ops, int64_t n_ops, char *out, int64_t out_cap);
+
+/* pinned host memory for arenas / results */
+MGL_SW_API void *mgl_sw_host_alloc(uint64_t bytes);
+MGL_SW_API void mgl_sw_host_free(void *p);
+
+/* planning only (no GPU needed): how a batch would be bucketed; used by tests and tools */
+MGL_SW_API int mgl_sw_plan_summary(const mgl_sw_batch *batch, int allow_s16, uint64_t *out8);
+
+/* deterministic synthetic pairs of BASELINE.json configs 2..5 (sw_synth.cpp): sizes first, then bytes */
+MGL_SW_API int mgl_sw_synth_sizes(int config, uint64_t seed, uint64_t first, int64_t n, uint32_t *ref_len, uint32_t *alt_len);
+MGL_SW_API int mgl_sw_synth_fill(int config, uint64_t seed, uint64_t first, int64_t n, const uint64_t *ref_off,
+                                 const uint64_t *alt_off, uint8_t *arena);
+
+/* integer issue-rate microbenchmarks for the roofline denominator */
+MGL_SW_API int mgl_sw_int_peak_count(void);
+MGL_SW_API const char *mgl_sw_int_peak_name(int which);
+MGL_SW_API int mgl_sw_int_peak(int device, int which, double *ops_per_s, double *sm_mhz);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,260 @@
+/*
+ * sw_capi.cpp -- the extern "C" surface declared in include/mgl_sw.h.
+ * Thin: argument checks, locking, and translation to the engine.
+ */
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/mgl_sw.h"
+#include "sw_engine.h"
+#include "sw_kernels.h"
+
+using namespace mglsw;
+
+struct mgl_sw_handle {
+    Engine *engine;
+    std::mutex mu;
+    std::string err;
+};
+
+namespace {
+
+int to_batch(const mgl_sw_batch *b, BatchIn &in)
+{
+    if (!b || b->n < 0) return MGL_SW_E_INVALID;
+    in.n = b->n; in.arena = b->arena; in.arena_bytes = b->arena_bytes;
+    in.ref_off = b->ref_off; in.alt_off = b->alt_off; in.ref_len = b->ref_len; in.alt_len = b->alt_len;
+    in.strategies = b->strategies; in.strategy = b->strategy;
+    in.scores = normalise_scores(b->match, b->mismatch, b->gap_open, b->gap_extend);
+    return MGL_SW_OK;
+}
+
+void to_stats(const BatchStats &s, mgl_sw_stats *o)
+{
+    if (!o) return;
+    o->cells = s.cells; o->pairs = s.pairs; o->pairs_s16 = s.pairs_s16; o->pairs_s32 = s.pairs_s32;
+    o->fill_launches = s.fill_launches; o->other_launches = s.other_launches; o->chunks = s.chunks;
+    o->trace_bytes = s.trace_bytes; o->h2d_bytes = s.h2d_bytes; o->d2h_bytes = s.d2h_bytes;
+    o->fill_ms = s.fill_ms; o->trace_ms = s.trace_ms; o->post_ms = s.post_ms; o->device_ms = s.device_ms;
+}
+
+mgl_sw_handle *g_default = nullptr;
+std::once_flag g_default_once;
+int g_default_rc = MGL_SW_E_NO_DEVICE;
+
+void make_default()
+{
+    const char *env = std::getenv("MGL_SW_DEVICE");
+    g_default_rc = mgl_sw_create(env ? std::atoi(env) : 0, &g_default);
+}
+
+}  // namespace
+
+extern "C" {
+
+int mgl_sw_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+const char *mgl_sw_version(void) { return "mgl_sw_b200 0.1 (sm_100a)"; }
+
+int mgl_sw_create(int device, mgl_sw_handle **out)
+{
+    if (!out) return MGL_SW_E_INVALID;
+    *out = nullptr;
+    int n = mgl_sw_device_count();
+    if (n <= 0 || device < 0 || device >= n) return MGL_SW_E_NO_DEVICE;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return MGL_SW_E_NO_DEVICE;
+    if (prop.major != 10) {       /* the kernels are sm_100a only: refuse rather than fall back */
+        std::fprintf(stderr, "mgl_sw: device %d is sm_%d%d, this library is built for sm_100a only\n", device, prop.major, prop.minor);
+        return MGL_SW_E_NO_DEVICE;
+    }
+    mgl_sw_handle *h = new (std::nothrow) mgl_sw_handle();
+    if (!h) return MGL_SW_E_INVALID;
+    h->engine = new Engine(device);
+    *out = h;
+    return MGL_SW_OK;
+}
+
+void mgl_sw_destroy(mgl_sw_handle *h)
+{
+    if (!h) return;
+    delete h->engine;
+    delete h;
+}
+
+const char *mgl_sw_last_error(mgl_sw_handle *h) { return h ? h->engine->last_error().c_str() : "no handle"; }
+
+int mgl_sw_set_option(mgl_sw_handle *h, const char *name, int64_t value)
+{
+    if (!h || !name) return MGL_SW_E_INVALID;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (!std::strcmp(name, "allow_s16")) h->engine->allow_s16 = value != 0;
+    else if (!std::strcmp(name, "chunk_pairs")) { if (value < 1 || value > (1 << 22)) return MGL_SW_E_INVALID; h->engine->chunk_pairs = (u32)value; }
+    else if (!std::strcmp(name, "trace_budget_mb")) { if (value < 0) return MGL_SW_E_INVALID; h->engine->trace_budget_bytes = (u64)value << 20; }
+    else return MGL_SW_E_INVALID;
+    return MGL_SW_OK;
+}
+
+int mgl_sw_align_batch(mgl_sw_handle *h, const mgl_sw_batch *batch, mgl_sw_result *result, mgl_sw_stats *stats)
+{
+    if (!h || !result) return MGL_SW_E_INVALID;
+    BatchIn in;
+    int rc = to_batch(batch, in);
+    if (rc != MGL_SW_OK) return rc;
+    BatchOut out;
+    out.offsets = result->offsets; out.cigar_start = result->cigar_start; out.ops = result->ops;
+    out.ops_cap = result->ops_cap; out.ops_total = 0;
+    BatchStats bs;
+    std::memset(&bs, 0, sizeof bs);
+    std::lock_guard<std::mutex> lk(h->mu);
+    rc = h->engine->align_batch(in, out, &bs);
+    result->ops_total = out.ops_total;
+    to_stats(bs, stats);
+    return rc;
+}
+
+int mgl_sw_resident_prepare(mgl_sw_handle *h, const mgl_sw_batch *batch)
+{
+    if (!h) return MGL_SW_E_INVALID;
+    BatchIn in;
+    int rc = to_batch(batch, in);
+    if (rc != MGL_SW_OK) return rc;
+    std::lock_guard<std::mutex> lk(h->mu);
+    return h->engine->prepare_resident(in);
+}
+
+int mgl_sw_resident_run(mgl_sw_handle *h, mgl_sw_stats *stats)
+{
+    if (!h) return MGL_SW_E_INVALID;
+    BatchStats bs;
+    std::memset(&bs, 0, sizeof bs);
+    std::lock_guard<std::mutex> lk(h->mu);
+    int rc = h->engine->run_resident(&bs);
+    to_stats(bs, stats);
+    return rc;
+}
+
+int mgl_sw_resident_fetch(mgl_sw_handle *h, mgl_sw_result *result)
+{
+    if (!h || !result || !result->offsets || !result->cigar_start) return MGL_SW_E_INVALID;
+    BatchOut out;
+    out.offsets = result->offsets; out.cigar_start = result->cigar_start; out.ops = result->ops;
+    out.ops_cap = result->ops_cap; out.ops_total = 0;
+    std::lock_guard<std::mutex> lk(h->mu);
+    int rc = h->engine->fetch_resident(out);
+    result->ops_total = out.ops_total;
+    return rc;
+}
+
+void mgl_sw_resident_drop(mgl_sw_handle *h)
+{
+    if (!h) return;
+    std::lock_guard<std::mutex> lk(h->mu);
+    h->engine->drop_resident();
+}
+
+int mgl_sw_format_cigar(const uint32_t *ops, int64_t n_ops, char *out, int64_t out_cap)
+{
+    static const char kOp[] = "MIDNSHP=X";
+    int64_t pos = 0;
+    for (int64_t k = 0; k < n_ops; k++) {
+        char tmp[16];
+        const uint32_t op = ops[k] & 15u;
+        const int len = std::snprintf(tmp, sizeof tmp, "%u%c", ops[k] >> 4, op < 9 ? kOp[op] : '?');
+        if (pos + len > out_cap) return -1;
+        std::memcpy(out + pos, tmp, (size_t)len);
+        pos += len;
+    }
+    if (pos < out_cap) out[pos] = 0;
+    return (int)pos;
+}
+
+int mgl_sw_align_one(const uint8_t *ref, int32_t ref_len, const uint8_t *alt, int32_t alt_len,
+                     int32_t match, int32_t mismatch, int32_t gap_open, int32_t gap_extend,
+                     int32_t strategy, char *cigar_out, int32_t cigar_cap, int32_t *cigar_len, int32_t *offset)
+{
+    if (!ref || !alt || ref_len <= 0 || alt_len <= 0 || !cigar_out || !offset) return MGL_SW_E_INVALID;
+    std::call_once(g_default_once, make_default);
+    if (g_default_rc != MGL_SW_OK || !g_default) return MGL_SW_E_NO_DEVICE;
+    std::vector<uint8_t> arena((size_t)ref_len + alt_len);
+    std::memcpy(arena.data(), ref, (size_t)ref_len);
+    std::memcpy(arena.data() + ref_len, alt, (size_t)alt_len);
+    const uint64_t ro = 0, ao = (uint64_t)ref_len;
+    const uint32_t rl = (uint32_t)ref_len, al = (uint32_t)alt_len;
+    mgl_sw_batch b;
+    std::memset(&b, 0, sizeof b);
+    b.n = 1; b.arena = arena.data(); b.arena_bytes = arena.size();
+    b.ref_off = &ro; b.ref_len = &rl; b.alt_off = &ao; b.alt_len = &al;
+    b.strategy = strategy; b.match = match; b.mismatch = mismatch; b.gap_open = gap_open; b.gap_extend = gap_extend;
+    std::vector<uint32_t> ops((size_t)ref_len + alt_len + 4);
+    int32_t off = 0;
+    uint64_t cs[2] = {0, 0};
+    mgl_sw_result r;
+    r.offsets = &off; r.cigar_start = cs; r.ops = ops.data(); r.ops_cap = ops.size(); r.ops_total = 0;
+    const int rc = mgl_sw_align_batch(g_default, &b, &r, nullptr);
+    if (rc != MGL_SW_OK) return rc;
+    const int len = mgl_sw_format_cigar(ops.data(), (int64_t)r.ops_total, cigar_out, cigar_cap);
+    if (len < 0) return MGL_SW_E_OPS_CAPACITY;
+    if (cigar_len) *cigar_len = len;
+    *offset = off;
+    return MGL_SW_OK;
+}
+
+void *mgl_sw_host_alloc(uint64_t bytes)
+{
+    void *p = nullptr;
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return p;
+}
+
+void mgl_sw_host_free(void *p) { if (p) cudaFreeHost(p); }
+
+int mgl_sw_plan_summary(const mgl_sw_batch *batch, int allow_s16, uint64_t *out8)
+{
+    BatchIn in;
+    int rc = to_batch(batch, in);
+    if (rc != MGL_SW_OK || !out8) return MGL_SW_E_INVALID;
+    std::vector<PairIn> pairs((size_t)in.n);
+    for (int64_t k = 0; k < in.n; k++) {
+        pairs[(size_t)k].ref_off = in.ref_off[k]; pairs[(size_t)k].alt_off = in.alt_off[k];
+        pairs[(size_t)k].tl = in.ref_len[k]; pairs[(size_t)k].ql = in.alt_len[k];
+        pairs[(size_t)k].strategy = in.strategies ? in.strategies[k] : in.strategy;
+    }
+    ChunkPlan plan;
+    const PlanStatus ps = plan_chunk(pairs.data(), (u32)in.n, in.scores, allow_s16 != 0, plan);
+    if (ps == PLAN_BAD_SCORES) return MGL_SW_E_SCORES;
+    if (ps == PLAN_BAD_PAIR) return MGL_SW_E_PAIR;
+    uint64_t n16 = 0, n32 = 0, padded = 0;
+    for (const UnitDesc &u : plan.units) {
+        if (!(u.flags & UNIT_ACTIVE)) continue;
+        const uint64_t k = 1 + (u.pair[1] != NO_PAIR ? 1 : 0);
+        if (u.flags & UNIT_S32) n32 += k; else n16 += k;
+    }
+    for (const Launch &L : plan.launches) padded += (uint64_t)L.n_units;
+    out8[0] = plan.launches.size(); out8[1] = plan.units.size(); out8[2] = n16; out8[3] = n32;
+    out8[4] = plan.trace_words; out8[5] = plan.cells; out8[6] = plan.scratch_words; out8[7] = padded;
+    return MGL_SW_OK;
+}
+
+int mgl_sw_int_peak_count(void) { return int_peak_count(); }
+const char *mgl_sw_int_peak_name(int which) { return int_peak_name(which); }
+int mgl_sw_int_peak(int device, int which, double *ops_per_s, double *sm_mhz)
+{
+    if (!ops_per_s) return MGL_SW_E_INVALID;
+    if (mgl_sw_device_count() <= 0) return MGL_SW_E_NO_DEVICE;
+    return run_int_peak(which, device, ops_per_s, sm_mhz) == cudaSuccess ? MGL_SW_OK : MGL_SW_E_CUDA;
+}
+
+}  // extern "C"

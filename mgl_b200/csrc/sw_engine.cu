@@ -1,0 +1,437 @@
+/* sw_engine.cu -- see sw_engine.h. */
+#include "sw_engine.h"
+
+#include <algorithm>
+#include <cstring>
+
+#include "../../include/mgl_sw.h"
+#include "sw_cell.h"
+#include "sw_kernels.h"
+#include "sw_layout.h"
+
+namespace mglsw {
+
+/* ---------------------------------------------------------------- buffers */
+
+cudaError_t DevBuf::reserve(size_t bytes)
+{
+    if (bytes <= cap) return cudaSuccess;
+    release();
+    size_t want = bytes + bytes / 8 + 256;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e != cudaSuccess) { p = nullptr; cap = 0; return e; }
+    cap = want;
+    return cudaSuccess;
+}
+void DevBuf::release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+
+cudaError_t PinBuf::reserve(size_t bytes)
+{
+    if (bytes <= cap) return cudaSuccess;
+    release();
+    size_t want = bytes + bytes / 8 + 256;
+    cudaError_t e = cudaHostAlloc(&p, want, cudaHostAllocDefault);
+    if (e != cudaSuccess) { p = nullptr; cap = 0; return e; }
+    cap = want;
+    return cudaSuccess;
+}
+void PinBuf::release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+
+void ChunkDev::release()
+{
+    units.release(); pair_unit.release(); ops_end.release(); strategy.release();
+    h_units.release(); h_pair_unit.release(); h_ops_end.release(); h_strategy.release();
+}
+
+void WorkSlot::release()
+{
+    trace.release(); carry.release(); lastrow.release(); scratch.release();
+    offsets.release(); n_ops.release(); starts.release(); ops.release();
+    h_n_ops.release(); h_total.release();
+    chunk.release();
+    if (ev_counts) cudaEventDestroy(ev_counts);
+    if (ev_done) cudaEventDestroy(ev_done);
+    if (stream) cudaStreamDestroy(stream);
+    ev_counts = ev_done = nullptr; stream = nullptr;
+}
+
+/* ---------------------------------------------------------------- engine */
+
+Engine::Engine(int device) : device_(device)
+{
+    if (cudaSetDevice(device_) != cudaSuccess) { err_ = "cudaSetDevice failed"; return; }
+    for (auto &s : slots_) {
+        cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking);
+        cudaEventCreateWithFlags(&s.ev_counts, cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&s.ev_done, cudaEventDisableTiming);
+    }
+    for (auto &e : tev_) cudaEventCreate(&e);
+}
+
+Engine::~Engine()
+{
+    cudaSetDevice(device_);
+    drop_resident();
+    for (auto &s : slots_) s.release();
+    for (auto &e : tev_) if (e) cudaEventDestroy(e);
+    arena_.release();
+}
+
+int Engine::fail(int code, const std::string &msg) { err_ = msg; return code; }
+
+int Engine::cuda_fail(cudaError_t e, const char *what)
+{
+    err_ = std::string(what) + ": " + cudaGetErrorString(e);
+    cudaGetLastError();
+    return MGL_SW_E_CUDA;
+}
+
+u64 Engine::budget()
+{
+    if (trace_budget_bytes) return trace_budget_bytes;
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return 4ull << 30;
+    u64 b = (u64)(free_b * 0.30);                 /* two slots + descriptors stay well inside HBM */
+    return std::max<u64>(std::min<u64>(b, 48ull << 30), 256ull << 20);
+}
+
+/*
+ * Plan the chunk that starts at pair `first`: at most chunk_pairs pairs, and
+ * as many as keep the estimated trace (0.5 B per padded cell) inside the budget.
+ */
+int Engine::plan_next(const BatchIn &in, int64_t first, ChunkDev &cd)
+{
+    const u64 limit = budget();
+    int64_t n = std::min<int64_t>(in.n - first, chunk_pairs);
+    u64 est = 0;
+    int64_t take = 0;
+    for (; take < n; take++) {
+        const u64 tl = in.ref_len[first + take], ql = in.alt_len[first + take];
+        const u64 bytes = (tl + 40) * (ql + 32) / 2 * 5 / 4;     /* padded rows/cols + 25 % */
+        if (take > 0 && est + bytes > limit) break;
+        est += bytes;
+    }
+    std::vector<PairIn> pairs((size_t)take);
+    for (int64_t k = 0; k < take; k++) {
+        PairIn &p = pairs[(size_t)k];
+        p.ref_off = in.ref_off[first + k]; p.alt_off = in.alt_off[first + k];
+        p.tl = in.ref_len[first + k]; p.ql = in.alt_len[first + k];
+        p.strategy = in.strategies ? in.strategies[first + k] : in.strategy;
+        if (p.ref_off + p.tl > in.arena_bytes || p.alt_off + p.ql > in.arena_bytes)
+            return fail(MGL_SW_E_INVALID, "pair " + std::to_string(first + k) + " lies outside the arena");
+    }
+    const PlanStatus ps = plan_chunk(pairs.data(), (u32)take, in.scores, allow_s16, cd.plan);
+    if (ps == PLAN_BAD_SCORES) return fail(MGL_SW_E_SCORES, "score set out of range");
+    if (ps == PLAN_BAD_PAIR) return fail(MGL_SW_E_PAIR, "empty or over-long sequence in batch");
+    cd.first = first;
+    cd.n = (u32)take;
+
+    /* stage descriptors in pinned memory so the uploads are asynchronous */
+    cudaError_t e;
+    const size_t nu = cd.plan.units.size();
+    if ((e = cd.h_units.reserve(nu * sizeof(UnitDesc))) != cudaSuccess) return cuda_fail(e, "pinned alloc");
+    if ((e = cd.h_pair_unit.reserve(take * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "pinned alloc");
+    if ((e = cd.h_ops_end.reserve(take * sizeof(u64))) != cudaSuccess) return cuda_fail(e, "pinned alloc");
+    if ((e = cd.h_strategy.reserve(take * sizeof(int))) != cudaSuccess) return cuda_fail(e, "pinned alloc");
+    std::memcpy(cd.h_units.p, cd.plan.units.data(), nu * sizeof(UnitDesc));
+    std::memcpy(cd.h_pair_unit.p, cd.plan.pair_unit.data(), take * sizeof(u32));
+    std::memcpy(cd.h_ops_end.p, cd.plan.ops_end.data(), take * sizeof(u64));
+    int *st = (int *)cd.h_strategy.p;
+    for (int64_t k = 0; k < take; k++) st[k] = pairs[(size_t)k].strategy;
+    return MGL_SW_OK;
+}
+
+int Engine::upload_chunk(const BatchIn &in, ChunkDev &cd, cudaStream_t st, bool upload_arena, BatchStats &bs)
+{
+    cudaError_t e;
+    const size_t nu = cd.plan.units.size(), n = cd.n;
+    if ((e = cd.units.reserve(nu * sizeof(UnitDesc))) != cudaSuccess) return cuda_fail(e, "cudaMalloc units");
+    if ((e = cd.pair_unit.reserve(n * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc");
+    if ((e = cd.ops_end.reserve(n * sizeof(u64))) != cudaSuccess) return cuda_fail(e, "cudaMalloc");
+    if ((e = cd.strategy.reserve(n * sizeof(int))) != cudaSuccess) return cuda_fail(e, "cudaMalloc");
+    if ((e = cudaMemcpyAsync(cd.units.p, cd.h_units.p, nu * sizeof(UnitDesc), cudaMemcpyHostToDevice, st)) != cudaSuccess) return cuda_fail(e, "H2D units");
+    if ((e = cudaMemcpyAsync(cd.pair_unit.p, cd.h_pair_unit.p, n * sizeof(u32), cudaMemcpyHostToDevice, st)) != cudaSuccess) return cuda_fail(e, "H2D");
+    if ((e = cudaMemcpyAsync(cd.ops_end.p, cd.h_ops_end.p, n * sizeof(u64), cudaMemcpyHostToDevice, st)) != cudaSuccess) return cuda_fail(e, "H2D");
+    if ((e = cudaMemcpyAsync(cd.strategy.p, cd.h_strategy.p, n * sizeof(int), cudaMemcpyHostToDevice, st)) != cudaSuccess) return cuda_fail(e, "H2D");
+    bs.h2d_bytes += nu * sizeof(UnitDesc) + n * (sizeof(u32) + sizeof(u64) + sizeof(int));
+    if (upload_arena) {
+        /* the byte range of the arena this chunk touches */
+        u64 lo = ~0ull, hi = 0;
+        for (size_t k = 0; k < n; k++) {
+            const int64_t p = cd.first + (int64_t)k;
+            lo = std::min<u64>(lo, std::min(in.ref_off[p], in.alt_off[p]));
+            hi = std::max<u64>(hi, std::max(in.ref_off[p] + in.ref_len[p], in.alt_off[p] + in.alt_len[p]));
+        }
+        if (hi > lo) {
+            if ((e = cudaMemcpyAsync((uint8_t *)arena_.p + lo, in.arena + lo, hi - lo, cudaMemcpyHostToDevice, st)) != cudaSuccess)
+                return cuda_fail(e, "H2D arena");
+            bs.h2d_bytes += hi - lo;
+        }
+    }
+    return MGL_SW_OK;
+}
+
+int Engine::ensure_slot(WorkSlot &ws, const ChunkPlan &plan, u32 n)
+{
+    cudaError_t e;
+    if ((e = ws.trace.reserve((plan.trace_words + 4) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc trace");
+    if ((e = ws.carry.reserve((plan.carry_entries + 1) * sizeof(Carry))) != cudaSuccess) return cuda_fail(e, "cudaMalloc carry");
+    if ((e = ws.lastrow.reserve((plan.lastrow_words + 1) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc lastrow");
+    if ((e = ws.scratch.reserve((plan.scratch_words + 1) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc scratch");
+    if ((e = ws.offsets.reserve((size_t)n * sizeof(int))) != cudaSuccess) return cuda_fail(e, "cudaMalloc");
+    if ((e = ws.n_ops.reserve((size_t)n * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc");
+    if ((e = ws.starts.reserve(((size_t)n + 1) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc");
+    if ((e = ws.ops.reserve((plan.scratch_words + 1) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc ops");
+    if ((e = ws.h_n_ops.reserve(((size_t)n + 1) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "pinned alloc");
+    return MGL_SW_OK;
+}
+
+/* fill launches -> traceback -> scan -> compact, all on the slot's stream */
+int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed)
+{
+    cudaError_t e;
+    cudaStream_t st = ws.stream;
+    const Scores &sc = resident_scores_;
+    if (timed) cudaEventRecord(tev_[0], st);
+    for (const Launch &L : cd.plan.launches) {
+        FillArgs a;
+        a.arena = (const uint8_t *)arena_.p;
+        a.units = (const UnitDesc *)cd.units.p;
+        a.trace = (u32 *)ws.trace.p;
+        a.carry = (Carry *)ws.carry.p;
+        a.lastrow = (u32 *)ws.lastrow.p;
+        a.n_warps = L.n_warps;
+        a.c = L.kind == KIND_S16X2 ? make_consts<S16x2>(sc, cd.plan.s16_bias) : make_consts<S32>(sc, 0);
+        if ((e = launch_fill_any(L.kind, L.G, L.K, a, L.first_unit, st)) != cudaSuccess)
+            return cuda_fail(e, "fill launch (is a kernel built for this kind/G/K?)");
+        bs.fill_launches++;
+        if (L.kind == KIND_S16X2) bs.pairs_s16 += 0; /* counted below */
+    }
+    if (timed) cudaEventRecord(tev_[1], st);
+    TraceArgs t;
+    t.units = (const UnitDesc *)cd.units.p;
+    t.pair_unit = (const u32 *)cd.pair_unit.p;
+    t.ops_end = (const u64 *)cd.ops_end.p;
+    t.strategy = (const int *)cd.strategy.p;
+    t.trace = (const u32 *)ws.trace.p;
+    t.carry = (const Carry *)ws.carry.p;
+    t.lastrow = (const u32 *)ws.lastrow.p;
+    t.scratch = (u32 *)ws.scratch.p;
+    t.offsets = (int *)ws.offsets.p;
+    t.n_ops = (u32 *)ws.n_ops.p;
+    t.n_pairs = cd.n;
+    if ((e = launch_traceback(t, st)) != cudaSuccess) return cuda_fail(e, "traceback launch");
+    if (timed) cudaEventRecord(tev_[2], st);
+    if ((e = launch_scan_counts((const u32 *)ws.n_ops.p, (u32 *)ws.starts.p, cd.n, st)) != cudaSuccess) return cuda_fail(e, "scan launch");
+    if ((e = launch_compact((const u32 *)ws.scratch.p, (const u64 *)cd.ops_end.p, (const u32 *)ws.n_ops.p,
+                            (const u32 *)ws.starts.p, (u32 *)ws.ops.p, cd.n, st)) != cudaSuccess) return cuda_fail(e, "compact launch");
+    if (timed) cudaEventRecord(tev_[3], st);
+    bs.other_launches += 3;
+    bs.chunks++;
+    bs.cells += cd.plan.cells;
+    bs.pairs += cd.n;
+    bs.trace_bytes += cd.plan.trace_words * 4;
+    for (const UnitDesc &u : cd.plan.units) {
+        if (!(u.flags & UNIT_ACTIVE)) continue;
+        const u64 k = 1 + (u.pair[1] != NO_PAIR ? 1 : 0);
+        if (u.flags & UNIT_S32) bs.pairs_s32 += k; else bs.pairs_s16 += k;
+    }
+    if (timed) {
+        if ((e = cudaEventSynchronize(tev_[3])) != cudaSuccess) return cuda_fail(e, "chunk sync");
+        float a = 0, b = 0, c = 0;
+        cudaEventElapsedTime(&a, tev_[0], tev_[1]);
+        cudaEventElapsedTime(&b, tev_[1], tev_[2]);
+        cudaEventElapsedTime(&c, tev_[2], tev_[3]);
+        bs.fill_ms += a; bs.trace_ms += b; bs.post_ms += c; bs.device_ms += a + b + c;
+    }
+    return MGL_SW_OK;
+}
+
+/* ---------------------------------------------------------------- streaming mode */
+
+namespace {
+struct InFlight { bool busy = false; int64_t first = 0; u32 n = 0; };
+}
+
+int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
+{
+    BatchStats bs;
+    std::memset(&bs, 0, sizeof bs);
+    if (in.n < 0 || (in.n > 0 && (!in.arena || !in.ref_off || !in.alt_off || !in.ref_len || !in.alt_len)))
+        return fail(MGL_SW_E_INVALID, "NULL batch array");
+    if (!out.offsets || !out.cigar_start || (!out.ops && out.ops_cap)) return fail(MGL_SW_E_INVALID, "NULL result array");
+    if (check_scores(in.scores) != PLAN_OK) return fail(MGL_SW_E_SCORES, "score set out of range");
+    cudaError_t e;
+    if ((e = cudaSetDevice(device_)) != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
+    resident_scores_ = in.scores;
+    out.ops_total = 0;
+    out.cigar_start[0] = 0;
+    if (in.n == 0) { if (stats) *stats = bs; return MGL_SW_OK; }
+    if ((e = arena_.reserve(in.arena_bytes + 16)) != cudaSuccess) return cuda_fail(e, "cudaMalloc arena");
+
+    /* arena upload policy: per-chunk byte ranges when the arena is laid out pair after pair,
+       one up-front copy when pairs share or scatter their sequences */
+    u64 total_len = 0;
+    for (int64_t p = 0; p < in.n; p++) total_len += (u64)in.ref_len[p] + in.alt_len[p];
+    const bool whole = in.arena_bytes > total_len + total_len / 2 + 4096 || total_len > in.arena_bytes + in.arena_bytes / 2;
+    if (whole) {
+        if ((e = cudaMemcpyAsync(arena_.p, in.arena, in.arena_bytes, cudaMemcpyHostToDevice, slots_[0].stream)) != cudaSuccess)
+            return cuda_fail(e, "H2D arena");
+        if ((e = cudaStreamSynchronize(slots_[0].stream)) != cudaSuccess) return cuda_fail(e, "H2D arena");
+        bs.h2d_bytes += in.arena_bytes;
+    }
+
+    InFlight fl[2];
+    u64 ops_running = 0;
+    bool overflow = false;
+    int rc = MGL_SW_OK;
+
+    auto finish = [&](int si) -> int {
+        WorkSlot &ws = slots_[si];
+        InFlight &f = fl[si];
+        if (!f.busy) return MGL_SW_OK;
+        f.busy = false;
+        cudaError_t ee;
+        if ((ee = cudaEventSynchronize(ws.ev_counts)) != cudaSuccess) return cuda_fail(ee, "chunk execution");
+        const u32 *cnt = (const u32 *)ws.h_n_ops.p;
+        const u64 total = cnt[f.n];
+        if (!overflow && ops_running + total <= out.ops_cap) {
+            if (total) {
+                if ((ee = cudaMemcpyAsync(out.ops + ops_running, ws.ops.p, total * sizeof(u32), cudaMemcpyDeviceToHost, ws.stream)) != cudaSuccess)
+                    return cuda_fail(ee, "D2H ops");
+                bs.d2h_bytes += total * sizeof(u32);
+            }
+        } else overflow = true;
+        cudaEventRecord(ws.ev_done, ws.stream);
+        u64 run = ops_running;
+        for (u32 k = 0; k < f.n; k++) { run += cnt[k]; out.cigar_start[f.first + k + 1] = run; }
+        ops_running = run;
+        if ((ee = cudaEventSynchronize(ws.ev_done)) != cudaSuccess) return cuda_fail(ee, "D2H ops");
+        return MGL_SW_OK;
+    };
+
+    int64_t first = 0;
+    int c = 0;
+    while (first < in.n && rc == MGL_SW_OK) {
+        const int si = c & 1;
+        WorkSlot &ws = slots_[si];
+        if ((rc = finish(si)) != MGL_SW_OK) break;              /* normally already free */
+        if ((rc = plan_next(in, first, ws.chunk)) != MGL_SW_OK) break;
+        if ((rc = ensure_slot(ws, ws.chunk.plan, ws.chunk.n)) != MGL_SW_OK) break;
+        if ((rc = upload_chunk(in, ws.chunk, ws.stream, !whole, bs)) != MGL_SW_OK) break;
+        if ((rc = run_chunk(ws.chunk, ws, bs, false)) != MGL_SW_OK) break;
+        const u32 n = ws.chunk.n;
+        if ((e = cudaMemcpyAsync(out.offsets + first, ws.offsets.p, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, ws.stream)) != cudaSuccess) { rc = cuda_fail(e, "D2H offsets"); break; }
+        if ((e = cudaMemcpyAsync(ws.h_n_ops.p, ws.n_ops.p, (size_t)n * sizeof(u32), cudaMemcpyDeviceToHost, ws.stream)) != cudaSuccess) { rc = cuda_fail(e, "D2H counts"); break; }
+        if ((e = cudaMemcpyAsync((u32 *)ws.h_n_ops.p + n, (u32 *)ws.starts.p + n, sizeof(u32), cudaMemcpyDeviceToHost, ws.stream)) != cudaSuccess) { rc = cuda_fail(e, "D2H total"); break; }
+        bs.d2h_bytes += (size_t)n * 8 + 4;
+        cudaEventRecord(ws.ev_counts, ws.stream);
+        fl[si].busy = true; fl[si].first = first; fl[si].n = n;
+        first += n;
+        c++;
+        /* while this chunk runs, bring the previous one home */
+        if ((rc = finish(si ^ 1)) != MGL_SW_OK) break;
+    }
+    if (rc == MGL_SW_OK) rc = finish(c & 1);                    /* older chunk first (if any) */
+    if (rc == MGL_SW_OK) rc = finish((c & 1) ^ 1);
+    if (rc != MGL_SW_OK) {
+        cudaDeviceSynchronize();
+        cudaGetLastError();
+        return rc;
+    }
+    out.ops_total = ops_running;
+    if (stats) *stats = bs;
+    if (overflow) return fail(MGL_SW_E_OPS_CAPACITY, "ops buffer too small: need " + std::to_string(ops_running));
+    return MGL_SW_OK;
+}
+
+/* ---------------------------------------------------------------- device-resident mode */
+
+void Engine::drop_resident()
+{
+    for (ChunkDev *cd : resident_) { cd->release(); delete cd; }
+    resident_.clear();
+    for (DevBuf &b : resident_results_) b.release();
+    resident_results_.clear();
+}
+
+int Engine::prepare_resident(const BatchIn &in)
+{
+    cudaError_t e;
+    if ((e = cudaSetDevice(device_)) != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
+    if (in.n <= 0 || !in.arena) return fail(MGL_SW_E_INVALID, "empty batch");
+    if (check_scores(in.scores) != PLAN_OK) return fail(MGL_SW_E_SCORES, "score set out of range");
+    drop_resident();
+    resident_scores_ = in.scores;
+    if ((e = arena_.reserve(in.arena_bytes + 16)) != cudaSuccess) return cuda_fail(e, "cudaMalloc arena");
+    if ((e = cudaMemcpy(arena_.p, in.arena, in.arena_bytes, cudaMemcpyHostToDevice)) != cudaSuccess) return cuda_fail(e, "H2D arena");
+    BatchStats bs;
+    std::memset(&bs, 0, sizeof bs);
+    int64_t first = 0;
+    while (first < in.n) {
+        ChunkDev *cd = new ChunkDev();
+        resident_.push_back(cd);
+        int rc = plan_next(in, first, *cd);
+        if (rc != MGL_SW_OK) { drop_resident(); return rc; }
+        rc = upload_chunk(in, *cd, slots_[0].stream, false, bs);
+        if (rc != MGL_SW_OK) { drop_resident(); return rc; }
+        first += cd->n;
+    }
+    if ((e = cudaStreamSynchronize(slots_[0].stream)) != cudaSuccess) return cuda_fail(e, "H2D descriptors");
+    for (ChunkDev *cd : resident_) {        /* pinned staging no longer needed */
+        cd->h_units.release(); cd->h_pair_unit.release(); cd->h_ops_end.release(); cd->h_strategy.release();
+    }
+    return MGL_SW_OK;
+}
+
+int Engine::run_resident(BatchStats *stats)
+{
+    cudaError_t e;
+    if ((e = cudaSetDevice(device_)) != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
+    if (resident_.empty()) return fail(MGL_SW_E_INVALID, "no resident batch");
+    BatchStats bs;
+    std::memset(&bs, 0, sizeof bs);
+    WorkSlot &ws = slots_[0];
+    for (ChunkDev *cd : resident_) {
+        int rc = ensure_slot(ws, cd->plan, cd->n);
+        if (rc != MGL_SW_OK) return rc;
+        rc = run_chunk(*cd, ws, bs, true);
+        if (rc != MGL_SW_OK) return rc;
+    }
+    if (stats) *stats = bs;
+    return MGL_SW_OK;
+}
+
+int Engine::fetch_resident(BatchOut &out)
+{
+    cudaError_t e;
+    if ((e = cudaSetDevice(device_)) != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
+    if (resident_.empty()) return fail(MGL_SW_E_INVALID, "no resident batch");
+    BatchStats bs;
+    std::memset(&bs, 0, sizeof bs);
+    WorkSlot &ws = slots_[0];
+    u64 run = 0;
+    bool overflow = false;
+    out.cigar_start[0] = 0;
+    std::vector<u32> cnt;
+    for (ChunkDev *cd : resident_) {
+        int rc = ensure_slot(ws, cd->plan, cd->n);
+        if (rc != MGL_SW_OK) return rc;
+        if ((rc = run_chunk(*cd, ws, bs, false)) != MGL_SW_OK) return rc;
+        cnt.resize((size_t)cd->n + 1);
+        if ((e = cudaMemcpyAsync(out.offsets + cd->first, ws.offsets.p, (size_t)cd->n * sizeof(int), cudaMemcpyDeviceToHost, ws.stream)) != cudaSuccess) return cuda_fail(e, "D2H");
+        if ((e = cudaMemcpyAsync(cnt.data(), ws.n_ops.p, (size_t)cd->n * sizeof(u32), cudaMemcpyDeviceToHost, ws.stream)) != cudaSuccess) return cuda_fail(e, "D2H");
+        if ((e = cudaMemcpyAsync(cnt.data() + cd->n, (u32 *)ws.starts.p + cd->n, sizeof(u32), cudaMemcpyDeviceToHost, ws.stream)) != cudaSuccess) return cuda_fail(e, "D2H");
+        if ((e = cudaStreamSynchronize(ws.stream)) != cudaSuccess) return cuda_fail(e, "chunk execution");
+        const u64 total = cnt[cd->n];
+        if (!overflow && run + total <= out.ops_cap) {
+            if (total && (e = cudaMemcpy(out.ops + run, ws.ops.p, total * sizeof(u32), cudaMemcpyDeviceToHost)) != cudaSuccess) return cuda_fail(e, "D2H ops");
+        } else overflow = true;
+        for (u32 k = 0; k < cd->n; k++) { run += cnt[k]; out.cigar_start[cd->first + k + 1] = run; }
+    }
+    out.ops_total = run;
+    if (overflow) return fail(MGL_SW_E_OPS_CAPACITY, "ops buffer too small: need " + std::to_string(run));
+    return MGL_SW_OK;
+}
+
+}  // namespace mglsw

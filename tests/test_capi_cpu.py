@@ -1,0 +1,75 @@
+"""CPU: the C-ABI library builds, loads, exports every symbol include/mgl_sw.h
+declares, plans batches, and refuses to compute without a GPU (no fallback)."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    import __graft_entry__ as g
+    from mgl_b200 import native
+    if not os.path.exists(native.LIB_PATH):
+        g.build()
+    return native.lib()
+
+
+def test_exports_every_declared_symbol(lib):
+    hdr = open(os.path.join(ROOT, "include", "mgl_sw.h")).read()
+    names = re.findall(r"MGL_SW_API\s+[\w\s\*]+?\b(mgl_sw_\w+)\s*\(", hdr)
+    assert len(names) >= 20
+    for n in names:
+        assert hasattr(lib, n), n
+    for n in ("initNative", "alignNative", "doneNative"):      # ...MicrosoftSmithWaterman.h:15,23,31
+        assert hasattr(lib, "Java_com_microsoft_mgl_smithwaterman_MicrosoftSmithWaterman_" + n)
+
+
+def test_format_cigar(lib):
+    ops = np.array([(3 << 4) | 0, (2 << 4) | 2, (15 << 4) | 0, (4 << 4) | 4, (1 << 4) | 1], dtype=np.uint32)
+    buf = C.create_string_buffer(64)
+    n = lib.mgl_sw_format_cigar(ops.ctypes.data, len(ops), buf, 64)
+    assert buf.value == b"3M2D15M4S1I" and n == 11
+    assert lib.mgl_sw_format_cigar(ops.ctypes.data, len(ops), buf, 4) == -1
+
+
+def test_plan_summary_buckets_config2(lib):
+    from mgl_b200 import native, synth
+    d = synth.generate(2, 4096)
+    b, keep = native.make_batch(d["arena"], d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, d["strategies"])
+    out = np.zeros(8, dtype=np.uint64)
+    assert lib.mgl_sw_plan_summary(C.byref(b), 1, out.ctypes.data) == 0
+    launches, units, n16, n32, trace_words, cells = (int(x) for x in out[:6])
+    assert n16 == 4096 and n32 == 0                  # config 2 is 16-bit safe: two pairs per register
+    assert units <= 4096 // 2 + 4 * launches + 64    # almost every unit holds two pairs
+    assert cells == d["cells"]
+    assert trace_words * 4 < 0.5 * cells * 1.6       # 4 bit/cell plus padding
+    assert lib.mgl_sw_plan_summary(C.byref(b), 0, out.ctypes.data) == 0
+    assert int(out[2]) == 0 and int(out[3]) == 4096
+
+
+def test_synth_is_a_pure_function_of_the_index():
+    from mgl_b200 import synth
+    a = synth.generate(5, 300, first=1000)
+    b = synth.generate(5, 100, first=1100)
+    for p in range(100):
+        assert synth.pair_bytes(a, 100 + p) == synth.pair_bytes(b, p)
+    c3 = synth.generate(3, 50)
+    assert 300 <= c3["ref_len"].min() and c3["ref_len"].max() <= 1000
+
+
+def test_no_cpu_fallback_without_a_gpu(lib):
+    if lib.mgl_sw_device_count() > 0:
+        pytest.skip("a GPU is present")
+    import mgl_b200
+    from mgl_b200 import native
+    sw = mgl_b200.MicrosoftSmithWaterman()
+    assert sw.load() is False                        # mirrors MicrosoftSmithWaterman.load: false, never throws
+    with pytest.raises(native.MglSwError):
+        sw.align(b"ACGT", b"ACGT", (10, -15, -30, -5), 1)
+    with pytest.raises(native.MglSwError):
+        mgl_b200.align_one_text(b"ACGT", b"ACGT", (10, -15, -30, -5), 1)

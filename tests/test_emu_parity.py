@@ -1,0 +1,72 @@
+"""CPU: the kernel LOGIC (planner + fill lanes + traceback, the same SW_HD code the
+CUDA kernels compile) run through the lock-step warp emulator in tests/emu and
+compared with the reference-generated golden vectors and with the oracle.
+The emulator is test infrastructure; the product has no CPU path."""
+import random
+from collections import defaultdict
+
+import pytest
+
+import emu_util as E
+
+
+def _by_params(golden):
+    by = defaultdict(list)
+    for c in golden["cases"]:
+        by[tuple(c["params"])].append(c)
+    return by
+
+
+@pytest.mark.parametrize("allow_s16", [True, False])
+def test_emulated_kernels_match_golden(golden, allow_s16):
+    by = _by_params(golden)
+    total = 0
+    # both arithmetics on the two BASELINE score sets; the 16-bit path additionally on every other score set
+    sets = list(by) if allow_s16 else [(10, -15, -30, -5), (200, -150, -260, -11), (3, -1, -2, 0)]
+    for p in sets:
+        cs = by[p]
+        pairs = [(c["ref"].encode("latin1"), c["alt"].encode("latin1")) for c in cs]
+        for si, s in enumerate(golden["strategies"]):
+            res, st = E.emu_align(pairs, p, s, allow_s16)
+            assert (st["s16"] > 0) == allow_s16
+            bad = [(c["ref"], c["alt"], p, s, r, tuple(c["expect"][si])) for c, r in zip(cs, res) if r != tuple(c["expect"][si])]
+            assert not bad, bad[:3]
+            total += len(cs)
+    assert total > 3000
+
+
+def test_emulated_mixed_strategies_in_one_batch(golden, oracle):
+    cs = [c for c in golden["cases"] if tuple(c["params"]) == (10, -15, -30, -5)][:200]
+    pairs = [(c["ref"].encode("latin1"), c["alt"].encode("latin1")) for c in cs]
+    strategies = [golden["strategies"][k % 4] for k in range(len(cs))]
+    res, _ = E.emu_align(pairs, (10, -15, -30, -5), strategies)
+    for k, (c, r) in enumerate(zip(cs, res)):
+        assert r == tuple(c["expect"][k % 4])
+
+
+def test_emulated_strip_mined_long_pairs(oracle):
+    """alt lengths around the lane-group and strip boundaries (192 = 8 * 24, 768 = 32 * 24, 1536)."""
+    rng = random.Random(11)
+    pairs = []
+    for ql in (191, 192, 193, 300, 767, 768, 769, 1000, 1537):
+        tl = rng.randint(150, 600)
+        ref = bytes(rng.choice(b"ACGT") for _ in range(tl))
+        alt = bytearray(rng.choice(b"ACGT") for _ in range(ql))
+        w = min(tl, ql)
+        alt[:w] = ref[:w]
+        for _ in range(6):
+            alt[rng.randrange(ql)] = rng.choice(b"ACGT")
+        del alt[ql // 3: ql // 3 + 2]
+        pairs.append((ref, bytes(alt)))
+    for params in ((200, -150, -260, -11), (10, -15, -30, -5)):
+        for s in oracle.STRATEGIES:
+            res, st = E.emu_align(pairs, params, s)
+            for (r, a), got in zip(pairs, res):
+                assert got == oracle.align(r, a, params, s), (len(r), len(a), params, s)
+
+
+def test_planner_rejects_bad_input():
+    with pytest.raises(RuntimeError):
+        E.emu_align([(b"ACGT", b"")], (10, -15, -30, -5), 1)
+    with pytest.raises(RuntimeError):
+        E.emu_align([(b"ACGT", b"ACGT")], (1 << 27, -(1 << 27), -(1 << 27), -5), 1)

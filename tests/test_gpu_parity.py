@@ -1,0 +1,193 @@
+"""GPU (B200): the CUDA path, called through the C-ABI, against the reference-
+generated golden vectors, the oracle on seeded fuzz and synthetic configs, and
+size-independent properties at BASELINE.json's full config-2 size.  Bit-exact:
+identical CIGAR text and offset on every pair."""
+import ctypes as C
+import random
+from collections import defaultdict
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def sw():
+    import mgl_b200
+    s = mgl_b200.MicrosoftSmithWaterman(0)
+    s._ensure()                      # raises when libmgl_sw.so or the B200 is missing: nothing to fall back to
+    yield s
+    s.close()
+
+
+def _check(sw, oracle, pairs, params, strategies, **opts):
+    st = strategies if not isinstance(strategies, int) else None
+    res = sw.align_batch(pairs, params, strategies if isinstance(strategies, int) else 1, st)
+    bad = []
+    for p, (r, a) in enumerate(pairs):
+        s = strategies if isinstance(strategies, int) else int(strategies[p])
+        exp = oracle.align(r, a, params, s)
+        got = (res.cigar(p), int(res.offsets[p]))
+        if got != exp:
+            bad.append((p, len(r), len(a), params, s, got, exp))
+    assert not bad, bad[:3]
+    return res
+
+
+@pytest.mark.parametrize("allow_s16", [1, 0])
+def test_golden_vectors(sw, golden, allow_s16):
+    sw.set_option("allow_s16", allow_s16)
+    by = defaultdict(list)
+    for c in golden["cases"]:
+        by[tuple(c["params"])].append(c)
+    total = 0
+    try:
+        for p, cs in by.items():
+            pairs = [(c["ref"].encode("latin1"), c["alt"].encode("latin1")) for c in cs]
+            for si, s in enumerate(golden["strategies"]):
+                res = sw.align_batch(pairs, p, s)
+                assert (res.stats["pairs_s16"] > 0) == bool(allow_s16)
+                bad = [(c["ref"], c["alt"], p, s) for k, c in enumerate(cs)
+                       if (res.cigar(k), int(res.offsets[k])) != tuple(c["expect"][si])]
+                assert not bad, bad[:3]
+                total += len(cs)
+    finally:
+        sw.set_option("allow_s16", 1)
+    assert total > 10000
+
+
+def test_single_pair_entry_points(sw, oracle):
+    """the reference's one-pair call: Python mirror of MicrosoftSmithWaterman.align, mgl_sw_align_one, and the JNI symbol"""
+    import mgl_b200
+    from mgl_b200 import native
+    P = mgl_b200.SWParameters(200, -150, -260, -11)
+    r = sw.align(b"GGGGACGTACGTCCCC", b"TTACGTACGTTT", P, mgl_b200.SWOverhangStrategy.SOFTCLIP)
+    assert (r.cigar, r.alignment_offset) == ("2I7M2I1M", 4)
+    one = mgl_b200.align_one_text(b"ACGTACGTAC", b"GGGGGGGGGGGG", P, mgl_b200.SWOverhangStrategy.IGNORE)
+    assert (one.cigar, one.alignment_offset) == ("13D1M", -11)
+
+    # Java_..._alignNative with a table-backed JNIEnv whose GetDirectBufferAddress (slot 230) is the identity
+    GETADDR = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_void_p)
+    ident = GETADDR(lambda env, buf: buf)
+    table = (C.c_void_p * 235)()
+    table[230] = C.cast(ident, C.c_void_p)
+    env = C.pointer(C.c_void_p(C.addressof(table)))
+    fn = native.lib().Java_com_microsoft_mgl_smithwaterman_MicrosoftSmithWaterman_alignNative
+    fn.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p] + [C.c_int] * 7
+    fn.restype = C.c_int
+    rng = random.Random(5)
+    for k in range(40):
+        ref = bytes(rng.choice(b"ACGT") for _ in range(rng.randint(1, 90)))
+        alt = bytes(rng.choice(b"ACGT") for _ in range(rng.randint(1, 90)))
+        s = (1, 2, 4, 8)[k % 4]
+        reads = C.create_string_buffer(ref + alt, len(ref) + len(alt))
+        cig = C.create_string_buffer(2 * max(len(ref), len(alt)) + 64)          # zero-filled like ByteBuffer.allocateDirect
+        off = fn(env, None, C.addressof(reads), C.addressof(cig), len(ref), len(alt), 10, -15, -30, -5, s)
+        assert (cig.value.decode().strip(), off) == oracle.align(ref, alt, (10, -15, -30, -5), s)
+
+
+def test_fuzz_vs_oracle(sw, oracle):
+    rng = random.Random(20261104)
+    score_sets = [(10, -15, -30, -5), (200, -150, -260, -11), (1, -1, -1, -1), (3, -1, -2, 0), (2, -3, -1, -4)]
+    for params in score_sets:
+        pairs = []
+        for k in range(1200):
+            alpha = rng.choice([b"A", b"AC", b"ACGT", b"ACGTN", b"acgtACGT"])
+            ref = bytes(rng.choice(alpha) for _ in range(rng.randint(1, 260)))
+            if rng.random() < 0.5:
+                i = rng.randrange(len(ref)); j = rng.randint(i + 1, len(ref))
+                alt = bytearray(ref[i:j])
+                for _ in range(rng.randint(0, 3)):
+                    alt[rng.randrange(len(alt))] = rng.choice(alpha)
+                alt = bytes(alt)
+            else:
+                alt = bytes(rng.choice(alpha) for _ in range(rng.randint(1, 260)))
+            pairs.append((ref, alt))
+        strategies = np.array([(1, 2, 4, 8)[k % 4] for k in range(len(pairs))], dtype=np.int32)
+        _check(sw, oracle, pairs, params, strategies)
+
+
+def test_empty_and_invalid_inputs(sw):
+    from mgl_b200 import native
+    res = sw.align_batch([], (10, -15, -30, -5), 1)
+    assert len(res.offsets) == 0 and int(res.cigar_start[0]) == 0
+    with pytest.raises(native.MglSwError) as e:
+        sw.align_batch([(b"ACGT", b"")], (10, -15, -30, -5), 1)
+    assert e.value.code == native.E_PAIR
+    res = sw.align_batch([(b"ACGT" * 50, b"ACGT" * 50)] * 3, (10, -15, -30, -5), 1)   # still usable after an error
+    assert res.cigars() == ["200M"] * 3
+
+
+def test_tiny_ops_buffer_reports_needed_size(sw):
+    from mgl_b200 import native, synth
+    d = synth.generate(2, 2000)
+    b, keep = native.make_batch(d["arena"], d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, None)
+    off, cs, ops = np.zeros(2000, np.int32), np.zeros(2001, np.uint64), np.zeros(10, np.uint32)
+    r = native.Result()
+    r.offsets, r.cigar_start, r.ops, r.ops_cap = off.ctypes.data, cs.ctypes.data, ops.ctypes.data, 10
+    rc = native.lib().mgl_sw_align_batch(sw._ensure(), C.byref(b), C.byref(r), None)
+    assert rc == native.E_OPS_CAPACITY and r.ops_total >= 2000 and int(cs[-1]) == r.ops_total
+
+
+@pytest.mark.parametrize("config,n", [(2, 20000), (3, 3000), (5, 6000)])
+def test_synthetic_configs_vs_oracle(sw, oracle, config, n):
+    from mgl_b200 import synth
+    d = synth.generate(config, n)
+    res = sw.align_arrays(d["arena"], d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, d["strategies"])
+    assert res.stats["pairs"] == n
+    step = 1 if n <= 3000 else 5
+    for p in range(0, n, step):
+        r, a = synth.pair_bytes(d, p)
+        if len(r) * len(a) > 4_000_000:
+            continue                                  # the explicit-matrix oracle is kept to sizes it finishes quickly
+        exp = oracle.align(r, a, d["params"], int(d["strategies"][p]))
+        assert (res.cigar(p), int(res.offsets[p])) == exp, (config, p, len(r), len(a))
+
+
+def test_long_pairs_strip_mined_vs_reference_or_oracle(sw, oracle):
+    """config 4 shape (5-10 kbp): the whole-warp strip-mined kernel with HBM carry columns."""
+    from mgl_b200 import synth
+    d = synth.generate(4, 6)
+    res = sw.align_arrays(d["arena"], d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, d["strategies"])
+    assert res.stats["pairs_s32"] == 6
+    for p in range(6):
+        r, a = synth.pair_bytes(d, p)
+        if oracle.have_ref():
+            exp = oracle.ref_align(r, a, d["params"], 1, oracle.REF_SCALAR)      # the reference's own align_scalar
+        elif len(r) * len(a) <= 40_000_000:
+            exp = oracle.align(r, a, d["params"], 1)
+        else:
+            continue
+        assert (res.cigar(p), int(res.offsets[p])) == exp, (p, len(r), len(a))
+
+
+def test_full_size_config2_properties(sw):
+    """1 M pairs (BASELINE.json config 2): both arithmetics agree on every pair; CIGARs consume exactly the alt and
+    stay inside the ref; resident (kernel-timing) path returns the same results as the host-buffer path."""
+    from mgl_b200 import synth
+    n = 1_000_000
+    d = synth.generate(2, n)
+    args = (d["arena"], d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, d["strategies"])
+    a = sw.align_arrays(*args)
+    assert a.stats["pairs_s16"] == n
+    sw.set_option("allow_s16", 0)
+    try:
+        b = sw.align_arrays(*args)
+    finally:
+        sw.set_option("allow_s16", 1)
+    assert b.stats["pairs_s32"] == n
+    assert np.array_equal(a.offsets, b.offsets) and np.array_equal(a.cigar_start, b.cigar_start) and np.array_equal(a.ops, b.ops)
+    sw.resident_prepare(*args)
+    st = sw.resident_run()
+    assert st["cells"] == d["cells"]
+    c = sw.resident_fetch()
+    sw.resident_drop()
+    assert np.array_equal(a.offsets, c.offsets) and np.array_equal(a.ops, c.ops)
+    # CIGAR arithmetic: M + I + S == alt length; offset + M + D <= ref length
+    lens, op = (a.ops >> 4).astype(np.int64), a.ops & 15
+    pair_of = np.repeat(np.arange(n), np.diff(a.cigar_start).astype(np.int64))
+    q = np.bincount(pair_of, weights=lens * np.isin(op, (0, 1, 4)), minlength=n)
+    t = np.bincount(pair_of, weights=lens * np.isin(op, (0, 2)), minlength=n)
+    assert np.array_equal(q.astype(np.int64), d["alt_len"].astype(np.int64))
+    assert (a.offsets >= 0).all() and (a.offsets + t <= d["ref_len"]).all()
