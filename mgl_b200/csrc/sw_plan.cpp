@@ -31,6 +31,27 @@ struct Keyed {
     u32 idx;
 };
 
+/* stable LSD radix sort on the 64-bit key, 16 bits a pass; passes whose digit is constant are skipped */
+void radix_sort(std::vector<Keyed> &v)
+{
+    const size_t n = v.size();
+    if (n < 2) return;
+    std::vector<Keyed> tmp(n);
+    std::vector<u32> hist(65536);
+    Keyed *src = v.data(), *dst = tmp.data();
+    for (int pass = 0; pass < 4; pass++) {
+        const int sh = 16 * pass;
+        std::fill(hist.begin(), hist.end(), 0u);
+        for (size_t k = 0; k < n; k++) hist[(src[k].key >> sh) & 0xffffu]++;
+        if (hist[(src[0].key >> sh) & 0xffffu] == n) continue;
+        u32 run = 0;
+        for (u32 &h : hist) { const u32 c = h; h = run; run += c; }
+        for (size_t k = 0; k < n; k++) dst[hist[(src[k].key >> sh) & 0xffffu]++] = src[k];
+        std::swap(src, dst);
+    }
+    if (src != v.data()) std::memcpy(v.data(), src, n * sizeof(Keyed));
+}
+
 }  // namespace
 
 PlanStatus check_scores(const Scores &s)
@@ -62,6 +83,7 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
     if (check_scores(s) != PLAN_OK) return PLAN_BAD_SCORES;
     out.pair_unit.assign(n, 0);
     out.ops_end.assign(n, 0);
+    out.units.reserve(n / 2 + 64);
 
     /* pass 1: per-pair arithmetic class, and the shared 16-bit bias */
     std::vector<unsigned char> cand(n, 0);
@@ -106,9 +128,7 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
         order[p].key = ~key;            /* ascending sort of ~key == descending key */
         order[p].idx = p;
     }
-    std::sort(order.begin(), order.end(), [](const Keyed &a, const Keyed &b) {
-        return a.key != b.key ? a.key < b.key : a.idx < b.idx;
-    });
+    radix_sort(order);
 
     /* pass 3: units, warps, launches */
     auto launch_key = [](u64 k) { return (~k) >> 45; };          /* kind, G, nstrips, K */
