@@ -31,13 +31,27 @@
 
 namespace mglsw {
 
-SW_HD u32 bitsel(u32 mask, u32 a, u32 b) { return (a & mask) | (b & ~mask); }
-
 #if defined(__CUDA_ARCH__)
 #define SW_ON_DEVICE 1
 #else
 #define SW_ON_DEVICE 0
 #endif
+
+/*
+ * (a & mask) | (b & ~mask) as ONE LOP3.  Written as inline PTX on the device: left to the
+ * compiler, a chain of bit-selects whose unselected bits are dead is re-associated into
+ * and/or pairs that cost one more LOP3 per cell.
+ */
+SW_HD u32 bitsel(u32 mask, u32 a, u32 b)
+{
+#if SW_ON_DEVICE
+    u32 r;
+    asm("lop3.b32 %0, %1, %2, %3, 0xCA;" : "=r"(r) : "r"(mask), "r"(a), "r"(b));
+    return r;
+#else
+    return (a & mask) | (b & ~mask);
+#endif
+}
 
 struct S16x2 {
     static constexpr int KIND = KIND_S16X2;
@@ -140,6 +154,9 @@ SW_HD CellConsts make_consts(const Scores &s, int bias)
     /* M3, M4 are single-bit-per-half masks, so (M / rep(1)) is the per-half bit value */
     c.b3 = T::M3 + T::rep(s.go - s.ge);
     c.b4 = T::M4 + T::rep(s.go - s.ge);
+    c.one = 1u;
+    c.mone = 0xffffffffu;
+    c.neg_go = 0u - T::rep(s.go);       /* a 32-bit negation of the packed constant: added with a plain 32-bit add */
     c.bias = bias;
     c.s_match = s.match; c.s_go = s.go; c.s_ge = s.ge;
     return c;
@@ -149,22 +166,39 @@ SW_HD CellConsts make_consts(const Scores &s, int bias)
  * One cell.  In:  ra/bq packed ref/alt bytes, hdm = H[i-1][j-1] + match (+bias),
  * e = E[i][j], f = F[i][j].  Out: e = E[i+1][j], f = F[i][j+1], hm = H[i][j] + match,
  * acc gets the cell's nibble.
+ *
+ * Pipe balance (ncu, profiles/r01a_fill_full.txt: ALU pipe 95 % busy, FMA pipe 12 %
+ * with every add on the ALU).  An SM sub-partition issues one warp instruction
+ * per clock and owns one 16-lane ALU pipe (LOP3, SHF, IADD3, VIMNMX*, VIADDMNMX*)
+ * and one 16-lane FMA pipe (IMAD); each takes a warp instruction every second
+ * clock.  The DPX max / add-max and the bit merges exist only on the ALU pipe,
+ * so everything that is a plain add or subtract is written as a multiply-add
+ * with a runtime 1 / -1 (c.one, c.mone) and lands on the FMA pipe:
+ *     ALU: xor, min, max3, 2 x add-max, 1 predicate (IADD3), 3 bit-selects, shift, bit-select  = 11
+ *     FMA: d, 3 x (const - x), 3 predicates, h - go, h + match                               =  9
+ * `alu3` moves the third predicate between the pipes; callers alternate it by
+ * register index so that both pipes carry about 10.5 and 9.5 instructions per cell.
  */
 template <class T>
-SW_HD void sw_cell(const CellConsts &c, u32 ra, u32 bq, u32 hdm, u32 &e, u32 &f, u32 &hm, u32 &acc)
+SW_HD void sw_cell(const CellConsts &c, u32 ra, u32 bq, u32 hdm, u32 &e, u32 &f, u32 &hm, u32 &acc, bool alu3 = true)
 {
     const u32 x = ra ^ bq;
     const u32 m = T::min1(x);                 /* 0 match, 1 mismatch                     */
-    const u32 d = hdm + m * c.neg_delta;      /* H_diag + match - m * (match - mismatch) */
+    const u32 d = m * c.neg_delta + hdm;      /* H_diag + match - m * (match - mismatch) */
     const u32 h = T::max3(d, e, f);
-    const u32 t1 = d - h + c.b1;              /* d >= h        : diagonal source         */
-    const u32 t2 = f - e + c.b2;              /* F >= E        : horizontal beats vertical */
-    const u32 t3 = e - h + c.b3;              /* E - ge >= H - go : E extends            */
-    const u32 t4 = f - h + c.b4;              /* F - ge >= H - go : F extends            */
-    const u32 hgo = h - c.go;
+    const u32 nh1 = h * c.mone + c.b1;
+    const u32 t1 = d * c.one + nh1;           /* d - h + b1: d >= h, diagonal source     */
+    const u32 ne2 = e * c.mone + c.b2;
+    const u32 t2 = f * c.one + ne2;           /* f - e + b2: F >= E                      */
+    u32 t3;                                   /* e - h + b3: E - ge >= H - go, E extends */
+    if (alu3) t3 = e - h + c.b3;
+    else { const u32 nh3 = h * c.mone + c.b3; t3 = e * c.one + nh3; }
+    const u32 nh4 = h * c.mone + c.b4;
+    const u32 t4 = f * c.one + nh4;           /* f - h + b4: F - ge >= H - go, F extends */
+    const u32 hgo = h * c.one + c.neg_go;
     e = T::addmax(e, c.neg_ge, hgo);
     f = T::addmax(f, c.neg_ge, hgo);
-    hm = h + c.match;
+    hm = h * c.one + c.match;
     u32 w = bitsel(T::M3, t3, t4);
     w = bitsel(T::M2, t2, w);
     w = bitsel(T::M1, t1, w);

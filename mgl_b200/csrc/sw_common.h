@@ -74,6 +74,10 @@ struct CellConsts {
     u32 neg_ge;     /* -gap_extend, replicated two's complement                       */
     u32 match;      /* match score, replicated                                        */
     u32 b1, b2, b3, b4; /* comparison biases, see sw_cell.h                           */
+    u32 one, mone;  /* 1 and 0xffffffff as RUNTIME values: x * one + y and y - x as   */
+                    /* x * mone + y are then integer multiply-adds, which issue to    */
+                    /* the FMA pipe instead of the ALU pipe the DPX instructions use  */
+    u32 neg_go;     /* 0 - go: x + neg_go subtracts gap_open from both halves         */
     int bias;       /* value stored = true score + bias (0 for KIND_S32)              */
     int s_match, s_go, s_ge;   /* plain scalars for boundary arithmetic               */
 };

@@ -45,14 +45,17 @@ void ChunkDev::release()
 
 void WorkSlot::release()
 {
-    trace.release(); carry.release(); lastrow.release(); scratch.release();
+    trace.release(); carry.release(); lastrow.release(); colbest.release(); scratch.release();
     offsets.release(); n_ops.release(); starts.release(); ops.release();
     h_n_ops.release(); h_total.release();
     chunk.release();
     if (ev_counts) cudaEventDestroy(ev_counts);
     if (ev_done) cudaEventDestroy(ev_done);
+    if (ev_fill) cudaEventDestroy(ev_fill);
+    if (ev_post) cudaEventDestroy(ev_post);
     if (stream) cudaStreamDestroy(stream);
-    ev_counts = ev_done = nullptr; stream = nullptr;
+    if (post) cudaStreamDestroy(post);
+    ev_counts = ev_done = ev_fill = ev_post = nullptr; stream = post = nullptr;
 }
 
 /* ---------------------------------------------------------------- engine */
@@ -60,10 +63,16 @@ void WorkSlot::release()
 Engine::Engine(int device) : device_(device)
 {
     if (cudaSetDevice(device_) != cudaSuccess) { err_ = "cudaSetDevice failed"; return; }
+    int prio_lo = 0, prio_hi = 0;
+    cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
     for (auto &s : slots_) {
-        cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking);
+        cudaStreamCreateWithPriority(&s.stream, cudaStreamNonBlocking, prio_lo);
+        cudaStreamCreateWithPriority(&s.post, cudaStreamNonBlocking, prio_hi);
         cudaEventCreateWithFlags(&s.ev_counts, cudaEventDisableTiming);
         cudaEventCreateWithFlags(&s.ev_done, cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&s.ev_fill, cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&s.ev_post, cudaEventDisableTiming);
+        cudaEventRecord(s.ev_post, s.post);
     }
     for (auto &e : tev_) cudaEventCreate(&e);
 }
@@ -84,6 +93,20 @@ int Engine::cuda_fail(cudaError_t e, const char *what)
     err_ = std::string(what) + ": " + cudaGetErrorString(e);
     cudaGetLastError();
     return MGL_SW_E_CUDA;
+}
+
+/* device arena = front pad | caller's bytes | tail pad long enough for the rows a lane reads past its ref */
+int Engine::reserve_arena(const BatchIn &in)
+{
+    u32 max_tl = 0;
+    for (int64_t p = 0; p < in.n; p++) max_tl = std::max(max_tl, in.ref_len[p]);
+    const size_t need = MGLSW_ARENA_FRONT_PAD + in.arena_bytes + arena_tail_pad(max_tl);
+    if (need > arena_.cap) {
+        cudaError_t e = arena_.reserve(need);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaMalloc arena");
+        if ((e = cudaMemset(arena_.p, 0, arena_.cap)) != cudaSuccess) return cuda_fail(e, "cudaMemset arena");
+    }
+    return MGL_SW_OK;
 }
 
 u64 Engine::budget()
@@ -163,7 +186,7 @@ int Engine::upload_chunk(const BatchIn &in, ChunkDev &cd, cudaStream_t st, bool 
             hi = std::max<u64>(hi, std::max(in.ref_off[p] + in.ref_len[p], in.alt_off[p] + in.alt_len[p]));
         }
         if (hi > lo) {
-            if ((e = cudaMemcpyAsync((uint8_t *)arena_.p + lo, in.arena + lo, hi - lo, cudaMemcpyHostToDevice, st)) != cudaSuccess)
+            if ((e = cudaMemcpyAsync((uint8_t *)arena_dev() + lo, in.arena + lo, hi - lo, cudaMemcpyHostToDevice, st)) != cudaSuccess)
                 return cuda_fail(e, "H2D arena");
             bs.h2d_bytes += hi - lo;
         }
@@ -177,6 +200,7 @@ int Engine::ensure_slot(WorkSlot &ws, const ChunkPlan &plan, u32 n)
     if ((e = ws.trace.reserve((plan.trace_words + 4) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc trace");
     if ((e = ws.carry.reserve((plan.carry_entries + 1) * sizeof(Carry))) != cudaSuccess) return cuda_fail(e, "cudaMalloc carry");
     if ((e = ws.lastrow.reserve((plan.lastrow_words + 1) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc lastrow");
+    if ((e = ws.colbest.reserve((plan.units.size() + 1) * 4 * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc colbest");
     if ((e = ws.scratch.reserve((plan.scratch_words + 1) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc scratch");
     if ((e = ws.offsets.reserve((size_t)n * sizeof(int))) != cudaSuccess) return cuda_fail(e, "cudaMalloc");
     if ((e = ws.n_ops.reserve((size_t)n * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc");
@@ -186,46 +210,55 @@ int Engine::ensure_slot(WorkSlot &ws, const ChunkPlan &plan, u32 n)
     return MGL_SW_OK;
 }
 
-/* fill launches -> traceback -> scan -> compact, all on the slot's stream */
+/*
+ * fill launches on the slot's fill stream, then traceback -> scan -> compact on its (higher
+ * priority) post stream.  The slot's previous chunk must have left the post stream before the
+ * fill overwrites the trace.
+ */
 int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed)
 {
     cudaError_t e;
-    cudaStream_t st = ws.stream;
+    cudaStream_t st = ws.stream, pt = ws.post;
     const Scores &sc = resident_scores_;
+    if ((e = cudaStreamWaitEvent(st, ws.ev_post, 0)) != cudaSuccess) return cuda_fail(e, "stream wait");
     if (timed) cudaEventRecord(tev_[0], st);
     for (const Launch &L : cd.plan.launches) {
         FillArgs a;
-        a.arena = (const uint8_t *)arena_.p;
+        a.arena = arena_dev();
         a.units = (const UnitDesc *)cd.units.p;
         a.trace = (u32 *)ws.trace.p;
         a.carry = (Carry *)ws.carry.p;
         a.lastrow = (u32 *)ws.lastrow.p;
+        a.colbest = (u32 *)ws.colbest.p;
         a.n_warps = L.n_warps;
         a.c = L.kind == KIND_S16X2 ? make_consts<S16x2>(sc, cd.plan.s16_bias) : make_consts<S32>(sc, 0);
         if ((e = launch_fill_any(L.kind, L.G, L.K, a, L.first_unit, st)) != cudaSuccess)
             return cuda_fail(e, "fill launch (is a kernel built for this kind/G/K?)");
         bs.fill_launches++;
-        if (L.kind == KIND_S16X2) bs.pairs_s16 += 0; /* counted below */
     }
     if (timed) cudaEventRecord(tev_[1], st);
+    if ((e = cudaEventRecord(ws.ev_fill, st)) != cudaSuccess) return cuda_fail(e, "event record");
+    if ((e = cudaStreamWaitEvent(pt, ws.ev_fill, 0)) != cudaSuccess) return cuda_fail(e, "stream wait");
+    if (timed) cudaEventRecord(tev_[2], pt);
     TraceArgs t;
     t.units = (const UnitDesc *)cd.units.p;
     t.pair_unit = (const u32 *)cd.pair_unit.p;
     t.ops_end = (const u64 *)cd.ops_end.p;
     t.strategy = (const int *)cd.strategy.p;
     t.trace = (const u32 *)ws.trace.p;
-    t.carry = (const Carry *)ws.carry.p;
+    t.colbest = (const u32 *)ws.colbest.p;
     t.lastrow = (const u32 *)ws.lastrow.p;
     t.scratch = (u32 *)ws.scratch.p;
     t.offsets = (int *)ws.offsets.p;
     t.n_ops = (u32 *)ws.n_ops.p;
     t.n_pairs = cd.n;
-    if ((e = launch_traceback(t, st)) != cudaSuccess) return cuda_fail(e, "traceback launch");
-    if (timed) cudaEventRecord(tev_[2], st);
-    if ((e = launch_scan_counts((const u32 *)ws.n_ops.p, (u32 *)ws.starts.p, cd.n, st)) != cudaSuccess) return cuda_fail(e, "scan launch");
+    if ((e = launch_traceback(t, pt)) != cudaSuccess) return cuda_fail(e, "traceback launch");
+    if (timed) cudaEventRecord(tev_[3], pt);
+    if ((e = launch_scan_counts((const u32 *)ws.n_ops.p, (u32 *)ws.starts.p, cd.n, pt)) != cudaSuccess) return cuda_fail(e, "scan launch");
     if ((e = launch_compact((const u32 *)ws.scratch.p, (const u64 *)cd.ops_end.p, (const u32 *)ws.n_ops.p,
-                            (const u32 *)ws.starts.p, (u32 *)ws.ops.p, cd.n, st)) != cudaSuccess) return cuda_fail(e, "compact launch");
-    if (timed) cudaEventRecord(tev_[3], st);
+                            (const u32 *)ws.starts.p, (u32 *)ws.ops.p, cd.n, pt)) != cudaSuccess) return cuda_fail(e, "compact launch");
+    if (timed) cudaEventRecord(tev_[4], pt);
+    if ((e = cudaEventRecord(ws.ev_post, pt)) != cudaSuccess) return cuda_fail(e, "event record");
     bs.other_launches += 3;
     bs.chunks++;
     bs.cells += cd.plan.cells;
@@ -237,11 +270,11 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed)
         if (u.flags & UNIT_S32) bs.pairs_s32 += k; else bs.pairs_s16 += k;
     }
     if (timed) {
-        if ((e = cudaEventSynchronize(tev_[3])) != cudaSuccess) return cuda_fail(e, "chunk sync");
+        if ((e = cudaEventSynchronize(tev_[4])) != cudaSuccess) return cuda_fail(e, "chunk sync");
         float a = 0, b = 0, c = 0;
         cudaEventElapsedTime(&a, tev_[0], tev_[1]);
-        cudaEventElapsedTime(&b, tev_[1], tev_[2]);
-        cudaEventElapsedTime(&c, tev_[2], tev_[3]);
+        cudaEventElapsedTime(&b, tev_[2], tev_[3]);
+        cudaEventElapsedTime(&c, tev_[3], tev_[4]);
         bs.fill_ms += a; bs.trace_ms += b; bs.post_ms += c; bs.device_ms += a + b + c;
     }
     return MGL_SW_OK;
@@ -267,7 +300,7 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
     out.ops_total = 0;
     out.cigar_start[0] = 0;
     if (in.n == 0) { if (stats) *stats = bs; return MGL_SW_OK; }
-    if ((e = arena_.reserve(in.arena_bytes + 16)) != cudaSuccess) return cuda_fail(e, "cudaMalloc arena");
+    { const int rc0 = reserve_arena(in); if (rc0 != MGL_SW_OK) return rc0; }
 
     /* arena upload policy: per-chunk byte ranges when the arena is laid out pair after pair,
        one up-front copy when pairs share or scatter their sequences */
@@ -275,7 +308,7 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
     for (int64_t p = 0; p < in.n; p++) total_len += (u64)in.ref_len[p] + in.alt_len[p];
     const bool whole = in.arena_bytes > total_len + total_len / 2 + 4096 || total_len > in.arena_bytes + in.arena_bytes / 2;
     if (whole) {
-        if ((e = cudaMemcpyAsync(arena_.p, in.arena, in.arena_bytes, cudaMemcpyHostToDevice, slots_[0].stream)) != cudaSuccess)
+        if ((e = cudaMemcpyAsync((void *)arena_dev(), in.arena, in.arena_bytes, cudaMemcpyHostToDevice, slots_[0].stream)) != cudaSuccess)
             return cuda_fail(e, "H2D arena");
         if ((e = cudaStreamSynchronize(slots_[0].stream)) != cudaSuccess) return cuda_fail(e, "H2D arena");
         bs.h2d_bytes += in.arena_bytes;
@@ -297,12 +330,13 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         const u64 total = cnt[f.n];
         if (!overflow && ops_running + total <= out.ops_cap) {
             if (total) {
-                if ((ee = cudaMemcpyAsync(out.ops + ops_running, ws.ops.p, total * sizeof(u32), cudaMemcpyDeviceToHost, ws.stream)) != cudaSuccess)
+                if ((ee = cudaMemcpyAsync(out.ops + ops_running, ws.ops.p, total * sizeof(u32), cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess)
                     return cuda_fail(ee, "D2H ops");
                 bs.d2h_bytes += total * sizeof(u32);
             }
         } else overflow = true;
-        cudaEventRecord(ws.ev_done, ws.stream);
+        cudaEventRecord(ws.ev_done, ws.post);
+        cudaEventRecord(ws.ev_post, ws.post);
         u64 run = ops_running;
         for (u32 k = 0; k < f.n; k++) { run += cnt[k]; out.cigar_start[f.first + k + 1] = run; }
         ops_running = run;
@@ -321,11 +355,12 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         if ((rc = upload_chunk(in, ws.chunk, ws.stream, !whole, bs)) != MGL_SW_OK) break;
         if ((rc = run_chunk(ws.chunk, ws, bs, false)) != MGL_SW_OK) break;
         const u32 n = ws.chunk.n;
-        if ((e = cudaMemcpyAsync(out.offsets + first, ws.offsets.p, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, ws.stream)) != cudaSuccess) { rc = cuda_fail(e, "D2H offsets"); break; }
-        if ((e = cudaMemcpyAsync(ws.h_n_ops.p, ws.n_ops.p, (size_t)n * sizeof(u32), cudaMemcpyDeviceToHost, ws.stream)) != cudaSuccess) { rc = cuda_fail(e, "D2H counts"); break; }
-        if ((e = cudaMemcpyAsync((u32 *)ws.h_n_ops.p + n, (u32 *)ws.starts.p + n, sizeof(u32), cudaMemcpyDeviceToHost, ws.stream)) != cudaSuccess) { rc = cuda_fail(e, "D2H total"); break; }
+        if ((e = cudaMemcpyAsync(out.offsets + first, ws.offsets.p, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess) { rc = cuda_fail(e, "D2H offsets"); break; }
+        if ((e = cudaMemcpyAsync(ws.h_n_ops.p, ws.n_ops.p, (size_t)n * sizeof(u32), cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess) { rc = cuda_fail(e, "D2H counts"); break; }
+        if ((e = cudaMemcpyAsync((u32 *)ws.h_n_ops.p + n, (u32 *)ws.starts.p + n, sizeof(u32), cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess) { rc = cuda_fail(e, "D2H total"); break; }
         bs.d2h_bytes += (size_t)n * 8 + 4;
-        cudaEventRecord(ws.ev_counts, ws.stream);
+        cudaEventRecord(ws.ev_counts, ws.post);
+        cudaEventRecord(ws.ev_post, ws.post);
         fl[si].busy = true; fl[si].first = first; fl[si].n = n;
         first += n;
         c++;
@@ -363,8 +398,8 @@ int Engine::prepare_resident(const BatchIn &in)
     if (check_scores(in.scores) != PLAN_OK) return fail(MGL_SW_E_SCORES, "score set out of range");
     drop_resident();
     resident_scores_ = in.scores;
-    if ((e = arena_.reserve(in.arena_bytes + 16)) != cudaSuccess) return cuda_fail(e, "cudaMalloc arena");
-    if ((e = cudaMemcpy(arena_.p, in.arena, in.arena_bytes, cudaMemcpyHostToDevice)) != cudaSuccess) return cuda_fail(e, "H2D arena");
+    { const int rc0 = reserve_arena(in); if (rc0 != MGL_SW_OK) return rc0; }
+    if ((e = cudaMemcpy((void *)arena_dev(), in.arena, in.arena_bytes, cudaMemcpyHostToDevice)) != cudaSuccess) return cuda_fail(e, "H2D arena");
     BatchStats bs;
     std::memset(&bs, 0, sizeof bs);
     int64_t first = 0;
@@ -391,13 +426,45 @@ int Engine::run_resident(BatchStats *stats)
     if (resident_.empty()) return fail(MGL_SW_E_INVALID, "no resident batch");
     BatchStats bs;
     std::memset(&bs, 0, sizeof bs);
-    WorkSlot &ws = slots_[0];
-    for (ChunkDev *cd : resident_) {
-        int rc = ensure_slot(ws, cd->plan, cd->n);
-        if (rc != MGL_SW_OK) return rc;
-        rc = run_chunk(*cd, ws, bs, true);
+    if (!overlap) {
+        /* one chunk at a time on slot 0, every phase bracketed by events: per-kernel times */
+        WorkSlot &ws = slots_[0];
+        for (ChunkDev *cd : resident_) {
+            int rc = ensure_slot(ws, cd->plan, cd->n);
+            if (rc != MGL_SW_OK) return rc;
+            rc = run_chunk(*cd, ws, bs, true);
+            if (rc != MGL_SW_OK) return rc;
+        }
+        if (stats) *stats = bs;
+        return MGL_SW_OK;
+    }
+    /*
+     * Whole-batch throughput: chunks alternate between the two slots, so the traceback of chunk c
+     * (post stream) runs while chunk c + 1 fills.  One start event gates both fill streams; the
+     * time is start -> the later of the two post streams' last event.
+     */
+    for (size_t c = 0; c < resident_.size() && c < 2; c++) {
+        int rc = ensure_slot(slots_[c], resident_[c]->plan, resident_[c]->n);
         if (rc != MGL_SW_OK) return rc;
     }
+    for (size_t c = 2; c < resident_.size(); c++) {        /* grow each slot to its largest chunk before timing */
+        int rc = ensure_slot(slots_[c & 1], resident_[c]->plan, resident_[c]->n);
+        if (rc != MGL_SW_OK) return rc;
+    }
+    if ((e = cudaEventRecord(tev_[0], slots_[0].stream)) != cudaSuccess) return cuda_fail(e, "event record");
+    if ((e = cudaStreamWaitEvent(slots_[1].stream, tev_[0], 0)) != cudaSuccess) return cuda_fail(e, "stream wait");
+    for (size_t c = 0; c < resident_.size(); c++) {
+        int rc = run_chunk(*resident_[c], slots_[c & 1], bs, false);
+        if (rc != MGL_SW_OK) return rc;
+    }
+    cudaEventRecord(tev_[4], slots_[0].post);
+    cudaEventRecord(tev_[5], slots_[1].post);
+    if ((e = cudaEventSynchronize(tev_[4])) != cudaSuccess) return cuda_fail(e, "batch execution");
+    if ((e = cudaEventSynchronize(tev_[5])) != cudaSuccess) return cuda_fail(e, "batch execution");
+    float a = 0, b = 0;
+    cudaEventElapsedTime(&a, tev_[0], tev_[4]);
+    cudaEventElapsedTime(&b, tev_[0], tev_[5]);
+    bs.device_ms = a > b ? a : b;
     if (stats) *stats = bs;
     return MGL_SW_OK;
 }
@@ -419,10 +486,10 @@ int Engine::fetch_resident(BatchOut &out)
         if (rc != MGL_SW_OK) return rc;
         if ((rc = run_chunk(*cd, ws, bs, false)) != MGL_SW_OK) return rc;
         cnt.resize((size_t)cd->n + 1);
-        if ((e = cudaMemcpyAsync(out.offsets + cd->first, ws.offsets.p, (size_t)cd->n * sizeof(int), cudaMemcpyDeviceToHost, ws.stream)) != cudaSuccess) return cuda_fail(e, "D2H");
-        if ((e = cudaMemcpyAsync(cnt.data(), ws.n_ops.p, (size_t)cd->n * sizeof(u32), cudaMemcpyDeviceToHost, ws.stream)) != cudaSuccess) return cuda_fail(e, "D2H");
-        if ((e = cudaMemcpyAsync(cnt.data() + cd->n, (u32 *)ws.starts.p + cd->n, sizeof(u32), cudaMemcpyDeviceToHost, ws.stream)) != cudaSuccess) return cuda_fail(e, "D2H");
-        if ((e = cudaStreamSynchronize(ws.stream)) != cudaSuccess) return cuda_fail(e, "chunk execution");
+        if ((e = cudaMemcpyAsync(out.offsets + cd->first, ws.offsets.p, (size_t)cd->n * sizeof(int), cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess) return cuda_fail(e, "D2H");
+        if ((e = cudaMemcpyAsync(cnt.data(), ws.n_ops.p, (size_t)cd->n * sizeof(u32), cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess) return cuda_fail(e, "D2H");
+        if ((e = cudaMemcpyAsync(cnt.data() + cd->n, (u32 *)ws.starts.p + cd->n, sizeof(u32), cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess) return cuda_fail(e, "D2H");
+        if ((e = cudaStreamSynchronize(ws.post)) != cudaSuccess) return cuda_fail(e, "chunk execution");
         const u64 total = cnt[cd->n];
         if (!overflow && run + total <= out.ops_cap) {
             if (total && (e = cudaMemcpy(out.ops + run, ws.ops.p, total * sizeof(u32), cudaMemcpyDeviceToHost)) != cudaSuccess) return cuda_fail(e, "D2H ops");

@@ -17,6 +17,7 @@
 #include <string>
 #include <vector>
 
+#include "sw_fill.h"
 #include "sw_plan.h"
 
 namespace mglsw {
@@ -70,9 +71,12 @@ struct ChunkDev {
 };
 
 struct WorkSlot {
-    cudaStream_t stream = nullptr;
-    cudaEvent_t ev_counts = nullptr, ev_done = nullptr;
-    DevBuf trace, carry, lastrow, scratch, offsets, n_ops, starts, ops;
+    cudaStream_t stream = nullptr;       /* uploads and fill launches                                          */
+    cudaStream_t post = nullptr;         /* traceback, scan, compact, downloads: higher priority, so that the   */
+                                         /* latency-bound traceback of one chunk slips in between the blocks of */
+                                         /* the other slot's fill instead of queueing behind them               */
+    cudaEvent_t ev_fill = nullptr, ev_post = nullptr, ev_counts = nullptr, ev_done = nullptr;
+    DevBuf trace, carry, lastrow, colbest, scratch, offsets, n_ops, starts, ops;
     PinBuf h_n_ops, h_total;
     ChunkDev chunk;              /* descriptors of the chunk in flight (streaming mode) */
     void release();
@@ -96,6 +100,8 @@ public:
     void drop_resident();
 
     bool allow_s16 = true;
+    bool overlap = true;         /* run_resident: alternate the two slots so traceback(c) overlaps fill(c + 1);
+                                    false = one chunk at a time with per-kernel event timing */
     u32 chunk_pairs = 1u << 17;
     u64 trace_budget_bytes = 0;  /* 0: derived from free memory */
 
@@ -110,12 +116,14 @@ private:
 
     int device_;
     std::string err_;
-    DevBuf arena_;
+    DevBuf arena_;               /* device copy of the caller's arena, padded on both sides (sw_fill.h) */
+    const uint8_t *arena_dev() const { return (const uint8_t *)arena_.p + MGLSW_ARENA_FRONT_PAD; }
+    int reserve_arena(const BatchIn &in);
     WorkSlot slots_[2];
     std::vector<ChunkDev *> resident_;
     std::vector<DevBuf> resident_results_;   /* per chunk: offsets | starts | ops kept on device */
     Scores resident_scores_{};
-    cudaEvent_t tev_[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t tev_[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 };
 
 }  // namespace mglsw

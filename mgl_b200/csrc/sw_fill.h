@@ -8,12 +8,15 @@
  * and a 4-bit-per-cell trace accumulator).  Lane l is one row behind lane
  * l - 1; the two values that cross a lane boundary (H and F of the lane's last
  * real column) travel by warp shuffle.  Alt lengths beyond G * K columns are
- * processed as several strips; the last lane of a strip parks (H, F) per row
- * in a carry column in HBM which lane 0 of the next strip reads back -- the
- * GPU analogue of the score[]/step[] band carry in sw_avx.cpp:36-49,193-198.
- * The same carry column of the LAST strip is H[.][ql], which the traceback
- * kernel scans for the reference's last-column maximum (sw.cpp:100-104);
- * the registers of row tl are captured for the last-row scan (sw.cpp:116-127).
+ * processed as several strips (G == 32 only); the last lane of a strip parks
+ * (H, F) per row in a carry column in HBM which lane 0 of the next strip reads
+ * back -- the GPU analogue of the score[]/step[] band carry in
+ * sw_avx.cpp:36-49,193-198.
+ *
+ * Endpoint selection is fused into the fill: the lane that owns column ql keeps
+ * the running last-column maximum with the reference's tie-break (">=" while the
+ * row ascends, sw.cpp:100-104) and stores (value, row) once, at row tl; the
+ * registers of row tl are captured for the last-row scan (sw.cpp:116-127).
  *
  * FillLane is SW_HD: the CUDA kernel (sw_fill_kernel.cuh) drives 32 of them in
  * a warp with __shfl_up_sync; tests/emu drives 32 of them in a loop on the CPU.
@@ -33,13 +36,18 @@ namespace mglsw {
 
 struct Carry { u32 h, f; };   /* 8 bytes: H[i][last col] + match, F[i][last col + 1] (both + bias) */
 
+/* bytes readable before arena[0] and after the last sequence byte (see FillLane::fetch_ref) */
+#define MGLSW_ARENA_FRONT_PAD 64u
+SW_HD u64 arena_tail_pad(u32 max_ref_len) { return (u64)max_ref_len + 64u; }
+
 /* device buffers of one fill launch */
 struct FillArgs {
-    const uint8_t *arena;     /* raw sequence bytes                                   */
+    const uint8_t *arena;     /* raw sequence bytes; readable on [-FRONT_PAD, bytes + arena_tail_pad(max tl)) */
     const UnitDesc *units;    /* units of this launch, (32 / G) per warp              */
     u32 *trace;               /* trace buffer (word offsets in UnitDesc)              */
-    Carry *carry;             /* strip carry columns                                  */
+    Carry *carry;             /* strip carry columns (G == 32 launches only)          */
     u32 *lastrow;             /* captured last rows                                   */
+    u32 *colbest;             /* per unit 4 words: (value, row) of the last-column maximum of each half */
     u32 n_warps;
     CellConsts c;
 };
@@ -47,15 +55,19 @@ struct FillArgs {
 template <class T, int G, int K>
 struct FillLane {
     static constexpr int Q = (K + 3) / 4;
+    static constexpr bool STRIPS = (G == 32);    /* lane groups of 8 always cover the alt in one strip */
     u32 e[K], hm[K], bq[K], acc[K];
     u32 hleft;                /* H[i-1][first col - 1] + match: diagonal input of register 0 */
     u32 h_out, f_out;         /* this step's values for the right-hand neighbour      */
     u32 ra_next;              /* ref bytes of the next step's row (prefetched)        */
     Carry cin_next;           /* carry-in of the next step's row (strips > 0, lane 0) */
+    u32 bh, bf, bdec;         /* column-0 boundary of the next step's row (lane 0), and its per-row decrement */
+    u32 best0, best1;         /* running last-column maximum: S16x2 (value << 16 | row) per half; S32 value, row */
 
     /* lane constants */
-    const uint8_t *ref0, *ref1, *alt0, *alt1;
-    u32 tl0, tl1, tlmax, own_rows, ql;
+    const uint8_t *rp0, *rp1; /* rp[t] = ref byte of row t - lane                     */
+    const uint8_t *alt0, *alt1;
+    u32 tl0, tl1, own_rows, ql;
     u32 lane;                 /* lane inside the group                                */
     u32 wlane;                /* lane inside the warp                                 */
     u32 n;                    /* real columns of this lane in the current strip       */
@@ -68,23 +80,30 @@ struct FillLane {
     Carry *carry_cols;        /* two columns of carry_rows entries                    */
     u32 carry_rows;
     u32 *lastrow;             /* PAIRS regions of nslots * K words                    */
+    u32 *colbest;             /* this unit's 4 words                                  */
 
-    SW_HD void setup(const FillArgs &a, const UnitDesc &u, u32 warp_lane)
+    SW_HD void setup(const FillArgs &a, const UnitDesc &u, u32 warp_lane, u32 unit_index)
     {
         wlane = warp_lane;
         lane = warp_lane % G;
-        ref0 = a.arena + u.ref_off[0];
+        const uint8_t *ref0 = a.arena + u.ref_off[0];
         alt0 = a.arena + u.alt_off[0];
         const int two = (T::PAIRS == 2 && u.pair[1] != NO_PAIR);
-        ref1 = two ? a.arena + u.ref_off[1] : ref0;
+        const uint8_t *ref1 = two ? a.arena + u.ref_off[1] : ref0;
         alt1 = two ? a.arena + u.alt_off[1] : alt0;
+        /*
+         * Row i of pair p is ref_p[i - 1].  Rows outside 1..tl are computed and thrown away (the
+         * lane skew, a shorter partner in the same unit or warp); their bytes are read where they
+         * fall, inside the padding the engine keeps around the arena, instead of being clamped.
+         */
+        rp0 = ref0 - 1 - (int)lane;
+        rp1 = ref1 - 1 - (int)lane;
         tl0 = u.tl[0];
         tl1 = two ? u.tl[1] : u.tl[0];
-        tlmax = u.tlmax;
         own_rows = u.carry_rows - 1;
         ql = u.ql;
-        nstrips = u.nstrips;
-        nslots = u.nstrips * G;
+        nstrips = STRIPS ? u.nstrips : 1u;
+        nslots = nstrips * G;
         col_base = u.col_base;
         col_rem = u.col_rem;
         rb_count = u.rb_count;
@@ -95,25 +114,22 @@ struct FillLane {
         carry_cols = a.carry + u.carry_off;
         carry_rows = u.carry_rows;
         lastrow = a.lastrow + u.lastrow_off;
+        colbest = a.colbest + (size_t)unit_index * 4u;
         h_out = f_out = 0;
     }
 
     SW_HD int bnd(const CellConsts &c, int x) const { return boundary_score(x, (int)indel, c.s_go, c.s_ge); }
 
-    SW_HD u32 fetch_ref(int i) const
+    SW_HD u32 fetch_ref(u32 t) const
     {
-        int i0 = i < 1 ? 1 : (i > (int)tl0 ? (int)tl0 : i);
-        u32 r = SW_LDG(ref0 + (i0 - 1));
-        if (T::PAIRS == 2) {
-            int i1 = i < 1 ? 1 : (i > (int)tl1 ? (int)tl1 : i);
-            r |= (u32)SW_LDG(ref1 + (i1 - 1)) << 16;
-        }
+        u32 r = SW_LDG(rp0 + t);
+        if (T::PAIRS == 2) r |= (u32)SW_LDG(rp1 + t) << 16;
         return r;
     }
     SW_HD Carry fetch_carry(int i) const
     {
         Carry z; z.h = 0; z.f = 0;
-        if (strip == 0 || lane != 0) return z;
+        if (!STRIPS || strip == 0 || lane != 0) return z;
         int ii = i < 1 ? 1 : (i > (int)own_rows ? (int)own_rows : i);
         const Carry *col = carry_cols + (size_t)((strip - 1) & 1u) * carry_rows;
 #if SW_ON_DEVICE
@@ -135,6 +151,8 @@ struct FillLane {
             hm[k] = T::rep(c.bias + b + c.s_match);
         }
         hleft = T::rep(c.bias + c.s_match + bnd(c, (int)j0 - 1));
+        best0 = T::PAIRS == 2 ? 0u : 0x80000000u;
+        best1 = 0u;
     }
 
     SW_HD void strip_begin(const CellConsts &c, u32 s)
@@ -156,8 +174,17 @@ struct FillLane {
         reset_rows(c);
         h_out = T::rep(c.bias);
         f_out = T::rep(c.bias);
-        ra_next = fetch_ref(-(int)lane);
+        ra_next = fetch_ref(0);
         cin_next = fetch_carry(-(int)lane);
+        /*
+         * Column 0 as lane 0 of strip 0 sees it at step t (row t): H[t][0] + match and the F seed
+         * H[t][0] - go (sw.cpp:47-49 and :22-26,38).  Constant without the INDEL boundary, a ramp
+         * of -ge per row with it; kept as running values so a step costs two subtractions.
+         * The value for t == 0 is never used by a real row (row 0 is recomputed by reset_rows).
+         */
+        bdec = indel ? T::rep(c.s_ge) : 0u;
+        bh = T::rep(c.bias + c.s_match + (indel ? -c.s_go + c.s_ge : 0));
+        bf = T::rep(c.bias - c.s_go + (indel ? -c.s_go + c.s_ge : 0));
     }
 
     /*
@@ -168,21 +195,22 @@ struct FillLane {
     {
         const int i = (int)t - (int)lane;
         const u32 ra = ra_next;
-        const Carry cin = cin_next;
-        ra_next = fetch_ref(i + 1);
-        cin_next = fetch_carry(i + 1);
+        ra_next = fetch_ref(t + 1);
 
         u32 h_in = h_sh, f_in = f_sh;
-        if (lane == 0) {
-            if (strip == 0) {                       /* column 0: sw.cpp:47-49 and the f[] seeds :22-26,38 */
-                const int b = bnd(c, i);
-                h_in = T::rep(c.bias + c.s_match + b);
-                f_in = T::rep(c.bias + b - c.s_go);
-            } else {
-                h_in = cin.h;
-                f_in = cin.f;
+        if (STRIPS) {
+            const Carry cin = cin_next;
+            cin_next = fetch_carry(i + 1);
+            if (lane == 0) {
+                h_in = strip == 0 ? bh : cin.h;
+                f_in = strip == 0 ? bf : cin.f;
             }
+        } else if (lane == 0) {
+            h_in = bh;
+            f_in = bf;
         }
+        bh -= bdec;
+        bf -= bdec;
 
         u32 diag = hleft;
         hleft = h_in;
@@ -191,15 +219,23 @@ struct FillLane {
 #pragma unroll
         for (int k = 0; k < K; k++) {
             const u32 old = hm[k];
-            sw_cell<T>(c, ra, bq[k], diag, e[k], f, hm[k], acc[k]);
+            sw_cell<T>(c, ra, bq[k], diag, e[k], f, hm[k], acc[k], (k & 1) != 0);
             diag = old;
             if (k == K - 2) f_km2 = f;
         }
         if (n == (u32)K) { h_out = hm[K - 1]; f_out = f; }
         else             { h_out = K >= 2 ? hm[K >= 2 ? K - 2 : 0] : h_in; f_out = f_km2; }
 
+        /* running maximum of this lane's last column; meaningful in the lane that owns column ql */
+        if (T::PAIRS == 2) {
+            const u32 k0 = (h_out << 16) | ((u32)i & 0xffffu);
+            const u32 k1 = (h_out & 0xffff0000u) | ((u32)i & 0xffffu);
+            best0 = k0 > best0 ? k0 : best0;
+            best1 = k1 > best1 ? k1 : best1;
+        } else if ((int)h_out >= (int)best0) { best0 = h_out; best1 = (u32)i; }
+
         if (active) {
-            if (lane == G - 1 && i >= 1 && i <= (int)own_rows) {
+            if (STRIPS && lane == G - 1 && i >= 1 && i <= (int)own_rows) {
                 Carry *col = carry_cols + (size_t)(strip & 1u) * carry_rows;
 #if SW_ON_DEVICE
                 __stcg(reinterpret_cast<uint2 *>(col + i), make_uint2(h_out, f_out));
@@ -207,13 +243,19 @@ struct FillLane {
                 col[i].h = h_out; col[i].f = f_out;
 #endif
             }
+            const bool owner = (lane == G - 1) && (strip + 1 == nstrips);
             if (i == (int)tl0) {
 #pragma unroll
                 for (int k = 0; k < K; k++) lastrow[(size_t)slot * K + k] = hm[k];
+                if (owner) {
+                    if (T::PAIRS == 2) { colbest[0] = best0 >> 16; colbest[1] = best0 & 0xffffu; }
+                    else { colbest[0] = best0; colbest[1] = best1; }
+                }
             }
             if (T::PAIRS == 2 && i == (int)tl1) {
 #pragma unroll
                 for (int k = 0; k < K; k++) lastrow[(size_t)(nslots + slot) * K + k] = hm[k];
+                if (owner) { colbest[2] = best1 >> 16; colbest[3] = best1 & 0xffffu; }
             }
         }
         if (i == 0) reset_rows(c);

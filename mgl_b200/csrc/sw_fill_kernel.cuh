@@ -18,10 +18,11 @@ sw_fill_kernel(const __grid_constant__ FillArgs a, const u32 first_unit)
     const u32 warp = blockIdx.x * (MGLSW_FILL_THREADS / 32) + (threadIdx.x >> 5);
     if (warp >= a.n_warps) return;
     const u32 wl = threadIdx.x & 31u;
-    const UnitDesc &u = a.units[first_unit + warp * (32 / G) + wl / G];
+    const u32 ui = first_unit + warp * (32 / G) + wl / G;
+    const UnitDesc &u = a.units[ui];
 
     FillLane<T, G, K> L;
-    L.setup(a, u, wl);
+    L.setup(a, u, wl, ui);
     const u32 steps = u.rb_count * T::SPW;       /* same for every lane of the warp */
     const u32 nstrips = u.nstrips;
     for (u32 s = 0; s < nstrips; s++) {

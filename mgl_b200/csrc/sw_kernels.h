@@ -19,7 +19,7 @@ struct TraceArgs {
     const u64 *ops_end;       /* per pair: end of its scratch region (words)    */
     const int *strategy;      /* per pair                                       */
     const u32 *trace;
-    const Carry *carry;
+    const u32 *colbest;       /* per unit 4 words, written by the fill          */
     const u32 *lastrow;
     u32 *scratch;             /* CIGAR elements, written downwards from ops_end */
     int *offsets;             /* out, per pair                                  */

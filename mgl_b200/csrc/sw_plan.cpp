@@ -74,6 +74,7 @@ bool s16_bounds(const Scores &s, u32 tl, u32 ql, long long &lo, long long &hi)
     value_bounds(s, tl, ql, MGLSW_G_SHORT, lo, hi);
     if (2 * diff_bound(s) >= 4096) return false;           /* predicate bits 12..15 of each half */
     if (s.match - s.mismatch >= 32768) return false;
+    if (tl > 65535u) return false;                         /* the fused last-column maximum packs (value, row) in 32 bits */
     return hi - lo < 65000;
 }
 
@@ -204,8 +205,10 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
                 wu[g].group = g;
                 wu[g].trace_off = out.trace_words;
                 if (wu[g].flags & UNIT_ACTIVE) {
-                    wu[g].carry_off = out.carry_entries;
-                    out.carry_entries += 2ull * wu[g].carry_rows;
+                    if (L.G == MGLSW_G_LONG) {            /* only strip-mined units hand columns over through HBM */
+                        wu[g].carry_off = out.carry_entries;
+                        out.carry_entries += 2ull * wu[g].carry_rows;
+                    }
                     wu[g].lastrow_off = out.lastrow_words;
                     out.lastrow_words += (u64)(L.kind == KIND_S16X2 ? 2 : 1) * L.nstrips * L.G * L.K;
                 }

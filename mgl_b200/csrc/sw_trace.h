@@ -5,7 +5,7 @@
  *
  * Restates, with the same tie-breaks (paths relative to
  * /root/reference/src/main/native/mgl_sw/):
- *   last-column argmax, ">=" with ascending row            sw.cpp:100-104
+ *   last-column argmax, ">=" with ascending row            sw.cpp:100-104  (fused into the fill, read back here)
  *   last-row scan, ">" or equal-and-nearer-the-diagonal    sw.cpp:116-127
  *   traceback start cell per strategy                      sw.cpp:155-170
  *   walk with k-cell gap jumps and run merging             sw.cpp:173-214
@@ -64,22 +64,17 @@ struct PairResult {
  */
 template <class T>
 SW_HD PairResult traceback_pair(const UnitDesc &u, u32 half, u32 G, u32 K, const u32 *trace,
-                                const Carry *carry, const u32 *lastrow, int strategy, u32 *ops_end)
+                                const u32 *colbest4, const u32 *lastrow, int strategy, u32 *ops_end)
 {
     const int tl = (int)u.tl[half], ql = (int)u.ql;
     const u32 nslots = u.nstrips * G;
-    const Carry *col = carry + u.carry_off + (size_t)((u.nstrips - 1) & 1u) * u.carry_rows;
 
-    /* last column: sw.cpp:100-104 */
-    int mqe = -0x40000000, mqe_t = -1;
-    for (int i = 1; i <= tl; i++) {
+    /* last column: sw.cpp:100-104; the running maximum was kept by the fill (sw_fill.h), same "+ match + bias" as lastrow */
 #if SW_ON_DEVICE
-        const int v = T::half(__ldcg(&col[i].h), (int)half);
+    const int mqe = (int)__ldcg(colbest4 + 2 * half), mqe_t = (int)__ldcg(colbest4 + 2 * half + 1);
 #else
-        const int v = T::half(col[i].h, (int)half);
+    const int mqe = (int)colbest4[2 * half], mqe_t = (int)colbest4[2 * half + 1];
 #endif
-        if (v >= mqe) { mqe = v; mqe_t = i; }
-    }
 
     int I, J, run = 0, start_score = mqe;
     if (strategy == OS_INDEL) { I = tl; J = ql; }

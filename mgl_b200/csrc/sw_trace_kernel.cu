@@ -19,8 +19,9 @@ __global__ void __launch_bounds__(128) sw_traceback_kernel(const __grid_constant
     const u32 G = (u.flags & UNIT_G32) ? MGLSW_G_LONG : MGLSW_G_SHORT;
     u32 *end = a.scratch + a.ops_end[p];
     PairResult r;
-    if (u.flags & UNIT_S32) r = traceback_pair<S32>(u, half, G, u.regs, a.trace, a.carry, a.lastrow, a.strategy[p], end);
-    else                    r = traceback_pair<S16x2>(u, half, G, u.regs, a.trace, a.carry, a.lastrow, a.strategy[p], end);
+    const u32 *cb = a.colbest + (size_t)(pu >> 1) * 4u;
+    if (u.flags & UNIT_S32) r = traceback_pair<S32>(u, half, G, u.regs, a.trace, cb, a.lastrow, a.strategy[p], end);
+    else                    r = traceback_pair<S16x2>(u, half, G, u.regs, a.trace, cb, a.lastrow, a.strategy[p], end);
     a.offsets[p] = r.offset;
     a.n_ops[p] = r.n_ops;
 }
