@@ -11,6 +11,14 @@
 
 namespace mglsw {
 
+/*
+ * Resident blocks per SM the register allocation must allow.  A lane needs about 4 K + 48
+ * registers; the kernel is issue-bound with both integer pipes near 70 % (profiles/), and the
+ * fraction of issue slots it fills grows with the warps per scheduler (3 at 168 registers, 4 at
+ * 128), so the allocation is capped where that costs no spill inside the step loop.
+ */
+constexpr int fill_min_blocks(int K) { return K <= 5 ? 6 : K <= 11 ? 5 : K <= 20 ? 4 : 3; }
+
 template <class T, int G, int K>
 __global__ void __launch_bounds__(MGLSW_FILL_THREADS)
 sw_fill_kernel(const __grid_constant__ FillArgs a, const u32 first_unit)
