@@ -84,7 +84,7 @@ MGL_SW_API const char *mgl_sw_last_error(mgl_sw_handle *h);
 MGL_SW_API int mgl_sw_device_count(void);
 MGL_SW_API const char *mgl_sw_version(void);
 
-/* tuning knobs: "allow_s16" 0/1, "chunk_pairs", "trace_budget_mb", "overlap" 0/1 (resident_run: 1 = chunks
+/* tuning knobs: "allow_s16" 0/1, "chunk_pairs", "trace_budget_mb", "plan_threads", "overlap" 0/1 (resident_run: 1 = chunks
    alternate between two slots, whole-batch time only; 0 = one chunk at a time with per-kernel times) */
 MGL_SW_API int mgl_sw_set_option(mgl_sw_handle *h, const char *name, int64_t value);
 

@@ -2,7 +2,11 @@
 #include "sw_engine.h"
 
 #include <algorithm>
+#include <atomic>
+#include <condition_variable>
 #include <cstring>
+#include <mutex>
+#include <thread>
 
 #include "../../include/mgl_sw.h"
 #include "sw_cell.h"
@@ -48,7 +52,6 @@ void WorkSlot::release()
     trace.release(); carry.release(); lastrow.release(); colbest.release(); scratch.release();
     offsets.release(); n_ops.release(); starts.release(); ops.release();
     h_n_ops.release(); h_total.release();
-    chunk.release();
     if (ev_counts) cudaEventDestroy(ev_counts);
     if (ev_done) cudaEventDestroy(ev_done);
     if (ev_fill) cudaEventDestroy(ev_fill);
@@ -81,6 +84,7 @@ Engine::~Engine()
 {
     cudaSetDevice(device_);
     drop_resident();
+    for (ChunkDev *cd : ring_) { cd->release(); delete cd; }
     for (auto &s : slots_) s.release();
     for (auto &e : tev_) if (e) cudaEventDestroy(e);
     arena_.release();
@@ -119,13 +123,12 @@ u64 Engine::budget()
 }
 
 /*
- * Plan the chunk that starts at pair `first`: at most chunk_pairs pairs, and
- * as many as keep the estimated trace (0.5 B per padded cell) inside the budget.
+ * How many pairs the chunk starting at `first` takes: at most chunk_pairs, and as many as keep
+ * the estimated trace (0.5 B per padded cell) inside the budget.
  */
-int Engine::plan_next(const BatchIn &in, int64_t first, ChunkDev &cd)
+int64_t Engine::chunk_take(const BatchIn &in, int64_t first, u64 limit) const
 {
-    const u64 limit = budget();
-    int64_t n = std::min<int64_t>(in.n - first, chunk_pairs);
+    const int64_t n = std::min<int64_t>(in.n - first, chunk_pairs);
     u64 est = 0;
     int64_t take = 0;
     for (; take < n; take++) {
@@ -134,34 +137,54 @@ int Engine::plan_next(const BatchIn &in, int64_t first, ChunkDev &cd)
         if (take > 0 && est + bytes > limit) break;
         est += bytes;
     }
-    std::vector<PairIn> pairs((size_t)take);
+    return take;
+}
+
+/*
+ * Plan pairs [first, first + take) into cd and stage the descriptors in pinned memory.  Touches
+ * nothing of the engine but read-only options, so planner threads run it concurrently.
+ */
+int Engine::plan_range(const BatchIn &in, int64_t first, int64_t take, ChunkDev &cd, std::string &err) const
+{
+    std::vector<PairIn> &pairs = cd.pairs_scratch;
+    pairs.resize((size_t)take);
     for (int64_t k = 0; k < take; k++) {
         PairIn &p = pairs[(size_t)k];
         p.ref_off = in.ref_off[first + k]; p.alt_off = in.alt_off[first + k];
         p.tl = in.ref_len[first + k]; p.ql = in.alt_len[first + k];
         p.strategy = in.strategies ? in.strategies[first + k] : in.strategy;
-        if (p.ref_off + p.tl > in.arena_bytes || p.alt_off + p.ql > in.arena_bytes)
-            return fail(MGL_SW_E_INVALID, "pair " + std::to_string(first + k) + " lies outside the arena");
+        if (p.ref_off + p.tl > in.arena_bytes || p.alt_off + p.ql > in.arena_bytes) {
+            err = "pair " + std::to_string(first + k) + " lies outside the arena";
+            return MGL_SW_E_INVALID;
+        }
     }
     const PlanStatus ps = plan_chunk(pairs.data(), (u32)take, in.scores, allow_s16, cd.plan);
-    if (ps == PLAN_BAD_SCORES) return fail(MGL_SW_E_SCORES, "score set out of range");
-    if (ps == PLAN_BAD_PAIR) return fail(MGL_SW_E_PAIR, "empty or over-long sequence in batch");
+    if (ps == PLAN_BAD_SCORES) { err = "score set out of range"; return MGL_SW_E_SCORES; }
+    if (ps == PLAN_BAD_PAIR) { err = "empty or over-long sequence in batch"; return MGL_SW_E_PAIR; }
     cd.first = first;
     cd.n = (u32)take;
 
     /* stage descriptors in pinned memory so the uploads are asynchronous */
     cudaError_t e;
     const size_t nu = cd.plan.units.size();
-    if ((e = cd.h_units.reserve(nu * sizeof(UnitDesc))) != cudaSuccess) return cuda_fail(e, "pinned alloc");
-    if ((e = cd.h_pair_unit.reserve(take * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "pinned alloc");
-    if ((e = cd.h_ops_end.reserve(take * sizeof(u64))) != cudaSuccess) return cuda_fail(e, "pinned alloc");
-    if ((e = cd.h_strategy.reserve(take * sizeof(int))) != cudaSuccess) return cuda_fail(e, "pinned alloc");
+    if ((e = cd.h_units.reserve(nu * sizeof(UnitDesc))) != cudaSuccess || (e = cd.h_pair_unit.reserve(take * sizeof(u32))) != cudaSuccess ||
+        (e = cd.h_ops_end.reserve(take * sizeof(u64))) != cudaSuccess || (e = cd.h_strategy.reserve(take * sizeof(int))) != cudaSuccess) {
+        err = std::string("pinned alloc: ") + cudaGetErrorString(e);
+        return MGL_SW_E_CUDA;
+    }
     std::memcpy(cd.h_units.p, cd.plan.units.data(), nu * sizeof(UnitDesc));
     std::memcpy(cd.h_pair_unit.p, cd.plan.pair_unit.data(), take * sizeof(u32));
     std::memcpy(cd.h_ops_end.p, cd.plan.ops_end.data(), take * sizeof(u64));
     int *st = (int *)cd.h_strategy.p;
     for (int64_t k = 0; k < take; k++) st[k] = pairs[(size_t)k].strategy;
     return MGL_SW_OK;
+}
+
+int Engine::plan_next(const BatchIn &in, int64_t first, ChunkDev &cd)
+{
+    std::string err;
+    const int rc = plan_range(in, first, chunk_take(in, first, budget()), cd, err);
+    return rc == MGL_SW_OK ? rc : fail(rc, err);
 }
 
 int Engine::upload_chunk(const BatchIn &in, ChunkDev &cd, cudaStream_t st, bool upload_arena, BatchStats &bs)
@@ -264,11 +287,8 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed)
     bs.cells += cd.plan.cells;
     bs.pairs += cd.n;
     bs.trace_bytes += cd.plan.trace_words * 4;
-    for (const UnitDesc &u : cd.plan.units) {
-        if (!(u.flags & UNIT_ACTIVE)) continue;
-        const u64 k = 1 + (u.pair[1] != NO_PAIR ? 1 : 0);
-        if (u.flags & UNIT_S32) bs.pairs_s32 += k; else bs.pairs_s16 += k;
-    }
+    bs.pairs_s16 += cd.plan.pairs_s16;
+    bs.pairs_s32 += cd.plan.pairs_s32;
     if (timed) {
         if ((e = cudaEventSynchronize(tev_[4])) != cudaSuccess) return cuda_fail(e, "chunk sync");
         float a = 0, b = 0, c = 0;
@@ -344,17 +364,77 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         return MGL_SW_OK;
     };
 
-    int64_t first = 0;
+    /*
+     * Chunk boundaries first (a cheap scan), then the chunks are planned by a few host threads
+     * running ahead of the GPU into a ring of staging entries, while this thread uploads,
+     * launches and collects them in order.  Entry c % R is reused once chunk c - R has been
+     * collected; R = planners + 3 keeps every planner busy without blocking the collector.
+     */
+    std::vector<std::pair<int64_t, int64_t>> bounds;
+    {
+        const u64 limit = budget();
+        for (int64_t f0 = 0; f0 < in.n;) { const int64_t t = chunk_take(in, f0, limit); bounds.emplace_back(f0, t); f0 += t; }
+    }
+    const int nchunks = (int)bounds.size();
+    int nthreads = plan_threads > 0 ? plan_threads : (int)std::min<unsigned>(8u, std::max(1u, std::thread::hardware_concurrency() / 2));
+    nthreads = std::min(nthreads, nchunks);
+    const int R = nthreads + 3;
+    while ((int)ring_.size() < R) ring_.push_back(new ChunkDev());
+    std::vector<int> ready((size_t)nchunks, 0);          /* 0 pending, 1 planned, 2 failed */
+    std::vector<int> prc((size_t)nchunks, MGL_SW_OK);
+    std::vector<std::string> perr((size_t)nchunks);
+    std::mutex mu;
+    std::condition_variable cv;
+    int collected = 0;                                   /* chunks [0, collected) have released their ring entry */
+    bool stop = false;
+    std::atomic<int> next_chunk{0};
+    auto planner = [&]() {
+        cudaSetDevice(device_);
+        for (;;) {
+            const int k = next_chunk.fetch_add(1);
+            if (k >= nchunks) return;
+            {
+                std::unique_lock<std::mutex> lk(mu);
+                cv.wait(lk, [&] { return stop || k - collected < R; });
+                if (stop) return;
+            }
+            const int prc_k = plan_range(in, bounds[(size_t)k].first, bounds[(size_t)k].second, *ring_[(size_t)(k % R)], perr[(size_t)k]);
+            {
+                std::lock_guard<std::mutex> lk(mu);
+                prc[(size_t)k] = prc_k;
+                ready[(size_t)k] = prc_k == MGL_SW_OK ? 1 : 2;
+            }
+            cv.notify_all();
+        }
+    };
+    std::vector<std::thread> workers;
+    if (nchunks > 1) for (int t = 0; t < nthreads; t++) workers.emplace_back(planner);
+    auto release_upto = [&](int k) {                     /* chunks below k are collected */
+        { std::lock_guard<std::mutex> lk(mu); if (k > collected) collected = k; }
+        cv.notify_all();
+    };
+
     int c = 0;
-    while (first < in.n && rc == MGL_SW_OK) {
+    for (; c < nchunks && rc == MGL_SW_OK; c++) {
         const int si = c & 1;
         WorkSlot &ws = slots_[si];
-        if ((rc = finish(si)) != MGL_SW_OK) break;              /* normally already free */
-        if ((rc = plan_next(in, first, ws.chunk)) != MGL_SW_OK) break;
-        if ((rc = ensure_slot(ws, ws.chunk.plan, ws.chunk.n)) != MGL_SW_OK) break;
-        if ((rc = upload_chunk(in, ws.chunk, ws.stream, !whole, bs)) != MGL_SW_OK) break;
-        if ((rc = run_chunk(ws.chunk, ws, bs, false)) != MGL_SW_OK) break;
-        const u32 n = ws.chunk.n;
+        ChunkDev &cd = *ring_[(size_t)(c % R)];
+        if (nchunks == 1) {
+            std::string err;
+            rc = plan_range(in, bounds[0].first, bounds[0].second, cd, err);
+            if (rc != MGL_SW_OK) { fail(rc, err); break; }
+        } else {
+            std::unique_lock<std::mutex> lk(mu);
+            cv.wait(lk, [&] { return ready[(size_t)c] != 0; });
+            if (ready[(size_t)c] == 2) { rc = fail(prc[(size_t)c], perr[(size_t)c]); break; }
+        }
+        if ((rc = finish(si)) != MGL_SW_OK) break;              /* chunk c - 2: normally already home */
+        release_upto(c - 1);
+        const int64_t first = cd.first;
+        if ((rc = ensure_slot(ws, cd.plan, cd.n)) != MGL_SW_OK) break;
+        if ((rc = upload_chunk(in, cd, ws.stream, !whole, bs)) != MGL_SW_OK) break;
+        if ((rc = run_chunk(cd, ws, bs, false)) != MGL_SW_OK) break;
+        const u32 n = cd.n;
         if ((e = cudaMemcpyAsync(out.offsets + first, ws.offsets.p, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess) { rc = cuda_fail(e, "D2H offsets"); break; }
         if ((e = cudaMemcpyAsync(ws.h_n_ops.p, ws.n_ops.p, (size_t)n * sizeof(u32), cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess) { rc = cuda_fail(e, "D2H counts"); break; }
         if ((e = cudaMemcpyAsync((u32 *)ws.h_n_ops.p + n, (u32 *)ws.starts.p + n, sizeof(u32), cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess) { rc = cuda_fail(e, "D2H total"); break; }
@@ -362,11 +442,13 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         cudaEventRecord(ws.ev_counts, ws.post);
         cudaEventRecord(ws.ev_post, ws.post);
         fl[si].busy = true; fl[si].first = first; fl[si].n = n;
-        first += n;
-        c++;
         /* while this chunk runs, bring the previous one home */
         if ((rc = finish(si ^ 1)) != MGL_SW_OK) break;
+        release_upto(c);
     }
+    { std::lock_guard<std::mutex> lk(mu); stop = true; }
+    cv.notify_all();
+    for (std::thread &t : workers) t.join();
     if (rc == MGL_SW_OK) rc = finish(c & 1);                    /* older chunk first (if any) */
     if (rc == MGL_SW_OK) rc = finish((c & 1) ^ 1);
     if (rc != MGL_SW_OK) {

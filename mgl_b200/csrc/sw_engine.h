@@ -67,6 +67,7 @@ struct ChunkDev {
     int64_t first = 0; u32 n = 0;
     DevBuf units, pair_unit, ops_end, strategy;
     PinBuf h_units, h_pair_unit, h_ops_end, h_strategy;
+    std::vector<PairIn> pairs_scratch;
     void release();
 };
 
@@ -78,7 +79,6 @@ struct WorkSlot {
     cudaEvent_t ev_fill = nullptr, ev_post = nullptr, ev_counts = nullptr, ev_done = nullptr;
     DevBuf trace, carry, lastrow, colbest, scratch, offsets, n_ops, starts, ops;
     PinBuf h_n_ops, h_total;
-    ChunkDev chunk;              /* descriptors of the chunk in flight (streaming mode) */
     void release();
 };
 
@@ -103,12 +103,15 @@ public:
     bool overlap = true;         /* run_resident: alternate the two slots so traceback(c) overlaps fill(c + 1);
                                     false = one chunk at a time with per-kernel event timing */
     u32 chunk_pairs = 1u << 17;
+    int plan_threads = 0;        /* host planner threads of align_batch; 0: min(8, hardware threads / 2) */
     u64 trace_budget_bytes = 0;  /* 0: derived from free memory */
 
 private:
     int fail(int code, const std::string &msg);
     int cuda_fail(cudaError_t e, const char *what);
     int plan_next(const BatchIn &in, int64_t first, ChunkDev &cd);
+    int64_t chunk_take(const BatchIn &in, int64_t first, u64 limit) const;
+    int plan_range(const BatchIn &in, int64_t first, int64_t take, ChunkDev &cd, std::string &err) const;
     int upload_chunk(const BatchIn &in, ChunkDev &cd, cudaStream_t st, bool upload_arena, BatchStats &bs);
     int run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed);
     int ensure_slot(WorkSlot &ws, const ChunkPlan &plan, u32 n);
@@ -120,6 +123,7 @@ private:
     const uint8_t *arena_dev() const { return (const uint8_t *)arena_.p + MGLSW_ARENA_FRONT_PAD; }
     int reserve_arena(const BatchIn &in);
     WorkSlot slots_[2];
+    std::vector<ChunkDev *> ring_;           /* align_batch: staging entries the planner threads fill */
     std::vector<ChunkDev *> resident_;
     std::vector<DevBuf> resident_results_;   /* per chunk: offsets | starts | ops kept on device */
     Scores resident_scores_{};

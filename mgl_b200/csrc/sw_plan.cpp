@@ -165,6 +165,7 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
             u.ql = a.ql;
             out.pair_unit[p0] = (u32)out.units.size() * 2;
             L.cells += (u64)a.tl * a.ql;
+            (L.kind == KIND_S32 ? out.pairs_s32 : out.pairs_s16)++;
             q++;
             if (L.kind == KIND_S16X2 && q < end && pair_key(order[q].key) == pair_key(order[q - 1].key)) {
                 const u32 p1 = order[q].idx;
@@ -172,6 +173,7 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
                 u.pair[1] = p1; u.ref_off[1] = b.ref_off; u.alt_off[1] = b.alt_off; u.tl[1] = b.tl;
                 out.pair_unit[p1] = (u32)out.units.size() * 2 + 1;
                 L.cells += (u64)b.tl * b.ql;
+                out.pairs_s16++;
                 q++;
             }
             u.nstrips = L.nstrips;

@@ -43,6 +43,7 @@ struct ChunkPlan {
     u64 lastrow_words = 0;
     u64 scratch_words = 0;
     u64 cells = 0;                  /* sum tl * ql */
+    u64 pairs_s16 = 0, pairs_s32 = 0;
     int s16_bias = 0;
 };
 
