@@ -126,9 +126,9 @@ u64 Engine::budget()
  * How many pairs the chunk starting at `first` takes: at most chunk_pairs, and as many as keep
  * the estimated trace (0.5 B per padded cell) inside the budget.
  */
-int64_t Engine::chunk_take(const BatchIn &in, int64_t first, u64 limit) const
+int64_t Engine::chunk_take(const BatchIn &in, int64_t first, u64 limit, u32 max_pairs) const
 {
-    const int64_t n = std::min<int64_t>(in.n - first, chunk_pairs);
+    const int64_t n = std::min<int64_t>(in.n - first, max_pairs ? max_pairs : chunk_pairs);
     u64 est = 0;
     int64_t take = 0;
     for (; take < n; take++) {
@@ -183,7 +183,7 @@ int Engine::plan_range(const BatchIn &in, int64_t first, int64_t take, ChunkDev 
 int Engine::plan_next(const BatchIn &in, int64_t first, ChunkDev &cd)
 {
     std::string err;
-    const int rc = plan_range(in, first, chunk_take(in, first, budget()), cd, err);
+    const int rc = plan_range(in, first, chunk_take(in, first, budget(), 0), cd, err);
     return rc == MGL_SW_OK ? rc : fail(rc, err);
 }
 
@@ -373,7 +373,14 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
     std::vector<std::pair<int64_t, int64_t>> bounds;
     {
         const u64 limit = budget();
-        for (int64_t f0 = 0; f0 < in.n;) { const int64_t t = chunk_take(in, f0, limit); bounds.emplace_back(f0, t); f0 += t; }
+        /* the first chunks are small (1/8, 1/4, 1/2 of chunk_pairs): the GPU starts after one short plan, not a full one */
+        for (int64_t f0 = 0; f0 < in.n;) {
+            const size_t k = bounds.size();
+            const u32 cap = k < 3 ? std::max<u32>(chunk_pairs >> (3 - k), std::min<u32>(chunk_pairs, 4096u)) : chunk_pairs;
+            const int64_t t = chunk_take(in, f0, limit, cap);
+            bounds.emplace_back(f0, t);
+            f0 += t;
+        }
     }
     const int nchunks = (int)bounds.size();
     int nthreads = plan_threads > 0 ? plan_threads : (int)std::min<unsigned>(8u, std::max(1u, std::thread::hardware_concurrency() / 2));

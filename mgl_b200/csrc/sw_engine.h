@@ -110,7 +110,7 @@ private:
     int fail(int code, const std::string &msg);
     int cuda_fail(cudaError_t e, const char *what);
     int plan_next(const BatchIn &in, int64_t first, ChunkDev &cd);
-    int64_t chunk_take(const BatchIn &in, int64_t first, u64 limit) const;
+    int64_t chunk_take(const BatchIn &in, int64_t first, u64 limit, u32 max_pairs) const;
     int plan_range(const BatchIn &in, int64_t first, int64_t take, ChunkDev &cd, std::string &err) const;
     int upload_chunk(const BatchIn &in, ChunkDev &cd, cudaStream_t st, bool upload_arena, BatchStats &bs);
     int run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed);
