@@ -246,7 +246,7 @@ int mgl_sw_plan_summary(const mgl_sw_batch *batch, int allow_s16, uint64_t *out8
     }
     for (const Launch &L : plan.launches) padded += (uint64_t)L.n_units;
     out8[0] = plan.launches.size(); out8[1] = plan.units.size(); out8[2] = n16; out8[3] = n32;
-    out8[4] = plan.trace_words; out8[5] = plan.cells; out8[6] = plan.scratch_words; out8[7] = padded;
+    out8[4] = plan.ckpt_words; out8[5] = plan.cells; out8[6] = plan.scratch_words; out8[7] = padded;
     return MGL_SW_OK;
 }
 

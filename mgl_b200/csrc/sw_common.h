@@ -70,16 +70,14 @@ SW_HD int boundary_score(int x, int indel, int go, int ge)
  */
 struct CellConsts {
     u32 neg_delta;  /* 32-bit multiplier: -(match - mismatch)                         */
-    u32 go;         /* gap open, replicated                                           */
-    u32 neg_ge;     /* -gap_extend, replicated two's complement                       */
+    u32 neg_ge;     /* -gap_extend, replicated two's complement (per-half add-max)    */
     u32 match;      /* match score, replicated                                        */
-    u32 b1, b2, b3, b4; /* comparison biases, see sw_cell.h                           */
-    u32 one, mone;  /* 1 and 0xffffffff as RUNTIME values: x * one + y and y - x as   */
-                    /* x * mone + y are then integer multiply-adds, which issue to    */
-                    /* the FMA pipe instead of the ALU pipe the DPX instructions use  */
+    u32 one;        /* 1 as a RUNTIME value: x * one + y is then an integer multiply- */
+                    /* add, which issues to the FMA pipe instead of the ALU pipe the  */
+                    /* DPX instructions use                                           */
     u32 neg_go;     /* 0 - go: x + neg_go subtracts gap_open from both halves         */
     int bias;       /* value stored = true score + bias (0 for KIND_S32)              */
-    int s_match, s_go, s_ge;   /* plain scalars for boundary arithmetic               */
+    int s_match, s_mismatch, s_go, s_ge;   /* plain scalars for boundary arithmetic and the traceback's recomputation */
 };
 
 /*
@@ -89,7 +87,8 @@ struct CellConsts {
 struct UnitDesc {
     u64 ref_off[2];      /* byte offsets of the two refs in the sequence arena        */
     u64 alt_off[2];
-    u64 trace_off;       /* word offset of the owning warp's trace region             */
+    u64 col_off;         /* word offset of the owning warp's column checkpoints       */
+    u64 row_off;         /* word offset of the owning warp's row checkpoints          */
     u64 carry_off;       /* uint2 index of this unit's two strip-carry columns        */
     u64 lastrow_off;     /* word offset of this unit's last-row capture               */
     u32 pair[2];         /* chunk-local pair ids; NO_PAIR: half unused                */
@@ -99,7 +98,7 @@ struct UnitDesc {
     u32 nstrips;         /* column strips (same for every group of the warp)          */
     u32 col_base;        /* columns per lane slot: col_base or col_base + 1           */
     u32 col_rem;         /* the first col_rem slots get col_base + 1                  */
-    u32 rb_count;        /* trace row blocks per strip                                */
+    u32 rb_count;        /* row blocks (of MGLSW_RB steps) per strip                  */
     u32 carry_rows;      /* rows per carry column = own max tl + 1                    */
     u32 flags;           /* UNIT_* bits                                               */
     u32 group;           /* lane group index inside the warp                          */

@@ -49,7 +49,7 @@ void ChunkDev::release()
 
 void WorkSlot::release()
 {
-    trace.release(); carry.release(); lastrow.release(); colbest.release(); scratch.release();
+    ckpt.release(); carry.release(); lastrow.release(); colbest.release(); scratch.release();
     offsets.release(); n_ops.release(); starts.release(); ops.release();
     h_n_ops.release(); h_total.release();
     if (ev_counts) cudaEventDestroy(ev_counts);
@@ -124,7 +124,7 @@ u64 Engine::budget()
 
 /*
  * How many pairs the chunk starting at `first` takes: at most chunk_pairs, and as many as keep
- * the estimated trace (0.5 B per padded cell) inside the budget.
+ * the estimated checkpoints inside the budget.
  */
 int64_t Engine::chunk_take(const BatchIn &in, int64_t first, u64 limit, u32 max_pairs) const
 {
@@ -133,7 +133,7 @@ int64_t Engine::chunk_take(const BatchIn &in, int64_t first, u64 limit, u32 max_
     int64_t take = 0;
     for (; take < n; take++) {
         const u64 tl = in.ref_len[first + take], ql = in.alt_len[first + take];
-        const u64 bytes = (tl + 40) * (ql + 32) / 2 * 5 / 4;     /* padded rows/cols + 25 % */
+        const u64 bytes = (tl + 40) * (ql + 32) * 7 / 5;         /* checkpoints: 0.65 (u16x2) .. 1.3 (s32) B per padded cell */
         if (take > 0 && est + bytes > limit) break;
         est += bytes;
     }
@@ -220,7 +220,7 @@ int Engine::upload_chunk(const BatchIn &in, ChunkDev &cd, cudaStream_t st, bool 
 int Engine::ensure_slot(WorkSlot &ws, const ChunkPlan &plan, u32 n)
 {
     cudaError_t e;
-    if ((e = ws.trace.reserve((plan.trace_words + 4) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc trace");
+    if ((e = ws.ckpt.reserve((plan.ckpt_words + 4) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc checkpoints");
     if ((e = ws.carry.reserve((plan.carry_entries + 1) * sizeof(Carry))) != cudaSuccess) return cuda_fail(e, "cudaMalloc carry");
     if ((e = ws.lastrow.reserve((plan.lastrow_words + 1) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc lastrow");
     if ((e = ws.colbest.reserve((plan.units.size() + 1) * 4 * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc colbest");
@@ -249,7 +249,7 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed)
         FillArgs a;
         a.arena = arena_dev();
         a.units = (const UnitDesc *)cd.units.p;
-        a.trace = (u32 *)ws.trace.p;
+        a.ckpt = (u32 *)ws.ckpt.p;
         a.carry = (Carry *)ws.carry.p;
         a.lastrow = (u32 *)ws.lastrow.p;
         a.colbest = (u32 *)ws.colbest.p;
@@ -265,16 +265,18 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed)
     if (timed) cudaEventRecord(tev_[2], pt);
     TraceArgs t;
     t.units = (const UnitDesc *)cd.units.p;
-    t.pair_unit = (const u32 *)cd.pair_unit.p;
     t.ops_end = (const u64 *)cd.ops_end.p;
     t.strategy = (const int *)cd.strategy.p;
-    t.trace = (const u32 *)ws.trace.p;
+    t.ckpt = (const u32 *)ws.ckpt.p;
+    t.arena = arena_dev();
+    t.c16 = make_consts<S16x2>(sc, cd.plan.s16_bias);
+    t.c32 = make_consts<S32>(sc, 0);
     t.colbest = (const u32 *)ws.colbest.p;
     t.lastrow = (const u32 *)ws.lastrow.p;
     t.scratch = (u32 *)ws.scratch.p;
     t.offsets = (int *)ws.offsets.p;
     t.n_ops = (u32 *)ws.n_ops.p;
-    t.n_pairs = cd.n;
+    t.n_units = (u32)cd.plan.units.size();
     if ((e = launch_traceback(t, pt)) != cudaSuccess) return cuda_fail(e, "traceback launch");
     if (timed) cudaEventRecord(tev_[3], pt);
     if ((e = launch_scan_counts((const u32 *)ws.n_ops.p, (u32 *)ws.starts.p, cd.n, pt)) != cudaSuccess) return cuda_fail(e, "scan launch");
@@ -286,7 +288,7 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed)
     bs.chunks++;
     bs.cells += cd.plan.cells;
     bs.pairs += cd.n;
-    bs.trace_bytes += cd.plan.trace_words * 4;
+    bs.trace_bytes += cd.plan.ckpt_words * 4;
     bs.pairs_s16 += cd.plan.pairs_s16;
     bs.pairs_s32 += cd.plan.pairs_s32;
     if (timed) {

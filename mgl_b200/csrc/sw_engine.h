@@ -44,7 +44,7 @@ struct BatchOut {
 struct BatchStats {              /* filled by every run */
     uint64_t cells, pairs, pairs_s16, pairs_s32;
     uint64_t fill_launches, other_launches, chunks;
-    uint64_t trace_bytes;        /* trace words written * 4 */
+    uint64_t trace_bytes;        /* checkpoint words written * 4 */
     uint64_t h2d_bytes, d2h_bytes;
     double fill_ms, trace_ms, post_ms, device_ms;   /* device_ms etc. only from run_resident */
 };
@@ -77,7 +77,7 @@ struct WorkSlot {
                                          /* latency-bound traceback of one chunk slips in between the blocks of */
                                          /* the other slot's fill instead of queueing behind them               */
     cudaEvent_t ev_fill = nullptr, ev_post = nullptr, ev_counts = nullptr, ev_done = nullptr;
-    DevBuf trace, carry, lastrow, colbest, scratch, offsets, n_ops, starts, ops;
+    DevBuf ckpt, carry, lastrow, colbest, scratch, offsets, n_ops, starts, ops;
     PinBuf h_n_ops, h_total;
     void release();
 };

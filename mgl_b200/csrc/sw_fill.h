@@ -4,8 +4,10 @@
  * Replaces the reference's fill loops (calculateMatrix sw.cpp:5-146 and its
  * AVX2 twin calculateMatrix_avx sw_avx.cpp:110-322) with a strip-mined
  * wavefront: a group of G lanes sweeps the ref rows, each lane holding K
- * adjacent alt columns in registers (H of the previous row, E, the alt bytes
- * and a 4-bit-per-cell trace accumulator).  Lane l is one row behind lane
+ * adjacent alt columns in registers (H of the previous row, E and the alt
+ * bytes).  It keeps no per-cell record: it parks (H, F) of two columns per
+ * lane every step and (H, E) of every column every MGLSW_RB steps
+ * (sw_layout.h), from which the traceback recomputes the cells on its path.  Lane l is one row behind lane
  * l - 1; the two values that cross a lane boundary (H and F of the lane's last
  * real column) travel by warp shuffle.  Alt lengths beyond G * K columns are
  * processed as several strips (G == 32 only); the last lane of a strip parks
@@ -44,7 +46,7 @@ SW_HD u64 arena_tail_pad(u32 max_ref_len) { return (u64)max_ref_len + 64u; }
 struct FillArgs {
     const uint8_t *arena;     /* raw sequence bytes; readable on [-FRONT_PAD, bytes + arena_tail_pad(max tl)) */
     const UnitDesc *units;    /* units of this launch, (32 / G) per warp              */
-    u32 *trace;               /* trace buffer (word offsets in UnitDesc)              */
+    u32 *ckpt;                /* column and row checkpoints (word offsets in UnitDesc) */
     Carry *carry;             /* strip carry columns (G == 32 launches only)          */
     u32 *lastrow;             /* captured last rows                                   */
     u32 *colbest;             /* per unit 4 words: (value, row) of the last-column maximum of each half */
@@ -54,9 +56,11 @@ struct FillArgs {
 
 template <class T, int G, int K>
 struct FillLane {
-    static constexpr int Q = (K + 3) / 4;
+    static constexpr int SC = ((K + 1) / 2 + 3) / 4;   /* chunks per section of a row checkpoint */
+    static constexpr int Q2 = 4 * SC;                  /* 16-byte chunks of a row checkpoint     */
+    static constexpr int KM = (K + 1) / 2;       /* registers before the mid checkpoint   */
     static constexpr bool STRIPS = (G == 32);    /* lane groups of 8 always cover the alt in one strip */
-    u32 e[K], hm[K], bq[K], acc[K];
+    u32 e[K], hm[K], bq[K];
     u32 hleft;                /* H[i-1][first col - 1] + match: diagonal input of register 0 */
     u32 h_out, f_out;         /* this step's values for the right-hand neighbour      */
     u32 ra_next;              /* ref bytes of the next step's row (prefetched)        */
@@ -75,8 +79,8 @@ struct FillLane {
     u32 slot, nslots;
     u32 indel, active, strip, nstrips, rb_count;
     u32 col_base, col_rem;
-    u32 *trace_base;          /* trace words of the warp region                       */
-    u32 *trace_cur;           /* ... of the current strip                             */
+    u32 *col_base_p, *row_base_p;   /* the warp's column / row checkpoint regions      */
+    u32 *col_cur, *row_cur;         /* ... of the current strip, at this lane's slot   */
     Carry *carry_cols;        /* two columns of carry_rows entries                    */
     u32 carry_rows;
     u32 *lastrow;             /* PAIRS regions of nslots * K words                    */
@@ -109,8 +113,10 @@ struct FillLane {
         rb_count = u.rb_count;
         indel = (u.flags & UNIT_INDEL) ? 1u : 0u;
         active = (u.flags & UNIT_ACTIVE) ? 1u : 0u;
-        trace_base = a.trace + u.trace_off;
-        trace_cur = trace_base;
+        col_base_p = a.ckpt + u.col_off;
+        row_base_p = a.ckpt + u.row_off;
+        col_cur = col_base_p;
+        row_cur = row_base_p;
         carry_cols = a.carry + u.carry_off;
         carry_rows = u.carry_rows;
         lastrow = a.lastrow + u.lastrow_off;
@@ -158,7 +164,8 @@ struct FillLane {
     SW_HD void strip_begin(const CellConsts &c, u32 s)
     {
         strip = s;
-        trace_cur = trace_base + (size_t)s * strip_trace_words(rb_count, K);
+        col_cur = col_base_p + ((size_t)s * rb_count * MGLSW_RB * 32u + wlane) * 4u;
+        row_cur = row_base_p + ((size_t)s * rb_count * Q2 * 32u + wlane) * 4u;
         slot = s * G + lane;
         n = col_base + (slot < col_rem ? 1u : 0u);
         j0 = 1u + (slot < col_rem ? slot * (col_base + 1) : col_rem * (col_base + 1) + (slot - col_rem) * col_base);
@@ -169,7 +176,6 @@ struct FillLane {
             u32 b = SW_LDG(alt0 + (j - 1));
             if (T::PAIRS == 2) b |= (u32)SW_LDG(alt1 + (j - 1)) << 16;
             bq[k] = b;
-            acc[k] = 0;
         }
         reset_rows(c);
         h_out = T::rep(c.bias);
@@ -215,13 +221,14 @@ struct FillLane {
         u32 diag = hleft;
         hleft = h_in;
         u32 f = f_in;
-        u32 f_km2 = f_in;
+        u32 f_km2 = f_in, f_mid = f_in;
 #pragma unroll
         for (int k = 0; k < K; k++) {
             const u32 old = hm[k];
-            sw_cell<T>(c, ra, bq[k], diag, e[k], f, hm[k], acc[k], (k & 1) != 0);
+            sw_cell<T>(c, ra, bq[k], diag, e[k], f, hm[k]);
             diag = old;
             if (k == K - 2) f_km2 = f;
+            if (k == KM - 1) f_mid = f;
         }
         if (n == (u32)K) { h_out = hm[K - 1]; f_out = f; }
         else             { h_out = K >= 2 ? hm[K >= 2 ? K - 2 : 0] : h_in; f_out = f_km2; }
@@ -260,19 +267,35 @@ struct FillLane {
         }
         if (i == 0) reset_rows(c);
 
-        if ((t % T::SPW) == T::SPW - 1) {
-            u32 *dst = trace_cur + ((size_t)(t / T::SPW) * Q * 32u + wlane) * 4u;
-#pragma unroll
-            for (int q = 0; q < Q; q++) {
-                const u32 w0 = acc[4 * q];
-                const u32 w1 = 4 * q + 1 < K ? acc[4 * q + 1 < K ? 4 * q + 1 : 0] : 0u;
-                const u32 w2 = 4 * q + 2 < K ? acc[4 * q + 2 < K ? 4 * q + 2 : 0] : 0u;
-                const u32 w3 = 4 * q + 3 < K ? acc[4 * q + 3 < K ? 4 * q + 3 : 0] : 0u;
+        /* column checkpoint of this step: what leaves register KM - 1 and what leaves the lane */
+        {
+            u32 *dst = col_cur + (size_t)t * 128u;
 #if SW_ON_DEVICE
-                __stcs(reinterpret_cast<uint4 *>(dst + (size_t)q * 128u), make_uint4(w0, w1, w2, w3));
+            __stcs(reinterpret_cast<uint4 *>(dst), make_uint4(hm[KM - 1], f_mid, h_out, f_out));
+#else
+            dst[0] = hm[KM - 1]; dst[1] = f_mid; dst[2] = h_out; dst[3] = f_out;
+#endif
+        }
+        /* row checkpoint after the last step of a row block: H + match and E of every register */
+        if ((t % MGLSW_RB) == MGLSW_RB - 1) {
+            u32 *dst = row_cur + (size_t)(t / MGLSW_RB) * Q2 * 128u;
+#pragma unroll
+            for (int q = 0; q < Q2; q++) {
+                /* section q / SC: 0 H[0, KM)  1 H[KM, K)  2 E[0, KM)  3 E[KM, K); register = section base + 4 (q % SC) + x */
+                u32 w[4];
+#pragma unroll
+                for (int x = 0; x < 4; x++) {
+                    const int sec = q / SC, off = 4 * (q % SC) + x;
+                    const int reg = (sec & 1) ? KM + off : off;
+                    const bool ok = (sec & 1) ? reg < K : off < KM;
+                    const int rs = ok ? reg : 0;
+                    w[x] = ok ? (sec < 2 ? hm[rs] : e[rs]) : 0u;
+                }
+#if SW_ON_DEVICE
+                __stcs(reinterpret_cast<uint4 *>(dst + (size_t)q * 128u), make_uint4(w[0], w[1], w[2], w[3]));
 #else
                 u32 *p = dst + (size_t)q * 128u;
-                p[0] = w0; p[1] = w1; p[2] = w2; p[3] = w3;
+                p[0] = w[0]; p[1] = w[1]; p[2] = w[2]; p[3] = w[3];
 #endif
             }
         }

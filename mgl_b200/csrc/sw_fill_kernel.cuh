@@ -11,14 +11,6 @@
 
 namespace mglsw {
 
-/*
- * Resident blocks per SM the register allocation must allow.  A lane needs about 4 K + 48
- * registers; the kernel is issue-bound with both integer pipes near 70 % (profiles/), and the
- * fraction of issue slots it fills grows with the warps per scheduler (3 at 168 registers, 4 at
- * 128), so the allocation is capped where that costs no spill inside the step loop.
- */
-constexpr int fill_min_blocks(int K) { return K <= 5 ? 6 : K <= 11 ? 5 : K <= 20 ? 4 : 3; }
-
 template <class T, int G, int K>
 __global__ void __launch_bounds__(MGLSW_FILL_THREADS)
 sw_fill_kernel(const __grid_constant__ FillArgs a, const u32 first_unit)
@@ -31,7 +23,7 @@ sw_fill_kernel(const __grid_constant__ FillArgs a, const u32 first_unit)
 
     FillLane<T, G, K> L;
     L.setup(a, u, wl, ui);
-    const u32 steps = u.rb_count * T::SPW;       /* same for every lane of the warp */
+    const u32 steps = u.rb_count * MGLSW_RB;     /* same for every lane of the warp */
     const u32 nstrips = u.nstrips;
     for (u32 s = 0; s < nstrips; s++) {
         L.strip_begin(a.c, s);

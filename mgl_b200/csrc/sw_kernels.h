@@ -15,16 +15,17 @@ cudaError_t launch_fill_any(int kind, int G, int K, const FillArgs &a, u32 first
 
 struct TraceArgs {
     const UnitDesc *units;
-    const u32 *pair_unit;     /* per pair: unit * 2 + half                      */
     const u64 *ops_end;       /* per pair: end of its scratch region (words)    */
     const int *strategy;      /* per pair                                       */
-    const u32 *trace;
+    const u32 *ckpt;          /* checkpoints written by the fill                */
+    const uint8_t *arena;     /* sequences (padded device arena)                */
+    CellConsts c16, c32;      /* scores (+ bias) of the two arithmetics         */
     const u32 *colbest;       /* per unit 4 words, written by the fill          */
     const u32 *lastrow;
     u32 *scratch;             /* CIGAR elements, written downwards from ops_end */
     int *offsets;             /* out, per pair                                  */
     u32 *n_ops;               /* out, per pair                                  */
-    u32 n_pairs;
+    u32 n_units;              /* units of the chunk (padding units included)    */
 };
 cudaError_t launch_traceback(const TraceArgs &a, cudaStream_t stream);
 

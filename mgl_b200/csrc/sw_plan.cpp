@@ -19,7 +19,7 @@ long long ramp_margin(const Scores &s, int G)
     return (long long)(G + 4) * ((long long)s.match + absll(s.mismatch) + s.go + s.ge);
 }
 
-/* bound on |X - Y| of the four cell predicates (sw_cell.h), see DESIGN.md "difference bounds" */
+/* a coarse magnitude of one cell's score differences; only used to refuse absurd score sets */
 long long diff_bound(const Scores &s)
 {
     const long long g = std::max(s.go, s.ge);
@@ -57,7 +57,7 @@ void radix_sort(std::vector<Keyed> &v)
 PlanStatus check_scores(const Scores &s)
 {
     if (s.match <= 0 && s.mismatch == 0 && s.go == 0 && s.ge == 0) return PLAN_BAD_SCORES;
-    /* 32-bit predicates sit at bits 28..31: the smallest window is 2^28 */
+    /* keeps every intermediate of a cell far inside 32 bits whatever the lengths */
     if (2 * diff_bound(s) >= (1ll << 28)) return PLAN_BAD_SCORES;
     return PLAN_OK;
 }
@@ -72,7 +72,6 @@ static void value_bounds(const Scores &s, u32 tl, u32 ql, int G, long long &lo, 
 bool s16_bounds(const Scores &s, u32 tl, u32 ql, long long &lo, long long &hi)
 {
     value_bounds(s, tl, ql, MGLSW_G_SHORT, lo, hi);
-    if (2 * diff_bound(s) >= 4096) return false;           /* predicate bits 12..15 of each half */
     if (s.match - s.mismatch >= 32768) return false;
     if (tl > 65535u) return false;                         /* the fused last-column maximum packs (value, row) in 32 bits */
     return hi - lo < 65000;
@@ -149,7 +148,6 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
         L.K = (int)regs_per_lane(first.ql, L.nstrips * L.G);
         L.first_unit = (u32)out.units.size();
         L.cells = 0;
-        const u32 spw = L.kind == KIND_S16X2 ? S16x2::SPW : S32::SPW;
         const u32 upw = 32u / (u32)L.G;                          /* units per warp */
 
         u32 q = pos;
@@ -200,12 +198,13 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
             UnitDesc *wu = &out.units[L.first_unit + w * upw];
             u32 tlmax = 0;
             for (u32 g = 0; g < upw; g++) tlmax = std::max(tlmax, wu[g].carry_rows - 1);
-            const u32 rb = row_blocks(tlmax, (u32)L.G, spw);
+            const u32 rb = row_blocks(tlmax, (u32)L.G);
             for (u32 g = 0; g < upw; g++) {
                 wu[g].tlmax = tlmax;
                 wu[g].rb_count = rb;
                 wu[g].group = g;
-                wu[g].trace_off = out.trace_words;
+                wu[g].col_off = out.ckpt_words;
+                wu[g].row_off = out.ckpt_words + warp_col_words(L.nstrips, rb);
                 if (wu[g].flags & UNIT_ACTIVE) {
                     if (L.G == MGLSW_G_LONG) {            /* only strip-mined units hand columns over through HBM */
                         wu[g].carry_off = out.carry_entries;
@@ -215,7 +214,7 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
                     out.lastrow_words += (u64)(L.kind == KIND_S16X2 ? 2 : 1) * L.nstrips * L.G * L.K;
                 }
             }
-            out.trace_words += (u64)L.nstrips * strip_trace_words(rb, (u32)L.K);
+            out.ckpt_words += warp_col_words(L.nstrips, rb) + warp_row_words(L.nstrips, rb, (u32)L.K);
         }
         out.cells += L.cells;
         out.launches.push_back(L);

@@ -38,7 +38,7 @@ struct ChunkPlan {
     std::vector<Launch> launches;
     std::vector<u32> pair_unit;     /* per chunk-local pair: unit index * 2 + half */
     std::vector<u64> ops_end;       /* per pair: one-past-the-end word of its CIGAR scratch */
-    u64 trace_words = 0;
+    u64 ckpt_words = 0;             /* column + row checkpoints of every warp */
     u64 carry_entries = 0;
     u64 lastrow_words = 0;
     u64 scratch_words = 0;

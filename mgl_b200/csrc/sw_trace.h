@@ -1,17 +1,20 @@
 /*
- * sw_trace.h -- endpoint selection and traceback of one pair, from the 4-bit
- * trace the fill wrote.  One thread per pair on the GPU (sw_trace_kernel.cu);
- * SW_HD so the emulator under tests/emu can run the identical code.
+ * sw_trace.h -- endpoint selection and traceback of one pair, recomputing the
+ * cells on the path from the fill's checkpoints.  One thread per pair on the
+ * GPU (sw_trace_kernel.cu); SW_HD so the emulator under tests/emu can run the
+ * identical code.
  *
  * Restates, with the same tie-breaks (paths relative to
  * /root/reference/src/main/native/mgl_sw/):
- *   last-column argmax, ">=" with ascending row            sw.cpp:100-104  (fused into the fill, read back here)
+ *   cell predicates (source of H, open vs extend)          sw.cpp:60-93   (Replay::build, verbatim comparisons)
+ *   last-column argmax, ">=" with ascending row            sw.cpp:100-104 (fused into the fill, read back here)
  *   last-row scan, ">" or equal-and-nearer-the-diagonal    sw.cpp:116-127
  *   traceback start cell per strategy                      sw.cpp:155-170
  *   walk with k-cell gap jumps and run merging             sw.cpp:173-214
  *   overhang post-processing and offset                    sw.cpp:224-248
  *   zero-length elements dropped when printed              sw.cpp:251-252
- * The reference reads a gap length k from its int32 matrix; here k is recovered
+ * The reference reads a gap length k from its int32 matrix; here a cell's record
+ * is four bits (diag-source, F-source, E-extended, F-extended) and k is recovered
  * by following the extend bits: lenF[i][j] = 1 + number of consecutive cells
  * (i, j-1), (i, j-2), ... whose F-extend bit is set (the bit of cell (i, c) says
  * F[i][c+1] extended F[i][c], sw.cpp:84-93); likewise lenE with rows.
@@ -21,35 +24,170 @@
 #include "sw_cell.h"
 #include "sw_fill.h"
 #include "sw_layout.h"
+#include "sw_config.h"
+
+#define MGLSW_KH ((MGLSW_KMAX + 1) / 2)      /* columns of a block: at most half a lane's registers */
 
 namespace mglsw {
 
-struct TraceCursor {
-    const UnitDesc *u;
-    const u32 *trace;
-    u32 G, K, spw, half;
-    u32 slot, reg;           /* position of column J                                  */
-
-    SW_HD void seek(u32 J)   /* J >= 1 */
-    {
-        col_to_slot(*u, J - 1, slot, reg);
-    }
-    SW_HD void left()        /* J -> J - 1 (caller guarantees J - 1 >= 1) */
-    {
-        if (reg > 0) { reg--; return; }
-        slot--;
-        reg = slot_cols(*u, slot) - 1;
-    }
-    SW_HD u32 nibble(u32 I) const
-    {
-        const u64 w = trace_word_index(*u, G, K, spw, I, slot, reg);
 #if SW_ON_DEVICE
-        const u32 v = __ldcg(trace + w);
+#define SW_LDCG(p) __ldcg(p)
 #else
-        const u32 v = trace[w];
+#define SW_LDCG(p) (*(p))
 #endif
-        return (v >> trace_nibble_shift(G, spw, I, slot, half)) & 15u;
+
+struct W4 { u32 x, y, z, w; };
+struct W2 { u32 x, y; };
+SW_HD W4 load_w4(const u32 *p)
+{
+#if SW_ON_DEVICE
+    const uint4 v = __ldcg(reinterpret_cast<const uint4 *>(p));
+    W4 r; r.x = v.x; r.y = v.y; r.z = v.z; r.w = v.w; return r;
+#else
+    W4 r; r.x = p[0]; r.y = p[1]; r.z = p[2]; r.w = p[3]; return r;
+#endif
+}
+SW_HD W2 load_w2(const u32 *p)
+{
+#if SW_ON_DEVICE
+    const uint2 v = __ldcg(reinterpret_cast<const uint2 *>(p));
+    W2 r; r.x = v.x; r.y = v.y; return r;
+#else
+    W2 r; r.x = p[0]; r.y = p[1]; return r;
+#endif
+}
+
+/*
+ * The block of DP cells around the traceback's current position, recomputed from the
+ * checkpoints that bound it: rows ia..ib of columns ja..jb (1-based, inclusive), one
+ * 4-bit record per cell.  A block never extends below / right of the cell that asked for
+ * it: the traceback only moves up and left.
+ */
+template <class T>
+struct Replay {
+    /* the unit's geometry, copied out of its descriptor once */
+    const u32 *colp, *rowp;              /* checkpoint regions of the warp, at this unit's lane group */
+    const uint8_t *ref, *alt;            /* this pair's sequences */
+    u32 G, K, KM, SC, half, rbc;         /* SC = sec_chunks(K), rbc = row blocks per strip */
+    u32 cb, cr;                          /* col_base, col_rem */
+    int match, mismatch, go, ge, bias, indel;
+    int ia, ib, ja, jb;
+    u64 nib[MGLSW_RB];                   /* row i - ia: nibble of column j at bits 4 (j - ja) */
+    int hlv[MGLSW_RB + 1], fv[MGLSW_RB + 1];
+    u32 rbv[MGLSW_RB + 1];
+    u32 builds, cells;                   /* statistics */
+
+    SW_HD void init(const UnitDesc &u, u32 G_, u32 K_, u32 half_, const u32 *ckpt, const uint8_t *arena, const CellConsts &c)
+    {
+        G = G_; K = K_; KM = regs_mid(K_); SC = sec_chunks(K_); half = half_; rbc = u.rb_count;
+        cb = u.col_base; cr = u.col_rem;
+        colp = ckpt + u.col_off + (size_t)u.group * G_ * 4u;
+        rowp = ckpt + u.row_off + (size_t)u.group * G_ * 4u;
+        ref = arena + u.ref_off[half_]; alt = arena + u.alt_off[half_];
+        match = c.s_match; mismatch = c.s_mismatch; go = c.s_go; ge = c.s_ge; bias = c.bias;
+        indel = (u.flags & UNIT_INDEL) ? 1 : 0;
+        ia = 1; ib = 0; ja = 1; jb = 0; builds = 0; cells = 0;
     }
+
+    SW_HD int bnd(int x) const { return boundary_score(x, indel, go, ge); }
+    SW_HD int hval(u32 w) const { return T::half(w, (int)half) - bias - match; }   /* stored H + match + bias -> H */
+    SW_HD int gval(u32 w) const { return T::half(w, (int)half) - bias; }           /* stored E / F + bias      */
+
+    SW_HD void build(int I, int J)
+    {
+        /* (slot, register) of column J: sw_layout.h col_to_slot */
+        u32 slot, reg;
+        {
+            const u32 col = (u32)J - 1, wide = cr * (cb + 1);
+            if (col < wide) { slot = col / (cb + 1); reg = col - slot * (cb + 1); }
+            else { const u32 c2 = col - wide; slot = cr + c2 / cb; reg = c2 - (slot - cr) * cb; }
+        }
+        const u32 strip = slot / G, lane = slot - strip * G;
+        const bool sub = reg >= KM;
+        const u32 k_lo = sub ? KM : 0u;
+        const int ja_ = (int)(slot < cr ? slot * (cb + 1) : cr * (cb + 1) + (slot - cr) * cb) + 1 + (int)k_lo;
+        const int cnt = (int)(reg - k_lo) + 1;
+        const u32 rb = ((u32)I + lane) / MGLSW_RB;
+        int ia_ = (int)(rb * MGLSW_RB) - (int)lane;
+        if (ia_ < 1) ia_ = 1;
+        const int rows = I - ia_ + 1;                              /* 1 .. MGLSW_RB */
+
+        /* where the left boundary (H[i][ja_ - 1] + match, F[i][ja_]) of row i lives: a column checkpoint of step i + cl */
+        u32 cs = strip, cl = lane, word = 0;
+        if (!sub) { word = 2; if (lane > 0) cl = lane - 1; else { cl = G - 1; cs = strip - 1; } }
+        const bool edge = ja_ == 1;                                /* matrix column 0: no checkpoint, sw.cpp:47-49 and :22-26,38 */
+        const u32 *lp = colp + (((size_t)cs * rbc * MGLSW_RB + cl) * 32u + cl) * 4u + word;   /* + i * 128 */
+
+        /* every load of the block first, all independent: left boundary + corner + ref bytes, row checkpoint, alt bytes */
+#pragma unroll
+        for (int r = 0; r <= (int)MGLSW_RB; r++) {                 /* entry r is row ia_ - 1 + r; entry 0 only yields the corner */
+            const int i = ia_ - 1 + r;
+            int hl = 0, fin = 0; u32 rbyte = 0;
+            if (r <= rows) {
+                if (i >= 1) {
+                    if (edge) { hl = bnd(i); fin = hl - go; }
+                    else { const W2 v = load_w2(lp + (size_t)i * 128u); hl = hval(v.x); fin = gval(v.y); }
+                    rbyte = SW_LDG(ref + (i - 1));
+                } else hl = bnd(ja_ - 1);                          /* row 0: H[0][ja_ - 1] */
+            }
+            hlv[r] = hl; fv[r] = fin; rbv[r] = rbyte;
+        }
+        int Hp[MGLSW_KH], E[MGLSW_KH];
+        u32 ab[MGLSW_KH];
+        {
+            const u32 *rp0 = rowp + ((((size_t)strip * rbc + (rb - 1)) * (4u * SC) + (sub ? SC : 0u)) * 32u + lane) * 4u;
+#pragma unroll
+            for (int q = 0; q < MGLSW_KH / 4; q++) {
+                W4 hv, ev;
+                hv.x = hv.y = hv.z = hv.w = 0; ev = hv;
+                if (ia_ > 1 && 4 * q < cnt) {
+                    hv = load_w4(rp0 + (size_t)q * 128u);
+                    ev = load_w4(rp0 + (size_t)(q + 2 * SC) * 128u);
+                }
+                Hp[4 * q] = hval(hv.x); Hp[4 * q + 1] = hval(hv.y); Hp[4 * q + 2] = hval(hv.z); Hp[4 * q + 3] = hval(hv.w);
+                E[4 * q] = gval(ev.x); E[4 * q + 1] = gval(ev.y); E[4 * q + 2] = gval(ev.z); E[4 * q + 3] = gval(ev.w);
+            }
+        }
+#pragma unroll
+        for (int kk = 0; kk < MGLSW_KH; kk++) {
+            ab[kk] = 0x100u;                                       /* never equals a ref byte */
+            if (kk < cnt) {
+                const int j = ja_ + kk;
+                ab[kk] = SW_LDG(alt + (j - 1));
+                if (ia_ == 1) { const int b = bnd(j); Hp[kk] = b; E[kk] = b - go; }     /* rows 0 / 1 seeds: sw.cpp:10-18,29-35 */
+            }
+        }
+
+        for (int r = 1; r <= rows; r++) {
+            int diag = hlv[r - 1];                                 /* H[i - 1][ja_ - 1] */
+            int f = fv[r];
+            const u32 rbyte = rbv[r];
+            u32 lo = 0, hi = 0;
+#pragma unroll
+            for (int kk = 0; kk < MGLSW_KH; kk++) {
+                /* columns beyond cnt compute garbage that nobody reads (the block ends at column J) */
+                const int d = diag + (rbyte == ab[kk] ? match : mismatch);              /* sw.cpp:55 */
+                const int e = E[kk];
+                int h; u32 nb;
+                if (d >= e && d >= f) { h = d; nb = 8u; }                               /* :60-63 */
+                else if (f >= e)      { h = f; nb = 4u; }                               /* :64-67 */
+                else                  { h = e; nb = 0u; }                               /* :68-71 */
+                const int open = h - go;
+                if (open > e - ge) E[kk] = open; else { E[kk] = e - ge; nb |= 2u; }     /* :73-82, tie => extend */
+                if (open > f - ge) f = open;     else { f = f - ge;     nb |= 1u; }     /* :84-93 */
+                diag = Hp[kk];
+                Hp[kk] = h;
+                if (kk < 8) lo |= nb << (4 * kk); else hi |= nb << (4 * (kk - 8));
+            }
+            nib[r - 1] = (u64)lo | ((u64)hi << 32);
+        }
+        ia = ia_; ib = I; ja = ja_; jb = J;
+        builds++;
+        cells += (u32)(rows * cnt);
+    }
+
+    SW_HD bool inside(int i, int j) const { return i >= ia && i <= ib && j >= ja && j <= jb; }
+    SW_HD u32 at(int i, int j) const { return (u32)(nib[i - ia] >> (4 * (j - ja))) & 15u; }
 };
 
 struct PairResult {
@@ -63,8 +201,8 @@ struct PairResult {
  * downwards so that [ops_end - n_ops, ops_end) reads left to right.
  */
 template <class T>
-SW_HD PairResult traceback_pair(const UnitDesc &u, u32 half, u32 G, u32 K, const u32 *trace,
-                                const u32 *colbest4, const u32 *lastrow, int strategy, u32 *ops_end)
+SW_HD PairResult traceback_pair(const UnitDesc &u, u32 half, u32 G, u32 K, const u32 *ckpt, const uint8_t *arena,
+                                const CellConsts &c, const u32 *colbest4, const u32 *lastrow, int strategy, u32 *ops_end)
 {
     const int tl = (int)u.tl[half], ql = (int)u.ql;
     const u32 nslots = u.nstrips * G;
@@ -102,37 +240,46 @@ SW_HD PairResult traceback_pair(const UnitDesc &u, u32 half, u32 G, u32 K, const
 
     if (run > 0 && strategy == OS_SOFTCLIP) { SW_EMIT(OP_S, run); run = 0; }   /* sw.cpp:173-176 */
 
-    TraceCursor cur;
-    cur.u = &u; cur.trace = trace; cur.G = G; cur.K = K; cur.spw = T::SPW; cur.half = half;
-    cur.seek((u32)J);
+    Replay<T> rp;
+    rp.init(u, G, K, half, ckpt, arena, c);
 
-    u32 state = OP_M;
-    do {                                                                        /* sw.cpp:182-214 */
-        const u32 nb = cur.nibble((u32)I);
-        u32 next; int steplen = 1;
-        if (nb & 8u) {                       /* diagonal */
-            next = OP_M; I--; J--;
-            if (J >= 1) cur.left();
-        } else if (nb & 4u) {                /* horizontal gap: insertion, length lenF[I][J] */
-            next = OP_I;
-            int c = J - 1;
-            while (c >= 1) {
-                cur.left();
-                if (!(cur.nibble((u32)I) & 1u)) break;
-                steplen++; c--;
+    /*
+     * The walk of sw.cpp:182-214 as a state machine around ONE replay site, so that the 32 pairs
+     * of a warp rebuild their blocks together instead of each stalling the others:
+     *   mode 0  at cell (I, J), about to read which of diagonal / F / E produced H
+     *   mode 1  inside an insertion, at cell (I, cc): does F extend through it?
+     *   mode 2  inside a deletion,  at cell (r, J):  does E extend through it?
+     */
+    u32 state = OP_M, next = OP_M;
+    int mode = 0, steplen = 1, cc = 0, r = 0;
+    bool done = false;
+    while (!done) {
+        rp.build(mode == 2 ? r : I, mode == 1 ? cc : J);
+        for (;;) {
+            const int qi = mode == 2 ? r : I, qj = mode == 1 ? cc : J;
+            if (!rp.inside(qi, qj)) break;
+            const u32 nb = rp.at(qi, qj);
+            bool commit = false;
+            if (mode == 0) {
+                steplen = 1;
+                if (nb & 8u) { next = OP_M; I--; J--; commit = true; }           /* diagonal */
+                else if (nb & 4u) { next = OP_I; cc = J - 1; mode = 1; }          /* insertion of length lenF[I][J] */
+                else { next = OP_D; r = I - 1; mode = 2; }                        /* deletion of length lenE[I][J] */
+            } else if (mode == 1) {
+                if (nb & 1u) { steplen++; cc--; } else { J -= steplen; mode = 0; commit = true; }
+            } else {
+                if (nb & 2u) { steplen++; r--; } else { I -= steplen; mode = 0; commit = true; }
             }
-            /* cursor now sits on column c (>= 1) or is stale when c == 0 */
-            J -= steplen;
-            if (J >= 1 && J != c) cur.seek((u32)J);
-        } else {                             /* vertical gap: deletion, length lenE[I][J] */
-            next = OP_D;
-            int r = I - 1;
-            while (r >= 1 && (cur.nibble((u32)r) & 2u)) { steplen++; r--; }
-            I -= steplen;
+            /* a gap that reaches the matrix edge ends there */
+            if (mode == 1 && cc < 1) { J -= steplen; mode = 0; commit = true; }
+            if (mode == 2 && r < 1) { I -= steplen; mode = 0; commit = true; }
+            if (commit) {
+                if (next == state) run += steplen;
+                else { SW_EMIT(state, run); run = steplen; state = next; }
+                if (!(I > 0 && J > 0)) { done = true; break; }
+            }
         }
-        if (next == state) run += steplen;
-        else { SW_EMIT(state, run); run = steplen; state = next; }
-    } while (I > 0 && J > 0);
+    }
 
     PairResult res;
     if (strategy == OS_SOFTCLIP) {                                              /* sw.cpp:225-229 */

@@ -1,5 +1,5 @@
 /*
- * sw_trace_kernel.cu -- endpoint scan + traceback (one thread per pair), and
+ * sw_trace_kernel.cu -- endpoint scan + checkpoint replay + traceback (one thread per pair), and
  * the two small kernels that turn per-pair CIGAR scratch into one dense array.
  * Replaces calculateCigar / calculateCigar_avx (sw.cpp:149-255, sw_avx.cpp:324-430).
  */
@@ -9,27 +9,32 @@
 
 namespace mglsw {
 
-__global__ void __launch_bounds__(128) sw_traceback_kernel(const __grid_constant__ TraceArgs a)
+/*
+ * Thread 2 v + h handles half h of unit v: the threads of a warp walk pairs of one shape bucket
+ * whose checkpoints sit next to each other, instead of 32 unrelated pairs in input order.
+ */
+__global__ void __launch_bounds__(128, 4) sw_traceback_kernel(const __grid_constant__ TraceArgs a)
 {
-    const u32 p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= a.n_pairs) return;
-    const u32 pu = a.pair_unit[p];
-    const UnitDesc &u = a.units[pu >> 1];
-    const u32 half = pu & 1u;
+    const u32 tid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tid >= 2u * a.n_units) return;
+    const UnitDesc &u = a.units[tid >> 1];
+    const u32 half = tid & 1u;
+    const u32 p = u.pair[half];
+    if (!(u.flags & UNIT_ACTIVE) || p == NO_PAIR) return;
     const u32 G = (u.flags & UNIT_G32) ? MGLSW_G_LONG : MGLSW_G_SHORT;
     u32 *end = a.scratch + a.ops_end[p];
+    const u32 *cb = a.colbest + (size_t)(tid >> 1) * 4u;
     PairResult r;
-    const u32 *cb = a.colbest + (size_t)(pu >> 1) * 4u;
-    if (u.flags & UNIT_S32) r = traceback_pair<S32>(u, half, G, u.regs, a.trace, cb, a.lastrow, a.strategy[p], end);
-    else                    r = traceback_pair<S16x2>(u, half, G, u.regs, a.trace, cb, a.lastrow, a.strategy[p], end);
+    if (u.flags & UNIT_S32) r = traceback_pair<S32>(u, half, G, u.regs, a.ckpt, a.arena, a.c32, cb, a.lastrow, a.strategy[p], end);
+    else                    r = traceback_pair<S16x2>(u, half, G, u.regs, a.ckpt, a.arena, a.c16, cb, a.lastrow, a.strategy[p], end);
     a.offsets[p] = r.offset;
     a.n_ops[p] = r.n_ops;
 }
 
 cudaError_t launch_traceback(const TraceArgs &a, cudaStream_t stream)
 {
-    if (a.n_pairs == 0) return cudaSuccess;
-    sw_traceback_kernel<<<(a.n_pairs + 127) / 128, 128, 0, stream>>>(a);
+    if (a.n_units == 0) return cudaSuccess;
+    sw_traceback_kernel<<<(2u * a.n_units + 127) / 128, 128, 0, stream>>>(a);
     return cudaGetLastError();
 }
 

@@ -32,7 +32,7 @@ void emu_launch(const FillArgs &a, const Launch &L)
     for (u32 w = 0; w < L.n_warps; w++) {
         const UnitDesc *wu = a.units + L.first_unit + (size_t)w * upw;
         for (u32 l = 0; l < 32; l++) lanes[l].setup(a, wu[l / G], l, L.first_unit + w * upw + l / G);
-        const u32 steps = wu[0].rb_count * T::SPW;
+        const u32 steps = wu[0].rb_count * MGLSW_RB;
         for (u32 s = 0; s < wu[0].nstrips; s++) {
             for (u32 l = 0; l < 32; l++) lanes[l].strip_begin(a.c, s);
             for (u32 t = 0; t < steps; t++) {
@@ -84,7 +84,7 @@ int emu_align_batch(int n, const uint8_t *arena, const uint64_t *ref_off, const 
     const PlanStatus ps = plan_chunk(pairs.data(), (u32)n, s, allow_s16 != 0, plan);
     if (ps != PLAN_OK) return -(int)ps;
 
-    std::vector<u32> trace(plan.trace_words + 4, 0xdeadbeefu);
+    std::vector<u32> ckpt(plan.ckpt_words + 4, 0xdeadbeefu);
     std::vector<Carry> carry(plan.carry_entries + 1);
     std::vector<u32> colbest(plan.units.size() * 4 + 4, 0);
     /* the fill reads a few bytes outside each ref (sw_fill.h fetch_ref): give the arena the padding the engine gives it */
@@ -103,7 +103,7 @@ int emu_align_batch(int n, const uint8_t *arena, const uint64_t *ref_off, const 
     u32 n16 = 0, n32 = 0;
     for (const Launch &L : plan.launches) {
         FillArgs a;
-        a.arena = arena; a.units = plan.units.data(); a.trace = trace.data();
+        a.arena = arena; a.units = plan.units.data(); a.ckpt = ckpt.data();
         a.carry = carry.data(); a.lastrow = lastrow.data(); a.colbest = colbest.data(); a.n_warps = L.n_warps;
         a.c = L.kind == KIND_S16X2 ? make_consts<S16x2>(s, plan.s16_bias) : make_consts<S32>(s, 0);
         if (!emu_dispatch(a, L)) { std::fprintf(stderr, "emu: no kernel for kind %d G %d K %d\n", L.kind, L.G, L.K); return -10; }
@@ -114,8 +114,8 @@ int emu_align_batch(int n, const uint8_t *arena, const uint64_t *ref_off, const 
         const u32 G = (u.flags & UNIT_G32) ? MGLSW_G_LONG : MGLSW_G_SHORT;
         PairResult r;
         u32 *end = scratch.data() + plan.ops_end[p];
-        if (u.flags & UNIT_S32) { r = traceback_pair<S32>(u, half, G, u.regs, trace.data(), colbest.data() + (size_t)(plan.pair_unit[p] >> 1) * 4, lastrow.data(), strategies[p], end); n32++; }
-        else { r = traceback_pair<S16x2>(u, half, G, u.regs, trace.data(), colbest.data() + (size_t)(plan.pair_unit[p] >> 1) * 4, lastrow.data(), strategies[p], end); n16++; }
+        if (u.flags & UNIT_S32) { r = traceback_pair<S32>(u, half, G, u.regs, ckpt.data(), arena, make_consts<S32>(s, 0), colbest.data() + (size_t)(plan.pair_unit[p] >> 1) * 4, lastrow.data(), strategies[p], end); n32++; }
+        else { r = traceback_pair<S16x2>(u, half, G, u.regs, ckpt.data(), arena, make_consts<S16x2>(s, plan.s16_bias), colbest.data() + (size_t)(plan.pair_unit[p] >> 1) * 4, lastrow.data(), strategies[p], end); n16++; }
         offsets[p] = r.offset;
         n_ops[p] = r.n_ops;
         if ((int)r.n_ops > ops_stride) return -11;
