@@ -66,6 +66,7 @@ struct FillLane {
     u32 ra_next;              /* ref bytes of the next step's row (prefetched)        */
     Carry cin_next;           /* carry-in of the next step's row (strips > 0, lane 0) */
     u32 bh, bf, bdec;         /* column-0 boundary of the next step's row (lane 0), and its per-row decrement */
+    u32 ev_next;              /* step of this lane's next event (events())            */
     u32 best0, best1;         /* running last-column maximum: S16x2 (value << 16 | row) per half; S32 value, row */
 
     /* lane constants */
@@ -181,6 +182,7 @@ struct FillLane {
         h_out = T::rep(c.bias);
         f_out = T::rep(c.bias);
         ra_next = fetch_ref(0);
+        ev_next = lane;                               /* row 0 comes first: tl >= 1 */
         cin_next = fetch_carry(-(int)lane);
         /*
          * Column 0 as lane 0 of strip 0 sees it at step t (row t): H[t][0] + match and the F seed
@@ -193,10 +195,41 @@ struct FillLane {
         bf = T::rep(c.bias - c.s_go + (indel ? -c.s_go + c.s_ge : 0));
     }
 
+    /* row 0: start over from the boundary; row tl of a half: capture its last row and last-column maximum */
+    SW_HD void events(const CellConsts &c, u32 t)
+    {
+        const int i = (int)t - (int)lane;
+        if (active) {
+            const bool owner = (lane == G - 1) && (strip + 1 == nstrips);
+            if (i == (int)tl0) {
+#pragma unroll
+                for (int k = 0; k < K; k++) lastrow[(size_t)slot * K + k] = hm[k];
+                if (owner) {
+                    if (T::PAIRS == 2) { colbest[0] = best0 >> 16; colbest[1] = best0 & 0xffffu; }
+                    else { colbest[0] = best0; colbest[1] = best1; }
+                }
+            }
+            if (T::PAIRS == 2 && i == (int)tl1) {
+#pragma unroll
+                for (int k = 0; k < K; k++) lastrow[(size_t)(nslots + slot) * K + k] = hm[k];
+                if (owner) { colbest[2] = best1 >> 16; colbest[3] = best1 & 0xffffu; }
+            }
+        }
+        if (i == 0) reset_rows(c);
+        u32 nx = 0xffffffffu;
+        const u32 e1 = tl0 + lane, e2 = tl1 + lane;
+        if (e1 > t && e1 < nx) nx = e1;
+        if (e2 > t && e2 < nx) nx = e2;
+        ev_next = nx;
+    }
+
     /*
      * One wavefront step: this lane computes ref row i = t - lane over its K
      * registers.  h_sh / f_sh are the neighbour's previous-step outputs.
+     * EV = false leaves the event check out: the kernel uses it for groups of steps
+     * in which no lane of the warp has an event.
      */
+    template <bool EV = true>
     SW_HD void step(const CellConsts &c, u32 t, u32 h_sh, u32 f_sh)
     {
         const int i = (int)t - (int)lane;
@@ -235,37 +268,27 @@ struct FillLane {
 
         /* running maximum of this lane's last column; meaningful in the lane that owns column ql */
         if (T::PAIRS == 2) {
+#if SW_ON_DEVICE
+            const u32 k0 = __byte_perm((u32)i, h_out, 0x5410);       /* low half of h_out : low 16 bits of the row  */
+            const u32 k1 = __byte_perm((u32)i, h_out, 0x7610);       /* high half of h_out : low 16 bits of the row */
+#else
             const u32 k0 = (h_out << 16) | ((u32)i & 0xffffu);
             const u32 k1 = (h_out & 0xffff0000u) | ((u32)i & 0xffffu);
+#endif
             best0 = k0 > best0 ? k0 : best0;
             best1 = k1 > best1 ? k1 : best1;
         } else if ((int)h_out >= (int)best0) { best0 = h_out; best1 = (u32)i; }
 
-        if (active) {
-            if (STRIPS && lane == G - 1 && i >= 1 && i <= (int)own_rows) {
-                Carry *col = carry_cols + (size_t)(strip & 1u) * carry_rows;
+        if (STRIPS && active && lane == G - 1 && i >= 1 && i <= (int)own_rows) {
+            Carry *col = carry_cols + (size_t)(strip & 1u) * carry_rows;
 #if SW_ON_DEVICE
-                __stcg(reinterpret_cast<uint2 *>(col + i), make_uint2(h_out, f_out));
+            __stcg(reinterpret_cast<uint2 *>(col + i), make_uint2(h_out, f_out));
 #else
-                col[i].h = h_out; col[i].f = f_out;
+            col[i].h = h_out; col[i].f = f_out;
 #endif
-            }
-            const bool owner = (lane == G - 1) && (strip + 1 == nstrips);
-            if (i == (int)tl0) {
-#pragma unroll
-                for (int k = 0; k < K; k++) lastrow[(size_t)slot * K + k] = hm[k];
-                if (owner) {
-                    if (T::PAIRS == 2) { colbest[0] = best0 >> 16; colbest[1] = best0 & 0xffffu; }
-                    else { colbest[0] = best0; colbest[1] = best1; }
-                }
-            }
-            if (T::PAIRS == 2 && i == (int)tl1) {
-#pragma unroll
-                for (int k = 0; k < K; k++) lastrow[(size_t)(nslots + slot) * K + k] = hm[k];
-                if (owner) { colbest[2] = best1 >> 16; colbest[3] = best1 & 0xffffu; }
-            }
         }
-        if (i == 0) reset_rows(c);
+        /* the three things that happen once per lane and strip (row 0, row tl of either half) hide behind one compare */
+        if (EV && t == ev_next) events(c, t);
 
         /* column checkpoint of this step: what leaves register KM - 1 and what leaves the lane */
         {

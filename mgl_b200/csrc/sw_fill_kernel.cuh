@@ -27,10 +27,24 @@ sw_fill_kernel(const __grid_constant__ FillArgs a, const u32 first_unit)
     const u32 nstrips = u.nstrips;
     for (u32 s = 0; s < nstrips; s++) {
         L.strip_begin(a.c, s);
-        for (u32 t = 0; t < steps; t++) {
-            const u32 h = __shfl_up_sync(0xffffffffu, L.h_out, 1, G);
-            const u32 f = __shfl_up_sync(0xffffffffu, L.f_out, 1, G);
-            L.step(a.c, t, h, f);
+        for (u32 g = 0; g < steps / 4; g++) {           /* steps is a multiple of MGLSW_RB = 8 */
+            const u32 t0 = g * 4u;
+            if (__any_sync(0xffffffffu, L.ev_next < t0 + 4u)) {
+                /* some lane starts its first row or reaches its last one in these four steps */
+#pragma unroll 1
+                for (u32 s4 = 0; s4 < 4; s4++) {
+                    const u32 h = __shfl_up_sync(0xffffffffu, L.h_out, 1, G);
+                    const u32 f = __shfl_up_sync(0xffffffffu, L.f_out, 1, G);
+                    L.template step<true>(a.c, t0 + s4, h, f);
+                }
+            } else {
+#pragma unroll
+                for (u32 s4 = 0; s4 < 4; s4++) {
+                    const u32 h = __shfl_up_sync(0xffffffffu, L.h_out, 1, G);
+                    const u32 f = __shfl_up_sync(0xffffffffu, L.f_out, 1, G);
+                    L.template step<false>(a.c, t0 + s4, h, f);
+                }
+            }
         }
         __syncwarp();                            /* carry column of strip s is read by lane 0 in strip s + 1 */
     }

@@ -30,7 +30,7 @@
 #define MGL_B200_SW_LAYOUT_H
 #include "sw_common.h"
 
-#define MGLSW_RB 16u             /* steps per row block (row checkpoint period) */
+#define MGLSW_RB 8u              /* steps per row block (row checkpoint period) */
 
 namespace mglsw {
 
