@@ -72,13 +72,14 @@ struct Replay {
     u32 cb, cr;                          /* col_base, col_rem */
     int match, mismatch, go, ge, bias, indel;
     int ia, ib, ja, jb;
-    u64 nib[MGLSW_RB];                   /* row i - ia: nibble of column j at bits 4 (j - ja) */
-    int hlv[MGLSW_RB + 1], fv[MGLSW_RB + 1];
-    u32 rbv[MGLSW_RB + 1];
+    u64 *nib;                            /* row i - ia at nib[(i - ia) * nstride]: nibble of column j at bits 4 (j - ja); */
+    u32 nstride;                         /* shared memory on the device (one column per thread), a plain array in the emulator */
     u32 builds, cells;                   /* statistics */
 
-    SW_HD void init(const UnitDesc &u, u32 G_, u32 K_, u32 half_, const u32 *ckpt, const uint8_t *arena, const CellConsts &c)
+    SW_HD void init(const UnitDesc &u, u32 G_, u32 K_, u32 half_, const u32 *ckpt, const uint8_t *arena, const CellConsts &c,
+                    u64 *nib_, u32 nstride_)
     {
+        nib = nib_; nstride = nstride_;
         G = G_; K = K_; KM = regs_mid(K_); SC = sec_chunks(K_); half = half_; rbc = u.rb_count;
         cb = u.col_base; cr = u.col_rem;
         colp = ckpt + u.col_off + (size_t)u.group * G_ * 4u;
@@ -118,50 +119,67 @@ struct Replay {
         const bool edge = ja_ == 1;                                /* matrix column 0: no checkpoint, sw.cpp:47-49 and :22-26,38 */
         const u32 *lp = colp + (((size_t)cs * rbc * MGLSW_RB + cl) * 32u + cl) * 4u + word;   /* + i * 128 */
 
-        /* every load of the block first, all independent: left boundary + corner + ref bytes, row checkpoint, alt bytes */
+        /*
+         * Every load of the block first, unconditional (indices clamped into the block, dead
+         * ones discarded afterwards) so that they are all in flight together: one memory round
+         * trip per block instead of one per row.
+         */
+        W2 lraw[MGLSW_RB + 1];
+        u32 rraw[MGLSW_RB + 1];
+        const u32 *lp_safe = edge ? colp : lp;                     /* column 0 has no checkpoint: read anything, use nothing */
 #pragma unroll
         for (int r = 0; r <= (int)MGLSW_RB; r++) {                 /* entry r is row ia_ - 1 + r; entry 0 only yields the corner */
-            const int i = ia_ - 1 + r;
-            int hl = 0, fin = 0; u32 rbyte = 0;
-            if (r <= rows) {
-                if (i >= 1) {
-                    if (edge) { hl = bnd(i); fin = hl - go; }
-                    else { const W2 v = load_w2(lp + (size_t)i * 128u); hl = hval(v.x); fin = gval(v.y); }
-                    rbyte = SW_LDG(ref + (i - 1));
-                } else hl = bnd(ja_ - 1);                          /* row 0: H[0][ja_ - 1] */
-            }
-            hlv[r] = hl; fv[r] = fin; rbv[r] = rbyte;
+            int ic = ia_ - 1 + r;
+            ic = ic < 1 ? 1 : (ic > I ? I : ic);
+            lraw[r] = load_w2(lp_safe + (edge ? 0u : (size_t)ic * 128u));
+            rraw[r] = SW_LDG(ref + (ic - 1));
         }
-        int Hp[MGLSW_KH], E[MGLSW_KH];
-        u32 ab[MGLSW_KH];
+        W4 hraw[MGLSW_KH / 4], eraw[MGLSW_KH / 4];
         {
-            const u32 *rp0 = rowp + ((((size_t)strip * rbc + (rb - 1)) * (4u * SC) + (sub ? SC : 0u)) * 32u + lane) * 4u;
+            const u32 rbm = rb >= 1 ? rb - 1 : 0u;
+            const u32 *rp0 = rowp + ((((size_t)strip * rbc + rbm) * (4u * SC) + (sub ? SC : 0u)) * 32u + lane) * 4u;
 #pragma unroll
             for (int q = 0; q < MGLSW_KH / 4; q++) {
-                W4 hv, ev;
-                hv.x = hv.y = hv.z = hv.w = 0; ev = hv;
-                if (ia_ > 1 && 4 * q < cnt) {
-                    hv = load_w4(rp0 + (size_t)q * 128u);
-                    ev = load_w4(rp0 + (size_t)(q + 2 * SC) * 128u);
-                }
-                Hp[4 * q] = hval(hv.x); Hp[4 * q + 1] = hval(hv.y); Hp[4 * q + 2] = hval(hv.z); Hp[4 * q + 3] = hval(hv.w);
-                E[4 * q] = gval(ev.x); E[4 * q + 1] = gval(ev.y); E[4 * q + 2] = gval(ev.z); E[4 * q + 3] = gval(ev.w);
+                const u32 qc = (u32)q < SC ? (u32)q : SC - 1;      /* stay inside the section */
+                hraw[q] = load_w4(rp0 + (size_t)qc * 128u);
+                eraw[q] = load_w4(rp0 + (size_t)(qc + 2 * SC) * 128u);
             }
+        }
+        u32 ab[MGLSW_KH];
+#pragma unroll
+        for (int kk = 0; kk < MGLSW_KH; kk++) {
+            const int jc = ja_ + (kk < cnt ? kk : cnt - 1);
+            ab[kk] = SW_LDG(alt + (jc - 1));
+        }
+
+        int hlv[MGLSW_RB + 1], fv[MGLSW_RB + 1];
+#pragma unroll
+        for (int r = 0; r <= (int)MGLSW_RB; r++) {
+            const int i = ia_ - 1 + r;
+            int hl, fin;
+            if (i < 1) { hl = bnd(ja_ - 1); fin = 0; }            /* row 0: H[0][ja_ - 1] */
+            else if (edge) { hl = bnd(i); fin = hl - go; }
+            else { hl = hval(lraw[r].x); fin = gval(lraw[r].y); }
+            hlv[r] = hl; fv[r] = fin;
+        }
+        int Hp[MGLSW_KH], E[MGLSW_KH];
+#pragma unroll
+        for (int q = 0; q < MGLSW_KH / 4; q++) {
+            Hp[4 * q] = hval(hraw[q].x); Hp[4 * q + 1] = hval(hraw[q].y); Hp[4 * q + 2] = hval(hraw[q].z); Hp[4 * q + 3] = hval(hraw[q].w);
+            E[4 * q] = gval(eraw[q].x); E[4 * q + 1] = gval(eraw[q].y); E[4 * q + 2] = gval(eraw[q].z); E[4 * q + 3] = gval(eraw[q].w);
         }
 #pragma unroll
         for (int kk = 0; kk < MGLSW_KH; kk++) {
-            ab[kk] = 0x100u;                                       /* never equals a ref byte */
-            if (kk < cnt) {
-                const int j = ja_ + kk;
-                ab[kk] = SW_LDG(alt + (j - 1));
-                if (ia_ == 1) { const int b = bnd(j); Hp[kk] = b; E[kk] = b - go; }     /* rows 0 / 1 seeds: sw.cpp:10-18,29-35 */
-            }
+            if (ia_ == 1) { const int b = bnd(ja_ + kk); Hp[kk] = b; E[kk] = b - go; }  /* rows 0 / 1 seeds: sw.cpp:10-18,29-35 */
         }
 
-        for (int r = 1; r <= rows; r++) {
+        /* unrolled over the (at most MGLSW_RB) rows so that the boundary values stay in registers */
+#pragma unroll
+        for (int r = 1; r <= (int)MGLSW_RB; r++) {
+            if (r > rows) break;
             int diag = hlv[r - 1];                                 /* H[i - 1][ja_ - 1] */
             int f = fv[r];
-            const u32 rbyte = rbv[r];
+            const u32 rbyte = rraw[r];
             u32 lo = 0, hi = 0;
 #pragma unroll
             for (int kk = 0; kk < MGLSW_KH; kk++) {
@@ -179,7 +197,7 @@ struct Replay {
                 Hp[kk] = h;
                 if (kk < 8) lo |= nb << (4 * kk); else hi |= nb << (4 * (kk - 8));
             }
-            nib[r - 1] = (u64)lo | ((u64)hi << 32);
+            nib[(size_t)(r - 1) * nstride] = (u64)lo | ((u64)hi << 32);
         }
         ia = ia_; ib = I; ja = ja_; jb = J;
         builds++;
@@ -187,7 +205,7 @@ struct Replay {
     }
 
     SW_HD bool inside(int i, int j) const { return i >= ia && i <= ib && j >= ja && j <= jb; }
-    SW_HD u32 at(int i, int j) const { return (u32)(nib[i - ia] >> (4 * (j - ja))) & 15u; }
+    SW_HD u32 at(int i, int j) const { return (u32)(nib[(size_t)(i - ia) * nstride] >> (4 * (j - ja))) & 15u; }
 };
 
 struct PairResult {
@@ -202,7 +220,8 @@ struct PairResult {
  */
 template <class T>
 SW_HD PairResult traceback_pair(const UnitDesc &u, u32 half, u32 G, u32 K, const u32 *ckpt, const uint8_t *arena,
-                                const CellConsts &c, const u32 *colbest4, const u32 *lastrow, int strategy, u32 *ops_end)
+                                const CellConsts &c, const u32 *colbest4, const u32 *lastrow, int strategy, u32 *ops_end,
+                                u64 *nib, u32 nstride)
 {
     const int tl = (int)u.tl[half], ql = (int)u.ql;
     const u32 nslots = u.nstrips * G;
@@ -241,7 +260,7 @@ SW_HD PairResult traceback_pair(const UnitDesc &u, u32 half, u32 G, u32 K, const
     if (run > 0 && strategy == OS_SOFTCLIP) { SW_EMIT(OP_S, run); run = 0; }   /* sw.cpp:173-176 */
 
     Replay<T> rp;
-    rp.init(u, G, K, half, ckpt, arena, c);
+    rp.init(u, G, K, half, ckpt, arena, c, nib, nstride);
 
     /*
      * The walk of sw.cpp:182-214 as a state machine around ONE replay site, so that the 32 pairs

@@ -15,6 +15,7 @@ namespace mglsw {
  */
 __global__ void __launch_bounds__(128, 4) sw_traceback_kernel(const __grid_constant__ TraceArgs a)
 {
+    __shared__ u64 s_nib[MGLSW_RB * 128];          /* the replayed block's records, one column per thread */
     const u32 tid = blockIdx.x * blockDim.x + threadIdx.x;
     if (tid >= 2u * a.n_units) return;
     const UnitDesc &u = a.units[tid >> 1];
@@ -25,8 +26,8 @@ __global__ void __launch_bounds__(128, 4) sw_traceback_kernel(const __grid_const
     u32 *end = a.scratch + a.ops_end[p];
     const u32 *cb = a.colbest + (size_t)(tid >> 1) * 4u;
     PairResult r;
-    if (u.flags & UNIT_S32) r = traceback_pair<S32>(u, half, G, u.regs, a.ckpt, a.arena, a.c32, cb, a.lastrow, a.strategy[p], end);
-    else                    r = traceback_pair<S16x2>(u, half, G, u.regs, a.ckpt, a.arena, a.c16, cb, a.lastrow, a.strategy[p], end);
+    if (u.flags & UNIT_S32) r = traceback_pair<S32>(u, half, G, u.regs, a.ckpt, a.arena, a.c32, cb, a.lastrow, a.strategy[p], end, s_nib + threadIdx.x, 128u);
+    else                    r = traceback_pair<S16x2>(u, half, G, u.regs, a.ckpt, a.arena, a.c16, cb, a.lastrow, a.strategy[p], end, s_nib + threadIdx.x, 128u);
     a.offsets[p] = r.offset;
     a.n_ops[p] = r.n_ops;
 }

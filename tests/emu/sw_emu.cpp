@@ -113,9 +113,10 @@ int emu_align_batch(int n, const uint8_t *arena, const uint64_t *ref_off, const 
         const u32 half = plan.pair_unit[p] & 1u;
         const u32 G = (u.flags & UNIT_G32) ? MGLSW_G_LONG : MGLSW_G_SHORT;
         PairResult r;
+        u64 nibbuf[MGLSW_RB];
         u32 *end = scratch.data() + plan.ops_end[p];
-        if (u.flags & UNIT_S32) { r = traceback_pair<S32>(u, half, G, u.regs, ckpt.data(), arena, make_consts<S32>(s, 0), colbest.data() + (size_t)(plan.pair_unit[p] >> 1) * 4, lastrow.data(), strategies[p], end); n32++; }
-        else { r = traceback_pair<S16x2>(u, half, G, u.regs, ckpt.data(), arena, make_consts<S16x2>(s, plan.s16_bias), colbest.data() + (size_t)(plan.pair_unit[p] >> 1) * 4, lastrow.data(), strategies[p], end); n16++; }
+        if (u.flags & UNIT_S32) { r = traceback_pair<S32>(u, half, G, u.regs, ckpt.data(), arena, make_consts<S32>(s, 0), colbest.data() + (size_t)(plan.pair_unit[p] >> 1) * 4, lastrow.data(), strategies[p], end, nibbuf, 1u); n32++; }
+        else { r = traceback_pair<S16x2>(u, half, G, u.regs, ckpt.data(), arena, make_consts<S16x2>(s, plan.s16_bias), colbest.data() + (size_t)(plan.pair_unit[p] >> 1) * 4, lastrow.data(), strategies[p], end, nibbuf, 1u); n16++; }
         offsets[p] = r.offset;
         n_ops[p] = r.n_ops;
         if ((int)r.n_ops > ops_stride) return -11;
