@@ -87,8 +87,8 @@ struct CellConsts {
 struct UnitDesc {
     u64 ref_off[2];      /* byte offsets of the two refs in the sequence arena        */
     u64 alt_off[2];
-    u64 col_off;         /* word offset of the owning warp's column checkpoints       */
-    u64 row_off;         /* word offset of the owning warp's row checkpoints          */
+    u64 ckpt_off;        /* word offset of the owning warp's checkpoint regions       */
+    u64 reserved0;
     u64 carry_off;       /* uint2 index of this unit's two strip-carry columns        */
     u64 lastrow_off;     /* word offset of this unit's last-row capture               */
     u32 pair[2];         /* chunk-local pair ids; NO_PAIR: half unused                */

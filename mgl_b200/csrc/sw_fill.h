@@ -58,6 +58,7 @@ template <class T, int G, int K>
 struct FillLane {
     static constexpr int SC = ((K + 1) / 2 + 3) / 4;   /* chunks per section of a row checkpoint */
     static constexpr int Q2 = 4 * SC;                  /* 16-byte chunks of a row checkpoint     */
+    static constexpr int LS16 = (MGLSW_RB + Q2) | 1;   /* lane_stride16(K)                       */
     static constexpr int KM = (K + 1) / 2;       /* registers before the mid checkpoint   */
     static constexpr bool STRIPS = (G == 32);    /* lane groups of 8 always cover the alt in one strip */
     u32 e[K], hm[K], bq[K];
@@ -80,8 +81,9 @@ struct FillLane {
     u32 slot, nslots;
     u32 indel, active, strip, nstrips, rb_count;
     u32 col_base, col_rem;
-    u32 *col_base_p, *row_base_p;   /* the warp's column / row checkpoint regions      */
-    u32 *col_cur, *row_cur;         /* ... of the current strip, at this lane's slot   */
+    u32 *ckpt_base;           /* the warp's checkpoint regions in HBM                 */
+    u32 *ckpt_cur;            /* ... of the current strip                             */
+    u32 *stage;               /* device: the warp's staging region in shared memory; emulator: unused */
     Carry *carry_cols;        /* two columns of carry_rows entries                    */
     u32 carry_rows;
     u32 *lastrow;             /* PAIRS regions of nslots * K words                    */
@@ -114,10 +116,9 @@ struct FillLane {
         rb_count = u.rb_count;
         indel = (u.flags & UNIT_INDEL) ? 1u : 0u;
         active = (u.flags & UNIT_ACTIVE) ? 1u : 0u;
-        col_base_p = a.ckpt + u.col_off;
-        row_base_p = a.ckpt + u.row_off;
-        col_cur = col_base_p;
-        row_cur = row_base_p;
+        ckpt_base = a.ckpt + u.ckpt_off;
+        ckpt_cur = ckpt_base;
+        stage = nullptr;
         carry_cols = a.carry + u.carry_off;
         carry_rows = u.carry_rows;
         lastrow = a.lastrow + u.lastrow_off;
@@ -165,8 +166,7 @@ struct FillLane {
     SW_HD void strip_begin(const CellConsts &c, u32 s)
     {
         strip = s;
-        col_cur = col_base_p + ((size_t)s * rb_count * MGLSW_RB * 32u + wlane) * 4u;
-        row_cur = row_base_p + ((size_t)s * rb_count * Q2 * 32u + wlane) * 4u;
+        ckpt_cur = ckpt_base + (size_t)s * rb_count * (LS16 * 128u);
         slot = s * G + lane;
         n = col_base + (slot < col_rem ? 1u : 0u);
         j0 = 1u + (slot < col_rem ? slot * (col_base + 1) : col_rem * (col_base + 1) + (slot - col_rem) * col_base);
@@ -290,37 +290,48 @@ struct FillLane {
         /* the three things that happen once per lane and strip (row 0, row tl of either half) hide behind one compare */
         if (EV && t == ev_next) events(c, t);
 
-        /* column checkpoint of this step: what leaves register KM - 1 and what leaves the lane */
-        {
-            u32 *dst = col_cur + (size_t)t * 128u;
+        /*
+         * Checkpoints (sw_layout.h).  Every step: (H + match, F) leaving register KM - 1 and leaving the
+         * lane, into this lane's slice of the region being assembled.  After the last step of a row
+         * block: H + match and E of every register, then the region goes out to HBM.  On the device
+         * the region is assembled in shared memory and copied with 512-byte warp stores.
+         */
 #if SW_ON_DEVICE
-            __stcs(reinterpret_cast<uint4 *>(dst), make_uint4(hm[KM - 1], f_mid, h_out, f_out));
+        u32 *slice = stage + wlane * (LS16 * 4u);
+        *reinterpret_cast<uint4 *>(slice + (t % MGLSW_RB) * 4u) = make_uint4(hm[KM - 1], f_mid, h_out, f_out);
 #else
-            dst[0] = hm[KM - 1]; dst[1] = f_mid; dst[2] = h_out; dst[3] = f_out;
+        u32 *slice = ckpt_cur + (size_t)(t / MGLSW_RB) * (LS16 * 128u) + wlane * (LS16 * 4u);
+        { u32 *p = slice + (t % MGLSW_RB) * 4u; p[0] = hm[KM - 1]; p[1] = f_mid; p[2] = h_out; p[3] = f_out; }
 #endif
-        }
-        /* row checkpoint after the last step of a row block: H + match and E of every register */
         if ((t % MGLSW_RB) == MGLSW_RB - 1) {
-            u32 *dst = row_cur + (size_t)(t / MGLSW_RB) * Q2 * 128u;
 #pragma unroll
             for (int q = 0; q < Q2; q++) {
-                /* section q / SC: 0 H[0, KM)  1 H[KM, K)  2 E[0, KM)  3 E[KM, K); register = section base + 4 (q % SC) + x */
+                /* chunk q: section q / SC = 0 H[0, KM)  1 E[0, KM)  2 H[KM, K)  3 E[KM, K); register = section base + 4 (q % SC) + x */
                 u32 w[4];
 #pragma unroll
                 for (int x = 0; x < 4; x++) {
                     const int sec = q / SC, off = 4 * (q % SC) + x;
-                    const int reg = (sec & 1) ? KM + off : off;
-                    const bool ok = (sec & 1) ? reg < K : off < KM;
+                    const int reg = (sec & 2) ? KM + off : off;
+                    const bool ok = (sec & 2) ? reg < K : off < KM;
                     const int rs = ok ? reg : 0;
-                    w[x] = ok ? (sec < 2 ? hm[rs] : e[rs]) : 0u;
+                    w[x] = ok ? ((sec & 1) ? e[rs] : hm[rs]) : 0u;
                 }
+                u32 *p = slice + MGLSW_RB * 4u + q * 4;
 #if SW_ON_DEVICE
-                __stcs(reinterpret_cast<uint4 *>(dst + (size_t)q * 128u), make_uint4(w[0], w[1], w[2], w[3]));
+                *reinterpret_cast<uint4 *>(p) = make_uint4(w[0], w[1], w[2], w[3]);
 #else
-                u32 *p = dst + (size_t)q * 128u;
                 p[0] = w[0]; p[1] = w[1]; p[2] = w[2]; p[3] = w[3];
 #endif
             }
+#if SW_ON_DEVICE
+            __syncwarp();
+            u32 *dst = ckpt_cur + (size_t)(t / MGLSW_RB) * (LS16 * 128u) + wlane * 4u;
+            const u32 *src = stage + wlane * 4u;
+#pragma unroll
+            for (int q = 0; q < LS16; q++)
+                __stcs(reinterpret_cast<uint4 *>(dst + q * 128), *reinterpret_cast<const uint4 *>(src + q * 128));
+            __syncwarp();
+#endif
         }
     }
 };

@@ -21,8 +21,12 @@ sw_fill_kernel(const __grid_constant__ FillArgs a, const u32 first_unit)
     const u32 ui = first_unit + warp * (32 / G) + wl / G;
     const UnitDesc &u = a.units[ui];
 
+    /* one checkpoint region per warp, assembled here and copied out every MGLSW_RB steps */
+    __shared__ uint4 s_stage[MGLSW_FILL_THREADS / 32][FillLane<T, G, K>::LS16 * 32];
+
     FillLane<T, G, K> L;
     L.setup(a, u, wl, ui);
+    L.stage = reinterpret_cast<u32 *>(s_stage[threadIdx.x >> 5]);
     const u32 steps = u.rb_count * MGLSW_RB;     /* same for every lane of the warp */
     const u32 nstrips = u.nstrips;
     for (u32 s = 0; s < nstrips; s++) {

@@ -18,13 +18,21 @@
  * reference's predicates (sw.cpp:60-93), only the grid blocks its path crosses.
  *   column checkpoints  every step, every lane: (H + match, F) leaving the lane's register
  *                       KM - 1 ("mid") and leaving its last real register ("end", the pair
- *                       that is shuffled to the next lane): one 16-byte store per lane per
- *                       step, [strip][t][32 lanes][4 words] -- 512 contiguous bytes per warp.
+ *                       that is shuffled to the next lane): 16 bytes per lane per step.
  *   row checkpoints     after every MGLSW_RB-th step, every lane: (H + match, E) of all K
- *                       registers, [strip][row block][chunk][32 lanes][4 words].
+ *                       registers.
  * A block is (lane slot, half of its registers, row block): at most ceil(K / 2) columns by
- * MGLSW_RB rows.  About 0.65 B per cell at K = 20, and the path of a 150-column alignment
- * crosses ~25 blocks, i.e. ~4 % of the matrix is computed twice.
+ * MGLSW_RB rows; the path of a 150-column alignment crosses ~35 blocks, i.e. ~4 % of the
+ * matrix is computed twice.  About 1 B per cell at K = 20.
+ *
+ * Storage is READER-major: the traceback is one thread per pair chasing its own path, so what
+ * one block needs must be contiguous (random 8-byte reads cost a 32-byte sector, mostly wasted:
+ * the first layout made the traceback DRAM-bound at 8x read amplification).  Per warp, strip
+ * and row block there is one region of 32 lanes x lane_stride16(K) 16-byte units; a lane's
+ * slice holds its MGLSW_RB column checkpoints (128 B) followed by its row checkpoint in the
+ * order H[0,KM) E[0,KM) H[KM,K) E[KM,K), each section padded to whole 16-byte chunks.  The
+ * fill stages a region in shared memory and copies it out with 512-byte warp stores; the
+ * odd lane stride keeps both the 16-byte shared-memory stores and the copy conflict-free.
  */
 #ifndef MGL_B200_SW_LAYOUT_H
 #define MGL_B200_SW_LAYOUT_H
@@ -42,21 +50,24 @@ SW_HD u32 regs_per_lane(u32 ql, u32 slots) { return ceil_div_u32(ql, slots); }
 /* registers in the first half of a lane: the mid column checkpoint sits after register KM - 1 */
 SW_HD u32 regs_mid(u32 K) { return (K + 1) / 2; }
 
-/*
- * One lane's row checkpoint: four sections of sec_chunks(K) 16-byte chunks each --
- * H + match of registers [0, KM), H + match of [KM, K), E of [0, KM), E of [KM, K) -- so that
- * the registers of either half of the lane start on a chunk boundary and the traceback
- * reads them with 16-byte loads.
- */
+/* 16-byte chunks per section (H or E of one half of the lane's registers) of a row checkpoint */
 SW_HD u32 sec_chunks(u32 K) { return (regs_mid(K) + 3) / 4; }
-SW_HD u32 row_chunks(u32 K) { return 4 * sec_chunks(K); }
 
-/* number of steps (a multiple of the row block) for a warp iterating tlmax rows */
+/* 16-byte units of one lane's slice of a region: MGLSW_RB column checkpoints + 4 sections, made odd */
+SW_HD u32 lane_stride16(u32 K) { const u32 s = MGLSW_RB + 4 * sec_chunks(K); return s | 1u; }
+
+/* words of one region (one warp, one strip, one row block) */
+SW_HD u32 region_words(u32 K) { return lane_stride16(K) * 128u; }
+
+/* number of row blocks for a warp iterating tlmax rows; steps = row blocks * MGLSW_RB */
 SW_HD u32 row_blocks(u32 tlmax, u32 G) { return ceil_div_u32(tlmax + G, MGLSW_RB); }
 
-/* checkpoint words of one warp: column checkpoints of every strip, then row checkpoints */
-SW_HD u64 warp_col_words(u32 nstrips, u32 rb_count) { return (u64)nstrips * rb_count * MGLSW_RB * 128u; }
-SW_HD u64 warp_row_words(u32 nstrips, u32 rb_count, u32 K) { return (u64)nstrips * rb_count * row_chunks(K) * 128u; }
+/* checkpoint words of one warp */
+SW_HD u64 warp_ckpt_words(u32 nstrips, u32 rb_count, u32 K) { return (u64)nstrips * rb_count * region_words(K); }
+
+/* word offset, inside a lane's slice, of the column checkpoint of step t and of row-checkpoint chunk q of section (sub, is_e) */
+SW_HD u32 slice_col_word(u32 t) { return (t % MGLSW_RB) * 4u; }
+SW_HD u32 slice_row_word(u32 K, u32 sub, u32 is_e, u32 q) { return MGLSW_RB * 4u + ((sub * 2u + is_e) * sec_chunks(K) + q) * 4u; }
 
 /* columns of lane slot `slot` and its first column (0-based) */
 SW_HD u32 slot_cols(const UnitDesc &u, u32 slot) { return u.col_base + (slot < u.col_rem ? 1u : 0u); }
@@ -73,19 +84,10 @@ SW_HD void col_to_slot(const UnitDesc &u, u32 col, u32 &slot, u32 &reg)
     else { const u32 c = col - wide; slot = u.col_rem + c / u.col_base; reg = c - (slot - u.col_rem) * u.col_base; }
 }
 
-/*
- * Word index (relative to the checkpoint buffer) of the column checkpoint lane `lane` of group
- * u.group stored at step t of strip `strip`: 4 words (h_mid, f_mid, h_end, f_end).
- */
-SW_HD u64 col_ckpt_index(const UnitDesc &u, u32 G, u32 strip, u32 t, u32 lane)
+/* word index (relative to the checkpoint buffer) of the slice of lane `lane` of u's group in region (strip, rb) */
+SW_HD u64 slice_index(const UnitDesc &u, u32 G, u32 K, u32 strip, u32 rb, u32 lane)
 {
-    return u.col_off + (((u64)strip * u.rb_count * MGLSW_RB + t) * 32u + u.group * G + lane) * 4u;
-}
-
-/* Word index of chunk c (0 .. row_chunks(K) - 1) of the row checkpoint stored after the last step of row block rb. */
-SW_HD u64 row_ckpt_index(const UnitDesc &u, u32 G, u32 K, u32 strip, u32 rb, u32 lane, u32 c)
-{
-    return u.row_off + ((((u64)strip * u.rb_count + rb) * row_chunks(K) + c) * 32u + u.group * G + lane) * 4u;
+    return u.ckpt_off + ((u64)strip * u.rb_count + rb) * region_words(K) + (u64)(u.group * G + lane) * lane_stride16(K) * 4u;
 }
 
 }  // namespace mglsw

@@ -203,8 +203,7 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
                 wu[g].tlmax = tlmax;
                 wu[g].rb_count = rb;
                 wu[g].group = g;
-                wu[g].col_off = out.ckpt_words;
-                wu[g].row_off = out.ckpt_words + warp_col_words(L.nstrips, rb);
+                wu[g].ckpt_off = out.ckpt_words;
                 if (wu[g].flags & UNIT_ACTIVE) {
                     if (L.G == MGLSW_G_LONG) {            /* only strip-mined units hand columns over through HBM */
                         wu[g].carry_off = out.carry_entries;
@@ -214,7 +213,7 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
                     out.lastrow_words += (u64)(L.kind == KIND_S16X2 ? 2 : 1) * L.nstrips * L.G * L.K;
                 }
             }
-            out.ckpt_words += warp_col_words(L.nstrips, rb) + warp_row_words(L.nstrips, rb, (u32)L.K);
+            out.ckpt_words += warp_ckpt_words(L.nstrips, rb, (u32)L.K);
         }
         out.cells += L.cells;
         out.launches.push_back(L);

@@ -66,9 +66,9 @@ SW_HD W2 load_w2(const u32 *p)
 template <class T>
 struct Replay {
     /* the unit's geometry, copied out of its descriptor once */
-    const u32 *colp, *rowp;              /* checkpoint regions of the warp, at this unit's lane group */
+    const u32 *base;                     /* checkpoint regions of the warp, at this unit's lane group */
     const uint8_t *ref, *alt;            /* this pair's sequences */
-    u32 G, K, KM, SC, half, rbc;         /* SC = sec_chunks(K), rbc = row blocks per strip */
+    u32 G, K, KM, SC, LSW, RW, half, rbc; /* SC = sec_chunks(K), LSW / RW = words per lane slice / per region, rbc = row blocks per strip */
     u32 cb, cr;                          /* col_base, col_rem */
     int match, mismatch, go, ge, bias, indel;
     int ia, ib, ja, jb;
@@ -82,8 +82,8 @@ struct Replay {
         nib = nib_; nstride = nstride_;
         G = G_; K = K_; KM = regs_mid(K_); SC = sec_chunks(K_); half = half_; rbc = u.rb_count;
         cb = u.col_base; cr = u.col_rem;
-        colp = ckpt + u.col_off + (size_t)u.group * G_ * 4u;
-        rowp = ckpt + u.row_off + (size_t)u.group * G_ * 4u;
+        LSW = lane_stride16(K_) * 4u; RW = region_words(K_);
+        base = ckpt + u.ckpt_off + (size_t)u.group * G_ * LSW;
         ref = arena + u.ref_off[half_]; alt = arena + u.alt_off[half_];
         match = c.s_match; mismatch = c.s_mismatch; go = c.s_go; ge = c.s_ge; bias = c.bias;
         indel = (u.flags & UNIT_INDEL) ? 1 : 0;
@@ -117,7 +117,8 @@ struct Replay {
         u32 cs = strip, cl = lane, word = 0;
         if (!sub) { word = 2; if (lane > 0) cl = lane - 1; else { cl = G - 1; cs = strip - 1; } }
         const bool edge = ja_ == 1;                                /* matrix column 0: no checkpoint, sw.cpp:47-49 and :22-26,38 */
-        const u32 *lp = colp + (((size_t)cs * rbc * MGLSW_RB + cl) * 32u + cl) * 4u + word;   /* + i * 128 */
+        /* slice of lane cl in region (cs, step / MGLSW_RB), entry step % MGLSW_RB, words word..word+1 */
+        const u32 *lp = base + (size_t)cs * rbc * RW + (size_t)cl * LSW + word;
 
         /*
          * Every load of the block first, unconditional (indices clamped into the block, dead
@@ -126,23 +127,25 @@ struct Replay {
          */
         W2 lraw[MGLSW_RB + 1];
         u32 rraw[MGLSW_RB + 1];
-        const u32 *lp_safe = edge ? colp : lp;                     /* column 0 has no checkpoint: read anything, use nothing */
+        const u32 *lp_safe = edge ? base : lp;                     /* column 0 has no checkpoint: read anything, use nothing */
 #pragma unroll
         for (int r = 0; r <= (int)MGLSW_RB; r++) {                 /* entry r is row ia_ - 1 + r; entry 0 only yields the corner */
             int ic = ia_ - 1 + r;
             ic = ic < 1 ? 1 : (ic > I ? I : ic);
-            lraw[r] = load_w2(lp_safe + (edge ? 0u : (size_t)ic * 128u));
+            const u32 tt = edge ? 0u : (u32)ic + cl;               /* the step at which lane cl worked on row ic */
+            lraw[r] = load_w2(lp_safe + (size_t)(tt / MGLSW_RB) * RW + (tt % MGLSW_RB) * 4u);
             rraw[r] = SW_LDG(ref + (ic - 1));
         }
         W4 hraw[MGLSW_KH / 4], eraw[MGLSW_KH / 4];
         {
             const u32 rbm = rb >= 1 ? rb - 1 : 0u;
-            const u32 *rp0 = rowp + ((((size_t)strip * rbc + rbm) * (4u * SC) + (sub ? SC : 0u)) * 32u + lane) * 4u;
+            /* this lane's row checkpoint of the previous row block: H section of this half, E section right behind it */
+            const u32 *rp0 = base + ((size_t)strip * rbc + rbm) * RW + (size_t)lane * LSW + MGLSW_RB * 4u + (sub ? 2u * SC : 0u) * 4u;
 #pragma unroll
             for (int q = 0; q < MGLSW_KH / 4; q++) {
                 const u32 qc = (u32)q < SC ? (u32)q : SC - 1;      /* stay inside the section */
-                hraw[q] = load_w4(rp0 + (size_t)qc * 128u);
-                eraw[q] = load_w4(rp0 + (size_t)(qc + 2 * SC) * 128u);
+                hraw[q] = load_w4(rp0 + qc * 4u);
+                eraw[q] = load_w4(rp0 + (qc + SC) * 4u);
             }
         }
         u32 ab[MGLSW_KH];
