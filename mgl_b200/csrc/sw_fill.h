@@ -294,10 +294,14 @@ struct FillLane {
          * Checkpoints (sw_layout.h).  Every step: (H + match, F) leaving register KM - 1 and leaving the
          * lane, into this lane's slice of the region being assembled.  After the last step of a row
          * block: H + match and E of every register, then the region goes out to HBM.  On the device
-         * the region is assembled in shared memory and copied with 512-byte warp stores.
+         * the region is assembled in shared memory and leaves with one bulk asynchronous copy.
          */
 #if SW_ON_DEVICE
         u32 *slice = stage + wlane * (LS16 * 4u);
+        if ((t % MGLSW_RB) == 0) {                     /* the bulk copy of the previous region must have read the staging buffer */
+            if (wlane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            __syncwarp();
+        }
         *reinterpret_cast<uint4 *>(slice + (t % MGLSW_RB) * 4u) = make_uint4(hm[KM - 1], f_mid, h_out, f_out);
 #else
         u32 *slice = ckpt_cur + (size_t)(t / MGLSW_RB) * (LS16 * 128u) + wlane * (LS16 * 4u);
@@ -324,13 +328,15 @@ struct FillLane {
 #endif
             }
 #if SW_ON_DEVICE
+            /* one TMA bulk store (UBLKCP) moves the assembled region: shared memory -> HBM, off the issue slots */
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncwarp();
-            u32 *dst = ckpt_cur + (size_t)(t / MGLSW_RB) * (LS16 * 128u) + wlane * 4u;
-            const u32 *src = stage + wlane * 4u;
-#pragma unroll
-            for (int q = 0; q < LS16; q++)
-                __stcs(reinterpret_cast<uint4 *>(dst + q * 128), *reinterpret_cast<const uint4 *>(src + q * 128));
-            __syncwarp();
+            if (wlane == 0) {
+                u32 *dst = ckpt_cur + (size_t)(t / MGLSW_RB) * (LS16 * 128u);
+                const u32 src = (u32)__cvta_generic_to_shared(stage);
+                asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;\n\tcp.async.bulk.commit_group;"
+                             :: "l"(dst), "r"(src), "n"(LS16 * 512) : "memory");
+            }
 #endif
         }
     }

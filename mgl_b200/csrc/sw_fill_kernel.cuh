@@ -52,6 +52,9 @@ sw_fill_kernel(const __grid_constant__ FillArgs a, const u32 first_unit)
         }
         __syncwarp();                            /* carry column of strip s is read by lane 0 in strip s + 1 */
     }
+    /* the last region's bulk store still reads this block's shared memory */
+    if (wl == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    __syncwarp();
 }
 
 template <class T, int G, int K>
