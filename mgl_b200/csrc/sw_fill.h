@@ -40,6 +40,7 @@ struct Carry { u32 h, f; };   /* 8 bytes: H[i][last col] + match, F[i][last col 
 
 /* bytes readable before arena[0] and after the last sequence byte (see FillLane::fetch_ref) */
 #define MGLSW_ARENA_FRONT_PAD 64u
+#define MGLSW_REF_AHEAD 4u       /* steps between loading a ref byte and using it: covers an L2 round trip */
 SW_HD u64 arena_tail_pad(u32 max_ref_len) { return (u64)max_ref_len + 64u; }
 
 /* device buffers of one fill launch */
@@ -64,7 +65,7 @@ struct FillLane {
     u32 e[K], hm[K], bq[K];
     u32 hleft;                /* H[i-1][first col - 1] + match: diagonal input of register 0 */
     u32 h_out, f_out;         /* this step's values for the right-hand neighbour      */
-    u32 ra_next;              /* ref bytes of the next step's row (prefetched)        */
+    u32 rq0[MGLSW_REF_AHEAD], rq1[MGLSW_REF_AHEAD];   /* ref bytes of the next steps' rows, loaded MGLSW_REF_AHEAD steps early, merged at use */
     Carry cin_next;           /* carry-in of the next step's row (strips > 0, lane 0) */
     u32 bh, bf, bdec;         /* column-0 boundary of the next step's row (lane 0), and its per-row decrement */
     u32 ev_next;              /* step of this lane's next event (events())            */
@@ -128,11 +129,13 @@ struct FillLane {
 
     SW_HD int bnd(const CellConsts &c, int x) const { return boundary_score(x, (int)indel, c.s_go, c.s_ge); }
 
-    SW_HD u32 fetch_ref(u32 t) const
+    /* the ref bytes of step t into the last queue slot; the slots move up one step at a time */
+    SW_HD void fetch_ref(u32 t)
     {
-        u32 r = SW_LDG(rp0 + t);
-        if (T::PAIRS == 2) r |= (u32)SW_LDG(rp1 + t) << 16;
-        return r;
+#pragma unroll
+        for (int q = 0; q + 1 < (int)MGLSW_REF_AHEAD; q++) { rq0[q] = rq0[q + 1]; rq1[q] = rq1[q + 1]; }
+        rq0[MGLSW_REF_AHEAD - 1] = SW_LDG(rp0 + t);
+        rq1[MGLSW_REF_AHEAD - 1] = T::PAIRS == 2 ? (u32)SW_LDG(rp1 + t) : 0u;
     }
     SW_HD Carry fetch_carry(int i) const
     {
@@ -181,7 +184,7 @@ struct FillLane {
         reset_rows(c);
         h_out = T::rep(c.bias);
         f_out = T::rep(c.bias);
-        ra_next = fetch_ref(0);
+        for (u32 q = 0; q < MGLSW_REF_AHEAD; q++) fetch_ref(q);
         ev_next = lane;                               /* row 0 comes first: tl >= 1 */
         cin_next = fetch_carry(-(int)lane);
         /*
@@ -233,8 +236,8 @@ struct FillLane {
     SW_HD void step(const CellConsts &c, u32 t, u32 h_sh, u32 f_sh)
     {
         const int i = (int)t - (int)lane;
-        const u32 ra = ra_next;
-        ra_next = fetch_ref(t + 1);
+        const u32 ra = T::PAIRS == 2 ? (rq0[0] | (rq1[0] << 16)) : rq0[0];
+        fetch_ref(t + MGLSW_REF_AHEAD);
 
         u32 h_in = h_sh, f_in = f_sh;
         if (STRIPS) {
