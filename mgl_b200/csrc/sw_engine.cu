@@ -50,7 +50,7 @@ void ChunkDev::release()
 void WorkSlot::release()
 {
     ckpt.release(); carry.release(); lastrow.release(); colbest.release(); scratch.release();
-    offsets.release(); n_ops.release(); starts.release(); ops.release();
+    offsets.release(); n_ops.release(); starts.release(); tiles.release(); ops.release();
     h_n_ops.release(); h_total.release();
     if (ev_counts) cudaEventDestroy(ev_counts);
     if (ev_done) cudaEventDestroy(ev_done);
@@ -228,6 +228,7 @@ int Engine::ensure_slot(WorkSlot &ws, const ChunkPlan &plan, u32 n)
     if ((e = ws.offsets.reserve((size_t)n * sizeof(int))) != cudaSuccess) return cuda_fail(e, "cudaMalloc");
     if ((e = ws.n_ops.reserve((size_t)n * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc");
     if ((e = ws.starts.reserve(((size_t)n + 1) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc");
+    if ((e = ws.tiles.reserve(((size_t)n / 1024 + 2) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc");
     if ((e = ws.ops.reserve((plan.scratch_words + 1) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc ops");
     if ((e = ws.h_n_ops.reserve(((size_t)n + 1) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "pinned alloc");
     return MGL_SW_OK;
@@ -279,12 +280,12 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed)
     t.n_units = (u32)cd.plan.units.size();
     if ((e = launch_traceback(t, pt)) != cudaSuccess) return cuda_fail(e, "traceback launch");
     if (timed) cudaEventRecord(tev_[3], pt);
-    if ((e = launch_scan_counts((const u32 *)ws.n_ops.p, (u32 *)ws.starts.p, cd.n, pt)) != cudaSuccess) return cuda_fail(e, "scan launch");
+    if ((e = launch_scan_counts((const u32 *)ws.n_ops.p, (u32 *)ws.starts.p, (u32 *)ws.tiles.p, cd.n, pt)) != cudaSuccess) return cuda_fail(e, "scan launch");
     if ((e = launch_compact((const u32 *)ws.scratch.p, (const u64 *)cd.ops_end.p, (const u32 *)ws.n_ops.p,
-                            (const u32 *)ws.starts.p, (u32 *)ws.ops.p, cd.n, pt)) != cudaSuccess) return cuda_fail(e, "compact launch");
+                            (const u32 *)ws.starts.p, (const u32 *)ws.tiles.p, (u32 *)ws.ops.p, cd.n, pt)) != cudaSuccess) return cuda_fail(e, "compact launch");
     if (timed) cudaEventRecord(tev_[4], pt);
     if ((e = cudaEventRecord(ws.ev_post, pt)) != cudaSuccess) return cuda_fail(e, "event record");
-    bs.other_launches += 3;
+    bs.other_launches += 4;
     bs.chunks++;
     bs.cells += cd.plan.cells;
     bs.pairs += cd.n;

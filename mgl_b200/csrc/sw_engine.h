@@ -77,7 +77,7 @@ struct WorkSlot {
                                          /* latency-bound traceback of one chunk slips in between the blocks of */
                                          /* the other slot's fill instead of queueing behind them               */
     cudaEvent_t ev_fill = nullptr, ev_post = nullptr, ev_counts = nullptr, ev_done = nullptr;
-    DevBuf ckpt, carry, lastrow, colbest, scratch, offsets, n_ops, starts, ops;
+    DevBuf ckpt, carry, lastrow, colbest, scratch, offsets, n_ops, starts, tiles, ops;
     PinBuf h_n_ops, h_total;
     void release();
 };

@@ -29,11 +29,12 @@ struct TraceArgs {
 };
 cudaError_t launch_traceback(const TraceArgs &a, cudaStream_t stream);
 
-/* exclusive scan of n_ops -> starts[0..n], starts[n] = total (n <= 2^24) */
-cudaError_t launch_scan_counts(const u32 *n_ops, u32 *starts, u32 n, cudaStream_t stream);
+/* two-level exclusive scan of n_ops: starts[p] = offset inside p's tile of 1024 pairs, tile_sum[t] = offset of tile t,
+   starts[n] = total.  tile_sum needs ceil(n / 1024) words. */
+cudaError_t launch_scan_counts(const u32 *n_ops, u32 *starts, u32 *tile_sum, u32 n, cudaStream_t stream);
 
-/* ops_out[starts[p] ..] = scratch[ops_end[p] - n_ops[p] .. ops_end[p]) */
-cudaError_t launch_compact(const u32 *scratch, const u64 *ops_end, const u32 *n_ops, const u32 *starts,
+/* ops_out[tile_off[p / 1024] + starts[p] ..] = scratch[ops_end[p] - n_ops[p] .. ops_end[p]) */
+cudaError_t launch_compact(const u32 *scratch, const u64 *ops_end, const u32 *n_ops, const u32 *starts, const u32 *tile_off,
                            u32 *ops_out, u32 n, cudaStream_t stream);
 
 /* integer-pipe microbenchmarks (int_peak.cu): ops per second of one instruction mix */

@@ -39,16 +39,45 @@ cudaError_t launch_traceback(const TraceArgs &a, cudaStream_t stream)
     return cudaGetLastError();
 }
 
-/* single-block exclusive scan: each thread owns a contiguous slice */
-__global__ void __launch_bounds__(1024) sw_scan_kernel(const u32 *__restrict__ n_ops, u32 *__restrict__ starts, u32 n)
+/*
+ * Exclusive scan of the per-pair element counts, two levels.  Level 1: each block scans 1024
+ * counts (coalesced 16-byte loads, warp shuffles) into block-local offsets and one block total.
+ * Level 2: one block scans the block totals in place and writes the grand total to starts[n].
+ * The compaction adds the two.
+ */
+#define SCAN_TILE 1024u
+__global__ void __launch_bounds__(256) sw_scan_tiles_kernel(const u32 *__restrict__ n_ops, u32 *__restrict__ starts,
+                                                            u32 *__restrict__ tile_sum, u32 n)
+{
+    __shared__ u32 wsum[8];
+    const u32 base = blockIdx.x * SCAN_TILE + threadIdx.x * 4u;
+    u32 v[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) v[k] = base + k < n ? n_ops[base + k] : 0u;
+    const u32 mine = v[0] + v[1] + v[2] + v[3];
+    u32 incl = mine;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const u32 x = __shfl_up_sync(0xffffffffu, incl, d); if ((threadIdx.x & 31u) >= (u32)d) incl += x; }
+    if ((threadIdx.x & 31u) == 31u) wsum[threadIdx.x >> 5] = incl;
+    __syncthreads();
+    u32 woff = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++) { if ((u32)w < (threadIdx.x >> 5)) woff += wsum[w]; total += wsum[w]; }
+    u32 run = woff + incl - mine;
+#pragma unroll
+    for (int k = 0; k < 4; k++) { if (base + k < n) starts[base + k] = run; run += v[k]; }
+    if (threadIdx.x == 0) tile_sum[blockIdx.x] = total;
+}
+
+__global__ void __launch_bounds__(1024) sw_scan_totals_kernel(u32 *__restrict__ tile_sum, u32 *__restrict__ starts, u32 n_tiles, u32 n)
 {
     __shared__ u32 part[1024];
     const u32 tid = threadIdx.x;
-    const u32 per = (n + 1023u) / 1024u;
-    const u32 lo = tid * per < n ? tid * per : n;
-    const u32 hi = lo + per < n ? lo + per : n;
+    const u32 per = (n_tiles + 1023u) / 1024u;
+    const u32 lo = tid * per < n_tiles ? tid * per : n_tiles;
+    const u32 hi = lo + per < n_tiles ? lo + per : n_tiles;
     u32 sum = 0;
-    for (u32 k = lo; k < hi; k++) sum += n_ops[k];
+    for (u32 k = lo; k < hi; k++) sum += tile_sum[k];
     part[tid] = sum;
     __syncthreads();
     for (u32 d = 1; d < 1024; d <<= 1) {
@@ -58,33 +87,35 @@ __global__ void __launch_bounds__(1024) sw_scan_kernel(const u32 *__restrict__ n
         __syncthreads();
     }
     u32 run = part[tid] - sum;
-    for (u32 k = lo; k < hi; k++) { starts[k] = run; run += n_ops[k]; }
+    for (u32 k = lo; k < hi; k++) { const u32 c = tile_sum[k]; tile_sum[k] = run; run += c; }
     if (tid == 1023) starts[n] = part[1023];
 }
 
-cudaError_t launch_scan_counts(const u32 *n_ops, u32 *starts, u32 n, cudaStream_t stream)
+cudaError_t launch_scan_counts(const u32 *n_ops, u32 *starts, u32 *tile_sum, u32 n, cudaStream_t stream)
 {
-    sw_scan_kernel<<<1, 1024, 0, stream>>>(n_ops, starts, n);
+    const u32 n_tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+    if (n_tiles) sw_scan_tiles_kernel<<<n_tiles, 256, 0, stream>>>(n_ops, starts, tile_sum, n);
+    sw_scan_totals_kernel<<<1, 1024, 0, stream>>>(tile_sum, starts, n_tiles, n);
     return cudaGetLastError();
 }
 
 __global__ void __launch_bounds__(256) sw_compact_kernel(const u32 *__restrict__ scratch, const u64 *__restrict__ ops_end,
                                                          const u32 *__restrict__ n_ops, const u32 *__restrict__ starts,
-                                                         u32 *__restrict__ ops_out, u32 n)
+                                                         const u32 *__restrict__ tile_off, u32 *__restrict__ ops_out, u32 n)
 {
     const u32 p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
     const u32 cnt = n_ops[p];
     const u32 *src = scratch + (ops_end[p] - cnt);
-    u32 *dst = ops_out + starts[p];
+    u32 *dst = ops_out + tile_off[p / SCAN_TILE] + starts[p];
     for (u32 k = 0; k < cnt; k++) dst[k] = src[k];
 }
 
-cudaError_t launch_compact(const u32 *scratch, const u64 *ops_end, const u32 *n_ops, const u32 *starts,
+cudaError_t launch_compact(const u32 *scratch, const u64 *ops_end, const u32 *n_ops, const u32 *starts, const u32 *tile_off,
                            u32 *ops_out, u32 n, cudaStream_t stream)
 {
     if (n == 0) return cudaSuccess;
-    sw_compact_kernel<<<(n + 255) / 256, 256, 0, stream>>>(scratch, ops_end, n_ops, starts, ops_out, n);
+    sw_compact_kernel<<<(n + 255) / 256, 256, 0, stream>>>(scratch, ops_end, n_ops, starts, tile_off, ops_out, n);
     return cudaGetLastError();
 }
 
