@@ -43,6 +43,8 @@ def parse():
     ap.add_argument("--pairs", type=int, default=0, help="pairs per GPU (default: the config's size)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--chunk-pairs", type=int, default=0, help="engine chunk size (0: library default)")
+    ap.add_argument("--plan-threads", type=int, default=0, help="host planner threads (0: library default)")
     return ap.parse_args()
 
 
@@ -208,6 +210,10 @@ def main():
     d = synth.generate(args.config, n, first=rank * n, pinned=True)       # this rank's shard of the stream
     sw = mgl_b200.MicrosoftSmithWaterman(local)
     sw._ensure()                                                          # no GPU / no extension -> raises
+    if args.chunk_pairs:
+        sw.set_option("chunk_pairs", args.chunk_pairs)
+    if args.plan_threads:
+        sw.set_option("plan_threads", args.plan_threads)
 
     # integer issue rates (roofline denominator), measured on this box
     peaks = {}

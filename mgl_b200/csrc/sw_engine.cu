@@ -3,6 +3,9 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <condition_variable>
 #include <cstring>
 #include <mutex>
@@ -118,7 +121,7 @@ u64 Engine::budget()
     if (trace_budget_bytes) return trace_budget_bytes;
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return 4ull << 30;
-    u64 b = (u64)(free_b * 0.30);                 /* two slots + descriptors stay well inside HBM */
+    u64 b = (u64)(free_b * 0.60 / MGLSW_SLOTS);   /* all slots + descriptors stay well inside HBM */
     return std::max<u64>(std::min<u64>(b, 48ull << 30), 256ull << 20);
 }
 
@@ -311,6 +314,7 @@ struct InFlight { bool busy = false; int64_t first = 0; u32 n = 0; };
 
 int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
 {
+    const auto fn_t0 = std::chrono::steady_clock::now();
     BatchStats bs;
     std::memset(&bs, 0, sizeof bs);
     if (in.n < 0 || (in.n > 0 && (!in.arena || !in.ref_off || !in.alt_off || !in.ref_len || !in.alt_len)))
@@ -337,7 +341,7 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         bs.h2d_bytes += in.arena_bytes;
     }
 
-    InFlight fl[2];
+    InFlight fl[MGLSW_SLOTS];
     u64 ops_running = 0;
     bool overflow = false;
     int rc = MGL_SW_OK;
@@ -371,7 +375,7 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
      * Chunk boundaries first (a cheap scan), then the chunks are planned by a few host threads
      * running ahead of the GPU into a ring of staging entries, while this thread uploads,
      * launches and collects them in order.  Entry c % R is reused once chunk c - R has been
-     * collected; R = planners + 3 keeps every planner busy without blocking the collector.
+     * collected; R = planners + slots + 1 keeps every planner busy without blocking the collector.
      */
     std::vector<std::pair<int64_t, int64_t>> bounds;
     {
@@ -388,7 +392,7 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
     const int nchunks = (int)bounds.size();
     int nthreads = plan_threads > 0 ? plan_threads : (int)std::min<unsigned>(8u, std::max(1u, std::thread::hardware_concurrency() / 2));
     nthreads = std::min(nthreads, nchunks);
-    const int R = nthreads + 3;
+    const int R = nthreads + MGLSW_SLOTS + 1;
     while ((int)ring_.size() < R) ring_.push_back(new ChunkDev());
     std::vector<int> ready((size_t)nchunks, 0);          /* 0 pending, 1 planned, 2 failed */
     std::vector<int> prc((size_t)nchunks, MGL_SW_OK);
@@ -424,9 +428,14 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         cv.notify_all();
     };
 
+    const bool tl_on = std::getenv("MGL_SW_TIMELINE") != nullptr;     /* host timeline of the chunk pipeline on stderr */
+    const auto tl_t0 = std::chrono::steady_clock::now();
+    auto tl_ms = [&]() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tl_t0).count(); };
+    if (tl_on) std::fprintf(stderr, "[mgl_sw] %d chunks, %d planner threads, setup took %.2f ms\n", nchunks, nthreads,
+                            std::chrono::duration<double, std::milli>(tl_t0 - fn_t0).count());
     int c = 0;
     for (; c < nchunks && rc == MGL_SW_OK; c++) {
-        const int si = c & 1;
+        const int si = c % MGLSW_SLOTS;
         WorkSlot &ws = slots_[si];
         ChunkDev &cd = *ring_[(size_t)(c % R)];
         if (nchunks == 1) {
@@ -438,8 +447,10 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
             cv.wait(lk, [&] { return ready[(size_t)c] != 0; });
             if (ready[(size_t)c] == 2) { rc = fail(prc[(size_t)c], perr[(size_t)c]); break; }
         }
-        if ((rc = finish(si)) != MGL_SW_OK) break;              /* chunk c - 2: normally already home */
-        release_upto(c - 1);
+        const double t_ready = tl_ms();
+        if ((rc = finish(si)) != MGL_SW_OK) break;              /* chunk c - MGLSW_SLOTS: already home */
+        release_upto(c - MGLSW_SLOTS + 1);
+        const double t_slot = tl_ms();
         const int64_t first = cd.first;
         if ((rc = ensure_slot(ws, cd.plan, cd.n)) != MGL_SW_OK) break;
         if ((rc = upload_chunk(in, cd, ws.stream, !whole, bs)) != MGL_SW_OK) break;
@@ -452,15 +463,17 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         cudaEventRecord(ws.ev_counts, ws.post);
         cudaEventRecord(ws.ev_post, ws.post);
         fl[si].busy = true; fl[si].first = first; fl[si].n = n;
-        /* while this chunk runs, bring the previous one home */
-        if ((rc = finish(si ^ 1)) != MGL_SW_OK) break;
-        release_upto(c);
+        const double t_launched = tl_ms();
+        /* while the newest chunks run, bring the oldest one home: its slot is the next chunk's */
+        if ((rc = finish((c + 1) % MGLSW_SLOTS)) != MGL_SW_OK) break;
+        release_upto(c - MGLSW_SLOTS + 2);
+        if (tl_on) std::fprintf(stderr, "[mgl_sw] chunk %d n=%u: planned by %.2f ms, slot free %.2f, launched %.2f, previous chunk home %.2f\n",
+                                c, n, t_ready, t_slot, t_launched, tl_ms());
     }
     { std::lock_guard<std::mutex> lk(mu); stop = true; }
     cv.notify_all();
     for (std::thread &t : workers) t.join();
-    if (rc == MGL_SW_OK) rc = finish(c & 1);                    /* older chunk first (if any) */
-    if (rc == MGL_SW_OK) rc = finish((c & 1) ^ 1);
+    for (int k = 0; k < MGLSW_SLOTS && rc == MGL_SW_OK; k++) rc = finish((c + k) % MGLSW_SLOTS);   /* oldest first */
     if (rc != MGL_SW_OK) {
         cudaDeviceSynchronize();
         cudaGetLastError();
@@ -468,6 +481,7 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
     }
     out.ops_total = ops_running;
     if (stats) *stats = bs;
+    if (tl_on) std::fprintf(stderr, "[mgl_sw] batch done at %.2f ms\n", tl_ms());
     if (overflow) return fail(MGL_SW_E_OPS_CAPACITY, "ops buffer too small: need " + std::to_string(ops_running));
     return MGL_SW_OK;
 }
@@ -531,31 +545,30 @@ int Engine::run_resident(BatchStats *stats)
         return MGL_SW_OK;
     }
     /*
-     * Whole-batch throughput: chunks alternate between the two slots, so the traceback of chunk c
-     * (post stream) runs while chunk c + 1 fills.  One start event gates both fill streams; the
-     * time is start -> the later of the two post streams' last event.
+     * Whole-batch throughput: chunks rotate through the work slots, so the traceback of chunk c
+     * (post stream) runs while the next chunks fill.  One start event gates every fill stream; the
+     * time is start -> the latest of the post streams' last events.
      */
-    for (size_t c = 0; c < resident_.size() && c < 2; c++) {
-        int rc = ensure_slot(slots_[c], resident_[c]->plan, resident_[c]->n);
-        if (rc != MGL_SW_OK) return rc;
-    }
-    for (size_t c = 2; c < resident_.size(); c++) {        /* grow each slot to its largest chunk before timing */
-        int rc = ensure_slot(slots_[c & 1], resident_[c]->plan, resident_[c]->n);
+    for (size_t c = 0; c < resident_.size(); c++) {        /* grow each slot to its largest chunk before timing */
+        int rc = ensure_slot(slots_[c % MGLSW_SLOTS], resident_[c]->plan, resident_[c]->n);
         if (rc != MGL_SW_OK) return rc;
     }
     if ((e = cudaEventRecord(tev_[0], slots_[0].stream)) != cudaSuccess) return cuda_fail(e, "event record");
-    if ((e = cudaStreamWaitEvent(slots_[1].stream, tev_[0], 0)) != cudaSuccess) return cuda_fail(e, "stream wait");
+    for (int k = 1; k < MGLSW_SLOTS; k++)
+        if ((e = cudaStreamWaitEvent(slots_[k].stream, tev_[0], 0)) != cudaSuccess) return cuda_fail(e, "stream wait");
     for (size_t c = 0; c < resident_.size(); c++) {
-        int rc = run_chunk(*resident_[c], slots_[c & 1], bs, false);
+        int rc = run_chunk(*resident_[c], slots_[c % MGLSW_SLOTS], bs, false);
         if (rc != MGL_SW_OK) return rc;
     }
-    cudaEventRecord(tev_[4], slots_[0].post);
-    cudaEventRecord(tev_[5], slots_[1].post);
-    if ((e = cudaEventSynchronize(tev_[4])) != cudaSuccess) return cuda_fail(e, "batch execution");
-    if ((e = cudaEventSynchronize(tev_[5])) != cudaSuccess) return cuda_fail(e, "batch execution");
-    float a = 0, b = 0;
-    cudaEventElapsedTime(&a, tev_[0], tev_[4]);
-    cudaEventElapsedTime(&b, tev_[0], tev_[5]);
+    float a = 0;
+    for (int k = 0; k < MGLSW_SLOTS; k++) cudaEventRecord(tev_[5 + k], slots_[k].post);
+    for (int k = 0; k < MGLSW_SLOTS; k++) {
+        if ((e = cudaEventSynchronize(tev_[5 + k])) != cudaSuccess) return cuda_fail(e, "batch execution");
+        float b = 0;
+        cudaEventElapsedTime(&b, tev_[0], tev_[5 + k]);
+        a = b > a ? b : a;
+    }
+    const float b = a;
     bs.device_ms = a > b ? a : b;
     if (stats) *stats = bs;
     return MGL_SW_OK;

