@@ -102,7 +102,8 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
     const long long bias16 = std::min<long long>(need_bias, 49152);
     out.s16_bias = (int)bias16;
 
-    /* pass 2: sort key = (kind, G, nstrips, K, indel, ql, tl), all descending so heavy work launches first */
+    /* pass 2: sort key = (kind, G, K, nstrips, indel, ql, tl), all descending so heavy work launches first;
+       one launch per (kind, G, K): the strip count is a per-warp run-time value, not a kernel */
     std::vector<Keyed> order(n);
     for (u32 p = 0; p < n; p++) {
         const PairIn &pr = pairs[p];
@@ -120,8 +121,8 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
         /* 1 + 1 + 12 + 5 + 1 bits of launch key, then 24 + 20 bits of shape (tl clipped for the key only) */
         u64 key = (u64)(kind == KIND_S32 ? 1 : 0);
         key = (key << 1) | (G == (u32)MGLSW_G_LONG ? 1u : 0u);
-        key = (key << 12) | std::min<u32>(nstrips, 4095);
         key = (key << 5) | K;
+        key = (key << 12) | std::min<u32>(nstrips, 4095);
         key = (key << 1) | indel;
         key = (key << 24) | pr.ql;
         key = (key << 20) | std::min<u32>(pr.tl, (1u << 20) - 1);
@@ -131,7 +132,7 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
     radix_sort(order);
 
     /* pass 3: units, warps, launches */
-    auto launch_key = [](u64 k) { return (~k) >> 45; };          /* kind, G, nstrips, K */
+    auto launch_key = [](u64 k) { return (~k) >> 57; };          /* kind, G, K */
     auto pair_key = [](u64 k) { return (~k) >> 20; };            /* ... + indel + ql     */
     u32 pos = 0;
     while (pos < n) {
@@ -144,7 +145,7 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
         const u64 nk = ~order[pos].key;
         L.kind = ((nk >> 63) & 1) ? KIND_S32 : KIND_S16X2;
         L.G = ((nk >> 62) & 1) ? MGLSW_G_LONG : MGLSW_G_SHORT;
-        L.nstrips = L.G == MGLSW_G_SHORT ? 1u : ceil_div_u32(first.ql, (u32)MGLSW_G_LONG * MGLSW_KMAX);
+        L.nstrips = L.G == MGLSW_G_SHORT ? 1u : ceil_div_u32(first.ql, (u32)MGLSW_G_LONG * MGLSW_KMAX);   /* of its first unit */
         L.K = (int)regs_per_lane(first.ql, L.nstrips * L.G);
         L.first_unit = (u32)out.units.size();
         L.cells = 0;
@@ -174,8 +175,8 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
                 out.pairs_s16++;
                 q++;
             }
-            u.nstrips = L.nstrips;
-            const u32 slots = L.nstrips * (u32)L.G;
+            u.nstrips = L.G == MGLSW_G_SHORT ? 1u : ceil_div_u32(u.ql, (u32)MGLSW_G_LONG * MGLSW_KMAX);
+            const u32 slots = u.nstrips * (u32)L.G;
             u.col_base = u.ql / slots;
             u.col_rem = u.ql % slots;
             u.carry_rows = std::max(u.tl[0], u.tl[1]) + 1;
@@ -210,10 +211,10 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
                         out.carry_entries += 2ull * wu[g].carry_rows;
                     }
                     wu[g].lastrow_off = out.lastrow_words;
-                    out.lastrow_words += (u64)(L.kind == KIND_S16X2 ? 2 : 1) * L.nstrips * L.G * L.K;
+                    out.lastrow_words += (u64)(L.kind == KIND_S16X2 ? 2 : 1) * wu[g].nstrips * L.G * L.K;
                 }
             }
-            out.ckpt_words += warp_ckpt_words(L.nstrips, rb, (u32)L.K);
+            out.ckpt_words += warp_ckpt_words(wu[0].nstrips, rb, (u32)L.K);   /* G = 32: one unit per warp; G = 8: one strip */
         }
         out.cells += L.cells;
         out.launches.push_back(L);
