@@ -59,9 +59,15 @@ void WorkSlot::release()
     if (ev_done) cudaEventDestroy(ev_done);
     if (ev_fill) cudaEventDestroy(ev_fill);
     if (ev_post) cudaEventDestroy(ev_post);
+    if (ev_fork) cudaEventDestroy(ev_fork);
+    for (int k = 0; k < MGLSW_SIDE; k++) {
+        if (ev_side[k]) cudaEventDestroy(ev_side[k]);
+        if (side[k]) cudaStreamDestroy(side[k]);
+        ev_side[k] = nullptr; side[k] = nullptr;
+    }
     if (stream) cudaStreamDestroy(stream);
     if (post) cudaStreamDestroy(post);
-    ev_counts = ev_done = ev_fill = ev_post = nullptr; stream = post = nullptr;
+    ev_counts = ev_done = ev_fill = ev_post = ev_fork = nullptr; stream = post = nullptr;
 }
 
 /* ---------------------------------------------------------------- engine */
@@ -78,6 +84,11 @@ Engine::Engine(int device) : device_(device)
         cudaEventCreateWithFlags(&s.ev_done, cudaEventDisableTiming);
         cudaEventCreateWithFlags(&s.ev_fill, cudaEventDisableTiming);
         cudaEventCreateWithFlags(&s.ev_post, cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&s.ev_fork, cudaEventDisableTiming);
+        for (int k = 0; k < MGLSW_SIDE; k++) {
+            cudaStreamCreateWithPriority(&s.side[k], cudaStreamNonBlocking, prio_lo);
+            cudaEventCreateWithFlags(&s.ev_side[k], cudaEventDisableTiming);
+        }
         cudaEventRecord(s.ev_post, s.post);
     }
     for (auto &e : tev_) cudaEventCreate(&e);
@@ -249,7 +260,17 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed)
     const Scores &sc = resident_scores_;
     if ((e = cudaStreamWaitEvent(st, ws.ev_post, 0)) != cudaSuccess) return cuda_fail(e, "stream wait");
     if (timed) cudaEventRecord(tev_[0], st);
+    /* the buckets are independent: launch i goes to stream i mod (1 + MGLSW_SIDE), side streams fork from and join `st` */
+    const int nside = (int)std::min<size_t>(MGLSW_SIDE, cd.plan.launches.size() > 0 ? cd.plan.launches.size() - 1 : 0);
+    if (nside > 0) {
+        if ((e = cudaEventRecord(ws.ev_fork, st)) != cudaSuccess) return cuda_fail(e, "event record");
+        for (int k = 0; k < nside; k++)
+            if ((e = cudaStreamWaitEvent(ws.side[k], ws.ev_fork, 0)) != cudaSuccess) return cuda_fail(e, "stream wait");
+    }
+    int li = 0;
     for (const Launch &L : cd.plan.launches) {
+        const int lane = li++ % (nside + 1);
+        cudaStream_t ls = lane == 0 ? st : ws.side[lane - 1];
         FillArgs a;
         a.arena = arena_dev();
         a.units = (const UnitDesc *)cd.units.p;
@@ -259,9 +280,13 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed)
         a.colbest = (u32 *)ws.colbest.p;
         a.n_warps = L.n_warps;
         a.c = L.kind == KIND_S16X2 ? make_consts<S16x2>(sc, cd.plan.s16_bias) : make_consts<S32>(sc, 0);
-        if ((e = launch_fill_any(L.kind, L.G, L.K, a, L.first_unit, st)) != cudaSuccess)
+        if ((e = launch_fill_any(L.kind, L.G, L.K, a, L.first_unit, ls)) != cudaSuccess)
             return cuda_fail(e, "fill launch (is a kernel built for this kind/G/K?)");
         bs.fill_launches++;
+    }
+    for (int k = 0; k < nside; k++) {
+        if ((e = cudaEventRecord(ws.ev_side[k], ws.side[k])) != cudaSuccess) return cuda_fail(e, "event record");
+        if ((e = cudaStreamWaitEvent(st, ws.ev_side[k], 0)) != cudaSuccess) return cuda_fail(e, "stream wait");
     }
     if (timed) cudaEventRecord(tev_[1], st);
     if ((e = cudaEventRecord(ws.ev_fill, st)) != cudaSuccess) return cuda_fail(e, "event record");

@@ -22,6 +22,9 @@
 
 /* work slots: chunks in flight at once (each owns checkpoint, scratch and result buffers and two streams) */
 #define MGLSW_SLOTS 4
+/* side streams of a slot: a chunk's fill launches (one per (arithmetic, G, K) bucket) are independent, so they are
+   spread over these and run side by side; a bucket of a few long pairs no longer holds the whole GPU */
+#define MGLSW_SIDE 7
 
 namespace mglsw {
 
@@ -79,6 +82,8 @@ struct WorkSlot {
     cudaStream_t post = nullptr;         /* traceback, scan, compact, downloads: higher priority, so that the   */
                                          /* latency-bound traceback of one chunk slips in between the blocks of */
                                          /* the other slot's fill instead of queueing behind them               */
+    cudaStream_t side[MGLSW_SIDE] = {};  /* further fill launches of the same chunk, forked from / joined into `stream` */
+    cudaEvent_t ev_fork = nullptr, ev_side[MGLSW_SIDE] = {};
     cudaEvent_t ev_fill = nullptr, ev_post = nullptr, ev_counts = nullptr, ev_done = nullptr;
     DevBuf ckpt, carry, lastrow, colbest, scratch, offsets, n_ops, starts, tiles, ops;
     PinBuf h_n_ops, h_total;
