@@ -13,6 +13,7 @@
 
 #include "../../include/mgl_sw.h"
 #include "sw_cell.h"
+#include "sw_config.h"
 #include "sw_kernels.h"
 #include "sw_layout.h"
 
@@ -130,10 +131,14 @@ int Engine::reserve_arena(const BatchIn &in)
 u64 Engine::budget()
 {
     if (trace_budget_bytes) return trace_budget_bytes;
+    /* taken once, from the memory free before this engine owns any work buffer: chunk boundaries (and so the sizes the
+       slots grow to) must not move from one batch to the next as the engine's own buffers eat into the free figure */
+    if (budget_auto_) return budget_auto_;
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return 4ull << 30;
     u64 b = (u64)(free_b * 0.60 / MGLSW_SLOTS);   /* all slots + descriptors stay well inside HBM */
-    return std::max<u64>(std::min<u64>(b, 48ull << 30), 256ull << 20);
+    budget_auto_ = std::max<u64>(std::min<u64>(b, 48ull << 30), 256ull << 20);
+    return budget_auto_;
 }
 
 /*
@@ -147,7 +152,11 @@ int64_t Engine::chunk_take(const BatchIn &in, int64_t first, u64 limit, u32 max_
     int64_t take = 0;
     for (; take < n; take++) {
         const u64 tl = in.ref_len[first + take], ql = in.alt_len[first + take];
-        const u64 bytes = (tl + 40) * (ql + 32) * 7 / 5;         /* checkpoints: 0.65 (u16x2) .. 1.3 (s32) B per padded cell */
+        /* checkpoint bytes with the planner's geometry (sw_plan.cpp), as if the pair ran alone in 32-bit arithmetic */
+        const u32 G = ql <= (u64)MGLSW_G_SHORT * MGLSW_KMAX ? MGLSW_G_SHORT : MGLSW_G_LONG;
+        const u32 ns = G == MGLSW_G_SHORT ? 1u : ceil_div_u32((u32)ql, (u32)MGLSW_G_LONG * MGLSW_KMAX);
+        const u32 K = regs_per_lane((u32)ql, ns * G);
+        const u64 bytes = (u64)ns * row_blocks((u32)tl, G) * lane_stride16(K) * 16u * G;
         if (take > 0 && est + bytes > limit) break;
         est += bytes;
     }

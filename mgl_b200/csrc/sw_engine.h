@@ -126,6 +126,7 @@ private:
     u64 budget();
 
     int device_;
+    u64 budget_auto_ = 0;        /* budget() when trace_budget_bytes == 0, fixed at first use */
     std::string err_;
     DevBuf arena_;               /* device copy of the caller's arena, padded on both sides (sw_fill.h) */
     const uint8_t *arena_dev() const { return (const uint8_t *)arena_.p + MGLSW_ARENA_FRONT_PAD; }

@@ -65,10 +65,10 @@ struct FillLane {
     u32 e[K], hm[K], bq[K];
     u32 hleft;                /* H[i-1][first col - 1] + match: diagonal input of register 0 */
     u32 h_out, f_out;         /* this step's values for the right-hand neighbour      */
+    u32 f_mid;                /* F leaving register KM - 1 at the lane's latest row    */
     u32 rq0[MGLSW_REF_AHEAD], rq1[MGLSW_REF_AHEAD];   /* ref bytes of the next steps' rows, loaded MGLSW_REF_AHEAD steps early, merged at use */
     Carry cin_next;           /* carry-in of the next step's row (strips > 0, lane 0) */
     u32 bh, bf, bdec;         /* column-0 boundary of the next step's row (lane 0), and its per-row decrement */
-    u32 ev_next;              /* step of this lane's next event (events())            */
     u32 best0, best1;         /* running last-column maximum: S16x2 (value << 16 | row) per half; S32 value, row */
 
     /* lane constants */
@@ -184,55 +184,71 @@ struct FillLane {
         reset_rows(c);
         h_out = T::rep(c.bias);
         f_out = T::rep(c.bias);
+        f_mid = T::rep(c.bias);
         for (u32 q = 0; q < MGLSW_REF_AHEAD; q++) fetch_ref(q);
-        ev_next = lane;                               /* row 0 comes first: tl >= 1 */
         cin_next = fetch_carry(-(int)lane);
         /*
          * Column 0 as lane 0 of strip 0 sees it at step t (row t): H[t][0] + match and the F seed
          * H[t][0] - go (sw.cpp:47-49 and :22-26,38).  Constant without the INDEL boundary, a ramp
          * of -ge per row with it; kept as running values so a step costs two subtractions.
-         * The value for t == 0 is never used by a real row (row 0 is recomputed by reset_rows).
+         * The value for t == 0 is never used: a lane sits out the steps of rows < 1 (step()).
          */
         bdec = indel ? T::rep(c.s_ge) : 0u;
         bh = T::rep(c.bias + c.s_match + (indel ? -c.s_go + c.s_ge : 0));
         bf = T::rep(c.bias - c.s_go + (indel ? -c.s_go + c.s_ge : 0));
     }
 
-    /* row 0: start over from the boundary; row tl of a half: capture its last row and last-column maximum */
-    SW_HD void events(const CellConsts &c, u32 t)
+    /*
+     * A lane only WORKS on rows 1..tl0 (tl0 >= tl1: the longer ref of a unit sits in the low half);
+     * at the other steps of the warp's loop -- before its row 1 (the lane skew), after its last row
+     * (a longer ref in another lane group) -- it sits out and its registers keep what they hold.  So
+     * the state strip_begin() sets up is still intact when row 1 arrives, and after the loop the
+     * registers still hold row tl0: the last row (sw.cpp:116-127) and the last-column maximum
+     * (sw.cpp:100-104) are stored once, by all lanes together, in strip_end().  Only a high half
+     * with a shorter ref has to be captured on the way, at its row tl1.
+     */
+    SW_HD bool works_at(u32 t) const { const int i = (int)t - (int)lane; return i >= 1 && i <= (int)tl0; }
+    SW_HD bool hi_event_at(u32 t) const { return T::PAIRS == 2 && tl1 != tl0 && (int)t - (int)lane == (int)tl1; }
+    /* true if this lane works at all four steps t0 .. t0 + 3 and has no high-half capture among them */
+    SW_HD bool quiet4(u32 t0) const
     {
-        const int i = (int)t - (int)lane;
-        if (active) {
-            const bool owner = (lane == G - 1) && (strip + 1 == nstrips);
-            if (i == (int)tl0) {
+        const int i0 = (int)t0 - (int)lane;
+        bool q = i0 >= 1 && i0 + 3 <= (int)tl0;
+        if (T::PAIRS == 2 && tl1 != tl0 && (int)tl1 >= i0 && (int)tl1 <= i0 + 3) q = false;
+        return q;
+    }
+    SW_HD void capture_hi()
+    {
+        if (!active) return;
 #pragma unroll
-                for (int k = 0; k < K; k++) lastrow[(size_t)slot * K + k] = hm[k];
-                if (owner) {
-                    if (T::PAIRS == 2) { colbest[0] = best0 >> 16; colbest[1] = best0 & 0xffffu; }
-                    else { colbest[0] = best0; colbest[1] = best1; }
-                }
-            }
-            if (T::PAIRS == 2 && i == (int)tl1) {
+        for (int k = 0; k < K; k++) lastrow[(size_t)(nslots + slot) * K + k] = hm[k];
+        if (lane == G - 1 && strip + 1 == nstrips) { colbest[2] = best1 >> 16; colbest[3] = best1 & 0xffffu; }
+    }
+    SW_HD void strip_end()
+    {
+        if (!active) return;
+        const bool owner = (lane == G - 1) && (strip + 1 == nstrips);
 #pragma unroll
-                for (int k = 0; k < K; k++) lastrow[(size_t)(nslots + slot) * K + k] = hm[k];
-                if (owner) { colbest[2] = best1 >> 16; colbest[3] = best1 & 0xffffu; }
-            }
+        for (int k = 0; k < K; k++) lastrow[(size_t)slot * K + k] = hm[k];
+        if (T::PAIRS == 2 && tl1 == tl0) {
+#pragma unroll
+            for (int k = 0; k < K; k++) lastrow[(size_t)(nslots + slot) * K + k] = hm[k];
         }
-        if (i == 0) reset_rows(c);
-        u32 nx = 0xffffffffu;
-        const u32 e1 = tl0 + lane, e2 = tl1 + lane;
-        if (e1 > t && e1 < nx) nx = e1;
-        if (e2 > t && e2 < nx) nx = e2;
-        ev_next = nx;
+        if (owner) {
+            if (T::PAIRS == 2) {
+                colbest[0] = best0 >> 16; colbest[1] = best0 & 0xffffu;
+                if (tl1 == tl0) { colbest[2] = best1 >> 16; colbest[3] = best1 & 0xffffu; }
+            } else { colbest[0] = best0; colbest[1] = best1; }
+        }
     }
 
     /*
      * One wavefront step: this lane computes ref row i = t - lane over its K
      * registers.  h_sh / f_sh are the neighbour's previous-step outputs.
-     * EV = false leaves the event check out: the kernel uses it for groups of steps
-     * in which no lane of the warp has an event.
+     * MASKED = false: the caller knows that every lane of the warp works at this step (quiet4());
+     * MASKED = true: the lane checks for itself, and sits out or captures its high half.
      */
-    template <bool EV = true>
+    template <bool MASKED = true>
     SW_HD void step(const CellConsts &c, u32 t, u32 h_sh, u32 f_sh)
     {
         const int i = (int)t - (int)lane;
@@ -254,44 +270,46 @@ struct FillLane {
         bh -= bdec;
         bf -= bdec;
 
-        u32 diag = hleft;
-        hleft = h_in;
-        u32 f = f_in;
-        u32 f_km2 = f_in, f_mid = f_in;
+        if (!MASKED || works_at(t)) {
+            u32 diag = hleft;
+            hleft = h_in;
+            u32 f = f_in;
+            u32 f_km2 = f_in, f_mid_ = f_in;
 #pragma unroll
-        for (int k = 0; k < K; k++) {
-            const u32 old = hm[k];
-            sw_cell<T>(c, ra, bq[k], diag, e[k], f, hm[k]);
-            diag = old;
-            if (k == K - 2) f_km2 = f;
-            if (k == KM - 1) f_mid = f;
-        }
-        if (n == (u32)K) { h_out = hm[K - 1]; f_out = f; }
-        else             { h_out = K >= 2 ? hm[K >= 2 ? K - 2 : 0] : h_in; f_out = f_km2; }
+            for (int k = 0; k < K; k++) {
+                const u32 old = hm[k];
+                sw_cell<T>(c, ra, bq[k], diag, e[k], f, hm[k]);
+                diag = old;
+                if (k == K - 2) f_km2 = f;
+                if (k == KM - 1) f_mid_ = f;
+            }
+            f_mid = f_mid_;
+            if (n == (u32)K) { h_out = hm[K - 1]; f_out = f; }
+            else             { h_out = K >= 2 ? hm[K >= 2 ? K - 2 : 0] : h_in; f_out = f_km2; }
 
-        /* running maximum of this lane's last column; meaningful in the lane that owns column ql */
-        if (T::PAIRS == 2) {
+            /* running maximum of this lane's last column; meaningful in the lane that owns column ql */
+            if (T::PAIRS == 2) {
 #if SW_ON_DEVICE
-            const u32 k0 = __byte_perm((u32)i, h_out, 0x5410);       /* low half of h_out : low 16 bits of the row  */
-            const u32 k1 = __byte_perm((u32)i, h_out, 0x7610);       /* high half of h_out : low 16 bits of the row */
+                const u32 k0 = __byte_perm((u32)i, h_out, 0x5410);       /* low half of h_out : low 16 bits of the row  */
+                const u32 k1 = __byte_perm((u32)i, h_out, 0x7610);       /* high half of h_out : low 16 bits of the row */
 #else
-            const u32 k0 = (h_out << 16) | ((u32)i & 0xffffu);
-            const u32 k1 = (h_out & 0xffff0000u) | ((u32)i & 0xffffu);
+                const u32 k0 = (h_out << 16) | ((u32)i & 0xffffu);
+                const u32 k1 = (h_out & 0xffff0000u) | ((u32)i & 0xffffu);
 #endif
-            best0 = k0 > best0 ? k0 : best0;
-            best1 = k1 > best1 ? k1 : best1;
-        } else if ((int)h_out >= (int)best0) { best0 = h_out; best1 = (u32)i; }
+                best0 = k0 > best0 ? k0 : best0;
+                best1 = k1 > best1 ? k1 : best1;
+            } else if ((int)h_out >= (int)best0) { best0 = h_out; best1 = (u32)i; }
 
-        if (STRIPS && active && lane == G - 1 && i >= 1 && i <= (int)own_rows) {
-            Carry *col = carry_cols + (size_t)(strip & 1u) * carry_rows;
+            if (STRIPS && active && lane == G - 1) {
+                Carry *col = carry_cols + (size_t)(strip & 1u) * carry_rows;
 #if SW_ON_DEVICE
-            __stcg(reinterpret_cast<uint2 *>(col + i), make_uint2(h_out, f_out));
+                __stcg(reinterpret_cast<uint2 *>(col + i), make_uint2(h_out, f_out));
 #else
-            col[i].h = h_out; col[i].f = f_out;
+                col[i].h = h_out; col[i].f = f_out;
 #endif
+            }
+            if (MASKED && hi_event_at(t)) capture_hi();
         }
-        /* the three things that happen once per lane and strip (row 0, row tl of either half) hide behind one compare */
-        if (EV && t == ev_next) events(c, t);
 
         /*
          * Checkpoints (sw_layout.h).  Every step: (H + match, F) leaving register KM - 1 and leaving the

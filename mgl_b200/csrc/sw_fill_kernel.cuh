@@ -12,7 +12,10 @@
 namespace mglsw {
 
 template <class T, int G, int K>
-__global__ void __launch_bounds__(MGLSW_FILL_THREADS)
+#ifndef MGLSW_FILL_MINB
+#define MGLSW_FILL_MINB 3
+#endif
+__global__ void __launch_bounds__(MGLSW_FILL_THREADS, MGLSW_FILL_MINB)
 sw_fill_kernel(const __grid_constant__ FillArgs a, const u32 first_unit)
 {
     const u32 warp = blockIdx.x * (MGLSW_FILL_THREADS / 32) + (threadIdx.x >> 5);
@@ -33,8 +36,8 @@ sw_fill_kernel(const __grid_constant__ FillArgs a, const u32 first_unit)
         L.strip_begin(a.c, s);
         for (u32 g = 0; g < steps / 4; g++) {           /* steps is a multiple of MGLSW_RB = 8 */
             const u32 t0 = g * 4u;
-            if (__any_sync(0xffffffffu, L.ev_next < t0 + 4u)) {
-                /* some lane starts its first row or reaches its last one in these four steps */
+            if (!__all_sync(0xffffffffu, L.quiet4(t0))) {
+                /* some lane has not reached its row 1 yet, is past its last row, or captures a high half in these four steps */
 #pragma unroll 1
                 for (u32 s4 = 0; s4 < 4; s4++) {
                     const u32 h = __shfl_up_sync(0xffffffffu, L.h_out, 1, G);
@@ -50,6 +53,7 @@ sw_fill_kernel(const __grid_constant__ FillArgs a, const u32 first_unit)
                 }
             }
         }
+        L.strip_end();
         __syncwarp();                            /* carry column of strip s is read by lane 0 in strip s + 1 */
     }
     /* the last region's bulk store still reads this block's shared memory */

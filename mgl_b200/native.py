@@ -8,7 +8,8 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libmgl_sw.so")
+# MGL_SW_LIB: developer knob for A/B runs of differently built kernels; unset in production
+LIB_PATH = os.environ.get("MGL_SW_LIB") or os.path.join(HERE, "libmgl_sw.so")
 
 OK, E_INVALID, E_SCORES, E_PAIR, E_CUDA, E_OPS_CAPACITY, E_NO_DEVICE = 0, -1, -2, -3, -4, -5, -6
 _CODES = {E_INVALID: "invalid argument", E_SCORES: "score set out of range", E_PAIR: "empty or over-long sequence",

@@ -36,13 +36,18 @@ void emu_launch(const FillArgs &a, const Launch &L)
         for (u32 s = 0; s < wu[0].nstrips; s++) {
             for (u32 l = 0; l < 32; l++) lanes[l].strip_begin(a.c, s);
             for (u32 t = 0; t < steps; t++) {
+                /* the kernel's choice between the unmasked and the masked step, per group of four steps (sw_fill_kernel.cuh) */
+                bool quiet = true;
+                for (u32 l = 0; l < 32; l++) quiet = quiet && lanes[l].quiet4(t & ~3u);
                 u32 hs[32], fs[32];
                 for (u32 l = 0; l < 32; l++) { hs[l] = lanes[l].h_out; fs[l] = lanes[l].f_out; }
                 for (u32 l = 0; l < 32; l++) {
                     const u32 src = (l % G) ? l - 1 : l;      /* __shfl_up_sync(.., 1, G) */
-                    lanes[l].step(a.c, t, hs[src], fs[src]);
+                    if (quiet) lanes[l].template step<false>(a.c, t, hs[src], fs[src]);
+                    else lanes[l].template step<true>(a.c, t, hs[src], fs[src]);
                 }
             }
+            for (u32 l = 0; l < 32; l++) lanes[l].strip_end();
         }
     }
 }
