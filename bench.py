@@ -263,7 +263,10 @@ def main():
     e2e_ms = 0.0
     h2d = d2h = 0
     if not args.no_e2e:
-        out = (native.pinned_array(n, np.int32), native.pinned_array(n + 1, np.uint64), native.pinned_array(8 * n, np.uint32))
+        # CIGAR element capacity: 8 per pair covers the short-read configs; long pairs carry ~1 element per 40 bases
+        total_len = int(d["ref_len"].astype(np.int64).sum() + d["alt_len"].astype(np.int64).sum())
+        out = (native.pinned_array(n, np.int32), native.pinned_array(n + 1, np.uint64),
+               native.pinned_array(max(8 * n, total_len // 8), np.uint32))
         for _ in range(min(args.warmup, 2)):
             sw.align_arrays(d["arena"], d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, d["strategies"], out=out)
         barrier(dist, local)
