@@ -44,7 +44,6 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--chunk-pairs", type=int, default=0, help="engine chunk size (0: library default)")
-    ap.add_argument("--acgt", type=int, default=1, help="0: switch the byte-permute (all-ACGT) cell off (A/B runs)")
     ap.add_argument("--plan-threads", type=int, default=0, help="host planner threads (0: library default)")
     return ap.parse_args()
 
@@ -211,8 +210,6 @@ def main():
     d = synth.generate(args.config, n, first=rank * n, pinned=True)       # this rank's shard of the stream
     sw = mgl_b200.MicrosoftSmithWaterman(local)
     sw._ensure()                                                          # no GPU / no extension -> raises
-    if not args.acgt:
-        sw.set_option("allow_acgt", 0)
     if args.chunk_pairs:
         sw.set_option("chunk_pairs", args.chunk_pairs)
     if args.plan_threads:

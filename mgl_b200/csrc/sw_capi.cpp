@@ -101,7 +101,6 @@ int mgl_sw_set_option(mgl_sw_handle *h, const char *name, int64_t value)
     if (!h || !name) return MGL_SW_E_INVALID;
     std::lock_guard<std::mutex> lk(h->mu);
     if (!std::strcmp(name, "allow_s16")) h->engine->allow_s16 = value != 0;
-    else if (!std::strcmp(name, "allow_acgt")) h->engine->allow_acgt = value != 0;
     else if (!std::strcmp(name, "overlap")) h->engine->overlap = value != 0;
     else if (!std::strcmp(name, "plan_threads")) { if (value < 0 || value > 64) return MGL_SW_E_INVALID; h->engine->plan_threads = (int)value; }
     else if (!std::strcmp(name, "chunk_pairs")) { if (value < 1 || value > (1 << 22)) return MGL_SW_E_INVALID; h->engine->chunk_pairs = (u32)value; }

@@ -105,41 +105,6 @@ struct S32 {
     }
 };
 
-/*
- * ACGT fast path.  When every byte of a unit's sequences is one of A, C, G, T (checked on the
- * device by sw_classify_kernel; anything else takes the general byte-compare cell), the
- * mismatch indicator of a cell is ONE byte-permute instead of xor + min:
- *   code(b)  = (b >> 1) & 3                      A 0, C 1, T 2, G 3
- *   table(r) = 0x01010101 ^ (1 << 8 code(r))     byte c of the ref base's table = (c != code(r))
- *   m        = PRMT(table(r0), table(r1), sel)   sel nibbles: code(a0) | 8 | 4 + code(a1) | 8
- * Selector nibble 8 = "byte 0, replicate its sign bit" = 0x00 (table bytes are 0 or 1), so m has
- * pair 0's flag in its low half and pair 1's in its high half, exactly what xor + min gives.
- * The table of a ref byte is looked up in a 256-entry shared-memory array one step ahead of its
- * use; the selectors are built once per strip.  One ALU-pipe instruction fewer per cell, and the
- * ALU pipe is what bounds the fill.
- */
-SW_HD bool is_acgt(u32 b) { return b == 0x41u || b == 0x43u || b == 0x47u || b == 0x54u; }
-SW_HD u32 base_code(u32 b) { return (b >> 1) & 3u; }
-SW_HD u32 base_table(u32 b) { return is_acgt(b) ? (0x01010101u ^ (1u << (8u * base_code(b)))) : 0x01010101u; }
-SW_HD u32 byte_perm_sw(u32 x, u32 y, u32 s)
-{
-#if SW_ON_DEVICE
-    u32 r;
-    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(x), "r"(y), "r"(s));   /* default mode: selector bit 3 replicates the byte's sign */
-    return r;
-#else
-    const u64 xy = (u64)x | ((u64)y << 32);
-    u32 r = 0;
-    for (int k = 0; k < 4; k++) {
-        const u32 nib = (s >> (4 * k)) & 15u;
-        u32 b = (u32)(xy >> (8 * (nib & 7u))) & 0xffu;
-        if (nib & 8u) b = (b & 0x80u) ? 0xffu : 0u;
-        r |= b << (8 * k);
-    }
-    return r;
-#endif
-}
-
 template <class T>
 SW_HD CellConsts make_consts(const Scores &s, int bias)
 {
@@ -163,17 +128,6 @@ SW_HD CellConsts make_consts(const Scores &s, int bias)
  * in c.one) so that they issue to the FMA pipe -- an SM sub-partition owns one 16-lane
  * pipe of each kind and one issue slot per clock (int_peak.cu measures both).
  */
-template <class T>
-SW_HD void sw_cell_m(const CellConsts &c, u32 m, u32 hdm, u32 &e, u32 &f, u32 &hm)
-{
-    const u32 d = m * c.neg_delta + hdm;      /* H_diag + match - m * (match - mismatch) */
-    const u32 h = T::max3(d, e, f);
-    const u32 hgo = h * c.one + c.neg_go;
-    e = T::addmax(e, c.neg_ge, hgo);
-    f = T::addmax(f, c.neg_ge, hgo);
-    hm = h * c.one + c.match;
-}
-
 template <class T>
 SW_HD void sw_cell(const CellConsts &c, u32 ra, u32 bq, u32 hdm, u32 &e, u32 &f, u32 &hm)
 {

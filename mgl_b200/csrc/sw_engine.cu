@@ -54,7 +54,7 @@ void ChunkDev::release()
 void WorkSlot::release()
 {
     ckpt.release(); carry.release(); lastrow.release(); colbest.release(); scratch.release();
-    offsets.release(); n_ops.release(); starts.release(); tiles.release(); ops.release(); acgt.release();
+    offsets.release(); n_ops.release(); starts.release(); tiles.release(); ops.release();
     h_n_ops.release(); h_total.release();
     if (ev_counts) cudaEventDestroy(ev_counts);
     if (ev_done) cudaEventDestroy(ev_done);
@@ -248,7 +248,6 @@ int Engine::ensure_slot(WorkSlot &ws, const ChunkPlan &plan, u32 n)
     if ((e = ws.lastrow.reserve((plan.lastrow_words + 1) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc lastrow");
     if ((e = ws.colbest.reserve((plan.units.size() + 1) * 4 * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc colbest");
     if ((e = ws.scratch.reserve((plan.scratch_words + 1) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc scratch");
-    if ((e = ws.acgt.reserve(plan.units.size() + 1)) != cudaSuccess) return cuda_fail(e, "cudaMalloc acgt");
     if ((e = ws.offsets.reserve((size_t)n * sizeof(int))) != cudaSuccess) return cuda_fail(e, "cudaMalloc");
     if ((e = ws.n_ops.reserve((size_t)n * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc");
     if ((e = ws.starts.reserve(((size_t)n + 1) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc");
@@ -270,11 +269,6 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed)
     const Scores &sc = resident_scores_;
     if ((e = cudaStreamWaitEvent(st, ws.ev_post, 0)) != cudaSuccess) return cuda_fail(e, "stream wait");
     if (timed) cudaEventRecord(tev_[0], st);
-    if (allow_acgt) {
-        if ((e = launch_classify(arena_dev(), (const UnitDesc *)cd.units.p, (u32)cd.plan.units.size(), (uint8_t *)ws.acgt.p, st)) != cudaSuccess)
-            return cuda_fail(e, "classify launch");
-        bs.other_launches++;
-    }
     /* the buckets are independent: launch i goes to stream i mod (1 + MGLSW_SIDE), side streams fork from and join `st` */
     const int nside = (int)std::min<size_t>(MGLSW_SIDE, cd.plan.launches.size() > 0 ? cd.plan.launches.size() - 1 : 0);
     if (nside > 0) {
@@ -293,7 +287,6 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed)
         a.carry = (Carry *)ws.carry.p;
         a.lastrow = (u32 *)ws.lastrow.p;
         a.colbest = (u32 *)ws.colbest.p;
-        a.acgt = allow_acgt ? (const uint8_t *)ws.acgt.p : nullptr;
         a.n_warps = L.n_warps;
         a.c = L.kind == KIND_S16X2 ? make_consts<S16x2>(sc, cd.plan.s16_bias) : make_consts<S32>(sc, 0);
         if ((e = launch_fill_any(L.kind, L.G, L.K, a, L.first_unit, ls)) != cudaSuccess)

@@ -85,7 +85,7 @@ struct WorkSlot {
     cudaStream_t side[MGLSW_SIDE] = {};  /* further fill launches of the same chunk, forked from / joined into `stream` */
     cudaEvent_t ev_fork = nullptr, ev_side[MGLSW_SIDE] = {};
     cudaEvent_t ev_fill = nullptr, ev_post = nullptr, ev_counts = nullptr, ev_done = nullptr;
-    DevBuf ckpt, carry, lastrow, colbest, scratch, offsets, n_ops, starts, tiles, ops, acgt;
+    DevBuf ckpt, carry, lastrow, colbest, scratch, offsets, n_ops, starts, tiles, ops;
     PinBuf h_n_ops, h_total;
     void release();
 };
@@ -108,7 +108,6 @@ public:
     void drop_resident();
 
     bool allow_s16 = true;
-    bool allow_acgt = true;      /* classify units on the device and run all-ACGT ones through the byte-permute cell (sw_cell.h) */
     bool overlap = true;         /* run_resident: alternate the two slots so traceback(c) overlaps fill(c + 1);
                                     false = one chunk at a time with per-kernel event timing */
     u32 chunk_pairs = 1u << 16;  /* measured: 64 Ki pairs per chunk with four slots is within 1 % of the best device rate and plans in < 5 ms */

@@ -51,7 +51,6 @@ struct FillArgs {
     Carry *carry;             /* strip carry columns (G == 32 launches only)          */
     u32 *lastrow;             /* captured last rows                                   */
     u32 *colbest;             /* per unit 4 words: (value, row) of the last-column maximum of each half */
-    const uint8_t *acgt;      /* per unit: 1 if all its sequence bytes are A/C/G/T (sw_classify_kernel), or NULL */
     u32 n_warps;
     CellConsts c;
 };
@@ -68,8 +67,6 @@ struct FillLane {
     u32 h_out, f_out;         /* this step's values for the right-hand neighbour      */
     u32 f_mid;                /* F leaving register KM - 1 at the lane's latest row    */
     u32 rq0[MGLSW_REF_AHEAD], rq1[MGLSW_REF_AHEAD];   /* ref bytes of the next steps' rows, loaded MGLSW_REF_AHEAD steps early, merged at use */
-    u32 tq0, tq1;             /* ACGT fast path: mismatch tables (sw_cell.h) of this step's ref bytes, looked up one step ahead */
-    const u32 *lut;           /* ... the 256-entry byte -> table array (shared memory on the device) */
     Carry cin_next;           /* carry-in of the next step's row (strips > 0, lane 0) */
     u32 bh, bf, bdec;         /* column-0 boundary of the next step's row (lane 0), and its per-row decrement */
     u32 best0, best1;         /* running last-column maximum: S16x2 (value << 16 | row) per half; S32 value, row */
@@ -123,7 +120,6 @@ struct FillLane {
         ckpt_base = a.ckpt + u.ckpt_off;
         ckpt_cur = ckpt_base;
         stage = nullptr;
-        lut = nullptr;
         carry_cols = a.carry + u.carry_off;
         carry_rows = u.carry_rows;
         lastrow = a.lastrow + u.lastrow_off;
@@ -170,8 +166,6 @@ struct FillLane {
         best1 = 0u;
     }
 
-    /* FAST: the ACGT fast path -- bq[] holds byte-permute selectors instead of alt bytes */
-    template <bool FAST = false>
     SW_HD void strip_begin(const CellConsts &c, u32 s)
     {
         strip = s;
@@ -184,11 +178,7 @@ struct FillLane {
             u32 j = j0 + (u32)k;                      /* 1-based column */
             if (j > ql) j = ql;                       /* virtual register: any byte will do */
             u32 b = SW_LDG(alt0 + (j - 1));
-            if (FAST) b = base_code(b) | 0x8880u;
-            if (T::PAIRS == 2) {
-                const u32 b1 = SW_LDG(alt1 + (j - 1));
-                b = FAST ? ((b & 0xf0ffu) | ((4u + base_code(b1)) << 8)) : (b | (b1 << 16));
-            }
+            if (T::PAIRS == 2) b |= (u32)SW_LDG(alt1 + (j - 1)) << 16;
             bq[k] = b;
         }
         reset_rows(c);
@@ -196,8 +186,6 @@ struct FillLane {
         f_out = T::rep(c.bias);
         f_mid = T::rep(c.bias);
         for (u32 q = 0; q < MGLSW_REF_AHEAD; q++) fetch_ref(q);
-        tq0 = tq1 = 0u;
-        if (FAST) { tq0 = lut[rq0[0]]; tq1 = T::PAIRS == 2 ? lut[rq1[0]] : 0u; }
         cin_next = fetch_carry(-(int)lane);
         /*
          * Column 0 as lane 0 of strip 0 sees it at step t (row t): H[t][0] + match and the F seed
@@ -260,14 +248,12 @@ struct FillLane {
      * MASKED = false: the caller knows that every lane of the warp works at this step (quiet4());
      * MASKED = true: the lane checks for itself, and sits out or captures its high half.
      */
-    template <bool MASKED = true, bool FAST = false>
+    template <bool MASKED = true>
     SW_HD void step(const CellConsts &c, u32 t, u32 h_sh, u32 f_sh)
     {
         const int i = (int)t - (int)lane;
-        const u32 ra = FAST ? 0u : (T::PAIRS == 2 ? (rq0[0] | (rq1[0] << 16)) : rq0[0]);
-        const u32 ta = tq0, tb = tq1;
+        const u32 ra = T::PAIRS == 2 ? (rq0[0] | (rq1[0] << 16)) : rq0[0];
         fetch_ref(t + MGLSW_REF_AHEAD);
-        if (FAST) { tq0 = lut[rq0[0]]; if (T::PAIRS == 2) tq1 = lut[rq1[0]]; }      /* tables of step t + 1 */
 
         u32 h_in = h_sh, f_in = f_sh;
         if (STRIPS) {
@@ -292,8 +278,7 @@ struct FillLane {
 #pragma unroll
             for (int k = 0; k < K; k++) {
                 const u32 old = hm[k];
-                if (FAST) sw_cell_m<T>(c, byte_perm_sw(ta, tb, bq[k]), diag, e[k], f, hm[k]);
-                else sw_cell<T>(c, ra, bq[k], diag, e[k], f, hm[k]);
+                sw_cell<T>(c, ra, bq[k], diag, e[k], f, hm[k]);
                 diag = old;
                 if (k == K - 2) f_km2 = f;
                 if (k == KM - 1) f_mid_ = f;
@@ -370,13 +355,8 @@ struct FillLane {
             if (wlane == 0) {
                 u32 *dst = ckpt_cur + (size_t)(t / MGLSW_RB) * (LS16 * 128u);
                 const u32 src = (u32)__cvta_generic_to_shared(stage);
-#ifndef MGLSW_EXPERIMENT_STORE_DIV          /* developer experiment: 0 = no store, n = store 1/n of the region (results are then wrong) */
                 asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;\n\tcp.async.bulk.commit_group;"
                              :: "l"(dst), "r"(src), "n"(LS16 * 512) : "memory");
-#elif MGLSW_EXPERIMENT_STORE_DIV > 0
-                asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;\n\tcp.async.bulk.commit_group;"
-                             :: "l"(dst), "r"(src), "n"((LS16 * 512 / MGLSW_EXPERIMENT_STORE_DIV) & ~15) : "memory");
-#endif
             }
 #endif
         }

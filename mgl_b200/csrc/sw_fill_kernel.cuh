@@ -11,36 +11,6 @@
 
 namespace mglsw {
 
-/* the warp's loop over strips and steps; FAST = every sequence byte of the warp's units is A/C/G/T (sw_cell.h) */
-template <bool FAST, int G, class L_t>
-__device__ __forceinline__ void fill_warp(L_t &L, const CellConsts &c, u32 steps, u32 nstrips)
-{
-    for (u32 s = 0; s < nstrips; s++) {
-        L.template strip_begin<FAST>(c, s);
-        for (u32 g = 0; g < steps / 4; g++) {           /* steps is a multiple of MGLSW_RB = 8 */
-            const u32 t0 = g * 4u;
-            if (!__all_sync(0xffffffffu, L.quiet4(t0))) {
-                /* some lane has not reached its row 1 yet, is past its last row, or captures a high half in these four steps */
-#pragma unroll 1
-                for (u32 s4 = 0; s4 < 4; s4++) {
-                    const u32 h = __shfl_up_sync(0xffffffffu, L.h_out, 1, G);
-                    const u32 f = __shfl_up_sync(0xffffffffu, L.f_out, 1, G);
-                    L.template step<true, FAST>(c, t0 + s4, h, f);
-                }
-            } else {
-#pragma unroll
-                for (u32 s4 = 0; s4 < 4; s4++) {
-                    const u32 h = __shfl_up_sync(0xffffffffu, L.h_out, 1, G);
-                    const u32 f = __shfl_up_sync(0xffffffffu, L.f_out, 1, G);
-                    L.template step<false, FAST>(c, t0 + s4, h, f);
-                }
-            }
-        }
-        L.strip_end();
-        __syncwarp();                            /* carry column of strip s is read by lane 0 in strip s + 1 */
-    }
-}
-
 template <class T, int G, int K>
 #ifndef MGLSW_FILL_MINB
 #define MGLSW_FILL_MINB 3
@@ -48,11 +18,6 @@ template <class T, int G, int K>
 __global__ void __launch_bounds__(MGLSW_FILL_THREADS, MGLSW_FILL_MINB)
 sw_fill_kernel(const __grid_constant__ FillArgs a, const u32 first_unit)
 {
-    /* byte -> mismatch table of the ACGT fast path */
-    __shared__ u32 s_lut[256];
-    for (u32 b = threadIdx.x; b < 256u; b += MGLSW_FILL_THREADS) s_lut[b] = base_table(b);
-    __syncthreads();
-
     const u32 warp = blockIdx.x * (MGLSW_FILL_THREADS / 32) + (threadIdx.x >> 5);
     if (warp >= a.n_warps) return;
     const u32 wl = threadIdx.x & 31u;
@@ -65,12 +30,32 @@ sw_fill_kernel(const __grid_constant__ FillArgs a, const u32 first_unit)
     FillLane<T, G, K> L;
     L.setup(a, u, wl, ui);
     L.stage = reinterpret_cast<u32 *>(s_stage[threadIdx.x >> 5]);
-    L.lut = s_lut;
     const u32 steps = u.rb_count * MGLSW_RB;     /* same for every lane of the warp */
     const u32 nstrips = u.nstrips;
-    const bool fast = a.acgt != nullptr && __all_sync(0xffffffffu, a.acgt[ui] != 0);
-    if (fast) fill_warp<true, G>(L, a.c, steps, nstrips);
-    else      fill_warp<false, G>(L, a.c, steps, nstrips);
+    for (u32 s = 0; s < nstrips; s++) {
+        L.strip_begin(a.c, s);
+        for (u32 g = 0; g < steps / 4; g++) {           /* steps is a multiple of MGLSW_RB = 8 */
+            const u32 t0 = g * 4u;
+            if (!__all_sync(0xffffffffu, L.quiet4(t0))) {
+                /* some lane has not reached its row 1 yet, is past its last row, or captures a high half in these four steps */
+#pragma unroll 1
+                for (u32 s4 = 0; s4 < 4; s4++) {
+                    const u32 h = __shfl_up_sync(0xffffffffu, L.h_out, 1, G);
+                    const u32 f = __shfl_up_sync(0xffffffffu, L.f_out, 1, G);
+                    L.template step<true>(a.c, t0 + s4, h, f);
+                }
+            } else {
+#pragma unroll
+                for (u32 s4 = 0; s4 < 4; s4++) {
+                    const u32 h = __shfl_up_sync(0xffffffffu, L.h_out, 1, G);
+                    const u32 f = __shfl_up_sync(0xffffffffu, L.f_out, 1, G);
+                    L.template step<false>(a.c, t0 + s4, h, f);
+                }
+            }
+        }
+        L.strip_end();
+        __syncwarp();                            /* carry column of strip s is read by lane 0 in strip s + 1 */
+    }
     /* the last region's bulk store still reads this block's shared memory */
     if (wl == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     __syncwarp();

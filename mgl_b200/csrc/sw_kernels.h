@@ -13,9 +13,6 @@ namespace mglsw {
 /* fill: fails with cudaErrorInvalidValue when no kernel was built for (kind, G, K) */
 cudaError_t launch_fill_any(int kind, int G, int K, const FillArgs &a, u32 first_unit, cudaStream_t stream);
 
-/* acgt[u] = 1 iff every ref and alt byte of unit u (both halves) is A, C, G or T: admits the unit to the fill's fast path */
-cudaError_t launch_classify(const uint8_t *arena, const UnitDesc *units, u32 n_units, uint8_t *acgt, cudaStream_t stream);
-
 struct TraceArgs {
     const UnitDesc *units;
     const u64 *ops_end;       /* per pair: end of its scratch region (words)    */

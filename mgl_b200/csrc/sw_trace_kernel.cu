@@ -32,34 +32,6 @@ __global__ void __launch_bounds__(128, 4) sw_traceback_kernel(const __grid_const
     a.n_ops[p] = r.n_ops;
 }
 
-/*
- * One warp per unit reads the unit's sequences once (32 consecutive bytes per load) and votes.
- * ~0.6 KB per pair: two orders of magnitude below the fill's own traffic.
- */
-__global__ void __launch_bounds__(256) sw_classify_kernel(const uint8_t *__restrict__ arena, const UnitDesc *__restrict__ units,
-                                                          u32 n_units, uint8_t *__restrict__ acgt)
-{
-    const u32 w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
-    if (w >= n_units) return;
-    const UnitDesc &u = units[w];
-    bool ok = true;
-    const int halves = u.pair[1] != NO_PAIR ? 2 : 1;
-    for (int h = 0; h < halves; h++) {
-        const uint8_t *r = arena + u.ref_off[h], *q = arena + u.alt_off[h];
-        for (u32 k = lane; k < u.tl[h]; k += 32u) ok = ok && is_acgt(__ldg(r + k));
-        for (u32 k = lane; k < u.ql; k += 32u) ok = ok && is_acgt(__ldg(q + k));
-    }
-    ok = __all_sync(0xffffffffu, ok);
-    if (lane == 0) acgt[w] = ok ? 1 : 0;
-}
-
-cudaError_t launch_classify(const uint8_t *arena, const UnitDesc *units, u32 n_units, uint8_t *acgt, cudaStream_t stream)
-{
-    if (n_units == 0) return cudaSuccess;
-    sw_classify_kernel<<<(n_units * 32u + 255u) / 256u, 256, 0, stream>>>(arena, units, n_units, acgt);
-    return cudaGetLastError();
-}
-
 cudaError_t launch_traceback(const TraceArgs &a, cudaStream_t stream)
 {
     if (a.n_units == 0) return cudaSuccess;

@@ -24,34 +24,17 @@ using namespace mglsw;
 
 namespace {
 
-u32 g_lut[256];
-
-template <class T, int G, int K, bool FAST>
-void emu_warp(const FillArgs &a, const Launch &L, u32 w);
-
 template <class T, int G, int K>
 void emu_launch(const FillArgs &a, const Launch &L)
 {
     const u32 upw = 32 / G;
-    for (u32 w = 0; w < L.n_warps; w++) {
-        /* the kernel's warp vote: the byte-permute cell only if every unit of the warp is all-ACGT */
-        bool fast = a.acgt != nullptr;
-        for (u32 g = 0; g < upw && fast; g++) fast = a.acgt[L.first_unit + w * upw + g] != 0;
-        if (fast) emu_warp<T, G, K, true>(a, L, w); else emu_warp<T, G, K, false>(a, L, w);
-    }
-}
-
-template <class T, int G, int K, bool FAST>
-void emu_warp(const FillArgs &a, const Launch &L, u32 w)
-{
-    const u32 upw = 32 / G;
     std::vector<FillLane<T, G, K>> lanes(32);
-    {
+    for (u32 w = 0; w < L.n_warps; w++) {
         const UnitDesc *wu = a.units + L.first_unit + (size_t)w * upw;
-        for (u32 l = 0; l < 32; l++) { lanes[l].setup(a, wu[l / G], l, L.first_unit + w * upw + l / G); lanes[l].lut = g_lut; }
+        for (u32 l = 0; l < 32; l++) lanes[l].setup(a, wu[l / G], l, L.first_unit + w * upw + l / G);
         const u32 steps = wu[0].rb_count * MGLSW_RB;
         for (u32 s = 0; s < wu[0].nstrips; s++) {
-            for (u32 l = 0; l < 32; l++) lanes[l].template strip_begin<FAST>(a.c, s);
+            for (u32 l = 0; l < 32; l++) lanes[l].strip_begin(a.c, s);
             for (u32 t = 0; t < steps; t++) {
                 /* the kernel's choice between the unmasked and the masked step, per group of four steps (sw_fill_kernel.cuh) */
                 bool quiet = true;
@@ -60,8 +43,8 @@ void emu_warp(const FillArgs &a, const Launch &L, u32 w)
                 for (u32 l = 0; l < 32; l++) { hs[l] = lanes[l].h_out; fs[l] = lanes[l].f_out; }
                 for (u32 l = 0; l < 32; l++) {
                     const u32 src = (l % G) ? l - 1 : l;      /* __shfl_up_sync(.., 1, G) */
-                    if (quiet) lanes[l].template step<false, FAST>(a.c, t, hs[src], fs[src]);
-                    else lanes[l].template step<true, FAST>(a.c, t, hs[src], fs[src]);
+                    if (quiet) lanes[l].template step<false>(a.c, t, hs[src], fs[src]);
+                    else lanes[l].template step<true>(a.c, t, hs[src], fs[src]);
                 }
             }
             for (u32 l = 0; l < 32; l++) lanes[l].strip_end();
@@ -103,7 +86,7 @@ int emu_align_batch(int n, const uint8_t *arena, const uint64_t *ref_off, const 
         pairs[p].strategy = strategies[p];
     }
     ChunkPlan plan;
-    const PlanStatus ps = plan_chunk(pairs.data(), (u32)n, s, (allow_s16 & 1) != 0, plan);
+    const PlanStatus ps = plan_chunk(pairs.data(), (u32)n, s, allow_s16 != 0, plan);
     if (ps != PLAN_OK) return -(int)ps;
 
     std::vector<u32> ckpt(plan.ckpt_words + 4, 0xdeadbeefu);
@@ -122,24 +105,11 @@ int emu_align_batch(int n, const uint8_t *arena, const uint64_t *ref_off, const 
     std::vector<u32> lastrow(plan.lastrow_words + 1, 0);
     std::vector<u32> scratch(plan.scratch_words + 1, 0);
 
-    /* what sw_classify_kernel computes on the device; bit 1 of allow_s16 switches the fast path off */
-    for (u32 b = 0; b < 256; b++) g_lut[b] = base_table(b);
-    std::vector<uint8_t> acgt(plan.units.size() + 1, 0);
-    for (size_t k = 0; k < plan.units.size(); k++) {
-        const UnitDesc &u = plan.units[k];
-        bool ok = true;
-        for (int h = 0; h < (u.pair[1] != NO_PAIR ? 2 : 1); h++) {
-            for (u32 x = 0; x < u.tl[h]; x++) ok = ok && is_acgt(arena[u.ref_off[h] + x]);
-            for (u32 x = 0; x < u.ql; x++) ok = ok && is_acgt(arena[u.alt_off[h] + x]);
-        }
-        acgt[k] = ok ? 1 : 0;
-    }
     u32 n16 = 0, n32 = 0;
     for (const Launch &L : plan.launches) {
         FillArgs a;
         a.arena = arena; a.units = plan.units.data(); a.ckpt = ckpt.data();
         a.carry = carry.data(); a.lastrow = lastrow.data(); a.colbest = colbest.data(); a.n_warps = L.n_warps;
-        a.acgt = (allow_s16 & 2) ? nullptr : acgt.data();
         a.c = L.kind == KIND_S16X2 ? make_consts<S16x2>(s, plan.s16_bias) : make_consts<S32>(s, 0);
         if (!emu_dispatch(a, L)) { std::fprintf(stderr, "emu: no kernel for kind %d G %d K %d\n", L.kind, L.G, L.K); return -10; }
     }

@@ -48,7 +48,7 @@ def pack_batch(pairs):
     return arena, offs[0::2].copy(), ref_len, offs[1::2].copy(), alt_len
 
 
-def emu_align(pairs, params, strategies, allow_s16=True, allow_acgt=True):
+def emu_align(pairs, params, strategies, allow_s16=True):
     """-> list of (cigar text, offset), plus stats dict"""
     lib = _load()
     n = len(pairs)
@@ -62,7 +62,7 @@ def emu_align(pairs, params, strategies, allow_s16=True, allow_acgt=True):
     ops = np.zeros(n * stride, dtype=np.uint32)
     stats = np.zeros(4, dtype=np.uint32)
     rc = lib.emu_align_batch(n, arena.ctypes.data, ro.ctypes.data, rl.ctypes.data, ao.ctypes.data, al.ctypes.data,
-                             st.ctypes.data, params[0], params[1], params[2], params[3], (1 if allow_s16 else 0) | (0 if allow_acgt else 2),
+                             st.ctypes.data, params[0], params[1], params[2], params[3], 1 if allow_s16 else 0,
                              offsets.ctypes.data, n_ops.ctypes.data, ops.ctypes.data, stride, stats.ctypes.data)
     if rc != 0:
         raise RuntimeError(f"emu_align_batch rc={rc}")

@@ -35,11 +35,9 @@ def _check(sw, oracle, pairs, params, strategies, **opts):
     return res
 
 
-@pytest.mark.parametrize("allow_s16,allow_acgt", [(1, 1), (0, 1), (1, 0), (0, 0)])
-def test_golden_vectors(sw, golden, allow_s16, allow_acgt):
-    """both arithmetics x both cells (byte-permute for all-ACGT units, byte-compare otherwise / when switched off)"""
+@pytest.mark.parametrize("allow_s16", [1, 0])
+def test_golden_vectors(sw, golden, allow_s16):
     sw.set_option("allow_s16", allow_s16)
-    sw.set_option("allow_acgt", allow_acgt)
     by = defaultdict(list)
     for c in golden["cases"]:
         by[tuple(c["params"])].append(c)
@@ -56,7 +54,6 @@ def test_golden_vectors(sw, golden, allow_s16, allow_acgt):
                 total += len(cs)
     finally:
         sw.set_option("allow_s16", 1)
-        sw.set_option("allow_acgt", 1)
     assert total > 10000
 
 

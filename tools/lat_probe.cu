@@ -11,6 +11,16 @@
 
 using namespace mglsw;
 
+/* helpers of the byte-permute ("ACGT") cell variant that was measured and dropped */
+__host__ __device__ inline bool is_acgt(unsigned b) { return b == 0x41u || b == 0x43u || b == 0x47u || b == 0x54u; }
+__host__ __device__ inline unsigned base_table(unsigned b) { return is_acgt(b) ? (0x01010101u ^ (1u << (8u * ((b >> 1) & 3u)))) : 0x01010101u; }
+__device__ inline unsigned byte_perm_sw(unsigned x, unsigned y, unsigned s)
+{
+    unsigned r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(x), "r"(y), "r"(s));
+    return r;
+}
+
 template <int W>
 __device__ __forceinline__ unsigned chain_op(unsigned x, unsigned a, unsigned b)
 {
