@@ -30,7 +30,9 @@ sys.path.insert(0, ROOT)
 METRIC = "GCUPS, Smith-Waterman affine-gap fill + traceback + CIGAR (1 CUP = one DP cell)"
 UNIT = "GCUPS"
 ALGO_OPS_PER_CELL = 10          # SURVEY.md 8(d), counted from sw.cpp:55-93
-TRACE_BYTES_PER_CELL = 0.5      # 4-bit trace
+# DRAM bytes per DP cell of the fill kernel from the ncu --set full capture of the same command
+# (profiles/r01m_fill_trace_full_config2.txt: K = 20 launch, dram read + write 3.756 GB for 3.365 Gcells)
+NCU_FILL_DRAM_BYTES_PER_CELL = {2: 1.116}
 
 
 def parse():
@@ -166,7 +168,7 @@ def run_reference(args, rank, world):
     n = args.pairs or DEFAULT_PAIRS[args.config]
     d = synth.generate(args.config, n)
     if not O.have_ref():
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libmgl_sw_ref.so was not built (no reference sources on this box)"}))
+        emit(({"impl": "reference", "unavailable": "oracle/_ref/libmgl_sw_ref.so was not built (no reference sources on this box)"}))
         return
     threads = O.ref_max_threads()
     probe = min(n, max(64, 40 * threads))
@@ -182,7 +184,7 @@ def run_reference(args, rank, world):
         tot_cells += c
     val = tot_cells / tot_s / 1e9
     sample = f"each step = first {n_sample} pairs of the workload ({tot_cells / args.steps / 1e9:.2f} Gcells)"
-    print(json.dumps({
+    emit(({
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": tot_s / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "int32", "data": "synthetic",
@@ -193,8 +195,26 @@ def run_reference(args, rank, world):
     }))
 
 
+_REAL_STDOUT = None
+
+
+def protect_stdout():
+    """Libraries (NCCL's version banner, torchrun) write to fd 1; the contract is ONE JSON line there.
+    Everything else goes to stderr; emit() writes the line to the real stdout."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
+def emit(obj):
+    _REAL_STDOUT.write(json.dumps(obj) + "\n")
+    _REAL_STDOUT.flush()
+
+
 def main():
     args = parse()
+    protect_stdout()
     rank, world, local, dist = dist_setup(args.gpus)
     if args.impl == "reference":
         run_reference(args, rank, world)
@@ -246,8 +266,8 @@ def main():
         launches += st["fill_launches"] + st["other_launches"]
     barrier(dist, local)
     wall_ms = (time.perf_counter() - t0) * 1e3
-    clocks = sampler.stop() if rank == 0 else None
     cells_step = st["cells"]
+    ckpt_bytes_step = st["trace_bytes"]                 # checkpoint bytes the fill launches of one step write (planner's count)
     sw.set_option("overlap", 0)
     fill_ms = trace_ms = post_ms = serial_ms = 0.0
     fill_launches = 0
@@ -277,6 +297,7 @@ def main():
         e2e_ms = (time.perf_counter() - t0) * 1e3
         barrier(dist, local)
 
+    clocks = sampler.stop() if rank == 0 else None     # sampled over all three timed passes (value, per-kernel, e2e)
     (dev_ms, fill_ms, wall_ms, e2e_ms), (cells_all, pairs_all) = reduce_max_sum(
         dist, local, [dev_ms, fill_ms, wall_ms, e2e_ms], [float(cells_step), float(n)])
 
@@ -305,11 +326,18 @@ def main():
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "int", "achieved": fill_cups * ALGO_OPS_PER_CELL / 1e9, "peak": p_int, "unit": "Gop/s",
-                         "frac": (fill_cups * ALGO_OPS_PER_CELL / 1e9 / p_int) if p_int else None, "traffic": None,
-                         "note": "dominant kernel = sw_fill_kernel; algorithmic 10 int ops/cell; peak = max(iadd3, imnmx) measured live by int_peak.cu"},
-            "roofline_hbm": {"bound": "hbm", "achieved": fill_cups * TRACE_BYTES_PER_CELL / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                             "frac": fill_cups * TRACE_BYTES_PER_CELL / 1e9 / hbm_peak, "traffic": None,
-                             "note": "4-bit trace writes of the fill kernel; peak = MEASURED_PEAKS.json hbm_gbs" + ("" if measured else " (fallback 6650)")},
+                         "frac": (fill_cups * ALGO_OPS_PER_CELL / 1e9 / p_int) if p_int else None,
+                         "traffic": (NCU_FILL_DRAM_BYTES_PER_CELL[args.config] * cells_step / max(1, fill_launches // K))
+                         if args.config in NCU_FILL_DRAM_BYTES_PER_CELL else None,
+                         "note": "dominant kernel = sw_fill_kernel (all its launches of a step, timed with CUDA events on their stream in the "
+                                 "one-chunk-at-a-time pass); algorithmic 10 int ops/cell (SURVEY.md 8d) x cells; peak = max(iadd3, imnmx) measured "
+                                 "live by int_peak.cu (not in MEASURED_PEAKS.json); u16x2 arithmetic does two cells per lane-op, which is how frac "
+                                 "can exceed 1; traffic = ncu dram bytes per cell x cells per average fill launch"},
+            "roofline_hbm": {"bound": "hbm", "achieved": ckpt_bytes_step * K / (fill_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                             "frac": ckpt_bytes_step * K / (fill_ms * 1e-3) / 1e9 / hbm_peak,
+                             "algorithmic_bytes_per_cell": ckpt_bytes_step / cells_step,
+                             "note": "checkpoint writes of the fill kernel (the only O(cells) HBM traffic on the path); peak = MEASURED_PEAKS.json hbm_gbs"
+                                     + ("" if measured else " (fallback 6650)")},
             "int_peaks_gops": peaks,
         }
         if not args.no_e2e:
@@ -320,7 +348,7 @@ def main():
             cb = cpu_baseline(d)
             if cb:
                 line["cpu_baseline"] = cb
-        print(json.dumps(line))
+        emit((line))
     if dist is not None:
         dist.destroy_process_group()
 
