@@ -27,6 +27,9 @@
 #include "sw_config.h"
 
 #define MGLSW_KH ((MGLSW_KMAX + 1) / 2)      /* columns of a block: at most half a lane's registers */
+/* 64-bit words of one pair's replay buffer: MGLSW_RB rows of 4-bit records, then the H values on the block's left
+   boundary column (MGLSW_RB + 1 rows) and top boundary row (MGLSW_KH columns) as 32-bit integers */
+#define MGLSW_TRACE_BUF (MGLSW_RB + (MGLSW_RB + 1 + MGLSW_KH + 1) / 2)
 
 namespace mglsw {
 
@@ -93,6 +96,65 @@ struct Replay {
     SW_HD int bnd(int x) const { return boundary_score(x, indel, go, ge); }
     SW_HD int hval(u32 w) const { return T::half(w, (int)half) - bias - match; }   /* stored H + match + bias -> H */
     SW_HD int gval(u32 w) const { return T::half(w, (int)half) - bias; }           /* stored E / F + bias      */
+
+    /* H on the boundary of the block built last: entry r = H[ia - 1 + r][ja - 1], entry MGLSW_RB + 1 + kk = H[ia - 1][ja + kk] */
+    SW_HD void put_h(u32 idx, int v) { reinterpret_cast<u32 *>(nib + (size_t)(MGLSW_RB + idx / 2u) * nstride)[idx & 1u] = (u32)v; }
+    SW_HD int get_h(u32 idx) const { return (int)reinterpret_cast<const u32 *>(nib + (size_t)(MGLSW_RB + idx / 2u) * nstride)[idx & 1u]; }
+    /* after the walk left the block through its top or left edge: H of the cell it stands on, if that is a boundary cell */
+    SW_HD bool boundary_h(int i, int j, int &h) const
+    {
+        if (ib < ia) return false;
+        if (j == ja - 1 && i >= ia - 1 && i <= ib) { h = get_h((u32)(i - (ia - 1))); return true; }
+        if (i == ia - 1 && j >= ja && j <= jb) { h = get_h(MGLSW_RB + 1u + (u32)(j - ja)); return true; }
+        return false;
+    }
+
+    /*
+     * Diagonal hop.  H[i][j] >= H[i-1][j-1] + s(i, j) holds at every cell (H is the maximum of three
+     * candidates, sw.cpp:55-71), with equality exactly when the reference's traceback takes the
+     * diagonal there (its test d >= E && d >= F, sw.cpp:60, is d == H).  Summed along L diagonal
+     * cells: H[I][J] - H[I-L][J-L] >= sum of the L substitution scores, with equality iff EVERY one
+     * of the L cells is a diagonal step.  So when H is known at (I, J) and at the next checkpointed
+     * cell up the diagonal -- the column left of J's block (every row of it is stored by the fill), or
+     * row 0 / column 0 -- one 8-byte load and L byte compares decide L traceback steps, and no block
+     * is recomputed.  Returns L (> 0) and H[I-L][J-L] on success, 0 if some cell on the way is a gap
+     * or a tie that goes another way: the caller then replays the block as usual.
+     */
+    SW_HD int hop(int I, int J, int hcur, int &hnext) const
+    {
+        u32 slot, reg;
+        {
+            const u32 col = (u32)J - 1, wide = cr * (cb + 1);
+            if (col < wide) { slot = col / (cb + 1); reg = col - slot * (cb + 1); }
+            else { const u32 c2 = col - wide; slot = cr + c2 / cb; reg = c2 - (slot - cr) * cb; }
+        }
+        const u32 strip = slot / G, lane = slot - strip * G;
+        const bool sub = reg >= KM;
+        const u32 k_lo = sub ? KM : 0u;
+        const int jc = (int)(slot < cr ? slot * (cb + 1) : cr * (cb + 1) + (slot - cr) * cb) + (int)k_lo;   /* = ja - 1 of J's block */
+        int L = J - jc;
+        if (L > I) L = I;
+        const int it = I - L, jt = J - L;
+        int ht;
+        if (it == 0) ht = bnd(jt);                                  /* row 0, sw.cpp:29-35 */
+        else if (jt == 0) ht = bnd(it);                             /* column 0, sw.cpp:47-49 */
+        else {
+            u32 cs = strip, cl = lane, word = 0;
+            if (!sub) { word = 2; if (lane > 0) cl = lane - 1; else { cl = G - 1; cs = strip - 1; } }
+            const u32 tt = (u32)it + cl;                            /* the step at which lane cl worked on row it */
+            const u32 *lp = base + (size_t)cs * rbc * RW + (size_t)cl * LSW + word;
+            ht = hval(load_w2(lp + (size_t)(tt / MGLSW_RB) * RW + (tt % MGLSW_RB) * 4u).x);
+        }
+        int sum = 0;
+#pragma unroll
+        for (int t = 0; t < MGLSW_KH; t++) {
+            const int tc = t < L ? t : L - 1;                       /* stay inside the sequences; extra terms are not added */
+            const u32 rb_ = SW_LDG(ref + (I - 1 - tc)), ab_ = SW_LDG(alt + (J - 1 - tc));
+            if (t < L) sum += rb_ == ab_ ? match : mismatch;
+        }
+        hnext = ht;
+        return hcur - ht == sum ? L : 0;
+    }
 
     SW_HD void build(int I, int J)
     {
@@ -176,6 +238,12 @@ struct Replay {
             if (ia_ == 1) { const int b = bnd(ja_ + kk); Hp[kk] = b; E[kk] = b - go; }  /* rows 0 / 1 seeds: sw.cpp:10-18,29-35 */
         }
 
+        /* keep H of the block's left boundary column and top boundary row: the walk needs it when it leaves the block */
+#pragma unroll
+        for (int r = 0; r <= (int)MGLSW_RB; r++) put_h((u32)r, hlv[r]);
+#pragma unroll
+        for (int kk = 0; kk < MGLSW_KH; kk++) put_h(MGLSW_RB + 1u + (u32)kk, Hp[kk]);
+
         /* unrolled over the (at most MGLSW_RB) rows so that the boundary values stay in registers */
 #pragma unroll
         for (int r = 1; r <= (int)MGLSW_RB; r++) {
@@ -215,6 +283,7 @@ struct PairResult {
     int offset;
     u32 n_ops;
     int score;               /* biased score of the start cell (diagnostic)            */
+    u32 builds, hops;        /* blocks recomputed / diagonal hops taken (diagnostic)   */
 };
 
 /*
@@ -275,7 +344,27 @@ SW_HD PairResult traceback_pair(const UnitDesc &u, u32 half, u32 G, u32 K, const
     u32 state = OP_M, next = OP_M;
     int mode = 0, steplen = 1, cc = 0, r = 0;
     bool done = false;
+    /* H at (I, J), when known: at the start cell (the score that selected it) and on checkpointed cells */
+    int hcur = start_score - c.bias - c.s_match;
+    u32 hops = 0;
+    bool hk = strategy != OS_INDEL;          /* INDEL starts at (tl, ql), whose score was not looked up */
     while (!done) {
+        /*
+         * Phase A: while H is known, try to cross the block with one diagonal hop (Replay::hop).  A
+         * clean stretch of the alignment costs one load and <= 12 byte compares per block; threads of
+         * the warp run ahead independently here and meet again at the one replay site below.
+         */
+        while (hk && !done) {
+            int hn;
+            const int L = rp.hop(I, J, hcur, hn);
+            if (L == 0) break;
+            if (state == OP_M) run += L;
+            else { SW_EMIT(state, run); run = L; state = OP_M; }
+            I -= L; J -= L; hcur = hn; hops++;
+            if (!(I > 0 && J > 0)) done = true;
+        }
+        if (done) break;
+        /* Phase B: recompute the block around the current cell and walk inside it */
         rp.build(mode == 2 ? r : I, mode == 1 ? cc : J);
         for (;;) {
             const int qi = mode == 2 ? r : I, qj = mode == 1 ? cc : J;
@@ -301,6 +390,8 @@ SW_HD PairResult traceback_pair(const UnitDesc &u, u32 half, u32 G, u32 K, const
                 if (!(I > 0 && J > 0)) { done = true; break; }
             }
         }
+        /* left the block between two cells (not inside a gap): H is known again if we stand on its boundary */
+        hk = !done && mode == 0 && rp.boundary_h(I, J, hcur);
     }
 
     PairResult res;
@@ -320,6 +411,7 @@ SW_HD PairResult traceback_pair(const UnitDesc &u, u32 half, u32 G, u32 K, const
 #undef SW_EMIT
     res.n_ops = (u32)(ops_end - p);
     res.score = start_score;
+    res.builds = rp.builds; res.hops = hops;
     return res;
 }
 

@@ -15,7 +15,7 @@ namespace mglsw {
  */
 __global__ void __launch_bounds__(128, 4) sw_traceback_kernel(const __grid_constant__ TraceArgs a)
 {
-    __shared__ u64 s_nib[MGLSW_RB * 128];          /* the replayed block's records, one column per thread */
+    __shared__ u64 s_nib[MGLSW_TRACE_BUF * 128];   /* the replayed block: records and boundary H values, one column per thread */
     const u32 tid = blockIdx.x * blockDim.x + threadIdx.x;
     if (tid >= 2u * a.n_units) return;
     const UnitDesc &u = a.units[tid >> 1];

@@ -71,7 +71,7 @@ extern "C" {
 /*
  * Align a batch through planner + emulated kernels.  ops_out: per pair a
  * region of ops_stride words, elements left to right.  Returns 0, or a
- * negative code.  stats (optional, 4 words): launches, s16 pairs, s32 pairs, units.
+ * negative code.  stats (optional, 6 words): launches, s16 pairs, s32 pairs, units, blocks replayed, diagonal hops.
  */
 int emu_align_batch(int n, const uint8_t *arena, const uint64_t *ref_off, const uint32_t *ref_len,
                     const uint64_t *alt_off, const uint32_t *alt_len, const int32_t *strategies,
@@ -106,6 +106,7 @@ int emu_align_batch(int n, const uint8_t *arena, const uint64_t *ref_off, const 
     std::vector<u32> scratch(plan.scratch_words + 1, 0);
 
     u32 n16 = 0, n32 = 0;
+    if (stats) stats[4] = stats[5] = 0;
     for (const Launch &L : plan.launches) {
         FillArgs a;
         a.arena = arena; a.units = plan.units.data(); a.ckpt = ckpt.data();
@@ -118,10 +119,11 @@ int emu_align_batch(int n, const uint8_t *arena, const uint64_t *ref_off, const 
         const u32 half = plan.pair_unit[p] & 1u;
         const u32 G = (u.flags & UNIT_G32) ? MGLSW_G_LONG : MGLSW_G_SHORT;
         PairResult r;
-        u64 nibbuf[MGLSW_RB];
+        u64 nibbuf[MGLSW_TRACE_BUF];
         u32 *end = scratch.data() + plan.ops_end[p];
         if (u.flags & UNIT_S32) { r = traceback_pair<S32>(u, half, G, u.regs, ckpt.data(), arena, make_consts<S32>(s, 0), colbest.data() + (size_t)(plan.pair_unit[p] >> 1) * 4, lastrow.data(), strategies[p], end, nibbuf, 1u); n32++; }
         else { r = traceback_pair<S16x2>(u, half, G, u.regs, ckpt.data(), arena, make_consts<S16x2>(s, plan.s16_bias), colbest.data() + (size_t)(plan.pair_unit[p] >> 1) * 4, lastrow.data(), strategies[p], end, nibbuf, 1u); n16++; }
+        if (stats) { stats[4] += r.builds; stats[5] += r.hops; }
         offsets[p] = r.offset;
         n_ops[p] = r.n_ops;
         if ((int)r.n_ops > ops_stride) return -11;

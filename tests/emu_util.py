@@ -60,7 +60,7 @@ def emu_align(pairs, params, strategies, allow_s16=True):
     offsets = np.zeros(n, dtype=np.int32)
     n_ops = np.zeros(n, dtype=np.uint32)
     ops = np.zeros(n * stride, dtype=np.uint32)
-    stats = np.zeros(4, dtype=np.uint32)
+    stats = np.zeros(6, dtype=np.uint32)
     rc = lib.emu_align_batch(n, arena.ctypes.data, ro.ctypes.data, rl.ctypes.data, ao.ctypes.data, al.ctypes.data,
                              st.ctypes.data, params[0], params[1], params[2], params[3], 1 if allow_s16 else 0,
                              offsets.ctypes.data, n_ops.ctypes.data, ops.ctypes.data, stride, stats.ctypes.data)
@@ -71,4 +71,4 @@ def emu_align(pairs, params, strategies, allow_s16=True):
     for p in range(n):
         text = "".join(f"{int(o) >> 4}{OPS[int(o) & 15]}" for o in ops[p, : n_ops[p]])
         out.append((text, int(offsets[p])))
-    return out, dict(launches=int(stats[0]), s16=int(stats[1]), s32=int(stats[2]), units=int(stats[3]))
+    return out, dict(launches=int(stats[0]), s16=int(stats[1]), s32=int(stats[2]), units=int(stats[3]), builds=int(stats[4]), hops=int(stats[5]))
