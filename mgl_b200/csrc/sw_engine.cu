@@ -119,6 +119,11 @@ int Engine::reserve_arena(const BatchIn &in)
 {
     u32 max_tl = 0;
     for (int64_t p = 0; p < in.n; p++) max_tl = std::max(max_tl, in.ref_len[p]);
+    return reserve_arena(in, max_tl);
+}
+
+int Engine::reserve_arena(const BatchIn &in, u32 max_tl)
+{
     const size_t need = MGLSW_ARENA_FRONT_PAD + in.arena_bytes + arena_tail_pad(max_tl);
     if (need > arena_.cap) {
         cudaError_t e = arena_.reserve(need);
@@ -145,18 +150,22 @@ u64 Engine::budget()
  * How many pairs the chunk starting at `first` takes: at most chunk_pairs, and as many as keep
  * the estimated checkpoints inside the budget.
  */
-int64_t Engine::chunk_take(const BatchIn &in, int64_t first, u64 limit, u32 max_pairs) const
+/* checkpoint bytes of one pair with the planner's geometry (sw_plan.cpp), as if it ran alone in 32-bit arithmetic */
+static inline u64 pair_ckpt_bytes(u32 tl, u32 ql)
+{
+    const u32 G = ql <= (u32)MGLSW_G_SHORT * MGLSW_KMAX ? MGLSW_G_SHORT : MGLSW_G_LONG;
+    const u32 ns = G == MGLSW_G_SHORT ? 1u : ceil_div_u32(ql, (u32)MGLSW_G_LONG * MGLSW_KMAX);
+    const u32 K = regs_per_lane(ql, ns * G);
+    return (u64)ns * row_blocks(tl, G) * lane_stride16(K) * 16u * G;
+}
+
+int64_t Engine::chunk_take(const BatchIn &in, int64_t first, u64 limit, u32 max_pairs, const u32 *est256) const
 {
     const int64_t n = std::min<int64_t>(in.n - first, max_pairs ? max_pairs : chunk_pairs);
     u64 est = 0;
     int64_t take = 0;
     for (; take < n; take++) {
-        const u64 tl = in.ref_len[first + take], ql = in.alt_len[first + take];
-        /* checkpoint bytes with the planner's geometry (sw_plan.cpp), as if the pair ran alone in 32-bit arithmetic */
-        const u32 G = ql <= (u64)MGLSW_G_SHORT * MGLSW_KMAX ? MGLSW_G_SHORT : MGLSW_G_LONG;
-        const u32 ns = G == MGLSW_G_SHORT ? 1u : ceil_div_u32((u32)ql, (u32)MGLSW_G_LONG * MGLSW_KMAX);
-        const u32 K = regs_per_lane((u32)ql, ns * G);
-        const u64 bytes = (u64)ns * row_blocks((u32)tl, G) * lane_stride16(K) * 16u * G;
+        const u64 bytes = est256 ? ((u64)est256[first + take] << 8) : pair_ckpt_bytes(in.ref_len[first + take], in.alt_len[first + take]);
         if (take > 0 && est + bytes > limit) break;
         est += bytes;
     }
@@ -206,7 +215,7 @@ int Engine::plan_range(const BatchIn &in, int64_t first, int64_t take, ChunkDev 
 int Engine::plan_next(const BatchIn &in, int64_t first, ChunkDev &cd)
 {
     std::string err;
-    const int rc = plan_range(in, first, chunk_take(in, first, budget(), 0), cd, err);
+    const int rc = plan_range(in, first, chunk_take(in, first, budget(), 0, nullptr), cd, err);
     return rc == MGL_SW_OK ? rc : fail(rc, err);
 }
 
@@ -349,6 +358,11 @@ struct InFlight { bool busy = false; int64_t first = 0; u32 n = 0; };
 int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
 {
     const auto fn_t0 = std::chrono::steady_clock::now();
+    const bool tl_setup = std::getenv("MGL_SW_TIMELINE") != nullptr;
+    auto setup_mark = [&](const char *what) {
+        if (tl_setup) std::fprintf(stderr, "[mgl_sw] setup: %s at %.2f ms\n", what,
+                                   std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - fn_t0).count());
+    };
     BatchStats bs;
     std::memset(&bs, 0, sizeof bs);
     if (in.n < 0 || (in.n > 0 && (!in.arena || !in.ref_off || !in.alt_off || !in.ref_len || !in.alt_len)))
@@ -361,12 +375,40 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
     out.ops_total = 0;
     out.cigar_start[0] = 0;
     if (in.n == 0) { if (stats) *stats = bs; return MGL_SW_OK; }
-    { const int rc0 = reserve_arena(in); if (rc0 != MGL_SW_OK) return rc0; }
+    /* one parallel pass over the pair table: longest ref, total length, per-pair checkpoint estimate (units of 256 B).
+       Short-lived std::threads, not OpenMP: an OpenMP team keeps spinning after the loop and takes the cores the
+       planner threads need in the next few milliseconds (measured: first chunks planned 3x slower). */
+    u32 max_tl = 0;
+    u64 total_len = 0;
+    est256_.resize((size_t)in.n);
+    {
+        const int T = in.n > 65536 ? (int)std::min<unsigned>(8u, std::max(1u, std::thread::hardware_concurrency() / 2)) : 1;
+        std::vector<u32> tmax((size_t)T, 0);
+        std::vector<u64> tsum((size_t)T, 0);
+        auto scan = [&](int t) {
+            const int64_t lo = in.n * t / T, hi = in.n * (t + 1) / T;
+            u32 m = 0; u64 sum = 0;
+            u32 *est = est256_.data();
+            for (int64_t p = lo; p < hi; p++) {
+                const u32 tl = in.ref_len[p], ql = in.alt_len[p];
+                m = std::max(m, tl);
+                sum += (u64)tl + ql;
+                est[p] = (u32)std::min<u64>((pair_ckpt_bytes(tl, ql) + 255u) >> 8, 0xffffffffu);
+            }
+            tmax[(size_t)t] = m; tsum[(size_t)t] = sum;
+        };
+        std::vector<std::thread> th;
+        for (int t = 1; t < T; t++) th.emplace_back(scan, t);
+        scan(0);
+        for (std::thread &x : th) x.join();
+        for (int t = 0; t < T; t++) { max_tl = std::max(max_tl, tmax[(size_t)t]); total_len += tsum[(size_t)t]; }
+    }
+    setup_mark("pair table scanned");
+    { const int rc0 = reserve_arena(in, max_tl); if (rc0 != MGL_SW_OK) return rc0; }
+    setup_mark("arena reserved");
 
     /* arena upload policy: per-chunk byte ranges when the arena is laid out pair after pair,
        one up-front copy when pairs share or scatter their sequences */
-    u64 total_len = 0;
-    for (int64_t p = 0; p < in.n; p++) total_len += (u64)in.ref_len[p] + in.alt_len[p];
     const bool whole = in.arena_bytes > total_len + total_len / 2 + 4096 || total_len > in.arena_bytes + in.arena_bytes / 2;
     if (whole) {
         if ((e = cudaMemcpyAsync((void *)arena_dev(), in.arena, in.arena_bytes, cudaMemcpyHostToDevice, slots_[0].stream)) != cudaSuccess)
@@ -412,20 +454,26 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
      * collected; R = planners + slots + 1 keeps every planner busy without blocking the collector.
      */
     std::vector<std::pair<int64_t, int64_t>> bounds;
+    int nthreads = plan_threads > 0 ? plan_threads : (int)std::min<unsigned>(8u, std::max(1u, std::thread::hardware_concurrency() / 2));
     {
         const u64 limit = budget();
-        /* the first chunks are small (1/8, 1/4, 1/2 of chunk_pairs): the GPU starts after one short plan, not a full one */
+        /*
+         * Ramp: the planners all start at once, so the first round of chunks (one per planner) is a quarter of
+         * chunk_pairs, the second round half: the GPU gets work after a quarter of a full plan and the full-size
+         * chunks are ready before it runs dry.
+         */
         for (int64_t f0 = 0; f0 < in.n;) {
             const size_t k = bounds.size();
-            const u32 cap = k < 3 ? std::max<u32>(chunk_pairs >> (3 - k), std::min<u32>(chunk_pairs, 4096u)) : chunk_pairs;
-            const int64_t t = chunk_take(in, f0, limit, cap);
+            const u32 quarter = std::max<u32>(chunk_pairs >> 2, std::min<u32>(chunk_pairs, 4096u));
+            const u32 cap = k < (size_t)nthreads ? quarter : (k < 2 * (size_t)nthreads ? std::max<u32>(chunk_pairs >> 1, quarter) : chunk_pairs);
+            const int64_t t = chunk_take(in, f0, limit, cap, est256_.data());
             bounds.emplace_back(f0, t);
             f0 += t;
         }
     }
     const int nchunks = (int)bounds.size();
-    int nthreads = plan_threads > 0 ? plan_threads : (int)std::min<unsigned>(8u, std::max(1u, std::thread::hardware_concurrency() / 2));
     nthreads = std::min(nthreads, nchunks);
+    setup_mark("chunk bounds");
     const int R = nthreads + MGLSW_SLOTS + 1;
     while ((int)ring_.size() < R) ring_.push_back(new ChunkDev());
     std::vector<int> ready((size_t)nchunks, 0);          /* 0 pending, 1 planned, 2 failed */
@@ -462,6 +510,7 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         cv.notify_all();
     };
 
+    setup_mark("planners started");
     const bool tl_on = std::getenv("MGL_SW_TIMELINE") != nullptr;     /* host timeline of the chunk pipeline on stderr */
     const auto tl_t0 = std::chrono::steady_clock::now();
     auto tl_ms = [&]() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tl_t0).count(); };

@@ -118,7 +118,7 @@ private:
     int fail(int code, const std::string &msg);
     int cuda_fail(cudaError_t e, const char *what);
     int plan_next(const BatchIn &in, int64_t first, ChunkDev &cd);
-    int64_t chunk_take(const BatchIn &in, int64_t first, u64 limit, u32 max_pairs) const;
+    int64_t chunk_take(const BatchIn &in, int64_t first, u64 limit, u32 max_pairs, const u32 *est256) const;
     int plan_range(const BatchIn &in, int64_t first, int64_t take, ChunkDev &cd, std::string &err) const;
     int upload_chunk(const BatchIn &in, ChunkDev &cd, cudaStream_t st, bool upload_arena, BatchStats &bs);
     int run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed);
@@ -131,6 +131,8 @@ private:
     DevBuf arena_;               /* device copy of the caller's arena, padded on both sides (sw_fill.h) */
     const uint8_t *arena_dev() const { return (const uint8_t *)arena_.p + MGLSW_ARENA_FRONT_PAD; }
     int reserve_arena(const BatchIn &in);
+    int reserve_arena(const BatchIn &in, u32 max_tl);
+    std::vector<u32> est256_;    /* align_batch: per-pair checkpoint estimate, units of 256 B */
     WorkSlot slots_[MGLSW_SLOTS];
     std::vector<ChunkDev *> ring_;           /* align_batch: staging entries the planner threads fill */
     std::vector<ChunkDev *> resident_;

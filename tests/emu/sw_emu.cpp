@@ -124,6 +124,11 @@ int emu_align_batch(int n, const uint8_t *arena, const uint64_t *ref_off, const 
         if (u.flags & UNIT_S32) { r = traceback_pair<S32>(u, half, G, u.regs, ckpt.data(), arena, make_consts<S32>(s, 0), colbest.data() + (size_t)(plan.pair_unit[p] >> 1) * 4, lastrow.data(), strategies[p], end, nibbuf, 1u); n32++; }
         else { r = traceback_pair<S16x2>(u, half, G, u.regs, ckpt.data(), arena, make_consts<S16x2>(s, plan.s16_bias), colbest.data() + (size_t)(plan.pair_unit[p] >> 1) * 4, lastrow.data(), strategies[p], end, nibbuf, 1u); n16++; }
         if (stats) { stats[4] += r.builds; stats[5] += r.hops; }
+        if (const char *dump = std::getenv("EMU_DUMP")) {        /* developer aid: per-pair replay / hop counts in thread order */
+            static FILE *fp = nullptr;
+            if (!fp) fp = std::fopen(dump, "w");
+            if (fp) { std::fprintf(fp, "%u %u %u\n", plan.pair_unit[p], r.builds, r.hops); std::fflush(fp); }
+        }
         offsets[p] = r.offset;
         n_ops[p] = r.n_ops;
         if ((int)r.n_ops > ops_stride) return -11;
