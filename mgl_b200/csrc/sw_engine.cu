@@ -379,29 +379,30 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
        Short-lived std::threads, not OpenMP: an OpenMP team keeps spinning after the loop and takes the cores the
        planner threads need in the next few milliseconds (measured: first chunks planned 3x slower). */
     u32 max_tl = 0;
-    u64 total_len = 0;
+    u64 total_len = 0, total_est256 = 0;
     est256_.resize((size_t)in.n);
     {
         const int T = in.n > 65536 ? (int)std::min<unsigned>(8u, std::max(1u, std::thread::hardware_concurrency() / 2)) : 1;
         std::vector<u32> tmax((size_t)T, 0);
-        std::vector<u64> tsum((size_t)T, 0);
+        std::vector<u64> tsum((size_t)T, 0), tes((size_t)T, 0);
         auto scan = [&](int t) {
             const int64_t lo = in.n * t / T, hi = in.n * (t + 1) / T;
-            u32 m = 0; u64 sum = 0;
+            u32 m = 0; u64 sum = 0, es = 0;
             u32 *est = est256_.data();
             for (int64_t p = lo; p < hi; p++) {
                 const u32 tl = in.ref_len[p], ql = in.alt_len[p];
                 m = std::max(m, tl);
                 sum += (u64)tl + ql;
                 est[p] = (u32)std::min<u64>((pair_ckpt_bytes(tl, ql) + 255u) >> 8, 0xffffffffu);
+                es += est[p];
             }
-            tmax[(size_t)t] = m; tsum[(size_t)t] = sum;
+            tmax[(size_t)t] = m; tsum[(size_t)t] = sum; tes[(size_t)t] = es;
         };
         std::vector<std::thread> th;
         for (int t = 1; t < T; t++) th.emplace_back(scan, t);
         scan(0);
         for (std::thread &x : th) x.join();
-        for (int t = 0; t < T; t++) { max_tl = std::max(max_tl, tmax[(size_t)t]); total_len += tsum[(size_t)t]; }
+        for (int t = 0; t < T; t++) { max_tl = std::max(max_tl, tmax[(size_t)t]); total_len += tsum[(size_t)t]; total_est256 += tes[(size_t)t]; }
     }
     setup_mark("pair table scanned");
     { const int rc0 = reserve_arena(in, max_tl); if (rc0 != MGL_SW_OK) return rc0; }
@@ -458,14 +459,19 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
     {
         const u64 limit = budget();
         /*
-         * Ramp: the planners all start at once, so the first round of chunks (one per planner) is a quarter of
-         * chunk_pairs, the second round half: the GPU gets work after a quarter of a full plan and the full-size
-         * chunks are ready before it runs dry.
+         * Ramp.  A batch of short pairs (a chunk is two or three kernels): the planners all start at once, so the
+         * first round of chunks (one per planner) is a quarter of chunk_pairs, the second round half: the GPU gets
+         * work after a quarter of a full plan and the full-size chunks are ready before it runs dry.  Longer or
+         * mixed pairs spread a chunk over up to 66 kernels, and small chunks would cut those into slivers
+         * (measured: config 3 e2e 1296 -> 1112 GCUPS): only the first three chunks are reduced (1/8, 1/4, 1/2).
          */
+        const bool short_pairs = in.n >= 4 * (int64_t)chunk_pairs && (total_est256 << 8) / (u64)in.n < 98304u;
         for (int64_t f0 = 0; f0 < in.n;) {
             const size_t k = bounds.size();
-            const u32 quarter = std::max<u32>(chunk_pairs >> 2, std::min<u32>(chunk_pairs, 4096u));
-            const u32 cap = k < (size_t)nthreads ? quarter : (k < 2 * (size_t)nthreads ? std::max<u32>(chunk_pairs >> 1, quarter) : chunk_pairs);
+            const u32 floor_ = std::min<u32>(chunk_pairs, 4096u);
+            u32 cap = chunk_pairs;
+            if (short_pairs) cap = k < (size_t)nthreads ? std::max<u32>(chunk_pairs >> 2, floor_) : (k < 2 * (size_t)nthreads ? std::max<u32>(chunk_pairs >> 1, floor_) : chunk_pairs);
+            else if (k < 3) cap = std::max<u32>(chunk_pairs >> (3 - k), floor_);
             const int64_t t = chunk_take(in, f0, limit, cap, est256_.data());
             bounds.emplace_back(f0, t);
             f0 += t;

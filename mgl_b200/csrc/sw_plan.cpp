@@ -2,6 +2,7 @@
 #include "sw_plan.h"
 
 #include <algorithm>
+
 #include <cstring>
 
 #include "sw_cell.h"
@@ -26,30 +27,64 @@ long long diff_bound(const Scores &s)
     return 2 * ((long long)s.match + g) + absll(s.mismatch) + s.go + s.ge;
 }
 
-struct Keyed {
-    u64 key;
-    u32 idx;
-};
-
-/* stable LSD radix sort on the 64-bit key, 16 bits a pass; passes whose digit is constant are skipped */
-void radix_sort(std::vector<Keyed> &v)
+/*
+ * Stable sort of (key, index) by the 64-bit key.  The keys of one chunk differ in few bits (config 2: 9 bits
+ * of ref length, 4 of alt length, 2 of K), so the bits that vary at all are first gathered into a compact key
+ * (order-preserving: the gather keeps bit order), and that is sorted by LSD radix passes of <= 11 bits --
+ * one pass for a batch of short reads instead of three 16-bit passes over 64 Ki buckets.
+ */
+u64 gather_bits(u64 v, u64 mask)                     /* portable: one iteration per mask bit */
 {
-    const size_t n = v.size();
-    if (n < 2) return;
-    std::vector<Keyed> tmp(n);
-    std::vector<u32> hist(65536);
-    Keyed *src = v.data(), *dst = tmp.data();
-    for (int pass = 0; pass < 4; pass++) {
-        const int sh = 16 * pass;
-        std::fill(hist.begin(), hist.end(), 0u);
-        for (size_t k = 0; k < n; k++) hist[(src[k].key >> sh) & 0xffffu]++;
-        if (hist[(src[0].key >> sh) & 0xffffu] == n) continue;
+    u64 r = 0;
+    for (u64 bit = 1; mask; mask &= mask - 1, bit <<= 1)
+        if (v & mask & (0 - mask)) r |= bit;
+    return r;
+}
+
+#if defined(__x86_64__) && defined(__GNUC__)
+__attribute__((target("bmi2"))) void gather_all_bmi2(u64 *key, u32 n, u64 mask)
+{
+    for (u32 k = 0; k < n; k++) key[k] = __builtin_ia32_pext_di(key[k], mask);
+}
+#endif
+
+void gather_all(u64 *key, u32 n, u64 mask)
+{
+#if defined(__x86_64__) && defined(__GNUC__)
+    static const bool have_bmi2 = __builtin_cpu_supports("bmi2");
+    if (have_bmi2) { gather_all_bmi2(key, n, mask); return; }
+#endif
+    for (u32 k = 0; k < n; k++) key[k] = gather_bits(key[k], mask);
+}
+
+/* returns the mask of the key bits that vary; sort_key then holds the sorted keys reduced to those bits */
+u64 sort_by_key(ChunkPlan &w, u32 n)
+{
+    std::vector<u64> &key = w.sort_key;
+    std::vector<u32> &idx = w.sort_idx;
+    if (n < 2) return 0;
+    u64 diff = 0;
+    for (u32 k = 1; k < n; k++) diff |= key[k] ^ key[0];
+    if (diff == 0) return 0;
+    const int bits = __builtin_popcountll(diff);
+    if (bits < 64) gather_all(key.data(), n, diff);
+    const int passes = (bits + 10) / 11, per = (bits + passes - 1) / passes;       /* <= 11 bits per pass */
+    w.sort_tmp.resize(n); w.sort_idx_tmp.resize(n); w.sort_hist.resize((size_t)1 << per);
+    u64 *ks = key.data(), *kd = w.sort_tmp.data();
+    u32 *is = idx.data(), *id = w.sort_idx_tmp.data();
+    const u32 dm = (1u << per) - 1u;
+    for (int pass = 0; pass < passes; pass++) {
+        const int sh = pass * per;
+        u32 *hist = w.sort_hist.data();
+        std::fill(hist, hist + dm + 1, 0u);
+        for (u32 k = 0; k < n; k++) hist[(ks[k] >> sh) & dm]++;
         u32 run = 0;
-        for (u32 &h : hist) { const u32 c = h; h = run; run += c; }
-        for (size_t k = 0; k < n; k++) dst[hist[(src[k].key >> sh) & 0xffffu]++] = src[k];
-        std::swap(src, dst);
+        for (u32 d = 0; d <= dm; d++) { const u32 c = hist[d]; hist[d] = run; run += c; }
+        for (u32 k = 0; k < n; k++) { const u32 at = hist[(ks[k] >> sh) & dm]++; kd[at] = ks[k]; id[at] = is[k]; }
+        std::swap(ks, kd); std::swap(is, id);
     }
-    if (src != v.data()) std::memcpy(v.data(), src, n * sizeof(Keyed));
+    if (is != idx.data()) { std::memcpy(idx.data(), is, n * sizeof(u32)); std::memcpy(key.data(), ks, n * sizeof(u64)); }
+    return diff;
 }
 
 }  // namespace
@@ -79,14 +114,15 @@ bool s16_bounds(const Scores &s, u32 tl, u32 ql, long long &lo, long long &hi)
 
 PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s16, ChunkPlan &out)
 {
-    out = ChunkPlan();
+    out.reset();
     if (check_scores(s) != PLAN_OK) return PLAN_BAD_SCORES;
     out.pair_unit.assign(n, 0);
     out.ops_end.assign(n, 0);
-    out.units.reserve(n / 2 + 64);
+    out.units.reserve(n + 64);
 
     /* pass 1: per-pair arithmetic class, and the shared 16-bit bias */
-    std::vector<unsigned char> cand(n, 0);
+    std::vector<unsigned char> &cand = out.cand;
+    cand.assign(n, 0);
     long long need_bias = 0;
     for (u32 p = 0; p < n; p++) {
         const PairIn &pr = pairs[p];
@@ -104,7 +140,8 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
 
     /* pass 2: sort key = (kind, G, K, nstrips, indel, ql, tl), all descending so heavy work launches first;
        one launch per (kind, G, K): the strip count is a per-warp run-time value, not a kernel */
-    std::vector<Keyed> order(n);
+    out.full_key.resize(n); out.sort_key.resize(n); out.sort_idx.resize(n);
+    u64 *const fkey = out.full_key.data();
     for (u32 p = 0; p < n; p++) {
         const PairIn &pr = pairs[p];
         int kind = KIND_S32;
@@ -126,23 +163,27 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
         key = (key << 1) | indel;
         key = (key << 24) | pr.ql;
         key = (key << 20) | std::min<u32>(pr.tl, (1u << 20) - 1);
-        order[p].key = ~key;            /* ascending sort of ~key == descending key */
-        order[p].idx = p;
+        fkey[p] = ~key;                 /* ascending sort of ~key == descending key */
+        out.sort_key[p] = ~key;
+        out.sort_idx[p] = p;
     }
-    radix_sort(order);
+    const u64 varying = sort_by_key(out, n);
+    const u32 *const order = out.sort_idx.data();     /* pair ids in launch order */
+    /* the sorted keys, reduced to their varying bits: two keys agree on a field iff their reduced keys agree on the
+       field's reduced mask (read in order: no random access to the full keys) */
+    const u64 *const skey = out.sort_key.data();
+    const u64 m_launch = varying == ~0ull ? (0x7full << 57) : gather_bits(0x7full << 57, varying);     /* kind, G, K */
+    const u64 m_pair = varying == ~0ull ? (~0ull << 20) : gather_bits(~0ull << 20, varying);           /* ... + strips, indel, ql */
 
     /* pass 3: units, warps, launches */
-    auto launch_key = [](u64 k) { return (~k) >> 57; };          /* kind, G, K */
-    auto pair_key = [](u64 k) { return (~k) >> 20; };            /* ... + indel + ql     */
     u32 pos = 0;
     while (pos < n) {
-        const u64 lk = launch_key(order[pos].key);
         u32 end = pos;
-        while (end < n && launch_key(order[end].key) == lk) end++;
+        while (end < n && ((skey[end] ^ skey[pos]) & m_launch) == 0) end++;
 
-        const PairIn &first = pairs[order[pos].idx];
+        const PairIn &first = pairs[order[pos]];
         Launch L;
-        const u64 nk = ~order[pos].key;
+        const u64 nk = ~fkey[order[pos]];
         L.kind = ((nk >> 63) & 1) ? KIND_S32 : KIND_S16X2;
         L.G = ((nk >> 62) & 1) ? MGLSW_G_LONG : MGLSW_G_SHORT;
         L.nstrips = L.G == MGLSW_G_SHORT ? 1u : ceil_div_u32(first.ql, (u32)MGLSW_G_LONG * MGLSW_KMAX);   /* of its first unit */
@@ -155,7 +196,7 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
         while (q < end) {
             UnitDesc u;
             std::memset(&u, 0, sizeof u);
-            const u32 p0 = order[q].idx;
+            const u32 p0 = order[q];
             const PairIn &a = pairs[p0];
             u.pair[0] = p0; u.pair[1] = NO_PAIR;
             u.ref_off[0] = u.ref_off[1] = a.ref_off;
@@ -166,8 +207,8 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
             L.cells += (u64)a.tl * a.ql;
             (L.kind == KIND_S32 ? out.pairs_s32 : out.pairs_s16)++;
             q++;
-            if (L.kind == KIND_S16X2 && q < end && pair_key(order[q].key) == pair_key(order[q - 1].key)) {
-                const u32 p1 = order[q].idx;
+            if (L.kind == KIND_S16X2 && q < end && ((skey[q] ^ skey[q - 1]) & m_pair) == 0) {
+                const u32 p1 = order[q];
                 const PairIn &b = pairs[p1];
                 u.pair[1] = p1; u.ref_off[1] = b.ref_off; u.alt_off[1] = b.alt_off; u.tl[1] = b.tl;
                 out.pair_unit[p1] = (u32)out.units.size() * 2 + 1;

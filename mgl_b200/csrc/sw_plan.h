@@ -45,6 +45,16 @@ struct ChunkPlan {
     u64 cells = 0;                  /* sum tl * ql */
     u64 pairs_s16 = 0, pairs_s32 = 0;
     int s16_bias = 0;
+    /* scratch of plan_chunk, kept between calls so that a planner thread does not reallocate per chunk */
+    std::vector<u64> full_key, sort_key, sort_tmp;
+    std::vector<u32> sort_idx, sort_idx_tmp, sort_hist;
+    std::vector<unsigned char> cand;
+    void reset()                     /* empty, capacity kept */
+    {
+        units.clear(); launches.clear(); pair_unit.clear(); ops_end.clear();
+        ckpt_words = carry_entries = lastrow_words = scratch_words = cells = pairs_s16 = pairs_s32 = 0;
+        s16_bias = 0;
+    }
 };
 
 /* limits a score set must respect for either arithmetic (checked once per batch) */
