@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <condition_variable>
 #include <mutex>
 #include <new>
 #include <string>
@@ -183,6 +184,83 @@ int mgl_sw_format_cigar(const uint32_t *ops, int64_t n_ops, char *out, int64_t o
     return (int)pos;
 }
 
+/*
+ * One pair per call is what the reference's JNI offers (...SmithWaterman.cpp:44-71), and a JVM calls it from many
+ * threads at once.  Calls that arrive while a batch is running are therefore COALESCED: the first caller becomes
+ * the leader, takes every request that is pending (its own included), runs them as one mgl_sw_align_batch per
+ * score set, hands the results back and wakes the others.  A lone caller pays no waiting time (no linger window):
+ * batching comes only from the requests that queue up behind the batch in flight.
+ */
+namespace {
+struct OneReq {
+    const uint8_t *ref, *alt;
+    int32_t ref_len, alt_len, match, mismatch, gap_open, gap_extend, strategy;
+    std::vector<uint32_t> ops;
+    int32_t offset = 0;
+    int rc = MGL_SW_OK;
+    bool done = false;
+};
+std::mutex g_one_mu;
+std::condition_variable g_one_cv;
+std::vector<OneReq *> g_one_queue;
+bool g_one_leader = false;
+
+void run_one_group(std::vector<OneReq *> &grp)
+{
+    const size_t n = grp.size();
+    size_t bytes = 0;
+    for (OneReq *r : grp) bytes += (size_t)r->ref_len + (size_t)r->alt_len;
+    std::vector<uint8_t> arena(bytes);
+    std::vector<uint64_t> ro(n), ao(n), cs(n + 1);
+    std::vector<uint32_t> rl(n), al(n);
+    std::vector<int32_t> st(n), off(n);
+    size_t at = 0, cap = 0;
+    for (size_t k = 0; k < n; k++) {
+        OneReq *r = grp[k];
+        ro[k] = at; std::memcpy(arena.data() + at, r->ref, (size_t)r->ref_len); at += (size_t)r->ref_len;
+        ao[k] = at; std::memcpy(arena.data() + at, r->alt, (size_t)r->alt_len); at += (size_t)r->alt_len;
+        rl[k] = (uint32_t)r->ref_len; al[k] = (uint32_t)r->alt_len; st[k] = r->strategy;
+        cap += (size_t)r->ref_len + (size_t)r->alt_len + 4;
+    }
+    std::vector<uint32_t> ops(cap);
+    mgl_sw_batch b;
+    std::memset(&b, 0, sizeof b);
+    b.n = (int64_t)n; b.arena = arena.data(); b.arena_bytes = arena.size();
+    b.ref_off = ro.data(); b.ref_len = rl.data(); b.alt_off = ao.data(); b.alt_len = al.data();
+    b.strategies = st.data(); b.strategy = st[0];
+    b.match = grp[0]->match; b.mismatch = grp[0]->mismatch; b.gap_open = grp[0]->gap_open; b.gap_extend = grp[0]->gap_extend;
+    mgl_sw_result res;
+    res.offsets = off.data(); res.cigar_start = cs.data(); res.ops = ops.data(); res.ops_cap = ops.size(); res.ops_total = 0;
+    const int rc = mgl_sw_align_batch(g_default, &b, &res, nullptr);
+    for (size_t k = 0; k < n; k++) {
+        OneReq *r = grp[k];
+        r->rc = rc;
+        if (rc == MGL_SW_OK) {
+            r->offset = off[k];
+            r->ops.assign(ops.begin() + (ptrdiff_t)cs[k], ops.begin() + (ptrdiff_t)cs[k + 1]);
+        }
+    }
+}
+
+void run_one_batch(std::vector<OneReq *> &batch)
+{
+    /* a batch carries one score set: group the requests by theirs (in practice all calls of a run share it) */
+    std::vector<char> taken(batch.size(), 0);
+    for (size_t i = 0; i < batch.size(); i++) {
+        if (taken[i]) continue;
+        std::vector<OneReq *> grp;
+        for (size_t j = i; j < batch.size(); j++) {
+            OneReq *a = batch[i], *c = batch[j];
+            if (!taken[j] && a->match == c->match && a->mismatch == c->mismatch && a->gap_open == c->gap_open && a->gap_extend == c->gap_extend) {
+                taken[j] = 1;
+                grp.push_back(c);
+            }
+        }
+        run_one_group(grp);
+    }
+}
+}  // namespace
+
 int mgl_sw_align_one(const uint8_t *ref, int32_t ref_len, const uint8_t *alt, int32_t alt_len,
                      int32_t match, int32_t mismatch, int32_t gap_open, int32_t gap_extend,
                      int32_t strategy, char *cigar_out, int32_t cigar_cap, int32_t *cigar_len, int32_t *offset)
@@ -190,27 +268,34 @@ int mgl_sw_align_one(const uint8_t *ref, int32_t ref_len, const uint8_t *alt, in
     if (!ref || !alt || ref_len <= 0 || alt_len <= 0 || !cigar_out || !offset) return MGL_SW_E_INVALID;
     std::call_once(g_default_once, make_default);
     if (g_default_rc != MGL_SW_OK || !g_default) return MGL_SW_E_NO_DEVICE;
-    std::vector<uint8_t> arena((size_t)ref_len + alt_len);
-    std::memcpy(arena.data(), ref, (size_t)ref_len);
-    std::memcpy(arena.data() + ref_len, alt, (size_t)alt_len);
-    const uint64_t ro = 0, ao = (uint64_t)ref_len;
-    const uint32_t rl = (uint32_t)ref_len, al = (uint32_t)alt_len;
-    mgl_sw_batch b;
-    std::memset(&b, 0, sizeof b);
-    b.n = 1; b.arena = arena.data(); b.arena_bytes = arena.size();
-    b.ref_off = &ro; b.ref_len = &rl; b.alt_off = &ao; b.alt_len = &al;
-    b.strategy = strategy; b.match = match; b.mismatch = mismatch; b.gap_open = gap_open; b.gap_extend = gap_extend;
-    std::vector<uint32_t> ops((size_t)ref_len + alt_len + 4);
-    int32_t off = 0;
-    uint64_t cs[2] = {0, 0};
-    mgl_sw_result r;
-    r.offsets = &off; r.cigar_start = cs; r.ops = ops.data(); r.ops_cap = ops.size(); r.ops_total = 0;
-    const int rc = mgl_sw_align_batch(g_default, &b, &r, nullptr);
-    if (rc != MGL_SW_OK) return rc;
-    const int len = mgl_sw_format_cigar(ops.data(), (int64_t)r.ops_total, cigar_out, cigar_cap);
+    OneReq req;
+    req.ref = ref; req.alt = alt; req.ref_len = ref_len; req.alt_len = alt_len;
+    req.match = match; req.mismatch = mismatch; req.gap_open = gap_open; req.gap_extend = gap_extend; req.strategy = strategy;
+    {
+        std::unique_lock<std::mutex> lk(g_one_mu);
+        g_one_queue.push_back(&req);
+        while (!req.done) {
+            if (!g_one_leader) {
+                /* lead: take everything that is pending, run it outside the lock */
+                g_one_leader = true;
+                std::vector<OneReq *> batch;
+                batch.swap(g_one_queue);
+                lk.unlock();
+                run_one_batch(batch);
+                lk.lock();
+                for (OneReq *r : batch) r->done = true;
+                g_one_leader = false;
+                g_one_cv.notify_all();
+            } else {
+                g_one_cv.wait(lk);
+            }
+        }
+    }
+    if (req.rc != MGL_SW_OK) return req.rc;
+    const int len = mgl_sw_format_cigar(req.ops.data(), (int64_t)req.ops.size(), cigar_out, cigar_cap);
     if (len < 0) return MGL_SW_E_OPS_CAPACITY;
     if (cigar_len) *cigar_len = len;
-    *offset = off;
+    *offset = req.offset;
     return MGL_SW_OK;
 }
 

@@ -25,7 +25,7 @@ cudaError_t DevBuf::reserve(size_t bytes)
 {
     if (bytes <= cap) return cudaSuccess;
     release();
-    size_t want = bytes + bytes / 8 + 256;
+    size_t want = bytes + std::min<size_t>(bytes / 8, (size_t)256 << 20) + 256;     /* headroom against regrowth, bounded for the multi-GB checkpoint buffers */
     cudaError_t e = cudaMalloc(&p, want);
     if (e != cudaSuccess) { p = nullptr; cap = 0; return e; }
     cap = want;
@@ -141,7 +141,7 @@ u64 Engine::budget()
     if (budget_auto_) return budget_auto_;
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return 4ull << 30;
-    u64 b = (u64)(free_b * 0.60 / MGLSW_SLOTS);   /* all slots + descriptors stay well inside HBM */
+    u64 b = (u64)(free_b * 0.72 / MGLSW_SLOTS);   /* all slots + descriptors stay well inside HBM */
     budget_auto_ = std::max<u64>(std::min<u64>(b, 48ull << 30), 256ull << 20);
     return budget_auto_;
 }

@@ -191,3 +191,35 @@ def test_full_size_config2_properties(sw):
     t = np.bincount(pair_of, weights=lens * np.isin(op, (0, 2)), minlength=n)
     assert np.array_equal(q.astype(np.int64), d["alt_len"].astype(np.int64))
     assert (a.offsets >= 0).all() and (a.offsets + t <= d["ref_len"]).all()
+
+
+def test_concurrent_single_pair_calls_are_coalesced(sw, oracle):
+    """the reference's entry is one pair per call from many JVM threads (static native, re-entrant): concurrent
+    mgl_sw_align_one calls must all return the reference's answer (they are coalesced into batches underneath)"""
+    import threading
+    import mgl_b200
+    rng = random.Random(77)
+    jobs = []
+    for k in range(16 * 60):
+        ref = bytes(rng.choice(b"ACGT") for _ in range(rng.randint(20, 300)))
+        i = rng.randrange(len(ref)); j = rng.randint(i + 1, len(ref))
+        alt = bytearray(ref[i:j]) + bytes(rng.choice(b"ACGT") for _ in range(rng.randint(0, 6)))
+        if len(alt) > 3:
+            alt[rng.randrange(len(alt))] = rng.choice(b"ACGT")
+        params = ((10, -15, -30, -5), (200, -150, -260, -11))[k % 2]
+        jobs.append((ref, bytes(alt), params, (1, 2, 4, 8)[k % 4]))
+    got = [None] * len(jobs)
+
+    def work(t):
+        for k in range(t, len(jobs), 16):
+            r, a, p, s = jobs[k]
+            one = mgl_b200.align_one_text(r, a, p, s)
+            got[k] = (one.cigar, one.alignment_offset)
+
+    threads = [threading.Thread(target=work, args=(t,)) for t in range(16)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    for k, (r, a, p, s) in enumerate(jobs):
+        assert got[k] == oracle.align(r, a, p, s), (k, len(r), len(a), p, s)
