@@ -298,7 +298,7 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed)
         a.colbest = (u32 *)ws.colbest.p;
         a.n_warps = L.n_warps;
         a.c = L.kind == KIND_S16X2 ? make_consts<S16x2>(sc, cd.plan.s16_bias) : make_consts<S32>(sc, 0);
-        if ((e = launch_fill_any(L.kind, L.G, L.K, a, L.first_unit, ls)) != cudaSuccess)
+        if ((e = launch_fill_any(L.kind, L.G, L.K, L.pipe, a, L.first_unit, ls)) != cudaSuccess)
             return cuda_fail(e, "fill launch (is a kernel built for this kind/G/K?)");
         bs.fill_launches++;
     }

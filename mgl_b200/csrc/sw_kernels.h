@@ -11,7 +11,7 @@
 namespace mglsw {
 
 /* fill: fails with cudaErrorInvalidValue when no kernel was built for (kind, G, K) */
-cudaError_t launch_fill_any(int kind, int G, int K, const FillArgs &a, u32 first_unit, cudaStream_t stream);
+cudaError_t launch_fill_any(int kind, int G, int K, int pipe, const FillArgs &a, u32 first_unit, cudaStream_t stream);
 
 struct TraceArgs {
     const UnitDesc *units;

@@ -155,11 +155,13 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
         else { G = MGLSW_G_LONG; nstrips = ceil_div_u32(pr.ql, (u32)MGLSW_G_LONG * MGLSW_KMAX); }
         const u32 K = regs_per_lane(pr.ql, nstrips * G);
         const u32 indel = (pr.strategy & (OS_INDEL | OS_LEADING_INDEL)) ? 1u : 0u;
-        /* 1 + 1 + 12 + 5 + 1 bits of launch key, then 24 + 20 bits of shape (tl clipped for the key only) */
+        /* 1 + 1 + 5 + 1 bits of launch key (kind, G, K, strips pipelined over the block's warps), then 11 + 1 + 24 + 20
+           bits of shape (strips and tl clipped for the key only) */
         u64 key = (u64)(kind == KIND_S32 ? 1 : 0);
         key = (key << 1) | (G == (u32)MGLSW_G_LONG ? 1u : 0u);
         key = (key << 5) | K;
-        key = (key << 12) | std::min<u32>(nstrips, 4095);
+        key = (key << 1) | (nstrips >= (u32)MGLSW_PIPE_MIN_STRIPS ? 1u : 0u);
+        key = (key << 11) | std::min<u32>(nstrips, 2047);
         key = (key << 1) | indel;
         key = (key << 24) | pr.ql;
         key = (key << 20) | std::min<u32>(pr.tl, (1u << 20) - 1);
@@ -172,7 +174,7 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
     /* the sorted keys, reduced to their varying bits: two keys agree on a field iff their reduced keys agree on the
        field's reduced mask (read in order: no random access to the full keys) */
     const u64 *const skey = out.sort_key.data();
-    const u64 m_launch = varying == ~0ull ? (0x7full << 57) : gather_bits(0x7full << 57, varying);     /* kind, G, K */
+    const u64 m_launch = varying == ~0ull ? (0xffull << 56) : gather_bits(0xffull << 56, varying);     /* kind, G, K, pipelined */
     const u64 m_pair = varying == ~0ull ? (~0ull << 20) : gather_bits(~0ull << 20, varying);           /* ... + strips, indel, ql */
 
     /* pass 3: units, warps, launches */
@@ -186,6 +188,7 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
         const u64 nk = ~fkey[order[pos]];
         L.kind = ((nk >> 63) & 1) ? KIND_S32 : KIND_S16X2;
         L.G = ((nk >> 62) & 1) ? MGLSW_G_LONG : MGLSW_G_SHORT;
+        L.pipe = (int)((nk >> 56) & 1);
         L.nstrips = L.G == MGLSW_G_SHORT ? 1u : ceil_div_u32(first.ql, (u32)MGLSW_G_LONG * MGLSW_KMAX);   /* of its first unit */
         L.K = (int)regs_per_lane(first.ql, L.nstrips * L.G);
         L.first_unit = (u32)out.units.size();

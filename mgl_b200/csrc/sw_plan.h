@@ -26,6 +26,7 @@ struct PairIn {
 struct Launch {
     int kind;            /* KIND_S16X2 / KIND_S32 */
     int G, K;
+    int pipe;            /* G == 32 only: one unit per block, its strips pipelined over the block's warps */
     u32 nstrips;
     u32 first_unit;      /* index into ChunkPlan::units */
     u32 n_units;         /* multiple of 32 / G (tail padded with inactive units) */
