@@ -223,3 +223,25 @@ def test_concurrent_single_pair_calls_are_coalesced(sw, oracle):
         t.join()
     for k, (r, a, p, s) in enumerate(jobs):
         assert got[k] == oracle.align(r, a, p, s), (k, len(r), len(a), p, s)
+
+
+def test_pipelined_strips_edge_shapes(sw, oracle):
+    """pairs of >= 4 strips run one per block with the strips pipelined over its warps (sw_fill_pipe.cuh): refs shorter
+    than the lane skew, the 3 / 4 strip boundary (alt 2304 / 2305), every strategy"""
+    rng = random.Random(4242)
+    pairs = []
+    for tl, ql in ((1, 3000), (5, 2500), (31, 2305), (33, 2400), (40, 3100), (700, 2304), (650, 2305), (1500, 3073), (900, 4000)):
+        ref = bytes(rng.choice(b"ACGT") for _ in range(tl))
+        alt = bytearray(rng.choice(b"ACGT") for _ in range(ql))
+        w = min(tl, ql)
+        start = rng.randrange(0, ql - w + 1)
+        alt[start:start + w] = ref[:w]
+        for _ in range(8):
+            alt[rng.randrange(ql)] = rng.choice(b"ACGT")
+        pairs.append((ref, bytes(alt)))
+    for params in ((200, -150, -260, -11), (10, -15, -30, -5)):
+        strategies = np.array([(1, 2, 4, 8)[k % 4] for k in range(len(pairs))], dtype=np.int32)
+        res = _check(sw, oracle, pairs, params, strategies)
+        strategies = np.array([(2, 8, 1, 4)[k % 4] for k in range(len(pairs))], dtype=np.int32)
+        _check(sw, oracle, pairs, params, strategies)
+    assert res.stats["pairs_s32"] >= 7
