@@ -379,22 +379,23 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
        Short-lived std::threads, not OpenMP: an OpenMP team keeps spinning after the loop and takes the cores the
        planner threads need in the next few milliseconds (measured: first chunks planned 3x slower). */
     u32 max_tl = 0;
-    u64 total_len = 0, total_est256 = 0;
-    est256_.resize((size_t)in.n);
+    u64 total_len = 0, total_est = 0;
+    estpre_.resize((size_t)in.n);                     /* per slice: inclusive prefix sums of the per-pair checkpoint estimate (bytes) */
+    const int T = in.n > 65536 ? (int)std::min<unsigned>(8u, std::max(1u, std::thread::hardware_concurrency() / 2)) : 1;
+    std::vector<u64> slice_off((size_t)T + 1, 0);
     {
-        const int T = in.n > 65536 ? (int)std::min<unsigned>(8u, std::max(1u, std::thread::hardware_concurrency() / 2)) : 1;
         std::vector<u32> tmax((size_t)T, 0);
         std::vector<u64> tsum((size_t)T, 0), tes((size_t)T, 0);
         auto scan = [&](int t) {
             const int64_t lo = in.n * t / T, hi = in.n * (t + 1) / T;
             u32 m = 0; u64 sum = 0, es = 0;
-            u32 *est = est256_.data();
+            u64 *pre = estpre_.data();
             for (int64_t p = lo; p < hi; p++) {
                 const u32 tl = in.ref_len[p], ql = in.alt_len[p];
                 m = std::max(m, tl);
                 sum += (u64)tl + ql;
-                est[p] = (u32)std::min<u64>((pair_ckpt_bytes(tl, ql) + 255u) >> 8, 0xffffffffu);
-                es += est[p];
+                es += pair_ckpt_bytes(tl, ql);
+                pre[p] = es;
             }
             tmax[(size_t)t] = m; tsum[(size_t)t] = sum; tes[(size_t)t] = es;
         };
@@ -402,8 +403,29 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         for (int t = 1; t < T; t++) th.emplace_back(scan, t);
         scan(0);
         for (std::thread &x : th) x.join();
-        for (int t = 0; t < T; t++) { max_tl = std::max(max_tl, tmax[(size_t)t]); total_len += tsum[(size_t)t]; total_est256 += tes[(size_t)t]; }
+        for (int t = 0; t < T; t++) {
+            max_tl = std::max(max_tl, tmax[(size_t)t]); total_len += tsum[(size_t)t];
+            slice_off[(size_t)t + 1] = slice_off[(size_t)t] + tes[(size_t)t];
+        }
+        total_est = slice_off[(size_t)T];
     }
+    /* checkpoint estimate of pairs [0, x) */
+    auto est_before = [&](int64_t x) -> u64 {
+        if (x <= 0) return 0;
+        int t = (int)(((x - 1) * T) / in.n);
+        while (t + 1 < T && in.n * (t + 1) / T <= x - 1) t++;
+        while (t > 0 && in.n * t / T > x - 1) t--;
+        return estpre_[(size_t)(x - 1)] + slice_off[(size_t)t];
+    };
+    /* pairs the chunk starting at f0 takes: at most cap, and as many as keep the estimated checkpoints inside limit */
+    auto take_at = [&](int64_t f0, u32 cap, u64 limit) -> int64_t {
+        int64_t t = std::min<int64_t>(in.n - f0, cap);
+        const u64 base = est_before(f0);
+        if (est_before(f0 + t) - base <= limit) return t;
+        int64_t lo = 1, hi = t;                           /* largest t with the sum inside the limit, at least one pair */
+        while (lo < hi) { const int64_t mid = (lo + hi + 1) / 2; if (est_before(f0 + mid) - base <= limit) lo = mid; else hi = mid - 1; }
+        return lo;
+    };
     setup_mark("pair table scanned");
     { const int rc0 = reserve_arena(in, max_tl); if (rc0 != MGL_SW_OK) return rc0; }
     setup_mark("arena reserved");
@@ -465,14 +487,17 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
          * mixed pairs spread a chunk over up to 66 kernels, and small chunks would cut those into slivers
          * (measured: config 3 e2e 1296 -> 1112 GCUPS): only the first three chunks are reduced (1/8, 1/4, 1/2).
          */
-        const bool short_pairs = in.n >= 4 * (int64_t)chunk_pairs && (total_est256 << 8) / (u64)in.n < 98304u;
+        const bool short_pairs = in.n >= 4 * (int64_t)chunk_pairs && total_est / (u64)in.n < 196608u;
         for (int64_t f0 = 0; f0 < in.n;) {
             const size_t k = bounds.size();
             const u32 floor_ = std::min<u32>(chunk_pairs, 4096u);
             u32 cap = chunk_pairs;
-            if (short_pairs) cap = k < (size_t)nthreads ? std::max<u32>(chunk_pairs >> 2, floor_) : (k < 2 * (size_t)nthreads ? std::max<u32>(chunk_pairs >> 1, floor_) : chunk_pairs);
-            else if (k < 3) cap = std::max<u32>(chunk_pairs >> (3 - k), floor_);
-            const int64_t t = chunk_take(in, f0, limit, cap, est256_.data());
+            if (short_pairs) {
+                /* two small starters (1/16, 1/8) so the GPU has work within a fraction of a millisecond, then the ramp */
+                if (k < 2) cap = std::max<u32>(chunk_pairs >> (4 - k), floor_);
+                else cap = k < 2 + (size_t)nthreads ? std::max<u32>(chunk_pairs >> 2, floor_) : (k < 2 + 2 * (size_t)nthreads ? std::max<u32>(chunk_pairs >> 1, floor_) : chunk_pairs);
+            } else if (k < 3) cap = std::max<u32>(chunk_pairs >> (3 - k), floor_);
+            const int64_t t = take_at(f0, cap, limit);
             bounds.emplace_back(f0, t);
             f0 += t;
         }

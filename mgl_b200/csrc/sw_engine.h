@@ -132,7 +132,7 @@ private:
     const uint8_t *arena_dev() const { return (const uint8_t *)arena_.p + MGLSW_ARENA_FRONT_PAD; }
     int reserve_arena(const BatchIn &in);
     int reserve_arena(const BatchIn &in, u32 max_tl);
-    std::vector<u32> est256_;    /* align_batch: per-pair checkpoint estimate, units of 256 B */
+    std::vector<u64> estpre_;    /* align_batch: prefix sums of the per-pair checkpoint estimate */
     WorkSlot slots_[MGLSW_SLOTS];
     std::vector<ChunkDev *> ring_;           /* align_batch: staging entries the planner threads fill */
     std::vector<ChunkDev *> resident_;
