@@ -145,13 +145,32 @@ struct Replay {
             const u32 *lp = base + (size_t)cs * rbc * RW + (size_t)cl * LSW + word;
             ht = hval(load_w2(lp + (size_t)(tt / MGLSW_RB) * RW + (tt % MGLSW_RB) * 4u).x);
         }
-        int sum = 0;
-#pragma unroll
-        for (int t = 0; t < MGLSW_KH; t++) {
-            const int tc = t < L ? t : L - 1;                       /* stay inside the sequences; extra terms are not added */
-            const u32 rb_ = SW_LDG(ref + (I - 1 - tc)), ab_ = SW_LDG(alt + (J - 1 - tc));
-            if (t < L) sum += rb_ == ab_ ? match : mismatch;
+        /* mismatches among ref[I-L .. I-1] vs alt[J-L .. J-1] (both ascending): the sum of the L substitution scores */
+        int nm = 0;
+#if SW_ON_DEVICE
+        {
+            /* 16 aligned bytes cover the <= 12 wanted ones at any alignment (the arena is padded on both sides);
+               funnel shifts line them up, a per-byte compare and a population count do the rest */
+            const uint8_t *pr = ref + (I - L), *pa = alt + (J - L);
+            const u32 *wr = reinterpret_cast<const u32 *>(reinterpret_cast<size_t>(pr) & ~(size_t)3);
+            const u32 *wa = reinterpret_cast<const u32 *>(reinterpret_cast<size_t>(pa) & ~(size_t)3);
+            const u32 sr = ((u32)reinterpret_cast<size_t>(pr) & 3u) * 8u, sa = ((u32)reinterpret_cast<size_t>(pa) & 3u) * 8u;
+            const u32 r0 = __ldg(wr), r1 = __ldg(wr + 1), r2 = __ldg(wr + 2), r3 = __ldg(wr + 3);
+            const u32 a0 = __ldg(wa), a1 = __ldg(wa + 1), a2 = __ldg(wa + 2), a3 = __ldg(wa + 3);
+            static_assert(MGLSW_KH <= 12, "the hop compares at most 12 bytes");
+            const u32 x0 = __vcmpne4(__funnelshift_r(r0, r1, sr), __funnelshift_r(a0, a1, sa));
+            const u32 x1 = __vcmpne4(__funnelshift_r(r1, r2, sr), __funnelshift_r(a1, a2, sa));
+            const u32 x2 = __vcmpne4(__funnelshift_r(r2, r3, sr), __funnelshift_r(a2, a3, sa));
+            /* keep bytes 0 .. L-1 */
+            const u32 m0 = L >= 4 ? 0xffffffffu : (0xffffffffu >> (8u * (4u - (u32)L)));
+            const u32 m1 = L >= 8 ? 0xffffffffu : (L <= 4 ? 0u : (0xffffffffu >> (8u * (8u - (u32)L))));
+            const u32 m2 = L >= 12 ? 0xffffffffu : (L <= 8 ? 0u : (0xffffffffu >> (8u * (12u - (u32)L))));
+            nm = (__popc(x0 & m0) + __popc(x1 & m1) + __popc(x2 & m2)) >> 3;
         }
+#else
+        for (int t = 0; t < L; t++) nm += ref[I - 1 - t] != alt[J - 1 - t] ? 1 : 0;
+#endif
+        const int sum = L * match - nm * (match - mismatch);
         hnext = ht;
         return hcur - ht == sum ? L : 0;
     }
