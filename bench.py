@@ -46,6 +46,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--chunk-pairs", type=int, default=0, help="engine chunk size (0: library default)")
+    ap.add_argument("--pipe-wide", type=int, default=-1, help="long-pair kernel on eight warps per pair: 0 never, 1 auto, 2 always (-1: library default)")
     ap.add_argument("--plan-threads", type=int, default=0, help="host planner threads (0: library default)")
     return ap.parse_args()
 
@@ -232,6 +233,8 @@ def main():
     sw._ensure()                                                          # no GPU / no extension -> raises
     if args.chunk_pairs:
         sw.set_option("chunk_pairs", args.chunk_pairs)
+    if args.pipe_wide >= 0:
+        sw.set_option("pipe_wide", args.pipe_wide)
     if args.plan_threads:
         sw.set_option("plan_threads", args.plan_threads)
 

@@ -105,6 +105,7 @@ int mgl_sw_set_option(mgl_sw_handle *h, const char *name, int64_t value)
     else if (!std::strcmp(name, "overlap")) h->engine->overlap = value != 0;
     else if (!std::strcmp(name, "plan_threads")) { if (value < 0 || value > 64) return MGL_SW_E_INVALID; h->engine->plan_threads = (int)value; }
     else if (!std::strcmp(name, "chunk_pairs")) { if (value < 1 || value > (1 << 22)) return MGL_SW_E_INVALID; h->engine->chunk_pairs = (u32)value; }
+    else if (!std::strcmp(name, "pipe_wide")) { if (value < 0 || value > 2) return MGL_SW_E_INVALID; h->engine->pipe_wide = (int)value; }
     else if (!std::strcmp(name, "trace_budget_mb")) { if (value < 0) return MGL_SW_E_INVALID; h->engine->trace_budget_bytes = (u64)value << 20; }
     else return MGL_SW_E_INVALID;
     return MGL_SW_OK;

@@ -159,6 +159,19 @@ static inline u64 pair_ckpt_bytes(u32 tl, u32 ql)
     return (u64)ns * row_blocks(tl, G) * lane_stride16(K) * 16u * G;
 }
 
+/*
+ * Pairs per chunk for a batch.  Short pairs: chunk_pairs (a chunk is a millisecond of work, more buys nothing).
+ * Longer or mixed pairs: a chunk holds its work slot at least as long as its slowest pair takes (a 10 kbp pair
+ * is milliseconds on its own), so the chunk must carry enough other work to fill that time: four times as many
+ * pairs, which in practice means "as many as the checkpoint budget holds" (measured on config 5: 16 Ki pairs per
+ * chunk 313 GCUPS, 32 Ki 509, 64 Ki 827, 128 Ki 1052).
+ */
+u32 Engine::chunk_cap(u64 total_est, int64_t n) const
+{
+    const bool short_pairs = n > 0 && total_est / (u64)n < 196608u;
+    return short_pairs ? chunk_pairs : (u32)std::min<u64>((u64)chunk_pairs * 4u, 1u << 22);
+}
+
 int64_t Engine::chunk_take(const BatchIn &in, int64_t first, u64 limit, u32 max_pairs, const u32 *est256) const
 {
     const int64_t n = std::min<int64_t>(in.n - first, max_pairs ? max_pairs : chunk_pairs);
@@ -215,7 +228,7 @@ int Engine::plan_range(const BatchIn &in, int64_t first, int64_t take, ChunkDev 
 int Engine::plan_next(const BatchIn &in, int64_t first, ChunkDev &cd)
 {
     std::string err;
-    const int rc = plan_range(in, first, chunk_take(in, first, budget(), 0, nullptr), cd, err);
+    const int rc = plan_range(in, first, chunk_take(in, first, budget(), chunk_cap_, nullptr), cd, err);
     return rc == MGL_SW_OK ? rc : fail(rc, err);
 }
 
@@ -298,7 +311,8 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed)
         a.colbest = (u32 *)ws.colbest.p;
         a.n_warps = L.n_warps;
         a.c = L.kind == KIND_S16X2 ? make_consts<S16x2>(sc, cd.plan.s16_bias) : make_consts<S32>(sc, 0);
-        if ((e = launch_fill_any(L.kind, L.G, L.K, L.pipe, a, L.first_unit, ls)) != cudaSuccess)
+        const int pipe = !L.pipe ? 0 : (pipe_wide == 2 || (pipe_wide == 1 && L.n_warps <= MGLSW_PIPE_WIDE_MAX_UNITS)) ? 2 : 1;
+        if ((e = launch_fill_any(L.kind, L.G, L.K, pipe, a, L.first_unit, ls)) != cudaSuccess)
             return cuda_fail(e, "fill launch (is a kernel built for this kind/G/K?)");
         bs.fill_launches++;
     }
@@ -488,10 +502,11 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
          * (measured: config 3 e2e 1296 -> 1112 GCUPS): only the first three chunks are reduced (1/8, 1/4, 1/2).
          */
         const bool short_pairs = in.n >= 4 * (int64_t)chunk_pairs && total_est / (u64)in.n < 196608u;
+        const u32 cap_full = chunk_cap(total_est, in.n);         /* the cap for THIS batch; the ramp stays in units of the option */
         for (int64_t f0 = 0; f0 < in.n;) {
             const size_t k = bounds.size();
             const u32 floor_ = std::min<u32>(chunk_pairs, 4096u);
-            u32 cap = chunk_pairs;
+            u32 cap = cap_full;
             if (short_pairs) {
                 /* two small starters (1/16, 1/8) so the GPU has work within a fraction of a millisecond, then the ramp */
                 if (k < 2) cap = std::max<u32>(chunk_pairs >> (4 - k), floor_);
@@ -622,6 +637,11 @@ int Engine::prepare_resident(const BatchIn &in)
     if ((e = cudaMemcpy((void *)arena_dev(), in.arena, in.arena_bytes, cudaMemcpyHostToDevice)) != cudaSuccess) return cuda_fail(e, "H2D arena");
     BatchStats bs;
     std::memset(&bs, 0, sizeof bs);
+    {
+        u64 total_est = 0;
+        for (int64_t k = 0; k < in.n; k++) total_est += pair_ckpt_bytes(in.ref_len[k], in.alt_len[k]);
+        chunk_cap_ = chunk_cap(total_est, in.n);
+    }
     int64_t first = 0;
     while (first < in.n) {
         ChunkDev *cd = new ChunkDev();

@@ -112,6 +112,7 @@ public:
                                     false = one chunk at a time with per-kernel event timing */
     u32 chunk_pairs = 1u << 16;  /* measured: 64 Ki pairs per chunk with four slots is within 1 % of the best device rate and plans in < 5 ms */
     int plan_threads = 0;        /* host planner threads of align_batch; 0: min(8, hardware threads / 2) */
+    int pipe_wide = 1;           /* pipelined long-pair launches on eight warps per pair: 0 never, 1 when the launch has few pairs, 2 always */
     u64 trace_budget_bytes = 0;  /* 0: derived from free memory */
 
 private:
@@ -124,6 +125,8 @@ private:
     int run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed);
     int ensure_slot(WorkSlot &ws, const ChunkPlan &plan, u32 n);
     u64 budget();
+    u32 chunk_cap(u64 total_est, int64_t n) const;
+    u32 chunk_cap_ = 0;          /* prepare_resident: pairs per chunk of the resident batch */
 
     int device_;
     u64 budget_auto_ = 0;        /* budget() when trace_budget_bytes == 0, fixed at first use */

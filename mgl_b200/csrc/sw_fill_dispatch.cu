@@ -10,13 +10,13 @@ MGLSW_FOR_K_1_24(MGLSW_DECL, S16x2, 8)
 MGLSW_FOR_K_1_24(MGLSW_DECL, S32, 8)
 MGLSW_FOR_K_7_24(MGLSW_DECL, S32, 32)
 #undef MGLSW_DECL
-#define MGLSW_DECL_PIPE(T, G, K) extern template cudaError_t launch_fill_pipe<T, K>(const FillArgs &, u32, cudaStream_t);
+#define MGLSW_DECL_PIPE(T, G, K) extern template cudaError_t launch_fill_pipe<T, K>(const FillArgs &, u32, bool, cudaStream_t);
 MGLSW_FOR_K_7_24(MGLSW_DECL_PIPE, S32, 32)
 #undef MGLSW_DECL_PIPE
 
 #define MGLSW_CASE(T, GG, KK) if (G == GG && K == KK) return launch_fill<T, GG, KK>(a, first_unit, stream);
 
-#define MGLSW_CASE_PIPE(T, GG, KK) if (K == KK) return launch_fill_pipe<T, KK>(a, first_unit, stream);
+#define MGLSW_CASE_PIPE(T, GG, KK) if (K == KK) return launch_fill_pipe<T, KK>(a, first_unit, pipe > 1, stream);
 
 cudaError_t launch_fill_any(int kind, int G, int K, int pipe, const FillArgs &a, u32 first_unit, cudaStream_t stream)
 {

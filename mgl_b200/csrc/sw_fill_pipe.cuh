@@ -25,13 +25,20 @@
 
 namespace mglsw {
 
-template <class T, int K>
-__global__ void __launch_bounds__(MGLSW_FILL_THREADS, 3)
-sw_fill_pipe_kernel(const __grid_constant__ FillArgs a, const u32 first_unit)
+/*
+ * W warps share one pair.  W = 4 (three blocks per SM) is the throughput shape: a launch with many
+ * long pairs fills the GPU with blocks anyway.  W = 8 is the latency shape: a launch with only a few
+ * long pairs (a mixed batch has ~60 per chunk) would otherwise decide how long its chunk holds a
+ * work slot; eight warps finish a 13-strip pair in two rounds instead of four.
+ */
+template <class T, int K, int W>
+__device__ __forceinline__ void fill_pipe_body(const FillArgs &a, const u32 first_unit)
 {
-    constexpr int G = 32, W = MGLSW_FILL_THREADS / 32;
-    __shared__ unsigned long long s_prog[W];
-    __shared__ uint4 s_stage[W][FillLane<T, G, K>::LS16 * 32];
+    constexpr int G = 32;
+    /* dynamic shared memory (W = 8 needs more than the 48 KB a static array may have): progress words, then one staging region per warp */
+    extern __shared__ __align__(128) unsigned char s_dyn[];
+    unsigned long long *s_prog = reinterpret_cast<unsigned long long *>(s_dyn);
+    uint4 (*s_stage)[FillLane<T, G, K>::LS16 * 32] = reinterpret_cast<uint4 (*)[FillLane<T, G, K>::LS16 * 32]>(s_dyn + 128);
     if (threadIdx.x < W) s_prog[threadIdx.x] = 0ull;
     __syncthreads();
     if (blockIdx.x >= a.n_warps) return;                 /* n_warps = units of this launch (one per block) */
@@ -96,10 +103,34 @@ sw_fill_pipe_kernel(const __grid_constant__ FillArgs a, const u32 first_unit)
 }
 
 template <class T, int K>
-cudaError_t launch_fill_pipe(const FillArgs &a, u32 first_unit, cudaStream_t stream)
+__global__ void __launch_bounds__(128, 3)
+sw_fill_pipe_kernel(const __grid_constant__ FillArgs a, const u32 first_unit)
+{
+    fill_pipe_body<T, K, 4>(a, first_unit);
+}
+
+/* 168 registers as in the other fill kernels: one of these blocks and one four-warp block share an SM */
+template <class T, int K>
+__global__ void __maxnreg__(168)
+sw_fill_pipe_wide_kernel(const __grid_constant__ FillArgs a, const u32 first_unit)
+{
+    fill_pipe_body<T, K, MGLSW_PIPE_WIDE_WARPS>(a, first_unit);
+}
+
+template <class T, int K>
+cudaError_t launch_fill_pipe(const FillArgs &a, u32 first_unit, bool wide, cudaStream_t stream)
 {
     if (a.n_warps == 0) return cudaSuccess;
-    sw_fill_pipe_kernel<T, K><<<a.n_warps, MGLSW_FILL_THREADS, 0, stream>>>(a, first_unit);
+    constexpr size_t per_warp = (size_t)FillLane<T, 32, K>::LS16 * 512u;
+    const size_t smem = 128u + per_warp * (wide ? MGLSW_PIPE_WIDE_WARPS : 4);
+    static cudaError_t attr = [] {
+        cudaError_t e = cudaFuncSetAttribute(sw_fill_pipe_wide_kernel<T, K>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)(128u + per_warp * MGLSW_PIPE_WIDE_WARPS));
+        return e;
+    }();
+    if (attr != cudaSuccess) return attr;
+    if (wide) sw_fill_pipe_wide_kernel<T, K><<<a.n_warps, 32 * MGLSW_PIPE_WIDE_WARPS, smem, stream>>>(a, first_unit);
+    else      sw_fill_pipe_kernel<T, K><<<a.n_warps, 128, smem, stream>>>(a, first_unit);
     return cudaGetLastError();
 }
 

@@ -7,5 +7,5 @@
 #error "compile with -DINST_K=<7..24>"
 #endif
 namespace mglsw {
-template cudaError_t launch_fill_pipe<S32, INST_K>(const FillArgs &, u32, cudaStream_t);
+template cudaError_t launch_fill_pipe<S32, INST_K>(const FillArgs &, u32, bool, cudaStream_t);
 }

@@ -306,30 +306,38 @@ struct PairResult {
 };
 
 /*
- * ops_end points one past the pair's scratch region; elements are written
- * downwards so that [ops_end - n_ops, ops_end) reads left to right.
+ * The cell the traceback starts from (sw.cpp:155-170), from what the fill left behind: the running
+ * last-column maximum (sw.cpp:100-104, kept by sw_fill.h) and the captured last row (scanned here as
+ * sw.cpp:116-127 does).  `score` is H of that cell in the fill's representation (+ match + bias);
+ * `seg` the reference's seg_length.  Also the whole result of the score-only entry point.
  */
+struct StartCell { int i, j, seg, score; };
+
 template <class T>
-SW_HD PairResult traceback_pair(const UnitDesc &u, u32 half, u32 G, u32 K, const u32 *ckpt, const uint8_t *arena,
-                                const CellConsts &c, const u32 *colbest4, const u32 *lastrow, int strategy, u32 *ops_end,
-                                u64 *nib, u32 nstride)
+SW_HD StartCell select_start(const UnitDesc &u, u32 half, u32 G, u32 K, const u32 *colbest4, const u32 *lastrow, int strategy)
 {
     const int tl = (int)u.tl[half], ql = (int)u.ql;
     const u32 nslots = u.nstrips * G;
-
-    /* last column: sw.cpp:100-104; the running maximum was kept by the fill (sw_fill.h), same "+ match + bias" as lastrow */
+    const u32 *row = lastrow + u.lastrow_off + (size_t)half * nslots * K;
 #if SW_ON_DEVICE
     const int mqe = (int)__ldcg(colbest4 + 2 * half), mqe_t = (int)__ldcg(colbest4 + 2 * half + 1);
 #else
     const int mqe = (int)colbest4[2 * half], mqe_t = (int)colbest4[2 * half + 1];
 #endif
-
-    int I, J, run = 0, start_score = mqe;
-    if (strategy == OS_INDEL) { I = tl; J = ql; }
-    else if (strategy != OS_LEADING_INDEL) {
+    StartCell sc;
+    if (strategy == OS_INDEL) {
+        /* the corner (tl, ql): its H is the last real entry of the captured row */
+        u32 slot, reg;
+        col_to_slot(u, (u32)ql - 1u, slot, reg);
+#if SW_ON_DEVICE
+        const u32 w = __ldcg(row + (size_t)slot * K + reg);
+#else
+        const u32 w = row[(size_t)slot * K + reg];
+#endif
+        sc.i = tl; sc.j = ql; sc.seg = 0; sc.score = T::half(w, (int)half);
+    } else if (strategy != OS_LEADING_INDEL) {
         /* last row: sw.cpp:116-127 */
         int best = mqe, best_t = mqe_t, best_q = ql, seg = 0;
-        const u32 *row = lastrow + u.lastrow_off + (size_t)half * nslots * K;
         u32 slot = 0, reg = 0;
         for (int j = 1; j <= ql; j++) {
 #if SW_ON_DEVICE
@@ -342,8 +350,23 @@ SW_HD PairResult traceback_pair(const UnitDesc &u, u32 half, u32 G, u32 K, const
             if (s > best || (s == best && da < db)) { best = s; best_t = tl; best_q = j; seg = ql - j; }
             if (++reg >= slot_cols(u, slot)) { reg = 0; slot++; }
         }
-        I = best_t; J = best_q; run = seg; start_score = best;
-    } else { I = mqe_t; J = ql; }
+        sc.i = best_t; sc.j = best_q; sc.seg = seg; sc.score = best;
+    } else { sc.i = mqe_t; sc.j = ql; sc.seg = 0; sc.score = mqe; }
+    return sc;
+}
+
+/*
+ * ops_end points one past the pair's scratch region; elements are written
+ * downwards so that [ops_end - n_ops, ops_end) reads left to right.
+ */
+template <class T>
+SW_HD PairResult traceback_pair(const UnitDesc &u, u32 half, u32 G, u32 K, const u32 *ckpt, const uint8_t *arena,
+                                const CellConsts &c, const u32 *colbest4, const u32 *lastrow, int strategy, u32 *ops_end,
+                                u64 *nib, u32 nstride)
+{
+    const StartCell st = select_start<T>(u, half, G, K, colbest4, lastrow, strategy);
+    int I = st.i, J = st.j, run = st.seg;
+    const int start_score = st.score;
 
     u32 *p = ops_end;
 #define SW_EMIT(op, len) do { if ((len) > 0) *--p = ((u32)(len) << 4) | (u32)(op); } while (0)
@@ -366,7 +389,7 @@ SW_HD PairResult traceback_pair(const UnitDesc &u, u32 half, u32 G, u32 K, const
     /* H at (I, J), when known: at the start cell (the score that selected it) and on checkpointed cells */
     int hcur = start_score - c.bias - c.s_match;
     u32 hops = 0;
-    bool hk = strategy != OS_INDEL;          /* INDEL starts at (tl, ql), whose score was not looked up */
+    bool hk = true;
     while (!done) {
         /*
          * Phase A: while H is known, try to cross the block with one diagonal hop (Replay::hop).  A

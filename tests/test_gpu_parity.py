@@ -239,9 +239,14 @@ def test_pipelined_strips_edge_shapes(sw, oracle):
         for _ in range(8):
             alt[rng.randrange(ql)] = rng.choice(b"ACGT")
         pairs.append((ref, bytes(alt)))
-    for params in ((200, -150, -260, -11), (10, -15, -30, -5)):
-        strategies = np.array([(1, 2, 4, 8)[k % 4] for k in range(len(pairs))], dtype=np.int32)
-        res = _check(sw, oracle, pairs, params, strategies)
-        strategies = np.array([(2, 8, 1, 4)[k % 4] for k in range(len(pairs))], dtype=np.int32)
-        _check(sw, oracle, pairs, params, strategies)
-    assert res.stats["pairs_s32"] >= 7
+    try:
+        for wide in (0, 2):                       # four warps per pair (throughput shape), eight (latency shape)
+            sw.set_option("pipe_wide", wide)
+            for params in ((200, -150, -260, -11), (10, -15, -30, -5)):
+                strategies = np.array([(1, 2, 4, 8)[k % 4] for k in range(len(pairs))], dtype=np.int32)
+                res = _check(sw, oracle, pairs, params, strategies)
+                strategies = np.array([(2, 8, 1, 4)[k % 4] for k in range(len(pairs))], dtype=np.int32)
+                _check(sw, oracle, pairs, params, strategies)
+            assert res.stats["pairs_s32"] >= 7
+    finally:
+        sw.set_option("pipe_wide", 1)
