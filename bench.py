@@ -300,9 +300,21 @@ def main():
         e2e_ms = (time.perf_counter() - t0) * 1e3
         barrier(dist, local)
 
+    # ---- score only: same host buffers through mgl_sw_score_batch, no checkpoints, no traceback
+    so_ms = 0.0
+    if not args.no_e2e:
+        so_out = native.pinned_array(3 * n, np.int32).reshape(n, 3)
+        sw.score_arrays(d["arena"], d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, d["strategies"], out=so_out)
+        barrier(dist, local)
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            sw.score_arrays(d["arena"], d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, d["strategies"], out=so_out)
+        so_ms = (time.perf_counter() - t0) * 1e3
+        barrier(dist, local)
+
     clocks = sampler.stop() if rank == 0 else None     # sampled over all three timed passes (value, per-kernel, e2e)
-    (dev_ms, fill_ms, wall_ms, e2e_ms), (cells_all, pairs_all) = reduce_max_sum(
-        dist, local, [dev_ms, fill_ms, wall_ms, e2e_ms], [float(cells_step), float(n)])
+    (dev_ms, fill_ms, wall_ms, e2e_ms, so_ms), (cells_all, pairs_all) = reduce_max_sum(
+        dist, local, [dev_ms, fill_ms, wall_ms, e2e_ms, so_ms], [float(cells_step), float(n)])
 
     if rank == 0:
         K = args.steps
@@ -347,6 +359,9 @@ def main():
             line["e2e"] = {"value": cells_all * K / (e2e_ms * 1e-3) / 1e9, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                            "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms / K,
                            "alignments_per_s": pairs_all * K / (e2e_ms * 1e-3)}
+            line["score_only_e2e"] = {"value": cells_all * K / (so_ms * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": so_ms / K,
+                                      "d2h_bytes_per_step": 12 * n,
+                                      "note": "mgl_sw_score_batch, host buffers in and out: the fill without checkpoints, start cell and score per pair"}
         if world == 1 and not args.no_cpu_baseline:
             cb = cpu_baseline(d)
             if cb:

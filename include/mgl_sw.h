@@ -84,12 +84,22 @@ MGL_SW_API const char *mgl_sw_last_error(mgl_sw_handle *h);
 MGL_SW_API int mgl_sw_device_count(void);
 MGL_SW_API const char *mgl_sw_version(void);
 
-/* tuning knobs: "allow_s16" 0/1, "chunk_pairs", "trace_budget_mb", "plan_threads", "overlap" 0/1 (resident_run: 1 = chunks
+/* tuning knobs: "allow_s16" 0/1, "chunk_pairs", "trace_budget_mb", "plan_threads", "pipe_wide" 0/1/2 (long-pair
+   kernel on eight warps per pair: never / for launches of few pairs / always), "overlap" 0/1 (resident_run: 1 = chunks
    alternate between two slots, whole-batch time only; 0 = one chunk at a time with per-kernel times) */
 MGL_SW_API int mgl_sw_set_option(mgl_sw_handle *h, const char *name, int64_t value);
 
 /* the batched aligner: host buffers in, host buffers out */
 MGL_SW_API int mgl_sw_align_batch(mgl_sw_handle *h, const mgl_sw_batch *batch, mgl_sw_result *result, mgl_sw_stats *stats);
+
+/*
+ * Score only (no caller in the reference today): the fill without checkpoints and no
+ * traceback.  score3[3p .. 3p+2] = { H of the cell the traceback would start from, its row (ref
+ * position, 1-based), its column (alt position) }: the corner for INDEL, the last-column maximum for
+ * LEADING_INDEL, the better of last column and last row otherwise (ScoreMax, sw_common.h:36-40, as used by
+ * sw.cpp:155-170).  Same inputs, errors and threading as mgl_sw_align_batch.
+ */
+MGL_SW_API int mgl_sw_score_batch(mgl_sw_handle *h, const mgl_sw_batch *batch, int32_t *score3, mgl_sw_stats *stats);
 
 /* device-resident variant for kernel timing: inputs uploaded once, kernels timed with CUDA events */
 MGL_SW_API int mgl_sw_resident_prepare(mgl_sw_handle *h, const mgl_sw_batch *batch);

@@ -129,6 +129,24 @@ int mgl_sw_align_batch(mgl_sw_handle *h, const mgl_sw_batch *batch, mgl_sw_resul
     return rc;
 }
 
+int mgl_sw_score_batch(mgl_sw_handle *h, const mgl_sw_batch *batch, int32_t *score3, mgl_sw_stats *stats)
+{
+    if (!h || !score3) return MGL_SW_E_INVALID;
+    BatchIn in;
+    int rc = to_batch(batch, in);
+    if (rc != MGL_SW_OK) return rc;
+    in.score_only = true;
+    BatchOut out;
+    out.offsets = nullptr; out.cigar_start = nullptr; out.ops = nullptr; out.ops_cap = 0; out.ops_total = 0;
+    out.score3 = score3;
+    BatchStats bs;
+    std::memset(&bs, 0, sizeof bs);
+    std::lock_guard<std::mutex> lk(h->mu);
+    rc = h->engine->align_batch(in, out, &bs);
+    to_stats(bs, stats);
+    return rc;
+}
+
 int mgl_sw_resident_prepare(mgl_sw_handle *h, const mgl_sw_batch *batch)
 {
     if (!h) return MGL_SW_E_INVALID;

@@ -11,7 +11,7 @@
 #define MGLSW_G_LONG 32          /* whole warp per pair, strip-mined              */
 #define MGLSW_FILL_THREADS 128   /* 4 warps per block                             */
 #define MGLSW_PIPE_WIDE_WARPS 8    /* warps per pair of the latency-shaped pipelined kernel (launches of few long pairs) */
-#define MGLSW_PIPE_WIDE_MAX_UNITS 160  /* a pipelined launch of at most this many pairs uses it */
+#define MGLSW_PIPE_WIDE_MAX_UNITS 160  /* a chunk with at most this many pipelined pairs uses it */
 #define MGLSW_PIPE_MIN_STRIPS 4   /* pairs of at least this many strips run one per block, strips pipelined over its warps */
 
 /* X(kind_type, G, K) for every instantiated kernel */

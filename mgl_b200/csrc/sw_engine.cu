@@ -54,7 +54,7 @@ void ChunkDev::release()
 void WorkSlot::release()
 {
     ckpt.release(); carry.release(); lastrow.release(); colbest.release(); scratch.release();
-    offsets.release(); n_ops.release(); starts.release(); tiles.release(); ops.release();
+    offsets.release(); n_ops.release(); starts.release(); tiles.release(); ops.release(); score3.release();
     h_n_ops.release(); h_total.release();
     if (ev_counts) cudaEventDestroy(ev_counts);
     if (ev_done) cudaEventDestroy(ev_done);
@@ -208,6 +208,23 @@ int Engine::plan_range(const BatchIn &in, int64_t first, int64_t take, ChunkDev 
     if (ps == PLAN_BAD_PAIR) { err = "empty or over-long sequence in batch"; return MGL_SW_E_PAIR; }
     cd.first = first;
     cd.n = (u32)take;
+    if (in.score_only) {
+        /*
+         * Nothing reads the checkpoints of a score-only run.  The fill kernels are the same binaries (a "do not
+         * store" flag inside the step loop cost the general path 7 % on config 3 when it was tried), so their
+         * regions are folded onto a small sink instead: every warp writes region w mod S of S regions that together
+         * fit the L2, and the stores never reach HBM as O(cells) traffic.
+         */
+        u64 maxw = 0;
+        for (const UnitDesc &u : cd.plan.units) maxw = std::max<u64>(maxw, warp_ckpt_words(u.nstrips, u.rb_count, u.regs));
+        const u64 S = std::max<u64>(1, std::min<u64>(64, (64ull << 20) / (maxw * 4 + 1)));
+        for (const Launch &L : cd.plan.launches) {
+            const u32 upw = 32u / (u32)L.G;
+            for (u32 w = 0; w < L.n_warps; w++)
+                for (u32 g = 0; g < upw; g++) cd.plan.units[L.first_unit + w * upw + g].ckpt_off = (w % S) * maxw;
+        }
+        cd.plan.ckpt_words = S * maxw;
+    }
 
     /* stage descriptors in pinned memory so the uploads are asynchronous */
     cudaError_t e;
@@ -262,9 +279,17 @@ int Engine::upload_chunk(const BatchIn &in, ChunkDev &cd, cudaStream_t st, bool 
     return MGL_SW_OK;
 }
 
-int Engine::ensure_slot(WorkSlot &ws, const ChunkPlan &plan, u32 n)
+int Engine::ensure_slot(WorkSlot &ws, const ChunkPlan &plan, u32 n, bool score_only)
 {
     cudaError_t e;
+    if (score_only) {                       /* a small shared checkpoint sink (plan_range), no CIGAR scratch: the fill's side buffers and three words per pair */
+        if ((e = ws.ckpt.reserve((plan.ckpt_words + 4) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc checkpoints");
+        if ((e = ws.carry.reserve((plan.carry_entries + 1) * sizeof(Carry))) != cudaSuccess) return cuda_fail(e, "cudaMalloc carry");
+        if ((e = ws.lastrow.reserve((plan.lastrow_words + 1) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc lastrow");
+        if ((e = ws.colbest.reserve((plan.units.size() + 1) * 4 * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc colbest");
+        if ((e = ws.score3.reserve((size_t)n * 3 * sizeof(int))) != cudaSuccess) return cuda_fail(e, "cudaMalloc");
+        return MGL_SW_OK;
+    }
     if ((e = ws.ckpt.reserve((plan.ckpt_words + 4) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc checkpoints");
     if ((e = ws.carry.reserve((plan.carry_entries + 1) * sizeof(Carry))) != cudaSuccess) return cuda_fail(e, "cudaMalloc carry");
     if ((e = ws.lastrow.reserve((plan.lastrow_words + 1) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc lastrow");
@@ -284,7 +309,7 @@ int Engine::ensure_slot(WorkSlot &ws, const ChunkPlan &plan, u32 n)
  * priority) post stream.  The slot's previous chunk must have left the post stream before the
  * fill overwrites the trace.
  */
-int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed)
+int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed, bool score_only)
 {
     cudaError_t e;
     cudaStream_t st = ws.stream, pt = ws.post;
@@ -298,6 +323,9 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed)
         for (int k = 0; k < nside; k++)
             if ((e = cudaStreamWaitEvent(ws.side[k], ws.ev_fork, 0)) != cudaSuccess) return cuda_fail(e, "stream wait");
     }
+    /* long pairs of the whole chunk (they spread over several (K) launches): few -> the latency shape of the pipelined kernel */
+    u32 pipe_units = 0;
+    for (const Launch &L : cd.plan.launches) if (L.pipe) pipe_units += L.n_warps;
     int li = 0;
     for (const Launch &L : cd.plan.launches) {
         const int lane = li++ % (nside + 1);
@@ -311,7 +339,7 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed)
         a.colbest = (u32 *)ws.colbest.p;
         a.n_warps = L.n_warps;
         a.c = L.kind == KIND_S16X2 ? make_consts<S16x2>(sc, cd.plan.s16_bias) : make_consts<S32>(sc, 0);
-        const int pipe = !L.pipe ? 0 : (pipe_wide == 2 || (pipe_wide == 1 && L.n_warps <= MGLSW_PIPE_WIDE_MAX_UNITS)) ? 2 : 1;
+        const int pipe = !L.pipe ? 0 : (pipe_wide == 2 || (pipe_wide == 1 && pipe_units <= MGLSW_PIPE_WIDE_MAX_UNITS)) ? 2 : 1;
         if ((e = launch_fill_any(L.kind, L.G, L.K, pipe, a, L.first_unit, ls)) != cudaSuccess)
             return cuda_fail(e, "fill launch (is a kernel built for this kind/G/K?)");
         bs.fill_launches++;
@@ -338,6 +366,18 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed)
     t.offsets = (int *)ws.offsets.p;
     t.n_ops = (u32 *)ws.n_ops.p;
     t.n_units = (u32)cd.plan.units.size();
+    t.score3 = (int *)ws.score3.p;
+    if (score_only) {
+        if ((e = launch_endpoints(t, pt)) != cudaSuccess) return cuda_fail(e, "endpoint launch");
+        if ((e = cudaEventRecord(ws.ev_post, pt)) != cudaSuccess) return cuda_fail(e, "event record");
+        bs.other_launches += 1;
+        bs.chunks++;
+        bs.cells += cd.plan.cells;
+        bs.pairs += cd.n;
+        bs.pairs_s16 += cd.plan.pairs_s16;
+        bs.pairs_s32 += cd.plan.pairs_s32;
+        return MGL_SW_OK;
+    }
     if ((e = launch_traceback(t, pt)) != cudaSuccess) return cuda_fail(e, "traceback launch");
     if (timed) cudaEventRecord(tev_[3], pt);
     if ((e = launch_scan_counts((const u32 *)ws.n_ops.p, (u32 *)ws.starts.p, (u32 *)ws.tiles.p, cd.n, pt)) != cudaSuccess) return cuda_fail(e, "scan launch");
@@ -381,13 +421,14 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
     std::memset(&bs, 0, sizeof bs);
     if (in.n < 0 || (in.n > 0 && (!in.arena || !in.ref_off || !in.alt_off || !in.ref_len || !in.alt_len)))
         return fail(MGL_SW_E_INVALID, "NULL batch array");
-    if (!out.offsets || !out.cigar_start || (!out.ops && out.ops_cap)) return fail(MGL_SW_E_INVALID, "NULL result array");
+    const bool so = in.score_only;
+    if (so ? !out.score3 : (!out.offsets || !out.cigar_start || (!out.ops && out.ops_cap))) return fail(MGL_SW_E_INVALID, "NULL result array");
     if (check_scores(in.scores) != PLAN_OK) return fail(MGL_SW_E_SCORES, "score set out of range");
     cudaError_t e;
     if ((e = cudaSetDevice(device_)) != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
     resident_scores_ = in.scores;
     out.ops_total = 0;
-    out.cigar_start[0] = 0;
+    if (!so) out.cigar_start[0] = 0;
     if (in.n == 0) { if (stats) *stats = bs; return MGL_SW_OK; }
     /* one parallel pass over the pair table: longest ref, total length, per-pair checkpoint estimate (units of 256 B).
        Short-lived std::threads, not OpenMP: an OpenMP team keeps spinning after the loop and takes the cores the
@@ -466,6 +507,7 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         f.busy = false;
         cudaError_t ee;
         if ((ee = cudaEventSynchronize(ws.ev_counts)) != cudaSuccess) return cuda_fail(ee, "chunk execution");
+        if (so) return MGL_SW_OK;                         /* the three words per pair came home with ev_counts */
         const u32 *cnt = (const u32 *)ws.h_n_ops.p;
         const u64 total = cnt[f.n];
         if (!overflow && ops_running + total <= out.ops_cap) {
@@ -493,7 +535,7 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
     std::vector<std::pair<int64_t, int64_t>> bounds;
     int nthreads = plan_threads > 0 ? plan_threads : (int)std::min<unsigned>(8u, std::max(1u, std::thread::hardware_concurrency() / 2));
     {
-        const u64 limit = budget();
+        const u64 limit = so ? ~0ull : budget();          /* a score-only run parks no checkpoints */
         /*
          * Ramp.  A batch of short pairs (a chunk is two or three kernels): the planners all start at once, so the
          * first round of chunks (one per planner) is a quarter of chunk_pairs, the second round half: the GPU gets
@@ -581,10 +623,20 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         release_upto(c - MGLSW_SLOTS + 1);
         const double t_slot = tl_ms();
         const int64_t first = cd.first;
-        if ((rc = ensure_slot(ws, cd.plan, cd.n)) != MGL_SW_OK) break;
+        if ((rc = ensure_slot(ws, cd.plan, cd.n, so)) != MGL_SW_OK) break;
         if ((rc = upload_chunk(in, cd, ws.stream, !whole, bs)) != MGL_SW_OK) break;
-        if ((rc = run_chunk(cd, ws, bs, false)) != MGL_SW_OK) break;
+        if ((rc = run_chunk(cd, ws, bs, false, so)) != MGL_SW_OK) break;
         const u32 n = cd.n;
+        if (so) {
+            if ((e = cudaMemcpyAsync(out.score3 + 3 * first, ws.score3.p, (size_t)n * 3 * sizeof(int), cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess) { rc = cuda_fail(e, "D2H scores"); break; }
+            bs.d2h_bytes += (size_t)n * 12;
+            cudaEventRecord(ws.ev_counts, ws.post);
+            cudaEventRecord(ws.ev_post, ws.post);
+            fl[si].busy = true; fl[si].first = first; fl[si].n = n;
+            if ((rc = finish((c + 1) % MGLSW_SLOTS)) != MGL_SW_OK) break;
+            release_upto(c - MGLSW_SLOTS + 2);
+            continue;
+        }
         if ((e = cudaMemcpyAsync(out.offsets + first, ws.offsets.p, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess) { rc = cuda_fail(e, "D2H offsets"); break; }
         if ((e = cudaMemcpyAsync(ws.h_n_ops.p, ws.n_ops.p, (size_t)n * sizeof(u32), cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess) { rc = cuda_fail(e, "D2H counts"); break; }
         if ((e = cudaMemcpyAsync((u32 *)ws.h_n_ops.p + n, (u32 *)ws.starts.p + n, sizeof(u32), cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess) { rc = cuda_fail(e, "D2H total"); break; }

@@ -25,9 +25,12 @@ struct TraceArgs {
     u32 *scratch;             /* CIGAR elements, written downwards from ops_end */
     int *offsets;             /* out, per pair                                  */
     u32 *n_ops;               /* out, per pair                                  */
+    int *score3;              /* out, score-only runs: per pair {score, end_ref, end_alt} */
     u32 n_units;              /* units of the chunk (padding units included)    */
 };
 cudaError_t launch_traceback(const TraceArgs &a, cudaStream_t stream);
+/* score-only runs: the traceback's start cell (sw.cpp:155-170) and its H, nothing else (needs units, strategy, c16, c32, colbest, lastrow, score3) */
+cudaError_t launch_endpoints(const TraceArgs &a, cudaStream_t stream);
 
 /* two-level exclusive scan of n_ops: starts[p] = offset inside p's tile of 1024 pairs, tile_sum[t] = offset of tile t,
    starts[n] = total.  tile_sum needs ceil(n / 1024) words. */

@@ -32,6 +32,36 @@ __global__ void __launch_bounds__(128, 4) sw_traceback_kernel(const __grid_const
     a.n_ops[p] = r.n_ops;
 }
 
+/*
+ * Score-only runs: no traceback, only the cell it would start from (sw.cpp:155-170: the corner, the
+ * last-column maximum, or the better of last column and last row, by strategy) and the score there.
+ */
+__global__ void __launch_bounds__(128) sw_endpoint_kernel(const __grid_constant__ TraceArgs a)
+{
+    const u32 tid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tid >= 2u * a.n_units) return;
+    const UnitDesc &u = a.units[tid >> 1];
+    const u32 half = tid & 1u;
+    const u32 p = u.pair[half];
+    if (!(u.flags & UNIT_ACTIVE) || p == NO_PAIR) return;
+    const u32 G = (u.flags & UNIT_G32) ? MGLSW_G_LONG : MGLSW_G_SHORT;
+    const u32 *cb = a.colbest + (size_t)(tid >> 1) * 4u;
+    StartCell st;
+    int h;
+    if (u.flags & UNIT_S32) { st = select_start<S32>(u, half, G, u.regs, cb, a.lastrow, a.strategy[p]); h = st.score - a.c32.bias - a.c32.s_match; }
+    else                    { st = select_start<S16x2>(u, half, G, u.regs, cb, a.lastrow, a.strategy[p]); h = st.score - a.c16.bias - a.c16.s_match; }
+    a.score3[3 * (size_t)p] = h;
+    a.score3[3 * (size_t)p + 1] = st.i;
+    a.score3[3 * (size_t)p + 2] = st.j;
+}
+
+cudaError_t launch_endpoints(const TraceArgs &a, cudaStream_t stream)
+{
+    if (a.n_units == 0) return cudaSuccess;
+    sw_endpoint_kernel<<<(2u * a.n_units + 127) / 128, 128, 0, stream>>>(a);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_traceback(const TraceArgs &a, cudaStream_t stream)
 {
     if (a.n_units == 0) return cudaSuccess;

@@ -60,6 +60,8 @@ def lib():
         L.mgl_sw_version.restype = C.c_char_p
         L.mgl_sw_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_int64]
         L.mgl_sw_align_batch.argtypes = [C.c_void_p, C.POINTER(Batch), C.POINTER(Result), C.POINTER(Stats)]
+        L.mgl_sw_score_batch.argtypes = [C.c_void_p, C.POINTER(Batch), C.c_void_p, C.POINTER(Stats)]
+        L.mgl_sw_score_batch.restype = C.c_int
         L.mgl_sw_resident_prepare.argtypes = [C.c_void_p, C.POINTER(Batch)]
         L.mgl_sw_resident_run.argtypes = [C.c_void_p, C.POINTER(Stats)]
         L.mgl_sw_resident_fetch.argtypes = [C.c_void_p, C.POINTER(Result)]

@@ -62,6 +62,20 @@ def _params(parameters) -> Tuple[int, int, int, int]:
     return parameters.as_tuple() if isinstance(parameters, SWParameters) else tuple(int(x) for x in parameters)
 
 
+def _pack_pairs(pairs: Sequence[Tuple[bytes, bytes]]):
+    """[(ref, alt), ...] -> one arena, ref ‖ alt per pair (the layout of alignNative's readsBuffer, .java:73-75)"""
+    n = len(pairs)
+    ref_len = np.fromiter((len(r) for r, _ in pairs), dtype=np.uint32, count=n)
+    alt_len = np.fromiter((len(a) for _, a in pairs), dtype=np.uint32, count=n)
+    sizes = np.empty(2 * n, dtype=np.uint64)
+    sizes[0::2], sizes[1::2] = ref_len, alt_len
+    offs = np.zeros(2 * n, dtype=np.uint64)
+    if n:
+        offs[1:] = np.cumsum(sizes)[:-1]
+    arena = np.frombuffer(b"".join(r + a for r, a in pairs), dtype=np.uint8)
+    return arena, offs[0::2].copy(), ref_len, offs[1::2].copy(), alt_len
+
+
 class MicrosoftSmithWaterman:
     """SWAlignerNativeBinding implementation backed by one B200."""
 
@@ -114,17 +128,8 @@ class MicrosoftSmithWaterman:
     # -- the batched call --
     def align_batch(self, pairs: Sequence[Tuple[bytes, bytes]], parameters, overhang_strategy=SWOverhangStrategy.SOFTCLIP,
                     strategies: Optional[Sequence[int]] = None) -> BatchResult:
-        n = len(pairs)
-        ref_len = np.fromiter((len(r) for r, _ in pairs), dtype=np.uint32, count=n)
-        alt_len = np.fromiter((len(a) for _, a in pairs), dtype=np.uint32, count=n)
-        sizes = np.empty(2 * n, dtype=np.uint64)
-        sizes[0::2], sizes[1::2] = ref_len, alt_len
-        offs = np.zeros(2 * n, dtype=np.uint64)
-        if n:
-            offs[1:] = np.cumsum(sizes)[:-1]
-        arena = np.frombuffer(b"".join(r + a for r, a in pairs), dtype=np.uint8)
-        return self.align_arrays(arena, offs[0::2].copy(), ref_len, offs[1::2].copy(), alt_len, parameters,
-                                 overhang_strategy, strategies)
+        arena, ref_off, ref_len, alt_off, alt_len = _pack_pairs(pairs)
+        return self.align_arrays(arena, ref_off, ref_len, alt_off, alt_len, parameters, overhang_strategy, strategies)
 
     def align_arrays(self, arena, ref_off, ref_len, alt_off, alt_len, parameters,
                      overhang_strategy=SWOverhangStrategy.SOFTCLIP, strategies=None, ops_cap: Optional[int] = None,
@@ -152,6 +157,26 @@ class MicrosoftSmithWaterman:
             break
         del keep
         return BatchResult(offsets, cigar_start, ops[: int(r.ops_total)], st.as_dict())
+
+    # -- score only: no traceback --
+    def score_arrays(self, arena, ref_off, ref_len, alt_off, alt_len, parameters,
+                     overhang_strategy=SWOverhangStrategy.SOFTCLIP, strategies=None, out: Optional[np.ndarray] = None):
+        """(score3, stats): score3[p] = (H of the traceback's start cell, its ref row, its alt column), sw.cpp:155-170."""
+        h = self._ensure()
+        b, keep = native.make_batch(arena, ref_off, ref_len, alt_off, alt_len, _params(parameters),
+                                    int(overhang_strategy), strategies)
+        score3 = out if out is not None else np.zeros((int(b.n), 3), dtype=np.int32)
+        st = native.Stats()
+        rc = native.lib().mgl_sw_score_batch(h, C.byref(b), score3.ctypes.data, C.byref(st))
+        if rc != native.OK:
+            raise self._err(rc)
+        del keep
+        return score3, st.as_dict()
+
+    def score_batch(self, pairs: Sequence[Tuple[bytes, bytes]], parameters, overhang_strategy=SWOverhangStrategy.SOFTCLIP,
+                    strategies: Optional[Sequence[int]] = None) -> np.ndarray:
+        arena, ref_off, ref_len, alt_off, alt_len = _pack_pairs(pairs)
+        return self.score_arrays(arena, ref_off, ref_len, alt_off, alt_len, parameters, overhang_strategy, strategies)[0]
 
     # -- device-resident timing path used by bench.py --
     def resident_prepare(self, arena, ref_off, ref_len, alt_off, alt_len, parameters, overhang_strategy=1, strategies=None):

@@ -8,6 +8,7 @@
  */
 #include <chrono>
 #include <cstdint>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -73,6 +74,24 @@ int mgl_ref_align_jni(const uint8_t *reads, int tl, int ql, int match, int misma
     static FakeJvm jvm;
     return Java_com_microsoft_mgl_smithwaterman_MicrosoftSmithWaterman_alignNative(
         &jvm.env, nullptr, (jobject)reads, (jobject)cigar_buf, tl, ql, match, mismatch, go, ge, strategy);
+}
+
+/*
+ * The reference's ScoreMax (sw_common.h:36-40) for one pair: its own calculateMatrix (sw.cpp:5-146) run the way
+ * align_scalar does (sw.cpp:258-272), the traceback left out.  out6 = {mqe, mqe_t, max, max_t, max_q, seg_length}.
+ * Pins the start cell and score of the score-only entry point.  Returns 0, -1 out of memory.
+ */
+int mgl_ref_scoremax(const uint8_t *ref, int tl, const uint8_t *alt, int ql,
+                     int match, int mismatch, int go, int ge, int strategy, int32_t *out6)
+{
+    ScoreMax ez;
+    const size_t cells = ((size_t)tl + 1) * ((size_t)ql + 1);
+    int *bck = (int *)calloc(cells, sizeof(int));
+    if (!bck) return -1;
+    calculateMatrix((const char *)ref, tl, (const char *)alt, ql, bck, normalise(match, mismatch, go, ge), strategy, &ez);
+    free(bck);
+    out6[0] = ez.mqe; out6[1] = ez.mqe_t; out6[2] = ez.max; out6[3] = ez.max_t; out6[4] = ez.max_q; out6[5] = ez.seg_length;
+    return 0;
 }
 
 int mgl_ref_max_threads(void)

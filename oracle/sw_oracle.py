@@ -69,6 +69,10 @@ def _load_ref():
                                           C.c_char_p]
         lib.mgl_ref_align_jni.restype = C.c_int
         lib.mgl_ref_max_threads.restype = C.c_int
+        if hasattr(lib, "mgl_ref_scoremax"):
+            lib.mgl_ref_scoremax.argtypes = [C.c_char_p, C.c_int, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                             C.c_int, C.POINTER(C.c_int32)]
+            lib.mgl_ref_scoremax.restype = C.c_int
         lib.mgl_ref_align_batch.argtypes = [C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                             C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                             C.c_int, C.c_void_p, C.c_void_p, C.c_int]
@@ -97,6 +101,45 @@ def align_ops(ref: bytes, alt: bytes, params, strategy) -> Tuple[List[int], Orac
     if rc != 0:
         raise RuntimeError(f"oracle_sw_align rc={rc}")
     return list(ops[: res.n_ops]), res
+
+
+def score3(ref: bytes, alt: bytes, params, strategy) -> Tuple[int, int, int]:
+    """Oracle (score, row, column) of the cell the traceback starts from (sw.cpp:155-170)."""
+    _, res = align_ops(ref, alt, params, strategy)
+    return res.score, res.start_i, res.start_j
+
+
+def path_score(cigar: str, offset: int, ref: bytes, alt: bytes, params) -> int:
+    """Score of the alignment a CIGAR describes, under the recurrence of sw.cpp:55-93: per-base match / mismatch for M,
+    -open - (len - 1) * extend per I / D run; S clips cost nothing.  For the INDEL strategies this is H[tl][ql] resp.
+    H[mqe_t][ql], which ties the score-only result to the reference's OUTPUT where its ScoreMax has no field."""
+    import re
+    m, x, go, ge = abs(params[0]), -abs(params[1]), abs(params[2]), abs(params[3])
+    i, j, s = offset, 0, 0
+    for ln, op in re.findall(r"(\d+)([MIDS])", cigar):
+        ln = int(ln)
+        if op == "M":
+            s += sum(m if ref[i + k] == alt[j + k] else x for k in range(ln))
+            i += ln
+            j += ln
+        elif op == "I":
+            s -= go + (ln - 1) * ge
+            j += ln
+        elif op == "D":
+            s -= go + (ln - 1) * ge
+            i += ln
+        else:
+            j += ln
+    return s
+
+
+def ref_scoremax(ref: bytes, alt: bytes, params, strategy) -> dict:
+    """The reference's own ScoreMax (its calculateMatrix, oracle/_ref)."""
+    lib = _load_ref()
+    out = (C.c_int32 * 6)()
+    if lib.mgl_ref_scoremax(ref, len(ref), alt, len(alt), params[0], params[1], params[2], params[3], strategy, out) != 0:
+        raise MemoryError("mgl_ref_scoremax")
+    return dict(zip(("mqe", "mqe_t", "max", "max_t", "max_q", "seg_length"), list(out)))
 
 
 REF_SCALAR, REF_AVX, REF_DISPATCH = 0, 1, 2

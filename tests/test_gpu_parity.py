@@ -250,3 +250,52 @@ def test_pipelined_strips_edge_shapes(sw, oracle):
             assert res.stats["pairs_s32"] >= 7
     finally:
         sw.set_option("pipe_wide", 1)
+
+
+def test_score_only_batch(sw, oracle, golden):
+    """mgl_sw_score_batch (no checkpoints, no traceback): (score, row, column) of the traceback's start cell against the
+    oracle (pinned to the reference's ScoreMax in tests/test_oracle.py): golden cases, both arithmetics, lane groups of
+    8 and 32, strip-mined and pipelined pairs, every strategy"""
+    rng = random.Random(777)
+    pairs = [(c["ref"].encode("latin1"), c["alt"].encode("latin1")) for c in golden["cases"][:400]]
+    for tl, ql in ((1, 1), (7, 300), (300, 7), (450, 150), (500, 193), (900, 700), (640, 1000), (33, 2400), (800, 2305), (1200, 3100)):
+        ref = bytes(rng.choice(b"ACGT") for _ in range(tl))
+        alt = bytearray(rng.choice(b"ACGT") for _ in range(ql))
+        w = min(tl, ql)
+        start = rng.randrange(0, ql - w + 1)
+        alt[start:start + w] = ref[:w]
+        for _ in range(6):
+            alt[rng.randrange(ql)] = rng.choice(b"ACGT")
+        pairs.append((ref, bytes(alt)))
+    for params in ((10, -15, -30, -5), (200, -150, -260, -11)):
+        for rot in range(2):
+            strategies = np.array([(1, 2, 4, 8)[(k + rot) % 4] for k in range(len(pairs))], dtype=np.int32)
+            got = sw.score_batch(pairs, params, 1, strategies)
+            bad = []
+            for k, (r, a) in enumerate(pairs):
+                exp = oracle.score3(r, a, params, int(strategies[k]))
+                if tuple(int(x) for x in got[k]) != exp:
+                    bad.append((k, len(r), len(a), params, int(strategies[k]), tuple(int(x) for x in got[k]), exp))
+            assert not bad, bad[:3]
+    # the same handle still aligns afterwards (slots switch back to checkpointed runs)
+    _check(sw, oracle, pairs[-10:], (200, -150, -260, -11), np.array([1, 2, 4, 8, 1, 2, 4, 8, 1, 2], dtype=np.int32))
+
+
+def test_score_only_matches_alignment_on_synthetic_config(sw):
+    """config 2 and 3 shapes, 20 000 pairs: the score-only start cell agrees with the alignment's own end point
+    (offset + ref bases consumed = start row; alt bases before the trailing clip = start column)"""
+    from mgl_b200 import synth
+    for config in (2, 3):
+        d = synth.generate(config, 20000)
+        res = sw.align_arrays(d["arena"], d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, d["strategies"],
+                              ops_cap=16 * 20000)
+        sc, _ = sw.score_arrays(d["arena"], d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, d["strategies"])
+        cs = res.cigar_start.astype(np.int64)
+        for p in range(0, 20000, 7):
+            ops = res.ops[cs[p]: cs[p + 1]]
+            ref_used = sum(int(x) >> 4 for x in ops if (int(x) & 15) in (0, 2))
+            alt_used = sum(int(x) >> 4 for x in ops if (int(x) & 15) in (0, 1, 4))
+            strat = int(d["strategies"][p])
+            trail = int(ops[-1]) >> 4 if (int(ops[-1]) & 15) == 4 and strat == 1 and len(ops) > 1 else 0
+            assert int(res.offsets[p]) + ref_used == int(sc[p, 1]), (config, p)
+            assert alt_used - trail == int(sc[p, 2]), (config, p)

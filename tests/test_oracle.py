@@ -66,3 +66,36 @@ def test_reference_jni_entry_matches_oracle(oracle):
     r, a = b"GGGGACGTACGTCCCC", b"TTACGTACGTTT"
     assert oracle.ref_align_jni(r, a, (200, -150, -260, -11), oracle.SOFTCLIP) == ("2I7M2I1M", 4)
     assert oracle.align(r, a, (200, -150, -260, -11), oracle.SOFTCLIP) == ("2I7M2I1M", 4)
+
+
+def test_start_cell_and_score_vs_reference_scoremax(oracle):
+    """the oracle's (score, row, column) of the traceback start cell -- what mgl_sw_score_batch returns -- against the
+    reference's own ScoreMax (its calculateMatrix, sw.cpp:5-146) and against the score of the reference's output CIGAR"""
+    if not oracle.have_ref():
+        pytest.skip("oracle/_ref not built (no /root/reference here)")
+    rng = random.Random(8104)
+    score_sets = [(10, -15, -30, -5), (200, -150, -260, -11), (1, -1, -1, -1), (3, -1, -2, 0)]   # open >= extend: CIGAR runs = gaps
+    for k in range(600):
+        alpha = rng.choice(["AC", "ACGT", "ACGTN"])
+        ref = bytes(rng.choice(alpha.encode()) for _ in range(rng.randint(1, 150)))
+        if rng.random() < 0.6:
+            i = rng.randrange(len(ref)); j = rng.randint(i + 1, len(ref))
+            alt = bytearray(ref[i:j])
+            for _ in range(rng.randint(0, 4)):
+                alt[rng.randrange(len(alt))] = rng.choice(alpha.encode())
+            alt = bytes(alt) + bytes(rng.choice(alpha.encode()) for _ in range(rng.randint(0, 6)))
+        else:
+            alt = bytes(rng.choice(alpha.encode()) for _ in range(rng.randint(1, 150)))
+        p = score_sets[k % len(score_sets)]
+        for s in oracle.STRATEGIES:
+            score, si, sj = oracle.score3(ref, alt, p, s)
+            ez = oracle.ref_scoremax(ref, alt, p, s)
+            if s == oracle.INDEL:
+                assert (si, sj) == (len(ref), len(alt))
+            elif s == oracle.LEADING_INDEL:
+                assert (score, si, sj) == (ez["mqe"], ez["mqe_t"], len(alt)), (ref, alt, p, s)
+            else:
+                assert (score, si, sj) == (ez["max"], ez["max_t"], ez["max_q"]), (ref, alt, p, s)
+            if s != oracle.IGNORE:          # IGNORE folds the overhangs into M: its CIGAR is not a scored path
+                cigar, off = oracle.ref_align(ref, alt, p, s)
+                assert oracle.path_score(cigar, off, ref, alt, p) == score, (ref, alt, p, s, cigar, off)
