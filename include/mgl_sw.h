@@ -93,6 +93,21 @@ MGL_SW_API int mgl_sw_set_option(mgl_sw_handle *h, const char *name, int64_t val
 MGL_SW_API int mgl_sw_align_batch(mgl_sw_handle *h, const mgl_sw_batch *batch, mgl_sw_result *result, mgl_sw_stats *stats);
 
 /*
+ * The same batch with the CIGARs formatted on the device: pair p's text is
+ * text[text_start[p] .. text_start[p+1]), exactly the characters alignNative writes to cigarBuffer
+ * (to_string(length) + state per element, sw.cpp:251-252; no NUL, ...SmithWaterman.cpp:65).
+ * MGL_SW_E_OPS_CAPACITY when text_cap is too small: text_total holds the characters needed.
+ */
+typedef struct mgl_sw_text_result {
+    int32_t *offsets;             /* n                                                        */
+    uint64_t *text_start;         /* n + 1                                                    */
+    char *text;                   /* text_cap characters                                      */
+    uint64_t text_cap;
+    uint64_t text_total;          /* out */
+} mgl_sw_text_result;
+MGL_SW_API int mgl_sw_align_batch_text(mgl_sw_handle *h, const mgl_sw_batch *batch, mgl_sw_text_result *result, mgl_sw_stats *stats);
+
+/*
  * Score only (no caller in the reference today): the fill without checkpoints and no
  * traceback.  score3[3p .. 3p+2] = { H of the cell the traceback would start from, its row (ref
  * position, 1-based), its column (alt position) }: the corner for INDEL, the last-column maximum for

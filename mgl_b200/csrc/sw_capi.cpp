@@ -129,6 +129,25 @@ int mgl_sw_align_batch(mgl_sw_handle *h, const mgl_sw_batch *batch, mgl_sw_resul
     return rc;
 }
 
+int mgl_sw_align_batch_text(mgl_sw_handle *h, const mgl_sw_batch *batch, mgl_sw_text_result *result, mgl_sw_stats *stats)
+{
+    if (!h || !result) return MGL_SW_E_INVALID;
+    BatchIn in;
+    int rc = to_batch(batch, in);
+    if (rc != MGL_SW_OK) return rc;
+    in.text = true;
+    BatchOut out;
+    out.offsets = result->offsets; out.cigar_start = result->text_start; out.ops = nullptr; out.ops_cap = 0; out.ops_total = 0;
+    out.text = result->text; out.text_cap = result->text_cap;
+    BatchStats bs;
+    std::memset(&bs, 0, sizeof bs);
+    std::lock_guard<std::mutex> lk(h->mu);
+    rc = h->engine->align_batch(in, out, &bs);
+    result->text_total = out.ops_total;
+    to_stats(bs, stats);
+    return rc;
+}
+
 int mgl_sw_score_batch(mgl_sw_handle *h, const mgl_sw_batch *batch, int32_t *score3, mgl_sw_stats *stats)
 {
     if (!h || !score3) return MGL_SW_E_INVALID;

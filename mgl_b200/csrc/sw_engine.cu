@@ -54,7 +54,7 @@ void ChunkDev::release()
 void WorkSlot::release()
 {
     ckpt.release(); carry.release(); lastrow.release(); colbest.release(); scratch.release();
-    offsets.release(); n_ops.release(); starts.release(); tiles.release(); ops.release(); score3.release();
+    offsets.release(); n_ops.release(); starts.release(); tiles.release(); ops.release(); score3.release(); n_chars.release();
     h_n_ops.release(); h_total.release();
     if (ev_counts) cudaEventDestroy(ev_counts);
     if (ev_done) cudaEventDestroy(ev_done);
@@ -279,9 +279,10 @@ int Engine::upload_chunk(const BatchIn &in, ChunkDev &cd, cudaStream_t st, bool 
     return MGL_SW_OK;
 }
 
-int Engine::ensure_slot(WorkSlot &ws, const ChunkPlan &plan, u32 n, bool score_only)
+int Engine::ensure_slot(WorkSlot &ws, const ChunkPlan &plan, u32 n, bool score_only, bool text)
 {
     cudaError_t e;
+    if (text && (e = ws.n_chars.reserve((size_t)n * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc");
     if (score_only) {                       /* a small shared checkpoint sink (plan_range), no CIGAR scratch: the fill's side buffers and three words per pair */
         if ((e = ws.ckpt.reserve((plan.ckpt_words + 4) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc checkpoints");
         if ((e = ws.carry.reserve((plan.carry_entries + 1) * sizeof(Carry))) != cudaSuccess) return cuda_fail(e, "cudaMalloc carry");
@@ -309,7 +310,7 @@ int Engine::ensure_slot(WorkSlot &ws, const ChunkPlan &plan, u32 n, bool score_o
  * priority) post stream.  The slot's previous chunk must have left the post stream before the
  * fill overwrites the trace.
  */
-int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed, bool score_only)
+int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed, bool score_only, bool text)
 {
     cudaError_t e;
     cudaStream_t st = ws.stream, pt = ws.post;
@@ -380,9 +381,19 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed, bo
     }
     if ((e = launch_traceback(t, pt)) != cudaSuccess) return cuda_fail(e, "traceback launch");
     if (timed) cudaEventRecord(tev_[3], pt);
-    if ((e = launch_scan_counts((const u32 *)ws.n_ops.p, (u32 *)ws.starts.p, (u32 *)ws.tiles.p, cd.n, pt)) != cudaSuccess) return cuda_fail(e, "scan launch");
-    if ((e = launch_compact((const u32 *)ws.scratch.p, (const u64 *)cd.ops_end.p, (const u32 *)ws.n_ops.p,
-                            (const u32 *)ws.starts.p, (const u32 *)ws.tiles.p, (u32 *)ws.ops.p, cd.n, pt)) != cudaSuccess) return cuda_fail(e, "compact launch");
+    if (text) {
+        /* characters per pair -> the same scan -> characters; the packed elements stay in the scratch buffer */
+        if ((e = launch_text_len((const u32 *)ws.scratch.p, (const u64 *)cd.ops_end.p, (const u32 *)ws.n_ops.p, (u32 *)ws.n_chars.p, cd.n, pt)) != cudaSuccess)
+            return cuda_fail(e, "text length launch");
+        if ((e = launch_scan_counts((const u32 *)ws.n_chars.p, (u32 *)ws.starts.p, (u32 *)ws.tiles.p, cd.n, pt)) != cudaSuccess) return cuda_fail(e, "scan launch");
+        if ((e = launch_text_format((const u32 *)ws.scratch.p, (const u64 *)cd.ops_end.p, (const u32 *)ws.n_ops.p, (const u32 *)ws.starts.p,
+                                    (const u32 *)ws.tiles.p, (char *)ws.ops.p, cd.n, pt)) != cudaSuccess) return cuda_fail(e, "text format launch");
+        bs.other_launches += 1;
+    } else {
+        if ((e = launch_scan_counts((const u32 *)ws.n_ops.p, (u32 *)ws.starts.p, (u32 *)ws.tiles.p, cd.n, pt)) != cudaSuccess) return cuda_fail(e, "scan launch");
+        if ((e = launch_compact((const u32 *)ws.scratch.p, (const u64 *)cd.ops_end.p, (const u32 *)ws.n_ops.p,
+                                (const u32 *)ws.starts.p, (const u32 *)ws.tiles.p, (u32 *)ws.ops.p, cd.n, pt)) != cudaSuccess) return cuda_fail(e, "compact launch");
+    }
     if (timed) cudaEventRecord(tev_[4], pt);
     if ((e = cudaEventRecord(ws.ev_post, pt)) != cudaSuccess) return cuda_fail(e, "event record");
     bs.other_launches += 4;
@@ -421,8 +432,11 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
     std::memset(&bs, 0, sizeof bs);
     if (in.n < 0 || (in.n > 0 && (!in.arena || !in.ref_off || !in.alt_off || !in.ref_len || !in.alt_len)))
         return fail(MGL_SW_E_INVALID, "NULL batch array");
-    const bool so = in.score_only;
-    if (so ? !out.score3 : (!out.offsets || !out.cigar_start || (!out.ops && out.ops_cap))) return fail(MGL_SW_E_INVALID, "NULL result array");
+    const bool so = in.score_only, tx = in.text && !so;
+    if (so ? !out.score3 : (!out.offsets || !out.cigar_start || (tx ? (!out.text && out.text_cap) : (!out.ops && out.ops_cap))))
+        return fail(MGL_SW_E_INVALID, "NULL result array");
+    const u64 out_cap = tx ? out.text_cap : out.ops_cap;       /* elements: characters of a text run, packed words otherwise */
+    const size_t esz = tx ? 1 : sizeof(u32);
     if (check_scores(in.scores) != PLAN_OK) return fail(MGL_SW_E_SCORES, "score set out of range");
     cudaError_t e;
     if ((e = cudaSetDevice(device_)) != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
@@ -510,11 +524,12 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         if (so) return MGL_SW_OK;                         /* the three words per pair came home with ev_counts */
         const u32 *cnt = (const u32 *)ws.h_n_ops.p;
         const u64 total = cnt[f.n];
-        if (!overflow && ops_running + total <= out.ops_cap) {
+        if (!overflow && ops_running + total <= out_cap) {
             if (total) {
-                if ((ee = cudaMemcpyAsync(out.ops + ops_running, ws.ops.p, total * sizeof(u32), cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess)
+                void *dst = tx ? (void *)(out.text + ops_running) : (void *)(out.ops + ops_running);
+                if ((ee = cudaMemcpyAsync(dst, ws.ops.p, total * esz, cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess)
                     return cuda_fail(ee, "D2H ops");
-                bs.d2h_bytes += total * sizeof(u32);
+                bs.d2h_bytes += total * esz;
             }
         } else overflow = true;
         cudaEventRecord(ws.ev_done, ws.post);
@@ -623,9 +638,9 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         release_upto(c - MGLSW_SLOTS + 1);
         const double t_slot = tl_ms();
         const int64_t first = cd.first;
-        if ((rc = ensure_slot(ws, cd.plan, cd.n, so)) != MGL_SW_OK) break;
+        if ((rc = ensure_slot(ws, cd.plan, cd.n, so, tx)) != MGL_SW_OK) break;
         if ((rc = upload_chunk(in, cd, ws.stream, !whole, bs)) != MGL_SW_OK) break;
-        if ((rc = run_chunk(cd, ws, bs, false, so)) != MGL_SW_OK) break;
+        if ((rc = run_chunk(cd, ws, bs, false, so, tx)) != MGL_SW_OK) break;
         const u32 n = cd.n;
         if (so) {
             if ((e = cudaMemcpyAsync(out.score3 + 3 * first, ws.score3.p, (size_t)n * 3 * sizeof(int), cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess) { rc = cuda_fail(e, "D2H scores"); break; }
@@ -638,7 +653,7 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
             continue;
         }
         if ((e = cudaMemcpyAsync(out.offsets + first, ws.offsets.p, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess) { rc = cuda_fail(e, "D2H offsets"); break; }
-        if ((e = cudaMemcpyAsync(ws.h_n_ops.p, ws.n_ops.p, (size_t)n * sizeof(u32), cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess) { rc = cuda_fail(e, "D2H counts"); break; }
+        if ((e = cudaMemcpyAsync(ws.h_n_ops.p, tx ? ws.n_chars.p : ws.n_ops.p, (size_t)n * sizeof(u32), cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess) { rc = cuda_fail(e, "D2H counts"); break; }
         if ((e = cudaMemcpyAsync((u32 *)ws.h_n_ops.p + n, (u32 *)ws.starts.p + n, sizeof(u32), cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess) { rc = cuda_fail(e, "D2H total"); break; }
         bs.d2h_bytes += (size_t)n * 8 + 4;
         cudaEventRecord(ws.ev_counts, ws.post);

@@ -37,6 +37,7 @@ struct BatchIn {
     const int32_t *strategies;   /* per pair, or NULL */
     int strategy;                /* used when strategies == NULL */
     Scores scores;
+    bool text = false;           /* CIGARs formatted on the device: BatchOut::text instead of ::ops */
     bool score_only = false;     /* no traceback: BatchOut::score3 only */
 };
 
@@ -46,6 +47,8 @@ struct BatchOut {
     uint32_t *ops;               /* ops_cap packed elements */
     uint64_t ops_cap;
     uint64_t ops_total;          /* out */
+    char *text = nullptr;        /* text runs: text_cap characters, pair p's CIGAR is text[cigar_start[p] .. cigar_start[p+1]), no NUL; */
+    uint64_t text_cap = 0;       /* ops_total then counts characters                                                             */
     int32_t *score3 = nullptr;   /* score-only runs: n x {score, end_ref, end_alt}; the other arrays are not touched */
 };
 
@@ -87,7 +90,7 @@ struct WorkSlot {
     cudaStream_t side[MGLSW_SIDE] = {};  /* further fill launches of the same chunk, forked from / joined into `stream` */
     cudaEvent_t ev_fork = nullptr, ev_side[MGLSW_SIDE] = {};
     cudaEvent_t ev_fill = nullptr, ev_post = nullptr, ev_counts = nullptr, ev_done = nullptr;
-    DevBuf ckpt, carry, lastrow, colbest, scratch, offsets, n_ops, starts, tiles, ops, score3;
+    DevBuf ckpt, carry, lastrow, colbest, scratch, offsets, n_ops, starts, tiles, ops, score3, n_chars;
     PinBuf h_n_ops, h_total;
     void release();
 };
@@ -124,8 +127,8 @@ private:
     int64_t chunk_take(const BatchIn &in, int64_t first, u64 limit, u32 max_pairs, const u32 *est256) const;
     int plan_range(const BatchIn &in, int64_t first, int64_t take, ChunkDev &cd, std::string &err) const;
     int upload_chunk(const BatchIn &in, ChunkDev &cd, cudaStream_t st, bool upload_arena, BatchStats &bs);
-    int run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed, bool score_only = false);
-    int ensure_slot(WorkSlot &ws, const ChunkPlan &plan, u32 n, bool score_only = false);
+    int run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed, bool score_only = false, bool text = false);
+    int ensure_slot(WorkSlot &ws, const ChunkPlan &plan, u32 n, bool score_only = false, bool text = false);
     u64 budget();
     u32 chunk_cap(u64 total_est, int64_t n) const;
     u32 chunk_cap_ = 0;          /* prepare_resident: pairs per chunk of the resident batch */

@@ -20,6 +20,7 @@
 #include <jni.h>
 
 #include <cstdio>
+#include <mutex>
 #include <vector>
 
 #include "../../include/mgl_sw.h"
@@ -53,5 +54,55 @@ JNIEXPORT jint JNICALL Java_com_microsoft_mgl_smithwaterman_MicrosoftSmithWaterm
 }
 
 JNIEXPORT void JNICALL Java_com_microsoft_mgl_smithwaterman_MicrosoftSmithWaterman_doneNative(JNIEnv *, jclass) {}
+
+/*
+ * The batched crossing (no counterpart in the reference, whose align() is one pair per call,
+ * MicrosoftSmithWaterman.java:66-86).  Binds to
+ *   private static native int alignBatchNative(ByteBuffer arena, long arenaBytes, int n,
+ *           ByteBuffer refOff, ByteBuffer refLen, ByteBuffer altOff, ByteBuffer altLen,           // long[n], int[n], long[n], int[n]
+ *           int match, int mismatch, int gapOpen, int gapExtend, int overhangStrategy, ByteBuffer strategies,  // int[n] or null
+ *           ByteBuffer offsetsOut, ByteBuffer cigarStartOut, ByteBuffer cigarTextOut, long textCap);  // int[n], long[n+1], byte[textCap]
+ * (INTEGRATION.md has the Java side).  All buffers are direct and in native byte order; pair p's CIGAR is the
+ * characters cigarTextOut[cigarStartOut[p] .. cigarStartOut[p+1]), exactly what alignNative would have written for
+ * it, formatted on the GPU.  Returns 0 or an MGL_SW_E_* code; on MGL_SW_E_OPS_CAPACITY cigarStartOut[n] holds the
+ * text capacity needed.  One process-wide handle per device 0, created by the first call.
+ */
+JNIEXPORT jint JNICALL Java_com_microsoft_mgl_smithwaterman_MicrosoftSmithWaterman_alignBatchNative(
+    JNIEnv *env, jclass, jobject arena, jlong arenaBytes, jint n, jobject refOff, jobject refLen, jobject altOff, jobject altLen,
+    jint match, jint mismatch, jint gapOpen, jint gapExtend, jint overhangStrategy, jobject strategies,
+    jobject offsetsOut, jobject cigarStartOut, jobject cigarTextOut, jlong textCap)
+{
+    static mgl_sw_handle *handle = nullptr;
+    static std::mutex mu;
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        if (!handle) {
+            const int rc = mgl_sw_create(0, &handle);
+            if (rc != MGL_SW_OK) { handle = nullptr; return rc; }
+        }
+    }
+    if (n < 0 || arenaBytes < 0 || textCap < 0) return MGL_SW_E_INVALID;
+    mgl_sw_batch b;
+    b.n = n;
+    b.arena = (const uint8_t *)env->GetDirectBufferAddress(arena);
+    b.arena_bytes = (uint64_t)arenaBytes;
+    b.ref_off = (const uint64_t *)env->GetDirectBufferAddress(refOff);
+    b.ref_len = (const uint32_t *)env->GetDirectBufferAddress(refLen);
+    b.alt_off = (const uint64_t *)env->GetDirectBufferAddress(altOff);
+    b.alt_len = (const uint32_t *)env->GetDirectBufferAddress(altLen);
+    b.strategies = strategies ? (const int32_t *)env->GetDirectBufferAddress(strategies) : nullptr;
+    b.strategy = overhangStrategy;
+    b.match = match; b.mismatch = mismatch; b.gap_open = gapOpen; b.gap_extend = gapExtend;
+    mgl_sw_text_result r;
+    r.offsets = (int32_t *)env->GetDirectBufferAddress(offsetsOut);
+    r.text_start = (uint64_t *)env->GetDirectBufferAddress(cigarStartOut);
+    r.text = (char *)env->GetDirectBufferAddress(cigarTextOut);
+    r.text_cap = (uint64_t)textCap;
+    r.text_total = 0;
+    if (n > 0 && (!b.arena || !b.ref_off || !b.ref_len || !b.alt_off || !b.alt_len || !r.offsets || !r.text_start || (!r.text && textCap))) return MGL_SW_E_INVALID;
+    const int rc = mgl_sw_align_batch_text(handle, &b, &r, nullptr);
+    if (rc == MGL_SW_E_OPS_CAPACITY && r.text_start) r.text_start[n] = r.text_total;
+    return rc;
+}
 
 }  // extern "C"

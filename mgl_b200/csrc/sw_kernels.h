@@ -40,6 +40,11 @@ cudaError_t launch_scan_counts(const u32 *n_ops, u32 *starts, u32 *tile_sum, u32
 cudaError_t launch_compact(const u32 *scratch, const u64 *ops_end, const u32 *n_ops, const u32 *starts, const u32 *tile_off,
                            u32 *ops_out, u32 n, cudaStream_t stream);
 
+/* text CIGARs on the device: characters per pair, then (after launch_scan_counts over them) the characters themselves */
+cudaError_t launch_text_len(const u32 *scratch, const u64 *ops_end, const u32 *n_ops, u32 *n_chars, u32 n, cudaStream_t stream);
+cudaError_t launch_text_format(const u32 *scratch, const u64 *ops_end, const u32 *n_ops, const u32 *starts, const u32 *tile_off,
+                               char *text_out, u32 n, cudaStream_t stream);
+
 /* integer-pipe microbenchmarks (int_peak.cu): ops per second of one instruction mix */
 cudaError_t run_int_peak(int which, int device, double *ops_per_s, double *sm_mhz);
 int int_peak_count();

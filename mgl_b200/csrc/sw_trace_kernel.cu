@@ -149,4 +149,62 @@ cudaError_t launch_compact(const u32 *scratch, const u64 *ops_end, const u32 *n_
     return cudaGetLastError();
 }
 
+/*
+ * Text CIGARs on the device: what the reference builds with to_string(length) + state per
+ * element, elements of length <= 0 skipped (sw.cpp:251-252; the traceback never emits those).  Two passes over a
+ * pair's packed elements: count the characters, then (after the same scan that places packed elements) write them.
+ */
+__device__ __forceinline__ u32 dec_digits(u32 v)
+{
+    u32 d = 1;
+    while (v >= 10u) { v /= 10u; d++; }
+    return d;
+}
+
+__global__ void __launch_bounds__(256) sw_text_len_kernel(const u32 *__restrict__ scratch, const u64 *__restrict__ ops_end,
+                                                          const u32 *__restrict__ n_ops, u32 *__restrict__ n_chars, u32 n)
+{
+    const u32 p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    const u32 cnt = n_ops[p];
+    const u32 *src = scratch + (ops_end[p] - cnt);
+    u32 chars = 0;
+    for (u32 k = 0; k < cnt; k++) chars += dec_digits(src[k] >> 4) + 1u;
+    n_chars[p] = chars;
+}
+
+__global__ void __launch_bounds__(256) sw_text_format_kernel(const u32 *__restrict__ scratch, const u64 *__restrict__ ops_end,
+                                                             const u32 *__restrict__ n_ops, const u32 *__restrict__ starts,
+                                                             const u32 *__restrict__ tile_off, char *__restrict__ text_out, u32 n)
+{
+    const u32 p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    const u32 cnt = n_ops[p];
+    const u32 *src = scratch + (ops_end[p] - cnt);
+    char *dst = text_out + tile_off[p / SCAN_TILE] + starts[p];
+    for (u32 k = 0; k < cnt; k++) {
+        const u32 e = src[k];
+        u32 len = e >> 4;
+        const u32 d = dec_digits(len);
+        for (u32 q = d; q-- > 0;) { dst[q] = (char)('0' + len % 10u); len /= 10u; }
+        dst[d] = "MIDNSHP=X"[e & 15u];                        /* BAM numbering, as mgl_sw_format_cigar */
+        dst += d + 1u;
+    }
+}
+
+cudaError_t launch_text_len(const u32 *scratch, const u64 *ops_end, const u32 *n_ops, u32 *n_chars, u32 n, cudaStream_t stream)
+{
+    if (n == 0) return cudaSuccess;
+    sw_text_len_kernel<<<(n + 255) / 256, 256, 0, stream>>>(scratch, ops_end, n_ops, n_chars, n);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_text_format(const u32 *scratch, const u64 *ops_end, const u32 *n_ops, const u32 *starts, const u32 *tile_off,
+                               char *text_out, u32 n, cudaStream_t stream)
+{
+    if (n == 0) return cudaSuccess;
+    sw_text_format_kernel<<<(n + 255) / 256, 256, 0, stream>>>(scratch, ops_end, n_ops, starts, tile_off, text_out, n);
+    return cudaGetLastError();
+}
+
 }  // namespace mglsw

@@ -34,6 +34,11 @@ class Result(C.Structure):
                 ("ops_cap", C.c_uint64), ("ops_total", C.c_uint64)]
 
 
+class TextResult(C.Structure):
+    _fields_ = [("offsets", C.c_void_p), ("text_start", C.c_void_p), ("text", C.c_void_p),
+                ("text_cap", C.c_uint64), ("text_total", C.c_uint64)]
+
+
 class Stats(C.Structure):
     _fields_ = [(k, C.c_uint64) for k in ("cells", "pairs", "pairs_s16", "pairs_s32", "fill_launches", "other_launches",
                                           "chunks", "trace_bytes", "h2d_bytes", "d2h_bytes")] + \
@@ -60,6 +65,8 @@ def lib():
         L.mgl_sw_version.restype = C.c_char_p
         L.mgl_sw_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_int64]
         L.mgl_sw_align_batch.argtypes = [C.c_void_p, C.POINTER(Batch), C.POINTER(Result), C.POINTER(Stats)]
+        L.mgl_sw_align_batch_text.argtypes = [C.c_void_p, C.POINTER(Batch), C.POINTER(TextResult), C.POINTER(Stats)]
+        L.mgl_sw_align_batch_text.restype = C.c_int
         L.mgl_sw_score_batch.argtypes = [C.c_void_p, C.POINTER(Batch), C.c_void_p, C.POINTER(Stats)]
         L.mgl_sw_score_batch.restype = C.c_int
         L.mgl_sw_resident_prepare.argtypes = [C.c_void_p, C.POINTER(Batch)]

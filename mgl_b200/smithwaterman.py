@@ -158,6 +158,43 @@ class MicrosoftSmithWaterman:
         del keep
         return BatchResult(offsets, cigar_start, ops[: int(r.ops_total)], st.as_dict())
 
+    # -- text CIGARs formatted on the device --
+    def align_arrays_text(self, arena, ref_off, ref_len, alt_off, alt_len, parameters,
+                          overhang_strategy=SWOverhangStrategy.SOFTCLIP, strategies=None, text_cap: Optional[int] = None,
+                          out: Optional[Tuple[np.ndarray, np.ndarray, np.ndarray]] = None):
+        """(offsets, text_start, text bytes, stats): pair p's CIGAR is text[text_start[p]:text_start[p + 1]] -- the
+        characters alignNative writes to cigarBuffer (sw.cpp:251-252)."""
+        h = self._ensure()
+        b, keep = native.make_batch(arena, ref_off, ref_len, alt_off, alt_len, _params(parameters),
+                                    int(overhang_strategy), strategies)
+        n = int(b.n)
+        if out is None:
+            cap = int(text_cap) if text_cap is not None else max(64, 24 * n)
+            out = (np.zeros(n, dtype=np.int32), np.zeros(n + 1, dtype=np.uint64), np.zeros(cap, dtype=np.uint8))
+        offsets, text_start, text = out
+        st = native.Stats()
+        while True:
+            r = native.TextResult()
+            r.offsets, r.text_start, r.text = offsets.ctypes.data, text_start.ctypes.data, text.ctypes.data
+            r.text_cap = len(text)
+            rc = native.lib().mgl_sw_align_batch_text(h, C.byref(b), C.byref(r), C.byref(st))
+            if rc == native.E_OPS_CAPACITY:
+                text = np.zeros(int(r.text_total), dtype=np.uint8)
+                continue
+            if rc != native.OK:
+                raise self._err(rc)
+            break
+        del keep
+        return offsets, text_start, text[: int(r.text_total)], st.as_dict()
+
+    def align_batch_text(self, pairs: Sequence[Tuple[bytes, bytes]], parameters, overhang_strategy=SWOverhangStrategy.SOFTCLIP,
+                         strategies: Optional[Sequence[int]] = None):
+        """[(cigar text, offset), ...] in input order."""
+        arena, ref_off, ref_len, alt_off, alt_len = _pack_pairs(pairs)
+        offsets, start, text, _ = self.align_arrays_text(arena, ref_off, ref_len, alt_off, alt_len, parameters, overhang_strategy, strategies)
+        raw = text.tobytes()
+        return [(raw[int(start[p]): int(start[p + 1])].decode("ascii"), int(offsets[p])) for p in range(len(pairs))]
+
     # -- score only: no traceback (SURVEY.md 8f row 4) --
     def score_arrays(self, arena, ref_off, ref_len, alt_off, alt_len, parameters,
                      overhang_strategy=SWOverhangStrategy.SOFTCLIP, strategies=None, out: Optional[np.ndarray] = None):

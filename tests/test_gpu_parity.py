@@ -299,3 +299,64 @@ def test_score_only_matches_alignment_on_synthetic_config(sw):
             trail = int(ops[-1]) >> 4 if (int(ops[-1]) & 15) == 4 and strat == 1 and len(ops) > 1 else 0
             assert int(res.offsets[p]) + ref_used == int(sc[p, 1]), (config, p)
             assert alt_used - trail == int(sc[p, 2]), (config, p)
+
+
+def test_text_cigars_formatted_on_device(sw, oracle, golden):
+    """mgl_sw_align_batch_text: the characters alignNative writes (sw.cpp:251-252), formatted by the GPU, against the
+    oracle's text -- golden cases, long elements (4- and 5-digit lengths), a capacity retry"""
+    rng = random.Random(99)
+    pairs = [(c["ref"].encode("latin1"), c["alt"].encode("latin1")) for c in golden["cases"][:600]]
+    for tl, ql in ((1200, 1100), (12000, 25), (30, 11000), (2500, 2400)):
+        ref = bytes(rng.choice(b"ACGT") for _ in range(tl))
+        w = min(tl, ql)
+        alt = bytearray(ref[:w]) + bytearray(rng.choice(b"ACGT") for _ in range(ql - w))
+        pairs.append((ref, bytes(alt)))
+    for params in ((10, -15, -30, -5), (200, -150, -260, -11)):
+        strategies = np.array([(1, 2, 4, 8)[k % 4] for k in range(len(pairs))], dtype=np.int32)
+        got = sw.align_batch_text(pairs, params, 1, strategies)
+        bad = [(k, got[k], oracle.align(r, a, params, int(strategies[k]))) for k, (r, a) in enumerate(pairs)
+               if got[k] != oracle.align(r, a, params, int(strategies[k]))]
+        assert not bad, bad[:3]
+    # capacity: too small a text buffer reports what is needed and the retry succeeds
+    from mgl_b200.smithwaterman import _pack_pairs
+    arena, ro, rl, ao, al = _pack_pairs(pairs[:50])
+    offsets, start, text, _ = sw.align_arrays_text(arena, ro, rl, ao, al, (10, -15, -30, -5), 1, None, text_cap=8)
+    assert int(start[-1]) == len(text) > 8
+
+
+def test_jni_batch_symbol(sw, oracle):
+    """Java_..._alignBatchNative through a table-backed JNIEnv (GetDirectBufferAddress = identity): what a Java
+    alignBatch would receive, against the oracle"""
+    from mgl_b200 import native
+    from mgl_b200.smithwaterman import _pack_pairs
+    GETADDR = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_void_p)
+    ident = GETADDR(lambda env, buf: buf)
+    table = (C.c_void_p * 235)()
+    table[230] = C.cast(ident, C.c_void_p)
+    env = C.pointer(C.c_void_p(C.addressof(table)))
+    fn = native.lib().Java_com_microsoft_mgl_smithwaterman_MicrosoftSmithWaterman_alignBatchNative
+    fn.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int] + [C.c_void_p] * 4 + [C.c_int] * 5 + [C.c_void_p] * 4 + [C.c_int64]
+    fn.restype = C.c_int
+    rng = random.Random(31)
+    pairs = []
+    for _ in range(300):
+        ref = bytes(rng.choice(b"ACGT") for _ in range(rng.randint(20, 400)))
+        i = rng.randrange(len(ref) - 10)
+        alt = bytearray(ref[i: i + rng.randint(10, 150)])
+        for _ in range(rng.randint(0, 3)):
+            alt[rng.randrange(len(alt))] = rng.choice(b"ACGT")
+        pairs.append((ref, bytes(alt)))
+    arena, ro, rl, ao, al = _pack_pairs(pairs)
+    n = len(pairs)
+    strategies = np.array([(1, 2, 4, 8)[k % 4] for k in range(n)], dtype=np.int32)
+    offsets, start, text = np.zeros(n, np.int32), np.zeros(n + 1, np.uint64), np.zeros(64 * n, np.uint8)
+    rc = fn(env, None, arena.ctypes.data, arena.nbytes, n, ro.ctypes.data, rl.ctypes.data, ao.ctypes.data, al.ctypes.data,
+            10, -15, -30, -5, 1, strategies.ctypes.data, offsets.ctypes.data, start.ctypes.data, text.ctypes.data, text.nbytes)
+    assert rc == 0
+    raw = text.tobytes()
+    for k, (r, a) in enumerate(pairs):
+        assert (raw[int(start[k]): int(start[k + 1])].decode(), int(offsets[k])) == oracle.align(r, a, (10, -15, -30, -5), int(strategies[k])), k
+    # too small a text buffer: the code and the needed capacity
+    rc = fn(env, None, arena.ctypes.data, arena.nbytes, n, ro.ctypes.data, rl.ctypes.data, ao.ctypes.data, al.ctypes.data,
+            10, -15, -30, -5, 1, None, offsets.ctypes.data, start.ctypes.data, text.ctypes.data, 16)
+    assert rc == native.E_OPS_CAPACITY and int(start[n]) > 16
