@@ -22,6 +22,8 @@
 typedef int32_t jint;
 typedef int64_t jlong;
 typedef int8_t  jbyte;
+typedef uint8_t jboolean;
+typedef double  jdouble;
 
 #ifdef __cplusplus
 class _jobject {};
