@@ -1,0 +1,380 @@
+/*
+ * ph_engine.cu -- PairHMM on the B200: kernels, device buffers and the C-ABI of include/mgl_pairhmm.h.
+ *
+ * One warp per (read, haplotype) pair, running PhLane (ph_lane.h).  The job of the reference's JNI entry
+ * (...MicrosoftPairHmm.cc:77-222): float for every pair, the pairs whose float result is below MIN_ACCEPTED again in
+ * double, log10(result) - log10(INITIAL_CONSTANT) out.  Here that is two launches per precision shape with no host
+ * round trip between them: the float kernel writes the final value or appends the pair to a redo list (atomic
+ * counter), the double kernel is launched over the worst case and its warps beyond the counter leave at once.
+ *
+ * Rows per lane (RPL 1/2/4/8 = bands of 32/64/128/256 read rows) is picked per launch from the longest read, so a
+ * 101-base read runs RPL 4 in one band; longer reads go band by band through a carry row in shared memory.
+ * Roofline: FP32 (FP64 for the redo pass) FMA pipe -- 8 flops-instructions and 2 selects per cell, no O(cells)
+ * memory traffic at all (a pair reads readLen * 5 + hapLen bytes and writes 8).
+ */
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/mgl_pairhmm.h"
+#include "ph_lane.h"
+#include "ph_tables.h"
+
+namespace mglph {
+
+struct JobDev {
+    const uint8_t *reads, *haps;
+    const int64_t *read_off;      /* R + 1: byte offset of each read's five tracks */
+    const int64_t *hap_off;       /* H + 1 */
+    int R, H;
+};
+
+template <class N>
+struct KArgs {
+    JobDev job;
+    Tables<N> tb;
+    N log10_initial;
+    double *out;                  /* R * H */
+    unsigned int *redo;           /* float pass: pairs to recompute in double; double pass: the list to run (or NULL: all pairs) */
+    unsigned int *redo_count;
+    int carry_cols;               /* columns the shared-memory carry row of one warp holds */
+};
+
+template <class N> struct ShflT;
+template <> struct ShflT<float> { static __device__ __forceinline__ float up(float v) { return __shfl_up_sync(0xffffffffu, v, 1); } };
+template <> struct ShflT<double> { static __device__ __forceinline__ double up(double v) { return __shfl_up_sync(0xffffffffu, v, 1); } };
+
+/* FROM_LIST: warp w runs pair redo[w] if w < *redo_count (the double pass behind a float pass) */
+template <class N, int RPL, bool FROM_LIST, bool ESCALATE>
+__global__ void __launch_bounds__(128) ph_forward_kernel(const KArgs<N> a)
+{
+    extern __shared__ __align__(16) unsigned char s_raw[];
+    const int warp_in_block = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const unsigned int w = blockIdx.x * (blockDim.x >> 5) + warp_in_block;
+    const unsigned int n_pairs = (unsigned int)a.job.R * (unsigned int)a.job.H;
+    unsigned int p;
+    if (FROM_LIST) {
+        if (w >= *a.redo_count) return;
+        p = a.redo[w];
+    } else {
+        if (w >= n_pairs) return;
+        p = w;
+    }
+    const int r = (int)(p / (unsigned int)a.job.H), h = (int)(p % (unsigned int)a.job.H);
+    PairView pv;
+    pv.rl = (int)((a.job.read_off[r + 1] - a.job.read_off[r]) / 5);
+    pv.hl = (int)(a.job.hap_off[h + 1] - a.job.hap_off[h]);
+    pv.rs = a.job.reads + a.job.read_off[r];
+    pv.q = pv.rs + pv.rl; pv.ins = pv.q + pv.rl; pv.del = pv.ins + pv.rl; pv.gcp = pv.del + pv.rl;
+    pv.hap = a.job.haps + a.job.hap_off[h];
+
+    Top<N> *carry = reinterpret_cast<Top<N> *>(s_raw) + (size_t)warp_in_block * (a.carry_cols + 1);
+    const N y_initial = a.tb.initial / (N)pv.hl;                       /* compute_prob_scalar.cc:104 */
+    const int nb = ph_bands(pv.rl, RPL);
+    PhLane<N, RPL> L;
+    for (int b = 0; b < nb; b++) {
+        L.band_begin(a.tb, pv, b, lane, y_initial);
+        const bool park = b + 1 < nb;
+        for (int t = 0; t < pv.hl + 31; t++) {
+            Top<N> top;
+            top.m = ShflT<N>::up(L.bottom.m);
+            top.x = ShflT<N>::up(L.bottom.x);
+            top.y = ShflT<N>::up(L.bottom.y);
+            if (lane == 0) {
+                if (b == 0) { top.m = (N)0; top.x = (N)0; top.y = y_initial; }
+                else if (t + 1 <= pv.hl) top = carry[t + 1];
+            }
+            const bool active = L.step(pv, t, top);
+            if (park) {
+                if (active && lane == 31) carry[t - 31 + 1] = L.bottom;
+                __syncwarp();
+            }
+        }
+    }
+    const int ll = ph_last_lane(pv.rl, RPL);
+    if (lane == ll) {
+        const N res = L.result;
+        if (ESCALATE && (double)res < (double)MGLPH_MIN_ACCEPTED) {    /* ...MicrosoftPairHmm.cc:182 */
+            a.redo[atomicAdd(a.redo_count, 1u)] = p;
+        } else {
+            a.out[p] = log10((double)res) - (double)a.log10_initial;    /* .cc:188,206 */
+        }
+    }
+}
+
+template <class N, bool FROM_LIST, bool ESCALATE>
+static cudaError_t launch_forward(int rpl, unsigned int warps, size_t smem, const KArgs<N> &a, cudaStream_t st)
+{
+    if (warps == 0) return cudaSuccess;
+    const unsigned int blocks = (warps + 3) / 4;
+#define PH_LAUNCH(R_)                                                                                                   \
+    do {                                                                                                                \
+        if (smem > 48 * 1024) {                                                                                         \
+            cudaError_t e = cudaFuncSetAttribute(ph_forward_kernel<N, R_, FROM_LIST, ESCALATE>,                         \
+                                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);               \
+            if (e != cudaSuccess) return e;                                                                             \
+        }                                                                                                               \
+        ph_forward_kernel<N, R_, FROM_LIST, ESCALATE><<<blocks, 128, smem, st>>>(a);                                    \
+    } while (0)
+    switch (rpl) {
+    case 1: PH_LAUNCH(1); break;
+    case 2: PH_LAUNCH(2); break;
+    case 4: PH_LAUNCH(4); break;
+    default: PH_LAUNCH(8); break;
+    }
+#undef PH_LAUNCH
+    return cudaGetLastError();
+}
+
+struct Buf {
+    void *p = nullptr; size_t cap = 0;
+    cudaError_t reserve(size_t bytes)
+    {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        const size_t want = bytes + bytes / 4 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+class Engine {
+public:
+    explicit Engine(int device) : device_(device) {}
+    ~Engine()
+    {
+        cudaSetDevice(device_);
+        for (Buf *b : {&reads_, &haps_, &roff_, &hoff_, &out_, &redo_, &tab_}) b->release();
+        if (stream_) cudaStreamDestroy(stream_);
+        if (ev0_) cudaEventDestroy(ev0_);
+        if (ev1_) cudaEventDestroy(ev1_);
+    }
+    std::string err;
+    std::mutex mu;
+
+    int init()
+    {
+        cudaError_t e;
+        int n = 0;
+        if (cudaGetDeviceCount(&n) != cudaSuccess || device_ < 0 || device_ >= n) { err = "no such CUDA device"; return MGL_PH_E_NO_DEVICE; }
+        cudaDeviceProp prop;
+        if ((e = cudaGetDeviceProperties(&prop, device_)) != cudaSuccess) return cuda_fail(e, "device properties");
+        if (prop.major != 10) { err = "built for sm_100a (B200) only"; return MGL_PH_E_NO_DEVICE; }
+        if ((e = cudaSetDevice(device_)) != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
+        if ((e = cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking)) != cudaSuccess) return cuda_fail(e, "stream");
+        if ((e = cudaEventCreate(&ev0_)) != cudaSuccess || (e = cudaEventCreate(&ev1_)) != cudaSuccess) return cuda_fail(e, "event");
+        /* tables: float ph2pr | float mm | double ph2pr | double mm */
+        const HostTables<float> &tf = tables_f();
+        const HostTables<double> &td = tables_d();
+        const size_t fb = (128 + MGLPH_MM_ENTRIES) * sizeof(float), db = (128 + MGLPH_MM_ENTRIES) * sizeof(double);
+        const size_t foff = 0, doff = (fb + 255) / 256 * 256;
+        if ((e = tab_.reserve(doff + db)) != cudaSuccess) return cuda_fail(e, "cudaMalloc tables");
+        std::vector<unsigned char> host(doff + db, 0);
+        std::memcpy(host.data() + foff, tf.ph2pr.data(), 128 * sizeof(float));
+        std::memcpy(host.data() + foff + 128 * sizeof(float), tf.mm.data(), MGLPH_MM_ENTRIES * sizeof(float));
+        std::memcpy(host.data() + doff, td.ph2pr.data(), 128 * sizeof(double));
+        std::memcpy(host.data() + doff + 128 * sizeof(double), td.mm.data(), MGLPH_MM_ENTRIES * sizeof(double));
+        if ((e = cudaMemcpy(tab_.p, host.data(), host.size(), cudaMemcpyHostToDevice)) != cudaSuccess) return cuda_fail(e, "H2D tables");
+        tf_.ph2pr = (const float *)((unsigned char *)tab_.p + foff); tf_.mm = tf_.ph2pr + 128; tf_.initial = tf.initial;
+        td_.ph2pr = (const double *)((unsigned char *)tab_.p + doff); td_.mm = td_.ph2pr + 128; td_.initial = td.initial;
+        return MGL_PH_OK;
+    }
+
+    /* validate the three buffers, build the offset tables, upload */
+    int upload(const int32_t *lengths, const uint8_t *reads, const uint8_t *haps, mgl_pairhmm_stats &st)
+    {
+        if (!lengths) { err = "NULL lengths"; return MGL_PH_E_INVALID; }
+        const int32_t R = lengths[0];
+        if (R < 0) { err = "negative read count"; return MGL_PH_E_INVALID; }
+        const int32_t H = lengths[1 + R];
+        if (H < 0) { err = "negative haplotype count"; return MGL_PH_E_INVALID; }
+        if ((R > 0 && !reads) || (H > 0 && !haps)) { err = "NULL buffer"; return MGL_PH_E_INVALID; }
+        if ((uint64_t)R * (uint64_t)H > 0xfffffff0ull) { err = "more than 2^32 pairs in one call"; return MGL_PH_E_INVALID; }
+        std::vector<int64_t> ro((size_t)R + 1, 0), ho((size_t)H + 1, 0);
+        max_rl_ = 0; max_hl_ = 0;
+        uint64_t sum_rl = 0, sum_hl = 0;
+        for (int32_t r = 0; r < R; r++) {
+            const int32_t n = lengths[1 + r];
+            if (n <= 0) { err = "empty read"; return MGL_PH_E_INVALID; }
+            ro[(size_t)r + 1] = ro[(size_t)r] + 5ll * n;
+            max_rl_ = n > max_rl_ ? n : max_rl_;
+            sum_rl += (uint64_t)n;
+        }
+        for (int32_t h = 0; h < H; h++) {
+            const int32_t n = lengths[2 + R + h];
+            if (n <= 0) { err = "empty haplotype"; return MGL_PH_E_INVALID; }
+            ho[(size_t)h + 1] = ho[(size_t)h] + n;
+            max_hl_ = n > max_hl_ ? n : max_hl_;
+            sum_hl += (uint64_t)n;
+        }
+        R_ = R; H_ = H;
+        cells_ = sum_rl * sum_hl;
+        cudaError_t e;
+        if ((e = cudaSetDevice(device_)) != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
+        const size_t np = (size_t)R * (size_t)H;
+        if ((e = reads_.reserve((size_t)ro[(size_t)R] + 16)) != cudaSuccess || (e = haps_.reserve((size_t)ho[(size_t)H] + 16)) != cudaSuccess ||
+            (e = roff_.reserve(ro.size() * 8)) != cudaSuccess || (e = hoff_.reserve(ho.size() * 8)) != cudaSuccess ||
+            (e = out_.reserve(np * 8 + 8)) != cudaSuccess || (e = redo_.reserve(np * 4 + 16)) != cudaSuccess)
+            return cuda_fail(e, "cudaMalloc");
+        if (np == 0) return MGL_PH_OK;
+        if ((e = cudaMemcpyAsync(reads_.p, reads, (size_t)ro[(size_t)R], cudaMemcpyHostToDevice, stream_)) != cudaSuccess ||
+            (e = cudaMemcpyAsync(haps_.p, haps, (size_t)ho[(size_t)H], cudaMemcpyHostToDevice, stream_)) != cudaSuccess ||
+            (e = cudaMemcpyAsync(roff_.p, ro.data(), ro.size() * 8, cudaMemcpyHostToDevice, stream_)) != cudaSuccess ||
+            (e = cudaMemcpyAsync(hoff_.p, ho.data(), ho.size() * 8, cudaMemcpyHostToDevice, stream_)) != cudaSuccess)
+            return cuda_fail(e, "H2D");
+        if ((e = cudaStreamSynchronize(stream_)) != cudaSuccess) return cuda_fail(e, "H2D");   /* ro / ho are locals */
+        st.h2d_bytes += (uint64_t)ro[(size_t)R] + (uint64_t)ho[(size_t)H] + (ro.size() + ho.size()) * 8;
+        return MGL_PH_OK;
+    }
+
+    /* the kernels of one job on stream_, bracketed by events */
+    int run(int use_double, mgl_pairhmm_stats &st)
+    {
+        const size_t np = (size_t)R_ * (size_t)H_;
+        st.pairs += np; st.cells += cells_;
+        if (np == 0) return MGL_PH_OK;
+        cudaError_t e;
+        if ((e = cudaSetDevice(device_)) != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
+        const int rpl = max_rl_ <= 32 ? 1 : max_rl_ <= 64 ? 2 : max_rl_ <= 128 ? 4 : 8;
+        const bool multi = max_rl_ > 32 * rpl;
+        JobDev job;
+        job.reads = (const uint8_t *)reads_.p; job.haps = (const uint8_t *)haps_.p;
+        job.read_off = (const int64_t *)roff_.p; job.hap_off = (const int64_t *)hoff_.p;
+        job.R = R_; job.H = H_;
+        unsigned int *redo_count = (unsigned int *)redo_.p, *redo = redo_count + 4;
+        const int carry_cols = multi ? max_hl_ + 1 : 0;
+        const size_t smem_f = 4 * (size_t)(carry_cols + 1) * sizeof(Top<float>), smem_d = 4 * (size_t)(carry_cols + 1) * sizeof(Top<double>);
+        if (smem_d > 220 * 1024) { err = "haplotype of " + std::to_string(max_hl_) + " bases with reads longer than 256: carry row exceeds shared memory"; return MGL_PH_E_TOO_LONG; }
+        KArgs<float> af;
+        af.job = job; af.tb = tf_; af.log10_initial = tables_f().log10_initial; af.out = (double *)out_.p;
+        af.redo = redo; af.redo_count = redo_count; af.carry_cols = carry_cols;
+        KArgs<double> ad;
+        ad.job = job; ad.tb = td_; ad.log10_initial = tables_d().log10_initial; ad.out = (double *)out_.p;
+        ad.redo = redo; ad.redo_count = redo_count; ad.carry_cols = carry_cols;
+        if ((e = cudaEventRecord(ev0_, stream_)) != cudaSuccess) return cuda_fail(e, "event record");
+        if (use_double) {
+            if ((e = launch_forward<double, false, false>(rpl, (unsigned int)np, smem_d, ad, stream_)) != cudaSuccess) return cuda_fail(e, "double launch");
+            st.launches += 1; st.pairs_double += np;
+        } else {
+            if ((e = cudaMemsetAsync(redo_count, 0, 16, stream_)) != cudaSuccess) return cuda_fail(e, "memset");
+            if ((e = launch_forward<float, false, true>(rpl, (unsigned int)np, smem_f, af, stream_)) != cudaSuccess) return cuda_fail(e, "float launch");
+            if ((e = launch_forward<double, true, false>(rpl, (unsigned int)np, smem_d, ad, stream_)) != cudaSuccess) return cuda_fail(e, "double launch");
+            st.launches += 2;
+        }
+        if ((e = cudaEventRecord(ev1_, stream_)) != cudaSuccess) return cuda_fail(e, "event record");
+        return MGL_PH_OK;
+    }
+
+    int fetch(double *out, int use_double, mgl_pairhmm_stats &st)
+    {
+        const size_t np = (size_t)R_ * (size_t)H_;
+        if (np == 0) return MGL_PH_OK;
+        cudaError_t e;
+        unsigned int count = 0;
+        if (out && (e = cudaMemcpyAsync(out, out_.p, np * 8, cudaMemcpyDeviceToHost, stream_)) != cudaSuccess) return cuda_fail(e, "D2H");
+        if (!use_double && (e = cudaMemcpyAsync(&count, redo_.p, 4, cudaMemcpyDeviceToHost, stream_)) != cudaSuccess) return cuda_fail(e, "D2H");
+        if ((e = cudaStreamSynchronize(stream_)) != cudaSuccess) return cuda_fail(e, "kernel execution");
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, ev0_, ev1_) == cudaSuccess) st.device_ms += ms;
+        if (!use_double) st.pairs_double += count;
+        if (out) st.d2h_bytes += np * 8;
+        return MGL_PH_OK;
+    }
+
+    int cuda_fail(cudaError_t e, const char *what)
+    {
+        err = std::string(what) + ": " + cudaGetErrorString(e);
+        cudaGetLastError();
+        return MGL_PH_E_CUDA;
+    }
+
+private:
+    int device_;
+    cudaStream_t stream_ = nullptr;
+    cudaEvent_t ev0_ = nullptr, ev1_ = nullptr;
+    Buf reads_, haps_, roff_, hoff_, out_, redo_, tab_;
+    Tables<float> tf_{};
+    Tables<double> td_{};
+    int R_ = 0, H_ = 0, max_rl_ = 0, max_hl_ = 0;
+    uint64_t cells_ = 0;
+};
+
+}  // namespace mglph
+
+struct mgl_pairhmm_handle { mglph::Engine *engine; };
+
+extern "C" {
+
+int mgl_pairhmm_create(int device, mgl_pairhmm_handle **out)
+{
+    if (!out) return MGL_PH_E_INVALID;
+    *out = nullptr;
+    mglph::Engine *e = new mglph::Engine(device);
+    const int rc = e->init();
+    if (rc != MGL_PH_OK) { std::fprintf(stderr, "mgl_pairhmm: %s\n", e->err.c_str()); delete e; return rc; }
+    *out = new mgl_pairhmm_handle{e};
+    return MGL_PH_OK;
+}
+
+void mgl_pairhmm_destroy(mgl_pairhmm_handle *h)
+{
+    if (!h) return;
+    delete h->engine;
+    delete h;
+}
+
+const char *mgl_pairhmm_last_error(mgl_pairhmm_handle *h) { return h ? h->engine->err.c_str() : "NULL handle"; }
+
+int mgl_pairhmm_compute(mgl_pairhmm_handle *h, const int32_t *lengths, const uint8_t *reads, const uint8_t *haps,
+                        int use_double, double *out, mgl_pairhmm_stats *stats)
+{
+    if (!h || !out) return MGL_PH_E_INVALID;
+    mgl_pairhmm_stats st;
+    std::memset(&st, 0, sizeof st);
+    std::lock_guard<std::mutex> lk(h->engine->mu);
+    int rc = h->engine->upload(lengths, reads, haps, st);
+    if (rc == MGL_PH_OK) rc = h->engine->run(use_double, st);
+    if (rc == MGL_PH_OK) rc = h->engine->fetch(out, use_double, st);
+    if (stats) *stats = st;
+    return rc;
+}
+
+int mgl_pairhmm_resident_prepare(mgl_pairhmm_handle *h, const int32_t *lengths, const uint8_t *reads, const uint8_t *haps)
+{
+    if (!h) return MGL_PH_E_INVALID;
+    mgl_pairhmm_stats st;
+    std::memset(&st, 0, sizeof st);
+    std::lock_guard<std::mutex> lk(h->engine->mu);
+    return h->engine->upload(lengths, reads, haps, st);
+}
+
+int mgl_pairhmm_resident_run(mgl_pairhmm_handle *h, int use_double, mgl_pairhmm_stats *stats)
+{
+    if (!h) return MGL_PH_E_INVALID;
+    mgl_pairhmm_stats st;
+    std::memset(&st, 0, sizeof st);
+    std::lock_guard<std::mutex> lk(h->engine->mu);
+    int rc = h->engine->run(use_double, st);
+    if (rc == MGL_PH_OK) rc = h->engine->fetch(nullptr, use_double, st);
+    if (stats) *stats = st;
+    return rc;
+}
+
+int mgl_pairhmm_resident_fetch(mgl_pairhmm_handle *h, double *out)
+{
+    if (!h || !out) return MGL_PH_E_INVALID;
+    mgl_pairhmm_stats st;
+    std::memset(&st, 0, sizeof st);
+    std::lock_guard<std::mutex> lk(h->engine->mu);
+    return h->engine->fetch(out, 1, st);
+}
+
+}  // extern "C"

@@ -1,0 +1,144 @@
+/*
+ * ph_lane.h -- the PairHMM forward algorithm, one lane's view.
+ *
+ * Replaces the reference's inner loops (compute_full_prob_core_1X, compute_prob_scalar.cc:5-44, and the AVX2
+ * bands of compute_prob_avx{f,d}.cc) for one (read, haplotype) pair.  A warp takes a band of 32 * RPL read rows:
+ * lane l owns rows l*RPL .. l*RPL + RPL - 1 of the band and sweeps the haplotype columns one per step, one column
+ * behind lane l - 1, so at step t it is at column t - l + 1.  Everything that is constant along a row (the five
+ * transition probabilities of compute_prob_scalar.cc:73-81 and the two emission values :25-34) sits in the lane's
+ * registers for the whole band; per step a lane receives (M, X, Y) of the row above its first row from lane l - 1
+ * (one shuffle each) and keeps the previous column of its own rows.  Reads longer than one band go band by band:
+ * the last lane parks its bottom row in a carry row (shared memory on the device) that lane 0 reads back in the
+ * next band -- the same hand-over the reference's AVX bands do through pRow0/pRow1 (compute_prob_avxf.cc:670-672).
+ *
+ *   M[r][c] = distm * (M[r-1][c-1] * pMM[r] + (X[r-1][c-1] + Y[r-1][c-1]) * pGapM[r])      compute_prob_scalar.cc:39
+ *   Y[r][c] = M[r][c-1] * pMY[r] + Y[r][c-1] * pZZ[r]                                      :41
+ *   X[r][c] = M[r-1][c] * pMX[r] + X[r-1][c] * pZZ[r]                                      :43
+ *   row 0: M = X = 0, Y = INITIAL_CONSTANT / hapLen (:104,119-125); column 0 of rows >= 1: all 0 (:140-142)
+ *   result = sum over columns 1..hapLen of M[readLen][c] + X[readLen][c], left to right (:213,310)
+ *
+ * PhLane is PH_HD: ph_kernel.cu drives 32 of them in a warp with __shfl_up_sync; tests/emu/ph_emu.cpp drives 32 of
+ * them in a loop on the CPU.
+ */
+#ifndef MGL_B200_PH_LANE_H
+#define MGL_B200_PH_LANE_H
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define PH_HD __host__ __device__ __forceinline__
+#else
+#define PH_HD inline
+#endif
+
+namespace mglph {
+
+/* quality tables in the reference's arithmetic (built on the host by ph_tables.cpp from Context.h) */
+template <class N>
+struct Tables {
+    const N *ph2pr;       /* 128 entries: 10^(-q/10)                                   (Context.h:101,137)  */
+    const N *mm;          /* matchToMatchProb, triangular, qualities 0..127            (Context.h:47-58)    */
+    N initial;            /* INITIAL_CONSTANT: 2^120 float, 2^1020 double              (Context.h:105,141)  */
+};
+
+struct PairView {
+    const uint8_t *rs, *q, *ins, *del, *gcp;   /* the read's five tracks                                    */
+    const uint8_t *hap;
+    int rl, hl;
+};
+
+template <class N>
+struct Top { N m, x, y; };
+
+template <class N, int RPL>
+struct PhLane {
+    N pMM[RPL], pGapM[RPL], pMX[RPL], pMY[RPL], pZZ[RPL];
+    N dmatch[RPL], dmis[RPL];
+    unsigned base[RPL];              /* the read base of each row (a byte array would live in local memory) */
+    N Mp[RPL], Xp[RPL], Yp[RPL];    /* previous column of my rows                                           */
+    Top<N> tprev;                   /* the row above my first row, at my previous column                    */
+    Top<N> bottom;                  /* my last row at the column I computed last: what lane l + 1 receives  */
+    N result;
+    int lane;
+    bool last;                      /* my bottom row is the read's last row (in this band)                   */
+
+    /*
+     * Rows [band * 32 * RPL + lane * RPL - pad, + RPL) of the read, pad = ph_pad(rl, RPL): the read is pushed down
+     * by `pad` rows so that its LAST row is always some lane's bottom row (the sum over the last row then needs no
+     * indexed access to the row registers, which would put them in local memory).  The pad rows above the read
+     * behave as DP row 0: M = X = 0 and Y = yInitial in every column.
+     */
+    PH_HD void band_begin(const Tables<N> &tb, const PairView &pv, int band, int lane_, N y_initial)
+    {
+        lane = lane_;
+        const int pad = (RPL - pv.rl % RPL) % RPL;
+        last = band * 32 * RPL + lane * RPL + (RPL - 1) - pad == pv.rl - 1;
+        const N one = (N)1.0, three = (N)3.0;
+#pragma unroll
+        for (int k = 0; k < RPL; k++) {
+            const int row = band * 32 * RPL + lane * RPL + k - pad;    /* 0-based index into the read */
+            Mp[k] = Xp[k] = Yp[k] = (N)0;                              /* column 0 of rows >= 1 */
+            if (row < 0) {                                             /* a copy of DP row 0: Y carries yInitial along, M and X stay 0 */
+                pMM[k] = pGapM[k] = pMX[k] = pMY[k] = dmatch[k] = dmis[k] = (N)0;
+                pZZ[k] = one;
+                base[k] = 0;
+                Yp[k] = y_initial;
+            } else if (row < pv.rl) {
+                const int qi = pv.ins[row] & 127, qd = pv.del[row] & 127, qc = pv.gcp[row] & 127;
+                const int lo = qi <= qd ? qi : qd, hi = qi <= qd ? qd : qi;   /* Context.h:118-128 */
+                pMM[k] = tb.mm[((hi * (hi + 1)) >> 1) + lo];
+                pGapM[k] = one - tb.ph2pr[qc];
+                pMX[k] = tb.ph2pr[qi];
+                pMY[k] = tb.ph2pr[qd];
+                pZZ[k] = tb.ph2pr[qc];
+                const N dq = tb.ph2pr[pv.q[row] & 127];
+                dmatch[k] = one - dq;
+                dmis[k] = dq * (one / three);                          /* distm * threeOver, compute_prob_scalar.cc:16,33 */
+                base[k] = pv.rs[row];
+            } else {                                                   /* below the read: computes zeros nobody uses */
+                pMM[k] = pGapM[k] = pMX[k] = pMY[k] = pZZ[k] = dmatch[k] = dmis[k] = (N)0;
+                base[k] = 0;
+            }
+        }
+        /* the row above my first row at column 0: DP row 0 (Y = yInitial) only for lane 0 of band 0 */
+        tprev.m = (N)0; tprev.x = (N)0;
+        tprev.y = (band == 0 && lane == 0) ? y_initial : (N)0;
+        bottom.m = bottom.x = bottom.y = (N)0;
+        if (band == 0) result = (N)0;
+    }
+
+    /*
+     * One step: my column is c = t - lane + 1; `top` is the row above my first row at column c (from lane l - 1's
+     * `bottom`, or for lane 0 DP row 0 / the carry row).  Returns true if the column was inside 1..hl.
+     */
+    PH_HD bool step(const PairView &pv, int t, const Top<N> &top)
+    {
+        const int c = t - lane + 1;
+        if (c < 1 || c > pv.hl) return false;
+        const uint8_t hb = pv.hap[c - 1];
+        N dM = tprev.m, dX = tprev.x, dY = tprev.y;
+        N uM = top.m, uX = top.x;
+#pragma unroll
+        for (int k = 0; k < RPL; k++) {
+            const bool match = (base[k] == (unsigned)hb) | (base[k] == (unsigned)'N') | (hb == 'N');       /* compute_prob_scalar.cc:25 */
+            const N distm = match ? dmatch[k] : dmis[k];
+            const N Mn = distm * (dM * pMM[k] + (dX + dY) * pGapM[k]);
+            const N Yn = Mp[k] * pMY[k] + Yp[k] * pZZ[k];
+            const N Xn = uM * pMX[k] + uX * pZZ[k];
+            dM = Mp[k]; dX = Xp[k]; dY = Yp[k];
+            uM = Mn; uX = Xn;
+            Mp[k] = Mn; Xp[k] = Xn; Yp[k] = Yn;
+        }
+        tprev = top;
+        bottom.m = Mp[RPL - 1]; bottom.x = Xp[RPL - 1]; bottom.y = Yp[RPL - 1];
+        if (last) result += bottom.m + bottom.x;
+        return true;
+    }
+};
+
+/* rows the read is pushed down by, bands it then needs, and the lane whose bottom row is its last row */
+PH_HD int ph_pad(int rl, int rpl) { return (rpl - rl % rpl) % rpl; }
+PH_HD int ph_bands(int rl, int rpl) { return (rl + ph_pad(rl, rpl) + 32 * rpl - 1) / (32 * rpl); }
+PH_HD int ph_last_lane(int rl, int rpl) { return ((rl + ph_pad(rl, rpl) - 1) % (32 * rpl)) / rpl; }
+
+}  // namespace mglph
+#endif

@@ -72,3 +72,30 @@ def emu_align(pairs, params, strategies, allow_s16=True):
         text = "".join(f"{int(o) >> 4}{OPS[int(o) & 15]}" for o in ops[p, : n_ops[p]])
         out.append((text, int(offsets[p])))
     return out, dict(launches=int(stats[0]), s16=int(stats[1]), s32=int(stats[2]), units=int(stats[3]), builds=int(stats[4]), hops=int(stats[5]))
+
+
+# ---- PairHMM lane code (mgl_b200/csrc/ph_lane.h) on the CPU
+PH_EMU_SO = os.path.join(HERE, "emu", "libph_emu.so")
+_ph_lib = None
+
+
+def build_ph_emu(force=False):
+    srcs = [os.path.join(HERE, "emu", "ph_emu.cpp"), os.path.join(CSRC, "ph_tables.cpp")]
+    deps = srcs + [os.path.join(CSRC, "ph_lane.h"), os.path.join(CSRC, "ph_tables.h")]
+    if force or not os.path.exists(PH_EMU_SO) or any(os.path.getmtime(d) > os.path.getmtime(PH_EMU_SO) for d in deps):
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-ffp-contract=off", "-shared", "-fPIC", "-o", PH_EMU_SO] + srcs)
+    return PH_EMU_SO
+
+
+def ph_emu(reads, haps, use_double=False, rpl=4):
+    """log10 likelihoods [n_reads, n_haps] from the emulated warp (rows per lane = rpl)"""
+    global _ph_lib
+    from oracle import pairhmm_oracle as P
+    if _ph_lib is None:
+        _ph_lib = C.CDLL(build_ph_emu())
+        _ph_lib.ph_emu.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        _ph_lib.ph_emu.restype = C.c_int
+    lengths, rb, hb = P.pack(reads, haps)
+    out = np.zeros((len(reads), len(haps)), dtype=np.float64)
+    _ph_lib.ph_emu(lengths.ctypes.data, rb.ctypes.data, hb.ctypes.data, int(use_double), int(rpl), out.ctypes.data)
+    return out

@@ -73,3 +73,22 @@ def test_no_cpu_fallback_without_a_gpu(lib):
         sw.align(b"ACGT", b"ACGT", (10, -15, -30, -5), 1)
     with pytest.raises(native.MglSwError):
         mgl_b200.align_one_text(b"ACGT", b"ACGT", (10, -15, -30, -5), 1)
+
+
+def test_pairhmm_library_exports_every_declared_symbol():
+    import __graft_entry__ as g
+    from mgl_b200 import pairhmm
+    if not os.path.exists(pairhmm.LIB_PATH):
+        g.build()
+    L = pairhmm.lib()
+    hdr = open(os.path.join(ROOT, "include", "mgl_pairhmm.h")).read()
+    names = re.findall(r"MGL_PH_API\s+[\w\s\*]+?\b(mgl_pairhmm_\w+)\s*\(", hdr)
+    assert len(names) >= 7
+    for n in names:
+        assert hasattr(L, n), n
+    for n in ("initNative", "computeLikelihoodsNative", "doneNative"):     # ...MicrosoftPairHmm.h:15,23,31
+        assert hasattr(L, "Java_com_microsoft_mgl_pairhmm_MicrosoftPairHmm_" + n)
+    h = C.c_void_p()
+    import ctypes
+    if ctypes.CDLL(None) and L.mgl_pairhmm_create(0, C.byref(h)) != 0:
+        assert pairhmm.MicrosoftPairHmm().load() is False        # no GPU: no fallback, load() reports it

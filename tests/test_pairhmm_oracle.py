@@ -77,3 +77,22 @@ def test_oracle_vs_live_reference(ph):
         ref = ph.ref_likelihoods(reads, haps, use_double)
         ok = np.isfinite(ref)
         assert ok.mean() > 0.9 and np.all(np.abs(got - ref)[ok] <= TOL)
+
+
+@pytest.mark.parametrize("rpl", [1, 2, 4, 8])
+def test_lane_code_through_warp_emulator(ph, ph_golden, rpl):
+    """the PhLane code the CUDA kernel compiles (ph_lane.h), run by a lock-step CPU emulation of a warp with every
+    rows-per-lane shape (bands of 32/64/128/256 rows: reads of 1..260 bases cross the band boundary), against the
+    reference-generated vectors"""
+    import emu_util
+    for c in ph_golden["file"][::8]:
+        got = emu_util.ph_emu([_read(c["read"])], [c["hap"].encode("latin1")], False, rpl)[0, 0]
+        assert abs(got - c["expected_file"]) <= TOL
+    for b in ph_golden["batch"][:4]:
+        reads = [_read(r) for r in b["reads"]]
+        haps = [h.encode("latin1") for h in b["haps"]]
+        keep = np.array(b["finite"], dtype=bool)
+        for use_double, key in ((False, "ref_float"), (True, "ref_double")):
+            got = emu_util.ph_emu(reads, haps, use_double, rpl)
+            exp = np.array([[v if v is not None else np.nan for v in row] for row in b[key]])
+            assert np.all(np.abs(got - exp)[keep] <= TOL), (rpl, key, float(np.nanmax(np.abs(got - exp)[keep])))
