@@ -80,7 +80,10 @@ __global__ void __launch_bounds__(128) ph_forward_kernel(const KArgs<N> a)
     for (int b = 0; b < nb; b++) {
         L.band_begin(a.tb, pv, b, lane, y_initial);
         const bool park = b + 1 < nb;
+        unsigned hb_next = ph_hap_byte(pv, 0, lane);
         for (int t = 0; t < pv.hl + 31; t++) {
+            const unsigned hb = hb_next;
+            hb_next = ph_hap_byte(pv, t + 1, lane);
             Top<N> top;
             top.m = ShflT<N>::up(L.bottom.m);
             top.x = ShflT<N>::up(L.bottom.x);
@@ -89,7 +92,7 @@ __global__ void __launch_bounds__(128) ph_forward_kernel(const KArgs<N> a)
                 if (b == 0) { top.m = (N)0; top.x = (N)0; top.y = y_initial; }
                 else if (t + 1 <= pv.hl) top = carry[t + 1];
             }
-            const bool active = L.step(pv, t, top);
+            const bool active = L.step(pv, t, top, hb);
             if (park) {
                 if (active && lane == 31) carry[t - 31 + 1] = L.bottom;
                 __syncwarp();
@@ -124,7 +127,10 @@ static cudaError_t launch_forward(int rpl, unsigned int warps, size_t smem, cons
     switch (rpl) {
     case 1: PH_LAUNCH(1); break;
     case 2: PH_LAUNCH(2); break;
+    case 3: PH_LAUNCH(3); break;
     case 4: PH_LAUNCH(4); break;
+    case 5: PH_LAUNCH(5); break;
+    case 6: PH_LAUNCH(6); break;
     default: PH_LAUNCH(8); break;
     }
 #undef PH_LAUNCH
@@ -243,7 +249,9 @@ public:
         if (np == 0) return MGL_PH_OK;
         cudaError_t e;
         if ((e = cudaSetDevice(device_)) != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
-        const int rpl = max_rl_ <= 32 ? 1 : max_rl_ <= 64 ? 2 : max_rl_ <= 128 ? 4 : 8;
+        /* rows per lane: the longest read in one band when it has <= 256 rows (a 150-base read: 5 rows on each of 30 lanes) */
+        int rpl = (max_rl_ + 31) / 32;
+        if (rpl == 7 || rpl > 8) rpl = 8;
         const bool multi = max_rl_ > 32 * rpl;
         JobDev job;
         job.reads = (const uint8_t *)reads_.p; job.haps = (const uint8_t *)haps_.p;

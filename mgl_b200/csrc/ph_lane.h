@@ -108,18 +108,18 @@ struct PhLane {
 
     /*
      * One step: my column is c = t - lane + 1; `top` is the row above my first row at column c (from lane l - 1's
-     * `bottom`, or for lane 0 DP row 0 / the carry row).  Returns true if the column was inside 1..hl.
+     * `bottom`, or for lane 0 DP row 0 / the carry row); hb = hap_byte(pv, t), fetched by the caller a step ahead so
+     * that the load is not on the step's critical path.  Returns true if the column was inside 1..hl.
      */
-    PH_HD bool step(const PairView &pv, int t, const Top<N> &top)
+    PH_HD bool step(const PairView &pv, int t, const Top<N> &top, unsigned hb)
     {
         const int c = t - lane + 1;
         if (c < 1 || c > pv.hl) return false;
-        const uint8_t hb = pv.hap[c - 1];
         N dM = tprev.m, dX = tprev.x, dY = tprev.y;
         N uM = top.m, uX = top.x;
 #pragma unroll
         for (int k = 0; k < RPL; k++) {
-            const bool match = (base[k] == (unsigned)hb) | (base[k] == (unsigned)'N') | (hb == 'N');       /* compute_prob_scalar.cc:25 */
+            const bool match = (base[k] == hb) | (base[k] == (unsigned)'N') | (hb == (unsigned)'N');       /* compute_prob_scalar.cc:25 */
             const N distm = match ? dmatch[k] : dmis[k];
             const N Mn = distm * (dM * pMM[k] + (dX + dY) * pGapM[k]);
             const N Yn = Mp[k] * pMY[k] + Yp[k] * pZZ[k];
@@ -134,6 +134,13 @@ struct PhLane {
         return true;
     }
 };
+
+/* the haplotype base lane `lane` meets at step t (any byte outside the haplotype: the step is skipped there) */
+PH_HD unsigned ph_hap_byte(const PairView &pv, int t, int lane)
+{
+    const int c = t - lane + 1;
+    return (c >= 1 && c <= pv.hl) ? (unsigned)pv.hap[c - 1] : 0u;
+}
 
 /* rows the read is pushed down by, bands it then needs, and the lane whose bottom row is its last row */
 PH_HD int ph_pad(int rl, int rpl) { return (rpl - rl % rpl) % rpl; }

@@ -32,7 +32,7 @@ static N run_pair(const Tables<N> &tb, const PairView &pv)
                     if (b == 0) { top.m = (N)0; top.x = (N)0; top.y = y_initial; }
                     else if (c <= pv.hl) top = carry[(size_t)c];
                 }
-                const bool active = L[(size_t)l].step(pv, t, top);
+                const bool active = L[(size_t)l].step(pv, t, top, ph_hap_byte(pv, t, l));
                 if (active && l == 31 && b + 1 < nb) carry[(size_t)(t - 31 + 1)] = L[(size_t)l].bottom;
             }
         }
@@ -48,7 +48,10 @@ static N run_any(const Tables<N> &tb, const PairView &pv, int rpl)
     switch (rpl) {
     case 1: return run_pair<N, 1>(tb, pv);
     case 2: return run_pair<N, 2>(tb, pv);
+    case 3: return run_pair<N, 3>(tb, pv);
     case 4: return run_pair<N, 4>(tb, pv);
+    case 5: return run_pair<N, 5>(tb, pv);
+    case 6: return run_pair<N, 6>(tb, pv);
     default: return run_pair<N, 8>(tb, pv);
     }
 }

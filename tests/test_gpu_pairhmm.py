@@ -79,9 +79,9 @@ def test_reference_generated_batches(hmm, ph_golden):
     assert n > 1000 and redone > 100        # the float -> double escalation ran on the device
 
 
-@pytest.mark.parametrize("max_read", [30, 60, 120, 250, 700])
+@pytest.mark.parametrize("max_read", [30, 60, 90, 120, 150, 190, 250, 700])
 def test_against_oracle_every_band_shape(hmm, oracle_ph, max_read):
-    """rows per lane 1/2/4/8 are picked from the longest read; 700-base reads take three bands through the
+    """rows per lane 1..6 or 8 are picked from the longest read; 700-base reads take three bands through the
     shared-memory carry row; reads of one base, haplotypes of one base, 'N' on both sides"""
     rng = random.Random(max_read)
     haps = [bytes(rng.choice(b"ACGTN") for _ in range(n)) for n in (1, 2, 9, 33, 150, 320, 511)]
