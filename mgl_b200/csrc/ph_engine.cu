@@ -71,7 +71,7 @@ __global__ void __launch_bounds__(128) ph_forward_kernel(const KArgs<N> a)
     pv.hl = (int)(a.job.hap_off[h + 1] - a.job.hap_off[h]);
     pv.rs = a.job.reads + a.job.read_off[r];
     pv.q = pv.rs + pv.rl; pv.ins = pv.q + pv.rl; pv.del = pv.ins + pv.rl; pv.gcp = pv.del + pv.rl;
-    pv.hap = a.job.haps + a.job.hap_off[h];
+    pv.hap = a.job.haps + MGLPH_HAP_PAD + a.job.hap_off[h];
 
     Top<N> *carry = reinterpret_cast<Top<N> *>(s_raw) + (size_t)warp_in_block * (a.carry_cols + 1);
     const N y_initial = a.tb.initial / (N)pv.hl;                       /* compute_prob_scalar.cc:104 */
@@ -81,6 +81,7 @@ __global__ void __launch_bounds__(128) ph_forward_kernel(const KArgs<N> a)
         L.band_begin(a.tb, pv, b, lane, y_initial);
         const bool park = b + 1 < nb;
         unsigned hb_next = ph_hap_byte(pv, 0, lane);
+#pragma unroll 2
         for (int t = 0; t < pv.hl + 31; t++) {
             const unsigned hb = hb_next;
             hb_next = ph_hap_byte(pv, t + 1, lane);
@@ -226,13 +227,13 @@ public:
         cudaError_t e;
         if ((e = cudaSetDevice(device_)) != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
         const size_t np = (size_t)R * (size_t)H;
-        if ((e = reads_.reserve((size_t)ro[(size_t)R] + 16)) != cudaSuccess || (e = haps_.reserve((size_t)ho[(size_t)H] + 16)) != cudaSuccess ||
+        if ((e = reads_.reserve((size_t)ro[(size_t)R] + 16)) != cudaSuccess || (e = haps_.reserve((size_t)ho[(size_t)H] + 2 * MGLPH_HAP_PAD)) != cudaSuccess ||
             (e = roff_.reserve(ro.size() * 8)) != cudaSuccess || (e = hoff_.reserve(ho.size() * 8)) != cudaSuccess ||
             (e = out_.reserve(np * 8 + 8)) != cudaSuccess || (e = redo_.reserve(np * 4 + 16)) != cudaSuccess)
             return cuda_fail(e, "cudaMalloc");
         if (np == 0) return MGL_PH_OK;
         if ((e = cudaMemcpyAsync(reads_.p, reads, (size_t)ro[(size_t)R], cudaMemcpyHostToDevice, stream_)) != cudaSuccess ||
-            (e = cudaMemcpyAsync(haps_.p, haps, (size_t)ho[(size_t)H], cudaMemcpyHostToDevice, stream_)) != cudaSuccess ||
+            (e = cudaMemcpyAsync((uint8_t *)haps_.p + MGLPH_HAP_PAD, haps, (size_t)ho[(size_t)H], cudaMemcpyHostToDevice, stream_)) != cudaSuccess ||
             (e = cudaMemcpyAsync(roff_.p, ro.data(), ro.size() * 8, cudaMemcpyHostToDevice, stream_)) != cudaSuccess ||
             (e = cudaMemcpyAsync(hoff_.p, ho.data(), ho.size() * 8, cudaMemcpyHostToDevice, stream_)) != cudaSuccess)
             return cuda_fail(e, "H2D");

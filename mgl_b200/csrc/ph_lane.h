@@ -92,8 +92,10 @@ struct PhLane {
                 pZZ[k] = tb.ph2pr[qc];
                 const N dq = tb.ph2pr[pv.q[row] & 127];
                 dmatch[k] = one - dq;
-                dmis[k] = dq * (one / three);                          /* distm * threeOver, compute_prob_scalar.cc:16,33 */
                 base[k] = pv.rs[row];
+                /* distm * threeOver (compute_prob_scalar.cc:16,33) -- or, for a read base 'N', which matches every
+                   haplotype base (:25), the match value again: the row-constant half of the test costs nothing per cell */
+                dmis[k] = base[k] == (unsigned)'N' ? dmatch[k] : dq * (one / three);
             } else {                                                   /* below the read: computes zeros nobody uses */
                 pMM[k] = pGapM[k] = pMX[k] = pMY[k] = pZZ[k] = dmatch[k] = dmis[k] = (N)0;
                 base[k] = 0;
@@ -117,9 +119,10 @@ struct PhLane {
         if (c < 1 || c > pv.hl) return false;
         N dM = tprev.m, dX = tprev.x, dY = tprev.y;
         N uM = top.m, uX = top.x;
+        const bool hap_n = hb == (unsigned)'N';
 #pragma unroll
         for (int k = 0; k < RPL; k++) {
-            const bool match = (base[k] == hb) | (base[k] == (unsigned)'N') | (hb == (unsigned)'N');       /* compute_prob_scalar.cc:25 */
+            const bool match = (base[k] == hb) || hap_n;               /* compute_prob_scalar.cc:25; a read 'N' is folded into dmis */
             const N distm = match ? dmatch[k] : dmis[k];
             const N Mn = distm * (dM * pMM[k] + (dX + dY) * pGapM[k]);
             const N Yn = Mp[k] * pMY[k] + Yp[k] * pZZ[k];
@@ -135,11 +138,13 @@ struct PhLane {
     }
 };
 
-/* the haplotype base lane `lane` meets at step t (any byte outside the haplotype: the step is skipped there) */
+/* the haplotype base lane `lane` meets at step t.  Outside columns 1..hl the step is skipped and any byte will do:
+   the load is unconditional, so the buffer holding the haplotypes is readable MGLPH_HAP_PAD bytes before its first
+   and after its last byte (the skew reaches 31 columns to either side). */
+#define MGLPH_HAP_PAD 64
 PH_HD unsigned ph_hap_byte(const PairView &pv, int t, int lane)
 {
-    const int c = t - lane + 1;
-    return (c >= 1 && c <= pv.hl) ? (unsigned)pv.hap[c - 1] : 0u;
+    return (unsigned)pv.hap[t - lane];
 }
 
 /* rows the read is pushed down by, bands it then needs, and the lane whose bottom row is its last row */

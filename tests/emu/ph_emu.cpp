@@ -3,6 +3,7 @@
  * the CUDA kernel compiles (mgl_b200/csrc/ph_lane.h); shuffles become array reads, the shared-memory carry row a
  * vector.  Lets the kernel logic be checked against the golden vectors in a container without a GPU.
  */
+#include <algorithm>
 #include <cmath>
 #include <cstdint>
 #include <vector>
@@ -74,7 +75,10 @@ extern "C" int ph_emu(const int32_t *lengths, const uint8_t *reads, const uint8_
         rp += 5 * (size_t)n;
         const uint8_t *hp = haps;
         for (int32_t h = 0; h < H; h++) {
-            pv.hap = hp; pv.hl = hl[h];
+            /* the kernel's haplotype buffer is padded on both sides (ph_hap_byte): give the emulator a padded copy */
+            std::vector<uint8_t> padded((size_t)hl[h] + 2 * MGLPH_HAP_PAD, 0);
+            std::copy(hp, hp + hl[h], padded.begin() + MGLPH_HAP_PAD);
+            pv.hap = padded.data() + MGLPH_HAP_PAD; pv.hl = hl[h];
             double res;
             bool redo = use_double != 0;
             if (!redo) {
