@@ -7,8 +7,9 @@
  * round trip between them: the float kernel writes the final value or appends the pair to a redo list (atomic
  * counter), the double kernel is launched over the worst case and its warps beyond the counter leave at once.
  *
- * Rows per lane (RPL 1/2/4/8 = bands of 32/64/128/256 read rows) is picked per launch from the longest read, so a
- * 101-base read runs RPL 4 in one band; longer reads go band by band through a carry row in shared memory.
+ * Lanes per pair (32, or 16 with two pairs per warp) and rows per lane are picked per launch from the longest read, so
+ * a 150-base read is 10 rows on each of 15 lanes in one band; reads beyond 256 bases go band by band through a carry
+ * row in shared memory.
  * Roofline: FP32 (FP64 for the redo pass) FMA pipe -- 8 flops-instructions and 2 selects per cell, no O(cells)
  * memory traffic at all (a pair reads readLen * 5 + hapLen bytes and writes 8).
  */
@@ -16,6 +17,7 @@
 
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -45,26 +47,30 @@ struct KArgs {
     int carry_cols;               /* columns the shared-memory carry row of one warp holds */
 };
 
-template <class N> struct ShflT;
-template <> struct ShflT<float> { static __device__ __forceinline__ float up(float v) { return __shfl_up_sync(0xffffffffu, v, 1); } };
-template <> struct ShflT<double> { static __device__ __forceinline__ double up(double v) { return __shfl_up_sync(0xffffffffu, v, 1); } };
+template <class N, int G> struct ShflT;
+template <int G> struct ShflT<float, G> { static __device__ __forceinline__ float up(float v) { return __shfl_up_sync(0xffffffffu, v, 1, G); } };
+template <int G> struct ShflT<double, G> { static __device__ __forceinline__ double up(double v) { return __shfl_up_sync(0xffffffffu, v, 1, G); } };
 
-/* FROM_LIST: warp w runs pair redo[w] if w < *redo_count (the double pass behind a float pass) */
-template <class N, int RPL, bool FROM_LIST, bool ESCALATE>
+/*
+ * G lanes per pair: 32 (one pair per warp) or 16 (two pairs per warp, each on RPL up to 10 rows per lane: the
+ * per-step overhead -- shuffles, skew test, register rotation -- is spread over twice the cells and the skew is 15
+ * columns instead of 31).  Work item i = warp * (32 / G) + group; FROM_LIST: item i is pair redo[i] for
+ * i < *redo_count (the double pass behind a float pass).  The groups of a warp run in lock step over the longer of
+ * their haplotypes and the larger of their band counts; a group that has finished sits the rest out.
+ */
+template <class N, int RPL, int G, bool FROM_LIST, bool ESCALATE>
 __global__ void __launch_bounds__(128) ph_forward_kernel(const KArgs<N> a)
 {
+    constexpr int PPW = 32 / G;
     extern __shared__ __align__(16) unsigned char s_raw[];
-    const int warp_in_block = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp_in_block = threadIdx.x >> 5, wl = threadIdx.x & 31, grp = wl / G, lane = wl % G;
     const unsigned int w = blockIdx.x * (blockDim.x >> 5) + warp_in_block;
-    const unsigned int n_pairs = (unsigned int)a.job.R * (unsigned int)a.job.H;
-    unsigned int p;
-    if (FROM_LIST) {
-        if (w >= *a.redo_count) return;
-        p = a.redo[w];
-    } else {
-        if (w >= n_pairs) return;
-        p = w;
-    }
+    const unsigned int count = FROM_LIST ? *a.redo_count : (unsigned int)a.job.R * (unsigned int)a.job.H;
+    if (w * PPW >= count) return;
+    unsigned int item = w * PPW + (unsigned int)grp;
+    const bool valid = item < count;
+    if (!valid) item = w * PPW;                          /* an odd tail: shadow the warp's first pair, write nothing */
+    const unsigned int p = FROM_LIST ? a.redo[item] : item;
     const int r = (int)(p / (unsigned int)a.job.H), h = (int)(p % (unsigned int)a.job.H);
     PairView pv;
     pv.rl = (int)((a.job.read_off[r + 1] - a.job.read_off[r]) / 5);
@@ -73,35 +79,44 @@ __global__ void __launch_bounds__(128) ph_forward_kernel(const KArgs<N> a)
     pv.q = pv.rs + pv.rl; pv.ins = pv.q + pv.rl; pv.del = pv.ins + pv.rl; pv.gcp = pv.del + pv.rl;
     pv.hap = a.job.haps + MGLPH_HAP_PAD + a.job.hap_off[h];
 
-    Top<N> *carry = reinterpret_cast<Top<N> *>(s_raw) + (size_t)warp_in_block * (a.carry_cols + 1);
+    Top<N> *carry = reinterpret_cast<Top<N> *>(s_raw) + (size_t)(warp_in_block * PPW + grp) * (a.carry_cols + 1);
     const N y_initial = a.tb.initial / (N)pv.hl;                       /* compute_prob_scalar.cc:104 */
-    const int nb = ph_bands(pv.rl, RPL);
-    PhLane<N, RPL> L;
-    for (int b = 0; b < nb; b++) {
-        L.band_begin(a.tb, pv, b, lane, y_initial);
-        const bool park = b + 1 < nb;
+    const int nb = ph_bands(pv.rl, RPL, G);
+    int nb_max = nb, hl_max = pv.hl;
+    if (PPW > 1) {
+        nb_max = max(nb_max, __shfl_xor_sync(0xffffffffu, nb_max, G));
+        hl_max = max(hl_max, __shfl_xor_sync(0xffffffffu, hl_max, G));
+    }
+    const int hl_own = pv.hl;
+    PhLane<N, RPL, G> L;
+    for (int b = 0; b < nb_max; b++) {
+        const bool live = b < nb;
+        if (live) L.band_begin(a.tb, pv, b, lane, y_initial);
+        pv.hl = live ? hl_own : 0;                                     /* a finished group: every step is outside 1..hl */
+        const bool park = live && b + 1 < nb;
+        const bool any_park = b + 1 < nb_max;
         unsigned hb_next = ph_hap_byte(pv, 0, lane);
 #pragma unroll 2
-        for (int t = 0; t < pv.hl + 31; t++) {
+        for (int t = 0; t < hl_max + G - 1; t++) {
             const unsigned hb = hb_next;
             hb_next = ph_hap_byte(pv, t + 1, lane);
             Top<N> top;
-            top.m = ShflT<N>::up(L.bottom.m);
-            top.x = ShflT<N>::up(L.bottom.x);
-            top.y = ShflT<N>::up(L.bottom.y);
+            top.m = ShflT<N, G>::up(L.bottom.m);
+            top.x = ShflT<N, G>::up(L.bottom.x);
+            top.y = ShflT<N, G>::up(L.bottom.y);
             if (lane == 0) {
                 if (b == 0) { top.m = (N)0; top.x = (N)0; top.y = y_initial; }
                 else if (t + 1 <= pv.hl) top = carry[t + 1];
             }
             const bool active = L.step(pv, t, top, hb);
-            if (park) {
-                if (active && lane == 31) carry[t - 31 + 1] = L.bottom;
+            if (any_park) {
+                if (park && active && lane == G - 1) carry[t - (G - 1) + 1] = L.bottom;
                 __syncwarp();
             }
         }
     }
-    const int ll = ph_last_lane(pv.rl, RPL);
-    if (lane == ll) {
+    const int ll = ph_last_lane(pv.rl, RPL, G);
+    if (valid && lane == ll) {
         const N res = L.result;
         if (ESCALATE && (double)res < (double)MGLPH_MIN_ACCEPTED) {    /* ...MicrosoftPairHmm.cc:182 */
             a.redo[atomicAdd(a.redo_count, 1u)] = p;
@@ -111,31 +126,58 @@ __global__ void __launch_bounds__(128) ph_forward_kernel(const KArgs<N> a)
     }
 }
 
+/* shape = G * 100 + RPL; `items` = pairs (or the worst-case length of the redo list) */
 template <class N, bool FROM_LIST, bool ESCALATE>
-static cudaError_t launch_forward(int rpl, unsigned int warps, size_t smem, const KArgs<N> &a, cudaStream_t st)
+static cudaError_t launch_forward(int shape, unsigned int items, int carry_cols, const KArgs<N> &a, cudaStream_t st)
 {
-    if (warps == 0) return cudaSuccess;
-    const unsigned int blocks = (warps + 3) / 4;
-#define PH_LAUNCH(R_)                                                                                                   \
+    if (items == 0) return cudaSuccess;
+    const int g = shape / 100;
+    const unsigned int ppw = 32u / (unsigned int)g;
+    const unsigned int warps = (items + ppw - 1) / ppw, blocks = (warps + 3) / 4;
+    const size_t smem = (size_t)4 * ppw * (size_t)(carry_cols + 1) * sizeof(Top<N>);
+#define PH_LAUNCH(R_, G_)                                                                                               \
     do {                                                                                                                \
         if (smem > 48 * 1024) {                                                                                         \
-            cudaError_t e = cudaFuncSetAttribute(ph_forward_kernel<N, R_, FROM_LIST, ESCALATE>,                         \
+            cudaError_t e = cudaFuncSetAttribute(ph_forward_kernel<N, R_, G_, FROM_LIST, ESCALATE>,                     \
                                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);               \
             if (e != cudaSuccess) return e;                                                                             \
         }                                                                                                               \
-        ph_forward_kernel<N, R_, FROM_LIST, ESCALATE><<<blocks, 128, smem, st>>>(a);                                    \
+        ph_forward_kernel<N, R_, G_, FROM_LIST, ESCALATE><<<blocks, 128, smem, st>>>(a);                                \
     } while (0)
-    switch (rpl) {
-    case 1: PH_LAUNCH(1); break;
-    case 2: PH_LAUNCH(2); break;
-    case 3: PH_LAUNCH(3); break;
-    case 4: PH_LAUNCH(4); break;
-    case 5: PH_LAUNCH(5); break;
-    case 6: PH_LAUNCH(6); break;
-    default: PH_LAUNCH(8); break;
+    switch (shape) {
+    case 3201: PH_LAUNCH(1, 32); break;
+    case 3202: PH_LAUNCH(2, 32); break;
+    case 3203: PH_LAUNCH(3, 32); break;
+    case 3204: PH_LAUNCH(4, 32); break;
+    case 3205: PH_LAUNCH(5, 32); break;
+    case 3206: PH_LAUNCH(6, 32); break;
+    case 3208: PH_LAUNCH(8, 32); break;
+    case 1605: if constexpr (sizeof(N) == 4) { PH_LAUNCH(5, 16); break; } else return cudaErrorInvalidValue;
+    case 1606: if constexpr (sizeof(N) == 4) { PH_LAUNCH(6, 16); break; } else return cudaErrorInvalidValue;
+    case 1607: if constexpr (sizeof(N) == 4) { PH_LAUNCH(7, 16); break; } else return cudaErrorInvalidValue;
+    case 1608: if constexpr (sizeof(N) == 4) { PH_LAUNCH(8, 16); break; } else return cudaErrorInvalidValue;
+    case 1610: if constexpr (sizeof(N) == 4) { PH_LAUNCH(10, 16); break; } else return cudaErrorInvalidValue;
+    default: return cudaErrorInvalidValue;
     }
 #undef PH_LAUNCH
     return cudaGetLastError();
+}
+
+/* whole-warp shape for reads of up to max_rl bases (one band up to 256 rows) */
+static int shape_g32(int max_rl)
+{
+    int rpl = (max_rl + 31) / 32;
+    if (rpl == 7 || rpl > 8) rpl = 8;
+    return 3200 + (rpl < 1 ? 1 : rpl);
+}
+/* float pass: reads of 65..160 bases run two pairs per warp */
+static int shape_float(int max_rl)
+{
+    if (max_rl > 64 && max_rl <= 160) {
+        const int rpl = (max_rl + 15) / 16;
+        return 1600 + (rpl == 9 ? 10 : rpl);
+    }
+    return shape_g32(max_rl);
 }
 
 struct Buf {
@@ -166,6 +208,7 @@ public:
     }
     std::string err;
     std::mutex mu;
+    bool force_g32 = false;       /* developer knob (MGL_PAIRHMM_G32=1): float pass on whole-warp shapes only */
 
     int init()
     {
@@ -176,6 +219,7 @@ public:
         if ((e = cudaGetDeviceProperties(&prop, device_)) != cudaSuccess) return cuda_fail(e, "device properties");
         if (prop.major != 10) { err = "built for sm_100a (B200) only"; return MGL_PH_E_NO_DEVICE; }
         if ((e = cudaSetDevice(device_)) != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
+        { const char *v = std::getenv("MGL_PAIRHMM_G32"); force_g32 = v && v[0] == '1'; }
         if ((e = cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking)) != cudaSuccess) return cuda_fail(e, "stream");
         if ((e = cudaEventCreate(&ev0_)) != cudaSuccess || (e = cudaEventCreate(&ev1_)) != cudaSuccess) return cuda_fail(e, "event");
         /* tables: float ph2pr | float mm | double ph2pr | double mm */
@@ -227,7 +271,7 @@ public:
         cudaError_t e;
         if ((e = cudaSetDevice(device_)) != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
         const size_t np = (size_t)R * (size_t)H;
-        if ((e = reads_.reserve((size_t)ro[(size_t)R] + 16)) != cudaSuccess || (e = haps_.reserve((size_t)ho[(size_t)H] + 2 * MGLPH_HAP_PAD)) != cudaSuccess ||
+        if ((e = reads_.reserve((size_t)ro[(size_t)R] + 16)) != cudaSuccess || (e = haps_.reserve((size_t)ho[(size_t)H] + 2 * MGLPH_HAP_PAD + (size_t)max_hl_)) != cudaSuccess ||
             (e = roff_.reserve(ro.size() * 8)) != cudaSuccess || (e = hoff_.reserve(ho.size() * 8)) != cudaSuccess ||
             (e = out_.reserve(np * 8 + 8)) != cudaSuccess || (e = redo_.reserve(np * 4 + 16)) != cudaSuccess)
             return cuda_fail(e, "cudaMalloc");
@@ -250,18 +294,20 @@ public:
         if (np == 0) return MGL_PH_OK;
         cudaError_t e;
         if ((e = cudaSetDevice(device_)) != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
-        /* rows per lane: the longest read in one band when it has <= 256 rows (a 150-base read: 5 rows on each of 30 lanes) */
-        int rpl = (max_rl_ + 31) / 32;
-        if (rpl == 7 || rpl > 8) rpl = 8;
-        const bool multi = max_rl_ > 32 * rpl;
+        /* shapes from the longest read: one band when it has <= 256 rows (150 bases: two pairs per warp, 10 rows on each
+           of 15 lanes; the double pass stays one pair per warp, its rows need two registers per value) */
+        const int shape_f = force_g32 ? shape_g32(max_rl_) : shape_float(max_rl_), shape_d = shape_g32(max_rl_);
+        const bool multi = max_rl_ > 256;
         JobDev job;
         job.reads = (const uint8_t *)reads_.p; job.haps = (const uint8_t *)haps_.p;
         job.read_off = (const int64_t *)roff_.p; job.hap_off = (const int64_t *)hoff_.p;
         job.R = R_; job.H = H_;
         unsigned int *redo_count = (unsigned int *)redo_.p, *redo = redo_count + 4;
         const int carry_cols = multi ? max_hl_ + 1 : 0;
-        const size_t smem_f = 4 * (size_t)(carry_cols + 1) * sizeof(Top<float>), smem_d = 4 * (size_t)(carry_cols + 1) * sizeof(Top<double>);
-        if (smem_d > 220 * 1024) { err = "haplotype of " + std::to_string(max_hl_) + " bases with reads longer than 256: carry row exceeds shared memory"; return MGL_PH_E_TOO_LONG; }
+        if (4 * (size_t)(carry_cols + 1) * sizeof(Top<double>) > 220 * 1024) {
+            err = "haplotype of " + std::to_string(max_hl_) + " bases with reads longer than 256: carry row exceeds shared memory";
+            return MGL_PH_E_TOO_LONG;
+        }
         KArgs<float> af;
         af.job = job; af.tb = tf_; af.log10_initial = tables_f().log10_initial; af.out = (double *)out_.p;
         af.redo = redo; af.redo_count = redo_count; af.carry_cols = carry_cols;
@@ -270,12 +316,12 @@ public:
         ad.redo = redo; ad.redo_count = redo_count; ad.carry_cols = carry_cols;
         if ((e = cudaEventRecord(ev0_, stream_)) != cudaSuccess) return cuda_fail(e, "event record");
         if (use_double) {
-            if ((e = launch_forward<double, false, false>(rpl, (unsigned int)np, smem_d, ad, stream_)) != cudaSuccess) return cuda_fail(e, "double launch");
+            if ((e = launch_forward<double, false, false>(shape_d, (unsigned int)np, carry_cols, ad, stream_)) != cudaSuccess) return cuda_fail(e, "double launch");
             st.launches += 1; st.pairs_double += np;
         } else {
             if ((e = cudaMemsetAsync(redo_count, 0, 16, stream_)) != cudaSuccess) return cuda_fail(e, "memset");
-            if ((e = launch_forward<float, false, true>(rpl, (unsigned int)np, smem_f, af, stream_)) != cudaSuccess) return cuda_fail(e, "float launch");
-            if ((e = launch_forward<double, true, false>(rpl, (unsigned int)np, smem_d, ad, stream_)) != cudaSuccess) return cuda_fail(e, "double launch");
+            if ((e = launch_forward<float, false, true>(shape_f, (unsigned int)np, carry_cols, af, stream_)) != cudaSuccess) return cuda_fail(e, "float launch");
+            if ((e = launch_forward<double, true, false>(shape_d, (unsigned int)np, carry_cols, ad, stream_)) != cudaSuccess) return cuda_fail(e, "double launch");
             st.launches += 2;
         }
         if ((e = cudaEventRecord(ev1_, stream_)) != cudaSuccess) return cuda_fail(e, "event record");

@@ -2,7 +2,8 @@
  * ph_lane.h -- the PairHMM forward algorithm, one lane's view.
  *
  * Replaces the reference's inner loops (compute_full_prob_core_1X, compute_prob_scalar.cc:5-44, and the AVX2
- * bands of compute_prob_avx{f,d}.cc) for one (read, haplotype) pair.  A warp takes a band of 32 * RPL read rows:
+ * bands of compute_prob_avx{f,d}.cc) for one (read, haplotype) pair.  A group of G lanes (a whole warp, or half a warp
+ * with another pair in the other half) takes a band of G * RPL read rows:
  * lane l owns rows l*RPL .. l*RPL + RPL - 1 of the band and sweeps the haplotype columns one per step, one column
  * behind lane l - 1, so at step t it is at column t - l + 1.  Everything that is constant along a row (the five
  * transition probabilities of compute_prob_scalar.cc:73-81 and the two emission values :25-34) sits in the lane's
@@ -49,7 +50,7 @@ struct PairView {
 template <class N>
 struct Top { N m, x, y; };
 
-template <class N, int RPL>
+template <class N, int RPL, int G = 32>
 struct PhLane {
     N pMM[RPL], pGapM[RPL], pMX[RPL], pMY[RPL], pZZ[RPL];
     N dmatch[RPL], dmis[RPL];
@@ -58,11 +59,11 @@ struct PhLane {
     Top<N> tprev;                   /* the row above my first row, at my previous column                    */
     Top<N> bottom;                  /* my last row at the column I computed last: what lane l + 1 receives  */
     N result;
-    int lane;
+    int lane;                       /* inside the group of G lanes                                           */
     bool last;                      /* my bottom row is the read's last row (in this band)                   */
 
     /*
-     * Rows [band * 32 * RPL + lane * RPL - pad, + RPL) of the read, pad = ph_pad(rl, RPL): the read is pushed down
+     * Rows [band * G * RPL + lane * RPL - pad, + RPL) of the read, pad = ph_pad(rl, RPL): the read is pushed down
      * by `pad` rows so that its LAST row is always some lane's bottom row (the sum over the last row then needs no
      * indexed access to the row registers, which would put them in local memory).  The pad rows above the read
      * behave as DP row 0: M = X = 0 and Y = yInitial in every column.
@@ -71,11 +72,11 @@ struct PhLane {
     {
         lane = lane_;
         const int pad = (RPL - pv.rl % RPL) % RPL;
-        last = band * 32 * RPL + lane * RPL + (RPL - 1) - pad == pv.rl - 1;
+        last = band * G * RPL + lane * RPL + (RPL - 1) - pad == pv.rl - 1;
         const N one = (N)1.0, three = (N)3.0;
 #pragma unroll
         for (int k = 0; k < RPL; k++) {
-            const int row = band * 32 * RPL + lane * RPL + k - pad;    /* 0-based index into the read */
+            const int row = band * G * RPL + lane * RPL + k - pad;     /* 0-based index into the read */
             Mp[k] = Xp[k] = Yp[k] = (N)0;                              /* column 0 of rows >= 1 */
             if (row < 0) {                                             /* a copy of DP row 0: Y carries yInitial along, M and X stay 0 */
                 pMM[k] = pGapM[k] = pMX[k] = pMY[k] = dmatch[k] = dmis[k] = (N)0;
@@ -140,7 +141,8 @@ struct PhLane {
 
 /* the haplotype base lane `lane` meets at step t.  Outside columns 1..hl the step is skipped and any byte will do:
    the load is unconditional, so the buffer holding the haplotypes is readable MGLPH_HAP_PAD bytes before its first
-   and after its last byte (the skew reaches 31 columns to either side). */
+   and after its last byte (the skew reaches 31 columns to either side), plus the longest haplotype behind the last
+   byte (a group sharing its warp with a longer haplotype keeps stepping). */
 #define MGLPH_HAP_PAD 64
 PH_HD unsigned ph_hap_byte(const PairView &pv, int t, int lane)
 {
@@ -149,8 +151,8 @@ PH_HD unsigned ph_hap_byte(const PairView &pv, int t, int lane)
 
 /* rows the read is pushed down by, bands it then needs, and the lane whose bottom row is its last row */
 PH_HD int ph_pad(int rl, int rpl) { return (rpl - rl % rpl) % rpl; }
-PH_HD int ph_bands(int rl, int rpl) { return (rl + ph_pad(rl, rpl) + 32 * rpl - 1) / (32 * rpl); }
-PH_HD int ph_last_lane(int rl, int rpl) { return ((rl + ph_pad(rl, rpl) - 1) % (32 * rpl)) / rpl; }
+PH_HD int ph_bands(int rl, int rpl, int g = 32) { return (rl + ph_pad(rl, rpl) + g * rpl - 1) / (g * rpl); }
+PH_HD int ph_last_lane(int rl, int rpl, int g = 32) { return ((rl + ph_pad(rl, rpl) - 1) % (g * rpl)) / rpl; }
 
 }  // namespace mglph
 #endif

@@ -13,20 +13,20 @@
 
 using namespace mglph;
 
-template <class N, int RPL>
+template <class N, int RPL, int G = 32>
 static N run_pair(const Tables<N> &tb, const PairView &pv)
 {
-    const int nb = ph_bands(pv.rl, RPL);
+    const int nb = ph_bands(pv.rl, RPL, G);
     const N y_initial = tb.initial / (N)pv.hl;
     std::vector<Top<N>> carry((size_t)pv.hl + 2);
-    std::vector<PhLane<N, RPL>> L(32);
+    std::vector<PhLane<N, RPL, G>> L(G);
     N result = (N)0;
     for (int b = 0; b < nb; b++) {
-        for (int l = 0; l < 32; l++) L[(size_t)l].band_begin(tb, pv, b, l, y_initial);
-        for (int t = 0; t < pv.hl + 31; t++) {
+        for (int l = 0; l < G; l++) L[(size_t)l].band_begin(tb, pv, b, l, y_initial);
+        for (int t = 0; t < pv.hl + G - 1; t++) {
             Top<N> bots[32];
-            for (int l = 0; l < 32; l++) bots[l] = L[(size_t)l].bottom;              /* what __shfl_up_sync delivers */
-            for (int l = 0; l < 32; l++) {
+            for (int l = 0; l < G; l++) bots[l] = L[(size_t)l].bottom;              /* what __shfl_up_sync delivers */
+            for (int l = 0; l < G; l++) {
                 Top<N> top = l > 0 ? bots[l - 1] : Top<N>{(N)0, (N)0, (N)0};
                 if (l == 0) {
                     const int c = t + 1;
@@ -34,11 +34,11 @@ static N run_pair(const Tables<N> &tb, const PairView &pv)
                     else if (c <= pv.hl) top = carry[(size_t)c];
                 }
                 const bool active = L[(size_t)l].step(pv, t, top, ph_hap_byte(pv, t, l));
-                if (active && l == 31 && b + 1 < nb) carry[(size_t)(t - 31 + 1)] = L[(size_t)l].bottom;
+                if (active && l == G - 1 && b + 1 < nb) carry[(size_t)(t - (G - 1) + 1)] = L[(size_t)l].bottom;
             }
         }
     }
-    const int ll = ph_last_lane(pv.rl, RPL);
+    const int ll = ph_last_lane(pv.rl, RPL, G);
     result = L[(size_t)ll].result;
     return result;
 }
@@ -53,6 +53,13 @@ static N run_any(const Tables<N> &tb, const PairView &pv, int rpl)
     case 4: return run_pair<N, 4>(tb, pv);
     case 5: return run_pair<N, 5>(tb, pv);
     case 6: return run_pair<N, 6>(tb, pv);
+    case 8: return run_pair<N, 8>(tb, pv);
+    /* half-warp groups: rpl = 100 + rows per lane */
+    case 105: return run_pair<N, 5, 16>(tb, pv);
+    case 106: return run_pair<N, 6, 16>(tb, pv);
+    case 107: return run_pair<N, 7, 16>(tb, pv);
+    case 108: return run_pair<N, 8, 16>(tb, pv);
+    case 110: return run_pair<N, 10, 16>(tb, pv);
     default: return run_pair<N, 8>(tb, pv);
     }
 }

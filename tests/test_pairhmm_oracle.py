@@ -79,7 +79,7 @@ def test_oracle_vs_live_reference(ph):
         assert ok.mean() > 0.9 and np.all(np.abs(got - ref)[ok] <= TOL)
 
 
-@pytest.mark.parametrize("rpl", [1, 2, 3, 4, 5, 6, 8])
+@pytest.mark.parametrize("rpl", [1, 2, 3, 4, 5, 6, 8, 105, 106, 107, 108, 110])   # 1xx: half-warp groups of 16 lanes
 def test_lane_code_through_warp_emulator(ph, ph_golden, rpl):
     """the PhLane code the CUDA kernel compiles (ph_lane.h), run by a lock-step CPU emulation of a warp with every
     rows-per-lane shape (bands of 32/64/128/256 rows: reads of 1..260 bases cross the band boundary), against the
