@@ -15,6 +15,7 @@
  */
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -33,6 +34,7 @@ struct JobDev {
     const uint8_t *reads, *haps;
     const int64_t *read_off;      /* R + 1: byte offset of each read's five tracks */
     const int64_t *hap_off;       /* H + 1 */
+    const int *read_list;         /* the reads of this launch (one shape bucket); its length x H work items */
     int R, H;
 };
 
@@ -44,6 +46,7 @@ struct KArgs {
     double *out;                  /* R * H */
     unsigned int *redo;           /* float pass: pairs to recompute in double; double pass: the list to run (or NULL: all pairs) */
     unsigned int *redo_count;
+    unsigned int items;           /* work items of this launch (not FROM_LIST) */
     int carry_cols;               /* columns the shared-memory carry row of one warp holds */
 };
 
@@ -65,13 +68,20 @@ __global__ void __launch_bounds__(128) ph_forward_kernel(const KArgs<N> a)
     extern __shared__ __align__(16) unsigned char s_raw[];
     const int warp_in_block = threadIdx.x >> 5, wl = threadIdx.x & 31, grp = wl / G, lane = wl % G;
     const unsigned int w = blockIdx.x * (blockDim.x >> 5) + warp_in_block;
-    const unsigned int count = FROM_LIST ? *a.redo_count : (unsigned int)a.job.R * (unsigned int)a.job.H;
+    const unsigned int count = FROM_LIST ? *a.redo_count : a.items;
     if (w * PPW >= count) return;
     unsigned int item = w * PPW + (unsigned int)grp;
     const bool valid = item < count;
     if (!valid) item = w * PPW;                          /* an odd tail: shadow the warp's first pair, write nothing */
-    const unsigned int p = FROM_LIST ? a.redo[item] : item;
-    const int r = (int)(p / (unsigned int)a.job.H), h = (int)(p % (unsigned int)a.job.H);
+    unsigned int p;
+    int r, h;
+    if (FROM_LIST) {
+        p = a.redo[item];
+        r = (int)(p / (unsigned int)a.job.H); h = (int)(p % (unsigned int)a.job.H);
+    } else {
+        r = a.job.read_list[item / (unsigned int)a.job.H]; h = (int)(item % (unsigned int)a.job.H);
+        p = (unsigned int)r * (unsigned int)a.job.H + (unsigned int)h;
+    }
     PairView pv;
     pv.rl = (int)((a.job.read_off[r + 1] - a.job.read_off[r]) / 5);
     pv.hl = (int)(a.job.hap_off[h + 1] - a.job.hap_off[h]);
@@ -128,9 +138,11 @@ __global__ void __launch_bounds__(128) ph_forward_kernel(const KArgs<N> a)
 
 /* shape = G * 100 + RPL; `items` = pairs (or the worst-case length of the redo list) */
 template <class N, bool FROM_LIST, bool ESCALATE>
-static cudaError_t launch_forward(int shape, unsigned int items, int carry_cols, const KArgs<N> &a, cudaStream_t st)
+static cudaError_t launch_forward(int shape, unsigned int items, int carry_cols, KArgs<N> a, cudaStream_t st)
 {
     if (items == 0) return cudaSuccess;
+    a.items = items;
+    a.carry_cols = carry_cols;
     const int g = shape / 100;
     const unsigned int ppw = 32u / (unsigned int)g;
     const unsigned int warps = (items + ppw - 1) / ppw, blocks = (warps + 3) / 4;
@@ -201,7 +213,7 @@ public:
     ~Engine()
     {
         cudaSetDevice(device_);
-        for (Buf *b : {&reads_, &haps_, &roff_, &hoff_, &out_, &redo_, &tab_}) b->release();
+        for (Buf *b : {&reads_, &haps_, &roff_, &hoff_, &out_, &redo_, &tab_, &order_}) b->release();
         if (stream_) cudaStreamDestroy(stream_);
         if (ev0_) cudaEventDestroy(ev0_);
         if (ev1_) cudaEventDestroy(ev1_);
@@ -267,18 +279,40 @@ public:
             sum_hl += (uint64_t)n;
         }
         R_ = R; H_ = H;
+        /*
+         * Shape buckets: a read's shape (lanes per pair x rows per lane) follows from its own length, so the reads are
+         * grouped by shape and each group is one launch -- a few 250-base reads do not push a region of 101-base
+         * reads onto the widest shape.  order = read indices, stable within a bucket.
+         */
+        buckets_.clear();
+        std::vector<int> order((size_t)R);
+        {
+            std::vector<std::pair<int, int>> key((size_t)R);
+            for (int32_t r = 0; r < R; r++) key[(size_t)r] = {shape_g32(lengths[1 + r]) * 10000 + (force_g32 ? 0 : shape_float(lengths[1 + r])), r};
+            std::stable_sort(key.begin(), key.end(), [](const std::pair<int, int> &x, const std::pair<int, int> &y) { return x.first < y.first; });
+            for (int32_t r = 0; r < R; r++) {
+                order[(size_t)r] = key[(size_t)r].second;
+                const int n = lengths[1 + key[(size_t)r].second];
+                if (buckets_.empty() || buckets_.back().key != key[(size_t)r].first)
+                    buckets_.push_back(Bucket{key[(size_t)r].first, force_g32 ? shape_g32(n) : shape_float(n), shape_g32(n), r, 0, 0});
+                buckets_.back().count++;
+                buckets_.back().max_rl = std::max(buckets_.back().max_rl, n);
+            }
+        }
         cells_ = sum_rl * sum_hl;
         cudaError_t e;
         if ((e = cudaSetDevice(device_)) != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
         const size_t np = (size_t)R * (size_t)H;
         if ((e = reads_.reserve((size_t)ro[(size_t)R] + 16)) != cudaSuccess || (e = haps_.reserve((size_t)ho[(size_t)H] + 2 * MGLPH_HAP_PAD + (size_t)max_hl_)) != cudaSuccess ||
             (e = roff_.reserve(ro.size() * 8)) != cudaSuccess || (e = hoff_.reserve(ho.size() * 8)) != cudaSuccess ||
+            (e = order_.reserve(order.size() * 4 + 4)) != cudaSuccess ||
             (e = out_.reserve(np * 8 + 8)) != cudaSuccess || (e = redo_.reserve(np * 4 + 16)) != cudaSuccess)
             return cuda_fail(e, "cudaMalloc");
         if (np == 0) return MGL_PH_OK;
         if ((e = cudaMemcpyAsync(reads_.p, reads, (size_t)ro[(size_t)R], cudaMemcpyHostToDevice, stream_)) != cudaSuccess ||
             (e = cudaMemcpyAsync((uint8_t *)haps_.p + MGLPH_HAP_PAD, haps, (size_t)ho[(size_t)H], cudaMemcpyHostToDevice, stream_)) != cudaSuccess ||
             (e = cudaMemcpyAsync(roff_.p, ro.data(), ro.size() * 8, cudaMemcpyHostToDevice, stream_)) != cudaSuccess ||
+            (e = cudaMemcpyAsync(order_.p, order.data(), order.size() * 4, cudaMemcpyHostToDevice, stream_)) != cudaSuccess ||
             (e = cudaMemcpyAsync(hoff_.p, ho.data(), ho.size() * 8, cudaMemcpyHostToDevice, stream_)) != cudaSuccess)
             return cuda_fail(e, "H2D");
         if ((e = cudaStreamSynchronize(stream_)) != cudaSuccess) return cuda_fail(e, "H2D");   /* ro / ho are locals */
@@ -294,14 +328,13 @@ public:
         if (np == 0) return MGL_PH_OK;
         cudaError_t e;
         if ((e = cudaSetDevice(device_)) != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
-        /* shapes from the longest read: one band when it has <= 256 rows (150 bases: two pairs per warp, 10 rows on each
-           of 15 lanes; the double pass stays one pair per warp, its rows need two registers per value) */
-        const int shape_f = force_g32 ? shape_g32(max_rl_) : shape_float(max_rl_), shape_d = shape_g32(max_rl_);
+        /* the redo pass runs one shape for whatever the float pass hands over: that of the longest read */
+        const int shape_redo = shape_g32(max_rl_);
         const bool multi = max_rl_ > 256;
         JobDev job;
         job.reads = (const uint8_t *)reads_.p; job.haps = (const uint8_t *)haps_.p;
         job.read_off = (const int64_t *)roff_.p; job.hap_off = (const int64_t *)hoff_.p;
-        job.R = R_; job.H = H_;
+        job.R = R_; job.H = H_; job.read_list = nullptr;
         unsigned int *redo_count = (unsigned int *)redo_.p, *redo = redo_count + 4;
         const int carry_cols = multi ? max_hl_ + 1 : 0;
         if (4 * (size_t)(carry_cols + 1) * sizeof(Top<double>) > 220 * 1024) {
@@ -315,14 +348,24 @@ public:
         ad.job = job; ad.tb = td_; ad.log10_initial = tables_d().log10_initial; ad.out = (double *)out_.p;
         ad.redo = redo; ad.redo_count = redo_count; ad.carry_cols = carry_cols;
         if ((e = cudaEventRecord(ev0_, stream_)) != cudaSuccess) return cuda_fail(e, "event record");
-        if (use_double) {
-            if ((e = launch_forward<double, false, false>(shape_d, (unsigned int)np, carry_cols, ad, stream_)) != cudaSuccess) return cuda_fail(e, "double launch");
-            st.launches += 1; st.pairs_double += np;
-        } else {
-            if ((e = cudaMemsetAsync(redo_count, 0, 16, stream_)) != cudaSuccess) return cuda_fail(e, "memset");
-            if ((e = launch_forward<float, false, true>(shape_f, (unsigned int)np, carry_cols, af, stream_)) != cudaSuccess) return cuda_fail(e, "float launch");
-            if ((e = launch_forward<double, true, false>(shape_d, (unsigned int)np, carry_cols, ad, stream_)) != cudaSuccess) return cuda_fail(e, "double launch");
-            st.launches += 2;
+        /* one launch per shape bucket (upload()): 150-base reads two pairs per warp on 10 rows per lane, a 250-base read
+           one pair per warp on 8; the double kernels stay one pair per warp (two registers per value) */
+        if (!use_double && (e = cudaMemsetAsync(redo_count, 0, 16, stream_)) != cudaSuccess) return cuda_fail(e, "memset");
+        for (const Bucket &bk : buckets_) {
+            const unsigned int items = (unsigned int)bk.count * (unsigned int)H_;
+            const int cc = bk.max_rl > 256 ? carry_cols : 0;
+            af.job.read_list = ad.job.read_list = (const int *)order_.p + bk.first;
+            if (use_double) {
+                if ((e = launch_forward<double, false, false>(bk.shape_d, items, cc, ad, stream_)) != cudaSuccess) return cuda_fail(e, "double launch");
+            } else {
+                if ((e = launch_forward<float, false, true>(bk.shape_f, items, cc, af, stream_)) != cudaSuccess) return cuda_fail(e, "float launch");
+            }
+            st.launches += 1;
+        }
+        if (use_double) st.pairs_double += np;
+        else {
+            if ((e = launch_forward<double, true, false>(shape_redo, (unsigned int)np, carry_cols, ad, stream_)) != cudaSuccess) return cuda_fail(e, "double launch");
+            st.launches += 1;
         }
         if ((e = cudaEventRecord(ev1_, stream_)) != cudaSuccess) return cuda_fail(e, "event record");
         return MGL_PH_OK;
@@ -355,7 +398,9 @@ private:
     int device_;
     cudaStream_t stream_ = nullptr;
     cudaEvent_t ev0_ = nullptr, ev1_ = nullptr;
-    Buf reads_, haps_, roff_, hoff_, out_, redo_, tab_;
+    Buf reads_, haps_, roff_, hoff_, out_, redo_, tab_, order_;
+    struct Bucket { int key, shape_f, shape_d, first, count, max_rl; };
+    std::vector<Bucket> buckets_;
     Tables<float> tf_{};
     Tables<double> td_{};
     int R_ = 0, H_ = 0, max_rl_ = 0, max_hl_ = 0;
