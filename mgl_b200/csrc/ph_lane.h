@@ -50,6 +50,27 @@ struct PairView {
 template <class N>
 struct Top { N m, x, y; };
 
+/*
+ * The emission value of one cell: `a` if the read base equals the haplotype base or the haplotype base is 'N', else
+ * `b` (compute_prob_scalar.cc:25-34; a read 'N' is folded into b by band_begin).  On the device, in float, this is
+ * one compare-with-or and one select; the compiler's own rendering of the C expression is a compare and two selects.
+ */
+template <class N>
+PH_HD N ph_emission(unsigned base, unsigned hb, unsigned hap_n, N a, N b)
+{
+    return (base == hb || hap_n) ? a : b;
+}
+#if defined(__CUDA_ARCH__)
+template <>
+__device__ __forceinline__ float ph_emission<float>(unsigned base, unsigned hb, unsigned hap_n, float a, float b)
+{
+    float d;
+    asm("{\n\t.reg .pred q, p;\n\tsetp.ne.u32 q, %3, 0;\n\tsetp.eq.or.u32 p, %1, %2, q;\n\tselp.f32 %0, %4, %5, p;\n\t}"
+        : "=f"(d) : "r"(base), "r"(hb), "r"(hap_n), "f"(a), "f"(b));
+    return d;
+}
+#endif
+
 template <class N, int RPL, int G = 32>
 struct PhLane {
     N pMM[RPL], pGapM[RPL], pMX[RPL], pMY[RPL], pZZ[RPL];
@@ -120,11 +141,10 @@ struct PhLane {
         if (c < 1 || c > pv.hl) return false;
         N dM = tprev.m, dX = tprev.x, dY = tprev.y;
         N uM = top.m, uX = top.x;
-        const bool hap_n = hb == (unsigned)'N';
+        const unsigned hap_n = hb == (unsigned)'N' ? 1u : 0u;
 #pragma unroll
         for (int k = 0; k < RPL; k++) {
-            const bool match = (base[k] == hb) || hap_n;               /* compute_prob_scalar.cc:25; a read 'N' is folded into dmis */
-            const N distm = match ? dmatch[k] : dmis[k];
+            const N distm = ph_emission<N>(base[k], hb, hap_n, dmatch[k], dmis[k]);
             const N Mn = distm * (dM * pMM[k] + (dX + dY) * pGapM[k]);
             const N Yn = Mp[k] * pMY[k] + Yp[k] * pZZ[k];
             const N Xn = uM * pMX[k] + uX * pZZ[k];

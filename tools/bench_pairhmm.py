@@ -26,7 +26,7 @@ METRIC = "GCUPS, PairHMM forward algorithm, float with double escalation (1 CUP 
 FLOPS_PER_CELL = 11.0
 
 
-def synth(n_reads, n_haps, read_len, hap_len, seed=0xF3):
+def synth(n_reads, n_haps, read_len, hap_len, seed=0xF3, mixed=False):
     rng = np.random.default_rng(seed)
     acgt = np.frombuffer(b"ACGT", dtype=np.uint8)
     base = acgt[rng.integers(0, 4, hap_len)]
@@ -37,7 +37,11 @@ def synth(n_reads, n_haps, read_len, hap_len, seed=0xF3):
             h[k] = acgt[rng.integers(0, 4)]
         haps.append(h)
     reads = []
+    lens = []
     for _ in range(n_reads):
+        if mixed:                                     # a region of trimmed and untrimmed reads: one launch per shape
+            read_len = int(rng.choice((76, 101, 101, 150, 150, 150, 250)))
+        lens.append(read_len)
         h = haps[int(rng.integers(0, n_haps))]
         s = int(rng.integers(0, hap_len - read_len + 1))
         b = h[s:s + read_len].copy()
@@ -46,8 +50,8 @@ def synth(n_reads, n_haps, read_len, hap_len, seed=0xF3):
         q = np.clip(rng.normal(32, 6, read_len), 6, 41).astype(np.uint8)
         q[err] = 8
         reads.append(np.concatenate([b, q, np.full(read_len, 45, np.uint8), np.full(read_len, 45, np.uint8), np.full(read_len, 10, np.uint8)]))
-    lengths = np.array([n_reads] + [read_len] * n_reads + [n_haps] + [hap_len] * n_haps, dtype=np.int32)
-    return lengths, np.concatenate(reads), np.concatenate(haps), n_reads * n_haps * read_len * hap_len
+    lengths = np.array([n_reads] + lens + [n_haps] + [hap_len] * n_haps, dtype=np.int32)
+    return lengths, np.concatenate(reads), np.concatenate(haps), int(sum(lens)) * n_haps * hap_len
 
 
 def sub_job(lengths, rb, n_reads_sample):
@@ -64,7 +68,7 @@ def cpu_reference(lengths, rb, hb, budget_s=12.0):
         return None
     threads = P.ref_max_threads()
     R = int(lengths[0]); H = int(lengths[1 + R])
-    rl = int(lengths[1]); hl = int(lengths[2 + R])
+    hl = int(lengths[2 + R])
     n = 64
     while True:
         sub, srb = sub_job(lengths, rb, n)
@@ -72,7 +76,7 @@ def cpu_reference(lengths, rb, hb, budget_s=12.0):
         if secs >= budget_s / 4 or n >= R:
             break
         n = min(R, int(n * max(2.0, budget_s / 2 / max(secs, 1e-3))))
-    cells = int(sub[0]) * H * rl * hl
+    cells = int(sub[1:1 + int(sub[0])].sum()) * H * hl
     return {"value": cells / secs / 1e9, "unit": "GCUPS", "cores": threads, "kind": "reference",
             "sample": f"first {int(sub[0])} of {R} reads x {H} haplotypes, oracle/_ref (the reference's AVX2 float kernel + double escalation behind its JNI entry), "
                       f"8 reads per JNI call over {threads} OpenMP threads, {secs:.2f} s"}, secs
@@ -89,9 +93,10 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--double", action="store_true", help="double throughout (useDoublePrecision)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--mixed", action="store_true", help="read lengths drawn from 76 / 101 / 150 / 250")
     args = ap.parse_args()
-    lengths, rb, hb, cells = synth(args.reads, args.haps, args.read_len, args.hap_len)
-    workload = f"{args.reads} reads x {args.read_len} b against {args.haps} haplotypes x {args.hap_len} b (one region, every pair)"
+    lengths, rb, hb, cells = synth(args.reads, args.haps, args.read_len, args.hap_len, mixed=args.mixed)
+    workload = f"{args.reads} reads x {'76-250 (mixed)' if args.mixed else args.read_len} b against {args.haps} haplotypes x {args.hap_len} b (one region, every pair)"
 
     if args.impl == "reference":
         cb, secs = cpu_reference(lengths, rb, hb, budget_s=20.0)
