@@ -270,6 +270,7 @@ def main():
     barrier(dist, local)
     wall_ms = (time.perf_counter() - t0) * 1e3
     cells_step = st["cells"]
+    all_s16 = st["pairs_s32"] == 0 and st["pairs_s16"] > 0    # every pair in u16x2 arithmetic: two cells per lane-op
     ckpt_bytes_step = st["trace_bytes"]                 # checkpoint bytes the fill launches of one step write (planner's count)
     sw.set_option("overlap", 0)
     fill_ms = trace_ms = post_ms = serial_ms = 0.0
@@ -320,7 +321,9 @@ def main():
         K = args.steps
         value = cells_all * K / (dev_ms * 1e-3) / 1e9
         fill_cups = cells_step * K / (fill_ms * 1e-3)                    # this GPU's fill kernels
-        p_int = max(peaks.get("iadd3_s32", 0.0), peaks.get("imnmx_s32", 0.0)) or None
+        p_int32 = max(peaks.get("iadd3_s32", 0.0), peaks.get("imnmx_s32", 0.0)) or None
+        # the denominator in the arithmetic the kernel runs: a u16x2 lane-op is two 16-bit cell-ops
+        p_int = (2.0 * p_int32 if all_s16 else p_int32) if p_int32 else None
         measured = {}
         try:
             measured = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -346,8 +349,12 @@ def main():
                          if args.config in NCU_FILL_DRAM_BYTES_PER_CELL else None,
                          "note": "dominant kernel = sw_fill_kernel (all its launches of a step, timed with CUDA events on their stream in the "
                                  "one-chunk-at-a-time pass); algorithmic 10 int ops/cell (SURVEY.md 8d) x cells; peak = max(iadd3, imnmx) measured "
-                                 "live by int_peak.cu (not in MEASURED_PEAKS.json); u16x2 arithmetic does two cells per lane-op, which is how frac "
-                                 "can exceed 1; traffic = ncu dram bytes per cell x cells per average fill launch"},
+                                 "live by int_peak.cu (not in MEASURED_PEAKS.json)"
+                                 + (", x 2 because every pair of this workload runs in u16x2 arithmetic (one lane-op = two 16-bit cell-ops); "
+                                    "against the plain 32-bit peak (peak_s32) the fraction would be twice this" if all_s16 else
+                                    "; pairs that run in u16x2 arithmetic do two cells per lane-op, so a mixed workload can exceed its 32-bit fraction")
+                                 + "; traffic = ncu dram bytes per cell x cells per average fill launch",
+                         "peak_s32": p_int32},
             "roofline_hbm": {"bound": "hbm", "achieved": ckpt_bytes_step * K / (fill_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                              "frac": ckpt_bytes_step * K / (fill_ms * 1e-3) / 1e9 / hbm_peak,
                              "algorithmic_bytes_per_cell": ckpt_bytes_step / cells_step,
