@@ -28,6 +28,12 @@
 #include "ph_lane.h"
 #include "ph_tables.h"
 
+/* column steps per loop trip (the loop-carried registers rotate once per trip).  Measured [B200, r02q]: 10 rows per lane
+   1 814 / 1 646 / 1 697 GCUPS with 1 / 2 / 4 steps per trip, 7 rows per lane 1 463 / 1 482 / 1 533. */
+#ifndef MGLPH_UNROLL
+#define MGLPH_UNROLL (RPL >= 10 ? 1 : 4)
+#endif
+
 namespace mglph {
 
 struct JobDev {
@@ -65,6 +71,7 @@ template <class N, int RPL, int G, bool FROM_LIST, bool ESCALATE>
 __global__ void __launch_bounds__(128) ph_forward_kernel(const KArgs<N> a)
 {
     constexpr int PPW = 32 / G;
+    constexpr int kUnroll = MGLPH_UNROLL;
     extern __shared__ __align__(16) unsigned char s_raw[];
     const int warp_in_block = threadIdx.x >> 5, wl = threadIdx.x & 31, grp = wl / G, lane = wl % G;
     const unsigned int w = blockIdx.x * (blockDim.x >> 5) + warp_in_block;
@@ -106,7 +113,7 @@ __global__ void __launch_bounds__(128) ph_forward_kernel(const KArgs<N> a)
         const bool park = live && b + 1 < nb;
         const bool any_park = b + 1 < nb_max;
         unsigned hb_next = ph_hap_byte(pv, 0, lane);
-#pragma unroll 2
+#pragma unroll kUnroll
         for (int t = 0; t < hl_max + G - 1; t++) {
             const unsigned hb = hb_next;
             hb_next = ph_hap_byte(pv, t + 1, lane);
