@@ -45,6 +45,7 @@ def parse():
     ap.add_argument("--pairs", type=int, default=0, help="pairs per GPU (default: the config's size)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-numa-bind", action="store_true", help="N > 1: do not bind each rank to the CPUs local to its GPU")
     ap.add_argument("--chunk-pairs", type=int, default=0, help="engine chunk size (0: library default)")
     ap.add_argument("--pipe-wide", type=int, default=-1, help="long-pair kernel on eight warps per pair: 0 never, 1 auto, 2 always (-1: library default)")
     ap.add_argument("--plan-threads", type=int, default=0, help="host planner threads (0: library default)")
@@ -199,6 +200,26 @@ def run_reference(args, rank, world):
 _REAL_STDOUT = None
 
 
+def bind_to_gpu_cpus(gpu):
+    """One process per GPU: run this rank (and allocate its pinned buffers, first touch) on the CPUs NVML reports as
+    local to its GPU, so that host-to-device copies do not cross the socket interconnect.  Application-side policy (the
+    library never changes its caller's affinity).  Returns the CPU count bound to, or None if NVML says nothing."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(gpu)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = {64 * w + b for w in range(words) for b in range(64) if (int(mask[w]) >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if cpus and len(cpus) < len(os.sched_getaffinity(0)):
+            os.sched_setaffinity(0, cpus)
+            return len(cpus)
+    except Exception:
+        pass
+    return None
+
+
 def protect_stdout():
     """Libraries (NCCL's version banner, torchrun) write to fd 1; the contract is ONE JSON line there.
     Everything else goes to stderr; emit() writes the line to the real stdout."""
@@ -227,6 +248,7 @@ def main():
     import mgl_b200
     from mgl_b200 import native, synth
 
+    numa = bind_to_gpu_cpus(local) if (world > 1 and not args.no_numa_bind) else None
     n = args.pairs or DEFAULT_PAIRS[args.config]
     d = synth.generate(args.config, n, first=rank * n, pinned=True)       # this rank's shard of the stream
     sw = mgl_b200.MicrosoftSmithWaterman(local)
@@ -335,7 +357,8 @@ def main():
             "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u16x2 (score-safe pairs) / int32", "data": "synthetic",
             "config": {"workload": WORKLOAD[args.config], "pairs_per_gpu": n, "cells_per_gpu": cells_step,
-                       "l2": "inputs_exceed_l2 (arena + trace per step >> 126 MB)", "sharding": "independent pairs, no collective"},
+                       "l2": "inputs_exceed_l2 (arena + trace per step >> 126 MB)", "sharding": "independent pairs, no collective",
+                       "cpu_binding": (f"each rank on the {numa} CPUs local to its GPU (NVML)" if numa else "none")},
             "alignments_per_s": pairs_all * K / (dev_ms * 1e-3),
             "wall_ms_per_step": wall_ms / K,
             "kernel_ms_per_step": {"fill": fill_ms / K, "traceback": trace_ms / K, "scan_compact": post_ms / K,
