@@ -156,9 +156,13 @@ def cpu_baseline(d, budget_s=12.0):
     rate = probe / max(secs, 1e-6)
     n_sample = int(min(n, max(probe, rate * budget_s)))
     secs, cells = cpu_reference_run(d, n_sample, threads)
+    # the 1-core figure SURVEY.md 8d asks for beside the all-core one: a sample sized for ~2 s on one thread
+    n_one = int(min(n, max(16, n_sample / max(secs, 1e-6) / max(threads, 1) * 2.0)))
+    secs1, cells1 = cpu_reference_run(d, n_one, 1)
     return {"value": cells / secs / 1e9, "unit": UNIT, "alignments_per_s": n_sample / secs, "cores": threads,
             "kind": "reference", "sample": f"first {n_sample} pairs of the workload, {cells / 1e9:.2f} Gcells, {secs:.2f} s, "
-            f"reference align_avx/align_scalar via the JNI dispatch rule, one pair per OpenMP task"}
+            f"reference align_avx/align_scalar via the JNI dispatch rule, one pair per OpenMP task",
+            "one_core": {"value": cells1 / secs1 / 1e9, "unit": UNIT, "sample": f"first {n_one} pairs, {secs1:.2f} s on one thread"}}
 
 
 def run_reference(args, rank, world):
