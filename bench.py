@@ -48,6 +48,8 @@ def parse():
     ap.add_argument("--no-numa-bind", action="store_true", help="N > 1: do not bind each rank to the CPUs local to its GPU")
     ap.add_argument("--chunk-pairs", type=int, default=0, help="engine chunk size (0: library default)")
     ap.add_argument("--pipe-wide", type=int, default=-1, help="long-pair kernel on eight warps per pair: 0 never, 1 auto, 2 always (-1: library default)")
+    ap.add_argument("--pack", type=int, default=-1, help="2-bit transport of all-ACGT arena ranges: 0 never, 1 when the planner is ahead, 2 always (-1: library default)")
+    ap.add_argument("--pack-lead", type=int, default=-1, help="chunks a planner must be ahead of the upload to pack (-1: library default)")
     ap.add_argument("--plan-threads", type=int, default=0, help="host planner threads (0: library default)")
     return ap.parse_args()
 
@@ -263,6 +265,10 @@ def main():
         sw.set_option("pipe_wide", args.pipe_wide)
     if args.plan_threads:
         sw.set_option("plan_threads", args.plan_threads)
+    if args.pack >= 0:
+        sw.set_option("pack_arena", args.pack)
+    if args.pack_lead >= 0:
+        sw.set_option("pack_lead", args.pack_lead)
 
     # integer issue rates (roofline denominator), measured on this box
     peaks = {}

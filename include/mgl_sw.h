@@ -84,7 +84,9 @@ MGL_SW_API const char *mgl_sw_last_error(mgl_sw_handle *h);
 MGL_SW_API int mgl_sw_device_count(void);
 MGL_SW_API const char *mgl_sw_version(void);
 
-/* tuning knobs: "allow_s16" 0/1, "chunk_pairs", "trace_budget_mb", "plan_threads", "pipe_wide" 0/1/2 (long-pair
+/* tuning knobs: "allow_s16" 0/1, "chunk_pairs", "trace_budget_mb", "plan_threads", "pack_arena" 0/1/2 (all-ACGT byte
+   ranges of the arena cross the host link at 2 bits per base and are expanded on the device: never / for chunks whose
+   planner thread is "pack_lead" chunks ahead of the upload / always), "pipe_wide" 0/1/2 (long-pair
    kernel on eight warps per pair: never / for launches of few pairs / always), "overlap" 0/1 (resident_run: 1 = chunks
    alternate between two slots, whole-batch time only; 0 = one chunk at a time with per-kernel times) */
 MGL_SW_API int mgl_sw_set_option(mgl_sw_handle *h, const char *name, int64_t value);
@@ -134,6 +136,12 @@ MGL_SW_API int mgl_sw_format_cigar(const uint32_t *ops, int64_t n_ops, char *out
 /* pinned host memory for arenas / results */
 MGL_SW_API void *mgl_sw_host_alloc(uint64_t bytes);
 MGL_SW_API void mgl_sw_host_free(void *p);
+
+/* host half of the 2-bit transport form (no GPU needed; tests): packs src[0, n) into dst, four bases per byte, base k in
+   bits 2 (k % 4) of byte k / 4, code = (byte >> 1) & 3; dst holds ((n + 15) / 16) * 4 bytes.  Returns 1 when packed,
+   0 when a byte outside ACGT makes the range travel raw, -1 on a NULL pointer or a dst_cap too small.
+   `scalar` != 0 forces the table loop instead of AVX2 */
+MGL_SW_API int mgl_sw_pack2bit_host(const uint8_t *src, uint64_t n, uint8_t *dst, uint64_t dst_cap, int scalar);
 
 /* planning only (no GPU needed): how a batch would be bucketed; used by tests and tools */
 MGL_SW_API int mgl_sw_plan_summary(const mgl_sw_batch *batch, int allow_s16, uint64_t *out8);

@@ -16,6 +16,7 @@
 #include "../../include/mgl_sw.h"
 #include "sw_engine.h"
 #include "sw_kernels.h"
+#include "sw_pack.h"
 
 using namespace mglsw;
 
@@ -106,6 +107,8 @@ int mgl_sw_set_option(mgl_sw_handle *h, const char *name, int64_t value)
     else if (!std::strcmp(name, "plan_threads")) { if (value < 0 || value > 64) return MGL_SW_E_INVALID; h->engine->plan_threads = (int)value; }
     else if (!std::strcmp(name, "chunk_pairs")) { if (value < 1 || value > (1 << 22)) return MGL_SW_E_INVALID; h->engine->chunk_pairs = (u32)value; }
     else if (!std::strcmp(name, "pipe_wide")) { if (value < 0 || value > 2) return MGL_SW_E_INVALID; h->engine->pipe_wide = (int)value; }
+    else if (!std::strcmp(name, "pack_arena")) { if (value < 0 || value > 2) return MGL_SW_E_INVALID; h->engine->pack_arena = (int)value; }
+    else if (!std::strcmp(name, "pack_lead")) { if (value < 0 || value > 1024) return MGL_SW_E_INVALID; h->engine->pack_lead = (int)value; }
     else if (!std::strcmp(name, "trace_budget_mb")) { if (value < 0) return MGL_SW_E_INVALID; h->engine->trace_budget_bytes = (u64)value << 20; }
     else return MGL_SW_E_INVALID;
     return MGL_SW_OK;
@@ -335,6 +338,12 @@ int mgl_sw_align_one(const uint8_t *ref, int32_t ref_len, const uint8_t *alt, in
     if (cigar_len) *cigar_len = len;
     *offset = req.offset;
     return MGL_SW_OK;
+}
+
+int mgl_sw_pack2bit_host(const uint8_t *src, uint64_t n, uint8_t *dst, uint64_t dst_cap, int scalar)
+{
+    if (!dst || (n && !src) || dst_cap < mglsw::pack2_bytes((size_t)n)) return -1;
+    return (scalar ? mglsw::pack2_scalar(src, (size_t)n, dst) : mglsw::pack2(src, (size_t)n, dst)) ? 1 : 0;
 }
 
 void *mgl_sw_host_alloc(uint64_t bytes)

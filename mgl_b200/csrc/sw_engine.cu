@@ -16,8 +16,36 @@
 #include "sw_config.h"
 #include "sw_kernels.h"
 #include "sw_layout.h"
+#include "sw_pack.h"
 
 namespace mglsw {
+
+/* ---------------------------------------------------------------- 2-bit transport form -> arena bytes */
+
+/*
+ * One thread per 16 bases: a u32 of the packed form (sw_pack.h) becomes the 16 original bytes, one 16-byte
+ * store.  `dst` is 16-byte aligned (the range starts at arena_lo & ~15); the last thread stores byte by byte
+ * so that nothing beyond arena_hi is written.  Pure HBM streaming: 1.25 B moved per base.
+ */
+__global__ void __launch_bounds__(256) sw_unpack2_kernel(const u32 *__restrict__ packed, uint8_t *__restrict__ dst, u64 nbases)
+{
+    const u64 t = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    const u64 base = t * 16;
+    if (base >= nbases) return;
+    const u32 w = packed[t];
+    u32 out[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const u32 b = (w >> (8 * k)) & 0xffu;
+        const u32 sel = (b & 3u) | (b & 0xcu) << 2 | (b & 0x30u) << 4 | (b & 0xc0u) << 6;   /* one code per selector nibble */
+        out[k] = __byte_perm(PACK2_BASES, 0u, sel);
+    }
+    if (base + 16 <= nbases) {
+        *reinterpret_cast<uint4 *>(dst + base) = make_uint4(out[0], out[1], out[2], out[3]);
+    } else {
+        for (u64 k = 0; base + k < nbases; k++) dst[base + k] = (uint8_t)(out[k >> 2] >> (8 * (k & 3)));
+    }
+}
 
 /* ---------------------------------------------------------------- buffers */
 
@@ -49,6 +77,7 @@ void ChunkDev::release()
 {
     units.release(); pair_unit.release(); ops_end.release(); strategy.release();
     h_units.release(); h_pair_unit.release(); h_ops_end.release(); h_strategy.release();
+    packed.release(); h_packed.release();
 }
 
 void WorkSlot::release()
@@ -193,6 +222,7 @@ int Engine::plan_range(const BatchIn &in, int64_t first, int64_t take, ChunkDev 
 {
     std::vector<PairIn> &pairs = cd.pairs_scratch;
     pairs.resize((size_t)take);
+    u64 lo = ~0ull, hi = 0;                /* the byte range of the arena this chunk touches */
     for (int64_t k = 0; k < take; k++) {
         PairIn &p = pairs[(size_t)k];
         p.ref_off = in.ref_off[first + k]; p.alt_off = in.alt_off[first + k];
@@ -202,7 +232,10 @@ int Engine::plan_range(const BatchIn &in, int64_t first, int64_t take, ChunkDev 
             err = "pair " + std::to_string(first + k) + " lies outside the arena";
             return MGL_SW_E_INVALID;
         }
+        lo = std::min<u64>(lo, std::min(p.ref_off, p.alt_off));
+        hi = std::max<u64>(hi, std::max(p.ref_off + p.tl, p.alt_off + p.ql));
     }
+    cd.arena_lo = lo; cd.arena_hi = hi; cd.packed_ok = false;
     const PlanStatus ps = plan_chunk(pairs.data(), (u32)take, in.scores, allow_s16, cd.plan);
     if (ps == PLAN_BAD_SCORES) { err = "score set out of range"; return MGL_SW_E_SCORES; }
     if (ps == PLAN_BAD_PAIR) { err = "empty or over-long sequence in batch"; return MGL_SW_E_PAIR; }
@@ -242,6 +275,23 @@ int Engine::plan_range(const BatchIn &in, int64_t first, int64_t take, ChunkDev 
     return MGL_SW_OK;
 }
 
+/*
+ * Transport form of the chunk's byte range (sw_pack.h), packed on a planner thread from a 16-byte aligned
+ * start so that the unpack kernel's stores are aligned.  The few bytes in front of arena_lo are the caller's
+ * too (they belong to an earlier chunk, which writes the same values).  A range with any byte outside ACGT,
+ * or one too small to be worth a second launch, goes up raw.
+ */
+int Engine::pack_chunk(const BatchIn &in, ChunkDev &cd, std::string &err) const
+{
+    cd.packed_ok = false;
+    if (cd.arena_hi <= cd.arena_lo || cd.arena_hi - cd.arena_lo < MGLSW_PACK_MIN_BYTES) return MGL_SW_OK;
+    const u64 lo16 = cd.arena_lo & ~15ull, nb = cd.arena_hi - lo16;
+    const cudaError_t e = cd.h_packed.reserve(pack2_bytes(nb));
+    if (e != cudaSuccess) { err = std::string("pinned alloc: ") + cudaGetErrorString(e); return MGL_SW_E_CUDA; }
+    cd.packed_ok = pack2(in.arena + lo16, nb, (uint8_t *)cd.h_packed.p);
+    return MGL_SW_OK;
+}
+
 int Engine::plan_next(const BatchIn &in, int64_t first, ChunkDev &cd)
 {
     std::string err;
@@ -262,14 +312,17 @@ int Engine::upload_chunk(const BatchIn &in, ChunkDev &cd, cudaStream_t st, bool 
     if ((e = cudaMemcpyAsync(cd.ops_end.p, cd.h_ops_end.p, n * sizeof(u64), cudaMemcpyHostToDevice, st)) != cudaSuccess) return cuda_fail(e, "H2D");
     if ((e = cudaMemcpyAsync(cd.strategy.p, cd.h_strategy.p, n * sizeof(int), cudaMemcpyHostToDevice, st)) != cudaSuccess) return cuda_fail(e, "H2D");
     bs.h2d_bytes += nu * sizeof(UnitDesc) + n * (sizeof(u32) + sizeof(u64) + sizeof(int));
-    if (upload_arena) {
-        /* the byte range of the arena this chunk touches */
-        u64 lo = ~0ull, hi = 0;
-        for (size_t k = 0; k < n; k++) {
-            const int64_t p = cd.first + (int64_t)k;
-            lo = std::min<u64>(lo, std::min(in.ref_off[p], in.alt_off[p]));
-            hi = std::max<u64>(hi, std::max(in.ref_off[p] + in.ref_len[p], in.alt_off[p] + in.alt_len[p]));
-        }
+    if (upload_arena && cd.packed_ok) {
+        const u64 lo16 = cd.arena_lo & ~15ull, nb = cd.arena_hi - lo16;
+        const size_t pb = pack2_bytes(nb);
+        if ((e = cd.packed.reserve(pb)) != cudaSuccess) return cuda_fail(e, "cudaMalloc packed arena");
+        if ((e = cudaMemcpyAsync(cd.packed.p, cd.h_packed.p, pb, cudaMemcpyHostToDevice, st)) != cudaSuccess) return cuda_fail(e, "H2D packed arena");
+        sw_unpack2_kernel<<<(unsigned)((nb / 16 + 256) / 256), 256, 0, st>>>((const u32 *)cd.packed.p, (uint8_t *)arena_dev() + lo16, nb);
+        if ((e = cudaGetLastError()) != cudaSuccess) return cuda_fail(e, "sw_unpack2_kernel");
+        bs.h2d_bytes += pb;
+        bs.other_launches++;
+    } else if (upload_arena) {
+        const u64 lo = cd.arena_lo, hi = cd.arena_hi;
         if (hi > lo) {
             if ((e = cudaMemcpyAsync((uint8_t *)arena_dev() + lo, in.arena + lo, hi - lo, cudaMemcpyHostToDevice, st)) != cudaSuccess)
                 return cuda_fail(e, "H2D arena");
@@ -502,6 +555,14 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
     /* arena upload policy: per-chunk byte ranges when the arena is laid out pair after pair,
        one up-front copy when pairs share or scatter their sequences */
     const bool whole = in.arena_bytes > total_len + total_len / 2 + 4096 || total_len > in.arena_bytes + in.arena_bytes / 2;
+    /*
+     * 2-bit transport (sw_pack.h) only pays while it overlaps: a planner packs its chunk when it is at least
+     * pack_lead chunks ahead of the one being uploaded -- the GPU or the host link is the slower side and the
+     * thread would otherwise wait for a ring entry -- and sends it raw when the uploader is close behind
+     * (planning is the slower side; packing would only add to it).  pack_arena 2 packs every chunk.
+     */
+    const bool pack_batch = pack_arena != 0 && !whole;
+    std::atomic<int> upload_cursor{0};
     if (whole) {
         if ((e = cudaMemcpyAsync((void *)arena_dev(), in.arena, in.arena_bytes, cudaMemcpyHostToDevice, slots_[0].stream)) != cudaSuccess)
             return cuda_fail(e, "H2D arena");
@@ -597,7 +658,9 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
                 cv.wait(lk, [&] { return stop || k - collected < R; });
                 if (stop) return;
             }
-            const int prc_k = plan_range(in, bounds[(size_t)k].first, bounds[(size_t)k].second, *ring_[(size_t)(k % R)], perr[(size_t)k]);
+            int prc_k = plan_range(in, bounds[(size_t)k].first, bounds[(size_t)k].second, *ring_[(size_t)(k % R)], perr[(size_t)k]);
+            if (prc_k == MGL_SW_OK && pack_batch && (pack_arena == 2 || k - upload_cursor.load(std::memory_order_relaxed) >= pack_lead))
+                prc_k = pack_chunk(in, *ring_[(size_t)(k % R)], perr[(size_t)k]);
             {
                 std::lock_guard<std::mutex> lk(mu);
                 prc[(size_t)k] = prc_k;
@@ -624,6 +687,7 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         const int si = c % MGLSW_SLOTS;
         WorkSlot &ws = slots_[si];
         ChunkDev &cd = *ring_[(size_t)(c % R)];
+        upload_cursor.store(c, std::memory_order_relaxed);
         if (nchunks == 1) {
             std::string err;
             rc = plan_range(in, bounds[0].first, bounds[0].second, cd, err);

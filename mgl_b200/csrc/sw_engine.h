@@ -78,6 +78,10 @@ struct ChunkDev {
     int64_t first = 0; u32 n = 0;
     DevBuf units, pair_unit, ops_end, strategy;
     PinBuf h_units, h_pair_unit, h_ops_end, h_strategy;
+    u64 arena_lo = 0, arena_hi = 0;      /* byte range of the caller's arena the chunk's pairs touch */
+    bool packed_ok = false;              /* h_packed holds [arena_lo & ~15, arena_hi) in the 2-bit transport form (sw_pack.h) */
+    DevBuf packed;
+    PinBuf h_packed;
     std::vector<PairIn> pairs_scratch;
     void release();
 };
@@ -119,6 +123,9 @@ public:
     int plan_threads = 0;        /* host planner threads of align_batch; 0: min(8, hardware threads / 2) */
     int pipe_wide = 1;           /* pipelined long-pair launches on eight warps per pair: 0 never, 1 when the launch has few pairs, 2 always */
     u64 trace_budget_bytes = 0;  /* 0: derived from free memory */
+    int pack_arena = 1;          /* align_batch: all-ACGT byte ranges cross the host link at 2 bits per base (sw_pack.h): */
+                                 /* 0 never, 1 chunks whose planner is pack_lead chunks ahead of the uploader, 2 every chunk */
+    int pack_lead = MGLSW_PACK_LEAD;
 
 private:
     int fail(int code, const std::string &msg);
@@ -126,6 +133,7 @@ private:
     int plan_next(const BatchIn &in, int64_t first, ChunkDev &cd);
     int64_t chunk_take(const BatchIn &in, int64_t first, u64 limit, u32 max_pairs, const u32 *est256) const;
     int plan_range(const BatchIn &in, int64_t first, int64_t take, ChunkDev &cd, std::string &err) const;
+    int pack_chunk(const BatchIn &in, ChunkDev &cd, std::string &err) const;
     int upload_chunk(const BatchIn &in, ChunkDev &cd, cudaStream_t st, bool upload_arena, BatchStats &bs);
     int run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed, bool score_only = false, bool text = false);
     int ensure_slot(WorkSlot &ws, const ChunkPlan &plan, u32 n, bool score_only = false, bool text = false);

@@ -81,6 +81,7 @@ def lib():
         L.mgl_sw_host_alloc.restype = C.c_void_p
         L.mgl_sw_host_free.argtypes = [C.c_void_p]
         L.mgl_sw_host_free.restype = None
+        L.mgl_sw_pack2bit_host.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_int]
         L.mgl_sw_plan_summary.argtypes = [C.POINTER(Batch), C.c_int, C.c_void_p]
         L.mgl_sw_int_peak_name.argtypes = [C.c_int]
         L.mgl_sw_int_peak_name.restype = C.c_char_p

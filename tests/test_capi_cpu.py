@@ -37,6 +37,45 @@ def test_format_cigar(lib):
     assert lib.mgl_sw_format_cigar(ops.ctypes.data, len(ops), buf, 4) == -1
 
 
+def _pack2_numpy(a):
+    """sw_pack.h restated: code = (byte >> 1) & 3, base k in bits 2 (k % 4) of byte k / 4, whole u32 words."""
+    out = np.zeros(((len(a) + 15) // 16) * 4, dtype=np.uint8)
+    codes = np.zeros(len(out) * 4, dtype=np.uint8)
+    codes[:len(a)] = (a >> 1) & 3
+    q = codes.reshape(-1, 4)
+    out[:] = q[:, 0] | q[:, 1] << 2 | q[:, 2] << 4 | q[:, 3] << 6
+    return out
+
+
+@pytest.mark.parametrize("scalar", [0, 1])
+def test_pack2bit_host(lib, scalar):
+    """The host half of the 2-bit transport form: AVX2 and table loop agree with the numpy restatement at every
+    length around the 32-base groups and the 4 KiB validity blocks, from unaligned starts, and any byte outside
+    ACGT -- wherever it sits -- refuses the range (it then travels raw)."""
+    rng = np.random.default_rng(0xACE)
+    src = np.frombuffer(b"ACGT", dtype=np.uint8)[rng.integers(0, 4, 70000)].copy()
+    for n in list(range(0, 70)) + [127, 128, 129, 4095, 4096, 4097, 4128, 8191, 65536, 69999]:
+        for start in (0, 1, 13):
+            a = src[start:start + n]
+            dst = np.full(((len(a) + 15) // 16) * 4 + 8, 0xEE, dtype=np.uint8)
+            assert lib.mgl_sw_pack2bit_host(a.ctypes.data, len(a), dst.ctypes.data, len(dst) - 8, scalar) == 1
+            assert np.array_equal(dst[:-8], _pack2_numpy(a)), (n, start)
+            assert (dst[-8:] == 0xEE).all()                    # nothing written past the packed words
+    # unpacking with the kernel's table gives the bytes back
+    a = src[:1000]
+    packed = _pack2_numpy(a)
+    codes = (packed[:, None] >> np.array([0, 2, 4, 6], dtype=np.uint8)) & 3
+    assert np.array_equal(np.frombuffer(b"ACTG", dtype=np.uint8)[codes.reshape(-1)[:1000]], a)
+    dst = np.zeros(70000, dtype=np.uint8)
+    for pos in (0, 31, 32, 4095, 4096, 40000, 69998, 69999):
+        for bad in (ord("N"), ord("a"), 0, 0x45, 0xC1):
+            b = src[:70000].copy()
+            b[pos] = bad
+            assert lib.mgl_sw_pack2bit_host(b.ctypes.data, len(b), dst.ctypes.data, len(dst), scalar) == 0, (pos, bad)
+    assert lib.mgl_sw_pack2bit_host(src.ctypes.data, 64, dst.ctypes.data, 15, scalar) == -1
+    assert lib.mgl_sw_pack2bit_host(None, 64, dst.ctypes.data, 64, scalar) == -1
+
+
 def test_plan_summary_buckets_config2(lib):
     from mgl_b200 import native, synth
     d = synth.generate(2, 4096)

@@ -145,6 +145,51 @@ def test_synthetic_configs_vs_oracle(sw, oracle, config, n):
         assert (res.cigar(p), int(res.offsets[p])) == exp, (config, p, len(r), len(a))
 
 
+def test_packed_and_raw_transport_give_the_same_results(sw, oracle):
+    """All-ACGT byte ranges may cross the host link at 2 bits per base and are expanded on the device (sw_pack.h); a
+    range holding any other byte travels raw.  Same CIGARs and offsets either way, and equal to the oracle's: every
+    chunk packed, none, the default (chunks planned ahead of the upload), and a batch with N / lower-case bytes in
+    some chunks only (the reference compares raw bytes, SW/sw.cpp:55: N == N, a != A)."""
+    from mgl_b200 import synth
+    n = 24000
+    d = synth.generate(2, n)
+    args = (d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, d["strategies"])
+    sw.set_option("chunk_pairs", 4096)                  # several chunks, each with its own byte range
+    try:
+        sw.set_option("pack_arena", 2)
+        packed = sw.align_arrays(d["arena"], *args)
+        sw.set_option("pack_arena", 0)
+        raw = sw.align_arrays(d["arena"], *args)
+        sw.set_option("pack_arena", 1)
+        auto = sw.align_arrays(d["arena"], *args)
+        sw.set_option("pack_arena", 2)
+        assert packed.stats["h2d_bytes"] < 0.5 * raw.stats["h2d_bytes"]
+        assert packed.stats["h2d_bytes"] <= auto.stats["h2d_bytes"] <= raw.stats["h2d_bytes"]
+        assert packed.stats["other_launches"] > raw.stats["other_launches"]        # the unpack launches
+        for r in (packed, auto):
+            assert np.array_equal(r.offsets, raw.offsets) and np.array_equal(r.cigar_start, raw.cigar_start)
+            assert np.array_equal(r.ops[:int(r.cigar_start[-1])], raw.ops[:int(raw.cigar_start[-1])])
+        for p in range(0, n, 7):
+            r, a = synth.pair_bytes(d, p)
+            assert (packed.cigar(p), int(packed.offsets[p])) == oracle.align(r, a, d["params"], int(d["strategies"][p])), p
+        # other bytes in the first, a middle and the last chunk: those chunks go up raw, the rest packed
+        arena = d["arena"].copy()
+        touched = []
+        for p, byte in ((5, ord("N")), (6, ord("N")), (9000, ord("a")), (n - 1, ord("N")), (n - 2, ord("c"))):
+            arena[int(d["ref_off"][p]) + 40 + len(touched)] = byte
+            arena[int(d["alt_off"][p]) + 20 + len(touched)] = byte
+            touched.append(p)
+        mixed = sw.align_arrays(arena, *args)
+        assert packed.stats["h2d_bytes"] < mixed.stats["h2d_bytes"] < 0.9 * raw.stats["h2d_bytes"]
+        dm = dict(d, arena=arena)
+        for p in sorted(set(touched + list(range(0, n, 11)))):
+            r, a = synth.pair_bytes(dm, p)
+            assert (mixed.cigar(p), int(mixed.offsets[p])) == oracle.align(r, a, d["params"], int(d["strategies"][p])), p
+    finally:
+        sw.set_option("pack_arena", 1)
+        sw.set_option("chunk_pairs", 1 << 16)
+
+
 def test_long_pairs_strip_mined_vs_reference_or_oracle(sw, oracle):
     """config 4 shape (5-10 kbp): the whole-warp strip-mined kernel with HBM carry columns."""
     from mgl_b200 import synth
