@@ -86,7 +86,8 @@ MGL_SW_API const char *mgl_sw_version(void);
 
 /* tuning knobs: "allow_s16" 0/1, "chunk_pairs", "trace_budget_mb", "plan_threads", "pack_arena" 0/1/2 (all-ACGT byte
    ranges of the arena cross the host link at 2 bits per base and are expanded on the device: never / for chunks whose
-   planner thread is "pack_lead" chunks ahead of the upload / always), "pipe_wide" 0/1/2 (long-pair
+   planner thread is "pack_lead" chunks ahead of the upload / always; default 0: it pays only where the link, not the
+   host's cores and memory, is the slower side), "pipe_wide" 0/1/2 (long-pair
    kernel on eight warps per pair: never / for launches of few pairs / always), "overlap" 0/1 (resident_run: 1 = chunks
    alternate between two slots, whole-batch time only; 0 = one chunk at a time with per-kernel times) */
 MGL_SW_API int mgl_sw_set_option(mgl_sw_handle *h, const char *name, int64_t value);

@@ -123,8 +123,10 @@ public:
     int plan_threads = 0;        /* host planner threads of align_batch; 0: min(8, hardware threads / 2) */
     int pipe_wide = 1;           /* pipelined long-pair launches on eight warps per pair: 0 never, 1 when the launch has few pairs, 2 always */
     u64 trace_budget_bytes = 0;  /* 0: derived from free memory */
-    int pack_arena = 1;          /* align_batch: all-ACGT byte ranges cross the host link at 2 bits per base (sw_pack.h): */
-                                 /* 0 never, 1 chunks whose planner is pack_lead chunks ahead of the uploader, 2 every chunk */
+    int pack_arena = 0;          /* align_batch: all-ACGT byte ranges cross the host link at 2 bits per base (sw_pack.h): */
+                                 /* 0 never, 1 chunks whose planner is pack_lead chunks ahead of the uploader, 2 every chunk. */
+                                 /* Off by default: on this pool's boxes the host cores and memory, not the link, are the   */
+                                 /* shared resource (profiles/r03c, r03e: 8 GPUs 8 640 GCUPS raw, 7 875 / 6 255 with 1 / 2)  */
     int pack_lead = MGLSW_PACK_LEAD;
 
 private:

@@ -148,7 +148,7 @@ def test_synthetic_configs_vs_oracle(sw, oracle, config, n):
 def test_packed_and_raw_transport_give_the_same_results(sw, oracle):
     """All-ACGT byte ranges may cross the host link at 2 bits per base and are expanded on the device (sw_pack.h); a
     range holding any other byte travels raw.  Same CIGARs and offsets either way, and equal to the oracle's: every
-    chunk packed, none, the default (chunks planned ahead of the upload), and a batch with N / lower-case bytes in
+    chunk packed, none, chunks planned ahead of the upload only, and a batch with N / lower-case bytes in
     some chunks only (the reference compares raw bytes, SW/sw.cpp:55: N == N, a != A)."""
     from mgl_b200 import synth
     n = 24000
@@ -186,7 +186,7 @@ def test_packed_and_raw_transport_give_the_same_results(sw, oracle):
             r, a = synth.pair_bytes(dm, p)
             assert (mixed.cigar(p), int(mixed.offsets[p])) == oracle.align(r, a, d["params"], int(d["strategies"][p])), p
     finally:
-        sw.set_option("pack_arena", 1)
+        sw.set_option("pack_arena", 0)                  # the library default
         sw.set_option("chunk_pairs", 1 << 16)
 
 
