@@ -32,6 +32,7 @@ def main():
     ap.add_argument("--dense", type=int, default=1_000_000)
     ap.add_argument("--kind", default="dispatch", choices=["dispatch", "scalar", "avx"])
     ap.add_argument("--slice", type=int, default=0, help="pairs per reference call (0: sized for ~1 GB of CIGAR text)")
+    ap.add_argument("--pack", type=int, default=-1, help="pack_arena option (2-bit transport of the arena): 0 / 1 / 2, -1 library default")
     args = ap.parse_args()
 
     import mgl_b200
@@ -45,6 +46,8 @@ def main():
     d = synth.generate(args.config, n)
     sw = mgl_b200.MicrosoftSmithWaterman(0)
     sw._ensure()
+    if args.pack >= 0:
+        sw.set_option("pack_arena", args.pack)
     total_len = int(d["ref_len"].astype(np.int64).sum() + d["alt_len"].astype(np.int64).sum())
     t0 = time.perf_counter()
     res = sw.align_arrays(d["arena"], d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, d["strategies"],
@@ -79,7 +82,7 @@ def main():
     mism = sum(1 for b in bad if b != "...")
     print(json.dumps({"config": args.config, "pairs": n, "checked": checked, "mismatches_shown": mism, "bit_exact": not bad,
                       "cells": int(d["cells"]), "reference": f"oracle/_ref {args.kind}, {threads} threads, {ref_s:.1f} s",
-                      "gpu_e2e_s": round(gpu_s, 3), "pairs_s16": int(res.stats["pairs_s16"]), "pairs_s32": int(res.stats["pairs_s32"]),
+                      "gpu_e2e_s": round(gpu_s, 3), "pack_arena": args.pack, "h2d_bytes": int(res.stats["h2d_bytes"]), "pairs_s16": int(res.stats["pairs_s16"]), "pairs_s32": int(res.stats["pairs_s32"]),
                       "first_bad": bad}))
     sw.close()
     return 0 if not bad else 2
