@@ -13,6 +13,7 @@
 #define MGLSW_PIPE_WIDE_WARPS 8    /* warps per pair of the latency-shaped pipelined kernel (launches of few long pairs) */
 #define MGLSW_PIPE_WIDE_MAX_UNITS 160  /* a chunk with at most this many pipelined pairs uses it */
 #define MGLSW_PIPE_MIN_STRIPS 4   /* pairs of at least this many strips run one per block, strips pipelined over its warps */
+#define MGLSW_SPIN_MIN_CPUS_PER_GPU 0 /* below this many hardware threads per visible GPU the collecting thread sleeps on its events (0: always spin) */
 #define MGLSW_PACK_LEAD 6          /* chunks a planner must be ahead of the uploader to spend time packing its chunk */
 #define MGLSW_PACK_MIN_BYTES 65536 /* a chunk's arena byte range below this is uploaded raw (one copy, no unpack launch) */
 

@@ -107,11 +107,26 @@ Engine::Engine(int device) : device_(device)
     if (cudaSetDevice(device_) != cudaSuccess) { err_ = "cudaSetDevice failed"; return; }
     int prio_lo = 0, prio_hi = 0;
     cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+    /*
+     * The two events align_batch's collecting thread waits on.  A plain event makes that thread spin on a CPU for the
+     * whole batch; with one process per GPU on a box of few CPUs per GPU that CPU is one the planner threads lack.
+     * MGL_SW_BLOCKING_SYNC=1 / 0 forces sleeping / spinning waits; unset: sleep when the box has fewer than
+     * MGLSW_SPIN_MIN_CPUS_PER_GPU hardware threads per visible GPU.
+     */
+    bool blocking = false;
+    {
+        const char *v = std::getenv("MGL_SW_BLOCKING_SYNC");
+        int ndev = 1;
+        if (v && (v[0] == '0' || v[0] == '1')) blocking = v[0] == '1';
+        else if (cudaGetDeviceCount(&ndev) == cudaSuccess && ndev > 0)
+            blocking = std::thread::hardware_concurrency() < (unsigned)ndev * MGLSW_SPIN_MIN_CPUS_PER_GPU;
+    }
+    const unsigned wait_flags = cudaEventDisableTiming | (blocking ? cudaEventBlockingSync : 0u);
     for (auto &s : slots_) {
         cudaStreamCreateWithPriority(&s.stream, cudaStreamNonBlocking, prio_lo);
         cudaStreamCreateWithPriority(&s.post, cudaStreamNonBlocking, prio_hi);
-        cudaEventCreateWithFlags(&s.ev_counts, cudaEventDisableTiming);
-        cudaEventCreateWithFlags(&s.ev_done, cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&s.ev_counts, wait_flags);
+        cudaEventCreateWithFlags(&s.ev_done, wait_flags);
         cudaEventCreateWithFlags(&s.ev_fill, cudaEventDisableTiming);
         cudaEventCreateWithFlags(&s.ev_post, cudaEventDisableTiming);
         cudaEventCreateWithFlags(&s.ev_fork, cudaEventDisableTiming);
