@@ -6,15 +6,22 @@ haplotypes, scores (10,-15,-30,-5), SOFTCLIP) per GPU.
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--pairs P] [--config C]
 
 A step is one pass of the hot path over the whole batch.  `value` is GCUPS with
-inputs resident in HBM (CUDA events on the launching stream, summed over the
-batch's kernels, max over ranks); `e2e` is the same metric through the C-ABI
-mgl_sw_align_batch with pinned HOST buffers in and out.  N > 1: one process per
-GPU (torchrun), each rank aligns its own shard of the synthetic stream, no
-data-path collective (pairs are independent) -> weak scaling.
+inputs resident in HBM (CUDA events on the launching streams around the whole
+batch, max over ranks); `e2e` is the same metric through the C-ABI
+mgl_sw_align_batch with pinned HOST buffers in and out (`e2e_pageable`: the same
+call from ordinary pageable memory, what a JVM direct ByteBuffer is).  N > 1: one
+process per GPU (torchrun), each rank aligns its own shard of the synthetic
+stream, no data-path collective (pairs are independent) -> weak scaling.
+
+The N = 1 line also carries `configs`: BASELINE.json configs 3, 4 and 5 measured
+the same way (3 steps each), and `pairhmm`, the library's second kernel; the
+N > 1 line carries `config5` (the scaling sweep's workload, 1 M mixed pairs per
+GPU standing in for 100 M: at ~1.4 TCUPS the full 1.5e13 cells are ~3 GPU-hours)
+and `multi_handle`: ONE process driving all N GPUs through mgl_sw_create_multi.
 
 --impl reference times the reference's own CPU implementation (oracle/_ref:
-the unmodified align_avx / align_scalar behind the JNI dispatch rule, all host
-threads) on a bounded sample of the same workload.
+the unmodified align_avx / align_scalar behind the JNI dispatch rule, every CPU
+this process may run on) on the same pairs per step, rank 0 only.
 """
 import argparse
 import json
@@ -30,9 +37,7 @@ sys.path.insert(0, ROOT)
 METRIC = "GCUPS, Smith-Waterman affine-gap fill + traceback + CIGAR (1 CUP = one DP cell)"
 UNIT = "GCUPS"
 ALGO_OPS_PER_CELL = 10          # SURVEY.md 8(d), counted from sw.cpp:55-93
-# DRAM bytes per DP cell of the fill kernel from the ncu --set full capture of the same command
-# (profiles/r01m_fill_trace_full_config2.txt: K = 20 launch, dram read + write 3.756 GB for 3.365 Gcells)
-NCU_FILL_DRAM_BYTES_PER_CELL = {2: 1.116}
+SUB_STEPS, SUB_WARMUP = 3, 3    # the `configs` / `config5` sub-records
 
 
 def parse():
@@ -45,20 +50,29 @@ def parse():
     ap.add_argument("--pairs", type=int, default=0, help="pairs per GPU (default: the config's size)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-sub", action="store_true", help="skip the configs / config5 / pairhmm / multi_handle sub-records")
     ap.add_argument("--no-numa-bind", action="store_true", help="N > 1: do not bind each rank to the CPUs local to its GPU")
     ap.add_argument("--chunk-pairs", type=int, default=0, help="engine chunk size (0: library default)")
     ap.add_argument("--pipe-wide", type=int, default=-1, help="long-pair kernel on eight warps per pair: 0 never, 1 auto, 2 always (-1: library default)")
     ap.add_argument("--pack", type=int, default=-1, help="2-bit transport of all-ACGT arena ranges: 0 never, 1 when the planner is ahead, 2 always (-1: library default)")
     ap.add_argument("--pack-lead", type=int, default=-1, help="chunks a planner must be ahead of the upload to pack (-1: library default)")
     ap.add_argument("--plan-threads", type=int, default=0, help="host planner threads (0: library default)")
+    ap.add_argument("--host-plan", type=int, default=-1, help="1: plan chunks on the host (the round-1 path) instead of on the device (-1: library default)")
     return ap.parse_args()
 
 
 DEFAULT_PAIRS = {2: 1_000_000, 3: 100_000, 4: 1_000, 5: 1_000_000}
+SUB_PAIRS = {3: 100_000, 4: 4_000, 5: 1_000_000}
 WORKLOAD = {2: "config 2: 150 bp reads vs 300-500 bp haplotypes, (10,-15,-30,-5), SOFTCLIP",
             3: "config 3: 300-1000 bp hap-to-ref, (200,-150,-260,-11), SOFTCLIP/INDEL",
             4: "config 4: 5-10 kbp pairs, (200,-150,-260,-11), SOFTCLIP",
             5: "config 5: mixed 90 % c2 / 9.9 % c3 / 0.1 % c4 shapes"}
+
+
+def config_dict(config, n):
+    """The workload both arms name, key for key (the driver compares them)."""
+    return {"workload": WORKLOAD[config], "pairs_per_gpu": n,
+            "l2": "inputs_exceed_l2 (arena + checkpoints per step >> 126 MB)", "sharding": "independent pairs, no collective"}
 
 
 class ClockSampler:
@@ -136,6 +150,8 @@ def barrier(dist, local):
         torch.cuda.synchronize(local)
 
 
+# ---------------------------------------------------------------- the reference's CPU path (oracle/_ref)
+
 def cpu_reference_run(d, n_sample, threads, want_output=False):
     """Time the reference's own CPU path (oracle/_ref) on the first n_sample pairs."""
     from oracle import sw_oracle as O
@@ -151,7 +167,7 @@ def cpu_baseline(d, budget_s=12.0):
     from oracle import sw_oracle as O
     if not O.have_ref():
         return None
-    threads = O.ref_max_threads()
+    threads = O.ref_max_threads()                      # the CPUs this process may run on (not OMP_NUM_THREADS)
     n = len(d["ref_len"])
     probe = min(n, max(64, 40 * threads))
     secs, cells = cpu_reference_run(d, probe, threads)
@@ -168,21 +184,28 @@ def cpu_baseline(d, budget_s=12.0):
 
 
 def run_reference(args, rank, world):
-    """--impl reference: the reference's CPU implementation, rank 0 only."""
+    """--impl reference: the reference's CPU implementation on the same pairs per step, rank 0 only.  Maps
+    oracle/ libraries only (the reference, and oracle/'s build of the input generator) -- nothing of the product."""
     if rank != 0:
         return
     from mgl_b200 import synth
     from oracle import sw_oracle as O
+    O.build()
+    synth.use_library(O.SYNTH_SO)           # same generator source, oracle/'s own build of it
     n = args.pairs or DEFAULT_PAIRS[args.config]
-    d = synth.generate(args.config, n)
     if not O.have_ref():
         emit(({"impl": "reference", "unavailable": "oracle/_ref/libmgl_sw_ref.so was not built (no reference sources on this box)"}))
         return
+    d = synth.generate(args.config, n)
     threads = O.ref_max_threads()
+    # every step = the whole per-GPU workload, as in our arm; only where that cannot end within a few minutes
+    # (config 4's long pairs: 56 alignments/s on 16 cores) a step is the first n_sample pairs of it
     probe = min(n, max(64, 40 * threads))
     secs, _ = cpu_reference_run(d, probe, threads)
-    per_step_budget = 60.0 / max(1, args.steps + args.warmup)
-    n_sample = int(min(n, max(probe, probe / max(secs, 1e-6) * min(per_step_budget, 10.0))))
+    per_step_budget = 240.0 / max(1, args.steps + args.warmup)
+    n_sample = int(min(n, max(probe, probe / max(secs, 1e-6) * per_step_budget)))
+    if n_sample > 0.8 * n:
+        n_sample = n
     for _ in range(args.warmup):
         cpu_reference_run(d, n_sample, threads)
     tot_s, tot_cells = 0.0, 0
@@ -191,12 +214,13 @@ def run_reference(args, rank, world):
         tot_s += s
         tot_cells += c
     val = tot_cells / tot_s / 1e9
-    sample = f"each step = first {n_sample} pairs of the workload ({tot_cells / args.steps / 1e9:.2f} Gcells)"
+    sample = (f"each step = all {n} pairs of the per-GPU workload" if n_sample == n else
+              f"each step = first {n_sample} of the {n} pairs of the per-GPU workload") + f" ({tot_cells / args.steps / 1e9:.2f} Gcells)"
     emit(({
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": tot_s / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "int32", "data": "synthetic",
-        "config": {"workload": WORKLOAD[args.config], "pairs_per_step": n_sample},
+        "config": config_dict(args.config, n),
         "alignments_per_s": n_sample * args.steps / tot_s,
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "reference", "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -240,6 +264,136 @@ def emit(obj):
     _REAL_STDOUT.flush()
 
 
+# ---------------------------------------------------------------- our arm: one workload, measured three ways
+
+def measure_device(sw, d, steps, warmup, dist, local):
+    """Inputs resident in HBM, kernels timed with CUDA events on their streams.
+    Pass 1 (`value`): the engine's production schedule -- chunks rotate through the work slots, so the traceback of
+    chunk c overlaps the fill of the next chunks; one event pair brackets the whole batch.
+    Pass 2 (roofline of the dominant kernel): one chunk at a time, every phase bracketed by events on its stream."""
+    sw.resident_prepare(d["arena"], d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, d["strategies"])
+    sw.set_option("overlap", 1)
+    for _ in range(warmup):
+        sw.resident_run()
+    barrier(dist, local)
+    r = {"dev_ms": 0.0, "launches": 0}
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        st = sw.resident_run()
+        r["dev_ms"] += st["device_ms"]
+        r["launches"] += st["fill_launches"] + st["other_launches"]
+    barrier(dist, local)
+    r["wall_ms"] = (time.perf_counter() - t0) * 1e3
+    r["cells_step"] = st["cells"]
+    r["all_s16"] = st["pairs_s32"] == 0 and st["pairs_s16"] > 0     # every pair in u16x2 arithmetic: two cells per lane-op
+    r["pairs_s16"], r["pairs_s32"] = st["pairs_s16"], st["pairs_s32"]
+    r["ckpt_bytes_step"] = st["trace_bytes"]           # checkpoint bytes the fill launches of one step write (planner's count)
+    sw.set_option("overlap", 0)
+    r.update(fill_ms=0.0, trace_ms=0.0, post_ms=0.0, serial_ms=0.0, fill_launches=0)
+    for k in range(min(warmup, 2) + steps):
+        st = sw.resident_run()
+        if k >= min(warmup, 2):
+            r["fill_ms"] += st["fill_ms"]; r["trace_ms"] += st["trace_ms"]; r["post_ms"] += st["post_ms"]
+            r["serial_ms"] += st["device_ms"]; r["fill_launches"] += st["fill_launches"]
+    sw.set_option("overlap", 1)
+    sw.resident_drop()
+    return r
+
+
+def ops_capacity(d):
+    import numpy as np
+    # CIGAR element capacity: 8 per pair covers the short-read configs; long pairs carry ~1 element per 40 bases
+    total_len = int(d["ref_len"].astype(np.int64).sum() + d["alt_len"].astype(np.int64).sum())
+    return max(8 * len(d["ref_len"]), total_len // 8)
+
+
+def measure_e2e(sw, d, steps, warmup, dist, local, pinned=True):
+    """mgl_sw_align_batch, host buffers in and out, copies inside the timed region.  pinned=False: the caller's
+    arena and result arrays are ordinary pageable memory (a JVM direct ByteBuffer)."""
+    import numpy as np
+    from mgl_b200 import native
+    n = len(d["ref_len"])
+    alloc = native.pinned_array if pinned else (lambda shape, dt: np.zeros(shape, dtype=dt))
+    out = (alloc(n, np.int32), alloc(n + 1, np.uint64), alloc(ops_capacity(d), np.uint32))
+    arena = d["arena"] if pinned else np.array(d["arena"], copy=True)
+    call = lambda: sw.align_arrays(arena, d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, d["strategies"], out=out)
+    for _ in range(warmup):
+        call()
+    barrier(dist, local)
+    t0, c0 = time.perf_counter(), time.process_time()
+    for _ in range(steps):
+        r = call()
+    ms, cpu_s = (time.perf_counter() - t0) * 1e3, time.process_time() - c0
+    barrier(dist, local)
+    return ms, int(r.stats["h2d_bytes"]), int(r.stats["d2h_bytes"]), cpu_s
+
+
+def measure_score_only(sw, d, steps, dist, local):
+    import numpy as np
+    from mgl_b200 import native
+    n = len(d["ref_len"])
+    so_out = native.pinned_array(3 * n, np.int32).reshape(n, 3)
+    call = lambda: sw.score_arrays(d["arena"], d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, d["strategies"], out=so_out)
+    call()
+    barrier(dist, local)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        call()
+    ms = (time.perf_counter() - t0) * 1e3
+    barrier(dist, local)
+    return ms
+
+
+def rooflines(r, d, K, p_int32, hbm_peak, measured):
+    """roofline / roofline_hbm of the fill launches of one workload from measure_device()'s per-kernel pass."""
+    fill_cups = r["cells_step"] * K / (r["fill_ms"] * 1e-3)
+    # the denominator in the arithmetic the kernel runs: a u16x2 lane-op is two 16-bit cell-ops
+    p_int = (2.0 * p_int32 if r["all_s16"] else p_int32) if p_int32 else None
+    launches_step = max(1, r["fill_launches"] // K)
+    arena_bytes = int(d["arena"].nbytes)
+    ach = fill_cups * ALGO_OPS_PER_CELL / 1e9
+    roof = {"bound": "int", "achieved": ach, "peak": p_int, "unit": "Gop/s", "frac": (ach / p_int) if p_int else None,
+            "traffic": (r["ckpt_bytes_step"] + arena_bytes) / launches_step,
+            "note": "dominant kernel = sw_fill_kernel (all its launches of a step, timed with CUDA events on their stream in the "
+                    "one-chunk-at-a-time pass); algorithmic 10 int ops/cell (SURVEY.md 8d) x cells; peak = max(iadd3, imnmx) measured "
+                    "live by int_peak.cu (not in MEASURED_PEAKS.json)"
+                    + (", x 2 because every pair of this workload runs in u16x2 arithmetic (one lane-op = two 16-bit cell-ops); "
+                       "against the plain 32-bit peak (peak_s32) the fraction would be twice this" if r["all_s16"] else
+                       "; pairs that run in u16x2 arithmetic do two cells per lane-op, so a mixed workload can exceed its 32-bit fraction")
+                    + "; traffic = bytes counted in THIS run per average fill launch: the checkpoint bytes the planner laid out "
+                      "(= what the launches write; ncu dram__bytes_write agrees within 1 %, profiles/) + the arena bytes they read once",
+            "peak_s32": p_int32}
+    hbm = {"bound": "hbm", "achieved": r["ckpt_bytes_step"] * K / (r["fill_ms"] * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+           "frac": r["ckpt_bytes_step"] * K / (r["fill_ms"] * 1e-3) / 1e9 / hbm_peak,
+           "algorithmic_bytes_per_cell": 0.5, "checkpoint_bytes_per_cell": r["ckpt_bytes_step"] / r["cells_step"],
+           "note": "checkpoint writes of the fill kernel (the only O(cells) HBM traffic on the path) against MEASURED_PEAKS.json hbm_gbs"
+                   + ("" if measured else " (fallback 6650)") + "; algorithmic = SURVEY.md 8d's 4-bit trace"}
+    return roof, hbm
+
+
+def sub_config(sw, config, n, rank, dist, local, p_int32, hbm_peak, measured, want_e2e=True):
+    """One BASELINE.json config as a sub-record: value, fill ms, roofline fraction, checkpoint B/cell, e2e."""
+    from mgl_b200 import synth
+    d = synth.generate(config, n, first=rank * n, pinned=True)
+    r = measure_device(sw, d, SUB_STEPS, SUB_WARMUP, dist, local)
+    e2e_ms = measure_e2e(sw, d, SUB_STEPS, 1, dist, local)[0] if want_e2e else 0.0
+    (dev_ms, fill_ms, e2e_ms), (cells_all, pairs_all) = reduce_max_sum(
+        dist, local, [r["dev_ms"], r["fill_ms"], e2e_ms], [float(r["cells_step"]), float(n)])
+    if rank != 0:
+        return None
+    K = SUB_STEPS
+    roof, hbm = rooflines(r, d, K, p_int32, hbm_peak, measured)
+    rec = {"workload": WORKLOAD[config], "pairs_per_gpu": n, "cells_per_gpu": r["cells_step"], "steps": K, "warmup": SUB_WARMUP,
+           "value": cells_all * K / (dev_ms * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": dev_ms / K,
+           "fill_ms_per_step": r["fill_ms"] / K, "traceback_ms_per_step": r["trace_ms"] / K, "fill_launches": r["fill_launches"] // K,
+           "pairs_s16": r["pairs_s16"], "pairs_s32": r["pairs_s32"],
+           "frac": roof["frac"], "roofline_peak_gops": roof["peak"], "checkpoint_bytes_per_cell": hbm["checkpoint_bytes_per_cell"],
+           "hbm_frac": hbm["frac"], "traffic": roof["traffic"]}
+    if want_e2e:
+        rec["e2e"] = {"value": cells_all * K / (e2e_ms * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": e2e_ms / K}
+    return rec
+
+
 def main():
     args = parse()
     protect_stdout()
@@ -259,16 +413,12 @@ def main():
     d = synth.generate(args.config, n, first=rank * n, pinned=True)       # this rank's shard of the stream
     sw = mgl_b200.MicrosoftSmithWaterman(local)
     sw._ensure()                                                          # no GPU / no extension -> raises
-    if args.chunk_pairs:
-        sw.set_option("chunk_pairs", args.chunk_pairs)
-    if args.pipe_wide >= 0:
-        sw.set_option("pipe_wide", args.pipe_wide)
-    if args.plan_threads:
-        sw.set_option("plan_threads", args.plan_threads)
-    if args.pack >= 0:
-        sw.set_option("pack_arena", args.pack)
-    if args.pack_lead >= 0:
-        sw.set_option("pack_lead", args.pack_lead)
+    for name, v in (("chunk_pairs", args.chunk_pairs), ("plan_threads", args.plan_threads)):
+        if v:
+            sw.set_option(name, v)
+    for name, v in (("pipe_wide", args.pipe_wide), ("pack_arena", args.pack), ("pack_lead", args.pack_lead), ("host_plan", args.host_plan)):
+        if v >= 0:
+            sw.set_option(name, v)
 
     # integer issue rates (roofline denominator), measured on this box
     peaks = {}
@@ -279,134 +429,96 @@ def main():
             ops, mhz = C.c_double(), C.c_double()
             if L.mgl_sw_int_peak(local, k, C.byref(ops), C.byref(mhz)) == 0:
                 peaks[L.mgl_sw_int_peak_name(k).decode()] = ops.value / 1e9
+    p_int32 = max(peaks.get("iadd3_s32", 0.0), peaks.get("imnmx_s32", 0.0)) or None
+    measured = {}
+    try:
+        measured = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = measured.get("hbm_gbs", 6650.0)
 
-    # ---- value: inputs resident in HBM, kernels timed with CUDA events on their streams.
-    # Pass 1 (the reported value): the engine's production schedule -- chunks alternate between two work slots, so the
-    # latency-bound traceback of chunk c overlaps the fill of chunk c + 1; one event pair brackets the whole batch.
-    # Pass 2 (roofline of the dominant kernel): one chunk at a time, every phase bracketed by events on its stream.
-    sw.resident_prepare(d["arena"], d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, d["strategies"])
-    sw.set_option("overlap", 1)
-    for _ in range(args.warmup):
-        sw.resident_run()
-    barrier(dist, local)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    dev_ms = 0.0
-    launches = 0
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        st = sw.resident_run()
-        dev_ms += st["device_ms"]
-        launches += st["fill_launches"] + st["other_launches"]
-    barrier(dist, local)
-    wall_ms = (time.perf_counter() - t0) * 1e3
-    cells_step = st["cells"]
-    all_s16 = st["pairs_s32"] == 0 and st["pairs_s16"] > 0    # every pair in u16x2 arithmetic: two cells per lane-op
-    ckpt_bytes_step = st["trace_bytes"]                 # checkpoint bytes the fill launches of one step write (planner's count)
-    sw.set_option("overlap", 0)
-    fill_ms = trace_ms = post_ms = serial_ms = 0.0
-    fill_launches = 0
-    for k in range(args.warmup + args.steps):
-        st = sw.resident_run()
-        if k >= args.warmup:
-            fill_ms += st["fill_ms"]; trace_ms += st["trace_ms"]; post_ms += st["post_ms"]; serial_ms += st["device_ms"]
-            fill_launches += st["fill_launches"]
-    sw.set_option("overlap", 1)
-    sw.resident_drop()
+    r = measure_device(sw, d, args.steps, args.warmup, dist, local)
 
-    # ---- e2e: host buffers through the C-ABI, copies inside the timed region
-    e2e_ms = 0.0
+    # ---- e2e: host buffers through the C-ABI, copies inside the timed region; then the score-only entry
+    e2e_ms = so_ms = pg_ms = e2e_cpu_s = 0.0
     h2d = d2h = 0
     if not args.no_e2e:
-        # CIGAR element capacity: 8 per pair covers the short-read configs; long pairs carry ~1 element per 40 bases
-        total_len = int(d["ref_len"].astype(np.int64).sum() + d["alt_len"].astype(np.int64).sum())
-        out = (native.pinned_array(n, np.int32), native.pinned_array(n + 1, np.uint64),
-               native.pinned_array(max(8 * n, total_len // 8), np.uint32))
-        for _ in range(min(args.warmup, 2)):
-            sw.align_arrays(d["arena"], d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, d["strategies"], out=out)
-        barrier(dist, local)
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            r = sw.align_arrays(d["arena"], d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, d["strategies"], out=out)
-            h2d, d2h = r.stats["h2d_bytes"], r.stats["d2h_bytes"]
-        e2e_ms = (time.perf_counter() - t0) * 1e3
-        barrier(dist, local)
-
-    # ---- score only: same host buffers through mgl_sw_score_batch, no checkpoints, no traceback
-    so_ms = 0.0
+        e2e_ms, h2d, d2h, e2e_cpu_s = measure_e2e(sw, d, args.steps, min(args.warmup, 2), dist, local)
+        so_ms = measure_score_only(sw, d, args.steps, dist, local)
+    clocks = sampler.stop() if rank == 0 else None     # sampled over the timed passes (value, per-kernel, e2e)
     if not args.no_e2e:
-        so_out = native.pinned_array(3 * n, np.int32).reshape(n, 3)
-        sw.score_arrays(d["arena"], d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, d["strategies"], out=so_out)
-        barrier(dist, local)
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            sw.score_arrays(d["arena"], d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, d["strategies"], out=so_out)
-        so_ms = (time.perf_counter() - t0) * 1e3
-        barrier(dist, local)
+        pg_ms = measure_e2e(sw, d, min(args.steps, 5), 1, dist, local, pinned=False)[0]
+    pg_steps = min(args.steps, 5)
 
-    clocks = sampler.stop() if rank == 0 else None     # sampled over all three timed passes (value, per-kernel, e2e)
-    (dev_ms, fill_ms, wall_ms, e2e_ms, so_ms), (cells_all, pairs_all) = reduce_max_sum(
-        dist, local, [dev_ms, fill_ms, wall_ms, e2e_ms, so_ms], [float(cells_step), float(n)])
+    (dev_ms, fill_ms, wall_ms, e2e_ms, so_ms, pg_ms), (cells_all, pairs_all) = reduce_max_sum(
+        dist, local, [r["dev_ms"], r["fill_ms"], r["wall_ms"], e2e_ms, so_ms, pg_ms], [float(r["cells_step"]), float(n)])
 
+    line = None
     if rank == 0:
         K = args.steps
-        value = cells_all * K / (dev_ms * 1e-3) / 1e9
-        fill_cups = cells_step * K / (fill_ms * 1e-3)                    # this GPU's fill kernels
-        p_int32 = max(peaks.get("iadd3_s32", 0.0), peaks.get("imnmx_s32", 0.0)) or None
-        # the denominator in the arithmetic the kernel runs: a u16x2 lane-op is two 16-bit cell-ops
-        p_int = (2.0 * p_int32 if all_s16 else p_int32) if p_int32 else None
-        measured = {}
-        try:
-            measured = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-        except Exception:
-            pass
-        hbm_peak = measured.get("hbm_gbs", 6650.0)
+        cells_step = r["cells_step"]
+        roof, hbm = rooflines(r, d, K, p_int32, hbm_peak, measured)
+        cfg = config_dict(args.config, n)
         line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": args.warmup,
+            "metric": METRIC, "value": cells_all * K / (dev_ms * 1e-3) / 1e9, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": args.warmup,
             "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u16x2 (score-safe pairs) / int32", "data": "synthetic",
-            "config": {"workload": WORKLOAD[args.config], "pairs_per_gpu": n, "cells_per_gpu": cells_step,
-                       "l2": "inputs_exceed_l2 (arena + trace per step >> 126 MB)", "sharding": "independent pairs, no collective",
-                       "cpu_binding": (f"each rank on the {numa} CPUs local to its GPU (NVML)" if numa else "none")},
+            "config": cfg,
+            "cells_per_gpu": cells_step,
+            "cpu_binding": (f"each rank on the {numa} CPUs local to its GPU (NVML)" if numa else "none"),
             "alignments_per_s": pairs_all * K / (dev_ms * 1e-3),
             "wall_ms_per_step": wall_ms / K,
-            "kernel_ms_per_step": {"fill": fill_ms / K, "traceback": trace_ms / K, "scan_compact": post_ms / K,
-                                   "serial_total": serial_ms / K, "fill_launches": fill_launches // K,
+            "kernel_ms_per_step": {"fill": r["fill_ms"] / K, "traceback": r["trace_ms"] / K, "scan_compact": r["post_ms"] / K,
+                                   "serial_total": r["serial_ms"] / K, "fill_launches": r["fill_launches"] // K,
                                    "note": "second pass, one chunk at a time, CUDA events around each phase on its stream"},
-            "gpu_launches": int(launches),
+            "gpu_launches": int(r["launches"]),
             "clocks": clocks,
-            "roofline": {"bound": "int", "achieved": fill_cups * ALGO_OPS_PER_CELL / 1e9, "peak": p_int, "unit": "Gop/s",
-                         "frac": (fill_cups * ALGO_OPS_PER_CELL / 1e9 / p_int) if p_int else None,
-                         "traffic": (NCU_FILL_DRAM_BYTES_PER_CELL[args.config] * cells_step / max(1, fill_launches // K))
-                         if args.config in NCU_FILL_DRAM_BYTES_PER_CELL else None,
-                         "note": "dominant kernel = sw_fill_kernel (all its launches of a step, timed with CUDA events on their stream in the "
-                                 "one-chunk-at-a-time pass); algorithmic 10 int ops/cell (SURVEY.md 8d) x cells; peak = max(iadd3, imnmx) measured "
-                                 "live by int_peak.cu (not in MEASURED_PEAKS.json)"
-                                 + (", x 2 because every pair of this workload runs in u16x2 arithmetic (one lane-op = two 16-bit cell-ops); "
-                                    "against the plain 32-bit peak (peak_s32) the fraction would be twice this" if all_s16 else
-                                    "; pairs that run in u16x2 arithmetic do two cells per lane-op, so a mixed workload can exceed its 32-bit fraction")
-                                 + "; traffic = ncu dram bytes per cell x cells per average fill launch",
-                         "peak_s32": p_int32},
-            "roofline_hbm": {"bound": "hbm", "achieved": ckpt_bytes_step * K / (fill_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                             "frac": ckpt_bytes_step * K / (fill_ms * 1e-3) / 1e9 / hbm_peak,
-                             "algorithmic_bytes_per_cell": ckpt_bytes_step / cells_step,
-                             "note": "checkpoint writes of the fill kernel (the only O(cells) HBM traffic on the path); peak = MEASURED_PEAKS.json hbm_gbs"
-                                     + ("" if measured else " (fallback 6650)")},
+            "roofline": roof,
+            "roofline_hbm": hbm,
             "int_peaks_gops": peaks,
         }
         if not args.no_e2e:
             line["e2e"] = {"value": cells_all * K / (e2e_ms * 1e-3) / 1e9, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                            "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms / K,
-                           "alignments_per_s": pairs_all * K / (e2e_ms * 1e-3)}
+                           "alignments_per_s": pairs_all * K / (e2e_ms * 1e-3),
+                           "host_cpu_ns_per_pair": e2e_cpu_s / (n * K) * 1e9,
+                           "host_cpu_note": "process CPU time (all threads of rank 0, spinning waits included) per pair inside the timed e2e calls"}
+            line["e2e_pageable"] = {"value": cells_all * pg_steps / (pg_ms * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": pg_ms / pg_steps,
+                                    "steps": pg_steps,
+                                    "note": "the same call with the caller's arena and result arrays in ordinary pageable memory (what a JVM "
+                                            "direct ByteBuffer is): every cudaMemcpyAsync is staged by the driver"}
             line["score_only_e2e"] = {"value": cells_all * K / (so_ms * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": so_ms / K,
                                       "d2h_bytes_per_step": 12 * n,
                                       "note": "mgl_sw_score_batch, host buffers in and out: the fill without checkpoints, start cell and score per pair"}
-        if world == 1 and not args.no_cpu_baseline:
-            cb = cpu_baseline(d)
-            if cb:
-                line["cpu_baseline"] = cb
+
+    # ---- sub-records (fixed 3 steps each, whatever --steps says)
+    if not args.no_sub and args.config == 2 and not args.pairs:
+        if world == 1:
+            subs = {}
+            for c in (3, 4, 5):
+                rec = sub_config(sw, c, SUB_PAIRS[c], rank, dist, local, p_int32, hbm_peak, measured)
+                subs[str(c)] = rec
+            if line is not None:
+                line["configs"] = subs
+                line["configs_note"] = ("BASELINE.json configs 3, 4, 5 measured like the headline (device-resident value, per-kernel fill time, "
+                                        "e2e through mgl_sw_align_batch), 3 steps after 3 warm-up steps each; config 4 at 4 000 of its 10 000 pairs, "
+                                        "config 5 at 1 M pairs standing in for 100 M (1.5e13 cells ~ 3 GPU-hours at 1.4 TCUPS)")
+        else:
+            rec = sub_config(sw, 5, SUB_PAIRS[5], rank, dist, local, p_int32, hbm_peak, measured)
+            if line is not None:
+                line["config5"] = rec
+                line["config5_note"] = ("BASELINE.json configs[4], the scaling sweep's workload: 1 M mixed pairs PER GPU (weak scaling) standing in "
+                                        "for 100 M pairs in total, which would be ~3 GPU-hours at 1.4 TCUPS")
+    if line is not None and world == 1 and not args.no_cpu_baseline:
+        cb = cpu_baseline(d)
+        if cb:
+            line["cpu_baseline"] = cb
+    if line is not None:
         emit((line))
+    sw.close()
     if dist is not None:
         dist.destroy_process_group()
 

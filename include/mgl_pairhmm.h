@@ -50,7 +50,11 @@ MGL_PH_API const char *mgl_pairhmm_last_error(mgl_pairhmm_handle *h);
  *   reads   : per read  bases | base quals | insertion GOP | deletion GOP | GCP   (readLen bytes each, phred)
  *   haps    : haplotype bases back to back
  *   out     : double[readCount * hapCount], read-major: log10 likelihood
- * Haplotypes of up to 9 000 bases (the carry row of a read longer than one band lives in shared memory).
+ * Reads of up to 256 bases (one band of 32 lanes x 8 rows) run against haplotypes of any length.  A call holding a
+ * longer read keeps a carry row per haplotype column in shared memory and is then limited to haplotypes of 2 344
+ * bases (220 KiB / 4 warps / 24 B): beyond that the call fails with MGL_PH_E_TOO_LONG -- through JNI a
+ * RuntimeException, never a silent result.  (The reference has no such limit; GATK's reads and haplotypes sit far
+ * inside it.)
  */
 MGL_PH_API int mgl_pairhmm_compute(mgl_pairhmm_handle *h, const int32_t *lengths, const uint8_t *reads, const uint8_t *haps,
                                    int use_double, double *out, mgl_pairhmm_stats *stats);

@@ -77,9 +77,28 @@ typedef struct mgl_sw_stats {
     double fill_ms, trace_ms, post_ms, device_ms;
 } mgl_sw_stats;
 
-/* lifecycle: one handle drives one GPU; calls on one handle are serialised internally */
+/* lifecycle: a handle drives one GPU, or a list of them; calls on one handle are serialised internally */
 MGL_SW_API int mgl_sw_create(int device, mgl_sw_handle **out);
+/*
+ * One handle over several GPUs of the box (SURVEY.md 8b "handle create/destroy (device list, streams)", 8e): every
+ * batch call on it cuts the batch into n_devices contiguous ranges of near-equal DP cells, runs range k on
+ * devices[k] (one host thread and one engine per device, nothing exchanged between GPUs: pairs are independent)
+ * and gathers the results in input order.  The same device may be listed more than once.  The resident_* entries
+ * use devices[0] only.
+ */
+MGL_SW_API int mgl_sw_create_multi(const int *devices, int n_devices, mgl_sw_handle **out);
+MGL_SW_API int mgl_sw_handle_devices(mgl_sw_handle *h, int *devices, int cap);   /* returns the device count */
 MGL_SW_API void mgl_sw_destroy(mgl_sw_handle *h);
+/*
+ * The process-wide handle behind the entry points that carry no handle (mgl_sw_align_one and the JNI symbols):
+ * created by the first caller over every visible GPU, or the comma-separated MGL_SW_DEVICES list, or the one device
+ * MGL_SW_DEVICE names.  mgl_sw_default_handle pins it (a reference count), mgl_sw_default_release unpins it;
+ * mgl_sw_shutdown -- what doneNative calls, MicrosoftSmithWaterman.java:89-92 -- waits for pinned users, then
+ * destroys it and frees its device memory; a later call creates it afresh.
+ */
+MGL_SW_API int mgl_sw_default_handle(mgl_sw_handle **out);
+MGL_SW_API void mgl_sw_default_release(void);
+MGL_SW_API void mgl_sw_shutdown(void);
 MGL_SW_API const char *mgl_sw_last_error(mgl_sw_handle *h);
 MGL_SW_API int mgl_sw_device_count(void);
 MGL_SW_API const char *mgl_sw_version(void);
@@ -88,7 +107,8 @@ MGL_SW_API const char *mgl_sw_version(void);
    ranges of the arena cross the host link at 2 bits per base and are expanded on the device: never / for chunks whose
    planner thread is "pack_lead" chunks ahead of the upload / always; default 0: it pays only where the link, not the
    host's cores and memory, is the slower side), "pipe_wide" 0/1/2 (long-pair
-   kernel on eight warps per pair: never / for launches of few pairs / always), "overlap" 0/1 (resident_run: 1 = chunks
+   kernel on eight warps per pair: never / for launches of few pairs / always), "host_plan" 0/1 (chunks planned by
+   device kernels / by host threads; the 2-bit transport implies host planning), "overlap" 0/1 (resident_run: 1 = chunks
    alternate between two slots, whole-batch time only; 0 = one chunk at a time with per-kernel times) */
 MGL_SW_API int mgl_sw_set_option(mgl_sw_handle *h, const char *name, int64_t value);
 
@@ -146,11 +166,6 @@ MGL_SW_API int mgl_sw_pack2bit_host(const uint8_t *src, uint64_t n, uint8_t *dst
 
 /* planning only (no GPU needed): how a batch would be bucketed; used by tests and tools */
 MGL_SW_API int mgl_sw_plan_summary(const mgl_sw_batch *batch, int allow_s16, uint64_t *out8);
-
-/* deterministic synthetic pairs of BASELINE.json configs 2..5 (sw_synth.cpp): sizes first, then bytes */
-MGL_SW_API int mgl_sw_synth_sizes(int config, uint64_t seed, uint64_t first, int64_t n, uint32_t *ref_len, uint32_t *alt_len);
-MGL_SW_API int mgl_sw_synth_fill(int config, uint64_t seed, uint64_t first, int64_t n, const uint64_t *ref_off,
-                                 const uint64_t *alt_off, uint8_t *arena);
 
 /* integer issue-rate microbenchmarks for the roofline denominator */
 MGL_SW_API int mgl_sw_int_peak_count(void);

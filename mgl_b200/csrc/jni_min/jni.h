@@ -1,11 +1,12 @@
 /*
  * Minimal, ABI-faithful <jni.h> for building the JNI entry points on a machine
  * without a JDK (this image has none).  Only what the Smith-Waterman binding
- * touches is declared: the primitive typedefs and JNIEnv::GetDirectBufferAddress.
+ * touches is declared: the primitive typedefs, JNIEnv::GetDirectBufferAddress, and
+ * FindClass / ThrowNew (a failed native call raises a Java RuntimeException).
  *
  * The JNIEnv layout follows the JNI specification's "Interface Function Table":
- * JNIEnv points to a table of function pointers in which slots 0-3 are reserved
- * and GetDirectBufferAddress is slot 230.  A library compiled against this
+ * JNIEnv points to a table of function pointers in which slots 0-3 are reserved,
+ * FindClass is slot 6, ThrowNew slot 14 and GetDirectBufferAddress slot 230.  A library compiled against this
  * header therefore calls the right slot of a real JVM's table.  When a JDK is
  * available, build with -I$JAVA_HOME/include -I$JAVA_HOME/include/linux instead
  * (mgl_b200/csrc/Makefile picks that up from JAVA_HOME).
@@ -36,6 +37,8 @@ typedef struct _jobject *jobject;
 typedef jobject jclass;
 #endif
 
+#define MGL_JNI_SLOT_FindClass 6
+#define MGL_JNI_SLOT_ThrowNew 14
 #define MGL_JNI_SLOT_GetDirectBufferAddress 230
 #define MGL_JNI_TABLE_SLOTS 235
 
@@ -48,7 +51,11 @@ typedef const struct JNINativeInterface_ *JNIEnv;
 #endif
 
 struct JNINativeInterface_ {
-    void *slots_0_229[MGL_JNI_SLOT_GetDirectBufferAddress];
+    void *slots_0_5[MGL_JNI_SLOT_FindClass];
+    jclass (JNICALL *FindClass)(JNIEnv *env, const char *name);
+    void *slots_7_13[MGL_JNI_SLOT_ThrowNew - MGL_JNI_SLOT_FindClass - 1];
+    jint (JNICALL *ThrowNew)(JNIEnv *env, jclass clazz, const char *msg);
+    void *slots_15_229[MGL_JNI_SLOT_GetDirectBufferAddress - MGL_JNI_SLOT_ThrowNew - 1];
     void *(JNICALL *GetDirectBufferAddress)(JNIEnv *env, jobject buf);
     void *slots_231_234[MGL_JNI_TABLE_SLOTS - MGL_JNI_SLOT_GetDirectBufferAddress - 1];
 };
@@ -57,6 +64,8 @@ struct JNINativeInterface_ {
 struct JNIEnv_ {
     const struct JNINativeInterface_ *functions;
     void *GetDirectBufferAddress(jobject buf) { return functions->GetDirectBufferAddress(this, buf); }
+    jclass FindClass(const char *name) { return functions->FindClass(this, name); }
+    jint ThrowNew(jclass clazz, const char *msg) { return functions->ThrowNew(this, clazz, msg); }
 };
 #endif
 

@@ -158,17 +158,22 @@ int Engine::cuda_fail(cudaError_t e, const char *what)
     return MGL_SW_E_CUDA;
 }
 
-/* device arena = front pad | caller's bytes | tail pad long enough for the rows a lane reads past its ref */
+/*
+ * device arena = front pad | the caller's bytes [base, base + span) | tail pad long enough for the rows a lane reads
+ * past its ref.  Only the byte range a batch's pairs touch is kept on the device (a shard of a multi-GPU call touches
+ * 1 / n of the caller's arena); arena_dev() is biased by -base so that device code keeps using the caller's offsets.
+ */
 int Engine::reserve_arena(const BatchIn &in)
 {
     u32 max_tl = 0;
     for (int64_t p = 0; p < in.n; p++) max_tl = std::max(max_tl, in.ref_len[p]);
-    return reserve_arena(in, max_tl);
+    return reserve_arena(0, in.arena_bytes, max_tl);
 }
 
-int Engine::reserve_arena(const BatchIn &in, u32 max_tl)
+int Engine::reserve_arena(u64 base, u64 span, u32 max_tl)
 {
-    const size_t need = MGLSW_ARENA_FRONT_PAD + in.arena_bytes + arena_tail_pad(max_tl);
+    arena_base_ = base;
+    const size_t need = MGLSW_ARENA_FRONT_PAD + span + arena_tail_pad(max_tl);
     if (need > arena_.cap) {
         cudaError_t e = arena_.reserve(need);
         if (e != cudaSuccess) return cuda_fail(e, "cudaMalloc arena");
@@ -243,7 +248,7 @@ int Engine::plan_range(const BatchIn &in, int64_t first, int64_t take, ChunkDev 
         p.ref_off = in.ref_off[first + k]; p.alt_off = in.alt_off[first + k];
         p.tl = in.ref_len[first + k]; p.ql = in.alt_len[first + k];
         p.strategy = in.strategies ? in.strategies[first + k] : in.strategy;
-        if (p.ref_off + p.tl > in.arena_bytes || p.alt_off + p.ql > in.arena_bytes) {
+        if (p.ref_off > in.arena_bytes || p.tl > in.arena_bytes - p.ref_off || p.alt_off > in.arena_bytes || p.ql > in.arena_bytes - p.alt_off) {
             err = "pair " + std::to_string(first + k) + " lies outside the arena";
             return MGL_SW_E_INVALID;
         }
@@ -510,31 +515,35 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
     if ((e = cudaSetDevice(device_)) != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
     resident_scores_ = in.scores;
     out.ops_total = 0;
-    if (!so) out.cigar_start[0] = 0;
+    if (!so && !out.keep_first_start) out.cigar_start[0] = 0;
     if (in.n == 0) { if (stats) *stats = bs; return MGL_SW_OK; }
     /* one parallel pass over the pair table: longest ref, total length, per-pair checkpoint estimate (units of 256 B).
        Short-lived std::threads, not OpenMP: an OpenMP team keeps spinning after the loop and takes the cores the
        planner threads need in the next few milliseconds (measured: first chunks planned 3x slower). */
     u32 max_tl = 0;
     u64 total_len = 0, total_est = 0;
+    u64 span_lo = ~0ull, span_hi = 0;                 /* the byte range of the caller's arena this batch touches (wrapped offsets are refused by plan_range) */
     estpre_.resize((size_t)in.n);                     /* per slice: inclusive prefix sums of the per-pair checkpoint estimate (bytes) */
-    const int T = in.n > 65536 ? (int)std::min<unsigned>(8u, std::max(1u, std::thread::hardware_concurrency() / 2)) : 1;
+    const int T = in.n > 65536 ? (scan_threads > 0 ? scan_threads : (int)std::min<unsigned>(8u, std::max(1u, std::thread::hardware_concurrency() / 2))) : 1;
     std::vector<u64> slice_off((size_t)T + 1, 0);
     {
         std::vector<u32> tmax((size_t)T, 0);
-        std::vector<u64> tsum((size_t)T, 0), tes((size_t)T, 0);
+        std::vector<u64> tsum((size_t)T, 0), tes((size_t)T, 0), tlo((size_t)T, ~0ull), thi((size_t)T, 0);
         auto scan = [&](int t) {
             const int64_t lo = in.n * t / T, hi = in.n * (t + 1) / T;
-            u32 m = 0; u64 sum = 0, es = 0;
+            u32 m = 0; u64 sum = 0, es = 0, alo = ~0ull, ahi = 0;
             u64 *pre = estpre_.data();
             for (int64_t p = lo; p < hi; p++) {
                 const u32 tl = in.ref_len[p], ql = in.alt_len[p];
+                const u64 ro = in.ref_off[p], ao = in.alt_off[p];
                 m = std::max(m, tl);
                 sum += (u64)tl + ql;
                 es += pair_ckpt_bytes(tl, ql);
                 pre[p] = es;
+                alo = std::min(alo, std::min(ro, ao));
+                ahi = std::max(ahi, std::max(ro + tl, ao + ql));
             }
-            tmax[(size_t)t] = m; tsum[(size_t)t] = sum; tes[(size_t)t] = es;
+            tmax[(size_t)t] = m; tsum[(size_t)t] = sum; tes[(size_t)t] = es; tlo[(size_t)t] = alo; thi[(size_t)t] = ahi;
         };
         std::vector<std::thread> th;
         for (int t = 1; t < T; t++) th.emplace_back(scan, t);
@@ -543,9 +552,13 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         for (int t = 0; t < T; t++) {
             max_tl = std::max(max_tl, tmax[(size_t)t]); total_len += tsum[(size_t)t];
             slice_off[(size_t)t + 1] = slice_off[(size_t)t] + tes[(size_t)t];
+            span_lo = std::min(span_lo, tlo[(size_t)t]); span_hi = std::max(span_hi, thi[(size_t)t]);
         }
         total_est = slice_off[(size_t)T];
+        span_hi = std::min<u64>(span_hi, in.arena_bytes);
+        span_lo = std::min(span_lo, span_hi) & ~63ull;
     }
+    const u64 span = span_hi - span_lo;
     /* checkpoint estimate of pairs [0, x) */
     auto est_before = [&](int64_t x) -> u64 {
         if (x <= 0) return 0;
@@ -564,12 +577,12 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         return lo;
     };
     setup_mark("pair table scanned");
-    { const int rc0 = reserve_arena(in, max_tl); if (rc0 != MGL_SW_OK) return rc0; }
+    { const int rc0 = reserve_arena(span_lo, span, max_tl); if (rc0 != MGL_SW_OK) return rc0; }
     setup_mark("arena reserved");
 
     /* arena upload policy: per-chunk byte ranges when the arena is laid out pair after pair,
        one up-front copy when pairs share or scatter their sequences */
-    const bool whole = in.arena_bytes > total_len + total_len / 2 + 4096 || total_len > in.arena_bytes + in.arena_bytes / 2;
+    const bool whole = span > total_len + total_len / 2 + 4096 || total_len > span + span / 2;
     /*
      * 2-bit transport (sw_pack.h) only pays while it overlaps: a planner packs its chunk when it is at least
      * pack_lead chunks ahead of the one being uploaded -- the GPU or the host link is the slower side and the
@@ -579,10 +592,10 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
     const bool pack_batch = pack_arena != 0 && !whole;
     std::atomic<int> upload_cursor{0};
     if (whole) {
-        if ((e = cudaMemcpyAsync((void *)arena_dev(), in.arena, in.arena_bytes, cudaMemcpyHostToDevice, slots_[0].stream)) != cudaSuccess)
+        if ((e = cudaMemcpyAsync((void *)(arena_dev() + span_lo), in.arena + span_lo, span, cudaMemcpyHostToDevice, slots_[0].stream)) != cudaSuccess)
             return cuda_fail(e, "H2D arena");
         if ((e = cudaStreamSynchronize(slots_[0].stream)) != cudaSuccess) return cuda_fail(e, "H2D arena");
-        bs.h2d_bytes += in.arena_bytes;
+        bs.h2d_bytes += span;
     }
 
     InFlight fl[MGLSW_SLOTS];

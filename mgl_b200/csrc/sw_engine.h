@@ -50,6 +50,7 @@ struct BatchOut {
     char *text = nullptr;        /* text runs: text_cap characters, pair p's CIGAR is text[cigar_start[p] .. cigar_start[p+1]), no NUL; */
     uint64_t text_cap = 0;       /* ops_total then counts characters                                                             */
     int32_t *score3 = nullptr;   /* score-only runs: n x {score, end_ref, end_alt}; the other arrays are not touched */
+    bool keep_first_start = false; /* cigar_start[0] is not written (it is the last entry of the previous shard of a multi-GPU call) */
 };
 
 struct BatchStats {              /* filled by every run */
@@ -121,6 +122,8 @@ public:
                                     false = one chunk at a time with per-kernel event timing */
     u32 chunk_pairs = 1u << 16;  /* measured: 64 Ki pairs per chunk with four slots is within 1 % of the best device rate and plans in < 5 ms */
     int plan_threads = 0;        /* host planner threads of align_batch; 0: min(8, hardware threads / 2) */
+    int scan_threads = 0;        /* short-lived threads of align_batch's pair-table scan; 0: min(8, hardware threads / 2) */
+    int host_plan = 0;           /* 1: chunks are planned by host threads (sw_plan.cpp), 0: by device kernels (sw_plan_dev.cu) */
     int pipe_wide = 1;           /* pipelined long-pair launches on eight warps per pair: 0 never, 1 when the launch has few pairs, 2 always */
     u64 trace_budget_bytes = 0;  /* 0: derived from free memory */
     int pack_arena = 0;          /* align_batch: all-ACGT byte ranges cross the host link at 2 bits per base (sw_pack.h): */
@@ -146,10 +149,12 @@ private:
     int device_;
     u64 budget_auto_ = 0;        /* budget() when trace_budget_bytes == 0, fixed at first use */
     std::string err_;
-    DevBuf arena_;               /* device copy of the caller's arena, padded on both sides (sw_fill.h) */
-    const uint8_t *arena_dev() const { return (const uint8_t *)arena_.p + MGLSW_ARENA_FRONT_PAD; }
+    DevBuf arena_;               /* device copy of bytes [arena_base_, ..) of the caller's arena, padded on both sides (sw_fill.h) */
+    u64 arena_base_ = 0;
+    /* where caller offset 0 would sit: device code adds the caller's own offsets (only [arena_base_, ..) is backed) */
+    const uint8_t *arena_dev() const { return (const uint8_t *)((uintptr_t)arena_.p + MGLSW_ARENA_FRONT_PAD - (uintptr_t)arena_base_); }
     int reserve_arena(const BatchIn &in);
-    int reserve_arena(const BatchIn &in, u32 max_tl);
+    int reserve_arena(u64 base, u64 span, u32 max_tl);
     std::vector<u64> estpre_;    /* align_batch: prefix sums of the per-pair checkpoint estimate */
     WorkSlot slots_[MGLSW_SLOTS];
     std::vector<ChunkDev *> ring_;           /* align_batch: staging entries the planner threads fill */

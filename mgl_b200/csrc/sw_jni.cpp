@@ -9,10 +9,12 @@
  * scores are taken with any sign, the CIGAR text is written to cigarBuffer
  * WITHOUT a terminating NUL (cigar.copy, :65,:69 -- Java trims the zero-filled
  * buffer), the return value is the alignment offset.  The reference has no
- * error channel; on a failure (no GPU, CUDA error) this writes nothing and
- * returns 0 after printing the reason to stderr -- it never silently computes
- * on the CPU.  initNative has no caller in the Java class (.java:94), so the
- * GPU context is created lazily by the first alignNative.
+ * error channel; on a failure (no GPU, CUDA error, over-long input) this writes
+ * nothing and raises java.lang.RuntimeException (jni_throw.h) -- it never
+ * silently computes on the CPU and never returns an empty result as if it were
+ * one.  initNative has no caller in the Java class (.java:94), so the GPU
+ * context is created lazily by the first alignNative; doneNative (called by
+ * close(), .java:89-92) releases it, and a later call creates it again.
  *
  * Built against <jni.h> from a JDK when JAVA_HOME is set, else against the
  * ABI-faithful jni_min/jni.h in this directory.
@@ -21,9 +23,11 @@
 
 #include <cstdio>
 #include <mutex>
+#include <string>
 #include <vector>
 
 #include "../../include/mgl_sw.h"
+#include "jni_throw.h"
 
 extern "C" {
 
@@ -35,7 +39,7 @@ JNIEXPORT jint JNICALL Java_com_microsoft_mgl_smithwaterman_MicrosoftSmithWaterm
 {
     const uint8_t *target = (const uint8_t *)env->GetDirectBufferAddress(readsBuffer);
     char *cigar = (char *)env->GetDirectBufferAddress(cigarBuffer);
-    if (!target || !cigar) return 0;
+    if (!target || !cigar) { mgl_jni_throw(env, "mgl_sw alignNative: readsBuffer and cigarBuffer must be direct ByteBuffers"); return 0; }
     const uint8_t *query = target + targetLength;
     /* capacity the Java side allocates: 2 * max(refLength, altLength) (.java:71) */
     const int cap = 2 * (targetLength > queryLength ? targetLength : queryLength);
@@ -44,7 +48,8 @@ JNIEXPORT jint JNICALL Java_com_microsoft_mgl_smithwaterman_MicrosoftSmithWaterm
     const int rc = mgl_sw_align_one(target, targetLength, query, queryLength, match, mismatch, gapOpen, gapExtend,
                                     overhangStrategy, text.data(), (int32_t)text.size(), &len, &offset);
     if (rc != MGL_SW_OK) {
-        std::fprintf(stderr, "mgl_sw alignNative: GPU alignment failed (code %d); no result written\n", rc);
+        const std::string msg = "mgl_sw alignNative: GPU alignment failed (code " + std::to_string(rc) + "); no result written";
+        mgl_jni_throw(env, msg.c_str());
         return 0;
     }
     /* the reference does not check capacity either (:65); copy what it would have copied */
@@ -53,7 +58,8 @@ JNIEXPORT jint JNICALL Java_com_microsoft_mgl_smithwaterman_MicrosoftSmithWaterm
     return offset;
 }
 
-JNIEXPORT void JNICALL Java_com_microsoft_mgl_smithwaterman_MicrosoftSmithWaterman_doneNative(JNIEnv *, jclass) {}
+/* close() -> doneNative (.java:89-92): the process-wide handle and its device buffers go; the next call recreates them */
+JNIEXPORT void JNICALL Java_com_microsoft_mgl_smithwaterman_MicrosoftSmithWaterman_doneNative(JNIEnv *, jclass) { mgl_sw_shutdown(); }
 
 /*
  * The batched crossing (no counterpart in the reference, whose align() is one pair per call,
@@ -65,23 +71,21 @@ JNIEXPORT void JNICALL Java_com_microsoft_mgl_smithwaterman_MicrosoftSmithWaterm
  * (INTEGRATION.md has the Java side).  All buffers are direct and in native byte order; pair p's CIGAR is the
  * characters cigarTextOut[cigarStartOut[p] .. cigarStartOut[p+1]), exactly what alignNative would have written for
  * it, formatted on the GPU.  Returns 0 or an MGL_SW_E_* code; on MGL_SW_E_OPS_CAPACITY cigarStartOut[n] holds the
- * text capacity needed.  One process-wide handle per device 0, created by the first call.
+ * text capacity needed (the Java side retries with a larger buffer); any other failure also raises
+ * java.lang.RuntimeException.  Runs on the process-wide handle (mgl_sw_default_handle): every visible GPU, or the
+ * MGL_SW_DEVICES list, the batch cut by DP cells across them.
  */
 JNIEXPORT jint JNICALL Java_com_microsoft_mgl_smithwaterman_MicrosoftSmithWaterman_alignBatchNative(
     JNIEnv *env, jclass, jobject arena, jlong arenaBytes, jint n, jobject refOff, jobject refLen, jobject altOff, jobject altLen,
     jint match, jint mismatch, jint gapOpen, jint gapExtend, jint overhangStrategy, jobject strategies,
     jobject offsetsOut, jobject cigarStartOut, jobject cigarTextOut, jlong textCap)
 {
-    static mgl_sw_handle *handle = nullptr;
-    static std::mutex mu;
+    mgl_sw_handle *handle = nullptr;
     {
-        std::lock_guard<std::mutex> lk(mu);
-        if (!handle) {
-            const int rc = mgl_sw_create(0, &handle);
-            if (rc != MGL_SW_OK) { handle = nullptr; return rc; }
-        }
+        const int rc = mgl_sw_default_handle(&handle);
+        if (rc != MGL_SW_OK) { mgl_jni_throw(env, "mgl_sw alignBatchNative: no usable B200 (sm_100a) device"); return rc; }
     }
-    if (n < 0 || arenaBytes < 0 || textCap < 0) return MGL_SW_E_INVALID;
+    if (n < 0 || arenaBytes < 0 || textCap < 0) { mgl_sw_default_release(); return MGL_SW_E_INVALID; }
     mgl_sw_batch b;
     b.n = n;
     b.arena = (const uint8_t *)env->GetDirectBufferAddress(arena);
@@ -99,9 +103,18 @@ JNIEXPORT jint JNICALL Java_com_microsoft_mgl_smithwaterman_MicrosoftSmithWaterm
     r.text = (char *)env->GetDirectBufferAddress(cigarTextOut);
     r.text_cap = (uint64_t)textCap;
     r.text_total = 0;
-    if (n > 0 && (!b.arena || !b.ref_off || !b.ref_len || !b.alt_off || !b.alt_len || !r.offsets || !r.text_start || (!r.text && textCap))) return MGL_SW_E_INVALID;
+    if (n > 0 && (!b.arena || !b.ref_off || !b.ref_len || !b.alt_off || !b.alt_len || !r.offsets || !r.text_start || (!r.text && textCap))) {
+        mgl_sw_default_release();
+        mgl_jni_throw(env, "mgl_sw alignBatchNative: every buffer must be a direct ByteBuffer");
+        return MGL_SW_E_INVALID;
+    }
     const int rc = mgl_sw_align_batch_text(handle, &b, &r, nullptr);
     if (rc == MGL_SW_E_OPS_CAPACITY && r.text_start) r.text_start[n] = r.text_total;
+    else if (rc != MGL_SW_OK) {
+        const std::string msg = std::string("mgl_sw alignBatchNative: failed (code ") + std::to_string(rc) + "): " + mgl_sw_last_error(handle);
+        mgl_jni_throw(env, msg.c_str());
+    }
+    mgl_sw_default_release();
     return rc;
 }
 

@@ -13,7 +13,7 @@
 #include <cstdint>
 #include <cstring>
 
-#include "../../include/mgl_sw.h"
+#include "../../include/mgl_synth.h"
 
 namespace {
 
@@ -84,24 +84,24 @@ void gen_pair(int config, uint64_t seed, uint64_t idx, uint8_t *ref, uint8_t *al
 
 extern "C" {
 
-MGL_SW_API int mgl_sw_synth_sizes(int config, uint64_t seed, uint64_t first, int64_t n, uint32_t *ref_len, uint32_t *alt_len)
+MGL_SYNTH_API int mgl_sw_synth_sizes(int config, uint64_t seed, uint64_t first, int64_t n, uint32_t *ref_len, uint32_t *alt_len)
 {
-    if (config < 2 || config > 5 || n < 0 || !ref_len || !alt_len) return MGL_SW_E_INVALID;
+    if (config < 2 || config > 5 || n < 0 || !ref_len || !alt_len) return -1;
 #pragma omp parallel for schedule(static)
     for (int64_t k = 0; k < n; k++) gen_pair(config, seed, first + (uint64_t)k, nullptr, nullptr, &ref_len[k], &alt_len[k]);
-    return MGL_SW_OK;
+    return 0;
 }
 
-MGL_SW_API int mgl_sw_synth_fill(int config, uint64_t seed, uint64_t first, int64_t n, const uint64_t *ref_off,
+MGL_SYNTH_API int mgl_sw_synth_fill(int config, uint64_t seed, uint64_t first, int64_t n, const uint64_t *ref_off,
                                  const uint64_t *alt_off, uint8_t *arena)
 {
-    if (config < 2 || config > 5 || n < 0 || !ref_off || !alt_off || !arena) return MGL_SW_E_INVALID;
+    if (config < 2 || config > 5 || n < 0 || !ref_off || !alt_off || !arena) return -1;
 #pragma omp parallel for schedule(static)
     for (int64_t k = 0; k < n; k++) {
         uint32_t tl, ql;
         gen_pair(config, seed, first + (uint64_t)k, arena + ref_off[k], arena + alt_off[k], &tl, &ql);
     }
-    return MGL_SW_OK;
+    return 0;
 }
 
 }  // extern "C"

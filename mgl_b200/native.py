@@ -58,6 +58,11 @@ def lib():
             raise MglSwError(E_NO_DEVICE, f"{LIB_PATH} not built (run __graft_entry__.build() or make -C mgl_b200/csrc)")
         L = C.CDLL(LIB_PATH)
         L.mgl_sw_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
+        L.mgl_sw_create_multi.argtypes = [C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_void_p)]
+        L.mgl_sw_handle_devices.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.c_int]
+        L.mgl_sw_default_handle.argtypes = [C.POINTER(C.c_void_p)]
+        L.mgl_sw_default_release.restype = None
+        L.mgl_sw_shutdown.restype = None
         L.mgl_sw_destroy.argtypes = [C.c_void_p]
         L.mgl_sw_destroy.restype = None
         L.mgl_sw_last_error.argtypes = [C.c_void_p]

@@ -77,9 +77,10 @@ def _pack_pairs(pairs: Sequence[Tuple[bytes, bytes]]):
 
 
 class MicrosoftSmithWaterman:
-    """SWAlignerNativeBinding implementation backed by one B200."""
+    """SWAlignerNativeBinding implementation backed by one B200, or by several: `device` may be a list, and every
+    batch call is then cut by DP cells across those GPUs (mgl_sw_create_multi) and gathered in input order."""
 
-    def __init__(self, device: int = 0):
+    def __init__(self, device=0):
         self._device = device
         self._h = None
 
@@ -94,7 +95,11 @@ class MicrosoftSmithWaterman:
     def _ensure(self):
         if self._h is None:
             h = C.c_void_p()
-            rc = native.lib().mgl_sw_create(self._device, C.byref(h))
+            if isinstance(self._device, (list, tuple)):
+                devs = (C.c_int * len(self._device))(*[int(x) for x in self._device])
+                rc = native.lib().mgl_sw_create_multi(devs, len(self._device), C.byref(h))
+            else:
+                rc = native.lib().mgl_sw_create(int(self._device), C.byref(h))
             if rc != native.OK:
                 raise native.MglSwError(rc)
             self._h = h

@@ -1,11 +1,35 @@
-"""Synthetic benchmark pairs (mgl_b200/csrc/sw_synth.cpp) as numpy arrays."""
+"""Synthetic benchmark pairs (mgl_b200/csrc/sw_synth.cpp, include/mgl_synth.h) as numpy arrays.  The generator
+is its own small library, libmgl_synth.so: importing this module does not load libmgl_sw.so (only pinned=True
+does, for cudaHostAlloc), so the reference arm of bench.py maps nothing of the product."""
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import numpy as np
 
-from . import native
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libmgl_synth.so")
+_lib = None
+
+
+def use_library(path: str):
+    """Load the generator from another build of the same source (bench.py's reference arm uses oracle/'s copy so that
+    it maps nothing of the product tree).  Must be called before the first generate()."""
+    global LIB_PATH, _lib
+    LIB_PATH, _lib = path, None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(f"{LIB_PATH} not built (run __graft_entry__.build() or make -C mgl_b200/csrc)")
+        L = C.CDLL(LIB_PATH)
+        L.mgl_sw_synth_sizes.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_int64, C.c_void_p, C.c_void_p]
+        L.mgl_sw_synth_fill.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
+        _lib = L
+    return _lib
 
 SEEDS = {2: 0xC2, 3: 0xC3, 4: 0xC4, 5: 0xC5}
 SCORES = {2: (10, -15, -30, -5), 3: (200, -150, -260, -11), 4: (200, -150, -260, -11), 5: (10, -15, -30, -5)}
@@ -13,25 +37,27 @@ SCORES = {2: (10, -15, -30, -5), 3: (200, -150, -260, -11), 4: (200, -150, -260,
 
 def generate(config: int, n: int, first: int = 0, seed: int | None = None, pinned: bool = False):
     """-> dict(arena, ref_off, ref_len, alt_off, alt_len, strategies, params, cells)"""
-    L = native.lib()
-    L.mgl_sw_synth_sizes.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_int64, C.c_void_p, C.c_void_p]
-    L.mgl_sw_synth_fill.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
+    L = lib()
     seed = SEEDS[config] if seed is None else seed
     ref_len = np.zeros(n, dtype=np.uint32)
     alt_len = np.zeros(n, dtype=np.uint32)
     rc = L.mgl_sw_synth_sizes(config, seed, first, n, ref_len.ctypes.data, alt_len.ctypes.data)
     if rc:
-        raise native.MglSwError(rc)
+        raise ValueError(f"mgl_sw_synth_sizes({config}, n={n}) failed")
     sizes = np.empty(2 * n, dtype=np.uint64)
     sizes[0::2], sizes[1::2] = ref_len, alt_len
     offs = np.zeros(2 * n, dtype=np.uint64)
     offs[1:] = np.cumsum(sizes)[:-1]
     total = int(sizes.sum())
-    arena = native.pinned_array(total, np.uint8) if pinned else np.zeros(total, dtype=np.uint8)
+    if pinned:
+        from . import native
+        arena = native.pinned_array(total, np.uint8)
+    else:
+        arena = np.zeros(total, dtype=np.uint8)
     ref_off, alt_off = offs[0::2].copy(), offs[1::2].copy()
     rc = L.mgl_sw_synth_fill(config, seed, first, n, ref_off.ctypes.data, alt_off.ctypes.data, arena.ctypes.data)
     if rc:
-        raise native.MglSwError(rc)
+        raise ValueError(f"mgl_sw_synth_fill({config}, n={n}) failed")
     idx = np.arange(first, first + n)
     if config == 3:
         strategies = np.where(idx % 2 == 0, 1, 2).astype(np.int32)     # even SOFTCLIP, odd INDEL

@@ -133,4 +133,40 @@ double mgl_ref_align_batch(int kind, int64_t n, const uint8_t *arena, const uint
     return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 }
 
+/*
+ * Full-size parity without n x stride bytes of text: runs the reference on every pair (one pair per OpenMP task) and
+ * compares with the caller's results in place -- offsets[k] and the packed elements (length << 4 | op, BAM numbering)
+ * ops[cigar_start[k] .. cigar_start[k+1]), printed the way sw.cpp:251-252 prints them.  Returns the number of
+ * differing pairs; the first `max_bad` differing indices land in bad_idx (ascending).  *secs = wall seconds.
+ */
+int64_t mgl_ref_check_batch(int kind, int64_t n, const uint8_t *arena, const uint64_t *ref_off,
+                            const uint64_t *alt_off, const uint32_t *ref_len, const uint32_t *alt_len,
+                            int match, int mismatch, int go, int ge, int strategy, const int32_t *strategies,
+                            int threads, const int32_t *got_offsets, const uint64_t *cigar_start, const uint32_t *ops,
+                            int64_t *bad_idx, int max_bad, double *secs)
+{
+    if (threads < 1) threads = 1;
+    static const char kOp[] = "MIDNSHP=X";
+    auto t0 = std::chrono::steady_clock::now();
+    int64_t nbad = 0;
+    std::vector<unsigned char> bad((size_t)n, 0);
+#pragma omp parallel for schedule(dynamic, 16) num_threads(threads) reduction(+ : nbad)
+    for (int64_t k = 0; k < n; k++) {
+        std::string cigar, got;
+        const int st = strategies ? strategies[k] : strategy;
+        const int off = run_one(kind, (const char *)arena + ref_off[k], (int)ref_len[k], (const char *)arena + alt_off[k],
+                                (int)alt_len[k], match, mismatch, go, ge, st, &cigar);
+        for (uint64_t e = cigar_start[k]; e < cigar_start[k + 1]; e++) {
+            const uint32_t op = ops[e] & 15u;
+            got += std::to_string(ops[e] >> 4);
+            got += op < 9 ? kOp[op] : '?';
+        }
+        if (off != got_offsets[k] || got != cigar) { bad[(size_t)k] = 1; nbad++; }
+    }
+    int w = 0;
+    for (int64_t k = 0; k < n && w < max_bad; k++) if (bad[(size_t)k]) bad_idx[w++] = k;
+    if (secs) *secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    return nbad;
+}
+
 }  // extern "C"

@@ -10,7 +10,7 @@
  * Parity status: PINNED.  The reference ships no golden vectors for this path
  * (SURVEY.md section 0, facts 1-2), so the restatement is pinned by executing the
  * reference's own C++ (oracle/_ref, built by oracle/Makefile from the sources
- * in place under /root/reference) -- see tests/test_oracle_vs_ref.py and the
+ * in place under /root/reference) -- see tests/test_oracle.py and the
  * committed outputs in tests/golden/.
  *
  * Reference lines restated (relative to src/main/native/mgl_sw/):

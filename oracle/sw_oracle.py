@@ -15,6 +15,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 ORACLE_SO = os.path.join(HERE, "libsw_oracle.so")
 REF_SO = os.path.join(HERE, "_ref", "libmgl_sw_ref.so")
+SYNTH_SO = os.path.join(HERE, "libsynth_inputs.so")      # the benchmark input generator, for bench.py's reference arm
 
 SOFTCLIP, INDEL, LEADING_INDEL, IGNORE = 1, 2, 4, 8      # sw_common.h:22-25
 STRATEGIES = (SOFTCLIP, INDEL, LEADING_INDEL, IGNORE)
@@ -28,7 +29,7 @@ class OracleResult(C.Structure):
 
 def build(force: bool = False) -> None:
     """Compile the C restatement (and the in-place reference when its sources are present)."""
-    if force or not os.path.exists(ORACLE_SO) or os.path.getmtime(ORACLE_SO) < os.path.getmtime(os.path.join(HERE, "sw_oracle.c")):
+    if force or not os.path.exists(ORACLE_SO) or not os.path.exists(SYNTH_SO) or os.path.getmtime(ORACLE_SO) < os.path.getmtime(os.path.join(HERE, "sw_oracle.c")):
         subprocess.check_call(["make", "-C", HERE, "oracle"], stdout=subprocess.DEVNULL)
     ref_src = os.environ.get("MGL_REFERENCE", "/root/reference")
     if os.path.isdir(os.path.join(ref_src, "src/main/native/mgl_sw")):
@@ -77,6 +78,10 @@ def _load_ref():
                                             C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                             C.c_int, C.c_void_p, C.c_void_p, C.c_int]
         lib.mgl_ref_align_batch.restype = C.c_double
+        if hasattr(lib, "mgl_ref_check_batch"):
+            lib.mgl_ref_check_batch.argtypes = [C.c_int, C.c_int64] + [C.c_void_p] * 5 + [C.c_int] * 5 + [C.c_void_p, C.c_int] + \
+                                               [C.c_void_p] * 4 + [C.c_int, C.POINTER(C.c_double)]
+            lib.mgl_ref_check_batch.restype = C.c_int64
         _ref = lib
     return _ref
 
@@ -169,7 +174,12 @@ def ref_align_jni(ref: bytes, alt: bytes, params, strategy) -> Tuple[str, int]:
 
 
 def ref_max_threads() -> int:
-    return int(_load_ref().mgl_ref_max_threads())
+    """Host threads the reference runs on: the CPUs this process may use.  NOT omp_get_max_threads(): launchers
+    such as torchrun export OMP_NUM_THREADS=1, which would silently time the reference on one core."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
 
 
 def ref_align_batch(arena: np.ndarray, ref_off, alt_off, ref_len, alt_len, params, strategy: int = SOFTCLIP,
@@ -203,3 +213,29 @@ def ref_align_batch(arena: np.ndarray, ref_off, alt_off, ref_len, alt_len, param
     raw = cig.reshape(n, cigar_stride)
     texts = [bytes(row).split(b"\0", 1)[0].decode() for row in raw]
     return secs, offsets, texts
+
+
+def ref_check_batch(arena: np.ndarray, ref_off, alt_off, ref_len, alt_len, params, strategies, got_offsets, cigar_start,
+                    ops, threads: Optional[int] = None, kind: int = REF_DISPATCH, max_bad: int = 8):
+    """Every pair through the reference (one pair per OpenMP task) and compared in place with the caller's results:
+    offsets[k] and the packed elements ops[cigar_start[k]:cigar_start[k+1]] printed as sw.cpp:251-252 prints them.
+    Returns (differing pairs, their first indices, seconds).  Full-size parity without n x stride bytes of text."""
+    lib = _load_ref()
+    n = len(ref_len)
+    arena = np.ascontiguousarray(arena, dtype=np.uint8)
+    ref_off = np.ascontiguousarray(ref_off, dtype=np.uint64)
+    alt_off = np.ascontiguousarray(alt_off, dtype=np.uint64)
+    ref_len = np.ascontiguousarray(ref_len, dtype=np.uint32)
+    alt_len = np.ascontiguousarray(alt_len, dtype=np.uint32)
+    strategies = np.ascontiguousarray(strategies, dtype=np.int32)
+    got_offsets = np.ascontiguousarray(got_offsets, dtype=np.int32)
+    cigar_start = np.ascontiguousarray(cigar_start, dtype=np.uint64)
+    ops = np.ascontiguousarray(ops, dtype=np.uint32)
+    assert len(strategies) == n and len(got_offsets) == n and len(cigar_start) == n + 1 and int(cigar_start[-1]) <= len(ops)
+    bad = np.full(max_bad, -1, dtype=np.int64)
+    secs = C.c_double()
+    nbad = lib.mgl_ref_check_batch(kind, n, arena.ctypes.data, ref_off.ctypes.data, alt_off.ctypes.data, ref_len.ctypes.data,
+                                   alt_len.ctypes.data, params[0], params[1], params[2], params[3], SOFTCLIP,
+                                   strategies.ctypes.data, threads or ref_max_threads(), got_offsets.ctypes.data,
+                                   cigar_start.ctypes.data, ops.ctypes.data, bad.ctypes.data, max_bad, C.byref(secs))
+    return int(nbad), [int(x) for x in bad if x >= 0], secs.value

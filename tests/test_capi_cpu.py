@@ -29,6 +29,31 @@ def test_exports_every_declared_symbol(lib):
         assert hasattr(lib, "Java_com_microsoft_mgl_smithwaterman_MicrosoftSmithWaterman_" + n)
 
 
+def test_synth_library_exports_its_header():
+    from mgl_b200 import synth
+    hdr = open(os.path.join(ROOT, "include", "mgl_synth.h")).read()
+    names = re.findall(r"MGL_SYNTH_API\s+[\w\s\*]+?\b(mgl_sw_synth_\w+)\s*\(", hdr)
+    assert sorted(names) == ["mgl_sw_synth_fill", "mgl_sw_synth_sizes"]
+    for n in names:
+        assert hasattr(synth.lib(), n), n
+
+
+def test_no_gpu_no_handle(lib):
+    """no device in this container: every way of getting a handle refuses (there is no CPU path to fall back to)"""
+    from mgl_b200 import native
+    if lib.mgl_sw_device_count() > 0:
+        pytest.skip("a GPU is present")
+    h = C.c_void_p()
+    assert lib.mgl_sw_create(0, C.byref(h)) == native.E_NO_DEVICE and not h.value
+    devs = (C.c_int * 2)(0, 1)
+    assert lib.mgl_sw_create_multi(devs, 2, C.byref(h)) == native.E_NO_DEVICE and not h.value
+    assert lib.mgl_sw_create_multi(None, 0, C.byref(h)) == native.E_INVALID
+    assert lib.mgl_sw_default_handle(C.byref(h)) == native.E_NO_DEVICE and not h.value
+    lib.mgl_sw_shutdown()                                   # nothing to release: returns at once
+    buf, ln, off = C.create_string_buffer(64), C.c_int32(), C.c_int32()
+    assert lib.mgl_sw_align_one(b"ACGT", 4, b"ACGT", 4, 10, -15, -30, -5, 1, buf, 64, C.byref(ln), C.byref(off)) == native.E_NO_DEVICE
+
+
 def test_format_cigar(lib):
     ops = np.array([(3 << 4) | 0, (2 << 4) | 2, (15 << 4) | 0, (4 << 4) | 4, (1 << 4) | 1], dtype=np.uint32)
     buf = C.create_string_buffer(64)

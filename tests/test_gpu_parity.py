@@ -132,17 +132,65 @@ def test_tiny_ops_buffer_reports_needed_size(sw):
 
 @pytest.mark.parametrize("config,n", [(2, 20000), (3, 3000), (5, 6000)])
 def test_synthetic_configs_vs_oracle(sw, oracle, config, n):
+    """the C restatement (oracle/sw_oracle.c) as the checker; pairs too large for its explicit matrices go to the
+    reference's own align_scalar (oracle/_ref) -- none is skipped when that library is present"""
     from mgl_b200 import synth
     d = synth.generate(config, n)
-    res = sw.align_arrays(d["arena"], d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, d["strategies"])
+    res = sw.align_arrays(d["arena"], d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, d["strategies"],
+                          ops_cap=max(8 * n, int(d["ref_len"].sum() + d["alt_len"].sum()) // 8))
     assert res.stats["pairs"] == n
     step = 1 if n <= 3000 else 5
-    for p in range(0, n, step):
+    big = np.nonzero(d["ref_len"].astype(np.int64) * d["alt_len"].astype(np.int64) > 4_000_000)[0]
+    checked_big = 0
+    for p in sorted(set(range(0, n, step)) | set(int(x) for x in big)):
         r, a = synth.pair_bytes(d, p)
         if len(r) * len(a) > 4_000_000:
-            continue                                  # the explicit-matrix oracle is kept to sizes it finishes quickly
-        exp = oracle.align(r, a, d["params"], int(d["strategies"][p]))
+            if not oracle.have_ref():
+                continue
+            exp = oracle.ref_align(r, a, d["params"], int(d["strategies"][p]), oracle.REF_SCALAR)
+            checked_big += 1
+        else:
+            exp = oracle.align(r, a, d["params"], int(d["strategies"][p]))
         assert (res.cigar(p), int(res.offsets[p])) == exp, (config, p, len(r), len(a))
+    if config == 5 and oracle.have_ref():
+        assert checked_big == len(big) > 0            # every config-4-shaped pair of the mixed chunk was compared
+
+
+# BASELINE.json configs at full size (config 4: 1 500 of its 10 000 pairs = 86 Gcells, config 5: 200 000 pairs as the
+# stand-in for 100 M -- every long pair among them is compared), every pair against the reference's own C++
+FULL_SIZE = [(2, 1_000_000), (3, 100_000), (4, 1_500), (5, 200_000)]
+
+
+@pytest.mark.parametrize("config,n", FULL_SIZE)
+def test_full_size_parity_vs_reference(sw, oracle, config, n):
+    """SURVEY.md 8d 'parity at scale': the CUDA path through mgl_sw_align_batch (host buffers in and out) against
+    oracle/_ref -- the reference's unmodified align_avx / align_scalar behind its JNI dispatch rule
+    (...SmithWaterman.cpp:62-70) -- on EVERY pair, CIGAR text and offset bit-exact; then the same batch again over
+    the 2-bit transport (pack_arena = 2), which must return identical arrays."""
+    from mgl_b200 import synth
+    if not oracle.have_ref():
+        pytest.skip("oracle/_ref/libmgl_sw_ref.so not built (it is compiled in the authoring container and travels to the GPU box)")
+    d = synth.generate(config, n)
+    args = (d["arena"], d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, d["strategies"])
+    cap = max(8 * n, int(d["ref_len"].astype(np.int64).sum() + d["alt_len"].astype(np.int64).sum()) // 8)
+    res = sw.align_arrays(*args, ops_cap=cap)
+    assert res.stats["pairs"] == n and res.stats["cells"] == d["cells"]
+    if config == 5:
+        long_pairs = int((d["alt_len"] > 4 * 32 * 24).sum())
+        assert long_pairs >= 100 and res.stats["pairs_s16"] > 0 and res.stats["pairs_s32"] > long_pairs   # a really mixed batch
+    nbad, first, secs = oracle.ref_check_batch(d["arena"], d["ref_off"], d["alt_off"], d["ref_len"], d["alt_len"], d["params"],
+                                               d["strategies"], res.offsets, res.cigar_start, res.ops)
+    detail = [(p, int(d["ref_len"][p]), int(d["alt_len"][p]), res.cigar(p)[:80], int(res.offsets[p]),
+               oracle.ref_align(*synth.pair_bytes(d, p), d["params"], int(d["strategies"][p]))) for p in first[:3]]
+    assert nbad == 0, (config, nbad, detail)
+    sw.set_option("pack_arena", 2)
+    try:
+        packed = sw.align_arrays(*args, ops_cap=cap)
+    finally:
+        sw.set_option("pack_arena", 0)
+    assert packed.stats["h2d_bytes"] < res.stats["h2d_bytes"]
+    assert np.array_equal(packed.offsets, res.offsets) and np.array_equal(packed.cigar_start, res.cigar_start)
+    assert np.array_equal(packed.ops, res.ops)
 
 
 def test_packed_and_raw_transport_give_the_same_results(sw, oracle):
@@ -405,3 +453,72 @@ def test_jni_batch_symbol(sw, oracle):
     rc = fn(env, None, arena.ctypes.data, arena.nbytes, n, ro.ctypes.data, rl.ctypes.data, ao.ctypes.data, al.ctypes.data,
             10, -15, -30, -5, 1, None, offsets.ctypes.data, start.ctypes.data, text.ctypes.data, 16)
     assert rc == native.E_OPS_CAPACITY and int(start[n]) > 16
+
+
+def test_multi_device_handle_matches_single_and_oracle(sw, oracle):
+    """mgl_sw_create_multi: one handle over a device list cuts the batch by DP cells, runs one
+    engine per entry and gathers in input order.  Output == the one-device handle's == the reference's on a 200 000-pair
+    config-5 batch (short, medium and long pairs in every shard), for packed elements, device-formatted text and the
+    score-only entry.  The list is every visible GPU, or device 0 three times on a one-GPU box (three engines sharing
+    it: the sharding, staging and gather logic is the same)."""
+    import mgl_b200
+    from mgl_b200 import native, synth
+    ndev = native.lib().mgl_sw_device_count()
+    devices = list(range(ndev)) if ndev > 1 else [0, 0, 0]
+    n = 200_000
+    d = synth.generate(5, n)
+    args = (d["arena"], d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, d["strategies"])
+    cap = max(8 * n, int(d["ref_len"].astype(np.int64).sum() + d["alt_len"].astype(np.int64).sum()) // 8)
+    single = sw.align_arrays(*args, ops_cap=cap)
+    multi = mgl_b200.MicrosoftSmithWaterman(devices)
+    try:
+        multi._ensure()
+        got = (C.c_int * 16)()
+        assert native.lib().mgl_sw_handle_devices(multi._h, got, 16) == len(devices) and list(got[:len(devices)]) == devices
+        res = multi.align_arrays(*args, ops_cap=cap)
+        assert res.stats["pairs"] == n and res.stats["cells"] == d["cells"]
+        assert np.array_equal(res.offsets, single.offsets) and np.array_equal(res.cigar_start, single.cigar_start)
+        assert np.array_equal(res.ops, single.ops)
+        if oracle.have_ref():
+            nbad, first, _ = oracle.ref_check_batch(d["arena"], d["ref_off"], d["alt_off"], d["ref_len"], d["alt_len"], d["params"],
+                                                    d["strategies"], res.offsets, res.cigar_start, res.ops)
+            assert nbad == 0, (nbad, first)
+        # too small an output buffer: the needed size comes back, as from one device
+        small = np.zeros(1000, dtype=np.uint32)
+        r = native.Result()
+        off, cs = np.zeros(n, np.int32), np.zeros(n + 1, np.uint64)
+        r.offsets, r.cigar_start, r.ops, r.ops_cap = off.ctypes.data, cs.ctypes.data, small.ctypes.data, len(small)
+        b, keep = native.make_batch(*args[:5], d["params"], 1, d["strategies"])
+        assert native.lib().mgl_sw_align_batch(multi._h, C.byref(b), C.byref(r), None) == native.E_OPS_CAPACITY
+        assert r.ops_total == len(single.ops)
+        # text and score-only through the same sharding
+        m = 30_000
+        sub = tuple(a[:m] if k in (1, 2, 3, 4) else a for k, a in enumerate(args[:5])) + (d["params"], 1, d["strategies"][:m])
+        t1 = sw.align_arrays_text(*sub)
+        t2 = multi.align_arrays_text(*sub)
+        assert np.array_equal(t1[0], t2[0]) and np.array_equal(t1[1], t2[1]) and np.array_equal(t1[2], t2[2])
+        s1, _ = sw.score_arrays(*sub)
+        s2, _ = multi.score_arrays(*sub)
+        assert np.array_equal(s1, s2)
+        # edge: fewer pairs than devices, and an empty batch
+        tiny = multi.align_batch([(b"ACGTACGTAC", b"ACGTTCGTAC")], (10, -15, -30, -5), 1)
+        assert tiny.cigars() == ["10M"]
+        assert len(multi.align_batch([], (10, -15, -30, -5), 1).offsets) == 0
+    finally:
+        multi.close()
+
+
+def test_default_handle_survives_done_native(sw, oracle):
+    """doneNative (MicrosoftSmithWaterman.close(), .java:89-92) releases the process-wide handle; the next alignNative
+    creates it again"""
+    import mgl_b200
+    from mgl_b200 import native
+    P = (200, -150, -260, -11)
+    one = mgl_b200.align_one_text(b"GGGGACGTACGTCCCC", b"TTACGTACGTTT", P, 1)
+    assert (one.cigar, one.alignment_offset) == ("2I7M2I1M", 4)
+    fn = native.lib().Java_com_microsoft_mgl_smithwaterman_MicrosoftSmithWaterman_doneNative
+    fn.argtypes, fn.restype = [C.c_void_p, C.c_void_p], None
+    fn(None, None)
+    fn(None, None)                                       # idempotent
+    one = mgl_b200.align_one_text(b"ACGTACGTAC", b"GGGGGGGGGGGG", P, 8)
+    assert (one.cigar, one.alignment_offset) == ("13D1M", -11)
