@@ -394,6 +394,34 @@ def sub_config(sw, config, n, rank, dist, local, p_int32, hbm_peak, measured, wa
     return rec
 
 
+def multi_handle_record(world, n_per_gpu, config=2):
+    """ONE process, one handle over all `world` GPUs (mgl_sw_create_multi): the JVM's situation -- a single caller
+    handing a batch of world x n pairs to the library, which cuts it by DP cells, runs one engine per GPU on its own
+    host thread and gathers in input order.  Host buffers in and out, like `e2e`."""
+    import numpy as np
+    import mgl_b200
+    from mgl_b200 import native, synth
+    n = world * n_per_gpu
+    d = synth.generate(config, n, pinned=True)
+    out = (native.pinned_array(n, np.int32), native.pinned_array(n + 1, np.uint64), native.pinned_array(ops_capacity(d), np.uint32))
+    m = mgl_b200.MicrosoftSmithWaterman(list(range(world)))
+    m._ensure()
+    call = lambda: m.align_arrays(d["arena"], d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, d["strategies"], out=out)
+    for _ in range(2):
+        call()
+    steps = 3
+    t0, c0 = time.perf_counter(), time.process_time()
+    for _ in range(steps):
+        r = call()
+    ms, cpu_s = (time.perf_counter() - t0) * 1e3, time.process_time() - c0
+    m.close()
+    return {"devices": world, "pairs": n, "cells": int(d["cells"]), "steps": steps, "value": d["cells"] * steps / (ms * 1e-3) / 1e9, "unit": UNIT,
+            "ms_per_step": ms / steps, "h2d_bytes_per_step": int(r.stats["h2d_bytes"]), "d2h_bytes_per_step": int(r.stats["d2h_bytes"]),
+            "host_cpu_ns_per_pair": cpu_s / (n * steps) * 1e9,
+            "note": "mgl_sw_align_batch on a handle made by mgl_sw_create_multi over every GPU of the run, called from rank 0 alone while "
+                    "the other ranks idle at a barrier; pinned host buffers in and out"}
+
+
 def main():
     args = parse()
     protect_stdout()
@@ -512,6 +540,15 @@ def main():
                 line["config5"] = rec
                 line["config5_note"] = ("BASELINE.json configs[4], the scaling sweep's workload: 1 M mixed pairs PER GPU (weak scaling) standing in "
                                         "for 100 M pairs in total, which would be ~3 GPU-hours at 1.4 TCUPS")
+    if world > 1 and not args.no_sub and args.config == 2 and not args.pairs:
+        sw.close()                                       # every rank gives its GPU back before one process drives them all
+        barrier(dist, local)
+        if rank == 0:
+            try:
+                line["multi_handle"] = multi_handle_record(world, n)
+            except Exception as ex:                      # the headline must not die with the sub-record
+                line["multi_handle"] = {"error": repr(ex)}
+        barrier(dist, local)
     if line is not None and world == 1 and not args.no_cpu_baseline:
         cb = cpu_baseline(d)
         if cb:

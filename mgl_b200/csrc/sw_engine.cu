@@ -78,6 +78,8 @@ void ChunkDev::release()
     units.release(); pair_unit.release(); ops_end.release(); strategy.release();
     h_units.release(); h_pair_unit.release(); h_ops_end.release(); h_strategy.release();
     packed.release(); h_packed.release();
+    table.release(); work.release(); h_table.release(); h_sum.release();
+    if (ev_plan) { cudaEventDestroy(ev_plan); ev_plan = nullptr; }
 }
 
 void WorkSlot::release()
@@ -122,6 +124,8 @@ Engine::Engine(int device) : device_(device)
             blocking = std::thread::hardware_concurrency() < (unsigned)ndev * MGLSW_SPIN_MIN_CPUS_PER_GPU;
     }
     const unsigned wait_flags = cudaEventDisableTiming | (blocking ? cudaEventBlockingSync : 0u);
+    wait_flags_ = wait_flags;
+    cudaStreamCreateWithPriority(&plan_stream_, cudaStreamNonBlocking, prio_hi);
     for (auto &s : slots_) {
         cudaStreamCreateWithPriority(&s.stream, cudaStreamNonBlocking, prio_lo);
         cudaStreamCreateWithPriority(&s.post, cudaStreamNonBlocking, prio_hi);
@@ -145,6 +149,7 @@ Engine::~Engine()
     drop_resident();
     for (ChunkDev *cd : ring_) { cd->release(); delete cd; }
     for (auto &s : slots_) s.release();
+    if (plan_stream_) cudaStreamDestroy(plan_stream_);
     for (auto &e : tev_) if (e) cudaEventDestroy(e);
     arena_.release();
 }
@@ -319,6 +324,86 @@ int Engine::plan_next(const BatchIn &in, int64_t first, ChunkDev &cd)
     return rc == MGL_SW_OK ? rc : fail(rc, err);
 }
 
+/*
+ * Device planner, host half.  The chunk's slice of the caller's pair table (28 bytes per pair) is staged in pinned
+ * memory -- the caller's arrays are ordinary memory, and a copy from them would be staged by the driver, synchronously --
+ * and goes up on the planner's stream, followed by the planning kernels and the copy home of the summary.  The host
+ * touches each pair twice here (the memcpy and the min / max of its offsets) and never again.
+ */
+int Engine::issue_plan_dev(const BatchIn &in, int64_t first, int64_t take, ChunkDev &cd, BatchStats &bs)
+{
+    cudaError_t e;
+    const u32 n = (u32)take;
+    cd.first = first; cd.n = n; cd.packed_ok = false;
+    cd.plan.reset();
+    if (!cd.ev_plan && (e = cudaEventCreateWithFlags(&cd.ev_plan, wait_flags_)) != cudaSuccess) return cuda_fail(e, "event create");
+    if (n > cd.lay.n_cap || !cd.work.p) {
+        cd.lay = plan_dev_layout(std::max<u32>(n + n / 8, 4096));
+        if ((e = cd.work.reserve(cd.lay.total)) != cudaSuccess) return cuda_fail(e, "cudaMalloc planner work buffer");
+    }
+    const size_t tbytes = (size_t)n * 28;
+    if ((e = cd.h_table.reserve(tbytes)) != cudaSuccess) return cuda_fail(e, "pinned alloc");
+    if ((e = cd.h_sum.reserve(sizeof(PlanSummary))) != cudaSuccess) return cuda_fail(e, "pinned alloc");
+    if ((e = cd.table.reserve(tbytes)) != cudaSuccess) return cuda_fail(e, "cudaMalloc pair table");
+    if ((e = cd.units.reserve((size_t)plan_dev_unit_capacity(n) * sizeof(UnitDesc))) != cudaSuccess) return cuda_fail(e, "cudaMalloc units");
+    if ((e = cd.ops_end.reserve((size_t)n * sizeof(u64))) != cudaSuccess) return cuda_fail(e, "cudaMalloc");
+    char *h = (char *)cd.h_table.p;
+    u64 *h_ro = (u64 *)h, *h_ao = (u64 *)(h + (size_t)n * 8);
+    u32 *h_tl = (u32 *)(h + (size_t)n * 16), *h_ql = (u32 *)(h + (size_t)n * 20);
+    int *h_st = (int *)(h + (size_t)n * 24);
+    std::memcpy(h_ro, in.ref_off + first, (size_t)n * 8);
+    std::memcpy(h_ao, in.alt_off + first, (size_t)n * 8);
+    std::memcpy(h_tl, in.ref_len + first, (size_t)n * 4);
+    std::memcpy(h_ql, in.alt_len + first, (size_t)n * 4);
+    if (in.strategies) std::memcpy(h_st, in.strategies + first, (size_t)n * 4);
+    else std::fill(h_st, h_st + n, in.strategy);
+    u64 lo = ~0ull, hi = 0;                    /* the byte range of the arena this chunk touches */
+    for (u32 k = 0; k < n; k++) {
+        const u64 ro = h_ro[k], ao = h_ao[k];
+        lo = std::min(lo, std::min(ro, ao));
+        hi = std::max(hi, std::max(ro + h_tl[k], ao + h_ql[k]));
+    }
+    cd.arena_lo = std::min(lo, in.arena_bytes); cd.arena_hi = std::min(hi, in.arena_bytes);   /* offsets outside the arena are refused by the planner */
+    if (cd.arena_lo > cd.arena_hi) cd.arena_lo = cd.arena_hi;
+    if ((e = cudaMemcpyAsync(cd.table.p, cd.h_table.p, tbytes, cudaMemcpyHostToDevice, plan_stream_)) != cudaSuccess) return cuda_fail(e, "H2D pair table");
+    bs.h2d_bytes += tbytes;
+    const char *d = (const char *)cd.table.p;
+    PlanDevIn pin;
+    pin.ref_off = (const u64 *)d; pin.alt_off = (const u64 *)(d + (size_t)n * 8);
+    pin.tl = (const u32 *)(d + (size_t)n * 16); pin.ql = (const u32 *)(d + (size_t)n * 20);
+    pin.strategy = (const int *)(d + (size_t)n * 24);
+    pin.n = n; pin.arena_bytes = in.arena_bytes; pin.s = in.scores; pin.allow_s16 = allow_s16 ? 1 : 0; pin.score_only = in.score_only ? 1 : 0;
+    if ((e = plan_dev_run(pin, cd.lay, (UnitDesc *)cd.units.p, (u64 *)cd.ops_end.p, cd.work.p, (PlanSummary *)cd.h_sum.p, plan_stream_)) != cudaSuccess)
+        return cuda_fail(e, "device planner");
+    if ((e = cudaEventRecord(cd.ev_plan, plan_stream_)) != cudaSuccess) return cuda_fail(e, "event record");
+    cd.d_units = (const UnitDesc *)cd.units.p; cd.d_ops_end = (const u64 *)cd.ops_end.p; cd.d_strategy = pin.strategy;
+    bs.other_launches += 20;                   /* 10 planner kernels + the sort's and the scans' own */
+    return MGL_SW_OK;
+}
+
+int Engine::collect_plan_dev(ChunkDev &cd)
+{
+    cudaError_t e;
+    if ((e = cudaEventSynchronize(cd.ev_plan)) != cudaSuccess) return cuda_fail(e, "device planner");
+    const PlanSummary &S = *(const PlanSummary *)cd.h_sum.p;
+    if (S.err_invalid) return fail(MGL_SW_E_INVALID, "pair " + std::to_string(cd.first + (int64_t)(0xffffffffu - S.err_invalid)) + " lies outside the arena");
+    if (S.err_pair) return fail(MGL_SW_E_PAIR, "empty or over-long sequence in batch (pair " + std::to_string(cd.first + (int64_t)(0xffffffffu - S.err_pair)) + ")");
+    if (S.overflow || S.n_launches > MGLSW_PLAN_MAX_LAUNCHES) return fail(MGL_SW_E_INVALID, "device planner: launch table overflow");
+    ChunkPlan &P = cd.plan;
+    P.reset();
+    for (u32 l = 0; l < S.n_launches; l++) {
+        const PlanLaunchDev &D = S.launch[l];
+        Launch L;
+        L.kind = (int)D.kind; L.G = (int)D.G; L.K = (int)D.K; L.pipe = (int)D.pipe; L.nstrips = 0;
+        L.first_unit = D.first_unit; L.n_units = D.n_units; L.n_warps = D.n_warps; L.cells = 0;
+        P.launches.push_back(L);
+    }
+    P.n_units = S.n_units;
+    P.ckpt_words = S.ckpt_words; P.carry_entries = S.carry_entries; P.lastrow_words = S.lastrow_words; P.scratch_words = S.scratch_words;
+    P.cells = S.cells; P.pairs_s16 = S.pairs_s16; P.pairs_s32 = S.pairs_s32; P.s16_bias = (int)S.s16_bias;
+    return MGL_SW_OK;
+}
+
 int Engine::upload_chunk(const BatchIn &in, ChunkDev &cd, cudaStream_t st, bool upload_arena, BatchStats &bs)
 {
     cudaError_t e;
@@ -332,6 +417,14 @@ int Engine::upload_chunk(const BatchIn &in, ChunkDev &cd, cudaStream_t st, bool 
     if ((e = cudaMemcpyAsync(cd.ops_end.p, cd.h_ops_end.p, n * sizeof(u64), cudaMemcpyHostToDevice, st)) != cudaSuccess) return cuda_fail(e, "H2D");
     if ((e = cudaMemcpyAsync(cd.strategy.p, cd.h_strategy.p, n * sizeof(int), cudaMemcpyHostToDevice, st)) != cudaSuccess) return cuda_fail(e, "H2D");
     bs.h2d_bytes += nu * sizeof(UnitDesc) + n * (sizeof(u32) + sizeof(u64) + sizeof(int));
+    cd.d_units = (const UnitDesc *)cd.units.p; cd.d_ops_end = (const u64 *)cd.ops_end.p; cd.d_strategy = (const int *)cd.strategy.p;
+    return upload_arena_range(in, cd, st, upload_arena, bs);
+}
+
+/* the bytes of the caller's arena this chunk's pairs touch, onto the chunk's stream (packed form when the planner made one) */
+int Engine::upload_arena_range(const BatchIn &in, ChunkDev &cd, cudaStream_t st, bool upload_arena, BatchStats &bs)
+{
+    cudaError_t e;
     if (upload_arena && cd.packed_ok) {
         const u64 lo16 = cd.arena_lo & ~15ull, nb = cd.arena_hi - lo16;
         const size_t pb = pack2_bytes(nb);
@@ -360,14 +453,14 @@ int Engine::ensure_slot(WorkSlot &ws, const ChunkPlan &plan, u32 n, bool score_o
         if ((e = ws.ckpt.reserve((plan.ckpt_words + 4) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc checkpoints");
         if ((e = ws.carry.reserve((plan.carry_entries + 1) * sizeof(Carry))) != cudaSuccess) return cuda_fail(e, "cudaMalloc carry");
         if ((e = ws.lastrow.reserve((plan.lastrow_words + 1) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc lastrow");
-        if ((e = ws.colbest.reserve((plan.units.size() + 1) * 4 * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc colbest");
+        if ((e = ws.colbest.reserve(((size_t)plan.n_units + 1) * 4 * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc colbest");
         if ((e = ws.score3.reserve((size_t)n * 3 * sizeof(int))) != cudaSuccess) return cuda_fail(e, "cudaMalloc");
         return MGL_SW_OK;
     }
     if ((e = ws.ckpt.reserve((plan.ckpt_words + 4) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc checkpoints");
     if ((e = ws.carry.reserve((plan.carry_entries + 1) * sizeof(Carry))) != cudaSuccess) return cuda_fail(e, "cudaMalloc carry");
     if ((e = ws.lastrow.reserve((plan.lastrow_words + 1) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc lastrow");
-    if ((e = ws.colbest.reserve((plan.units.size() + 1) * 4 * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc colbest");
+    if ((e = ws.colbest.reserve(((size_t)plan.n_units + 1) * 4 * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc colbest");
     if ((e = ws.scratch.reserve((plan.scratch_words + 1) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc scratch");
     if ((e = ws.offsets.reserve((size_t)n * sizeof(int))) != cudaSuccess) return cuda_fail(e, "cudaMalloc");
     if ((e = ws.n_ops.reserve((size_t)n * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc");
@@ -406,7 +499,7 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed, bo
         cudaStream_t ls = lane == 0 ? st : ws.side[lane - 1];
         FillArgs a;
         a.arena = arena_dev();
-        a.units = (const UnitDesc *)cd.units.p;
+        a.units = cd.d_units;
         a.ckpt = (u32 *)ws.ckpt.p;
         a.carry = (Carry *)ws.carry.p;
         a.lastrow = (u32 *)ws.lastrow.p;
@@ -427,9 +520,9 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed, bo
     if ((e = cudaStreamWaitEvent(pt, ws.ev_fill, 0)) != cudaSuccess) return cuda_fail(e, "stream wait");
     if (timed) cudaEventRecord(tev_[2], pt);
     TraceArgs t;
-    t.units = (const UnitDesc *)cd.units.p;
-    t.ops_end = (const u64 *)cd.ops_end.p;
-    t.strategy = (const int *)cd.strategy.p;
+    t.units = cd.d_units;
+    t.ops_end = cd.d_ops_end;
+    t.strategy = cd.d_strategy;
     t.ckpt = (const u32 *)ws.ckpt.p;
     t.arena = arena_dev();
     t.c16 = make_consts<S16x2>(sc, cd.plan.s16_bias);
@@ -439,7 +532,7 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed, bo
     t.scratch = (u32 *)ws.scratch.p;
     t.offsets = (int *)ws.offsets.p;
     t.n_ops = (u32 *)ws.n_ops.p;
-    t.n_units = (u32)cd.plan.units.size();
+    t.n_units = cd.plan.n_units;
     t.score3 = (int *)ws.score3.p;
     if (score_only) {
         if ((e = launch_endpoints(t, pt)) != cudaSuccess) return cuda_fail(e, "endpoint launch");
@@ -456,15 +549,15 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed, bo
     if (timed) cudaEventRecord(tev_[3], pt);
     if (text) {
         /* characters per pair -> the same scan -> characters; the packed elements stay in the scratch buffer */
-        if ((e = launch_text_len((const u32 *)ws.scratch.p, (const u64 *)cd.ops_end.p, (const u32 *)ws.n_ops.p, (u32 *)ws.n_chars.p, cd.n, pt)) != cudaSuccess)
+        if ((e = launch_text_len((const u32 *)ws.scratch.p, cd.d_ops_end, (const u32 *)ws.n_ops.p, (u32 *)ws.n_chars.p, cd.n, pt)) != cudaSuccess)
             return cuda_fail(e, "text length launch");
         if ((e = launch_scan_counts((const u32 *)ws.n_chars.p, (u32 *)ws.starts.p, (u32 *)ws.tiles.p, cd.n, pt)) != cudaSuccess) return cuda_fail(e, "scan launch");
-        if ((e = launch_text_format((const u32 *)ws.scratch.p, (const u64 *)cd.ops_end.p, (const u32 *)ws.n_ops.p, (const u32 *)ws.starts.p,
+        if ((e = launch_text_format((const u32 *)ws.scratch.p, cd.d_ops_end, (const u32 *)ws.n_ops.p, (const u32 *)ws.starts.p,
                                     (const u32 *)ws.tiles.p, (char *)ws.ops.p, cd.n, pt)) != cudaSuccess) return cuda_fail(e, "text format launch");
         bs.other_launches += 1;
     } else {
         if ((e = launch_scan_counts((const u32 *)ws.n_ops.p, (u32 *)ws.starts.p, (u32 *)ws.tiles.p, cd.n, pt)) != cudaSuccess) return cuda_fail(e, "scan launch");
-        if ((e = launch_compact((const u32 *)ws.scratch.p, (const u64 *)cd.ops_end.p, (const u32 *)ws.n_ops.p,
+        if ((e = launch_compact((const u32 *)ws.scratch.p, cd.d_ops_end, (const u32 *)ws.n_ops.p,
                                 (const u32 *)ws.starts.p, (const u32 *)ws.tiles.p, (u32 *)ws.ops.p, cd.n, pt)) != cudaSuccess) return cuda_fail(e, "compact launch");
     }
     if (timed) cudaEventRecord(tev_[4], pt);
@@ -636,8 +729,17 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
      * launches and collects them in order.  Entry c % R is reused once chunk c - R has been
      * collected; R = planners + slots + 1 keeps every planner busy without blocking the collector.
      */
+    /*
+     * Who plans: device kernels (sw_plan_dev.cu) unless the caller asked for the host planner, or for the 2-bit
+     * transport, whose packing is done by the host planner threads.  With device planning this thread stages each
+     * chunk's slice of the pair table, queues the planning kernels DEV_AHEAD chunks ahead of the chunk it launches,
+     * and reads back a summary; no planner threads exist.
+     */
+    const bool dev_plan = host_plan == 0 && pack_arena == 0;
+    const int DEV_AHEAD = 3;
     std::vector<std::pair<int64_t, int64_t>> bounds;
     int nthreads = plan_threads > 0 ? plan_threads : (int)std::min<unsigned>(8u, std::max(1u, std::thread::hardware_concurrency() / 2));
+    if (dev_plan) nthreads = 2;                           /* the ramp below counts chunks in planners: two rounds of two */
     {
         const u64 limit = so ? ~0ull : budget();          /* a score-only run parks no checkpoints */
         /*
@@ -664,9 +766,9 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         }
     }
     const int nchunks = (int)bounds.size();
-    nthreads = std::min(nthreads, nchunks);
+    nthreads = dev_plan ? 0 : std::min(nthreads, nchunks);
     setup_mark("chunk bounds");
-    const int R = nthreads + MGLSW_SLOTS + 1;
+    const int R = (dev_plan ? DEV_AHEAD : nthreads) + MGLSW_SLOTS + 1;
     while ((int)ring_.size() < R) ring_.push_back(new ChunkDev());
     std::vector<int> ready((size_t)nchunks, 0);          /* 0 pending, 1 planned, 2 failed */
     std::vector<int> prc((size_t)nchunks, MGL_SW_OK);
@@ -698,7 +800,8 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         }
     };
     std::vector<std::thread> workers;
-    if (nchunks > 1) for (int t = 0; t < nthreads; t++) workers.emplace_back(planner);
+    if (nchunks > 1 && !dev_plan) for (int t = 0; t < nthreads; t++) workers.emplace_back(planner);
+    int issued = 0;                                      /* device planning: chunks whose planning kernels are queued */
     auto release_upto = [&](int k) {                     /* chunks below k are collected */
         { std::lock_guard<std::mutex> lk(mu); if (k > collected) collected = k; }
         cv.notify_all();
@@ -716,7 +819,13 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         WorkSlot &ws = slots_[si];
         ChunkDev &cd = *ring_[(size_t)(c % R)];
         upload_cursor.store(c, std::memory_order_relaxed);
-        if (nchunks == 1) {
+        if (dev_plan) {
+            /* keep the planner DEV_AHEAD chunks ahead; entry k % R is free: chunk k - R came home SLOTS iterations ago */
+            for (; issued < nchunks && issued <= c + DEV_AHEAD && rc == MGL_SW_OK; issued++)
+                rc = issue_plan_dev(in, bounds[(size_t)issued].first, bounds[(size_t)issued].second, *ring_[(size_t)(issued % R)], bs);
+            if (rc != MGL_SW_OK) break;
+            if ((rc = collect_plan_dev(cd)) != MGL_SW_OK) break;
+        } else if (nchunks == 1) {
             std::string err;
             rc = plan_range(in, bounds[0].first, bounds[0].second, cd, err);
             if (rc != MGL_SW_OK) { fail(rc, err); break; }
@@ -731,7 +840,7 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         const double t_slot = tl_ms();
         const int64_t first = cd.first;
         if ((rc = ensure_slot(ws, cd.plan, cd.n, so, tx)) != MGL_SW_OK) break;
-        if ((rc = upload_chunk(in, cd, ws.stream, !whole, bs)) != MGL_SW_OK) break;
+        if ((rc = dev_plan ? upload_arena_range(in, cd, ws.stream, !whole, bs) : upload_chunk(in, cd, ws.stream, !whole, bs)) != MGL_SW_OK) break;
         if ((rc = run_chunk(cd, ws, bs, false, so, tx)) != MGL_SW_OK) break;
         const u32 n = cd.n;
         if (so) {

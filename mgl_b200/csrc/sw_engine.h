@@ -19,6 +19,7 @@
 
 #include "sw_fill.h"
 #include "sw_plan.h"
+#include "sw_plan_dev_api.h"
 
 /* work slots: chunks in flight at once (each owns checkpoint, scratch and result buffers and two streams) */
 #define MGLSW_SLOTS 4
@@ -84,6 +85,16 @@ struct ChunkDev {
     DevBuf packed;
     PinBuf h_packed;
     std::vector<PairIn> pairs_scratch;
+    /* what the kernels of this chunk read, whichever planner produced it */
+    const UnitDesc *d_units = nullptr;
+    const u64 *d_ops_end = nullptr;
+    const int *d_strategy = nullptr;
+    /* device planner (sw_plan_dev.cu): the chunk's slice of the pair table, staged in pinned memory and uploaded;
+       work buffer; the summary the host reads back; the event that says the summary is home */
+    DevBuf table, work;
+    PinBuf h_table, h_sum;
+    PlanDevLayout lay{};
+    cudaEvent_t ev_plan = nullptr;
     void release();
 };
 
@@ -136,10 +147,15 @@ private:
     int fail(int code, const std::string &msg);
     int cuda_fail(cudaError_t e, const char *what);
     int plan_next(const BatchIn &in, int64_t first, ChunkDev &cd);
+    /* device planner: stage + upload the pair-table slice and queue the planning kernels on plan_stream_;
+       then (later) wait for the summary and turn it into cd.plan */
+    int issue_plan_dev(const BatchIn &in, int64_t first, int64_t take, ChunkDev &cd, BatchStats &bs);
+    int collect_plan_dev(ChunkDev &cd);
     int64_t chunk_take(const BatchIn &in, int64_t first, u64 limit, u32 max_pairs, const u32 *est256) const;
     int plan_range(const BatchIn &in, int64_t first, int64_t take, ChunkDev &cd, std::string &err) const;
     int pack_chunk(const BatchIn &in, ChunkDev &cd, std::string &err) const;
     int upload_chunk(const BatchIn &in, ChunkDev &cd, cudaStream_t st, bool upload_arena, BatchStats &bs);
+    int upload_arena_range(const BatchIn &in, ChunkDev &cd, cudaStream_t st, bool upload_arena, BatchStats &bs);
     int run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed, bool score_only = false, bool text = false);
     int ensure_slot(WorkSlot &ws, const ChunkPlan &plan, u32 n, bool score_only = false, bool text = false);
     u64 budget();
@@ -157,6 +173,8 @@ private:
     int reserve_arena(u64 base, u64 span, u32 max_tl);
     std::vector<u64> estpre_;    /* align_batch: prefix sums of the per-pair checkpoint estimate */
     WorkSlot slots_[MGLSW_SLOTS];
+    cudaStream_t plan_stream_ = nullptr;     /* device planner: high priority, runs ahead of the fills */
+    unsigned wait_flags_ = 0;                /* flags of the events the host waits on (spinning or sleeping) */
     std::vector<ChunkDev *> ring_;           /* align_batch: staging entries the planner threads fill */
     std::vector<ChunkDev *> resident_;
     std::vector<DevBuf> resident_results_;   /* per chunk: offsets | starts | ops kept on device */

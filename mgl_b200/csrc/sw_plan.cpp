@@ -7,18 +7,13 @@
 
 #include "sw_cell.h"
 #include "sw_layout.h"
+#include "sw_plan_rules.h"
 
 namespace mglsw {
 
 namespace {
 
 long long absll(long long v) { return v < 0 ? -v : v; }
-
-/* margin for the garbage rows a lane computes before its row 1 and after its last row */
-long long ramp_margin(const Scores &s, int G)
-{
-    return (long long)(G + 4) * ((long long)s.match + absll(s.mismatch) + s.go + s.ge);
-}
 
 /* a coarse magnitude of one cell's score differences; only used to refuse absurd score sets */
 long long diff_bound(const Scores &s)
@@ -97,20 +92,7 @@ PlanStatus check_scores(const Scores &s)
     return PLAN_OK;
 }
 
-static void value_bounds(const Scores &s, u32 tl, u32 ql, int G, long long &lo, long long &hi)
-{
-    const long long m = ramp_margin(s, G);
-    lo = -(3ll * s.go + (long long)s.ge * ((long long)tl + ql + 2) + absll(s.mismatch)) - m;
-    hi = (long long)s.match * ((long long)std::min(tl, ql) + 2) + m;
-}
-
-bool s16_bounds(const Scores &s, u32 tl, u32 ql, long long &lo, long long &hi)
-{
-    value_bounds(s, tl, ql, MGLSW_G_SHORT, lo, hi);
-    if (s.match - s.mismatch >= 32768) return false;
-    if (tl > 65535u) return false;                         /* the fused last-column maximum packs (value, row) in 32 bits */
-    return hi - lo < 65000;
-}
+bool s16_bounds(const Scores &s, u32 tl, u32 ql, long long &lo, long long &hi) { return s16_bounds_hd(s, tl, ql, lo, hi); }
 
 PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s16, ChunkPlan &out)
 {
@@ -126,16 +108,14 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
     long long need_bias = 0;
     for (u32 p = 0; p < n; p++) {
         const PairIn &pr = pairs[p];
-        if (pr.tl == 0 || pr.ql == 0 || pr.tl > (1u << 24) || pr.ql > (1u << 24)) return PLAN_BAD_PAIR;
-        long long lo, hi;
-        value_bounds(s, pr.tl, pr.ql, MGLSW_G_LONG, lo, hi);
-        if (-lo >= (1ll << 30) || hi >= (1ll << 30)) return PLAN_BAD_PAIR;
-        if (allow_s16 && pr.ql <= (u32)MGLSW_G_SHORT * MGLSW_KMAX && s16_bounds(s, pr.tl, pr.ql, lo, hi)) {
+        if (!pair_ok(s, pr.tl, pr.ql)) return PLAN_BAD_PAIR;
+        long long need;
+        if (s16_candidate(s, allow_s16, pr.tl, pr.ql, need)) {
             cand[p] = 1;
-            need_bias = std::max(need_bias, -lo);
+            need_bias = std::max(need_bias, need);
         }
     }
-    const long long bias16 = std::min<long long>(need_bias, 49152);
+    const long long bias16 = s16_bias_of(need_bias);
     out.s16_bias = (int)bias16;
 
     /* pass 2: sort key = (kind, G, K, nstrips, indel, ql, tl), all descending so heavy work launches first;
@@ -144,27 +124,8 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
     u64 *const fkey = out.full_key.data();
     for (u32 p = 0; p < n; p++) {
         const PairIn &pr = pairs[p];
-        int kind = KIND_S32;
-        if (cand[p]) {
-            long long lo, hi;
-            s16_bounds(s, pr.tl, pr.ql, lo, hi);
-            if (-lo <= bias16 && hi <= 65535 - bias16) kind = KIND_S16X2;
-        }
-        u32 G, nstrips;
-        if (pr.ql <= (u32)MGLSW_G_SHORT * MGLSW_KMAX) { G = MGLSW_G_SHORT; nstrips = 1; }
-        else { G = MGLSW_G_LONG; nstrips = ceil_div_u32(pr.ql, (u32)MGLSW_G_LONG * MGLSW_KMAX); }
-        const u32 K = regs_per_lane(pr.ql, nstrips * G);
-        const u32 indel = (pr.strategy & (OS_INDEL | OS_LEADING_INDEL)) ? 1u : 0u;
-        /* 1 + 1 + 5 + 1 bits of launch key (kind, G, K, strips pipelined over the block's warps), then 11 + 1 + 24 + 20
-           bits of shape (strips and tl clipped for the key only) */
-        u64 key = (u64)(kind == KIND_S32 ? 1 : 0);
-        key = (key << 1) | (G == (u32)MGLSW_G_LONG ? 1u : 0u);
-        key = (key << 5) | K;
-        key = (key << 1) | (nstrips >= (u32)MGLSW_PIPE_MIN_STRIPS ? 1u : 0u);
-        key = (key << 11) | std::min<u32>(nstrips, 2047);
-        key = (key << 1) | indel;
-        key = (key << 24) | pr.ql;
-        key = (key << 20) | std::min<u32>(pr.tl, (1u << 20) - 1);
+        const int kind = (cand[p] && s16_fits(s, pr.tl, pr.ql, bias16)) ? KIND_S16X2 : KIND_S32;
+        const u64 key = pair_key(kind, pr.tl, pr.ql, pr.strategy);      /* sw_plan_rules.h */
         fkey[p] = ~key;                 /* ascending sort of ~key == descending key */
         out.sort_key[p] = ~key;
         out.sort_idx[p] = p;
@@ -272,6 +233,7 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
         out.ops_end[p] = acc;
     }
     out.scratch_words = acc;
+    out.n_units = (u32)out.units.size();
     return PLAN_OK;
 }
 

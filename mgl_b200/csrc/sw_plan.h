@@ -39,6 +39,8 @@ struct ChunkPlan {
     std::vector<Launch> launches;
     std::vector<u32> pair_unit;     /* per chunk-local pair: unit index * 2 + half */
     std::vector<u64> ops_end;       /* per pair: one-past-the-end word of its CIGAR scratch */
+    u32 n_units = 0;                /* unit descriptors of the chunk, padding included (== units.size() when planned on the host; */
+                                    /* a chunk planned on the device has its descriptors in HBM only and `units` stays empty)     */
     u64 ckpt_words = 0;             /* column + row checkpoints of every warp */
     u64 carry_entries = 0;
     u64 lastrow_words = 0;
@@ -52,7 +54,7 @@ struct ChunkPlan {
     std::vector<unsigned char> cand;
     void reset()                     /* empty, capacity kept */
     {
-        units.clear(); launches.clear(); pair_unit.clear(); ops_end.clear();
+        units.clear(); launches.clear(); pair_unit.clear(); ops_end.clear(); n_units = 0;
         ckpt_words = carry_entries = lastrow_words = scratch_words = cells = pairs_s16 = pairs_s32 = 0;
         s16_bias = 0;
     }

@@ -15,14 +15,91 @@
 #include <algorithm>
 #include <vector>
 
+#include <numeric>
+
 #include "sw_config.h"
 #include "sw_fill.h"
 #include "sw_plan.h"
+#include "sw_plan_dev.h"
 #include "sw_trace.h"
 
 using namespace mglsw;
 
 namespace {
+
+int g_device_plan = 0;
+
+/*
+ * The device planner (sw_plan_dev.h) on the CPU: the same stage bodies the CUDA kernels of sw_plan_dev.cu run, one
+ * loop iteration per thread, with std::stable_sort / std::partial_sum where the device uses a radix sort and scans.
+ * Produces the ChunkPlan the emulated kernels consume, so that planner + fill + traceback are checked end to end.
+ */
+PlanStatus plan_chunk_dev_emu(const PairIn *pairs, u32 n, u64 arena_bytes, const Scores &s, bool allow_s16, bool score_only, ChunkPlan &out)
+{
+    out.reset();
+    if (check_scores(s) != PLAN_OK) return PLAN_BAD_SCORES;
+    std::vector<u64> ro(n), ao(n);
+    std::vector<u32> tl(n), ql(n);
+    std::vector<int> strat(n);
+    for (u32 p = 0; p < n; p++) { ro[p] = pairs[p].ref_off; ao[p] = pairs[p].alt_off; tl[p] = pairs[p].tl; ql[p] = pairs[p].ql; strat[p] = pairs[p].strategy; }
+    PlanDevIn in;
+    in.ref_off = ro.data(); in.alt_off = ao.data(); in.tl = tl.data(); in.ql = ql.data(); in.strategy = strat.data();
+    in.n = n; in.arena_bytes = arena_bytes; in.s = s; in.allow_s16 = allow_s16 ? 1 : 0; in.score_only = score_only ? 1 : 0;
+    PlanState st;
+    std::memset(&st, 0, sizeof st);
+    std::vector<u64> oplen(n), key(n), skey(n), ops_end(n);
+    std::vector<u32> idx(n), order(n), runmark(n), run_start(n), uhead(n), urank(n);
+    for (u32 p = 0; p < n; p++) pd_stage_a(in, p, &st, oplen.data());
+    for (u32 p = 0; p < n; p++) {
+        const int kind = pd_stage_b(in, p, &st, key.data(), idx.data());
+        (kind == KIND_S16X2 ? st.pairs_s16 : st.pairs_s32)++;
+        st.cells += (u64)tl[p] * ql[p];
+    }
+    std::stable_sort(idx.begin(), idx.end(), [&](u32 a, u32 b) { return key[a] < key[b]; });
+    for (u32 q = 0; q < n; q++) { order[q] = idx[q]; skey[q] = key[idx[q]]; }
+    for (u32 q = n; q-- > 0;) pd_stage_c(n, q, skey.data(), &st, runmark.data());        /* any thread order: heads arrive unsorted */
+    { u32 m = 0; for (u32 q = 0; q < n; q++) { m = std::max(m, runmark[q]); run_start[q] = m; } }
+    for (u32 q = 0; q < n; q++) pd_stage_d(q, skey.data(), run_start.data(), uhead.data());
+    { u32 run = 0; for (u32 q = 0; q < n; q++) { urank[q] = run; run += uhead[q]; } }
+    pd_stage_e(n, skey.data(), urank.data(), uhead.data(), &st);
+    const u32 U = st.sum.n_units;
+    std::vector<UnitDesc> units(U);
+    std::memset(units.data(), 0xee, U * sizeof(UnitDesc));                                /* device memory is not zeroed either */
+    for (u32 q = 0; q < n; q++) pd_stage_f(in, q, order.data(), run_start.data(), uhead.data(), urank.data(), &st, units.data());
+    std::vector<U3> u3(U), u3x(U);
+    for (u32 u = 0; u < U; u++) pd_stage_g(u, &st, units.data(), u3.data());
+    { U3 run; run.a = run.b = run.c = 0; for (u32 u = 0; u < U; u++) { u3x[u] = run; run = run + u3[u]; } }
+    for (u32 u = 0; u < U; u++) pd_stage_h(in, u, &st, units.data(), u3.data(), u3x.data());
+    { u64 run = 0; for (u32 p = 0; p < n; p++) { run += oplen[p]; ops_end[p] = run; } }
+    pd_stage_i(in, &st, ops_end.data());
+
+    const PlanSummary &S = st.sum;
+    if (S.err_invalid) return PLAN_BAD_PAIR;
+    if (S.err_pair) return PLAN_BAD_PAIR;
+    if (S.overflow) return PLAN_BAD_PAIR;
+    out.units = units;
+    out.ops_end = ops_end;
+    out.pair_unit.assign(n, 0xffffffffu);
+    for (u32 u = 0; u < U; u++) {
+        if (!(units[u].flags & UNIT_ACTIVE)) continue;
+        for (u32 h = 0; h < 2; h++) if (units[u].pair[h] != NO_PAIR && (h == 0 || !(units[u].flags & UNIT_S32))) {
+            if (out.pair_unit[units[u].pair[h]] != 0xffffffffu) return PLAN_BAD_PAIR;     /* a pair placed twice */
+            out.pair_unit[units[u].pair[h]] = u * 2 + h;
+        }
+    }
+    for (u32 p = 0; p < n; p++) if (out.pair_unit[p] == 0xffffffffu) return PLAN_BAD_PAIR;   /* a pair not placed */
+    for (u32 l = 0; l < S.n_launches; l++) {
+        const PlanLaunchDev &D = S.launch[l];
+        Launch L;
+        L.kind = (int)D.kind; L.G = (int)D.G; L.K = (int)D.K; L.pipe = (int)D.pipe;
+        L.nstrips = units[D.first_unit].nstrips; L.first_unit = D.first_unit; L.n_units = D.n_units; L.n_warps = D.n_warps; L.cells = 0;
+        out.launches.push_back(L);
+    }
+    out.ckpt_words = S.ckpt_words; out.carry_entries = S.carry_entries; out.lastrow_words = S.lastrow_words;
+    out.scratch_words = S.scratch_words; out.cells = S.cells; out.pairs_s16 = S.pairs_s16; out.pairs_s32 = S.pairs_s32;
+    out.s16_bias = (int)S.s16_bias;
+    return PLAN_OK;
+}
 
 template <class T, int G, int K>
 void emu_launch(const FillArgs &a, const Launch &L)
@@ -68,6 +145,44 @@ bool emu_dispatch(const FillArgs &a, const Launch &L)
 
 extern "C" {
 
+/* 1: plan with the device planner's stage bodies (sw_plan_dev.h) instead of the host planner (sw_plan.cpp) */
+void emu_use_device_plan(int on) { g_device_plan = on; }
+
+/*
+ * Both planners on one chunk: sizes and bucket structure must agree exactly (the unit arrays may differ in the
+ * order of equal-key pairs only).  out[0..7] host, out[8..15] device: launches, units, s16 pairs, s32 pairs,
+ * checkpoint words, last-row words, carry entries, scratch words.  Returns 0, or a planner's status.
+ */
+int emu_compare_planners(int n, const uint64_t *ref_off, const uint32_t *ref_len, const uint64_t *alt_off, const uint32_t *alt_len,
+                         const int32_t *strategies, int match, int mismatch, int gap_open, int gap_extend, int allow_s16, uint64_t *out16)
+{
+    const Scores s = normalise_scores(match, mismatch, gap_open, gap_extend);
+    std::vector<PairIn> pairs(n);
+    u64 bytes = 0;
+    for (int p = 0; p < n; p++) {
+        pairs[p].ref_off = ref_off[p]; pairs[p].alt_off = alt_off[p]; pairs[p].tl = ref_len[p]; pairs[p].ql = alt_len[p]; pairs[p].strategy = strategies[p];
+        bytes = std::max<u64>(bytes, std::max(ref_off[p] + ref_len[p], alt_off[p] + alt_len[p]));
+    }
+    ChunkPlan a, b;
+    PlanStatus ps = plan_chunk(pairs.data(), (u32)n, s, allow_s16 != 0, a);
+    if (ps != PLAN_OK) return (int)ps;
+    ps = plan_chunk_dev_emu(pairs.data(), (u32)n, bytes, s, allow_s16 != 0, false, b);
+    if (ps != PLAN_OK) return 100 + (int)ps;
+    const ChunkPlan *pl[2] = {&a, &b};
+    for (int k = 0; k < 2; k++) {
+        uint64_t *o = out16 + 8 * k;
+        o[0] = pl[k]->launches.size(); o[1] = pl[k]->units.size(); o[2] = pl[k]->pairs_s16; o[3] = pl[k]->pairs_s32;
+        o[4] = pl[k]->ckpt_words; o[5] = pl[k]->lastrow_words; o[6] = pl[k]->carry_entries; o[7] = pl[k]->scratch_words;
+    }
+    /* launch tables agree field by field */
+    if (a.launches.size() != b.launches.size()) return 200;
+    for (size_t l = 0; l < a.launches.size(); l++) {
+        const Launch &x = a.launches[l], &y = b.launches[l];
+        if (x.kind != y.kind || x.G != y.G || x.K != y.K || x.pipe != y.pipe || x.first_unit != y.first_unit || x.n_units != y.n_units || x.n_warps != y.n_warps) return 201 + (int)l;
+    }
+    return 0;
+}
+
 /*
  * Align a batch through planner + emulated kernels.  ops_out: per pair a
  * region of ops_stride words, elements left to right.  Returns 0, or a
@@ -86,7 +201,10 @@ int emu_align_batch(int n, const uint8_t *arena, const uint64_t *ref_off, const 
         pairs[p].strategy = strategies[p];
     }
     ChunkPlan plan;
-    const PlanStatus ps = plan_chunk(pairs.data(), (u32)n, s, allow_s16 != 0, plan);
+    u64 caller_bytes = 0;
+    for (int p = 0; p < n; p++) caller_bytes = std::max<u64>(caller_bytes, std::max(ref_off[p] + ref_len[p], alt_off[p] + alt_len[p]));
+    const PlanStatus ps = g_device_plan ? plan_chunk_dev_emu(pairs.data(), (u32)n, caller_bytes, s, allow_s16 != 0, false, plan)
+                                        : plan_chunk(pairs.data(), (u32)n, s, allow_s16 != 0, plan);
     if (ps != PLAN_OK) return -(int)ps;
 
     std::vector<u32> ckpt(plan.ckpt_words + 4, 0xdeadbeefu);

@@ -48,9 +48,11 @@ def pack_batch(pairs):
     return arena, offs[0::2].copy(), ref_len, offs[1::2].copy(), alt_len
 
 
-def emu_align(pairs, params, strategies, allow_s16=True):
-    """-> list of (cigar text, offset), plus stats dict"""
+def emu_align(pairs, params, strategies, allow_s16=True, device_plan=False):
+    """-> list of (cigar text, offset), plus stats dict.  device_plan: the chunk is planned by the device planner's
+    stage bodies (mgl_b200/csrc/sw_plan_dev.h) instead of the host planner (sw_plan.cpp)."""
     lib = _load()
+    lib.emu_use_device_plan(1 if device_plan else 0)
     n = len(pairs)
     arena, ro, rl, ao, al = pack_batch(pairs)
     st = np.asarray(strategies, dtype=np.int32)
@@ -99,3 +101,25 @@ def ph_emu(reads, haps, use_double=False, rpl=4):
     out = np.zeros((len(reads), len(haps)), dtype=np.float64)
     _ph_lib.ph_emu(lengths.ctypes.data, rb.ctypes.data, hb.ctypes.data, int(use_double), int(rpl), out.ctypes.data)
     return out
+
+
+def compare_planners(pairs_lens, params, strategies, allow_s16=True):
+    """pairs_lens: [(tl, ql)].  Host planner vs device planner stage bodies on one chunk -> (rc, host8, device8):
+    launches, units, s16 pairs, s32 pairs, checkpoint / last-row / carry / scratch words."""
+    lib = _load()
+    n = len(pairs_lens)
+    rl = np.array([t for t, _ in pairs_lens], dtype=np.uint32)
+    al = np.array([q for _, q in pairs_lens], dtype=np.uint32)
+    sizes = np.empty(2 * n, dtype=np.uint64)
+    sizes[0::2], sizes[1::2] = rl, al
+    offs = np.concatenate([[0], np.cumsum(sizes)[:-1]]).astype(np.uint64)
+    ro, ao = offs[0::2].copy(), offs[1::2].copy()
+    st = np.asarray(strategies, dtype=np.int32)
+    if st.ndim == 0:
+        st = np.full(n, int(st), dtype=np.int32)
+    out = np.zeros(16, dtype=np.uint64)
+    lib.emu_compare_planners.restype = C.c_int
+    lib.emu_compare_planners.argtypes = [C.c_int] + [C.c_void_p] * 5 + [C.c_int] * 5 + [C.c_void_p]
+    rc = lib.emu_compare_planners(n, ro.ctypes.data, rl.ctypes.data, ao.ctypes.data, al.ctypes.data, st.ctypes.data,
+                                  params[0], params[1], params[2], params[3], 1 if allow_s16 else 0, out.ctypes.data)
+    return rc, [int(x) for x in out[:8]], [int(x) for x in out[8:]]

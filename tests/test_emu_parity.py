@@ -70,3 +70,68 @@ def test_planner_rejects_bad_input():
         E.emu_align([(b"ACGT", b"")], (10, -15, -30, -5), 1)
     with pytest.raises(RuntimeError):
         E.emu_align([(b"ACGT", b"ACGT")], (1 << 27, -(1 << 27), -(1 << 27), -5), 1)
+
+
+# ---- the device planner (mgl_b200/csrc/sw_plan_dev.h): its stage bodies run on the CPU by the emulator
+
+def test_device_planner_matches_host_planner_structure():
+    """Both planners on the same chunk: same launches (arithmetic, lane group, K, pipelined, first unit, units, warps),
+    same unit count, same checkpoint / last-row / carry / scratch sizes -- config-2, config-3, mixed and degenerate shapes."""
+    rng = random.Random(2024)
+    shapes = {
+        "config2": [(rng.randint(300, 500), rng.randint(145, 165)) for _ in range(5000)],
+        "config3": [(rng.randint(300, 1000), rng.randint(300, 1000)) for _ in range(1500)],
+        "mixed": [(rng.randint(300, 500), rng.randint(140, 170)) for _ in range(3000)] + [(rng.randint(300, 1000), rng.randint(300, 1000)) for _ in range(330)]
+                 + [(rng.randint(5000, 10000), rng.randint(5000, 10000)) for _ in range(7)] + [(1, 1), (1, 3000), (70000, 5), (5, 70000), (192, 192), (193, 193)],
+        "one": [(450, 150)],
+        "same": [(400, 150)] * 777,
+    }
+    for name, lens in shapes.items():
+        for params in ((10, -15, -30, -5), (200, -150, -260, -11)):
+            for allow in (True, False):
+                strategies = [(1, 2, 4, 8)[k % 4] for k in range(len(lens))]
+                rng.shuffle(lens)
+                rc, host, dev = E.compare_planners(lens, params, strategies, allow)
+                assert rc == 0 and host == dev, (name, params, allow, rc, host, dev)
+
+
+@pytest.mark.parametrize("allow_s16", [True, False])
+def test_device_planned_emulated_kernels_match_golden(golden, allow_s16):
+    """planner stages + fill lanes + traceback, all the code the GPU runs, against the reference-generated vectors"""
+    by = _by_params(golden)
+    total = 0
+    for p in [(10, -15, -30, -5), (200, -150, -260, -11), (3, -1, -2, 0)]:
+        cs = by[p]
+        pairs = [(c["ref"].encode("latin1"), c["alt"].encode("latin1")) for c in cs]
+        strategies = [golden["strategies"][k % 4] for k in range(len(cs))]
+        res, st = E.emu_align(pairs, p, strategies, allow_s16, device_plan=True)
+        assert (st["s16"] > 0) == allow_s16
+        bad = [(c["ref"], c["alt"], p, r, tuple(c["expect"][k % 4])) for k, (c, r) in enumerate(zip(cs, res)) if r != tuple(c["expect"][k % 4])]
+        assert not bad, bad[:3]
+        total += len(cs)
+    assert total > 1000
+
+
+def test_device_planned_strip_mined_and_mixed(oracle):
+    rng = random.Random(12)
+    pairs = []
+    for ql in (1, 7, 150, 151, 191, 192, 193, 300, 767, 768, 769, 1000, 1537, 2305):
+        for _ in range(2):
+            tl = rng.randint(1, 600)
+            ref = bytes(rng.choice(b"ACGT") for _ in range(tl))
+            alt = bytearray(rng.choice(b"ACGT") for _ in range(ql))
+            w = min(tl, ql)
+            alt[:w] = ref[:w]
+            for _ in range(4):
+                alt[rng.randrange(ql)] = rng.choice(b"ACGT")
+            pairs.append((ref, bytes(alt)))
+    for params in ((200, -150, -260, -11), (10, -15, -30, -5)):
+        strategies = [(1, 2, 4, 8)[k % 4] for k in range(len(pairs))]
+        res, st = E.emu_align(pairs, params, strategies, device_plan=True)
+        for k, ((r, a), got) in enumerate(zip(pairs, res)):
+            assert got == oracle.align(r, a, params, strategies[k]), (len(r), len(a), params, strategies[k])
+
+
+def test_device_planner_rejects_bad_input():
+    with pytest.raises(RuntimeError):
+        E.emu_align([(b"ACGT", b"ACGT"), (b"ACGT", b"")], (10, -15, -30, -5), 1, device_plan=True)

@@ -473,6 +473,8 @@ def test_multi_device_handle_matches_single_and_oracle(sw, oracle):
     multi = mgl_b200.MicrosoftSmithWaterman(devices)
     try:
         multi._ensure()
+        if ndev == 1:
+            multi.set_option("trace_budget_mb", 3000)     # three engines (and the fixture's) share one GPU's memory here
         got = (C.c_int * 16)()
         assert native.lib().mgl_sw_handle_devices(multi._h, got, 16) == len(devices) and list(got[:len(devices)]) == devices
         res = multi.align_arrays(*args, ops_cap=cap)
@@ -522,3 +524,58 @@ def test_default_handle_survives_done_native(sw, oracle):
     fn(None, None)                                       # idempotent
     one = mgl_b200.align_one_text(b"ACGTACGTAC", b"GGGGGGGGGGGG", P, 8)
     assert (one.cigar, one.alignment_offset) == ("13D1M", -11)
+
+
+def test_device_planner_and_host_planner_give_identical_results(sw, oracle):
+    """Chunks are planned by device kernels (sw_plan_dev.cu) unless "host_plan" is set: the same batches through both
+    planners must return identical arrays -- a mixed config-5 batch (every kernel shape, several chunks), tie-heavy
+    fuzz with all four strategies, text and score-only entries -- and bad input must fail the same way."""
+    from mgl_b200 import native, synth
+    n = 120_000
+    d = synth.generate(5, n)
+    args = (d["arena"], d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, d["strategies"])
+    cap = max(8 * n, int(d["ref_len"].astype(np.int64).sum() + d["alt_len"].astype(np.int64).sum()) // 8)
+    rng = random.Random(4)
+    fuzz = []
+    for k in range(3000):
+        alpha = rng.choice([b"A", b"AC", b"ACGT"])
+        ref = bytes(rng.choice(alpha) for _ in range(rng.randint(1, 400)))
+        alt = bytes(rng.choice(alpha) for _ in range(rng.randint(1, 260)))
+        fuzz.append((ref, alt))
+    fst = np.array([(1, 2, 4, 8)[k % 4] for k in range(len(fuzz))], dtype=np.int32)
+    got = {}
+    try:
+        for hp in (0, 1):
+            sw.set_option("host_plan", hp)
+            sw.set_option("chunk_pairs", 16384)
+            a = sw.align_arrays(*args, ops_cap=cap)
+            b = sw.align_batch(fuzz, (3, -1, -2, 0), 1, fst)
+            sw.set_option("allow_s16", 0)
+            c = sw.align_batch(fuzz, (3, -1, -2, 0), 1, fst)
+            sw.set_option("allow_s16", 1)
+            t = sw.align_arrays_text(*(x[:20000] if k in (1, 2, 3, 4) else x for k, x in enumerate(args[:5])), d["params"], 1, d["strategies"][:20000])
+            s3, _ = sw.score_arrays(*(x[:20000] if k in (1, 2, 3, 4) else x for k, x in enumerate(args[:5])), d["params"], 1, d["strategies"][:20000])
+            got[hp] = (a, b, c, t, s3)
+            assert a.stats["pairs"] == n and a.stats["cells"] == d["cells"] and a.stats["chunks"] > 4
+            with pytest.raises(native.MglSwError) as e:
+                sw.align_batch([(b"ACGT", b"ACGT")] * 5 + [(b"", b"ACGT")], (10, -15, -30, -5), 1)
+            assert e.value.code == native.E_PAIR
+            bad = native.make_batch(np.frombuffer(b"ACGTACGT", dtype=np.uint8), [0, 2 ** 63], [4, 4], [4, 4], [4, 4], (10, -15, -30, -5), 1, None)
+            r = native.Result()
+            off, cs, ops = np.zeros(2, np.int32), np.zeros(3, np.uint64), np.zeros(64, np.uint32)
+            r.offsets, r.cigar_start, r.ops, r.ops_cap = off.ctypes.data, cs.ctypes.data, ops.ctypes.data, 64
+            assert native.lib().mgl_sw_align_batch(sw._ensure(), C.byref(bad[0]), C.byref(r), None) == native.E_INVALID
+    finally:
+        sw.set_option("host_plan", 0)
+        sw.set_option("chunk_pairs", 1 << 16)
+        sw.set_option("allow_s16", 1)
+    for x, y in zip(got[0][:3], got[1][:3]):
+        assert np.array_equal(x.offsets, y.offsets) and np.array_equal(x.cigar_start, y.cigar_start) and np.array_equal(x.ops, y.ops)
+        assert x.stats["pairs_s16"] == y.stats["pairs_s16"] and x.stats["fill_launches"] == y.stats["fill_launches"]
+        assert x.stats["trace_bytes"] == y.stats["trace_bytes"]
+    for k in range(3):
+        assert np.array_equal(got[0][3][k], got[1][3][k])
+    assert np.array_equal(got[0][4], got[1][4])
+    for p in range(0, len(fuzz), 3):
+        exp = oracle.align(fuzz[p][0], fuzz[p][1], (3, -1, -2, 0), int(fst[p]))
+        assert (got[0][1].cigar(p), int(got[0][1].offsets[p])) == exp and (got[0][2].cigar(p), int(got[0][2].offsets[p])) == exp, p
