@@ -80,6 +80,7 @@ void ChunkDev::release()
     packed.release(); h_packed.release();
     table.release(); work.release(); h_table.release(); h_sum.release();
     if (ev_plan) { cudaEventDestroy(ev_plan); ev_plan = nullptr; }
+    for (auto &x : ev_dbg) if (x) { cudaEventDestroy(x); x = nullptr; }
 }
 
 void WorkSlot::release()
@@ -330,23 +331,24 @@ int Engine::plan_next(const BatchIn &in, int64_t first, ChunkDev &cd)
  * and goes up on the planner's stream, followed by the planning kernels and the copy home of the summary.  The host
  * touches each pair twice here (the memcpy and the min / max of its offsets) and never again.
  */
-int Engine::issue_plan_dev(const BatchIn &in, int64_t first, int64_t take, ChunkDev &cd, BatchStats &bs)
+int Engine::issue_plan_dev(const BatchIn &in, int64_t first, int64_t take, ChunkDev &cd, BatchStats &bs, std::string &err) const
 {
+    auto cfail = [&](cudaError_t ce, const char *what) { err = std::string(what) + ": " + cudaGetErrorString(ce); cudaGetLastError(); return (int)MGL_SW_E_CUDA; };
     cudaError_t e;
     const u32 n = (u32)take;
     cd.first = first; cd.n = n; cd.packed_ok = false;
     cd.plan.reset();
-    if (!cd.ev_plan && (e = cudaEventCreateWithFlags(&cd.ev_plan, wait_flags_)) != cudaSuccess) return cuda_fail(e, "event create");
+    if (!cd.ev_plan && (e = cudaEventCreateWithFlags(&cd.ev_plan, wait_flags_)) != cudaSuccess) return cfail(e, "event create");
     if (n > cd.lay.n_cap || !cd.work.p) {
         cd.lay = plan_dev_layout(std::max<u32>(n + n / 8, 4096));
-        if ((e = cd.work.reserve(cd.lay.total)) != cudaSuccess) return cuda_fail(e, "cudaMalloc planner work buffer");
+        if ((e = cd.work.reserve(cd.lay.total)) != cudaSuccess) return cfail(e, "cudaMalloc planner work buffer");
     }
     const size_t tbytes = (size_t)n * 28;
-    if ((e = cd.h_table.reserve(tbytes)) != cudaSuccess) return cuda_fail(e, "pinned alloc");
-    if ((e = cd.h_sum.reserve(sizeof(PlanSummary))) != cudaSuccess) return cuda_fail(e, "pinned alloc");
-    if ((e = cd.table.reserve(tbytes)) != cudaSuccess) return cuda_fail(e, "cudaMalloc pair table");
-    if ((e = cd.units.reserve((size_t)plan_dev_unit_capacity(n) * sizeof(UnitDesc))) != cudaSuccess) return cuda_fail(e, "cudaMalloc units");
-    if ((e = cd.ops_end.reserve((size_t)n * sizeof(u64))) != cudaSuccess) return cuda_fail(e, "cudaMalloc");
+    if ((e = cd.h_table.reserve(tbytes)) != cudaSuccess) return cfail(e, "pinned alloc");
+    if ((e = cd.h_sum.reserve(sizeof(PlanSummary))) != cudaSuccess) return cfail(e, "pinned alloc");
+    if ((e = cd.table.reserve(tbytes)) != cudaSuccess) return cfail(e, "cudaMalloc pair table");
+    if ((e = cd.units.reserve((size_t)plan_dev_unit_capacity(n) * sizeof(UnitDesc))) != cudaSuccess) return cfail(e, "cudaMalloc units");
+    if ((e = cd.ops_end.reserve((size_t)n * sizeof(u64))) != cudaSuccess) return cfail(e, "cudaMalloc");
     char *h = (char *)cd.h_table.p;
     u64 *h_ro = (u64 *)h, *h_ao = (u64 *)(h + (size_t)n * 8);
     u32 *h_tl = (u32 *)(h + (size_t)n * 16), *h_ql = (u32 *)(h + (size_t)n * 20);
@@ -365,7 +367,13 @@ int Engine::issue_plan_dev(const BatchIn &in, int64_t first, int64_t take, Chunk
     }
     cd.arena_lo = std::min(lo, in.arena_bytes); cd.arena_hi = std::min(hi, in.arena_bytes);   /* offsets outside the arena are refused by the planner */
     if (cd.arena_lo > cd.arena_hi) cd.arena_lo = cd.arena_hi;
-    if ((e = cudaMemcpyAsync(cd.table.p, cd.h_table.p, tbytes, cudaMemcpyHostToDevice, plan_stream_)) != cudaSuccess) return cuda_fail(e, "H2D pair table");
+    static const bool tl_dbg = std::getenv("MGL_SW_TIMELINE") != nullptr;
+    if (tl_dbg) {
+        if (!cd.ev_dbg[0]) for (auto &x : cd.ev_dbg) cudaEventCreate(&x);
+        cudaEventRecord(cd.ev_dbg[0], plan_stream_);
+    }
+    if ((e = cudaMemcpyAsync(cd.table.p, cd.h_table.p, tbytes, cudaMemcpyHostToDevice, plan_stream_)) != cudaSuccess) return cfail(e, "H2D pair table");
+    if (tl_dbg) cudaEventRecord(cd.ev_dbg[1], plan_stream_);
     bs.h2d_bytes += tbytes;
     const char *d = (const char *)cd.table.p;
     PlanDevIn pin;
@@ -374,8 +382,9 @@ int Engine::issue_plan_dev(const BatchIn &in, int64_t first, int64_t take, Chunk
     pin.strategy = (const int *)(d + (size_t)n * 24);
     pin.n = n; pin.arena_bytes = in.arena_bytes; pin.s = in.scores; pin.allow_s16 = allow_s16 ? 1 : 0; pin.score_only = in.score_only ? 1 : 0;
     if ((e = plan_dev_run(pin, cd.lay, (UnitDesc *)cd.units.p, (u64 *)cd.ops_end.p, cd.work.p, (PlanSummary *)cd.h_sum.p, plan_stream_)) != cudaSuccess)
-        return cuda_fail(e, "device planner");
-    if ((e = cudaEventRecord(cd.ev_plan, plan_stream_)) != cudaSuccess) return cuda_fail(e, "event record");
+        return cfail(e, "device planner");
+    if (tl_dbg) cudaEventRecord(cd.ev_dbg[2], plan_stream_);
+    if ((e = cudaEventRecord(cd.ev_plan, plan_stream_)) != cudaSuccess) return cfail(e, "event record");
     cd.d_units = (const UnitDesc *)cd.units.p; cd.d_ops_end = (const u64 *)cd.ops_end.p; cd.d_strategy = pin.strategy;
     bs.other_launches += 20;                   /* 10 planner kernels + the sort's and the scans' own */
     return MGL_SW_OK;
@@ -385,6 +394,13 @@ int Engine::collect_plan_dev(ChunkDev &cd)
 {
     cudaError_t e;
     if ((e = cudaEventSynchronize(cd.ev_plan)) != cudaSuccess) return cuda_fail(e, "device planner");
+    if (cd.ev_dbg[0] && std::getenv("MGL_SW_TIMELINE")) {
+        float a = 0, b = 0;
+        cudaEventSynchronize(cd.ev_dbg[2]);
+        cudaEventElapsedTime(&a, cd.ev_dbg[0], cd.ev_dbg[1]);
+        cudaEventElapsedTime(&b, cd.ev_dbg[1], cd.ev_dbg[2]);
+        std::fprintf(stderr, "[mgl_sw] plan of chunk at pair %lld (n=%u): table H2D %.3f ms, kernels + summary D2H %.3f ms on the planner stream\n", (long long)cd.first, cd.n, a, b);
+    }
     const PlanSummary &S = *(const PlanSummary *)cd.h_sum.p;
     if (S.err_invalid) return fail(MGL_SW_E_INVALID, "pair " + std::to_string(cd.first + (int64_t)(0xffffffffu - S.err_invalid)) + " lies outside the arena");
     if (S.err_pair) return fail(MGL_SW_E_PAIR, "empty or over-long sequence in batch (pair " + std::to_string(cd.first + (int64_t)(0xffffffffu - S.err_pair)) + ")");
@@ -731,12 +747,14 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
      */
     /*
      * Who plans: device kernels (sw_plan_dev.cu) unless the caller asked for the host planner, or for the 2-bit
-     * transport, whose packing is done by the host planner threads.  With device planning this thread stages each
-     * chunk's slice of the pair table, queues the planning kernels DEV_AHEAD chunks ahead of the chunk it launches,
-     * and reads back a summary; no planner threads exist.
+     * transport, whose packing is done by the host planner threads.  With device planning ONE helper thread stages
+     * each chunk's slice of the pair table and queues its planning kernels, as far ahead as the ring allows
+     * (DEV_AHEAD chunks beyond the slots: under load a plan's ~30 small dependent kernels get SM space mostly when a
+     * fill kernel drains, about one plan per chunk time, so the look-ahead must cover several chunks), and this
+     * thread reads back a summary per chunk.
      */
     const bool dev_plan = host_plan == 0 && pack_arena == 0;
-    const int DEV_AHEAD = 3;
+    const int DEV_AHEAD = 7;
     std::vector<std::pair<int64_t, int64_t>> bounds;
     int nthreads = plan_threads > 0 ? plan_threads : (int)std::min<unsigned>(8u, std::max(1u, std::thread::hardware_concurrency() / 2));
     if (dev_plan) nthreads = 2;                           /* the ramp below counts chunks in planners: two rounds of two */
@@ -766,7 +784,7 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         }
     }
     const int nchunks = (int)bounds.size();
-    nthreads = dev_plan ? 0 : std::min(nthreads, nchunks);
+    nthreads = dev_plan ? 1 : std::min(nthreads, nchunks);
     setup_mark("chunk bounds");
     const int R = (dev_plan ? DEV_AHEAD : nthreads) + MGLSW_SLOTS + 1;
     while ((int)ring_.size() < R) ring_.push_back(new ChunkDev());
@@ -778,6 +796,8 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
     int collected = 0;                                   /* chunks [0, collected) have released their ring entry */
     bool stop = false;
     std::atomic<int> next_chunk{0};
+    BatchStats bs_stage;                                 /* what the staging thread of the device planner counts; merged at the end */
+    std::memset(&bs_stage, 0, sizeof bs_stage);
     auto planner = [&]() {
         cudaSetDevice(device_);
         for (;;) {
@@ -788,7 +808,8 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
                 cv.wait(lk, [&] { return stop || k - collected < R; });
                 if (stop) return;
             }
-            int prc_k = plan_range(in, bounds[(size_t)k].first, bounds[(size_t)k].second, *ring_[(size_t)(k % R)], perr[(size_t)k]);
+            int prc_k = dev_plan ? issue_plan_dev(in, bounds[(size_t)k].first, bounds[(size_t)k].second, *ring_[(size_t)(k % R)], bs_stage, perr[(size_t)k])
+                                 : plan_range(in, bounds[(size_t)k].first, bounds[(size_t)k].second, *ring_[(size_t)(k % R)], perr[(size_t)k]);
             if (prc_k == MGL_SW_OK && pack_batch && (pack_arena == 2 || k - upload_cursor.load(std::memory_order_relaxed) >= pack_lead))
                 prc_k = pack_chunk(in, *ring_[(size_t)(k % R)], perr[(size_t)k]);
             {
@@ -800,17 +821,15 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         }
     };
     std::vector<std::thread> workers;
-    if (nchunks > 1 && !dev_plan) for (int t = 0; t < nthreads; t++) workers.emplace_back(planner);
-    int issued = 0;                                      /* device planning: chunks whose planning kernels are queued */
+    if (nchunks > 1) for (int t = 0; t < nthreads; t++) workers.emplace_back(planner);
     auto release_upto = [&](int k) {                     /* chunks below k are collected */
         { std::lock_guard<std::mutex> lk(mu); if (k > collected) collected = k; }
         cv.notify_all();
     };
-
-    setup_mark("planners started");
     const bool tl_on = std::getenv("MGL_SW_TIMELINE") != nullptr;     /* host timeline of the chunk pipeline on stderr */
     const auto tl_t0 = std::chrono::steady_clock::now();
     auto tl_ms = [&]() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tl_t0).count(); };
+    setup_mark("planners started");
     if (tl_on) std::fprintf(stderr, "[mgl_sw] %d chunks, %d planner threads, setup took %.2f ms\n", nchunks, nthreads,
                             std::chrono::duration<double, std::milli>(tl_t0 - fn_t0).count());
     int c = 0;
@@ -819,21 +838,16 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         WorkSlot &ws = slots_[si];
         ChunkDev &cd = *ring_[(size_t)(c % R)];
         upload_cursor.store(c, std::memory_order_relaxed);
-        if (dev_plan) {
-            /* keep the planner DEV_AHEAD chunks ahead; entry k % R is free: chunk k - R came home SLOTS iterations ago */
-            for (; issued < nchunks && issued <= c + DEV_AHEAD && rc == MGL_SW_OK; issued++)
-                rc = issue_plan_dev(in, bounds[(size_t)issued].first, bounds[(size_t)issued].second, *ring_[(size_t)(issued % R)], bs);
-            if (rc != MGL_SW_OK) break;
-            if ((rc = collect_plan_dev(cd)) != MGL_SW_OK) break;
-        } else if (nchunks == 1) {
+        if (nchunks == 1) {
             std::string err;
-            rc = plan_range(in, bounds[0].first, bounds[0].second, cd, err);
+            rc = dev_plan ? issue_plan_dev(in, bounds[0].first, bounds[0].second, cd, bs_stage, err) : plan_range(in, bounds[0].first, bounds[0].second, cd, err);
             if (rc != MGL_SW_OK) { fail(rc, err); break; }
         } else {
             std::unique_lock<std::mutex> lk(mu);
             cv.wait(lk, [&] { return ready[(size_t)c] != 0; });
             if (ready[(size_t)c] == 2) { rc = fail(prc[(size_t)c], perr[(size_t)c]); break; }
         }
+        if (dev_plan && (rc = collect_plan_dev(cd)) != MGL_SW_OK) break;     /* the summary of this chunk's plan */
         const double t_ready = tl_ms();
         if ((rc = finish(si)) != MGL_SW_OK) break;              /* chunk c - MGLSW_SLOTS: already home */
         release_upto(c - MGLSW_SLOTS + 1);
@@ -877,6 +891,7 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         return rc;
     }
     out.ops_total = ops_running;
+    bs.h2d_bytes += bs_stage.h2d_bytes; bs.other_launches += bs_stage.other_launches;
     if (stats) *stats = bs;
     if (tl_on) std::fprintf(stderr, "[mgl_sw] batch done at %.2f ms\n", tl_ms());
     if (overflow) return fail(MGL_SW_E_OPS_CAPACITY, "ops buffer too small: need " + std::to_string(ops_running));

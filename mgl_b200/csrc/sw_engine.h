@@ -95,6 +95,7 @@ struct ChunkDev {
     PinBuf h_table, h_sum;
     PlanDevLayout lay{};
     cudaEvent_t ev_plan = nullptr;
+    cudaEvent_t ev_dbg[3] = {};          /* MGL_SW_TIMELINE: timing events around the planner's upload and kernels */
     void release();
 };
 
@@ -149,7 +150,7 @@ private:
     int plan_next(const BatchIn &in, int64_t first, ChunkDev &cd);
     /* device planner: stage + upload the pair-table slice and queue the planning kernels on plan_stream_;
        then (later) wait for the summary and turn it into cd.plan */
-    int issue_plan_dev(const BatchIn &in, int64_t first, int64_t take, ChunkDev &cd, BatchStats &bs);
+    int issue_plan_dev(const BatchIn &in, int64_t first, int64_t take, ChunkDev &cd, BatchStats &bs, std::string &err) const;
     int collect_plan_dev(ChunkDev &cd);
     int64_t chunk_take(const BatchIn &in, int64_t first, u64 limit, u32 max_pairs, const u32 *est256) const;
     int plan_range(const BatchIn &in, int64_t first, int64_t take, ChunkDev &cd, std::string &err) const;

@@ -4,6 +4,8 @@
  * engine's cudaMemcpyAsync -- the hot kernels are the fill and the traceback).  Everything runs on one stream,
  * ahead of the chunk's fill; the host reads back PlanSummary (a few kilobytes) and never sees a unit descriptor.
  */
+#include <algorithm>
+
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 
@@ -15,25 +17,31 @@ namespace mglsw {
 namespace {
 
 constexpr int PT = 256;       /* threads per block of every planner kernel */
+/*
+ * Small grids, grid-stride loops.  The planner runs while the fill kernels of earlier chunks own every SM (their
+ * three blocks per SM take the whole register file), so a planner block starts only when a fill block retires;
+ * measured with one thread per item (256 blocks per kernel): 2.6 ms for the ~30 dependent kernels of one plan,
+ * each waiting for ~128 fill blocks to leave.  A few dozen blocks per kernel need a few dozen retirements.
+ */
+constexpr unsigned MAX_BLOCKS = 32;
+#define PD_FOR(i, n) for (u32 i = blockIdx.x * PT + threadIdx.x; i < (n); i += gridDim.x * PT)
 
 struct MaxU32 { __host__ __device__ __forceinline__ u32 operator()(u32 a, u32 b) const { return a > b ? a : b; } };
 struct AddU3 { __host__ __device__ __forceinline__ U3 operator()(const U3 &a, const U3 &b) const { return a + b; } };
 
 __global__ void __launch_bounds__(PT) pd_a_kernel(const PlanDevIn in, PlanState *st, u64 *oplen)
 {
-    const u32 p = blockIdx.x * PT + threadIdx.x;
-    if (p < in.n) pd_stage_a(in, p, st, oplen);
+    PD_FOR(p, in.n) pd_stage_a(in, p, st, oplen);
 }
 
 __global__ void __launch_bounds__(PT) pd_b_kernel(const PlanDevIn in, PlanState *st, u64 *key, u32 *idx)
 {
-    const u32 p = blockIdx.x * PT + threadIdx.x;
     u32 n16 = 0, n32 = 0;
     unsigned long long cells = 0;
-    if (p < in.n) {
+    PD_FOR(p, in.n) {
         const int kind = pd_stage_b(in, p, st, key, idx);
-        n16 = kind == KIND_S16X2; n32 = kind != KIND_S16X2;
-        cells = (unsigned long long)in.tl[p] * in.ql[p];
+        n16 += kind == KIND_S16X2; n32 += kind != KIND_S16X2;
+        cells += (unsigned long long)in.tl[p] * in.ql[p];
     }
     /* counts and cells: one atomic per warp */
 #pragma unroll
@@ -51,14 +59,12 @@ __global__ void __launch_bounds__(PT) pd_b_kernel(const PlanDevIn in, PlanState 
 
 __global__ void __launch_bounds__(PT) pd_c_kernel(u32 n, const u64 *skey, PlanState *st, u32 *runmark)
 {
-    const u32 q = blockIdx.x * PT + threadIdx.x;
-    if (q < n) pd_stage_c(n, q, skey, st, runmark);
+    PD_FOR(q, n) pd_stage_c(n, q, skey, st, runmark);
 }
 
 __global__ void __launch_bounds__(PT) pd_d_kernel(u32 n, const u64 *skey, const u32 *run_start, u32 *uhead)
 {
-    const u32 q = blockIdx.x * PT + threadIdx.x;
-    if (q < n) pd_stage_d(q, skey, run_start, uhead);
+    PD_FOR(q, n) pd_stage_d(q, skey, run_start, uhead);
 }
 
 __global__ void pd_e_kernel(u32 n, const u64 *skey, const u32 *urank, const u32 *uhead, PlanState *st)
@@ -69,23 +75,23 @@ __global__ void pd_e_kernel(u32 n, const u64 *skey, const u32 *urank, const u32 
 __global__ void __launch_bounds__(PT) pd_f_kernel(const PlanDevIn in, const u32 *order, const u32 *run_start, const u32 *uhead,
                                                   const u32 *urank, const PlanState *st, UnitDesc *units)
 {
-    const u32 q = blockIdx.x * PT + threadIdx.x;
-    if (q < in.n) pd_stage_f(in, q, order, run_start, uhead, urank, st, units);
+    PD_FOR(q, in.n) pd_stage_f(in, q, order, run_start, uhead, urank, st, units);
 }
 
 /* launched over the unit capacity (the host does not know the unit count yet): units beyond the plan report zero */
 __global__ void __launch_bounds__(PT) pd_g_kernel(u32 ucap, PlanState *st, UnitDesc *units, U3 *u3)
 {
-    const u32 u = blockIdx.x * PT + threadIdx.x;
-    if (u >= ucap) return;
-    if (u < st->sum.n_units) pd_stage_g(u, st, units, u3);
-    else { U3 z; z.a = z.b = z.c = 0; u3[u] = z; }
+    const u32 nu = st->sum.n_units;
+    PD_FOR(u, ucap) {
+        if (u < nu) pd_stage_g(u, st, units, u3);
+        else { U3 z; z.a = z.b = z.c = 0; u3[u] = z; }
+    }
 }
 
 __global__ void __launch_bounds__(PT) pd_h_kernel(const PlanDevIn in, u32 ucap, PlanState *st, UnitDesc *units, const U3 *u3, const U3 *u3x)
 {
-    const u32 u = blockIdx.x * PT + threadIdx.x;
-    if (u < ucap && u < st->sum.n_units) pd_stage_h(in, u, st, units, u3, u3x);
+    const u32 nu = st->sum.n_units < ucap ? st->sum.n_units : ucap;
+    PD_FOR(u, nu) pd_stage_h(in, u, st, units, u3, u3x);
 }
 
 __global__ void pd_i_kernel(const PlanDevIn in, PlanState *st, const u64 *ops_end)
@@ -147,7 +153,7 @@ cudaError_t plan_dev_run(const PlanDevIn &in, const PlanDevLayout &w, UnitDesc *
     void *tmp = base + w.cub;
     size_t tb = w.cub_bytes;
     const u32 ucap = plan_dev_unit_capacity(n);           /* of THIS chunk (<= the capacity the buffers were sized for) */
-    const unsigned gp = (n + PT - 1) / PT, gu = (ucap + PT - 1) / PT;
+    const unsigned gp = std::min<unsigned>((n + PT - 1) / PT, MAX_BLOCKS), gu = std::min<unsigned>((ucap + PT - 1) / PT, MAX_BLOCKS);
     cudaError_t e;
     if ((e = cudaMemsetAsync(state, 0, sizeof(PlanState), st)) != cudaSuccess) return e;
     pd_a_kernel<<<gp, PT, 0, st>>>(in, state, oplen);

@@ -203,6 +203,7 @@ def test_packed_and_raw_transport_give_the_same_results(sw, oracle):
     d = synth.generate(2, n)
     args = (d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, d["strategies"])
     sw.set_option("chunk_pairs", 4096)                  # several chunks, each with its own byte range
+    sw.set_option("host_plan", 1)                       # the 2-bit transport packs on the host planner's threads: compare like with like
     try:
         sw.set_option("pack_arena", 2)
         packed = sw.align_arrays(d["arena"], *args)
@@ -234,7 +235,8 @@ def test_packed_and_raw_transport_give_the_same_results(sw, oracle):
             r, a = synth.pair_bytes(dm, p)
             assert (mixed.cigar(p), int(mixed.offsets[p])) == oracle.align(r, a, d["params"], int(d["strategies"][p])), p
     finally:
-        sw.set_option("pack_arena", 0)                  # the library default
+        sw.set_option("pack_arena", 0)                  # the library defaults
+        sw.set_option("host_plan", 0)
         sw.set_option("chunk_pairs", 1 << 16)
 
 
