@@ -12,7 +12,7 @@
  * by the traceback, which recomputes the cells along its path from the fill's
  * checkpoints with the reference's comparisons verbatim (sw_trace.h).
  * Base comparison is raw byte equality (:55), so bytes are compared as they
- * come (x = a ^ b; mismatch iff x != 0) -- no 2-bit recoding.
+ * come (mismatch iff a - b != 0) -- no 2-bit recoding.
  *
  * S16x2: two pairs per register, unsigned 16-bit halves holding score + bias.
  *        Plain 32-bit adds/subs/IMADs act on both halves at once; that is
@@ -41,12 +41,16 @@ struct S16x2 {
     SW_HD static u32 rep(int v) { return ((u32)v & 0xffffu) * 0x00010001u; }
     SW_HD static int half(u32 v, int h) { return (int)((v >> (16 * h)) & 0xffffu); }
 
-    SW_HD static u32 min1(u32 x)
+    /* per half: 0 - byte (mod 2^16); a lane's alt bytes are stored this way once per strip */
+    SW_HD static u32 negb(u32 b) { return ((0u - (b & 0xffffu)) & 0xffffu) | ((0u - (b >> 16)) << 16); }
+    /* mismatch indicator, per half: min((a - b) mod 2^16, 1), with nb = negb(b): ONE instruction (VIADDMNMX.U16x2) */
+    SW_HD static u32 ne1(u32 a, u32 nb)
     {
 #if SW_ON_DEVICE
-        return __vminu2(x, 0x00010001u);
+        return __viaddmin_u16x2(a, nb, 0x00010001u);
 #else
-        return ((x & 0xffffu) ? 1u : 0u) | ((x >> 16) ? 0x10000u : 0u);
+        const u32 lo = (a + nb) & 0xffffu, hi = ((a >> 16) + (nb >> 16)) & 0xffffu;
+        return (lo ? 1u : 0u) | (hi ? 0x10000u : 0u);
 #endif
     }
     SW_HD static u32 max3(u32 a, u32 b, u32 c)
@@ -82,7 +86,16 @@ struct S32 {
     SW_HD static u32 rep(int v) { return (u32)v; }
     SW_HD static int half(u32 v, int) { return (int)v; }
 
-    SW_HD static u32 min1(u32 x) { return x < 1u ? x : 1u; }
+    SW_HD static u32 negb(u32 b) { return 0u - b; }
+    /* mismatch indicator: min((a - b) mod 2^32, 1) as unsigned, with nb = negb(b): ONE instruction (VIADDMNMX.U32) */
+    SW_HD static u32 ne1(u32 a, u32 nb)
+    {
+#if SW_ON_DEVICE
+        return __viaddmin_u32(a, nb, 1u);
+#else
+        return (a + nb) ? 1u : 0u;
+#endif
+    }
     SW_HD static u32 max3(u32 a, u32 b, u32 c)
     {
 #if SW_ON_DEVICE
@@ -120,19 +133,22 @@ SW_HD CellConsts make_consts(const Scores &s, int bias)
 }
 
 /*
- * One cell.  In:  ra/bq packed ref/alt bytes, hdm = H[i-1][j-1] + match (+bias),
- * e = E[i][j], f = F[i][j].  Out: e = E[i+1][j], f = F[i][j+1], hm = H[i][j] + match.
+ * One cell.  In:  ra packed ref bytes, nbq the lane's alt bytes NEGATED per half (T::negb, once per
+ * strip), hdm = H[i-1][j-1] + match (+bias), e = E[i][j], f = F[i][j].
+ * Out: e = E[i+1][j], f = F[i][j+1], hm = H[i][j] + match.
  *
- * Eight instructions: xor, min, max3 and the two add-max exist only on the ALU pipe;
- * the three plain adds are written as multiply-adds (by c.neg_delta, and by the runtime 1
- * in c.one) so that they issue to the FMA pipe -- an SM sub-partition owns one 16-lane
- * pipe of each kind and one issue slot per clock (int_peak.cu measures both).
+ * Seven instructions.  The byte comparison (sw.cpp:55) is one add-then-min: (a - b) mod 2^16 is 0
+ * for equal bytes and >= 1 otherwise, so min(a + (-b), 1) is the mismatch indicator (it was xor + min:
+ * one instruction more on the ALU pipe, which is the pipe that binds this kernel).  The add-min, max3
+ * and the two add-max exist only on the ALU pipe; the three plain adds are written as multiply-adds
+ * (by c.neg_delta, and by the runtime 1 in c.one) so that they issue to the FMA pipe -- an SM
+ * sub-partition owns one 16-lane pipe of each kind and one issue slot per clock (int_peak.cu
+ * measures both): 4 ALU + 3 FMA per cell.
  */
 template <class T>
-SW_HD void sw_cell(const CellConsts &c, u32 ra, u32 bq, u32 hdm, u32 &e, u32 &f, u32 &hm)
+SW_HD void sw_cell(const CellConsts &c, u32 ra, u32 nbq, u32 hdm, u32 &e, u32 &f, u32 &hm)
 {
-    const u32 x = ra ^ bq;
-    const u32 m = T::min1(x);                 /* 0 match, 1 mismatch                     */
+    const u32 m = T::ne1(ra, nbq);            /* 0 match, 1 mismatch                     */
     const u32 d = m * c.neg_delta + hdm;      /* H_diag + match - m * (match - mismatch) */
     const u32 h = T::max3(d, e, f);
     const u32 hgo = h * c.one + c.neg_go;

@@ -179,7 +179,7 @@ struct FillLane {
             if (j > ql) j = ql;                       /* virtual register: any byte will do */
             u32 b = SW_LDG(alt0 + (j - 1));
             if (T::PAIRS == 2) b |= (u32)SW_LDG(alt1 + (j - 1)) << 16;
-            bq[k] = b;
+            bq[k] = T::negb(b);                       /* stored negated: the cell's comparison is one add-then-min (sw_cell.h) */
         }
         reset_rows(c);
         h_out = T::rep(c.bias);
