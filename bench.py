@@ -545,7 +545,7 @@ def main():
         barrier(dist, local)
         if rank == 0:
             try:
-                line["multi_handle"] = multi_handle_record(world, n)
+                line["multi_handle"] = multi_handle_record(world, min(n, 500_000))
             except Exception as ex:                      # the headline must not die with the sub-record
                 line["multi_handle"] = {"error": repr(ex)}
         barrier(dist, local)

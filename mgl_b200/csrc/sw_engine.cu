@@ -326,10 +326,11 @@ int Engine::plan_next(const BatchIn &in, int64_t first, ChunkDev &cd)
 }
 
 /*
- * Device planner, host half.  The chunk's slice of the caller's pair table (28 bytes per pair) is staged in pinned
- * memory -- the caller's arrays are ordinary memory, and a copy from them would be staged by the driver, synchronously --
- * and goes up on the planner's stream, followed by the planning kernels and the copy home of the summary.  The host
- * touches each pair twice here (the memcpy and the min / max of its offsets) and never again.
+ * Device planner, host half.  The chunk's slice of the caller's pair table, plus the running end of each pair's CIGAR
+ * scratch (36 bytes per pair), is staged in pinned memory -- the caller's arrays are ordinary memory, and a copy from
+ * them would be staged by the driver, synchronously -- and goes up on the planner's stream, followed by the planning
+ * kernel and the copy home of the summary.  The host touches each pair twice here (the memcpy, and one loop for the
+ * min / max of its offsets and the scratch sum) and never again.
  */
 int Engine::issue_plan_dev(const BatchIn &in, int64_t first, int64_t take, ChunkDev &cd, BatchStats &bs, std::string &err) const
 {
@@ -343,31 +344,34 @@ int Engine::issue_plan_dev(const BatchIn &in, int64_t first, int64_t take, Chunk
         cd.lay = plan_dev_layout(std::max<u32>(n + n / 8, 4096));
         if ((e = cd.work.reserve(cd.lay.total)) != cudaSuccess) return cfail(e, "cudaMalloc planner work buffer");
     }
-    const size_t tbytes = (size_t)n * 28;
+    const size_t tbytes = (size_t)n * 36;
     if ((e = cd.h_table.reserve(tbytes)) != cudaSuccess) return cfail(e, "pinned alloc");
     if ((e = cd.h_sum.reserve(sizeof(PlanSummary))) != cudaSuccess) return cfail(e, "pinned alloc");
     if ((e = cd.table.reserve(tbytes)) != cudaSuccess) return cfail(e, "cudaMalloc pair table");
     if ((e = cd.units.reserve((size_t)plan_dev_unit_capacity(n) * sizeof(UnitDesc))) != cudaSuccess) return cfail(e, "cudaMalloc units");
-    if ((e = cd.ops_end.reserve((size_t)n * sizeof(u64))) != cudaSuccess) return cfail(e, "cudaMalloc");
+    /* table = ref_off | alt_off | ops_end (u64 each) | ref_len | alt_len | strategy (u32 each) */
     char *h = (char *)cd.h_table.p;
-    u64 *h_ro = (u64 *)h, *h_ao = (u64 *)(h + (size_t)n * 8);
-    u32 *h_tl = (u32 *)(h + (size_t)n * 16), *h_ql = (u32 *)(h + (size_t)n * 20);
-    int *h_st = (int *)(h + (size_t)n * 24);
+    u64 *h_ro = (u64 *)h, *h_ao = (u64 *)(h + (size_t)n * 8), *h_oe = (u64 *)(h + (size_t)n * 16);
+    u32 *h_tl = (u32 *)(h + (size_t)n * 24), *h_ql = (u32 *)(h + (size_t)n * 28);
+    int *h_st = (int *)(h + (size_t)n * 32);
     std::memcpy(h_ro, in.ref_off + first, (size_t)n * 8);
     std::memcpy(h_ao, in.alt_off + first, (size_t)n * 8);
     std::memcpy(h_tl, in.ref_len + first, (size_t)n * 4);
     std::memcpy(h_ql, in.alt_len + first, (size_t)n * 4);
     if (in.strategies) std::memcpy(h_st, in.strategies + first, (size_t)n * 4);
     else std::fill(h_st, h_st + n, in.strategy);
-    u64 lo = ~0ull, hi = 0;                    /* the byte range of the arena this chunk touches */
+    u64 lo = ~0ull, hi = 0, acc = 0;           /* the byte range of the arena this chunk touches; CIGAR scratch: tl + ql + 4 elements per pair, in chunk order */
     for (u32 k = 0; k < n; k++) {
         const u64 ro = h_ro[k], ao = h_ao[k];
+        const u32 tl = h_tl[k], ql = h_ql[k];
         lo = std::min(lo, std::min(ro, ao));
-        hi = std::max(hi, std::max(ro + h_tl[k], ao + h_ql[k]));
+        hi = std::max(hi, std::max(ro + tl, ao + ql));
+        acc += (u64)tl + ql + 4;
+        h_oe[k] = acc;
     }
     cd.arena_lo = std::min(lo, in.arena_bytes); cd.arena_hi = std::min(hi, in.arena_bytes);   /* offsets outside the arena are refused by the planner */
     if (cd.arena_lo > cd.arena_hi) cd.arena_lo = cd.arena_hi;
-    static const bool tl_dbg = std::getenv("MGL_SW_TIMELINE") != nullptr;
+    const bool tl_dbg = std::getenv("MGL_SW_TIMELINE") != nullptr;
     if (tl_dbg) {
         if (!cd.ev_dbg[0]) for (auto &x : cd.ev_dbg) cudaEventCreate(&x);
         cudaEventRecord(cd.ev_dbg[0], plan_stream_);
@@ -377,16 +381,16 @@ int Engine::issue_plan_dev(const BatchIn &in, int64_t first, int64_t take, Chunk
     bs.h2d_bytes += tbytes;
     const char *d = (const char *)cd.table.p;
     PlanDevIn pin;
-    pin.ref_off = (const u64 *)d; pin.alt_off = (const u64 *)(d + (size_t)n * 8);
-    pin.tl = (const u32 *)(d + (size_t)n * 16); pin.ql = (const u32 *)(d + (size_t)n * 20);
-    pin.strategy = (const int *)(d + (size_t)n * 24);
+    pin.ref_off = (const u64 *)d; pin.alt_off = (const u64 *)(d + (size_t)n * 8); pin.ops_end = (const u64 *)(d + (size_t)n * 16);
+    pin.tl = (const u32 *)(d + (size_t)n * 24); pin.ql = (const u32 *)(d + (size_t)n * 28);
+    pin.strategy = (const int *)(d + (size_t)n * 32);
     pin.n = n; pin.arena_bytes = in.arena_bytes; pin.s = in.scores; pin.allow_s16 = allow_s16 ? 1 : 0; pin.score_only = in.score_only ? 1 : 0;
-    if ((e = plan_dev_run(pin, cd.lay, (UnitDesc *)cd.units.p, (u64 *)cd.ops_end.p, cd.work.p, (PlanSummary *)cd.h_sum.p, plan_stream_)) != cudaSuccess)
+    if ((e = plan_dev_run(pin, cd.lay, (UnitDesc *)cd.units.p, cd.work.p, (PlanSummary *)cd.h_sum.p, plan_stream_)) != cudaSuccess)
         return cfail(e, "device planner");
     if (tl_dbg) cudaEventRecord(cd.ev_dbg[2], plan_stream_);
     if ((e = cudaEventRecord(cd.ev_plan, plan_stream_)) != cudaSuccess) return cfail(e, "event record");
-    cd.d_units = (const UnitDesc *)cd.units.p; cd.d_ops_end = (const u64 *)cd.ops_end.p; cd.d_strategy = pin.strategy;
-    bs.other_launches += 20;                   /* 10 planner kernels + the sort's and the scans' own */
+    cd.d_units = (const UnitDesc *)cd.units.p; cd.d_ops_end = pin.ops_end; cd.d_strategy = pin.strategy;
+    bs.other_launches += 1;
     return MGL_SW_OK;
 }
 

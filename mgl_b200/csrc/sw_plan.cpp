@@ -125,9 +125,9 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
     for (u32 p = 0; p < n; p++) {
         const PairIn &pr = pairs[p];
         const int kind = (cand[p] && s16_fits(s, pr.tl, pr.ql, bias16)) ? KIND_S16X2 : KIND_S32;
-        const u64 key = pair_key(kind, pr.tl, pr.ql, pr.strategy);      /* sw_plan_rules.h */
-        fkey[p] = ~key;                 /* ascending sort of ~key == descending key */
-        out.sort_key[p] = ~key;
+        const u64 key = pair_sort_key(kind, pr.tl, pr.ql, pr.strategy);      /* sw_plan_rules.h: ascending sort == heavy first */
+        fkey[p] = key;
+        out.sort_key[p] = key;
         out.sort_idx[p] = p;
     }
     const u64 varying = sort_by_key(out, n);
@@ -135,8 +135,9 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
     /* the sorted keys, reduced to their varying bits: two keys agree on a field iff their reduced keys agree on the
        field's reduced mask (read in order: no random access to the full keys) */
     const u64 *const skey = out.sort_key.data();
-    const u64 m_launch = varying == ~0ull ? (0xffull << 56) : gather_bits(0xffull << 56, varying);     /* kind, G, K, pipelined */
-    const u64 m_pair = varying == ~0ull ? (~0ull << 20) : gather_bits(~0ull << 20, varying);           /* ... + strips, indel, ql */
+    const u64 kmask = (1ull << MGLSW_KEY_BITS) - 1;
+    const u64 m_launch = gather_bits(kmask & (~0ull << MGLSW_KEY_LAUNCH_SHIFT), varying);     /* kind, G, K, pipelined */
+    const u64 m_pair = gather_bits(kmask & (~0ull << MGLSW_KEY_PAIR_SHIFT), varying);         /* ... + indel, alt length */
 
     /* pass 3: units, warps, launches */
     u32 pos = 0;
@@ -146,10 +147,10 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
 
         const PairIn &first = pairs[order[pos]];
         Launch L;
-        const u64 nk = ~fkey[order[pos]];
-        L.kind = ((nk >> 63) & 1) ? KIND_S32 : KIND_S16X2;
-        L.G = ((nk >> 62) & 1) ? MGLSW_G_LONG : MGLSW_G_SHORT;
-        L.pipe = (int)((nk >> 56) & 1);
+        const u32 nk = sort_key_to_key((u32)fkey[order[pos]]);
+        L.kind = key_kind(nk);
+        L.G = key_G(nk);
+        L.pipe = key_pipe(nk);
         L.nstrips = L.G == MGLSW_G_SHORT ? 1u : ceil_div_u32(first.ql, (u32)MGLSW_G_LONG * MGLSW_KMAX);   /* of its first unit */
         L.K = (int)regs_per_lane(first.ql, L.nstrips * L.G);
         L.first_unit = (u32)out.units.size();
@@ -171,12 +172,18 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
             L.cells += (u64)a.tl * a.ql;
             (L.kind == KIND_S32 ? out.pairs_s32 : out.pairs_s16)++;
             q++;
-            if (L.kind == KIND_S16X2 && q < end && ((skey[q] ^ skey[q - 1]) & m_pair) == 0) {
-                const u32 p1 = order[q];
+            /* the next position rides along unless it opens a unit of its own (sw_plan_rules.h opens_unit) */
+            if (L.kind == KIND_S16X2 && q < n && !opens_unit(L.kind, q, ((skey[q] ^ skey[q - 1]) & m_pair) != 0)) {
+                u32 p1 = order[q];
+                L.cells += (u64)pairs[p1].tl * pairs[p1].ql;
+                if (pairs[p1].tl > a.tl) {                   /* the longer ref sits in the low half (sw_fill.h); the key orders refs in steps of 8 only */
+                    u.pair[0] = p1; u.ref_off[0] = pairs[p1].ref_off; u.alt_off[0] = pairs[p1].alt_off; u.tl[0] = pairs[p1].tl;
+                    out.pair_unit[p1] = (u32)out.units.size() * 2;
+                    p1 = p0;
+                }
                 const PairIn &b = pairs[p1];
                 u.pair[1] = p1; u.ref_off[1] = b.ref_off; u.alt_off[1] = b.alt_off; u.tl[1] = b.tl;
                 out.pair_unit[p1] = (u32)out.units.size() * 2 + 1;
-                L.cells += (u64)b.tl * b.ql;
                 out.pairs_s16++;
                 q++;
             }
@@ -185,7 +192,7 @@ PlanStatus plan_chunk(const PairIn *pairs, u32 n, const Scores &s, bool allow_s1
             u.col_base = u.ql / slots;
             u.col_rem = u.ql % slots;
             u.carry_rows = std::max(u.tl[0], u.tl[1]) + 1;
-            u.flags = UNIT_ACTIVE | ((a.strategy & (OS_INDEL | OS_LEADING_INDEL)) ? UNIT_INDEL : 0u)
+            u.flags = UNIT_ACTIVE | ((pairs[p0].strategy & (OS_INDEL | OS_LEADING_INDEL)) ? UNIT_INDEL : 0u)
                     | (L.G == MGLSW_G_LONG ? UNIT_G32 : 0u) | (L.kind == KIND_S32 ? UNIT_S32 : 0u);
             u.regs = (u32)L.K;
             out.units.push_back(u);

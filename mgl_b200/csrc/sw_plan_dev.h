@@ -1,23 +1,22 @@
 /*
  * sw_plan_dev.h -- the chunk planner as data-parallel stages: one body per stage, run by one thread per pair /
- * sorted position / unit.  sw_plan_dev.cu wraps each body in a CUDA kernel (with a radix sort and four scans between
- * them); tests/emu runs the same bodies in loops on the CPU, so the planning LOGIC is checked against the oracle in a
- * container without a GPU.  The host planner (sw_plan.cpp) computes the same kind of plan on host threads and stays
- * available ("host_plan" option; the 2-bit transport uses it).
+ * sorted position / unit.  sw_plan_dev.cu runs the bodies inside ONE kernel of one thread block per chunk (with a
+ * block-wide radix sort and two scans between them); tests/emu runs the same bodies in loops on the CPU, so the
+ * planning LOGIC is checked against the oracle in a container without a GPU.  The host planner (sw_plan.cpp) computes
+ * the same plan on host threads and stays available ("host_plan" option; the 2-bit transport uses it).
  *
  * Why on the device: on a box whose host cores are shared by eight GPUs the host planner's ~140 ns of CPU per pair
  * (sort by shape, 112-byte unit descriptors, checkpoint layout) bound the end-to-end step.  Here the
- * host uploads the pair table (28 bytes per pair) and reads back a summary of a few kilobytes per chunk; the unit
+ * host uploads the pair table (36 bytes per pair) and reads back a summary of a few kilobytes per chunk; the unit
  * descriptors are born in HBM.
  *
  * It plays the role of the reference's per-call setup (align_avx, sw_avx.cpp:6-60: widening, padding, band
  * geometry) for a whole chunk; the reference has no batch and nothing to sort.
  *
  * Stages (n pairs, U padded units):
- *   A  per pair      validity, CIGAR scratch length, running maximum of the 16-bit bias the chunk needs
- *   B  per pair      arithmetic (needs the bias), bucket key                      -> radix sort (~key, pair)
- *   C  per position  run heads (pairs that may share a unit), launch heads        -> max-scan: run starts
- *   D  per position  which positions open a unit                                  -> sum-scan: unit ranks
+ *   A  per pair      validity, running maximum of the 16-bit bias the chunk needs
+ *   B  per pair      arithmetic (needs the bias), bucket key                      -> radix sort (key, pair)
+ *   C  per position  which positions open a unit, launch heads                    -> sum-scan: unit ranks
  *   E  one thread    launch table: positions, units (padded to whole warps), warps
  *   F  per position  unit descriptors (and the inactive copies that pad a launch's last warp)
  *   G  per unit      warp geometry: rows the warp iterates, row blocks, checkpoint words   -> sum-scan: placements
@@ -36,6 +35,7 @@ struct PlanDevIn {
     const u64 *ref_off, *alt_off;        /* the chunk's slice of the caller's pair table (device copies) */
     const u32 *tl, *ql;
     const int *strategy;
+    const u64 *ops_end;                  /* per pair: one-past-the-end word of its CIGAR scratch (a running sum the host makes while staging) */
     u32 n;
     u64 arena_bytes;                     /* the caller's arena size: every pair must lie inside it */
     Scores s;
@@ -83,51 +83,46 @@ SW_HD U3 operator+(const U3 &x, const U3 &y) { U3 r; r.a = x.a + y.a; r.b = x.b 
 #define PD_ATOMIC_MAX_U64(p, v) ([](unsigned long long *q_, unsigned long long v_) { const unsigned long long o_ = *q_; if (v_ > o_) *q_ = v_; return o_; }((p), (unsigned long long)(v)))
 #endif
 
-/* A: validity (an offset check that cannot wrap), scratch length, bias */
-SW_HD void pd_stage_a(const PlanDevIn &in, u32 p, PlanState *st, u64 *oplen)
+/* A: validity (an offset check that cannot wrap); returns the 16-bit bias this pair needs (0: not a u16x2 candidate),
+   of which the caller keeps the maximum in st->need_bias.  need16[p] / hi16[p] keep the pair's bounds for stage B. */
+SW_HD u32 pd_stage_a(const PlanDevIn &in, u32 p, PlanState *st, u32 *need16, u32 *hi16)
 {
+    need16[p] = 0u; hi16[p] = 0u;
     const u32 tl = in.tl[p], ql = in.ql[p];
     const u64 ro = in.ref_off[p], ao = in.alt_off[p], ab = in.arena_bytes;
-    oplen[p] = (u64)tl + ql + 4;                                 /* CIGAR scratch: tl + ql + 4 elements per pair, in chunk order */
-    if (ro > ab || tl > ab - ro || ao > ab || ql > ab - ao) { PD_ATOMIC_MAX_U32(&st->sum.err_invalid, 0xffffffffu - p); return; }
-    if (!pair_ok(in.s, tl, ql)) { PD_ATOMIC_MAX_U32(&st->sum.err_pair, 0xffffffffu - p); return; }
-    long long need;
-    if (s16_candidate(in.s, in.allow_s16 != 0, tl, ql, need)) PD_ATOMIC_MAX_U32(&st->need_bias, (u32)need);
+    if (ro > ab || tl > ab - ro || ao > ab || ql > ab - ao) { PD_ATOMIC_MAX_U32(&st->sum.err_invalid, 0xffffffffu - p); return 0u; }
+    if (!pair_ok(in.s, tl, ql)) { PD_ATOMIC_MAX_U32(&st->sum.err_pair, 0xffffffffu - p); return 0u; }
+    long long lo, hi;
+    if (!(in.allow_s16 != 0 && ql <= (u32)MGLSW_G_SHORT * MGLSW_KMAX && s16_bounds_hd(in.s, tl, ql, lo, hi))) return 0u;    /* sw_plan_rules.h s16_candidate */
+    need16[p] = (u32)(-lo); hi16[p] = (u32)(hi < 0 ? 0 : hi);       /* hi - lo < 65000 and lo < 0: both fit easily */
+    return (u32)(-lo);
 }
 
 /* B: arithmetic and bucket key; returns the arithmetic (the wrapper counts pairs and cells) */
-SW_HD int pd_stage_b(const PlanDevIn &in, u32 p, const PlanState *st, u64 *key, u32 *idx)
+SW_HD int pd_stage_b(const PlanDevIn &in, u32 p, const PlanState *st, const u32 *need16, const u32 *hi16, u32 *key, u32 *idx)
 {
     const u32 tl = in.tl[p], ql = in.ql[p];
-    const long long bias16 = s16_bias_of((long long)st->need_bias);
-    long long need;
-    int kind = KIND_S32;
-    if (tl != 0 && ql != 0 && s16_candidate(in.s, in.allow_s16 != 0, tl, ql, need) && s16_fits(in.s, tl, ql, bias16)) kind = KIND_S16X2;
-    key[p] = ~pair_key(kind, tl, ql, in.strategy[p]);            /* ascending sort of ~key == descending key */
+    const u32 bias16 = (u32)s16_bias_of((long long)st->need_bias);
+    /* a candidate stays inside 16 bits under the chunk's bias (sw_plan_rules.h s16_fits, from the bounds stage A kept) */
+    const int kind = (need16[p] != 0u && need16[p] <= bias16 && hi16[p] <= 65535u - bias16) ? KIND_S16X2 : KIND_S32;
+    key[p] = pair_sort_key(kind, tl, ql, in.strategy[p]);        /* ascending sort == heavy work first */
     idx[p] = p;
     return kind;
 }
 
-/* C: heads of runs of pairs that may share a unit, and heads of launches */
-SW_HD void pd_stage_c(u32 n, u32 q, const u64 *skey, PlanState *st, u32 *runmark)
+/* C: which positions open a unit (sw_plan_rules.h opens_unit), and the heads of launches */
+SW_HD void pd_stage_c(u32 q, const u32 *skey, PlanState *st, u32 *uhead)
 {
-    (void)n;
-    const u64 d = q == 0 ? ~0ull : (skey[q] ^ skey[q - 1]);
-    runmark[q] = (d >> MGLSW_KEY_PAIR_SHIFT) != 0 ? q : 0u;      /* q == 0 marks itself with 0 = its own start */
+    const u32 d = q == 0 ? ~0u : (skey[q] ^ skey[q - 1]);
+    uhead[q] = opens_unit(key_kind(sort_key_to_key(skey[q])), q, (d >> MGLSW_KEY_PAIR_SHIFT) != 0) ? 1u : 0u;
     if ((d >> MGLSW_KEY_LAUNCH_SHIFT) != 0) {
         const u32 slot = PD_ATOMIC_ADD_U32(&st->n_heads, 1u);
         if (slot < MGLSW_PLAN_MAX_LAUNCHES) st->head_q[slot] = q;
     }
 }
 
-/* D: a position opens a unit unless it is the second pair of a u16x2 unit (odd position inside its run) */
-SW_HD void pd_stage_d(u32 q, const u64 *skey, const u32 *run_start, u32 *uhead)
-{
-    uhead[q] = key_kind(~skey[q]) == KIND_S32 ? 1u : (((q - run_start[q]) & 1u) == 0u ? 1u : 0u);
-}
-
 /* E: the launch table (one thread; at most MGLSW_PLAN_MAX_LAUNCHES entries) */
-SW_HD void pd_stage_e(u32 n, const u64 *skey, const u32 *urank, const u32 *uhead, PlanState *st)
+SW_HD void pd_stage_e(u32 n, const u32 *skey, const u32 *urank, const u32 *uhead, PlanState *st)
 {
     PlanSummary &S = st->sum;
     u32 nh = st->n_heads;
@@ -146,7 +141,7 @@ SW_HD void pd_stage_e(u32 n, const u64 *skey, const u32 *urank, const u32 *uhead
         L.q1 = l + 1 < nh ? st->head_q[l + 1] : n;
         L.urank0 = urank[L.q0];
         L.units_real = (L.q1 < n ? urank[L.q1] : total) - L.urank0;
-        const u64 key = ~skey[L.q0];
+        const u32 key = sort_key_to_key(skey[L.q0]);
         L.kind = (u32)key_kind(key); L.G = (u32)key_G(key); L.K = (u32)key_K(key); L.pipe = (u32)key_pipe(key);
         const u32 upw = 32u / L.G;
         L.n_units = ceil_div_u32(L.units_real, upw) * upw;
@@ -174,7 +169,7 @@ SW_HD u32 pd_launch_of_unit(const PlanSummary &S, u32 u)
 }
 
 /* F: the unit a position opens; the launch's last unit also writes the inactive copies that pad its last warp */
-SW_HD void pd_stage_f(const PlanDevIn &in, u32 q, const u32 *order, const u32 *run_start, const u32 *uhead, const u32 *urank,
+SW_HD void pd_stage_f(const PlanDevIn &in, u32 q, const u32 *order, const u32 *uhead, const u32 *urank,
                       const PlanState *st, UnitDesc *units)
 {
     if (!uhead[q]) return;
@@ -184,14 +179,18 @@ SW_HD void pd_stage_f(const PlanDevIn &in, u32 q, const u32 *order, const u32 *r
     UnitDesc u;
     u.ckpt_off = 0; u.reserved0 = 0; u.carry_off = 0; u.lastrow_off = 0;
     u.tlmax = 0; u.rb_count = 0; u.group = 0;
-    const u32 p0 = order[q];
+    u32 p0 = order[q];
+    /* the next position rides along when it opens no unit of its own; the longer ref sits in the low half
+       (sw_fill.h) -- the key orders refs in steps of 8 rows only */
+    const bool two = L.kind == (u32)KIND_S16X2 && q + 1 < in.n && !uhead[q + 1];
+    u32 p1 = two ? order[q + 1] : NO_PAIR;
+    if (two && in.tl[p1] > in.tl[p0]) { const u32 t = p0; p0 = p1; p1 = t; }
     u.pair[0] = p0; u.pair[1] = NO_PAIR;
     u.ref_off[0] = u.ref_off[1] = in.ref_off[p0];
     u.alt_off[0] = u.alt_off[1] = in.alt_off[p0];
     u.tl[0] = u.tl[1] = in.tl[p0];
     u.ql = in.ql[p0];
-    if (L.kind == (u32)KIND_S16X2 && q + 1 < in.n && run_start[q + 1] == run_start[q]) {
-        const u32 p1 = order[q + 1];                             /* same alt length, ref no longer than p0's (sort order) */
+    if (two) {
         u.pair[1] = p1; u.ref_off[1] = in.ref_off[p1]; u.alt_off[1] = in.alt_off[p1]; u.tl[1] = in.tl[p1];
     }
     unit_geometry(u, L.G);
@@ -218,7 +217,7 @@ SW_HD void pd_stage_g(u32 u, PlanState *st, UnitDesc *units, U3 *u3)
         const u32 rb = row_blocks(tlmax, L.G);
         for (u32 x = 0; x < upw; x++) { units[u + x].tlmax = tlmax; units[u + x].rb_count = rb; units[u + x].group = x; }
         v.a = warp_ckpt_words(units[u].nstrips, rb, L.K);        /* G = 32: one unit per warp; G = 8: one strip */
-        PD_ATOMIC_MAX_U64(&st->maxw, v.a);
+        if (v.a > st->maxw) PD_ATOMIC_MAX_U64(&st->maxw, v.a);   /* the plain read only spares most of the atomics */
     }
     const UnitDesc &me = units[u];
     if (me.flags & UNIT_ACTIVE) {
@@ -251,8 +250,9 @@ SW_HD void pd_stage_h(const PlanDevIn &in, u32 u, PlanState *st, UnitDesc *units
 }
 
 /* I: the summary */
-SW_HD void pd_stage_i(const PlanDevIn &in, PlanState *st, const u64 *ops_end)
+SW_HD void pd_stage_i(const PlanDevIn &in, PlanState *st)
 {
+    const u64 *ops_end = in.ops_end;
     PlanSummary &S = st->sum;
     S.s16_bias = (u32)s16_bias_of((long long)st->need_bias);
     S.pairs_s16 = st->pairs_s16; S.pairs_s32 = st->pairs_s32;

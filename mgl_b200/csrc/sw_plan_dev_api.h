@@ -11,7 +11,7 @@ namespace mglsw {
 
 /* carve-up of the planner's work buffer for a capacity of n pairs (byte offsets; computed once per capacity) */
 struct PlanDevLayout {
-    size_t key, skey, idx, order, runmark, run_start, uhead, urank, oplen, u3, u3x, state, cub, total, cub_bytes;
+    size_t key0, key1, idx0, idx1, uhead, urank, u3, u3x, state, cnt, btot, wtot, wtot3, bar, total;
     u32 n_cap, ucap;
 };
 
@@ -20,12 +20,11 @@ u32 plan_dev_unit_capacity(u32 n);
 PlanDevLayout plan_dev_layout(u32 n_cap);
 
 /*
- * Plans one chunk on `st`: `in` holds DEVICE pointers to the chunk's pair table; `units` (plan_dev_unit_capacity(n)
- * descriptors) and `ops_end` (n words) receive what the fill and traceback kernels read; `work` is lay.total bytes;
- * h_summary (pinned) is complete when the stream reaches the end of this call's work.
+ * Plans one chunk with ONE kernel launch (16 blocks) on `st`: `in` holds DEVICE pointers to the chunk's pair table; `units`
+ * (plan_dev_unit_capacity(n) descriptors) receives what the fill and traceback kernels read; `work` is lay.total
+ * bytes; h_summary (pinned) is complete when the stream reaches the end of this call's work.
  */
-cudaError_t plan_dev_run(const PlanDevIn &in, const PlanDevLayout &lay, UnitDesc *units, u64 *ops_end, void *work,
-                         PlanSummary *h_summary, cudaStream_t st);
+cudaError_t plan_dev_run(const PlanDevIn &in, const PlanDevLayout &lay, UnitDesc *units, void *work, PlanSummary *h_summary, cudaStream_t st);
 
 }  // namespace mglsw
 #endif

@@ -76,31 +76,48 @@ SW_HD void pair_shape(u32 ql, u32 &G, u32 &nstrips, u32 &K)
 }
 
 /*
- * Bucket key, to be sorted DESCENDING (heavy work launches first): 1 + 1 + 5 + 1 bits of launch key (kind, G, K,
- * strips pipelined over the block's warps), then 11 + 1 + 24 + 20 bits of shape (strips and tl clipped for the key
- * only).  Pairs that agree on the top 44 bits (MGLSW_KEY_PAIR_SHIFT) may share a u16x2 unit.
+ * Bucket key, 30 bits, to be sorted DESCENDING (heavy work launches first):
+ *   [29:22] launch key: arithmetic (1 = 32-bit), lane group (1 = 32 lanes), K (5 bits), strips pipelined over a block
+ *   [21]    INDEL-type boundary
+ *   [20:13] alt length (lane groups of 8: exact, <= 192) or strip count (whole-warp units: clipped, order only)
+ *   [12:0]  ref length / 8, clipped: a warp's units share their row-block count, which moves in steps of 8 rows
+ * Pairs that agree on bits [29:13] (MGLSW_KEY_PAIR_SHIFT) may share a u16x2 unit: same kernel, same boundary kind,
+ * same alt length.  30 bits sort in five 6-bit radix passes (sw_plan_dev.cu).
  */
-#define MGLSW_KEY_LAUNCH_SHIFT 56
-#define MGLSW_KEY_PAIR_SHIFT 20
-SW_HD u64 pair_key(int kind, u32 tl, u32 ql, int strategy)
+#define MGLSW_KEY_BITS 30
+#define MGLSW_KEY_LAUNCH_SHIFT 22
+#define MGLSW_KEY_PAIR_SHIFT 13
+SW_HD u32 pair_key(int kind, u32 tl, u32 ql, int strategy)
 {
     u32 G, nstrips, K;
     pair_shape(ql, G, nstrips, K);
     const u32 indel = (strategy & (OS_INDEL | OS_LEADING_INDEL)) ? 1u : 0u;
-    u64 key = (u64)(kind == KIND_S32 ? 1 : 0);
+    const u32 qlq = G == (u32)MGLSW_G_SHORT ? ql : (nstrips < 255u ? nstrips : 255u);
+    const u32 tlq = (tl >> 3) < 8191u ? (tl >> 3) : 8191u;
+    u32 key = kind == KIND_S32 ? 1u : 0u;
     key = (key << 1) | (G == (u32)MGLSW_G_LONG ? 1u : 0u);
-    key = (key << 5) | K;
+    key = (key << 5) | (K & 31u);
     key = (key << 1) | (nstrips >= (u32)MGLSW_PIPE_MIN_STRIPS ? 1u : 0u);
-    key = (key << 11) | (nstrips < 2047u ? nstrips : 2047u);
     key = (key << 1) | indel;
-    key = (key << 24) | ql;
-    key = (key << 20) | (tl < (1u << 20) - 1 ? tl : (1u << 20) - 1);
+    key = (key << 8) | (qlq & 255u);
+    key = (key << 13) | tlq;
     return key;
 }
-SW_HD int key_kind(u64 key) { return ((key >> 63) & 1) ? KIND_S32 : KIND_S16X2; }
-SW_HD int key_G(u64 key) { return ((key >> 62) & 1) ? MGLSW_G_LONG : MGLSW_G_SHORT; }
-SW_HD int key_K(u64 key) { return (int)((key >> 57) & 31); }
-SW_HD int key_pipe(u64 key) { return (int)((key >> 56) & 1); }
+/* the form that is sorted ASCENDING */
+SW_HD u32 pair_sort_key(int kind, u32 tl, u32 ql, int strategy) { return ((1u << MGLSW_KEY_BITS) - 1u) - pair_key(kind, tl, ql, strategy); }
+SW_HD u32 sort_key_to_key(u32 skey) { return ((1u << MGLSW_KEY_BITS) - 1u) - skey; }
+SW_HD int key_kind(u32 key) { return ((key >> 29) & 1) ? KIND_S32 : KIND_S16X2; }
+SW_HD int key_G(u32 key) { return ((key >> 28) & 1) ? MGLSW_G_LONG : MGLSW_G_SHORT; }
+SW_HD int key_K(u32 key) { return (int)((key >> 23) & 31); }
+SW_HD int key_pipe(u32 key) { return (int)((key >> 22) & 1); }
+
+/*
+ * Which sorted positions open a unit.  32-bit arithmetic: every position.  u16x2: position q opens a unit if it is
+ * the first of its run (pairs equal on the bits above MGLSW_KEY_PAIR_SHIFT) or q is even; an odd position that is not
+ * a run head rides as the second pair of the unit q - 1 opened.  A rule of q and its left neighbour alone -- no scan
+ * over runs -- at the price of at most two single-pair units per run instead of one.
+ */
+SW_HD bool opens_unit(int kind, u32 q, bool run_head) { return kind == KIND_S32 || run_head || (q & 1u) == 0u; }
 
 /* the geometry fields of a unit that follow from its alt length and launch */
 SW_HD void unit_geometry(UnitDesc &u, u32 G)

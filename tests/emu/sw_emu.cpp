@@ -47,31 +47,31 @@ PlanStatus plan_chunk_dev_emu(const PairIn *pairs, u32 n, u64 arena_bytes, const
     in.n = n; in.arena_bytes = arena_bytes; in.s = s; in.allow_s16 = allow_s16 ? 1 : 0; in.score_only = score_only ? 1 : 0;
     PlanState st;
     std::memset(&st, 0, sizeof st);
-    std::vector<u64> oplen(n), key(n), skey(n), ops_end(n);
-    std::vector<u32> idx(n), order(n), runmark(n), run_start(n), uhead(n), urank(n);
-    for (u32 p = 0; p < n; p++) pd_stage_a(in, p, &st, oplen.data());
+    std::vector<u64> ops_end(n);
+    { u64 run = 0; for (u32 p = 0; p < n; p++) { run += (u64)tl[p] + ql[p] + 4; ops_end[p] = run; } }     /* the host makes this while staging */
+    in.ops_end = ops_end.data();
+    std::vector<u32> key(n), skey(n), idx(n), order(n), uhead(n), urank(n);
+    std::vector<u32> need16(n), hi16(n);
+    for (u32 p = 0; p < n; p++) { const u32 need = pd_stage_a(in, p, &st, need16.data(), hi16.data()); st.need_bias = std::max(st.need_bias, need); }
     for (u32 p = 0; p < n; p++) {
-        const int kind = pd_stage_b(in, p, &st, key.data(), idx.data());
+        const int kind = pd_stage_b(in, p, &st, need16.data(), hi16.data(), key.data(), idx.data());
         (kind == KIND_S16X2 ? st.pairs_s16 : st.pairs_s32)++;
         st.cells += (u64)tl[p] * ql[p];
     }
     std::stable_sort(idx.begin(), idx.end(), [&](u32 a, u32 b) { return key[a] < key[b]; });
     for (u32 q = 0; q < n; q++) { order[q] = idx[q]; skey[q] = key[idx[q]]; }
-    for (u32 q = n; q-- > 0;) pd_stage_c(n, q, skey.data(), &st, runmark.data());        /* any thread order: heads arrive unsorted */
-    { u32 m = 0; for (u32 q = 0; q < n; q++) { m = std::max(m, runmark[q]); run_start[q] = m; } }
-    for (u32 q = 0; q < n; q++) pd_stage_d(q, skey.data(), run_start.data(), uhead.data());
+    for (u32 q = n; q-- > 0;) pd_stage_c(q, skey.data(), &st, uhead.data());              /* any thread order: heads arrive unsorted */
     { u32 run = 0; for (u32 q = 0; q < n; q++) { urank[q] = run; run += uhead[q]; } }
     pd_stage_e(n, skey.data(), urank.data(), uhead.data(), &st);
     const u32 U = st.sum.n_units;
     std::vector<UnitDesc> units(U);
     std::memset(units.data(), 0xee, U * sizeof(UnitDesc));                                /* device memory is not zeroed either */
-    for (u32 q = 0; q < n; q++) pd_stage_f(in, q, order.data(), run_start.data(), uhead.data(), urank.data(), &st, units.data());
+    for (u32 q = 0; q < n; q++) pd_stage_f(in, q, order.data(), uhead.data(), urank.data(), &st, units.data());
     std::vector<U3> u3(U), u3x(U);
     for (u32 u = 0; u < U; u++) pd_stage_g(u, &st, units.data(), u3.data());
     { U3 run; run.a = run.b = run.c = 0; for (u32 u = 0; u < U; u++) { u3x[u] = run; run = run + u3[u]; } }
     for (u32 u = 0; u < U; u++) pd_stage_h(in, u, &st, units.data(), u3.data(), u3x.data());
-    { u64 run = 0; for (u32 p = 0; p < n; p++) { run += oplen[p]; ops_end[p] = run; } }
-    pd_stage_i(in, &st, ops_end.data());
+    pd_stage_i(in, &st);
 
     const PlanSummary &S = st.sum;
     if (S.err_invalid) return PLAN_BAD_PAIR;
