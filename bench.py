@@ -374,7 +374,7 @@ def rooflines(r, d, K, p_int32, hbm_peak, measured):
 def sub_config(sw, config, n, rank, dist, local, p_int32, hbm_peak, measured, want_e2e=True):
     """One BASELINE.json config as a sub-record: value, fill ms, roofline fraction, checkpoint B/cell, e2e."""
     from mgl_b200 import synth
-    d = synth.generate(config, n, first=rank * n, pinned=True)
+    d = synth.generate(config, n, first=rank * n, pinned=True, threads=4)
     r = measure_device(sw, d, SUB_STEPS, SUB_WARMUP, dist, local)
     e2e_ms = measure_e2e(sw, d, SUB_STEPS, 1, dist, local)[0] if want_e2e else 0.0
     (dev_ms, fill_ms, e2e_ms), (cells_all, pairs_all) = reduce_max_sum(
@@ -402,7 +402,7 @@ def multi_handle_record(world, n_per_gpu, config=2):
     import mgl_b200
     from mgl_b200 import native, synth
     n = world * n_per_gpu
-    d = synth.generate(config, n, pinned=True)
+    d = synth.generate(config, n, pinned=True, threads=16)
     out = (native.pinned_array(n, np.int32), native.pinned_array(n + 1, np.uint64), native.pinned_array(ops_capacity(d), np.uint32))
     m = mgl_b200.MicrosoftSmithWaterman(list(range(world)))
     m._ensure()
@@ -438,7 +438,7 @@ def main():
 
     numa = bind_to_gpu_cpus(local) if (world > 1 and not args.no_numa_bind) else None
     n = args.pairs or DEFAULT_PAIRS[args.config]
-    d = synth.generate(args.config, n, first=rank * n, pinned=True)       # this rank's shard of the stream
+    d = synth.generate(args.config, n, first=rank * n, pinned=True, threads=4)       # this rank's shard of the stream
     sw = mgl_b200.MicrosoftSmithWaterman(local)
     sw._ensure()                                                          # no GPU / no extension -> raises
     for name, v in (("chunk_pairs", args.chunk_pairs), ("plan_threads", args.plan_threads)):
@@ -545,7 +545,7 @@ def main():
         barrier(dist, local)
         if rank == 0:
             try:
-                line["multi_handle"] = multi_handle_record(world, min(n, 500_000))
+                line["multi_handle"] = multi_handle_record(world, n)
             except Exception as ex:                      # the headline must not die with the sub-record
                 line["multi_handle"] = {"error": repr(ex)}
         barrier(dist, local)

@@ -81,6 +81,8 @@ void ChunkDev::release()
     table.release(); work.release(); h_table.release(); h_sum.release();
     if (ev_plan) { cudaEventDestroy(ev_plan); ev_plan = nullptr; }
     for (auto &x : ev_dbg) if (x) { cudaEventDestroy(x); x = nullptr; }
+    if (ev_arena) { cudaEventDestroy(ev_arena); ev_arena = nullptr; }
+    if (ev_table) { cudaEventDestroy(ev_table); ev_table = nullptr; }
 }
 
 void WorkSlot::release()
@@ -127,6 +129,7 @@ Engine::Engine(int device) : device_(device)
     const unsigned wait_flags = cudaEventDisableTiming | (blocking ? cudaEventBlockingSync : 0u);
     wait_flags_ = wait_flags;
     cudaStreamCreateWithPriority(&plan_stream_, cudaStreamNonBlocking, prio_hi);
+    cudaStreamCreateWithPriority(&upload_stream_, cudaStreamNonBlocking, prio_lo);
     for (auto &s : slots_) {
         cudaStreamCreateWithPriority(&s.stream, cudaStreamNonBlocking, prio_lo);
         cudaStreamCreateWithPriority(&s.post, cudaStreamNonBlocking, prio_hi);
@@ -151,6 +154,7 @@ Engine::~Engine()
     for (ChunkDev *cd : ring_) { cd->release(); delete cd; }
     for (auto &s : slots_) s.release();
     if (plan_stream_) cudaStreamDestroy(plan_stream_);
+    if (upload_stream_) cudaStreamDestroy(upload_stream_);
     for (auto &e : tev_) if (e) cudaEventDestroy(e);
     arena_.release();
 }
@@ -332,7 +336,7 @@ int Engine::plan_next(const BatchIn &in, int64_t first, ChunkDev &cd)
  * kernel and the copy home of the summary.  The host touches each pair twice here (the memcpy, and one loop for the
  * min / max of its offsets and the scratch sum) and never again.
  */
-int Engine::issue_plan_dev(const BatchIn &in, int64_t first, int64_t take, ChunkDev &cd, BatchStats &bs, std::string &err) const
+int Engine::issue_plan_dev(const BatchIn &in, int64_t first, int64_t take, ChunkDev &cd, BatchStats &bs, std::string &err, bool upload_arena) const
 {
     auto cfail = [&](cudaError_t ce, const char *what) { err = std::string(what) + ": " + cudaGetErrorString(ce); cudaGetLastError(); return (int)MGL_SW_E_CUDA; };
     cudaError_t e;
@@ -372,11 +376,19 @@ int Engine::issue_plan_dev(const BatchIn &in, int64_t first, int64_t take, Chunk
     cd.arena_lo = std::min(lo, in.arena_bytes); cd.arena_hi = std::min(hi, in.arena_bytes);   /* offsets outside the arena are refused by the planner */
     if (cd.arena_lo > cd.arena_hi) cd.arena_lo = cd.arena_hi;
     const bool tl_dbg = std::getenv("MGL_SW_TIMELINE") != nullptr;
+    /*
+     * The table rides the SAME stream as the arena bytes (table 0, arena 0, table 1, arena 1, ...): the copy engine
+     * then serves them in exactly that order.  On the planner's own stream a table waited behind every arena copy this
+     * thread had queued ahead -- 5 ms for the second chunk of a batch, with the GPU idle (profiles/r06c).
+     */
+    if (!cd.ev_table && (e = cudaEventCreateWithFlags(&cd.ev_table, cudaEventDisableTiming)) != cudaSuccess) return cfail(e, "event create");
     if (tl_dbg) {
         if (!cd.ev_dbg[0]) for (auto &x : cd.ev_dbg) cudaEventCreate(&x);
-        cudaEventRecord(cd.ev_dbg[0], plan_stream_);
+        cudaEventRecord(cd.ev_dbg[0], upload_stream_);
     }
-    if ((e = cudaMemcpyAsync(cd.table.p, cd.h_table.p, tbytes, cudaMemcpyHostToDevice, plan_stream_)) != cudaSuccess) return cfail(e, "H2D pair table");
+    if ((e = cudaMemcpyAsync(cd.table.p, cd.h_table.p, tbytes, cudaMemcpyHostToDevice, upload_stream_)) != cudaSuccess) return cfail(e, "H2D pair table");
+    if ((e = cudaEventRecord(cd.ev_table, upload_stream_)) != cudaSuccess) return cfail(e, "event record");
+    if ((e = cudaStreamWaitEvent(plan_stream_, cd.ev_table, 0)) != cudaSuccess) return cfail(e, "stream wait");
     if (tl_dbg) cudaEventRecord(cd.ev_dbg[1], plan_stream_);
     bs.h2d_bytes += tbytes;
     const char *d = (const char *)cd.table.p;
@@ -389,6 +401,23 @@ int Engine::issue_plan_dev(const BatchIn &in, int64_t first, int64_t take, Chunk
         return cfail(e, "device planner");
     if (tl_dbg) cudaEventRecord(cd.ev_dbg[2], plan_stream_);
     if ((e = cudaEventRecord(cd.ev_plan, plan_stream_)) != cudaSuccess) return cfail(e, "event record");
+    /*
+     * The chunk's bytes of the arena go up NOW, on their own stream, as far ahead of the chunk's kernels as the ring
+     * lets this thread run: the upload depends on nothing the planner computes, and on a box whose GPUs share the
+     * host's memory path (eight GPUs: 23 GB/s each, tools/h2d_ceiling.py) the link is what a step waits for -- it
+     * must never idle behind a plan or a slot.  The chunk's fill waits for ev_arena.
+     */
+    cd.arena_ahead = false;
+    if (upload_arena) {
+        if (!cd.ev_arena && (e = cudaEventCreateWithFlags(&cd.ev_arena, cudaEventDisableTiming)) != cudaSuccess) return cfail(e, "event create");
+        if (cd.arena_hi > cd.arena_lo) {
+            if ((e = cudaMemcpyAsync((uint8_t *)arena_dev() + cd.arena_lo, in.arena + cd.arena_lo, cd.arena_hi - cd.arena_lo, cudaMemcpyHostToDevice, upload_stream_)) != cudaSuccess)
+                return cfail(e, "H2D arena");
+            bs.h2d_bytes += cd.arena_hi - cd.arena_lo;
+        }
+        if ((e = cudaEventRecord(cd.ev_arena, upload_stream_)) != cudaSuccess) return cfail(e, "event record");
+        cd.arena_ahead = true;
+    }
     cd.d_units = (const UnitDesc *)cd.units.p; cd.d_ops_end = pin.ops_end; cd.d_strategy = pin.strategy;
     bs.other_launches += 1;
     return MGL_SW_OK;
@@ -812,7 +841,7 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
                 cv.wait(lk, [&] { return stop || k - collected < R; });
                 if (stop) return;
             }
-            int prc_k = dev_plan ? issue_plan_dev(in, bounds[(size_t)k].first, bounds[(size_t)k].second, *ring_[(size_t)(k % R)], bs_stage, perr[(size_t)k])
+            int prc_k = dev_plan ? issue_plan_dev(in, bounds[(size_t)k].first, bounds[(size_t)k].second, *ring_[(size_t)(k % R)], bs_stage, perr[(size_t)k], !whole)
                                  : plan_range(in, bounds[(size_t)k].first, bounds[(size_t)k].second, *ring_[(size_t)(k % R)], perr[(size_t)k]);
             if (prc_k == MGL_SW_OK && pack_batch && (pack_arena == 2 || k - upload_cursor.load(std::memory_order_relaxed) >= pack_lead))
                 prc_k = pack_chunk(in, *ring_[(size_t)(k % R)], perr[(size_t)k]);
@@ -844,7 +873,7 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         upload_cursor.store(c, std::memory_order_relaxed);
         if (nchunks == 1) {
             std::string err;
-            rc = dev_plan ? issue_plan_dev(in, bounds[0].first, bounds[0].second, cd, bs_stage, err) : plan_range(in, bounds[0].first, bounds[0].second, cd, err);
+            rc = dev_plan ? issue_plan_dev(in, bounds[0].first, bounds[0].second, cd, bs_stage, err, !whole) : plan_range(in, bounds[0].first, bounds[0].second, cd, err);
             if (rc != MGL_SW_OK) { fail(rc, err); break; }
         } else {
             std::unique_lock<std::mutex> lk(mu);
@@ -858,7 +887,10 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         const double t_slot = tl_ms();
         const int64_t first = cd.first;
         if ((rc = ensure_slot(ws, cd.plan, cd.n, so, tx)) != MGL_SW_OK) break;
-        if ((rc = dev_plan ? upload_arena_range(in, cd, ws.stream, !whole, bs) : upload_chunk(in, cd, ws.stream, !whole, bs)) != MGL_SW_OK) break;
+        if (dev_plan) {
+            /* the staging thread sent the chunk's arena bytes ahead; its fill launches wait for them */
+            if (cd.arena_ahead && (e = cudaStreamWaitEvent(ws.stream, cd.ev_arena, 0)) != cudaSuccess) { rc = cuda_fail(e, "stream wait"); break; }
+        } else if ((rc = upload_chunk(in, cd, ws.stream, !whole, bs)) != MGL_SW_OK) break;
         if ((rc = run_chunk(cd, ws, bs, false, so, tx)) != MGL_SW_OK) break;
         const u32 n = cd.n;
         if (so) {

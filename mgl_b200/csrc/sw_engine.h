@@ -95,6 +95,9 @@ struct ChunkDev {
     PinBuf h_table, h_sum;
     PlanDevLayout lay{};
     cudaEvent_t ev_plan = nullptr;
+    cudaEvent_t ev_table = nullptr;      /* the chunk's pair table is on the device */
+    cudaEvent_t ev_arena = nullptr;      /* the chunk's arena bytes are on the device (sent ahead by the staging thread) */
+    bool arena_ahead = false;
     cudaEvent_t ev_dbg[3] = {};          /* MGL_SW_TIMELINE: timing events around the planner's upload and kernels */
     void release();
 };
@@ -150,7 +153,7 @@ private:
     int plan_next(const BatchIn &in, int64_t first, ChunkDev &cd);
     /* device planner: stage + upload the pair-table slice and queue the planning kernels on plan_stream_;
        then (later) wait for the summary and turn it into cd.plan */
-    int issue_plan_dev(const BatchIn &in, int64_t first, int64_t take, ChunkDev &cd, BatchStats &bs, std::string &err) const;
+    int issue_plan_dev(const BatchIn &in, int64_t first, int64_t take, ChunkDev &cd, BatchStats &bs, std::string &err, bool upload_arena) const;
     int collect_plan_dev(ChunkDev &cd);
     int64_t chunk_take(const BatchIn &in, int64_t first, u64 limit, u32 max_pairs, const u32 *est256) const;
     int plan_range(const BatchIn &in, int64_t first, int64_t take, ChunkDev &cd, std::string &err) const;
@@ -175,6 +178,7 @@ private:
     std::vector<u64> estpre_;    /* align_batch: prefix sums of the per-pair checkpoint estimate */
     WorkSlot slots_[MGLSW_SLOTS];
     cudaStream_t plan_stream_ = nullptr;     /* device planner: high priority, runs ahead of the fills */
+    cudaStream_t upload_stream_ = nullptr;   /* device planner mode: arena bytes of the chunks ahead */
     unsigned wait_flags_ = 0;                /* flags of the events the host waits on (spinning or sleeping) */
     std::vector<ChunkDev *> ring_;           /* align_batch: staging entries the planner threads fill */
     std::vector<ChunkDev *> resident_;

@@ -20,6 +20,9 @@
 #ifndef MGL_B200_SW_FILL_PIPE_CUH
 #define MGL_B200_SW_FILL_PIPE_CUH
 #include <cuda_runtime.h>
+
+#include <atomic>
+
 #include "sw_config.h"
 #include "sw_fill.h"
 
@@ -123,12 +126,16 @@ cudaError_t launch_fill_pipe(const FillArgs &a, u32 first_unit, bool wide, cudaS
     if (a.n_warps == 0) return cudaSuccess;
     constexpr size_t per_warp = (size_t)FillLane<T, 32, K>::LS16 * 512u;
     const size_t smem = 128u + per_warp * (wide ? MGLSW_PIPE_WIDE_WARPS : 4);
-    static cudaError_t attr = [] {
-        cudaError_t e = cudaFuncSetAttribute(sw_fill_pipe_wide_kernel<T, K>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)(128u + per_warp * MGLSW_PIPE_WIDE_WARPS));
-        return e;
-    }();
-    if (attr != cudaSuccess) return attr;
+    /* function attributes are per device: a handle over several GPUs launches this from one process on each of them */
+    static std::atomic<unsigned long long> done{0};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (wide && !(done.load(std::memory_order_relaxed) >> (dev & 63) & 1ull)) {
+        const cudaError_t e = cudaFuncSetAttribute(sw_fill_pipe_wide_kernel<T, K>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                   (int)(128u + per_warp * MGLSW_PIPE_WIDE_WARPS));
+        if (e != cudaSuccess) return e;
+        done.fetch_or(1ull << (dev & 63), std::memory_order_relaxed);
+    }
     if (wide) sw_fill_pipe_wide_kernel<T, K><<<a.n_warps, 32 * MGLSW_PIPE_WIDE_WARPS, smem, stream>>>(a, first_unit);
     else      sw_fill_pipe_kernel<T, K><<<a.n_warps, 128, smem, stream>>>(a, first_unit);
     return cudaGetLastError();

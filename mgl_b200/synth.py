@@ -35,13 +35,30 @@ SEEDS = {2: 0xC2, 3: 0xC3, 4: 0xC4, 5: 0xC5}
 SCORES = {2: (10, -15, -30, -5), 3: (200, -150, -260, -11), 4: (200, -150, -260, -11), 5: (10, -15, -30, -5)}
 
 
-def generate(config: int, n: int, first: int = 0, seed: int | None = None, pinned: bool = False):
+def generate(config: int, n: int, first: int = 0, seed: int | None = None, pinned: bool = False, threads: int = 1):
     """-> dict(arena, ref_off, ref_len, alt_off, alt_len, strategies, params, cells)"""
     L = lib()
     seed = SEEDS[config] if seed is None else seed
     ref_len = np.zeros(n, dtype=np.uint32)
     alt_len = np.zeros(n, dtype=np.uint32)
-    rc = L.mgl_sw_synth_sizes(config, seed, first, n, ref_len.ctypes.data, alt_len.ctypes.data)
+    # a pair is a pure function of its index, so ranges of the batch are generated side by side (ctypes drops the GIL)
+    T = max(1, min(int(threads), n // 65536 + 1))
+    cuts = [n * k // T for k in range(T + 1)]
+
+    def in_ranges(fn):
+        import threading
+        rcs = [0] * T
+        def work(k):
+            rcs[k] = fn(cuts[k], cuts[k + 1] - cuts[k])
+        th = [threading.Thread(target=work, args=(k,)) for k in range(1, T)]
+        for t in th:
+            t.start()
+        work(0)
+        for t in th:
+            t.join()
+        return max(abs(r) for r in rcs)
+
+    rc = in_ranges(lambda lo, cnt: L.mgl_sw_synth_sizes(config, seed, first + lo, cnt, ref_len.ctypes.data + 4 * lo, alt_len.ctypes.data + 4 * lo))
     if rc:
         raise ValueError(f"mgl_sw_synth_sizes({config}, n={n}) failed")
     sizes = np.empty(2 * n, dtype=np.uint64)
@@ -55,7 +72,7 @@ def generate(config: int, n: int, first: int = 0, seed: int | None = None, pinne
     else:
         arena = np.zeros(total, dtype=np.uint8)
     ref_off, alt_off = offs[0::2].copy(), offs[1::2].copy()
-    rc = L.mgl_sw_synth_fill(config, seed, first, n, ref_off.ctypes.data, alt_off.ctypes.data, arena.ctypes.data)
+    rc = in_ranges(lambda lo, cnt: L.mgl_sw_synth_fill(config, seed, first + lo, cnt, ref_off.ctypes.data + 8 * lo, alt_off.ctypes.data + 8 * lo, arena.ctypes.data))
     if rc:
         raise ValueError(f"mgl_sw_synth_fill({config}, n={n}) failed")
     idx = np.arange(first, first + n)
