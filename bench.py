@@ -127,8 +127,19 @@ def dist_setup(n_gpus):
         import torch.distributed as dist
         torch.cuda.set_device(local)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        global _CPU_GROUP
+        _CPU_GROUP = dist.new_group(backend="gloo")      # a barrier that keeps the waiting ranks off the GPUs (multi_handle)
         return rank, world, local, dist
     return rank, world, local, None
+
+
+_CPU_GROUP = None
+
+
+def cpu_barrier(dist):
+    """ranks wait in a socket, not in an NCCL kernel: nothing of theirs runs on any GPU meanwhile"""
+    if dist is not None:
+        dist.barrier(group=_CPU_GROUP)
 
 
 def reduce_max_sum(dist, local, tmax, tsum):
@@ -543,12 +554,13 @@ def main():
     if world > 1 and not args.no_sub and args.config == 2 and not args.pairs:
         sw.close()                                       # every rank gives its GPU back before one process drives them all
         barrier(dist, local)
+        cpu_barrier(dist)
         if rank == 0:
             try:
                 line["multi_handle"] = multi_handle_record(world, n)
             except Exception as ex:                      # the headline must not die with the sub-record
                 line["multi_handle"] = {"error": repr(ex)}
-        barrier(dist, local)
+        cpu_barrier(dist)
     if line is not None and world == 1 and not args.no_cpu_baseline:
         cb = cpu_baseline(d)
         if cb:
