@@ -144,6 +144,12 @@ SW_HD CellConsts make_consts(const Scores &s, int bias)
  * (by c.neg_delta, and by the runtime 1 in c.one) so that they issue to the FMA pipe -- an SM
  * sub-partition owns one 16-lane pipe of each kind and one issue slot per clock (int_peak.cu
  * measures both): 4 ALU + 3 FMA per cell.
+ *
+ * Measured and dropped on this form [B200, profiles/r08a, r08b]: (1) taking F off the max3 -> add -> add-max chain
+ * (F' = max(F - min(ge, go), max(d, E) - go): one add-max links a row's cells instead of three instructions) costs
+ * one instruction more per pipe and was 4 % SLOWER (fill 15.0 against 14.4 ms): the step is not bound by that
+ * chain; (2) the two plain adds as three-input IADD3 instead of IMAD: 12 % slower (15.8 against 14.1 ms), IADD3
+ * shares the ALU pipe's dispatch.
  */
 template <class T>
 SW_HD void sw_cell(const CellConsts &c, u32 ra, u32 nbq, u32 hdm, u32 &e, u32 &f, u32 &hm)
