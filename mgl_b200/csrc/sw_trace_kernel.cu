@@ -13,7 +13,10 @@ namespace mglsw {
  * Thread 2 v + h handles half h of unit v: the threads of a warp walk pairs of one shape bucket
  * whose checkpoints sit next to each other, instead of 32 unrelated pairs in input order.
  */
-__global__ void __launch_bounds__(128, 4) sw_traceback_kernel(const __grid_constant__ TraceArgs a)
+#ifndef MGLSW_TRACE_MINB
+#define MGLSW_TRACE_MINB 4
+#endif
+__global__ void __launch_bounds__(128, MGLSW_TRACE_MINB) sw_traceback_kernel(const __grid_constant__ TraceArgs a)
 {
     __shared__ u64 s_nib[MGLSW_TRACE_BUF * 128];   /* the replayed block: records and boundary H values, one column per thread */
     const u32 tid = blockIdx.x * blockDim.x + threadIdx.x;
