@@ -57,6 +57,7 @@ def parse():
     ap.add_argument("--pack", type=int, default=-1, help="2-bit transport of all-ACGT arena ranges: 0 never, 1 when the planner is ahead, 2 always (-1: library default)")
     ap.add_argument("--pack-lead", type=int, default=-1, help="chunks a planner must be ahead of the upload to pack (-1: library default)")
     ap.add_argument("--plan-threads", type=int, default=0, help="host planner threads (0: library default)")
+    ap.add_argument("--slots", type=int, default=-1, help="work slots (chunks in flight): 0 auto, 2..4 (-1: library default)")
     ap.add_argument("--host-plan", type=int, default=-1, help="1: plan chunks on the host (the round-1 path) instead of on the device (-1: library default)")
     return ap.parse_args()
 
@@ -405,6 +406,47 @@ def sub_config(sw, config, n, rank, dist, local, p_int32, hbm_peak, measured, wa
     return rec
 
 
+def pairhmm_record(local, ffma_gops, steps=5, warmup=3):
+    """The library's second kernel on one synthetic region: 4 096 reads x 150 b against 32
+    haplotypes x 400 b, every (read, haplotype) pair.  Device-resident value, e2e through mgl_pairhmm_compute, FP32
+    roofline against the FMA rate measured on this box (int_peak.cu ffma_f32 x 2 flops)."""
+    import importlib.util
+    import numpy as np
+    spec = importlib.util.spec_from_file_location("bench_pairhmm", os.path.join(ROOT, "tools", "bench_pairhmm.py"))
+    bp = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bp)
+    from mgl_b200 import pairhmm
+    reads, haps, read_len, hap_len = 4096, 32, 150, 400
+    lengths, rb, hb, cells = bp.synth(reads, haps, read_len, hap_len)
+    hmm = pairhmm.MicrosoftPairHmm(local)
+    hmm._ensure()
+    hmm.resident_prepare(lengths, rb, hb)
+    for _ in range(warmup):
+        hmm.resident_run(False)
+    dev_ms = 0.0
+    for _ in range(steps):
+        st = hmm.resident_run(False)
+        dev_ms += st["device_ms"]
+    redone = st["pairs_double"]
+    out = np.zeros(reads * haps, dtype=np.float64)
+    hmm.compute_buffers(lengths, rb, hb, out, False)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        hmm.compute_buffers(lengths, rb, hb, out, False)
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+    hmm.done()
+    value = cells * steps / (dev_ms * 1e-3) / 1e9
+    peak = 2.0 * ffma_gops / 1e3 if ffma_gops else None                  # TFLOP/s
+    ach = value * bp.FLOPS_PER_CELL / 1e3
+    return {"workload": f"{reads} reads x {read_len} b against {haps} haplotypes x {hap_len} b (one region, every pair)",
+            "pairs": reads * haps, "cells": cells, "steps": steps, "value": value, "unit": UNIT, "ms_per_step": dev_ms / steps,
+            "pairs_recomputed_in_double": int(redone),
+            "roofline": {"bound": "fp32", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": (ach / peak) if peak else None,
+                         "note": "ph_forward_kernel<float>; algorithmic 11 flops per cell (8 FP32 instructions, compute_prob_scalar.cc:39-43) "
+                                 "x cells / device time; peak = 2 flops x the FP32 FMA issue rate measured on this box by int_peak.cu (ffma_f32)"},
+            "e2e": {"value": cells * steps / (e2e_ms * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": e2e_ms / steps}}
+
+
 def multi_handle_record(world, n_per_gpu, config=2):
     """ONE process, one handle over all `world` GPUs (mgl_sw_create_multi): the JVM's situation -- a single caller
     handing a batch of world x n pairs to the library, which cuts it by DP cells, runs one engine per GPU on its own
@@ -455,7 +497,7 @@ def main():
     for name, v in (("chunk_pairs", args.chunk_pairs), ("plan_threads", args.plan_threads)):
         if v:
             sw.set_option(name, v)
-    for name, v in (("pipe_wide", args.pipe_wide), ("pack_arena", args.pack), ("pack_lead", args.pack_lead), ("host_plan", args.host_plan)):
+    for name, v in (("pipe_wide", args.pipe_wide), ("pack_arena", args.pack), ("pack_lead", args.pack_lead), ("host_plan", args.host_plan), ("slots", args.slots)):
         if v >= 0:
             sw.set_option(name, v)
 
@@ -561,6 +603,11 @@ def main():
             except Exception as ex:                      # the headline must not die with the sub-record
                 line["multi_handle"] = {"error": repr(ex)}
         cpu_barrier(dist)
+    if line is not None and world == 1 and not args.no_sub and args.config == 2 and not args.pairs:
+        try:
+            line["pairhmm"] = pairhmm_record(local, peaks.get("ffma_f32"))
+        except Exception as ex:
+            line["pairhmm"] = {"error": repr(ex)}
     if line is not None and world == 1 and not args.no_cpu_baseline:
         cb = cpu_baseline(d)
         if cb:

@@ -107,7 +107,11 @@ MGL_SW_API const char *mgl_sw_version(void);
    ranges of the arena cross the host link at 2 bits per base and are expanded on the device: never / for chunks whose
    planner thread is "pack_lead" chunks ahead of the upload / always; default 0: it pays only where the link, not the
    host's cores and memory, is the slower side), "pipe_wide" 0/1/2 (long-pair
-   kernel on eight warps per pair: never / for launches of few pairs / always), "host_plan" 0/1 (chunks planned by
+   kernel on eight warps per pair: never / for launches of few pairs / always), "exact_match_shortcut" 0/1
+   (default 0: the reference's own output; 1: a SOFTCLIP / IGNORE pair whose alt occurs verbatim in its ref returns
+   what GATK's SWNativeAlignerWrapper returns without calling the binding -- offset = last occurrence, CIGAR all M --
+   which the reference leaves to that wrapper, ...MicrosoftSmithWaterman.cpp:60), "slots" 0/2/3/4 (work slots, i.e. chunks
+   in flight: 0 = two for batches of long pairs, four otherwise), "host_plan" 0/1 (chunks planned by
    device kernels / by host threads; the 2-bit transport implies host planning), "overlap" 0/1 (resident_run: 1 = chunks
    alternate between two slots, whole-batch time only; 0 = one chunk at a time with per-kernel times) */
 MGL_SW_API int mgl_sw_set_option(mgl_sw_handle *h, const char *name, int64_t value);

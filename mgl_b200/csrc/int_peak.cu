@@ -11,11 +11,11 @@
 namespace mglsw {
 
 enum { PK_IADD3 = 0, PK_IMNMX, PK_VIMNMX3, PK_VIADDMNMX, PK_VIMNMX3_16, PK_VIADDMNMX_16, PK_LOP3, PK_SHF, PK_IMAD,
-       PK_MIX_ALU_IMAD, PK_PRMT, PK_COUNT };
+       PK_MIX_ALU_IMAD, PK_PRMT, PK_FFMA, PK_COUNT };
 
 static const char *const kNames[PK_COUNT] = {
     "iadd3_s32", "imnmx_s32", "vimnmx3_s32", "viaddmnmx_s32", "vimnmx3_u16x2", "viaddmnmx_u16x2", "lop3", "shf",
-    "imad_s32", "mix_iadd3+imad", "prmt"};
+    "imad_s32", "mix_iadd3+imad", "prmt", "ffma_f32"};
 
 template <int WHICH>
 __device__ __forceinline__ void op(unsigned &x, unsigned a, unsigned b)
@@ -30,6 +30,10 @@ __device__ __forceinline__ void op(unsigned &x, unsigned a, unsigned b)
     else if (WHICH == PK_SHF) asm volatile("shf.l.wrap.b32 %0, %0, %1, %2;" : "+r"(x) : "r"(a), "r"(b));
     else if (WHICH == PK_IMAD) asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(x) : "r"(a), "r"(b));
     else if (WHICH == PK_PRMT) asm volatile("prmt.b32 %0, %0, %1, %2;" : "+r"(x) : "r"(a), "r"(b));
+    /* FP32 multiply-add (the PairHMM roofline's denominator: 2 flops per instruction); the bit patterns are whatever
+       the integer chains hold -- the issue rate does not depend on the values */
+    else if (WHICH == PK_FFMA) asm volatile("{ .reg .f32 fa, fb, fc; mov.b32 fa, %0; mov.b32 fb, %1; mov.b32 fc, %2; fma.rn.f32 fa, fa, fb, fc; mov.b32 %0, fa; }"
+                                            : "+r"(x) : "r"(a), "r"(b));
 }
 
 template <int WHICH>
@@ -108,6 +112,7 @@ cudaError_t run_int_peak(int which, int device, double *ops_per_s, double *sm_mh
     case PK_LOP3: return time_one<PK_LOP3>(sms, ops_per_s);
     case PK_SHF: return time_one<PK_SHF>(sms, ops_per_s);
     case PK_IMAD: return time_one<PK_IMAD>(sms, ops_per_s);
+    case PK_FFMA: return time_one<PK_FFMA>(sms, ops_per_s);
     case PK_MIX_ALU_IMAD: return time_one<PK_MIX_ALU_IMAD>(sms, ops_per_s);
     case PK_PRMT: return time_one<PK_PRMT>(sms, ops_per_s);
     }

@@ -74,9 +74,11 @@ __global__ void __launch_bounds__(128) ph_forward_kernel(const KArgs<N> a)
     constexpr int kUnroll = MGLPH_UNROLL;
     extern __shared__ __align__(16) unsigned char s_raw[];
     const int warp_in_block = threadIdx.x >> 5, wl = threadIdx.x & 31, grp = wl / G, lane = wl % G;
-    const unsigned int w = blockIdx.x * (blockDim.x >> 5) + warp_in_block;
     const unsigned int count = FROM_LIST ? *a.redo_count : a.items;
-    if (w * PPW >= count) return;
+    /* the pass over the redo list does not know its length on the host: a bounded grid walks it (a float pass that
+       escalates nothing costs a few hundred blocks that leave at once, not one block per four pairs of the whole job) */
+    const unsigned int w_stride = FROM_LIST ? gridDim.x * (blockDim.x >> 5) : 0u;
+    for (unsigned int w = blockIdx.x * (blockDim.x >> 5) + warp_in_block; w * PPW < count; w += w_stride) {
     unsigned int item = w * PPW + (unsigned int)grp;
     const bool valid = item < count;
     if (!valid) item = w * PPW;                          /* an odd tail: shadow the warp's first pair, write nothing */
@@ -141,6 +143,9 @@ __global__ void __launch_bounds__(128) ph_forward_kernel(const KArgs<N> a)
             a.out[p] = log10((double)res) - (double)a.log10_initial;    /* .cc:188,206 */
         }
     }
+    if (!FROM_LIST) break;
+    __syncwarp();                                        /* the carry row is reused by the warp's next pair */
+    }
 }
 
 /* shape = G * 100 + RPL; `items` = pairs (or the worst-case length of the redo list) */
@@ -152,7 +157,8 @@ static cudaError_t launch_forward(int shape, unsigned int items, int carry_cols,
     a.carry_cols = carry_cols;
     const int g = shape / 100;
     const unsigned int ppw = 32u / (unsigned int)g;
-    const unsigned int warps = (items + ppw - 1) / ppw, blocks = (warps + 3) / 4;
+    const unsigned int warps = (items + ppw - 1) / ppw;
+    const unsigned int blocks = FROM_LIST ? std::min<unsigned int>((warps + 3) / 4, 148u * 8u) : (warps + 3) / 4;
     const size_t smem = (size_t)4 * ppw * (size_t)(carry_cols + 1) * sizeof(Top<N>);
 #define PH_LAUNCH(R_, G_)                                                                                               \
     do {                                                                                                                \

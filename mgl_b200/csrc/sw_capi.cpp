@@ -359,6 +359,8 @@ int mgl_sw_set_option(mgl_sw_handle *h, const char *name, int64_t value)
         else if (!std::strcmp(name, "pipe_wide")) { if (value < 0 || value > 2) return MGL_SW_E_INVALID; e->pipe_wide = (int)value; }
         else if (!std::strcmp(name, "pack_arena")) { if (value < 0 || value > 2) return MGL_SW_E_INVALID; e->pack_arena = (int)value; }
         else if (!std::strcmp(name, "pack_lead")) { if (value < 0 || value > 1024) return MGL_SW_E_INVALID; e->pack_lead = (int)value; }
+        else if (!std::strcmp(name, "exact_match_shortcut")) e->exact_shortcut = value != 0;
+        else if (!std::strcmp(name, "slots")) { if (value != 0 && (value < 2 || value > MGLSW_SLOTS)) return MGL_SW_E_INVALID; e->slots_opt = (int)value; }
         else if (!std::strcmp(name, "host_plan")) { if (value < 0 || value > 1) return MGL_SW_E_INVALID; e->host_plan = (int)value; }
         else if (!std::strcmp(name, "trace_budget_mb")) { if (value < 0) return MGL_SW_E_INVALID; e->trace_budget_bytes = (u64)value << 20; }
         else return MGL_SW_E_INVALID;

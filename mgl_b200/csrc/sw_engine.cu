@@ -197,12 +197,34 @@ u64 Engine::budget()
     if (trace_budget_bytes) return trace_budget_bytes;
     /* taken once, from the memory free before this engine owns any work buffer: chunk boundaries (and so the sizes the
        slots grow to) must not move from one batch to the next as the engine's own buffers eat into the free figure */
-    if (budget_auto_) return budget_auto_;
+    if (budget_auto_) return std::max<u64>(budget_auto_ / (u64)nslots_, 256ull << 20);
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return 4ull << 30;
-    u64 b = (u64)(free_b * 0.72 / MGLSW_SLOTS);   /* all slots + descriptors stay well inside HBM */
-    budget_auto_ = std::max<u64>(std::min<u64>(b, 48ull << 30), 256ull << 20);
-    return budget_auto_;
+    budget_auto_ = std::min<u64>((u64)(free_b * 0.72), (u64)MGLSW_SLOTS * (48ull << 30));   /* all slots + descriptors stay well inside HBM */
+    return std::max<u64>(budget_auto_ / (u64)nslots_, 256ull << 20);
+}
+
+/*
+ * Work slots of a batch.  Four let the traceback of a chunk hide behind the fills of the next three: right for short
+ * pairs, whose chunks are capped by pair count.  Longer pairs are capped by the HBM their checkpoints take, and there
+ * fewer slots mean larger chunks inside the same memory: launches of whole waves instead of slivers, and, for the
+ * pipelined long-pair kernel (one pair per block), enough pairs to fill every block slot -- a chunk of 320 pairs left
+ * a third of them empty.  Two slots for long and medium pairs, three for mixed batches.
+ * Slots whose buffers no longer fit the per-slot share are released first, so that a handle may alternate batch kinds.
+ */
+void Engine::choose_slots(u64 total_est, int64_t n)
+{
+    /* measured [B200, profiles/r10a]: config 4 (140 MB of checkpoints per pair) 1 706 GCUPS on four slots, 1 845 on two;
+       config 3 (1 MB per pair) 1 748 / 1 868; the mixed config 5 (0.28 MB per pair on average) 1 607 / 1 715 on three / 1 646 on two */
+    const u64 per_pair = n > 0 ? total_est / (u64)n : 0;
+    const int want = slots_opt >= 2 && slots_opt <= MGLSW_SLOTS ? slots_opt : (per_pair >= (512ull << 10) ? 2 : (per_pair >= 196608u ? 3 : MGLSW_SLOTS));
+    if (want == nslots_) return;
+    nslots_ = want;
+    const u64 share = budget() + budget() / 4 + (512ull << 20);
+    for (int k = 0; k < MGLSW_SLOTS; k++) {
+        WorkSlot &ws = slots_[k];
+        if (k >= nslots_ || ws.ckpt.cap > share) { cudaStreamSynchronize(ws.post); cudaStreamSynchronize(ws.stream); ws.ckpt.release(); ws.scratch.release(); ws.ops.release(); }
+    }
 }
 
 /*
@@ -595,6 +617,10 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed, bo
         return MGL_SW_OK;
     }
     if ((e = launch_traceback(t, pt)) != cudaSuccess) return cuda_fail(e, "traceback launch");
+    if (exact_shortcut) {
+        if ((e = launch_exact_match(t, pt)) != cudaSuccess) return cuda_fail(e, "exact-match launch");
+        bs.other_launches += 1;
+    }
     if (timed) cudaEventRecord(tev_[3], pt);
     if (text) {
         /* characters per pair -> the same scan -> characters; the packed elements stay in the scratch buffer */
@@ -701,6 +727,7 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         span_lo = std::min(span_lo, span_hi) & ~63ull;
     }
     const u64 span = span_hi - span_lo;
+    choose_slots(total_est, in.n);
     /* checkpoint estimate of pairs [0, x) */
     auto est_before = [&](int64_t x) -> u64 {
         if (x <= 0) return 0;
@@ -741,6 +768,7 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
     }
 
     InFlight fl[MGLSW_SLOTS];
+    const int NS = nslots_;
     u64 ops_running = 0;
     bool overflow = false;
     int rc = MGL_SW_OK;
@@ -819,7 +847,7 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
     const int nchunks = (int)bounds.size();
     nthreads = dev_plan ? 1 : std::min(nthreads, nchunks);
     setup_mark("chunk bounds");
-    const int R = (dev_plan ? DEV_AHEAD : nthreads) + MGLSW_SLOTS + 1;
+    const int R = (dev_plan ? DEV_AHEAD : nthreads) + NS + 1;
     while ((int)ring_.size() < R) ring_.push_back(new ChunkDev());
     std::vector<int> ready((size_t)nchunks, 0);          /* 0 pending, 1 planned, 2 failed */
     std::vector<int> prc((size_t)nchunks, MGL_SW_OK);
@@ -867,7 +895,7 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
                             std::chrono::duration<double, std::milli>(tl_t0 - fn_t0).count());
     int c = 0;
     for (; c < nchunks && rc == MGL_SW_OK; c++) {
-        const int si = c % MGLSW_SLOTS;
+        const int si = c % NS;
         WorkSlot &ws = slots_[si];
         ChunkDev &cd = *ring_[(size_t)(c % R)];
         upload_cursor.store(c, std::memory_order_relaxed);
@@ -882,8 +910,8 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         }
         if (dev_plan && (rc = collect_plan_dev(cd)) != MGL_SW_OK) break;     /* the summary of this chunk's plan */
         const double t_ready = tl_ms();
-        if ((rc = finish(si)) != MGL_SW_OK) break;              /* chunk c - MGLSW_SLOTS: already home */
-        release_upto(c - MGLSW_SLOTS + 1);
+        if ((rc = finish(si)) != MGL_SW_OK) break;              /* chunk c - NS: already home */
+        release_upto(c - NS + 1);
         const double t_slot = tl_ms();
         const int64_t first = cd.first;
         if ((rc = ensure_slot(ws, cd.plan, cd.n, so, tx)) != MGL_SW_OK) break;
@@ -899,8 +927,8 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
             cudaEventRecord(ws.ev_counts, ws.post);
             cudaEventRecord(ws.ev_post, ws.post);
             fl[si].busy = true; fl[si].first = first; fl[si].n = n;
-            if ((rc = finish((c + 1) % MGLSW_SLOTS)) != MGL_SW_OK) break;
-            release_upto(c - MGLSW_SLOTS + 2);
+            if ((rc = finish((c + 1) % NS)) != MGL_SW_OK) break;
+            release_upto(c - NS + 2);
             continue;
         }
         if ((e = cudaMemcpyAsync(out.offsets + first, ws.offsets.p, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess) { rc = cuda_fail(e, "D2H offsets"); break; }
@@ -912,15 +940,15 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         fl[si].busy = true; fl[si].first = first; fl[si].n = n;
         const double t_launched = tl_ms();
         /* while the newest chunks run, bring the oldest one home: its slot is the next chunk's */
-        if ((rc = finish((c + 1) % MGLSW_SLOTS)) != MGL_SW_OK) break;
-        release_upto(c - MGLSW_SLOTS + 2);
+        if ((rc = finish((c + 1) % NS)) != MGL_SW_OK) break;
+        release_upto(c - NS + 2);
         if (tl_on) std::fprintf(stderr, "[mgl_sw] chunk %d n=%u: planned by %.2f ms, slot free %.2f, launched %.2f, previous chunk home %.2f\n",
                                 c, n, t_ready, t_slot, t_launched, tl_ms());
     }
     { std::lock_guard<std::mutex> lk(mu); stop = true; }
     cv.notify_all();
     for (std::thread &t : workers) t.join();
-    for (int k = 0; k < MGLSW_SLOTS && rc == MGL_SW_OK; k++) rc = finish((c + k) % MGLSW_SLOTS);   /* oldest first */
+    for (int k = 0; k < NS && rc == MGL_SW_OK; k++) rc = finish((c + k) % NS);   /* oldest first */
     if (rc != MGL_SW_OK) {
         cudaDeviceSynchronize();
         cudaGetLastError();
@@ -959,6 +987,7 @@ int Engine::prepare_resident(const BatchIn &in)
     {
         u64 total_est = 0;
         for (int64_t k = 0; k < in.n; k++) total_est += pair_ckpt_bytes(in.ref_len[k], in.alt_len[k]);
+        choose_slots(total_est, in.n);
         chunk_cap_ = chunk_cap(total_est, in.n);
     }
     int64_t first = 0;
@@ -1003,14 +1032,14 @@ int Engine::run_resident(BatchStats *stats)
      * time is start -> the latest of the post streams' last events.
      */
     for (size_t c = 0; c < resident_.size(); c++) {        /* grow each slot to its largest chunk before timing */
-        int rc = ensure_slot(slots_[c % MGLSW_SLOTS], resident_[c]->plan, resident_[c]->n);
+        int rc = ensure_slot(slots_[c % nslots_], resident_[c]->plan, resident_[c]->n);
         if (rc != MGL_SW_OK) return rc;
     }
     if ((e = cudaEventRecord(tev_[0], slots_[0].stream)) != cudaSuccess) return cuda_fail(e, "event record");
     for (int k = 1; k < MGLSW_SLOTS; k++)
         if ((e = cudaStreamWaitEvent(slots_[k].stream, tev_[0], 0)) != cudaSuccess) return cuda_fail(e, "stream wait");
     for (size_t c = 0; c < resident_.size(); c++) {
-        int rc = run_chunk(*resident_[c], slots_[c % MGLSW_SLOTS], bs, false);
+        int rc = run_chunk(*resident_[c], slots_[c % nslots_], bs, false);
         if (rc != MGL_SW_OK) return rc;
     }
     float a = 0;

@@ -138,6 +138,8 @@ public:
     u32 chunk_pairs = 1u << 16;  /* measured: 64 Ki pairs per chunk with four slots is within 1 % of the best device rate and plans in < 5 ms */
     int plan_threads = 0;        /* host planner threads of align_batch; 0: min(8, hardware threads / 2) */
     int scan_threads = 0;        /* short-lived threads of align_batch's pair-table scan; 0: min(8, hardware threads / 2) */
+    bool exact_shortcut = false; /* SOFTCLIP / IGNORE pairs whose alt occurs verbatim in the ref answer as GATK's SWNativeAlignerWrapper does (sw_trace_kernel.cu) */
+    int slots_opt = 0;           /* work slots per batch: 0 = two for batches of long pairs, four otherwise; 2..4 forces */
     int host_plan = 0;           /* 1: chunks are planned by host threads (sw_plan.cpp), 0: by device kernels (sw_plan_dev.cu) */
     int pipe_wide = 1;           /* pipelined long-pair launches on eight warps per pair: 0 never, 1 when the launch has few pairs, 2 always */
     u64 trace_budget_bytes = 0;  /* 0: derived from free memory */
@@ -163,6 +165,8 @@ private:
     int run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed, bool score_only = false, bool text = false);
     int ensure_slot(WorkSlot &ws, const ChunkPlan &plan, u32 n, bool score_only = false, bool text = false);
     u64 budget();
+    void choose_slots(u64 total_est, int64_t n);
+    int nslots_ = MGLSW_SLOTS;   /* work slots of the current batch */
     u32 chunk_cap(u64 total_est, int64_t n) const;
     u32 chunk_cap_ = 0;          /* prepare_resident: pairs per chunk of the resident batch */
 

@@ -29,6 +29,9 @@ struct TraceArgs {
     u32 n_units;              /* units of the chunk (padding units included)    */
 };
 cudaError_t launch_traceback(const TraceArgs &a, cudaStream_t stream);
+/* opt-in: SOFTCLIP / IGNORE pairs whose alt occurs verbatim in the ref take GATK's wrapper answer (last occurrence, all M);
+   runs after launch_traceback on the same stream and overwrites offsets / n_ops / scratch of those pairs */
+cudaError_t launch_exact_match(const TraceArgs &a, cudaStream_t stream);
 /* score-only runs: the traceback's start cell (sw.cpp:155-170) and its H, nothing else (needs units, strategy, c16, c32, colbest, lastrow, score3) */
 cudaError_t launch_endpoints(const TraceArgs &a, cudaStream_t stream);
 

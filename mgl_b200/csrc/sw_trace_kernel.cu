@@ -58,6 +58,56 @@ __global__ void __launch_bounds__(128) sw_endpoint_kernel(const __grid_constant_
     a.score3[3 * (size_t)p + 2] = st.j;
 }
 
+/*
+ * The exact-substring shortcut, opt-in.  The reference skips it on purpose -- "we skip substring
+ * check since it performed by SWNativeAlignerWrapper" (...MicrosoftSmithWaterman.cpp:60) -- because GATK's wrapper
+ * around the native binding (external to the reference: org.broadinstitute.hellbender...SWNativeAlignerWrapper.align)
+ * answers SOFTCLIP and IGNORE calls itself when the alt occurs verbatim in the ref: offset = the LAST index at which
+ * it occurs, CIGAR = <alt length>M.  A batched entry that bypasses that wrapper has no such pre-check, and the DP's
+ * own answer can differ from it (repeats: the DP's tie rules need not pick the last occurrence).  With the option on,
+ * this kernel overrides the traceback's result for exactly those pairs: one warp per pair, 32 candidate starts at a
+ * time from the back of the ref, so the first group with a hit holds the last occurrence.
+ */
+__global__ void __launch_bounds__(128) sw_exact_match_kernel(const __grid_constant__ TraceArgs a)
+{
+    const u32 wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
+    if (wid >= 2u * a.n_units) return;
+    const UnitDesc &u = a.units[wid >> 1];
+    const u32 half = wid & 1u;
+    const u32 p = u.pair[half];
+    if (!(u.flags & UNIT_ACTIVE) || p == NO_PAIR || (half == 1u && (u.flags & UNIT_S32))) return;
+    const int strategy = a.strategy[p];
+    if (strategy != OS_SOFTCLIP && strategy != OS_IGNORE) return;
+    const int tl = (int)u.tl[half], ql = (int)u.ql;
+    if (ql > tl) return;
+    const uint8_t *ref = a.arena + u.ref_off[half], *alt = a.arena + u.alt_off[half];
+    for (int base = tl - ql; base >= 0; base -= 32) {
+        const int i = base - (int)lane;
+        bool hit = i >= 0;
+        if (hit) {
+            const uint8_t *r = ref + i;
+            for (int k = 0; k < ql; k++) if (__ldg(r + k) != __ldg(alt + k)) { hit = false; break; }
+        }
+        const u32 m = __ballot_sync(0xffffffffu, hit);
+        if (m) {
+            if (lane == 0) {
+                const int idx = base - (__ffs(m) - 1);                   /* the lowest lane with a hit = the largest start */
+                a.offsets[p] = idx;
+                a.n_ops[p] = 1u;
+                a.scratch[a.ops_end[p] - 1u] = ((u32)ql << 4) | OP_M;
+            }
+            return;
+        }
+    }
+}
+
+cudaError_t launch_exact_match(const TraceArgs &a, cudaStream_t stream)
+{
+    if (a.n_units == 0) return cudaSuccess;
+    sw_exact_match_kernel<<<(2u * a.n_units * 32u + 127) / 128, 128, 0, stream>>>(a);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_endpoints(const TraceArgs &a, cudaStream_t stream)
 {
     if (a.n_units == 0) return cudaSuccess;

@@ -581,3 +581,67 @@ def test_device_planner_and_host_planner_give_identical_results(sw, oracle):
     for p in range(0, len(fuzz), 3):
         exp = oracle.align(fuzz[p][0], fuzz[p][1], (3, -1, -2, 0), int(fst[p]))
         assert (got[0][1].cigar(p), int(got[0][1].offsets[p])) == exp and (got[0][2].cigar(p), int(got[0][2].offsets[p])) == exp, p
+
+
+def test_exact_match_shortcut_is_opt_in_and_matches_gatks_wrapper(sw, oracle):
+    """SURVEY.md 8f row 2.  Default: the reference's own output for every pair.  With "exact_match_shortcut": SOFTCLIP and
+    IGNORE pairs whose alt occurs verbatim in the ref return what GATK's SWNativeAlignerWrapper returns before it would
+    call the binding (...MicrosoftSmithWaterman.cpp:60 leaves the check to it): offset = the LAST occurrence, CIGAR = all M;
+    INDEL / LEADING_INDEL pairs and pairs without an exact occurrence are untouched."""
+    rng = random.Random(606)
+    pairs = []
+    for k in range(600):
+        unit = bytes(rng.choice(b"ACGT") for _ in range(rng.randint(3, 40)))
+        ref = (unit * rng.randint(1, 8) + bytes(rng.choice(b"ACGT") for _ in range(rng.randint(0, 60))))[: rng.randint(20, 400)]
+        if k % 3 == 0:
+            i = rng.randrange(len(ref)); j = rng.randint(i + 1, min(len(ref), i + 200))
+            alt = ref[i:j]                                            # verbatim, often repeated in the ref
+        elif k % 3 == 1:
+            alt = bytes(rng.choice(b"ACGT") for _ in range(rng.randint(1, 150)))
+        else:
+            i = rng.randrange(len(ref)); j = rng.randint(i + 1, min(len(ref), i + 200))
+            a = bytearray(ref[i:j]); a[rng.randrange(len(a))] = ord("N"); alt = bytes(a)
+        pairs.append((ref, alt))
+    params = (10, -15, -30, -5)
+    strategies = np.array([(1, 8, 2, 4)[k % 4] for k in range(len(pairs))], dtype=np.int32)
+    plain = sw.align_batch(pairs, params, 1, strategies)
+    sw.set_option("exact_match_shortcut", 1)
+    try:
+        short = sw.align_batch(pairs, params, 1, strategies)
+        text = sw.align_batch_text(pairs, params, 1, strategies)
+    finally:
+        sw.set_option("exact_match_shortcut", 0)
+    hits = differ = 0
+    for k, (r, a) in enumerate(pairs):
+        s = int(strategies[k])
+        dp = oracle.align(r, a, params, s)
+        assert (plain.cigar(k), int(plain.offsets[k])) == dp, k
+        at = r.rfind(a) if s in (1, 8) else -1
+        exp = (f"{len(a)}M", at) if at >= 0 else dp
+        assert (short.cigar(k), int(short.offsets[k])) == exp, (k, s, len(r), len(a), at)
+        assert text[k] == exp, k
+        hits += at >= 0
+        differ += at >= 0 and exp != dp
+    assert hits > 60 and differ > 0            # the shortcut fired, and somewhere it is not what the DP says (a repeat)
+
+
+def test_work_slots_follow_the_batch_kind(sw, oracle):
+    """two work slots for long pairs, three for mixed batches, four for short pairs: one handle alternates between them
+    (buffers of the other layout are released first) and every batch still matches the reference"""
+    from mgl_b200 import synth
+    for config, n in ((2, 30000), (4, 24), (5, 40000), (3, 4000), (2, 30000)):
+        d = synth.generate(config, n)
+        cap = max(8 * n, int(d["ref_len"].astype(np.int64).sum() + d["alt_len"].astype(np.int64).sum()) // 8)
+        res = sw.align_arrays(d["arena"], d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, d["strategies"], ops_cap=cap)
+        if oracle.have_ref():
+            nbad, first, _ = oracle.ref_check_batch(d["arena"], d["ref_off"], d["alt_off"], d["ref_len"], d["alt_len"], d["params"],
+                                                    d["strategies"], res.offsets, res.cigar_start, res.ops)
+            assert nbad == 0, (config, nbad, first)
+    for slots in (2, 3, 4):
+        sw.set_option("slots", slots)
+        d = synth.generate(3, 3000)
+        res = sw.align_arrays(d["arena"], d["ref_off"], d["ref_len"], d["alt_off"], d["alt_len"], d["params"], 1, d["strategies"], ops_cap=64 * 3000)
+        for p in range(0, 3000, 41):
+            r, a = synth.pair_bytes(d, p)
+            assert (res.cigar(p), int(res.offsets[p])) == oracle.align(r, a, d["params"], int(d["strategies"][p])), (slots, p)
+    sw.set_option("slots", 0)
