@@ -442,6 +442,7 @@ def pairhmm_record(local, ffma_gops, steps=5, warmup=3):
             "pairs": reads * haps, "cells": cells, "steps": steps, "value": value, "unit": UNIT, "ms_per_step": dev_ms / steps,
             "pairs_recomputed_in_double": int(redone),
             "roofline": {"bound": "fp32", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": (ach / peak) if peak else None,
+                         "peak_nominal": 148 * 128 * 2 * 1.965e9 / 1e12,
                          "note": "ph_forward_kernel<float>; algorithmic 11 flops per cell (8 FP32 instructions, compute_prob_scalar.cc:39-43) "
                                  "x cells / device time; peak = 2 flops x the FP32 FMA issue rate measured on this box by int_peak.cu (ffma_f32)"},
             "e2e": {"value": cells * steps / (e2e_ms * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": e2e_ms / steps}}

@@ -51,7 +51,8 @@ __global__ void __launch_bounds__(256) peak_kernel(unsigned *out, unsigned a, un
                 if (WHICH == PK_MIX_ALU_IMAD) {
                     if (k & 1) op<PK_IMAD>(x[k], x[(k + 2) & 7], x[(k + 4) & 7]);
                     else op<PK_IADD3>(x[k], x[(k + 2) & 7], x[(k + 4) & 7]);
-                } else op<WHICH>(x[k], x[(k + 1) & 7], x[(k + 3) & 7]);
+                } else if (WHICH == PK_FFMA) op<WHICH>(x[k], a, b);      /* x = x * a + b: loop-invariant operands, no register-bank pressure */
+                else op<WHICH>(x[k], x[(k + 1) & 7], x[(k + 3) & 7]);
             }
         }
     }

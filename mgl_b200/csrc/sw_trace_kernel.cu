@@ -63,8 +63,9 @@ __global__ void __launch_bounds__(128) sw_endpoint_kernel(const __grid_constant_
  * check since it performed by SWNativeAlignerWrapper" (...MicrosoftSmithWaterman.cpp:60) -- because GATK's wrapper
  * around the native binding (external to the reference: org.broadinstitute.hellbender...SWNativeAlignerWrapper.align)
  * answers SOFTCLIP and IGNORE calls itself when the alt occurs verbatim in the ref: offset = the LAST index at which
- * it occurs, CIGAR = <alt length>M.  A batched entry that bypasses that wrapper has no such pre-check, and the DP's
- * own answer can differ from it (repeats: the DP's tie rules need not pick the last occurrence).  With the option on,
+ * it occurs, CIGAR = <alt length>M.  A batched entry that bypasses that wrapper has no such pre-check.  (On every case
+ * tried the DP's own tie rules -- the last-column maximum with ">=", sw.cpp:100-104 -- pick the last occurrence as
+ * well, so the two agree; the option exists so that the wrapper's rule, not an observation, decides.)  With the option on,
  * this kernel overrides the traceback's result for exactly those pairs: one warp per pair, 32 candidate starts at a
  * time from the back of the ref, so the first group with a hit holds the last occurrence.
  */
