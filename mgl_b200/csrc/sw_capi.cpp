@@ -172,15 +172,18 @@ int run_multi(mgl_sw_handle *h, const BatchIn &in, BatchOut &out, BatchStats &to
             /* staging capacity: twice the shard's share of the caller's capacity; a shard that needs more (and less
                than the caller's whole capacity) is run again with exactly what it asked for */
             u64 want = std::min<u64>(cap, std::max<u64>(4096, 2 * (u64)((long double)cap * (hi - lo) / in.n) + 1024));
+            const bool direct = lo == 0;               /* the first shard's elements start at 0: straight into the caller's array */
+            if (direct) want = cap;
             for (int attempt = 0; attempt < 2; attempt++) {
                 PinBuf &pb = h->shard_out[(size_t)s];
                 cudaSetDevice(h->engines[(size_t)s]->device());
-                if (pb.reserve((size_t)want * esz + 16) != cudaSuccess) { rc[(size_t)s] = MGL_SW_E_CUDA; return; }
+                if (!direct && pb.reserve((size_t)want * esz + 16) != cudaSuccess) { rc[(size_t)s] = MGL_SW_E_CUDA; return; }
+                void *dst = direct ? (tx ? (void *)out.text : (void *)out.ops) : pb.p;
                 o.offsets = out.offsets + lo;
                 o.cigar_start = out.cigar_start + lo;
                 o.keep_first_start = lo > 0;           /* element lo belongs to the previous shard's last pair */
-                o.ops = tx ? nullptr : (u32 *)pb.p; o.ops_cap = tx ? 0 : want;
-                o.text = tx ? (char *)pb.p : nullptr; o.text_cap = tx ? want : 0;
+                o.ops = tx ? nullptr : (u32 *)dst; o.ops_cap = tx ? 0 : want;
+                o.text = tx ? (char *)dst : nullptr; o.text_cap = tx ? want : 0;
                 rc[(size_t)s] = h->engines[(size_t)s]->align_batch(sub, o, &st[(size_t)s]);
                 produced[(size_t)s] = o.ops_total;
                 if (rc[(size_t)s] != MGL_SW_E_OPS_CAPACITY || o.ops_total > cap || attempt == 1) break;
@@ -223,7 +226,7 @@ int run_multi(mgl_sw_handle *h, const BatchIn &in, BatchOut &out, BatchStats &to
         const int64_t lo = bounds[(size_t)s], hi = bounds[(size_t)s + 1];
         if (hi <= lo) return;
         char *dst = tx ? out.text : (char *)out.ops;
-        std::memcpy(dst + base[(size_t)s] * esz, h->shard_out[(size_t)s].p, (size_t)produced[(size_t)s] * esz);
+        if (lo > 0) std::memcpy(dst + base[(size_t)s] * esz, h->shard_out[(size_t)s].p, (size_t)produced[(size_t)s] * esz);
         if (s > 0) { const u64 b = base[(size_t)s]; for (int64_t p = lo + 1; p <= hi; p++) out.cigar_start[p] += b; }
     };
     {
@@ -281,7 +284,7 @@ int mgl_sw_create_multi(const int *devices, int n_devices, mgl_sw_handle **out)
     if (n_devices > 1) {
         /* the engines share the host's cores: each plans with its share of them */
         const int per = (int)std::max(1u, std::min(8u, std::thread::hardware_concurrency() / 2u / (unsigned)n_devices));
-        for (Engine *e : h->engines) { e->plan_threads = per; e->scan_threads = per; }
+        for (Engine *e : h->engines) { e->plan_threads = per; e->scan_threads = std::max(per, std::min(4, (int)(std::thread::hardware_concurrency() / (unsigned)n_devices))); }
     }
     *out = h;
     return MGL_SW_OK;
