@@ -107,7 +107,8 @@ MGL_SW_API const char *mgl_sw_version(void);
    ranges of the arena cross the host link at 2 bits per base and are expanded on the device: never / for chunks whose
    planner thread is "pack_lead" chunks ahead of the upload / always; default 0: it pays only where the link, not the
    host's cores and memory, is the slower side), "pipe_wide" 0/1/2 (long-pair
-   kernel on eight warps per pair: never / for launches of few pairs / always), "exact_match_shortcut" 0/1
+   kernel on eight warps per pair: never / for launches of few pairs / always), "copy_threads" (threads that stage a PAGEABLE arena into pinned
+   memory chunk by chunk; default 8 or half the hardware threads, 0 leaves it to the driver), "exact_match_shortcut" 0/1
    (default 0: the reference's own output; 1: a SOFTCLIP / IGNORE pair whose alt occurs verbatim in its ref returns
    what GATK's SWNativeAlignerWrapper returns without calling the binding -- offset = last occurrence, CIGAR all M --
    which the reference leaves to that wrapper, ...MicrosoftSmithWaterman.cpp:60), "slots" 0/2/3/4 (work slots, i.e. chunks

@@ -284,7 +284,7 @@ int mgl_sw_create_multi(const int *devices, int n_devices, mgl_sw_handle **out)
     if (n_devices > 1) {
         /* the engines share the host's cores: each plans with its share of them */
         const int per = (int)std::max(1u, std::min(8u, std::thread::hardware_concurrency() / 2u / (unsigned)n_devices));
-        for (Engine *e : h->engines) { e->plan_threads = per; e->scan_threads = std::max(per, std::min(4, (int)(std::thread::hardware_concurrency() / (unsigned)n_devices))); }
+        for (Engine *e : h->engines) { e->plan_threads = per; e->copy_threads = std::min(4, std::max(1, per)); e->scan_threads = std::max(per, std::min(4, (int)(std::thread::hardware_concurrency() / (unsigned)n_devices))); }
     }
     *out = h;
     return MGL_SW_OK;
@@ -362,6 +362,7 @@ int mgl_sw_set_option(mgl_sw_handle *h, const char *name, int64_t value)
         else if (!std::strcmp(name, "pipe_wide")) { if (value < 0 || value > 2) return MGL_SW_E_INVALID; e->pipe_wide = (int)value; }
         else if (!std::strcmp(name, "pack_arena")) { if (value < 0 || value > 2) return MGL_SW_E_INVALID; e->pack_arena = (int)value; }
         else if (!std::strcmp(name, "pack_lead")) { if (value < 0 || value > 1024) return MGL_SW_E_INVALID; e->pack_lead = (int)value; }
+        else if (!std::strcmp(name, "copy_threads")) { if (value < 0 || value > 32) return MGL_SW_E_INVALID; e->copy_threads = (int)value; }
         else if (!std::strcmp(name, "exact_match_shortcut")) e->exact_shortcut = value != 0;
         else if (!std::strcmp(name, "slots")) { if (value != 0 && (value < 2 || value > MGLSW_SLOTS)) return MGL_SW_E_INVALID; e->slots_opt = (int)value; }
         else if (!std::strcmp(name, "host_plan")) { if (value < 0 || value > 1) return MGL_SW_E_INVALID; e->host_plan = (int)value; }

@@ -93,6 +93,7 @@ struct ChunkDev {
        work buffer; the summary the host reads back; the event that says the summary is home */
     DevBuf table, work;
     PinBuf h_table, h_sum;
+    PinBuf h_arena;                      /* a pageable caller arena: the chunk's byte range, staged here by a few threads */
     PlanDevLayout lay{};
     cudaEvent_t ev_plan = nullptr;
     cudaEvent_t ev_table = nullptr;      /* the chunk's pair table is on the device */
@@ -139,6 +140,7 @@ public:
     int plan_threads = 0;        /* host planner threads of align_batch; 0: min(8, hardware threads / 2) */
     int scan_threads = 0;        /* short-lived threads of align_batch's pair-table scan; 0: min(8, hardware threads / 2) */
     bool exact_shortcut = false; /* SOFTCLIP / IGNORE pairs whose alt occurs verbatim in the ref answer as GATK's SWNativeAlignerWrapper does (sw_trace_kernel.cu) */
+    int copy_threads = 8;        /* threads that stage a PAGEABLE caller arena into pinned memory, chunk by chunk (0: leave it to the driver) */
     int slots_opt = 0;           /* work slots per batch: 0 = two for batches of long pairs, four otherwise; 2..4 forces */
     int host_plan = 0;           /* 1: chunks are planned by host threads (sw_plan.cpp), 0: by device kernels (sw_plan_dev.cu) */
     int pipe_wide = 1;           /* pipelined long-pair launches on eight warps per pair: 0 never, 1 when the launch has few pairs, 2 always */
@@ -175,6 +177,7 @@ private:
     std::string err_;
     DevBuf arena_;               /* device copy of bytes [arena_base_, ..) of the caller's arena, padded on both sides (sw_fill.h) */
     u64 arena_base_ = 0;
+    bool arena_pageable_ = false;   /* the current batch's arena is ordinary (unregistered) host memory */
     /* where caller offset 0 would sit: device code adds the caller's own offsets (only [arena_base_, ..) is backed) */
     const uint8_t *arena_dev() const { return (const uint8_t *)((uintptr_t)arena_.p + MGLSW_ARENA_FRONT_PAD - (uintptr_t)arena_base_); }
     int reserve_arena(const BatchIn &in);
