@@ -64,6 +64,41 @@ MGL_PH_API int mgl_pairhmm_resident_prepare(mgl_pairhmm_handle *h, const int32_t
 MGL_PH_API int mgl_pairhmm_resident_run(mgl_pairhmm_handle *h, int use_double, mgl_pairhmm_stats *stats);
 MGL_PH_API int mgl_pairhmm_resident_fetch(mgl_pairhmm_handle *h, double *out);
 
+/*
+ * The same job for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  NO COUNTERPART IN THE REFERENCE.
+ *
+ * Needs no handle and allocates nothing, neither device nor pinned memory: no cudaMalloc / cudaFree, no stream or
+ * event creation.  Everything mgl_pairhmm_compute keeps in cudaMalloc'ed buffers -- the float pass's redo list and
+ * its counter, the quality tables, the offset tables, the padded copies of reads and haplotypes, the likelihoods
+ * before they are copied out -- lives in ONE file-scope static __device__ array of the library
+ * (mgl_pairhmm_noalloc_scratch_bytes() bytes, about 3 MiB, held by every GPU that loads the library until exit).
+ * Hence the limits, beyond which the call fails with MGL_PH_E_TOO_LARGE and touches nothing:
+ *   reads <= MGL_PH_NOALLOC_MAX_READS, haplotypes <= MGL_PH_NOALLOC_MAX_HAPS, pairs <= MGL_PH_NOALLOC_MAX_PAIRS,
+ *   read bases in total <= MGL_PH_NOALLOC_MAX_READ_BASES, haplotype bases in total <= MGL_PH_NOALLOC_MAX_HAP_BASES.
+ *
+ * lengths is host memory (as above); reads, haps and out are the caller's buffers in the layout above and may be
+ * device pointers or host pointers (copied with cudaMemcpyDefault; pinned host memory keeps the copies asynchronous).
+ * stream is a cudaStream_t passed as a pointer, NULL for the default stream: copies and kernels are enqueued on it
+ * and, unless flags has MGL_PH_NOALLOC_NO_SYNC, waited for before the call returns.  The first call on a device
+ * does a one-time synchronous set-up (symbol address, table upload): make it before a capture begins.
+ * Every call shares the one array: host-side the calls are serialised, but two calls whose work OVERLAPS ON THE GPU
+ * (different streams, or NO_SYNC calls on streams that run concurrently) race on it -- order them on one stream.
+ * All reads run one kernel shape chosen from the longest read (mgl_pairhmm_compute picks a shape per read): results
+ * agree with mgl_pairhmm_compute within the library's 1e-5 tolerance on the log10 likelihood.
+ */
+#define MGL_PH_E_TOO_LARGE  -5   /* job beyond the static scratch of mgl_pairhmm_compute_noalloc       */
+#define MGL_PH_NOALLOC_MAX_READS       4096
+#define MGL_PH_NOALLOC_MAX_HAPS        1024
+#define MGL_PH_NOALLOC_MAX_PAIRS       65536
+#define MGL_PH_NOALLOC_MAX_READ_BASES  262144
+#define MGL_PH_NOALLOC_MAX_HAP_BASES   262144
+#define MGL_PH_NOALLOC_NO_SYNC         1
+MGL_PH_API int mgl_pairhmm_compute_noalloc(int device, const int32_t *lengths, const uint8_t *reads, const uint8_t *haps,
+                                           int use_double, double *out, void *stream, int flags);
+MGL_PH_API uint64_t mgl_pairhmm_noalloc_scratch_bytes(void);
+MGL_PH_API const char *mgl_pairhmm_noalloc_last_error(void);   /* of the calling thread's last failed call */
+
 #ifdef __cplusplus
 }
 #endif

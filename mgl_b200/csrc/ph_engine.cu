@@ -420,6 +420,172 @@ private:
     uint64_t cells_ = 0;
 };
 
+/*
+ * ---- mgl_pairhmm_compute_noalloc: the same job out of a static device array (include/mgl_pairhmm.h) ----
+ *
+ * No counterpart in the reference.  For callers that cannot call cudaMalloc: everything Engine keeps in cudaMalloc'ed
+ * buffers is one file-scope __device__ array here.  g_noalloc_scratch, as host code sees it, is only a host-side
+ * stand-in for the array: its device address comes from cudaGetSymbolAddress, once per device with that device
+ * current (noalloc_setup), and only that address is ever handed to a kernel or a copy.
+ * The array is shared by every call and keeps the last call's contents; what must start at zero (the redo counter)
+ * is cleared per call, everything else is overwritten before it is read.
+ */
+struct NoAllocScratch {
+    unsigned int redo_count[64];                                   /* [0]: the float pass's escalation counter */
+    float tab_f[128 + MGLPH_MM_ENTRIES];
+    double tab_d[128 + MGLPH_MM_ENTRIES];
+    int64_t read_off[MGL_PH_NOALLOC_MAX_READS + 1];
+    int64_t hap_off[MGL_PH_NOALLOC_MAX_HAPS + 1];
+    int read_list[MGL_PH_NOALLOC_MAX_READS];                       /* identity: one shape for every read */
+    int32_t lengths[MGL_PH_NOALLOC_MAX_READS + MGL_PH_NOALLOC_MAX_HAPS + 2];
+    unsigned int redo[MGL_PH_NOALLOC_MAX_PAIRS];
+    double out[MGL_PH_NOALLOC_MAX_PAIRS];
+    uint8_t reads[5 * MGL_PH_NOALLOC_MAX_READ_BASES + 16];
+    uint8_t haps[2 * MGL_PH_NOALLOC_MAX_HAP_BASES + 2 * MGLPH_HAP_PAD];   /* pad | bases | pad + the longest haplotype (ph_hap_byte) */
+};
+static __device__ __align__(256) unsigned char g_noalloc_scratch[sizeof(NoAllocScratch)];
+
+/* exclusive scan of mul * len[0, n) into off[0, n]; one block of 128 threads, a contiguous slice per thread */
+static __device__ void ph_noalloc_scan(const int32_t *len, int n, int mul, int64_t *off, int64_t *part)
+{
+    const int per = (n + 127) / 128, b = min(n, (int)threadIdx.x * per), e = min(n, b + per);
+    int64_t sum = 0;
+    for (int i = b; i < e; i++) sum += (int64_t)mul * len[i];
+    part[threadIdx.x] = sum;
+    __syncthreads();
+    int64_t base = 0;
+    for (int k = 0; k < (int)threadIdx.x; k++) base += part[k];
+    if (threadIdx.x == 0) off[0] = 0;
+    for (int i = b; i < e; i++) { base += (int64_t)mul * len[i]; off[i + 1] = base; }
+    __syncthreads();
+}
+
+/* lengths (as uploaded) -> byte offsets of the reads' five tracks and of the haplotypes, and the identity read list */
+__global__ void __launch_bounds__(128) ph_noalloc_offsets_kernel(NoAllocScratch *s, int R, int H)
+{
+    __shared__ int64_t part[128];
+    ph_noalloc_scan(s->lengths + 1, R, 5, s->read_off, part);
+    ph_noalloc_scan(s->lengths + 2 + R, H, 1, s->hap_off, part);
+    for (int r = (int)threadIdx.x; r < R; r += 128) s->read_list[r] = r;
+}
+
+static constexpr int kNoAllocMaxDevices = 64;
+static NoAllocScratch *g_noalloc_dev[kNoAllocMaxDevices];          /* device address of the array, per device, once set up */
+static std::mutex g_noalloc_mu;
+static thread_local char g_noalloc_err[256];
+
+static int noalloc_fail(int rc, const char *what, cudaError_t e = cudaSuccess)
+{
+    if (e != cudaSuccess) { std::snprintf(g_noalloc_err, sizeof g_noalloc_err, "%s: %s", what, cudaGetErrorString(e)); cudaGetLastError(); }
+    else std::snprintf(g_noalloc_err, sizeof g_noalloc_err, "%s", what);
+    return rc;
+}
+
+/* once per device, with that device current: the array's device address and the quality tables */
+static int noalloc_setup(int device)
+{
+    if (g_noalloc_dev[device]) return MGL_PH_OK;
+    cudaError_t e;
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return noalloc_fail(MGL_PH_E_CUDA, "device properties", e);
+    if (prop.major != 10) return noalloc_fail(MGL_PH_E_NO_DEVICE, "built for sm_100a (B200) only");
+    NoAllocScratch *s = nullptr;
+    if ((e = cudaGetSymbolAddress((void **)&s, g_noalloc_scratch)) != cudaSuccess || !s)
+        return noalloc_fail(MGL_PH_E_CUDA, "cudaGetSymbolAddress(static scratch)", e);
+    const HostTables<float> &tf = tables_f();
+    const HostTables<double> &td = tables_d();
+    if ((e = cudaMemcpy(s->tab_f, tf.ph2pr.data(), 128 * sizeof(float), cudaMemcpyHostToDevice)) != cudaSuccess ||
+        (e = cudaMemcpy(s->tab_f + 128, tf.mm.data(), MGLPH_MM_ENTRIES * sizeof(float), cudaMemcpyHostToDevice)) != cudaSuccess ||
+        (e = cudaMemcpy(s->tab_d, td.ph2pr.data(), 128 * sizeof(double), cudaMemcpyHostToDevice)) != cudaSuccess ||
+        (e = cudaMemcpy(s->tab_d + 128, td.mm.data(), MGLPH_MM_ENTRIES * sizeof(double), cudaMemcpyHostToDevice)) != cudaSuccess)
+        return noalloc_fail(MGL_PH_E_CUDA, "H2D tables", e);
+    g_noalloc_dev[device] = s;
+    return MGL_PH_OK;
+}
+
+static int noalloc_compute(int device, const int32_t *lengths, const uint8_t *reads, const uint8_t *haps, int use_double,
+                           double *out, cudaStream_t st, int flags)
+{
+    g_noalloc_err[0] = 0;
+    if (!lengths || !out) return noalloc_fail(MGL_PH_E_INVALID, "NULL lengths / out");
+    const int32_t R = lengths[0];
+    if (R < 0) return noalloc_fail(MGL_PH_E_INVALID, "negative read count");
+    if (R > MGL_PH_NOALLOC_MAX_READS) return noalloc_fail(MGL_PH_E_TOO_LARGE, "more reads than MGL_PH_NOALLOC_MAX_READS");
+    const int32_t H = lengths[1 + R];
+    if (H < 0) return noalloc_fail(MGL_PH_E_INVALID, "negative haplotype count");
+    if (H > MGL_PH_NOALLOC_MAX_HAPS) return noalloc_fail(MGL_PH_E_TOO_LARGE, "more haplotypes than MGL_PH_NOALLOC_MAX_HAPS");
+    if ((R > 0 && !reads) || (H > 0 && !haps)) return noalloc_fail(MGL_PH_E_INVALID, "NULL buffer");
+    const uint64_t np = (uint64_t)R * (uint64_t)H;
+    if (np > MGL_PH_NOALLOC_MAX_PAIRS) return noalloc_fail(MGL_PH_E_TOO_LARGE, "more pairs than MGL_PH_NOALLOC_MAX_PAIRS");
+    int max_rl = 0, max_hl = 0;
+    uint64_t sum_rl = 0, sum_hl = 0;
+    for (int32_t r = 0; r < R; r++) {
+        const int32_t n = lengths[1 + r];
+        if (n <= 0) return noalloc_fail(MGL_PH_E_INVALID, "empty read");
+        max_rl = n > max_rl ? n : max_rl; sum_rl += (uint64_t)n;
+        if (sum_rl > MGL_PH_NOALLOC_MAX_READ_BASES) return noalloc_fail(MGL_PH_E_TOO_LARGE, "more read bases than MGL_PH_NOALLOC_MAX_READ_BASES");
+    }
+    for (int32_t h = 0; h < H; h++) {
+        const int32_t n = lengths[2 + R + h];
+        if (n <= 0) return noalloc_fail(MGL_PH_E_INVALID, "empty haplotype");
+        max_hl = n > max_hl ? n : max_hl; sum_hl += (uint64_t)n;
+        if (sum_hl > MGL_PH_NOALLOC_MAX_HAP_BASES) return noalloc_fail(MGL_PH_E_TOO_LARGE, "more haplotype bases than MGL_PH_NOALLOC_MAX_HAP_BASES");
+    }
+    if (np == 0) return MGL_PH_OK;
+    const int carry_cols = max_rl > 256 ? max_hl + 1 : 0;
+    if (4 * (size_t)(carry_cols + 1) * sizeof(Top<double>) > 220 * 1024)
+        return noalloc_fail(MGL_PH_E_TOO_LONG, "haplotype too long for the carry row of reads longer than 256 bases");
+
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    cudaError_t e;
+    int n_dev = 0, prev = -1;
+    if (cudaGetDeviceCount(&n_dev) != cudaSuccess || device < 0 || device >= n_dev || device >= kNoAllocMaxDevices) {
+        cudaGetLastError();
+        return noalloc_fail(MGL_PH_E_NO_DEVICE, "no such CUDA device");
+    }
+    if ((e = cudaGetDevice(&prev)) != cudaSuccess || (e = cudaSetDevice(device)) != cudaSuccess) return noalloc_fail(MGL_PH_E_CUDA, "cudaSetDevice", e);
+    struct Restore { int d; ~Restore() { if (d >= 0) cudaSetDevice(d); } } restore{prev};
+    int rc = noalloc_setup(device);
+    if (rc != MGL_PH_OK) return rc;
+    NoAllocScratch *s = g_noalloc_dev[device];
+
+    if ((e = cudaMemcpyAsync(s->lengths, lengths, ((size_t)R + (size_t)H + 2) * sizeof(int32_t), cudaMemcpyDefault, st)) != cudaSuccess ||
+        (e = cudaMemcpyAsync(s->reads, reads, 5 * (size_t)sum_rl, cudaMemcpyDefault, st)) != cudaSuccess ||
+        (e = cudaMemcpyAsync(s->haps + MGLPH_HAP_PAD, haps, (size_t)sum_hl, cudaMemcpyDefault, st)) != cudaSuccess)
+        return noalloc_fail(MGL_PH_E_CUDA, "input copy", e);
+    ph_noalloc_offsets_kernel<<<1, 128, 0, st>>>(s, R, H);
+    if ((e = cudaGetLastError()) != cudaSuccess) return noalloc_fail(MGL_PH_E_CUDA, "offsets launch", e);
+
+    JobDev job;
+    job.reads = s->reads; job.haps = s->haps;
+    job.read_off = s->read_off; job.hap_off = s->hap_off;
+    job.read_list = s->read_list; job.R = R; job.H = H;
+    KArgs<double> ad;
+    ad.job = job; ad.tb.ph2pr = s->tab_d; ad.tb.mm = s->tab_d + 128; ad.tb.initial = tables_d().initial;
+    ad.log10_initial = tables_d().log10_initial; ad.out = s->out;
+    ad.redo = s->redo; ad.redo_count = s->redo_count; ad.carry_cols = carry_cols;
+    if (use_double) {
+        if ((e = launch_forward<double, false, false>(shape_g32(max_rl), (unsigned int)np, carry_cols, ad, st)) != cudaSuccess)
+            return noalloc_fail(MGL_PH_E_CUDA, "double launch", e);
+    } else {
+        KArgs<float> af;
+        af.job = job; af.tb.ph2pr = s->tab_f; af.tb.mm = s->tab_f + 128; af.tb.initial = tables_f().initial;
+        af.log10_initial = tables_f().log10_initial; af.out = s->out;
+        af.redo = s->redo; af.redo_count = s->redo_count; af.carry_cols = carry_cols;
+        /* the counter is the one thing that must start at zero: the array still holds the previous call's */
+        if ((e = cudaMemsetAsync(s->redo_count, 0, sizeof s->redo_count, st)) != cudaSuccess) return noalloc_fail(MGL_PH_E_CUDA, "memset", e);
+        if ((e = launch_forward<float, false, true>(shape_float(max_rl), (unsigned int)np, carry_cols, af, st)) != cudaSuccess)
+            return noalloc_fail(MGL_PH_E_CUDA, "float launch", e);
+        if ((e = launch_forward<double, true, false>(shape_g32(max_rl), (unsigned int)np, carry_cols, ad, st)) != cudaSuccess)
+            return noalloc_fail(MGL_PH_E_CUDA, "double launch", e);
+    }
+    if ((e = cudaMemcpyAsync(out, s->out, (size_t)np * sizeof(double), cudaMemcpyDefault, st)) != cudaSuccess)
+        return noalloc_fail(MGL_PH_E_CUDA, "output copy", e);
+    if (!(flags & MGL_PH_NOALLOC_NO_SYNC) && (e = cudaStreamSynchronize(st)) != cudaSuccess)
+        return noalloc_fail(MGL_PH_E_CUDA, "kernel execution", e);
+    return MGL_PH_OK;
+}
+
 }  // namespace mglph
 
 struct mgl_pairhmm_handle { mglph::Engine *engine; };
@@ -489,5 +655,15 @@ int mgl_pairhmm_resident_fetch(mgl_pairhmm_handle *h, double *out)
     std::lock_guard<std::mutex> lk(h->engine->mu);
     return h->engine->fetch(out, 1, st);
 }
+
+int mgl_pairhmm_compute_noalloc(int device, const int32_t *lengths, const uint8_t *reads, const uint8_t *haps,
+                                int use_double, double *out, void *stream, int flags)
+{
+    return mglph::noalloc_compute(device, lengths, reads, haps, use_double, out, (cudaStream_t)stream, flags);
+}
+
+uint64_t mgl_pairhmm_noalloc_scratch_bytes(void) { return sizeof(mglph::NoAllocScratch); }
+
+const char *mgl_pairhmm_noalloc_last_error(void) { return mglph::g_noalloc_err; }
 
 }  // extern "C"

@@ -11,7 +11,10 @@ from typing import Optional, Sequence
 import numpy as np
 
 LIB_PATH = os.environ.get("MGL_PAIRHMM_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "libmgl_pairhmm.so")
-OK, E_INVALID, E_NO_DEVICE, E_CUDA, E_TOO_LONG = 0, -1, -2, -3, -4
+OK, E_INVALID, E_NO_DEVICE, E_CUDA, E_TOO_LONG, E_TOO_LARGE = 0, -1, -2, -3, -4, -5
+NOALLOC_MAX_READS, NOALLOC_MAX_HAPS, NOALLOC_MAX_PAIRS = 4096, 1024, 65536       # include/mgl_pairhmm.h
+NOALLOC_MAX_READ_BASES = NOALLOC_MAX_HAP_BASES = 262144
+NOALLOC_NO_SYNC = 1
 _lib = None
 
 
@@ -43,6 +46,9 @@ def lib():
         L.mgl_pairhmm_resident_prepare.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.mgl_pairhmm_resident_run.argtypes = [C.c_void_p, C.c_int, C.POINTER(Stats)]
         L.mgl_pairhmm_resident_fetch.argtypes = [C.c_void_p, C.c_void_p]
+        L.mgl_pairhmm_compute_noalloc.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+        L.mgl_pairhmm_noalloc_scratch_bytes.restype = C.c_uint64
+        L.mgl_pairhmm_noalloc_last_error.restype = C.c_char_p
         _lib = L
     return _lib
 
@@ -74,6 +80,18 @@ def pack(reads: Sequence[ReadDataHolder], haps: Sequence[HaplotypeDataHolder]):
         if reads else np.zeros(0, np.uint8)
     hb = np.frombuffer(b"".join(h.haplotypeBases for h in haps), dtype=np.uint8).copy() if haps else np.zeros(0, np.uint8)
     return lengths, rb, hb
+
+
+def compute_noalloc(lengths: np.ndarray, reads, haps, out, use_double: bool = False, device: int = 0, stream: int = 0, flags: int = 0):
+    """mgl_pairhmm_compute_noalloc (no counterpart in the reference): the job out of the library's static device
+    array, no handle and no allocation.  `lengths` is a host int32 array; `reads`, `haps`, `out` are numpy arrays or
+    integer addresses (device or host pointers); `stream` is a cudaStream_t as an integer, 0 = the default stream."""
+    def addr(x):
+        return x.ctypes.data if isinstance(x, np.ndarray) else int(x)
+    rc = lib().mgl_pairhmm_compute_noalloc(device, lengths.ctypes.data, addr(reads), addr(haps), int(bool(use_double)), addr(out), stream or None, flags)
+    if rc != OK:
+        raise MglPairHmmError(rc, lib().mgl_pairhmm_noalloc_last_error().decode(errors="replace"))
+    return out
 
 
 class MicrosoftPairHmm:
