@@ -88,6 +88,7 @@ void ChunkDev::release()
 void WorkSlot::release()
 {
     ckpt.release(); carry.release(); lastrow.release(); colbest.release(); scratch.release();
+    startcell.release(); worklist.release();
     offsets.release(); n_ops.release(); starts.release(); tiles.release(); ops.release(); score3.release(); n_chars.release();
     h_n_ops.release(); h_total.release();
     if (ev_counts) cudaEventDestroy(ev_counts);
@@ -557,6 +558,8 @@ int Engine::ensure_slot(WorkSlot &ws, const ChunkPlan &plan, u32 n, bool score_o
     if ((e = ws.tiles.reserve(((size_t)n / 1024 + 2) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc");
     if ((e = ws.ops.reserve((plan.scratch_words + 1) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc ops");
     if ((e = ws.h_n_ops.reserve(((size_t)n + 1) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "pinned alloc");
+    if ((e = ws.startcell.reserve(((size_t)plan.n_units * 2 + 1) * sizeof(int4))) != cudaSuccess) return cuda_fail(e, "cudaMalloc");
+    if ((e = ws.worklist.reserve(((size_t)plan.n_units * 2 + 4) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc");
     return MGL_SW_OK;
 }
 
@@ -623,6 +626,9 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed, bo
     t.n_ops = (u32 *)ws.n_ops.p;
     t.n_units = cd.plan.n_units;
     t.score3 = (int *)ws.score3.p;
+    t.work_count = (u32 *)ws.worklist.p;
+    t.worklist = (u32 *)ws.worklist.p + 4;
+    t.startcell = (int4 *)ws.startcell.p;
     if (score_only) {
         if ((e = launch_endpoints(t, pt)) != cudaSuccess) return cuda_fail(e, "endpoint launch");
         if ((e = cudaEventRecord(ws.ev_post, pt)) != cudaSuccess) return cuda_fail(e, "event record");
@@ -634,6 +640,7 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed, bo
         bs.pairs_s32 += cd.plan.pairs_s32;
         return MGL_SW_OK;
     }
+    if ((e = launch_start(t, pt)) != cudaSuccess) return cuda_fail(e, "start-cell launch");
     if ((e = launch_traceback(t, pt)) != cudaSuccess) return cuda_fail(e, "traceback launch");
     if (exact_shortcut) {
         if ((e = launch_exact_match(t, pt)) != cudaSuccess) return cuda_fail(e, "exact-match launch");
@@ -655,7 +662,7 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed, bo
     }
     if (timed) cudaEventRecord(tev_[4], pt);
     if ((e = cudaEventRecord(ws.ev_post, pt)) != cudaSuccess) return cuda_fail(e, "event record");
-    bs.other_launches += 4;
+    bs.other_launches += 5;
     bs.chunks++;
     bs.cells += cd.plan.cells;
     bs.pairs += cd.n;

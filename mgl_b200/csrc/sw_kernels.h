@@ -27,12 +27,22 @@ struct TraceArgs {
     u32 *n_ops;               /* out, per pair                                  */
     int *score3;              /* out, score-only runs: per pair {score, end_ref, end_alt} */
     u32 n_units;              /* units of the chunk (padding units included)    */
+    /* launch_start -> launch_traceback: the pairs whose path has a gap, in the order the start kernel found them */
+    u32 *work_count;          /* one word, zeroed by launch_start                */
+    u32 *worklist;            /* 2 * n_units: pair slot (2 * unit + half) of entry k */
+    int4 *startcell;          /* 2 * n_units: {i, j, seg, score} of entry k (StartCell, sw_trace.h) */
 };
+/*
+ * The traceback's start cell of every pair (sw.cpp:116-127,155-170), found by a group of 8 lanes per pair reading the
+ * captured last row together; a pair whose whole path is one diagonal (sw_trace.h clean_path) gets its result written
+ * here, the others are appended to the worklist launch_traceback walks.  Must precede launch_traceback on the stream.
+ */
+cudaError_t launch_start(const TraceArgs &a, cudaStream_t stream);
 cudaError_t launch_traceback(const TraceArgs &a, cudaStream_t stream);
 /* opt-in: SOFTCLIP / IGNORE pairs whose alt occurs verbatim in the ref take GATK's wrapper answer (last occurrence, all M);
    runs after launch_traceback on the same stream and overwrites offsets / n_ops / scratch of those pairs */
 cudaError_t launch_exact_match(const TraceArgs &a, cudaStream_t stream);
-/* score-only runs: the traceback's start cell (sw.cpp:155-170) and its H, nothing else (needs units, strategy, c16, c32, colbest, lastrow, score3) */
+/* score-only runs: the traceback's start cell (sw.cpp:155-170) and its H, nothing else, by the same lane groups (needs units, strategy, c16, c32, colbest, lastrow, score3) */
 cudaError_t launch_endpoints(const TraceArgs &a, cudaStream_t stream);
 
 /* two-level exclusive scan of n_ops: starts[p] = offset inside p's tile of 1024 pairs, tile_sum[t] = offset of tile t,

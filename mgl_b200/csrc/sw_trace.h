@@ -66,7 +66,6 @@ SW_HD W2 load_w2(const u32 *p)
  * 4-bit record per cell.  A block never extends below / right of the cell that asked for
  * it: the traceback only moves up and left.
  */
-template <class T>
 struct Replay {
     /* the unit's geometry, copied out of its descriptor once */
     const u32 *base;                     /* checkpoint regions of the warp, at this unit's lane group */
@@ -74,15 +73,17 @@ struct Replay {
     u32 G, K, KM, SC, LSW, RW, half, rbc; /* SC = sec_chunks(K), LSW / RW = words per lane slice / per region, rbc = row blocks per strip */
     u32 cb, cr;                          /* col_base, col_rem */
     int match, mismatch, go, ge, bias, indel;
+    u32 sh, msk;                         /* this pair's half of a checkpoint word: bits [sh, sh + 16) of a u16x2 unit, the whole word of an s32 unit */
     int ia, ib, ja, jb;
     u64 *nib;                            /* row i - ia at nib[(i - ia) * nstride]: nibble of column j at bits 4 (j - ja); */
     u32 nstride;                         /* shared memory on the device (one column per thread), a plain array in the emulator */
     u32 builds, cells;                   /* statistics */
 
-    SW_HD void init(const UnitDesc &u, u32 G_, u32 K_, u32 half_, const u32 *ckpt, const uint8_t *arena, const CellConsts &c,
+    SW_HD void init(const UnitDesc &u, u32 G_, u32 K_, u32 half_, bool s32, const u32 *ckpt, const uint8_t *arena, const CellConsts &c,
                     u64 *nib_, u32 nstride_)
     {
         nib = nib_; nstride = nstride_;
+        sh = s32 ? 0u : 16u * half_; msk = s32 ? 0xffffffffu : 0xffffu;
         G = G_; K = K_; KM = regs_mid(K_); SC = sec_chunks(K_); half = half_; rbc = u.rb_count;
         cb = u.col_base; cr = u.col_rem;
         LSW = lane_stride16(K_) * 4u; RW = region_words(K_);
@@ -94,8 +95,8 @@ struct Replay {
     }
 
     SW_HD int bnd(int x) const { return boundary_score(x, indel, go, ge); }
-    SW_HD int hval(u32 w) const { return T::half(w, (int)half) - bias - match; }   /* stored H + match + bias -> H */
-    SW_HD int gval(u32 w) const { return T::half(w, (int)half) - bias; }           /* stored E / F + bias      */
+    SW_HD int hval(u32 w) const { return (int)((w >> sh) & msk) - bias - match; }   /* stored H + match + bias -> H */
+    SW_HD int gval(u32 w) const { return (int)((w >> sh) & msk) - bias; }           /* stored E / F + bias      */
 
     /* H on the boundary of the block built last: entry r = H[ia - 1 + r][ja - 1], entry MGLSW_RB + 1 + kk = H[ia - 1][ja + kk] */
     SW_HD void put_h(u32 idx, int v) { reinterpret_cast<u32 *>(nib + (size_t)(MGLSW_RB + idx / 2u) * nstride)[idx & 1u] = (u32)v; }
@@ -359,12 +360,63 @@ SW_HD StartCell select_start(const UnitDesc &u, u32 half, u32 G, u32 K, const u3
  * ops_end points one past the pair's scratch region; elements are written
  * downwards so that [ops_end - n_ops, ops_end) reads left to right.
  */
-template <class T>
-SW_HD PairResult traceback_pair(const UnitDesc &u, u32 half, u32 G, u32 K, const u32 *ckpt, const uint8_t *arena,
-                                const CellConsts &c, const u32 *colbest4, const u32 *lastrow, int strategy, u32 *ops_end,
-                                u64 *nib, u32 nstride)
+/* the end of the walk at (I, J) with I == 0 or J == 0: overhang post-processing and offset, sw.cpp:224-248 */
+SW_HD u32 *finish_walk(int strategy, u32 state, int run, int I, int J, u32 *p, int &offset)
 {
-    const StartCell st = select_start<T>(u, half, G, K, colbest4, lastrow, strategy);
+#define SW_EMIT(op, len) do { if ((len) > 0) *--p = ((u32)(len) << 4) | (u32)(op); } while (0)
+    if (strategy == OS_SOFTCLIP) {                                              /* sw.cpp:225-229 */
+        SW_EMIT(state, run);
+        SW_EMIT(OP_S, J);
+        offset = I;
+    } else if (strategy == OS_IGNORE) {                                         /* sw.cpp:230-233 */
+        SW_EMIT(state, run + J);
+        offset = I - J;
+    } else {                                                                    /* sw.cpp:234-248 */
+        SW_EMIT(state, run);
+        if (I > 0) SW_EMIT(OP_D, I);
+        else if (J > 0) SW_EMIT(OP_I, J);
+        offset = 0;
+    }
+#undef SW_EMIT
+    return p;
+}
+
+/*
+ * The whole path as ONE diagonal hop (Replay::hop with L = min(I, J)): from the start cell (I, J) with H known (the
+ * score that selected it) to row 0 or column 0, where H is the boundary score (sw.cpp:29-35, :47-49).
+ * H[I][J] - H[I-L][J-L] == the sum of the L substitution scores holds iff every cell on the way is a diagonal step
+ * of the reference's traceback (the argument above Replay::hop), i.e. iff the alignment has no gap at all -- then the
+ * CIGAR is known without reading a single checkpoint.  `nm` = mismatches among ref[I-L .. I) vs alt[J-L .. J),
+ * counted by the caller (a loop here in the emulator, a lane group in sw_start_kernel).  Returns false, writing
+ * nothing, when the path has a gap: the pair then goes through traceback_pair.
+ */
+SW_HD bool clean_path(const StartCell &st, int strategy, const CellConsts &c, int indel, int nm, u32 *ops_end, PairResult &res)
+{
+    const int L = st.i < st.j ? st.i : st.j;
+    const int it = st.i - L, jt = st.j - L;
+    const int ht = boundary_score(it == 0 ? jt : it, indel, c.s_go, c.s_ge);
+    const int hcur = st.score - c.bias - c.s_match;
+    if (hcur - ht != L * c.s_match - nm * (c.s_match - c.s_mismatch)) return false;
+    u32 *p = ops_end;
+    int run = st.seg;
+    if (run > 0 && strategy == OS_SOFTCLIP) { *--p = ((u32)run << 4) | (u32)OP_S; run = 0; }   /* sw.cpp:173-176 */
+    p = finish_walk(strategy, OP_M, run + L, it, jt, p, res.offset);
+    res.n_ops = (u32)(ops_end - p);
+    res.score = st.score;
+    res.builds = 0; res.hops = 1;
+    return true;
+}
+
+/*
+ * On the device ALL 32 lanes of a warp call this together (`live` false for a lane without a pair): once per round the
+ * warp meets at a vote, so that the lanes that need a block rebuilt run the one replay site together.  Left to the
+ * hardware's reconvergence the lanes drifted apart -- the replay ran 19 times per warp with 4 lanes each where the
+ * slowest pair needs 8 [B200, profiles/r19a].
+ */
+SW_HD PairResult traceback_pair(const UnitDesc &u, u32 half, bool s32, u32 G, u32 K, const u32 *ckpt, const uint8_t *arena,
+                                const CellConsts &c, const StartCell &st, int strategy, u32 *ops_end,
+                                u64 *nib, u32 nstride, bool live = true)
+{
     int I = st.i, J = st.j, run = st.seg;
     const int start_score = st.score;
 
@@ -373,8 +425,8 @@ SW_HD PairResult traceback_pair(const UnitDesc &u, u32 half, u32 G, u32 K, const
 
     if (run > 0 && strategy == OS_SOFTCLIP) { SW_EMIT(OP_S, run); run = 0; }   /* sw.cpp:173-176 */
 
-    Replay<T> rp;
-    rp.init(u, G, K, half, ckpt, arena, c, nib, nstride);
+    Replay rp;
+    rp.init(u, G, K, half, s32, ckpt, arena, c, nib, nstride);
 
     /*
      * The walk of sw.cpp:182-214 as a state machine around ONE replay site, so that the 32 pairs
@@ -385,12 +437,12 @@ SW_HD PairResult traceback_pair(const UnitDesc &u, u32 half, u32 G, u32 K, const
      */
     u32 state = OP_M, next = OP_M;
     int mode = 0, steplen = 1, cc = 0, r = 0;
-    bool done = false;
+    bool done = !live;
     /* H at (I, J), when known: at the start cell (the score that selected it) and on checkpointed cells */
     int hcur = start_score - c.bias - c.s_match;
     u32 hops = 0;
     bool hk = true;
-    while (!done) {
+    for (;;) {
         /*
          * Phase A: while H is known, try to cross the block with one diagonal hop (Replay::hop).  A
          * clean stretch of the alignment costs one load and <= 12 byte compares per block; threads of
@@ -405,7 +457,12 @@ SW_HD PairResult traceback_pair(const UnitDesc &u, u32 half, u32 G, u32 K, const
             I -= L; J -= L; hcur = hn; hops++;
             if (!(I > 0 && J > 0)) done = true;
         }
+#if SW_ON_DEVICE
+        if (__ballot_sync(0xffffffffu, !done) == 0u) break;       /* the warp's meeting point; leaves when every lane is done */
+        if (done) continue;
+#else
         if (done) break;
+#endif
         /* Phase B: recompute the block around the current cell and walk inside it */
         rp.build(mode == 2 ? r : I, mode == 1 ? cc : J);
         for (;;) {
@@ -436,21 +493,10 @@ SW_HD PairResult traceback_pair(const UnitDesc &u, u32 half, u32 G, u32 K, const
         hk = !done && mode == 0 && rp.boundary_h(I, J, hcur);
     }
 
-    PairResult res;
-    if (strategy == OS_SOFTCLIP) {                                              /* sw.cpp:225-229 */
-        SW_EMIT(state, run);
-        SW_EMIT(OP_S, J);
-        res.offset = I;
-    } else if (strategy == OS_IGNORE) {                                         /* sw.cpp:230-233 */
-        SW_EMIT(state, run + J);
-        res.offset = I - J;
-    } else {                                                                    /* sw.cpp:234-248 */
-        SW_EMIT(state, run);
-        if (I > 0) SW_EMIT(OP_D, I);
-        else if (J > 0) SW_EMIT(OP_I, J);
-        res.offset = 0;
-    }
 #undef SW_EMIT
+    PairResult res;
+    if (!live) { res.offset = 0; res.n_ops = 0; res.score = 0; res.builds = res.hops = 0; return res; }   /* wrote nothing */
+    p = finish_walk(strategy, state, run, I, J, p, res.offset);
     res.n_ops = (u32)(ops_end - p);
     res.score = start_score;
     res.builds = rp.builds; res.hops = hops;

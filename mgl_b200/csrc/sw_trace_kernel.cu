@@ -1,6 +1,6 @@
 /*
- * sw_trace_kernel.cu -- endpoint scan + checkpoint replay + traceback (one thread per pair), and
- * the two small kernels that turn per-pair CIGAR scratch into one dense array.
+ * sw_trace_kernel.cu -- start cells (a lane group per pair; gap-free paths end there), checkpoint replay + traceback of
+ * the others (one thread per pair), and the two small kernels that turn per-pair CIGAR scratch into one dense array.
  * Replaces calculateCigar / calculateCigar_avx (sw.cpp:149-255, sw_avx.cpp:324-430).
  */
 #include "sw_kernels.h"
@@ -10,8 +10,126 @@
 namespace mglsw {
 
 /*
- * Thread 2 v + h handles half h of unit v: the threads of a warp walk pairs of one shape bucket
- * whose checkpoints sit next to each other, instead of 32 unrelated pairs in input order.
+ * The start cell of one pair (select_start, sw_trace.h: sw.cpp:116-127 and :155-170) by a group of 8 lanes: lane g reads
+ * words g, g + 8, ... of the captured last row -- coalesced, all in flight together, where one thread per pair walked
+ * them one dependent load at a time.  The scan keeps the FIRST of the candidates with the best (score, distance to the
+ * diagonal) in its order -- last-column maximum first, then the last row by ascending column (it replaces only on a
+ * strict improvement) -- so the lanes keep (score, distance, column) and the reduction prefers the smaller column among
+ * equals; the last-column maximum wins every tie.  The same value in all 8 lanes.
+ */
+__device__ __forceinline__ StartCell start_cell_group(const UnitDesc &u, u32 half, bool s32, u32 G, u32 K, const u32 *colbest4,
+                                                      const u32 *lastrow, int strategy, u32 gl, unsigned gmask)
+{
+    const int tl = (int)u.tl[half], ql = (int)u.ql;
+    const u32 nslots = u.nstrips * G;
+    const u32 *row = lastrow + u.lastrow_off + (size_t)half * nslots * K;
+    const u32 sh = s32 ? 0u : 16u * half, msk = s32 ? 0xffffffffu : 0xffffu;
+    const int mqe = (int)__ldcg(colbest4 + 2 * half), mqe_t = (int)__ldcg(colbest4 + 2 * half + 1);
+    StartCell sc;
+    if (strategy == OS_INDEL) {
+        u32 slot, reg;
+        col_to_slot(u, (u32)ql - 1u, slot, reg);
+        sc.i = tl; sc.j = ql; sc.seg = 0; sc.score = (int)((__ldcg(row + (size_t)slot * K + reg) >> sh) & msk);
+    } else if (strategy == OS_LEADING_INDEL) {
+        sc.i = mqe_t; sc.j = ql; sc.seg = 0; sc.score = mqe;
+    } else {
+        int best = (int)0x80000000, bd = 0x7fffffff, bj = 0x7fffffff;
+        const u32 W = nslots * K;
+        u32 slot = gl / K, reg = gl - slot * K;
+        for (u32 w0 = gl; w0 < W; w0 += 32u) {
+            u32 v[4];
+#pragma unroll
+            for (int q = 0; q < 4; q++) v[q] = w0 + 8u * q < W ? __ldcg(row + w0 + 8u * q) : 0u;
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                if (w0 + 8u * q < W && reg < slot_cols(u, slot)) {
+                    const int j = (int)slot_first_col(u, slot) + (int)reg + 1;
+                    const int s = (int)((v[q] >> sh) & msk);
+                    const int da = tl - j < 0 ? j - tl : tl - j;
+                    if (s > best || (s == best && da < bd)) { best = s; bd = da; bj = j; }
+                }
+                reg += 8u;
+                while (reg >= K) { reg -= K; slot++; }
+            }
+        }
+#pragma unroll
+        for (int m = 1; m < 8; m <<= 1) {
+            const int os = __shfl_xor_sync(gmask, best, m), od = __shfl_xor_sync(gmask, bd, m), oj = __shfl_xor_sync(gmask, bj, m);
+            if (os > best || (os == best && (od < bd || (od == bd && oj < bj)))) { best = os; bd = od; bj = oj; }
+        }
+        const int db0 = mqe_t - ql < 0 ? ql - mqe_t : mqe_t - ql;
+        if (best > mqe || (best == mqe && bd < db0)) { sc.i = tl; sc.j = bj; sc.seg = ql - bj; sc.score = best; }
+        else { sc.i = mqe_t; sc.j = ql; sc.seg = 0; sc.score = mqe; }
+    }
+    return sc;
+}
+
+/*
+ * 8 lanes per pair slot (2 v + h = half h of unit v).  SCORE_ONLY: the start cell and its H are the result
+ * (mgl_sw_score_batch).  Otherwise the group also counts the mismatches along the diagonal from the start cell to row 0 /
+ * column 0: if the scores say that the whole path is that diagonal (clean_path) lane 0 writes the pair's CIGAR and
+ * offset and the pair is done -- no checkpoint is read; else the pair joins the worklist of sw_traceback_kernel.
+ */
+template <bool SCORE_ONLY>
+__global__ void __launch_bounds__(128) sw_start_kernel(const __grid_constant__ TraceArgs a)
+{
+    const u32 sid = (blockIdx.x * 128u + threadIdx.x) >> 3;
+    const u32 gl = threadIdx.x & 7u;
+    const unsigned gmask = 0xffu << (threadIdx.x & 24u);
+    bool push = false;
+    StartCell sc;
+    sc.i = sc.j = sc.seg = sc.score = 0;
+    if (sid < 2u * a.n_units) {
+        const UnitDesc &u = a.units[sid >> 1];
+        const u32 half = sid & 1u;
+        const u32 p = u.pair[half];
+        if ((u.flags & UNIT_ACTIVE) && p != NO_PAIR) {
+            const bool s32 = (u.flags & UNIT_S32) != 0;
+            const u32 G = (u.flags & UNIT_G32) ? MGLSW_G_LONG : MGLSW_G_SHORT;
+            const CellConsts &c = s32 ? a.c32 : a.c16;
+            const int strategy = a.strategy[p];
+            sc = start_cell_group(u, half, s32, G, u.regs, a.colbest + (size_t)(sid >> 1) * 4u, a.lastrow, strategy, gl, gmask);
+            if (SCORE_ONLY) {
+                if (gl == 0) {
+                    a.score3[3 * (size_t)p] = sc.score - c.bias - c.s_match;
+                    a.score3[3 * (size_t)p + 1] = sc.i;
+                    a.score3[3 * (size_t)p + 2] = sc.j;
+                }
+            } else {
+                const int L = sc.i < sc.j ? sc.i : sc.j;
+                const uint8_t *rf = a.arena + u.ref_off[half] + (sc.i - L), *al = a.arena + u.alt_off[half] + (sc.j - L);
+                int nm = 0;
+                for (int t = (int)gl; t < L; t += 8) nm += __ldg(rf + t) != __ldg(al + t) ? 1 : 0;
+#pragma unroll
+                for (int m = 1; m < 8; m <<= 1) nm += __shfl_xor_sync(gmask, nm, m);
+                if (gl == 0) {
+                    PairResult r;
+                    if (clean_path(sc, strategy, c, (u.flags & UNIT_INDEL) ? 1 : 0, nm, a.scratch + a.ops_end[p], r)) {
+                        a.offsets[p] = r.offset;
+                        a.n_ops[p] = r.n_ops;
+                    } else push = true;
+                }
+            }
+        }
+    }
+    if (SCORE_ONLY) return;
+    /* one atomic per warp: its (at most four) pairs take consecutive worklist entries */
+    const unsigned pm = __ballot_sync(0xffffffffu, push);
+    if (pm == 0u) return;
+    const u32 wl = threadIdx.x & 31u;
+    u32 base = 0;
+    if (wl == (u32)(__ffs(pm) - 1)) base = atomicAdd(a.work_count, (u32)__popc(pm));
+    base = __shfl_sync(0xffffffffu, base, __ffs(pm) - 1);
+    if (push) {
+        const u32 k = base + (u32)__popc(pm & ((1u << wl) - 1u));
+        a.worklist[k] = sid;
+        a.startcell[k] = make_int4(sc.i, sc.j, sc.seg, sc.score);
+    }
+}
+
+/*
+ * One thread per worklist entry: the pairs whose path has a gap, consecutive entries = neighbouring pair slots of one
+ * shape bucket, whose checkpoints sit next to each other.
  */
 #ifndef MGLSW_TRACE_MINB
 #define MGLSW_TRACE_MINB 4
@@ -19,43 +137,25 @@ namespace mglsw {
 __global__ void __launch_bounds__(128, MGLSW_TRACE_MINB) sw_traceback_kernel(const __grid_constant__ TraceArgs a)
 {
     __shared__ u64 s_nib[MGLSW_TRACE_BUF * 128];   /* the replayed block: records and boundary H values, one column per thread */
-    const u32 tid = blockIdx.x * blockDim.x + threadIdx.x;
-    if (tid >= 2u * a.n_units) return;
-    const UnitDesc &u = a.units[tid >> 1];
-    const u32 half = tid & 1u;
-    const u32 p = u.pair[half];
-    if (!(u.flags & UNIT_ACTIVE) || p == NO_PAIR) return;
+    const u32 k = blockIdx.x * blockDim.x + threadIdx.x;
+    const u32 count = __ldcg(a.work_count);
+    if ((k & ~31u) >= count) return;                /* whole warps leave; a lane past the end stays with its warp, idle */
+    const bool live = k < count;
+    const u32 sid = live ? a.worklist[k] : 0u;
+    StartCell sc;
+    sc.i = sc.j = 1; sc.seg = 0; sc.score = 0;
+    if (live) { const int4 s4 = a.startcell[k]; sc.i = s4.x; sc.j = s4.y; sc.seg = s4.z; sc.score = s4.w; }
+    const UnitDesc &u = a.units[sid >> 1];
+    const u32 half = sid & 1u;
+    const u32 p = live ? u.pair[half] : 0u;
+    const bool s32 = (u.flags & UNIT_S32) != 0;
     const u32 G = (u.flags & UNIT_G32) ? MGLSW_G_LONG : MGLSW_G_SHORT;
     u32 *end = a.scratch + a.ops_end[p];
-    const u32 *cb = a.colbest + (size_t)(tid >> 1) * 4u;
-    PairResult r;
-    if (u.flags & UNIT_S32) r = traceback_pair<S32>(u, half, G, u.regs, a.ckpt, a.arena, a.c32, cb, a.lastrow, a.strategy[p], end, s_nib + threadIdx.x, 128u);
-    else                    r = traceback_pair<S16x2>(u, half, G, u.regs, a.ckpt, a.arena, a.c16, cb, a.lastrow, a.strategy[p], end, s_nib + threadIdx.x, 128u);
+    const PairResult r = traceback_pair(u, half, s32, G, u.regs, a.ckpt, a.arena, s32 ? a.c32 : a.c16, sc, a.strategy[p], end,
+                                        s_nib + threadIdx.x, 128u, live);
+    if (!live) return;
     a.offsets[p] = r.offset;
     a.n_ops[p] = r.n_ops;
-}
-
-/*
- * Score-only runs: no traceback, only the cell it would start from (sw.cpp:155-170: the corner, the
- * last-column maximum, or the better of last column and last row, by strategy) and the score there.
- */
-__global__ void __launch_bounds__(128) sw_endpoint_kernel(const __grid_constant__ TraceArgs a)
-{
-    const u32 tid = blockIdx.x * blockDim.x + threadIdx.x;
-    if (tid >= 2u * a.n_units) return;
-    const UnitDesc &u = a.units[tid >> 1];
-    const u32 half = tid & 1u;
-    const u32 p = u.pair[half];
-    if (!(u.flags & UNIT_ACTIVE) || p == NO_PAIR) return;
-    const u32 G = (u.flags & UNIT_G32) ? MGLSW_G_LONG : MGLSW_G_SHORT;
-    const u32 *cb = a.colbest + (size_t)(tid >> 1) * 4u;
-    StartCell st;
-    int h;
-    if (u.flags & UNIT_S32) { st = select_start<S32>(u, half, G, u.regs, cb, a.lastrow, a.strategy[p]); h = st.score - a.c32.bias - a.c32.s_match; }
-    else                    { st = select_start<S16x2>(u, half, G, u.regs, cb, a.lastrow, a.strategy[p]); h = st.score - a.c16.bias - a.c16.s_match; }
-    a.score3[3 * (size_t)p] = h;
-    a.score3[3 * (size_t)p + 1] = st.i;
-    a.score3[3 * (size_t)p + 2] = st.j;
 }
 
 /*
@@ -112,13 +212,23 @@ cudaError_t launch_exact_match(const TraceArgs &a, cudaStream_t stream)
 cudaError_t launch_endpoints(const TraceArgs &a, cudaStream_t stream)
 {
     if (a.n_units == 0) return cudaSuccess;
-    sw_endpoint_kernel<<<(2u * a.n_units + 127) / 128, 128, 0, stream>>>(a);
+    sw_start_kernel<true><<<(2u * a.n_units * 8u + 127) / 128, 128, 0, stream>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_start(const TraceArgs &a, cudaStream_t stream)
+{
+    if (a.n_units == 0) return cudaSuccess;
+    cudaError_t e = cudaMemsetAsync(a.work_count, 0, sizeof(u32), stream);
+    if (e != cudaSuccess) return e;
+    sw_start_kernel<false><<<(2u * a.n_units * 8u + 127) / 128, 128, 0, stream>>>(a);
     return cudaGetLastError();
 }
 
 cudaError_t launch_traceback(const TraceArgs &a, cudaStream_t stream)
 {
     if (a.n_units == 0) return cudaSuccess;
+    /* the worklist's length is on the device: the grid covers every pair slot, blocks beyond the list leave at once */
     sw_traceback_kernel<<<(2u * a.n_units + 127) / 128, 128, 0, stream>>>(a);
     return cudaGetLastError();
 }

@@ -28,6 +28,7 @@ using namespace mglsw;
 namespace {
 
 int g_device_plan = 0;
+int g_clean_shortcut = 1;      /* the whole-path shortcut of sw_start_kernel (sw_trace.h clean_path); 0: every pair is walked */
 
 /*
  * The device planner (sw_plan_dev.h) on the CPU: the same stage bodies the CUDA kernels of sw_plan_dev.cu run, one
@@ -147,6 +148,7 @@ extern "C" {
 
 /* 1: plan with the device planner's stage bodies (sw_plan_dev.h) instead of the host planner (sw_plan.cpp) */
 void emu_use_device_plan(int on) { g_device_plan = on; }
+void emu_use_clean_shortcut(int on) { g_clean_shortcut = on; }
 
 /*
  * Both planners on one chunk: sizes and bucket structure must agree exactly (the unit arrays may differ in the
@@ -186,7 +188,8 @@ int emu_compare_planners(int n, const uint64_t *ref_off, const uint32_t *ref_len
 /*
  * Align a batch through planner + emulated kernels.  ops_out: per pair a
  * region of ops_stride words, elements left to right.  Returns 0, or a
- * negative code.  stats (optional, 6 words): launches, s16 pairs, s32 pairs, units, blocks replayed, diagonal hops.
+ * negative code.  stats (optional, 7 words): launches, s16 pairs, s32 pairs, units, blocks replayed, diagonal hops,
+ * pairs written down by the whole-path shortcut.
  */
 int emu_align_batch(int n, const uint8_t *arena, const uint64_t *ref_off, const uint32_t *ref_len,
                     const uint64_t *alt_off, const uint32_t *alt_len, const int32_t *strategies,
@@ -224,7 +227,7 @@ int emu_align_batch(int n, const uint8_t *arena, const uint64_t *ref_off, const 
     std::vector<u32> scratch(plan.scratch_words + 1, 0);
 
     u32 n16 = 0, n32 = 0;
-    if (stats) stats[4] = stats[5] = 0;
+    if (stats) stats[4] = stats[5] = stats[6] = 0;
     for (const Launch &L : plan.launches) {
         FillArgs a;
         a.arena = arena; a.units = plan.units.data(); a.ckpt = ckpt.data();
@@ -239,8 +242,25 @@ int emu_align_batch(int n, const uint8_t *arena, const uint64_t *ref_off, const 
         PairResult r;
         u64 nibbuf[MGLSW_TRACE_BUF];
         u32 *end = scratch.data() + plan.ops_end[p];
-        if (u.flags & UNIT_S32) { r = traceback_pair<S32>(u, half, G, u.regs, ckpt.data(), arena, make_consts<S32>(s, 0), colbest.data() + (size_t)(plan.pair_unit[p] >> 1) * 4, lastrow.data(), strategies[p], end, nibbuf, 1u); n32++; }
-        else { r = traceback_pair<S16x2>(u, half, G, u.regs, ckpt.data(), arena, make_consts<S16x2>(s, plan.s16_bias), colbest.data() + (size_t)(plan.pair_unit[p] >> 1) * 4, lastrow.data(), strategies[p], end, nibbuf, 1u); n16++; }
+        const bool s32 = (u.flags & UNIT_S32) != 0;
+        const CellConsts cc = s32 ? make_consts<S32>(s, 0) : make_consts<S16x2>(s, plan.s16_bias);
+        const u32 *cb4 = colbest.data() + (size_t)(plan.pair_unit[p] >> 1) * 4;
+        const StartCell sc = s32 ? select_start<S32>(u, half, G, u.regs, cb4, lastrow.data(), strategies[p])
+                                 : select_start<S16x2>(u, half, G, u.regs, cb4, lastrow.data(), strategies[p]);
+        if (s32) n32++; else n16++;
+        /* what sw_start_kernel does on the device: a path without a gap is written down at once (sw_trace.h clean_path) */
+        bool clean = false;
+        if (g_clean_shortcut) {
+            const int L = sc.i < sc.j ? sc.i : sc.j;
+            const uint8_t *rf = arena + u.ref_off[half] + (sc.i - L), *al = arena + u.alt_off[half] + (sc.j - L);
+            int nm = 0;
+            for (int t = 0; t < L; t++) nm += rf[t] != al[t] ? 1 : 0;
+            clean = clean_path(sc, strategies[p], cc, (u.flags & UNIT_INDEL) ? 1 : 0, nm, end, r);
+            if (clean && stats) stats[6]++;
+        }
+        if (!clean) {
+            r = traceback_pair(u, half, s32, G, u.regs, ckpt.data(), arena, cc, sc, strategies[p], end, nibbuf, 1u);
+        }
         if (stats) { stats[4] += r.builds; stats[5] += r.hops; }
         if (const char *dump = std::getenv("EMU_DUMP")) {        /* developer aid: per-pair replay / hop counts in thread order */
             static FILE *fp = nullptr;

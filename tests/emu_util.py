@@ -48,11 +48,12 @@ def pack_batch(pairs):
     return arena, offs[0::2].copy(), ref_len, offs[1::2].copy(), alt_len
 
 
-def emu_align(pairs, params, strategies, allow_s16=True, device_plan=False):
+def emu_align(pairs, params, strategies, allow_s16=True, device_plan=False, clean_shortcut=True):
     """-> list of (cigar text, offset), plus stats dict.  device_plan: the chunk is planned by the device planner's
     stage bodies (mgl_b200/csrc/sw_plan_dev.h) instead of the host planner (sw_plan.cpp)."""
     lib = _load()
     lib.emu_use_device_plan(1 if device_plan else 0)
+    lib.emu_use_clean_shortcut(1 if clean_shortcut else 0)
     n = len(pairs)
     arena, ro, rl, ao, al = pack_batch(pairs)
     st = np.asarray(strategies, dtype=np.int32)
@@ -62,7 +63,7 @@ def emu_align(pairs, params, strategies, allow_s16=True, device_plan=False):
     offsets = np.zeros(n, dtype=np.int32)
     n_ops = np.zeros(n, dtype=np.uint32)
     ops = np.zeros(n * stride, dtype=np.uint32)
-    stats = np.zeros(6, dtype=np.uint32)
+    stats = np.zeros(7, dtype=np.uint32)
     rc = lib.emu_align_batch(n, arena.ctypes.data, ro.ctypes.data, rl.ctypes.data, ao.ctypes.data, al.ctypes.data,
                              st.ctypes.data, params[0], params[1], params[2], params[3], 1 if allow_s16 else 0,
                              offsets.ctypes.data, n_ops.ctypes.data, ops.ctypes.data, stride, stats.ctypes.data)
@@ -73,7 +74,7 @@ def emu_align(pairs, params, strategies, allow_s16=True, device_plan=False):
     for p in range(n):
         text = "".join(f"{int(o) >> 4}{OPS[int(o) & 15]}" for o in ops[p, : n_ops[p]])
         out.append((text, int(offsets[p])))
-    return out, dict(launches=int(stats[0]), s16=int(stats[1]), s32=int(stats[2]), units=int(stats[3]), builds=int(stats[4]), hops=int(stats[5]))
+    return out, dict(launches=int(stats[0]), s16=int(stats[1]), s32=int(stats[2]), units=int(stats[3]), builds=int(stats[4]), hops=int(stats[5]), clean=int(stats[6]))
 
 
 # ---- PairHMM lane code (mgl_b200/csrc/ph_lane.h) on the CPU

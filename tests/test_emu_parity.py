@@ -17,22 +17,26 @@ def _by_params(golden):
     return by
 
 
-@pytest.mark.parametrize("allow_s16", [True, False])
-def test_emulated_kernels_match_golden(golden, allow_s16):
+@pytest.mark.parametrize("allow_s16,clean_shortcut", [(True, True), (False, True), (True, False)])
+def test_emulated_kernels_match_golden(golden, allow_s16, clean_shortcut):
+    """clean_shortcut: paths without a gap are written down from the start cell alone (sw_trace.h clean_path, what
+    sw_start_kernel does on the device); off: every pair is walked through hops and block replays"""
     by = _by_params(golden)
-    total = 0
+    total = clean = 0
     # both arithmetics on the two BASELINE score sets; the 16-bit path additionally on every other score set
     sets = list(by) if allow_s16 else [(10, -15, -30, -5), (200, -150, -260, -11), (3, -1, -2, 0)]
     for p in sets:
         cs = by[p]
         pairs = [(c["ref"].encode("latin1"), c["alt"].encode("latin1")) for c in cs]
         for si, s in enumerate(golden["strategies"]):
-            res, st = E.emu_align(pairs, p, s, allow_s16)
+            res, st = E.emu_align(pairs, p, s, allow_s16, clean_shortcut=clean_shortcut)
             assert (st["s16"] > 0) == allow_s16
+            clean += st["clean"]
             bad = [(c["ref"], c["alt"], p, s, r, tuple(c["expect"][si])) for c, r in zip(cs, res) if r != tuple(c["expect"][si])]
             assert not bad, bad[:3]
             total += len(cs)
     assert total > 3000
+    assert (clean > 300) if clean_shortcut else (clean == 0)
 
 
 def test_emulated_mixed_strategies_in_one_batch(golden, oracle):
