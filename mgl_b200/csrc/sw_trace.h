@@ -27,6 +27,7 @@
 #include "sw_config.h"
 
 #define MGLSW_KH ((MGLSW_KMAX + 1) / 2)      /* columns of a block: at most half a lane's registers */
+#define MGLSW_HOP_BLOCKS 4                    /* blocks one diagonal hop tries to cross per memory round trip */
 /* 64-bit words of one pair's replay buffer: MGLSW_RB rows of 4-bit records, then the H values on the block's left
    boundary column (MGLSW_RB + 1 rows) and top boundary row (MGLSW_KH columns) as 32-bit integers */
 #define MGLSW_TRACE_BUF (MGLSW_RB + (MGLSW_RB + 1 + MGLSW_KH + 1) / 2)
@@ -118,62 +119,92 @@ struct Replay {
      * of the L cells is a diagonal step.  So when H is known at (I, J) and at the next checkpointed
      * cell up the diagonal -- the column left of J's block (every row of it is stored by the fill), or
      * row 0 / column 0 -- one 8-byte load and L byte compares decide L traceback steps, and no block
-     * is recomputed.  Returns L (> 0) and H[I-L][J-L] on success, 0 if some cell on the way is a gap
-     * or a tie that goes another way: the caller then replays the block as usual.
+     * is recomputed.
+     * One call tries MGLSW_HOP_BLOCKS blocks in a row: the checkpointed cells up the diagonal follow from
+     * the unit's geometry alone, so their loads and the sequence bytes of the whole stretch are in flight
+     * together -- one memory round trip where block-by-block hops took one each (a clean stretch of a
+     * 150-column alignment is ~12 blocks).  Returns the steps taken over the leading clean blocks (0: the
+     * very first block holds a gap, or a tie that goes another way) and H at the cell reached; `blocked`
+     * says that the block after those is known not to be clean, so the caller replays it without asking again.
      */
-    SW_HD int hop(int I, int J, int hcur, int &hnext) const
+    SW_HD int hop(int I, int J, int hcur, int &hnext, bool &blocked) const
     {
-        u32 slot, reg;
-        {
-            const u32 col = (u32)J - 1, wide = cr * (cb + 1);
-            if (col < wide) { slot = col / (cb + 1); reg = col - slot * (cb + 1); }
-            else { const u32 c2 = col - wide; slot = cr + c2 / cb; reg = c2 - (slot - cr) * cb; }
+        int Lk[MGLSW_HOP_BLOCKS], hv[MGLSW_HOP_BLOCKS];
+        const u32 *ap[MGLSW_HOP_BLOCKS];
+        int Ik = I, Jk = J, S = 0;
+#pragma unroll
+        for (int k = 0; k < MGLSW_HOP_BLOCKS; k++) {
+            Lk[k] = 0; hv[k] = 0; ap[k] = nullptr;
+            if (Ik > 0 && Jk > 0) {
+                u32 slot, reg;
+                {
+                    const u32 col = (u32)Jk - 1, wide = cr * (cb + 1);
+                    if (col < wide) { slot = col / (cb + 1); reg = col - slot * (cb + 1); }
+                    else { const u32 c2 = col - wide; slot = cr + c2 / cb; reg = c2 - (slot - cr) * cb; }
+                }
+                const u32 strip = slot / G, lane = slot - strip * G;
+                const bool sub = reg >= KM;
+                const u32 k_lo = sub ? KM : 0u;
+                const int jc = (int)(slot < cr ? slot * (cb + 1) : cr * (cb + 1) + (slot - cr) * cb) + (int)k_lo;   /* = ja - 1 of Jk's block */
+                int L = Jk - jc;
+                if (L > Ik) L = Ik;
+                const int it = Ik - L, jt = Jk - L;
+                if (it == 0) hv[k] = bnd(jt);                               /* row 0, sw.cpp:29-35 */
+                else if (jt == 0) hv[k] = bnd(it);                          /* column 0, sw.cpp:47-49 */
+                else {
+                    u32 cs = strip, cl = lane, word = 0;
+                    if (!sub) { word = 2; if (lane > 0) cl = lane - 1; else { cl = G - 1; cs = strip - 1; } }
+                    const u32 tt = (u32)it + cl;                            /* the step at which lane cl worked on row it */
+                    ap[k] = base + (size_t)cs * rbc * RW + (size_t)cl * LSW + word + (size_t)(tt / MGLSW_RB) * RW + (tt % MGLSW_RB) * 4u;
+                }
+                Lk[k] = L; S += L; Ik = it; Jk = jt;
+            }
         }
-        const u32 strip = slot / G, lane = slot - strip * G;
-        const bool sub = reg >= KM;
-        const u32 k_lo = sub ? KM : 0u;
-        const int jc = (int)(slot < cr ? slot * (cb + 1) : cr * (cb + 1) + (slot - cr) * cb) + (int)k_lo;   /* = ja - 1 of J's block */
-        int L = J - jc;
-        if (L > I) L = I;
-        const int it = I - L, jt = J - L;
-        int ht;
-        if (it == 0) ht = bnd(jt);                                  /* row 0, sw.cpp:29-35 */
-        else if (jt == 0) ht = bnd(it);                             /* column 0, sw.cpp:47-49 */
-        else {
-            u32 cs = strip, cl = lane, word = 0;
-            if (!sub) { word = 2; if (lane > 0) cl = lane - 1; else { cl = G - 1; cs = strip - 1; } }
-            const u32 tt = (u32)it + cl;                            /* the step at which lane cl worked on row it */
-            const u32 *lp = base + (size_t)cs * rbc * RW + (size_t)cl * LSW + word;
-            ht = hval(load_w2(lp + (size_t)(tt / MGLSW_RB) * RW + (tt % MGLSW_RB) * 4u).x);
-        }
-        /* mismatches among ref[I-L .. I-1] vs alt[J-L .. J-1] (both ascending): the sum of the L substitution scores */
-        int nm = 0;
+        u32 raw[MGLSW_HOP_BLOCKS];
+#pragma unroll
+        for (int k = 0; k < MGLSW_HOP_BLOCKS; k++) raw[k] = ap[k] ? load_w2(ap[k]).x : 0u;
+        /* mismatches of the whole stretch, ref[I-S .. I) against alt[J-S .. J): bit u of mm = bytes u of the window of
+           MGLSW_HOP_BLOCKS * MGLSW_KH bytes that ENDS at (I, J) differ (the arena is padded in front by more than that) */
+        constexpr int WIN = MGLSW_HOP_BLOCKS * MGLSW_KH;
+        static_assert(WIN <= 48 && WIN % 4 == 0 && WIN + 4 <= (int)MGLSW_ARENA_FRONT_PAD, "mismatch window: one 64-bit mask, inside the arena's front padding");
+        u64 mm = 0;
 #if SW_ON_DEVICE
         {
-            /* 16 aligned bytes cover the <= 12 wanted ones at any alignment (the arena is padded on both sides);
-               funnel shifts line them up, a per-byte compare and a population count do the rest */
-            const uint8_t *pr = ref + (I - L), *pa = alt + (J - L);
+            const uint8_t *pr = ref + (I - WIN), *pa = alt + (J - WIN);
             const u32 *wr = reinterpret_cast<const u32 *>(reinterpret_cast<size_t>(pr) & ~(size_t)3);
             const u32 *wa = reinterpret_cast<const u32 *>(reinterpret_cast<size_t>(pa) & ~(size_t)3);
             const u32 sr = ((u32)reinterpret_cast<size_t>(pr) & 3u) * 8u, sa = ((u32)reinterpret_cast<size_t>(pa) & 3u) * 8u;
-            const u32 r0 = __ldg(wr), r1 = __ldg(wr + 1), r2 = __ldg(wr + 2), r3 = __ldg(wr + 3);
-            const u32 a0 = __ldg(wa), a1 = __ldg(wa + 1), a2 = __ldg(wa + 2), a3 = __ldg(wa + 3);
-            static_assert(MGLSW_KH <= 12, "the hop compares at most 12 bytes");
-            const u32 x0 = __vcmpne4(__funnelshift_r(r0, r1, sr), __funnelshift_r(a0, a1, sa));
-            const u32 x1 = __vcmpne4(__funnelshift_r(r1, r2, sr), __funnelshift_r(a1, a2, sa));
-            const u32 x2 = __vcmpne4(__funnelshift_r(r2, r3, sr), __funnelshift_r(a2, a3, sa));
-            /* keep bytes 0 .. L-1 */
-            const u32 m0 = L >= 4 ? 0xffffffffu : (0xffffffffu >> (8u * (4u - (u32)L)));
-            const u32 m1 = L >= 8 ? 0xffffffffu : (L <= 4 ? 0u : (0xffffffffu >> (8u * (8u - (u32)L))));
-            const u32 m2 = L >= 12 ? 0xffffffffu : (L <= 8 ? 0u : (0xffffffffu >> (8u * (12u - (u32)L))));
-            nm = (__popc(x0 & m0) + __popc(x1 & m1) + __popc(x2 & m2)) >> 3;
+            u32 rw[WIN / 4 + 1], aw[WIN / 4 + 1];
+#pragma unroll
+            for (int w = 0; w <= WIN / 4; w++) { rw[w] = __ldg(wr + w); aw[w] = __ldg(wa + w); }
+#pragma unroll
+            for (int w = 0; w < WIN / 4; w++) {
+                const u32 x = __vcmpne4(__funnelshift_r(rw[w], rw[w + 1], sr), __funnelshift_r(aw[w], aw[w + 1], sa));
+                mm |= (u64)(((x & 0x01010101u) * 0x10204080u) >> 28) << (4 * w);     /* one bit per byte */
+            }
         }
 #else
-        for (int t = 0; t < L; t++) nm += ref[I - 1 - t] != alt[J - 1 - t] ? 1 : 0;
+        for (int t = 0; t < S; t++) if (ref[I - 1 - t] != alt[J - 1 - t]) mm |= 1ull << (WIN - 1 - t);
 #endif
-        const int sum = L * match - nm * (match - mismatch);
-        hnext = ht;
-        return hcur - ht == sum ? L : 0;
+        int h = hcur, adv = 0, pos = WIN;
+        blocked = false;
+#pragma unroll
+        for (int k = 0; k < MGLSW_HOP_BLOCKS; k++) {
+            const int L = Lk[k];
+            if (L == 0 || blocked) continue;
+            pos -= L;
+            const int ht = ap[k] ? hval(raw[k]) : hv[k];
+#if SW_ON_DEVICE
+            const int nm = __popcll((mm >> pos) & ((1ull << L) - 1ull));
+#else
+            int nm = 0;
+            for (int t = 0; t < L; t++) nm += (int)((mm >> (pos + t)) & 1ull);
+#endif
+            if (h - ht == L * match - nm * (match - mismatch)) { h = ht; adv += L; }
+            else blocked = true;
+        }
+        hnext = h;
+        return adv;
     }
 
     SW_HD void build(int I, int J)
@@ -450,12 +481,14 @@ SW_HD PairResult traceback_pair(const UnitDesc &u, u32 half, bool s32, u32 G, u3
          */
         while (hk && !done) {
             int hn;
-            const int L = rp.hop(I, J, hcur, hn);
+            bool blocked;
+            const int L = rp.hop(I, J, hcur, hn, blocked);
             if (L == 0) break;
             if (state == OP_M) run += L;
             else { SW_EMIT(state, run); run = L; state = OP_M; }
             I -= L; J -= L; hcur = hn; hops++;
             if (!(I > 0 && J > 0)) done = true;
+            if (blocked) break;                       /* the next block is known to hold a gap: rebuild it */
         }
 #if SW_ON_DEVICE
         if (__ballot_sync(0xffffffffu, !done) == 0u) break;       /* the warp's meeting point; leaves when every lane is done */

@@ -131,12 +131,15 @@ __global__ void __launch_bounds__(128) sw_start_kernel(const __grid_constant__ T
  * One thread per worklist entry: the pairs whose path has a gap, consecutive entries = neighbouring pair slots of one
  * shape bucket, whose checkpoints sit next to each other.
  */
-#ifndef MGLSW_TRACE_MINB
-#define MGLSW_TRACE_MINB 4
+#ifndef MGLSW_TRACE_THREADS
+#define MGLSW_TRACE_THREADS 128
 #endif
-__global__ void __launch_bounds__(128, MGLSW_TRACE_MINB) sw_traceback_kernel(const __grid_constant__ TraceArgs a)
+#ifndef MGLSW_TRACE_MINB
+#define MGLSW_TRACE_MINB (512 / MGLSW_TRACE_THREADS)    /* 128 registers per thread */
+#endif
+__global__ void __launch_bounds__(MGLSW_TRACE_THREADS, MGLSW_TRACE_MINB) sw_traceback_kernel(const __grid_constant__ TraceArgs a)
 {
-    __shared__ u64 s_nib[MGLSW_TRACE_BUF * 128];   /* the replayed block: records and boundary H values, one column per thread */
+    __shared__ u64 s_nib[MGLSW_TRACE_BUF * MGLSW_TRACE_THREADS];   /* the replayed block: records and boundary H values, one column per thread */
     const u32 k = blockIdx.x * blockDim.x + threadIdx.x;
     const u32 count = __ldcg(a.work_count);
     if ((k & ~31u) >= count) return;                /* whole warps leave; a lane past the end stays with its warp, idle */
@@ -152,7 +155,7 @@ __global__ void __launch_bounds__(128, MGLSW_TRACE_MINB) sw_traceback_kernel(con
     const u32 G = (u.flags & UNIT_G32) ? MGLSW_G_LONG : MGLSW_G_SHORT;
     u32 *end = a.scratch + a.ops_end[p];
     const PairResult r = traceback_pair(u, half, s32, G, u.regs, a.ckpt, a.arena, s32 ? a.c32 : a.c16, sc, a.strategy[p], end,
-                                        s_nib + threadIdx.x, 128u, live);
+                                        s_nib + threadIdx.x, (u32)MGLSW_TRACE_THREADS, live);
     if (!live) return;
     a.offsets[p] = r.offset;
     a.n_ops[p] = r.n_ops;
@@ -229,7 +232,7 @@ cudaError_t launch_traceback(const TraceArgs &a, cudaStream_t stream)
 {
     if (a.n_units == 0) return cudaSuccess;
     /* the worklist's length is on the device: the grid covers every pair slot, blocks beyond the list leave at once */
-    sw_traceback_kernel<<<(2u * a.n_units + 127) / 128, 128, 0, stream>>>(a);
+    sw_traceback_kernel<<<(2u * a.n_units + MGLSW_TRACE_THREADS - 1) / MGLSW_TRACE_THREADS, MGLSW_TRACE_THREADS, 0, stream>>>(a);
     return cudaGetLastError();
 }
 

@@ -265,7 +265,7 @@ int emu_align_batch(int n, const uint8_t *arena, const uint64_t *ref_off, const 
         if (const char *dump = std::getenv("EMU_DUMP")) {        /* developer aid: per-pair replay / hop counts in thread order */
             static FILE *fp = nullptr;
             if (!fp) fp = std::fopen(dump, "w");
-            if (fp) { std::fprintf(fp, "%u %u %u\n", plan.pair_unit[p], r.builds, r.hops); std::fflush(fp); }
+            if (fp) { std::fprintf(fp, "%u %u %u %d %d\n", plan.pair_unit[p], r.builds, r.hops, r.score, clean ? 1 : 0); std::fflush(fp); }
         }
         offsets[p] = r.offset;
         n_ops[p] = r.n_ops;
