@@ -641,7 +641,7 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed, bo
         return MGL_SW_OK;
     }
     if ((e = launch_start(t, pt)) != cudaSuccess) return cuda_fail(e, "start-cell launch");
-    if ((e = launch_traceback(t, pt)) != cudaSuccess) return cuda_fail(e, "traceback launch");
+    if ((e = launch_traceback(t, pipe_units > 0, pt)) != cudaSuccess) return cuda_fail(e, "traceback launch");
     if (exact_shortcut) {
         if ((e = launch_exact_match(t, pt)) != cudaSuccess) return cuda_fail(e, "exact-match launch");
         bs.other_launches += 1;

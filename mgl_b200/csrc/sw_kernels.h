@@ -28,7 +28,7 @@ struct TraceArgs {
     int *score3;              /* out, score-only runs: per pair {score, end_ref, end_alt} */
     u32 n_units;              /* units of the chunk (padding units included)    */
     /* launch_start -> launch_traceback: the pairs whose path has a gap, in the order the start kernel found them */
-    u32 *work_count;          /* one word, zeroed by launch_start                */
+    u32 *work_count;          /* entries in the worklist; zeroed by launch_start */
     u32 *worklist;            /* 2 * n_units: pair slot (2 * unit + half) of entry k */
     int4 *startcell;          /* 2 * n_units: {i, j, seg, score} of entry k (StartCell, sw_trace.h) */
 };
@@ -38,7 +38,8 @@ struct TraceArgs {
  * here, the others are appended to the worklist launch_traceback walks.  Must precede launch_traceback on the stream.
  */
 cudaError_t launch_start(const TraceArgs &a, cudaStream_t stream);
-cudaError_t launch_traceback(const TraceArgs &a, cudaStream_t stream);
+/* has_wide: some pair of the chunk has MGLSW_HOP_WIDE_MIN_STRIPS column strips or more (a pipelined fill launch): the kernel with the four-block hop */
+cudaError_t launch_traceback(const TraceArgs &a, bool has_wide, cudaStream_t stream);
 /* opt-in: SOFTCLIP / IGNORE pairs whose alt occurs verbatim in the ref take GATK's wrapper answer (last occurrence, all M);
    runs after launch_traceback on the same stream and overwrites offsets / n_ops / scratch of those pairs */
 cudaError_t launch_exact_match(const TraceArgs &a, cudaStream_t stream);

@@ -27,7 +27,10 @@
 #include "sw_config.h"
 
 #define MGLSW_KH ((MGLSW_KMAX + 1) / 2)      /* columns of a block: at most half a lane's registers */
+#define MGLSW_HOP_WIDE_MIN_STRIPS MGLSW_PIPE_MIN_STRIPS   /* pairs of at least this many column strips (= the pipelined fill launches) hop MGLSW_HOP_BLOCKS blocks at a time */
+#ifndef MGLSW_HOP_BLOCKS
 #define MGLSW_HOP_BLOCKS 4                    /* blocks one diagonal hop tries to cross per memory round trip */
+#endif
 /* 64-bit words of one pair's replay buffer: MGLSW_RB rows of 4-bit records, then the H values on the block's left
    boundary column (MGLSW_RB + 1 rows) and top boundary row (MGLSW_KH columns) as 32-bit integers */
 #define MGLSW_TRACE_BUF (MGLSW_RB + (MGLSW_RB + 1 + MGLSW_KH + 1) / 2)
@@ -120,20 +123,24 @@ struct Replay {
      * cell up the diagonal -- the column left of J's block (every row of it is stored by the fill), or
      * row 0 / column 0 -- one 8-byte load and L byte compares decide L traceback steps, and no block
      * is recomputed.
-     * One call tries MGLSW_HOP_BLOCKS blocks in a row: the checkpointed cells up the diagonal follow from
-     * the unit's geometry alone, so their loads and the sequence bytes of the whole stretch are in flight
-     * together -- one memory round trip where block-by-block hops took one each (a clean stretch of a
-     * 150-column alignment is ~12 blocks).  Returns the steps taken over the leading clean blocks (0: the
-     * very first block holds a gap, or a tie that goes another way) and H at the cell reached; `blocked`
-     * says that the block after those is known not to be clean, so the caller replays it without asking again.
+     * hop<NB> tries NB blocks in a row: the checkpointed cells up the diagonal follow from the unit's
+     * geometry alone, so their loads and the sequence bytes of the whole stretch are in flight together --
+     * one memory round trip where block-by-block hops take one each (a clean stretch of a 150-column
+     * alignment is ~12 blocks).  Returns the steps taken over the leading clean blocks (0: the very first
+     * block holds a gap, or a tie that goes another way -- the caller then replays the block) and H at the
+     * cell reached; `blocked` says that the block after those is known not to be clean, so the caller
+     * replays it without asking again.  NB = MGLSW_HOP_BLOCKS costs three times the instructions of NB = 1
+     * whether it gets anywhere or not: it pays on long paths, where the chain of round trips is what the
+     * pair waits for (sw_traceback_kernel picks per warp).
      */
+    template <int NB>
     SW_HD int hop(int I, int J, int hcur, int &hnext, bool &blocked) const
     {
-        int Lk[MGLSW_HOP_BLOCKS], hv[MGLSW_HOP_BLOCKS];
-        const u32 *ap[MGLSW_HOP_BLOCKS];
+        int Lk[NB], hv[NB];
+        const u32 *ap[NB];
         int Ik = I, Jk = J, S = 0;
 #pragma unroll
-        for (int k = 0; k < MGLSW_HOP_BLOCKS; k++) {
+        for (int k = 0; k < NB; k++) {
             Lk[k] = 0; hv[k] = 0; ap[k] = nullptr;
             if (Ik > 0 && Jk > 0) {
                 u32 slot, reg;
@@ -160,13 +167,13 @@ struct Replay {
                 Lk[k] = L; S += L; Ik = it; Jk = jt;
             }
         }
-        u32 raw[MGLSW_HOP_BLOCKS];
+        u32 raw[NB];
 #pragma unroll
-        for (int k = 0; k < MGLSW_HOP_BLOCKS; k++) raw[k] = ap[k] ? load_w2(ap[k]).x : 0u;
+        for (int k = 0; k < NB; k++) raw[k] = ap[k] ? load_w2(ap[k]).x : 0u;
         /* mismatches of the whole stretch, ref[I-S .. I) against alt[J-S .. J): bit u of mm = bytes u of the window of
-           MGLSW_HOP_BLOCKS * MGLSW_KH bytes that ENDS at (I, J) differ (the arena is padded in front by more than that) */
-        constexpr int WIN = MGLSW_HOP_BLOCKS * MGLSW_KH;
-        static_assert(WIN <= 48 && WIN % 4 == 0 && WIN + 4 <= (int)MGLSW_ARENA_FRONT_PAD, "mismatch window: one 64-bit mask, inside the arena's front padding");
+           NB * MGLSW_KH bytes that ENDS at (I, J) differ (the arena is padded in front by more than that) */
+        constexpr int WIN = NB * MGLSW_KH;
+        static_assert(NB >= 1 && WIN <= 48 && WIN % 4 == 0 && WIN + 4 <= (int)MGLSW_ARENA_FRONT_PAD, "mismatch window: one 64-bit mask, inside the arena's front padding");
         u64 mm = 0;
 #if SW_ON_DEVICE
         {
@@ -189,7 +196,7 @@ struct Replay {
         int h = hcur, adv = 0, pos = WIN;
         blocked = false;
 #pragma unroll
-        for (int k = 0; k < MGLSW_HOP_BLOCKS; k++) {
+        for (int k = 0; k < NB; k++) {
             const int L = Lk[k];
             if (L == 0 || blocked) continue;
             pos -= L;
@@ -387,10 +394,6 @@ SW_HD StartCell select_start(const UnitDesc &u, u32 half, u32 G, u32 K, const u3
     return sc;
 }
 
-/*
- * ops_end points one past the pair's scratch region; elements are written
- * downwards so that [ops_end - n_ops, ops_end) reads left to right.
- */
 /* the end of the walk at (I, J) with I == 0 or J == 0: overhang post-processing and offset, sw.cpp:224-248 */
 SW_HD u32 *finish_walk(int strategy, u32 state, int run, int I, int J, u32 *p, int &offset)
 {
@@ -421,6 +424,18 @@ SW_HD u32 *finish_walk(int strategy, u32 state, int run, int I, int J, u32 *p, i
  * counted by the caller (a loop here in the emulator, a lane group in sw_start_kernel).  Returns false, writing
  * nothing, when the path has a gap: the pair then goes through traceback_pair.
  */
+/* can any mismatch count make clean_path succeed?  (the score deficit of the diagonal must be a whole number of mismatches,
+   at most its length) -- lets the caller skip counting: with config 3's scores 349 of 350 gapped pairs fail here */
+SW_HD bool clean_path_possible(const StartCell &st, const CellConsts &c, int indel)
+{
+    const int L = st.i < st.j ? st.i : st.j;
+    const int it = st.i - L, jt = st.j - L;
+    const int ht = boundary_score(it == 0 ? jt : it, indel, c.s_go, c.s_ge);
+    const int need = L * c.s_match - (st.score - c.bias - c.s_match - ht);       /* = mismatches x (match - mismatch) on a clean path */
+    const int per = c.s_match - c.s_mismatch;
+    return need >= 0 && need % per == 0 && need / per <= L;
+}
+
 SW_HD bool clean_path(const StartCell &st, int strategy, const CellConsts &c, int indel, int nm, u32 *ops_end, PairResult &res)
 {
     const int L = st.i < st.j ? st.i : st.j;
@@ -439,50 +454,50 @@ SW_HD bool clean_path(const StartCell &st, int strategy, const CellConsts &c, in
 }
 
 /*
- * On the device ALL 32 lanes of a warp call this together (`live` false for a lane without a pair): once per round the
- * warp meets at a vote, so that the lanes that need a block rebuilt run the one replay site together.  Left to the
- * hardware's reconvergence the lanes drifted apart -- the replay ran 19 times per warp with 4 lanes each where the
- * slowest pair needs 8 [B200, profiles/r19a].
+ * The walk of one pair (sw.cpp:173-214) as an object with two alternating phases, so that a warp can drive 32 of them
+ * around ONE replay site: hop_phase() runs ahead while H is known (each lane on its own), build_phase() rebuilds the
+ * block around the current cell and walks inside it (the lanes that need it, together).  The walk is a state machine:
+ *   mode 0  at cell (I, J), about to read which of diagonal / F / E produced H
+ *   mode 1  inside an insertion, at cell (I, cc): does F extend through it?
+ *   mode 2  inside a deletion,  at cell (r, J):  does E extend through it?
+ * ops_end points one past the pair's scratch region; elements are written downwards so that [ops_end - n_ops, ops_end)
+ * reads left to right.
  */
-SW_HD PairResult traceback_pair(const UnitDesc &u, u32 half, bool s32, u32 G, u32 K, const u32 *ckpt, const uint8_t *arena,
-                                const CellConsts &c, const StartCell &st, int strategy, u32 *ops_end,
-                                u64 *nib, u32 nstride, bool live = true)
-{
-    int I = st.i, J = st.j, run = st.seg;
-    const int start_score = st.score;
-
-    u32 *p = ops_end;
-#define SW_EMIT(op, len) do { if ((len) > 0) *--p = ((u32)(len) << 4) | (u32)(op); } while (0)
-
-    if (run > 0 && strategy == OS_SOFTCLIP) { SW_EMIT(OP_S, run); run = 0; }   /* sw.cpp:173-176 */
-
+struct Walker {
     Replay rp;
-    rp.init(u, G, K, half, s32, ckpt, arena, c, nib, nstride);
+    u32 *p, *ops_end;
+    int I, J, run, strategy, start_score;
+    u32 state, next, hops;
+    int mode, steplen, cc, r;
+    int hcur;                /* H at (I, J), when known: at the start cell (the score that selected it) and on checkpointed cells */
+    bool hk, done;
+
+#define SW_EMIT(op, len) do { if ((len) > 0) *--p = ((u32)(len) << 4) | (u32)(op); } while (0)
+    SW_HD void begin(const UnitDesc &u, u32 half, bool s32, u32 G, u32 K, const u32 *ckpt, const uint8_t *arena, const CellConsts &c,
+                     const StartCell &st, int strategy_, u32 *ops_end_, u64 *nib, u32 nstride)
+    {
+        I = st.i; J = st.j; run = st.seg; strategy = strategy_; start_score = st.score;
+        p = ops_end = ops_end_;
+        if (run > 0 && strategy == OS_SOFTCLIP) { SW_EMIT(OP_S, run); run = 0; }   /* sw.cpp:173-176 */
+        rp.init(u, G, K, half, s32, ckpt, arena, c, nib, nstride);
+        state = OP_M; next = OP_M; hops = 0;
+        mode = 0; steplen = 1; cc = 0; r = 0;
+        hcur = start_score - c.bias - c.s_match;
+        hk = true; done = false;
+    }
 
     /*
-     * The walk of sw.cpp:182-214 as a state machine around ONE replay site, so that the 32 pairs
-     * of a warp rebuild their blocks together instead of each stalling the others:
-     *   mode 0  at cell (I, J), about to read which of diagonal / F / E produced H
-     *   mode 1  inside an insertion, at cell (I, cc): does F extend through it?
-     *   mode 2  inside a deletion,  at cell (r, J):  does E extend through it?
+     * While H is known, cross blocks with diagonal hops (Replay::hop): a clean stretch of the alignment costs one
+     * memory round trip and a few byte compares per block or, `wide`, per MGLSW_HOP_BLOCKS blocks (Replay::hop<NB>; the
+     * caller's choice, the same for every lane of a warp so that they keep running the same code).  Returns when the
+     * pair is done or the block around (I, J) has to be rebuilt.
      */
-    u32 state = OP_M, next = OP_M;
-    int mode = 0, steplen = 1, cc = 0, r = 0;
-    bool done = !live;
-    /* H at (I, J), when known: at the start cell (the score that selected it) and on checkpointed cells */
-    int hcur = start_score - c.bias - c.s_match;
-    u32 hops = 0;
-    bool hk = true;
-    for (;;) {
-        /*
-         * Phase A: while H is known, try to cross the block with one diagonal hop (Replay::hop).  A
-         * clean stretch of the alignment costs one load and <= 12 byte compares per block; threads of
-         * the warp run ahead independently here and meet again at the one replay site below.
-         */
+    SW_HD void hop_phase(bool wide)
+    {
         while (hk && !done) {
             int hn;
-            bool blocked;
-            const int L = rp.hop(I, J, hcur, hn, blocked);
+            bool blocked = false;
+            const int L = wide ? rp.hop<MGLSW_HOP_BLOCKS>(I, J, hcur, hn, blocked) : rp.hop<1>(I, J, hcur, hn, blocked);
             if (L == 0) break;
             if (state == OP_M) run += L;
             else { SW_EMIT(state, run); run = L; state = OP_M; }
@@ -490,13 +505,11 @@ SW_HD PairResult traceback_pair(const UnitDesc &u, u32 half, bool s32, u32 G, u3
             if (!(I > 0 && J > 0)) done = true;
             if (blocked) break;                       /* the next block is known to hold a gap: rebuild it */
         }
-#if SW_ON_DEVICE
-        if (__ballot_sync(0xffffffffu, !done) == 0u) break;       /* the warp's meeting point; leaves when every lane is done */
-        if (done) continue;
-#else
-        if (done) break;
-#endif
-        /* Phase B: recompute the block around the current cell and walk inside it */
+    }
+
+    /* recompute the block around the current cell and walk inside it */
+    SW_HD void build_phase()
+    {
         rp.build(mode == 2 ? r : I, mode == 1 ? cc : J);
         for (;;) {
             const int qi = mode == 2 ? r : I, qj = mode == 1 ? cc : J;
@@ -525,15 +538,32 @@ SW_HD PairResult traceback_pair(const UnitDesc &u, u32 half, bool s32, u32 G, u3
         /* left the block between two cells (not inside a gap): H is known again if we stand on its boundary */
         hk = !done && mode == 0 && rp.boundary_h(I, J, hcur);
     }
-
 #undef SW_EMIT
-    PairResult res;
-    if (!live) { res.offset = 0; res.n_ops = 0; res.score = 0; res.builds = res.hops = 0; return res; }   /* wrote nothing */
-    p = finish_walk(strategy, state, run, I, J, p, res.offset);
-    res.n_ops = (u32)(ops_end - p);
-    res.score = start_score;
-    res.builds = rp.builds; res.hops = hops;
-    return res;
+
+    SW_HD PairResult finish()
+    {
+        PairResult res;
+        p = finish_walk(strategy, state, run, I, J, p, res.offset);
+        res.n_ops = (u32)(ops_end - p);
+        res.score = start_score;
+        res.builds = rp.builds; res.hops = hops;
+        return res;
+    }
+};
+
+/* one pair from start cell to CIGAR: what the emulator runs; the device drives Walkers itself (sw_traceback_kernel) */
+SW_HD PairResult traceback_pair(const UnitDesc &u, u32 half, bool s32, u32 G, u32 K, const u32 *ckpt, const uint8_t *arena,
+                                const CellConsts &c, const StartCell &st, int strategy, u32 *ops_end, u64 *nib, u32 nstride)
+{
+    Walker w;
+    w.begin(u, half, s32, G, K, ckpt, arena, c, st, strategy, ops_end, nib, nstride);
+    const bool wide = u.nstrips >= MGLSW_HOP_WIDE_MIN_STRIPS;
+    for (;;) {
+        w.hop_phase(wide);
+        if (w.done) break;
+        w.build_phase();
+    }
+    return w.finish();
 }
 
 }  // namespace mglsw

@@ -11,8 +11,8 @@ namespace mglsw {
 
 /*
  * The start cell of one pair (select_start, sw_trace.h: sw.cpp:116-127 and :155-170) by a group of 8 lanes: lane g reads
- * words g, g + 8, ... of the captured last row -- coalesced, all in flight together, where one thread per pair walked
- * them one dependent load at a time.  The scan keeps the FIRST of the candidates with the best (score, distance to the
+ * the words of lane slots g, g + 8, ... of the captured last row -- several in flight, where one thread per pair walked
+ * the whole row one dependent load at a time.  The scan keeps the FIRST of the candidates with the best (score, distance to the
  * diagonal) in its order -- last-column maximum first, then the last row by ascending column (it replaces only on a
  * strict improvement) -- so the lanes keep (score, distance, column) and the reduction prefers the smaller column among
  * equals; the last-column maximum wins every tie.  The same value in all 8 lanes.
@@ -33,23 +33,18 @@ __device__ __forceinline__ StartCell start_cell_group(const UnitDesc &u, u32 hal
     } else if (strategy == OS_LEADING_INDEL) {
         sc.i = mqe_t; sc.j = ql; sc.seg = 0; sc.score = mqe;
     } else {
+        /* lane g takes lane slots g, g + 8, ...: K consecutive words each, columns ascending; the 8 lanes of a group read
+           neighbouring 4 K-byte runs of one row, so the sectors are shared through L1 (the row was written by an earlier launch) */
         int best = (int)0x80000000, bd = 0x7fffffff, bj = 0x7fffffff;
-        const u32 W = nslots * K;
-        u32 slot = gl / K, reg = gl - slot * K;
-        for (u32 w0 = gl; w0 < W; w0 += 32u) {
-            u32 v[4];
-#pragma unroll
-            for (int q = 0; q < 4; q++) v[q] = w0 + 8u * q < W ? __ldcg(row + w0 + 8u * q) : 0u;
-#pragma unroll
-            for (int q = 0; q < 4; q++) {
-                if (w0 + 8u * q < W && reg < slot_cols(u, slot)) {
-                    const int j = (int)slot_first_col(u, slot) + (int)reg + 1;
-                    const int s = (int)((v[q] >> sh) & msk);
-                    const int da = tl - j < 0 ? j - tl : tl - j;
-                    if (s > best || (s == best && da < bd)) { best = s; bd = da; bj = j; }
-                }
-                reg += 8u;
-                while (reg >= K) { reg -= K; slot++; }
+        for (u32 slot = gl; slot < nslots; slot += 8u) {
+            const u32 cols = slot_cols(u, slot);
+            int j = (int)slot_first_col(u, slot) + 1;
+            const u32 *wp = row + (size_t)slot * K;
+#pragma unroll 4
+            for (u32 reg = 0; reg < cols; reg++, j++) {
+                const int s = (int)((wp[reg] >> sh) & msk);
+                const int da = tl - j < 0 ? j - tl : tl - j;
+                if (s > best || (s == best && da < bd)) { best = s; bd = da; bj = j; }
             }
         }
 #pragma unroll
@@ -96,18 +91,22 @@ __global__ void __launch_bounds__(128) sw_start_kernel(const __grid_constant__ T
                     a.score3[3 * (size_t)p + 2] = sc.j;
                 }
             } else {
-                const int L = sc.i < sc.j ? sc.i : sc.j;
-                const uint8_t *rf = a.arena + u.ref_off[half] + (sc.i - L), *al = a.arena + u.alt_off[half] + (sc.j - L);
-                int nm = 0;
-                for (int t = (int)gl; t < L; t += 8) nm += __ldg(rf + t) != __ldg(al + t) ? 1 : 0;
+                const int indel = (u.flags & UNIT_INDEL) ? 1 : 0;
+                if (!clean_path_possible(sc, c, indel)) push = gl == 0;
+                else {
+                    const int L = sc.i < sc.j ? sc.i : sc.j;
+                    const uint8_t *rf = a.arena + u.ref_off[half] + (sc.i - L), *al = a.arena + u.alt_off[half] + (sc.j - L);
+                    int nm = 0;
+                    for (int t = (int)gl; t < L; t += 8) nm += __ldg(rf + t) != __ldg(al + t) ? 1 : 0;
 #pragma unroll
-                for (int m = 1; m < 8; m <<= 1) nm += __shfl_xor_sync(gmask, nm, m);
-                if (gl == 0) {
-                    PairResult r;
-                    if (clean_path(sc, strategy, c, (u.flags & UNIT_INDEL) ? 1 : 0, nm, a.scratch + a.ops_end[p], r)) {
-                        a.offsets[p] = r.offset;
-                        a.n_ops[p] = r.n_ops;
-                    } else push = true;
+                    for (int m = 1; m < 8; m <<= 1) nm += __shfl_xor_sync(gmask, nm, m);
+                    if (gl == 0) {
+                        PairResult r;
+                        if (clean_path(sc, strategy, c, indel, nm, a.scratch + a.ops_end[p], r)) {
+                            a.offsets[p] = r.offset;
+                            a.n_ops[p] = r.n_ops;
+                        } else push = true;
+                    }
                 }
             }
         }
@@ -128,8 +127,13 @@ __global__ void __launch_bounds__(128) sw_start_kernel(const __grid_constant__ T
 }
 
 /*
- * One thread per worklist entry: the pairs whose path has a gap, consecutive entries = neighbouring pair slots of one
- * shape bucket, whose checkpoints sit next to each other.
+ * One lane per worklist entry: the pairs whose path has a gap, consecutive entries = neighbouring pair slots of one shape
+ * bucket, whose checkpoints sit next to each other.  Each lane drives a Walker (sw_trace.h); once per round the warp
+ * meets at a vote, so that the lanes that need a block rebuilt run the ONE replay site together.  Left to the hardware's
+ * reconvergence the lanes drifted apart: the replay ran 19 times per warp with 4 lanes each where the slowest pair
+ * needs 8 [B200, profiles/r19a]; which warps meet is decided below.  (Lanes that take the next entry off the list when their pair is done -- a grid of a
+ * third or a quarter of the list -- keep the replay site fuller but were slower, alone and in the overlapped step:
+ * profiles/r21a.)
  */
 #ifndef MGLSW_TRACE_THREADS
 #define MGLSW_TRACE_THREADS 128
@@ -137,6 +141,7 @@ __global__ void __launch_bounds__(128) sw_start_kernel(const __grid_constant__ T
 #ifndef MGLSW_TRACE_MINB
 #define MGLSW_TRACE_MINB (512 / MGLSW_TRACE_THREADS)    /* 128 registers per thread */
 #endif
+template <bool HAS_WIDE>    /* false: the chunk has no pair of MGLSW_HOP_WIDE_MIN_STRIPS strips, the kernel carries no hopn code */
 __global__ void __launch_bounds__(MGLSW_TRACE_THREADS, MGLSW_TRACE_MINB) sw_traceback_kernel(const __grid_constant__ TraceArgs a)
 {
     __shared__ u64 s_nib[MGLSW_TRACE_BUF * MGLSW_TRACE_THREADS];   /* the replayed block: records and boundary H values, one column per thread */
@@ -144,19 +149,44 @@ __global__ void __launch_bounds__(MGLSW_TRACE_THREADS, MGLSW_TRACE_MINB) sw_trac
     const u32 count = __ldcg(a.work_count);
     if ((k & ~31u) >= count) return;                /* whole warps leave; a lane past the end stays with its warp, idle */
     const bool live = k < count;
-    const u32 sid = live ? a.worklist[k] : 0u;
-    StartCell sc;
-    sc.i = sc.j = 1; sc.seg = 0; sc.score = 0;
-    if (live) { const int4 s4 = a.startcell[k]; sc.i = s4.x; sc.j = s4.y; sc.seg = s4.z; sc.score = s4.w; }
-    const UnitDesc &u = a.units[sid >> 1];
-    const u32 half = sid & 1u;
-    const u32 p = live ? u.pair[half] : 0u;
-    const bool s32 = (u.flags & UNIT_S32) != 0;
-    const u32 G = (u.flags & UNIT_G32) ? MGLSW_G_LONG : MGLSW_G_SHORT;
-    u32 *end = a.scratch + a.ops_end[p];
-    const PairResult r = traceback_pair(u, half, s32, G, u.regs, a.ckpt, a.arena, s32 ? a.c32 : a.c16, sc, a.strategy[p], end,
-                                        s_nib + threadIdx.x, (u32)MGLSW_TRACE_THREADS, live);
+    u32 p = 0, unit_flags = 0, strips = 0;
+    Walker w;
+    w.done = true;
+    if (live) {
+        const u32 sid = a.worklist[k];
+        const int4 s4 = a.startcell[k];
+        StartCell sc;
+        sc.i = s4.x; sc.j = s4.y; sc.seg = s4.z; sc.score = s4.w;
+        const UnitDesc &u = a.units[sid >> 1];
+        const u32 half = sid & 1u;
+        p = u.pair[half];
+        unit_flags = u.flags;
+        strips = u.nstrips;
+        const bool s32 = (u.flags & UNIT_S32) != 0;
+        const u32 G = (u.flags & UNIT_G32) ? MGLSW_G_LONG : MGLSW_G_SHORT;
+        w.begin(u, half, s32, G, u.regs, a.ckpt, a.arena, s32 ? a.c32 : a.c16, sc, a.strategy[p], a.scratch + a.ops_end[p],
+                s_nib + threadIdx.x, (u32)MGLSW_TRACE_THREADS);
+    }
+    /*
+     * Two choices per warp, so that its lanes keep running the same code [B200, profiles/r22b, r22c; traceback alone]:
+     * - the meeting point pays for short paths (lane groups of 8: at most 192 columns, a few hops between two rebuilt
+     *   blocks): config 2 5.6 -> 3.8 ms per 1 M pairs.  On long paths every round lasts as long as the longest clean
+     *   stretch among 32 lanes, so warps of whole-warp units let their lanes run free, as the hardware reconverges
+     *   them (config 3: 2.9 ms per 100 k pairs free, 5.1 ms met);
+     * - hops of MGLSW_HOP_BLOCKS blocks per round trip pay where the chain of round trips is what a pair waits for
+     *   (config 4's shapes; config 5 33 -> 29 ms per 1 M pairs); elsewhere their instructions cost more than the round
+     *   trips they save (config 3 2.9 -> 4.8 ms; config 2's overlapped step 15.8 -> 16.2 ms).
+     */
+    const bool meet = __all_sync(0xffffffffu, !live || !(unit_flags & UNIT_G32));
+    const bool wide = HAS_WIDE && __all_sync(0xffffffffu, !live || strips >= MGLSW_HOP_WIDE_MIN_STRIPS);
+    for (;;) {
+        if (!w.done) w.hop_phase(wide);                                /* each lane on its own */
+        if (meet) { if (__ballot_sync(0xffffffffu, !w.done) == 0u) break; }   /* leaves when every lane is done */
+        else if (w.done) break;
+        if (!w.done) w.build_phase();                                  /* met: the lanes that need it, together */
+    }
     if (!live) return;
+    const PairResult r = w.finish();
     a.offsets[p] = r.offset;
     a.n_ops[p] = r.n_ops;
 }
@@ -228,11 +258,13 @@ cudaError_t launch_start(const TraceArgs &a, cudaStream_t stream)
     return cudaGetLastError();
 }
 
-cudaError_t launch_traceback(const TraceArgs &a, cudaStream_t stream)
+cudaError_t launch_traceback(const TraceArgs &a, bool has_wide, cudaStream_t stream)
 {
     if (a.n_units == 0) return cudaSuccess;
-    /* the worklist's length is on the device: the grid covers every pair slot, blocks beyond the list leave at once */
-    sw_traceback_kernel<<<(2u * a.n_units + MGLSW_TRACE_THREADS - 1) / MGLSW_TRACE_THREADS, MGLSW_TRACE_THREADS, 0, stream>>>(a);
+    /* the worklist's length is on the device: the grid covers every pair slot, warps beyond the list leave at once */
+    const u32 blocks = (2u * a.n_units + MGLSW_TRACE_THREADS - 1) / MGLSW_TRACE_THREADS;
+    if (has_wide) sw_traceback_kernel<true><<<blocks, MGLSW_TRACE_THREADS, 0, stream>>>(a);
+    else sw_traceback_kernel<false><<<blocks, MGLSW_TRACE_THREADS, 0, stream>>>(a);
     return cudaGetLastError();
 }
 

@@ -250,7 +250,7 @@ int emu_align_batch(int n, const uint8_t *arena, const uint64_t *ref_off, const 
         if (s32) n32++; else n16++;
         /* what sw_start_kernel does on the device: a path without a gap is written down at once (sw_trace.h clean_path) */
         bool clean = false;
-        if (g_clean_shortcut) {
+        if (g_clean_shortcut && clean_path_possible(sc, cc, (u.flags & UNIT_INDEL) ? 1 : 0)) {
             const int L = sc.i < sc.j ? sc.i : sc.j;
             const uint8_t *rf = arena + u.ref_off[half] + (sc.i - L), *al = arena + u.alt_off[half] + (sc.j - L);
             int nm = 0;

@@ -52,7 +52,7 @@ def test_emulated_strip_mined_long_pairs(oracle):
     """alt lengths around the lane-group and strip boundaries (192 = 8 * 24, 768 = 32 * 24, 1536)."""
     rng = random.Random(11)
     pairs = []
-    for ql in (191, 192, 193, 300, 767, 768, 769, 1000, 1537, 2305):
+    for ql in (191, 192, 193, 300, 767, 768, 769, 1000, 1537, 2305, 3100):     # from 4 strips on (2305, 3100) the walk hops four blocks at a time
         tl = rng.randint(150, 600)
         ref = bytes(rng.choice(b"ACGT") for _ in range(tl))
         alt = bytearray(rng.choice(b"ACGT") for _ in range(ql))
