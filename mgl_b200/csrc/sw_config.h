@@ -12,6 +12,11 @@
 #define MGLSW_FILL_THREADS 128   /* 4 warps per block                             */
 #define MGLSW_PIPE_WIDE_WARPS 8    /* warps per pair of the latency-shaped pipelined kernel (launches of few long pairs) */
 #define MGLSW_PIPE_WIDE_MAX_UNITS 160  /* a chunk with at most this many pipelined pairs uses it */
+#ifndef MGLSW_TRACE_ROUNDS
+#define MGLSW_TRACE_ROUNDS 5        /* rebuilt blocks a short pair gets in the round kernels, one launch each, before a lane takes it to the end (sw_trace_kernel.cu) */
+#endif
+#define MGLSW_WC_LONG 14           /* work_count word of the whole-warp units' list */
+#define MGLSW_WC_WORDS 16
 #define MGLSW_PIPE_MIN_STRIPS 4   /* pairs of at least this many strips run one per block, strips pipelined over its warps */
 #define MGLSW_SPIN_MIN_CPUS_PER_GPU 0 /* below this many hardware threads per visible GPU the collecting thread sleeps on its events (0: always spin) */
 #define MGLSW_PACK_LEAD 6          /* chunks a planner must be ahead of the uploader to spend time packing its chunk */

@@ -88,7 +88,7 @@ void ChunkDev::release()
 void WorkSlot::release()
 {
     ckpt.release(); carry.release(); lastrow.release(); colbest.release(); scratch.release();
-    startcell.release(); worklist.release();
+    startcell.release(); worklist.release(); wstate.release();
     offsets.release(); n_ops.release(); starts.release(); tiles.release(); ops.release(); score3.release(); n_chars.release();
     h_n_ops.release(); h_total.release();
     if (ev_counts) cudaEventDestroy(ev_counts);
@@ -559,7 +559,8 @@ int Engine::ensure_slot(WorkSlot &ws, const ChunkPlan &plan, u32 n, bool score_o
     if ((e = ws.ops.reserve((plan.scratch_words + 1) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc ops");
     if ((e = ws.h_n_ops.reserve(((size_t)n + 1) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "pinned alloc");
     if ((e = ws.startcell.reserve(((size_t)plan.n_units * 2 + 1) * sizeof(int4))) != cudaSuccess) return cuda_fail(e, "cudaMalloc");
-    if ((e = ws.worklist.reserve(((size_t)plan.n_units * 2 + 4) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc");
+    if ((e = ws.worklist.reserve(((size_t)plan.n_units * 2 + MGLSW_WC_WORDS) * sizeof(u32))) != cudaSuccess) return cuda_fail(e, "cudaMalloc");
+    if ((e = ws.wstate.reserve(((size_t)plan.n_units * 2 + 1) * 2 * 3 * sizeof(uint4))) != cudaSuccess) return cuda_fail(e, "cudaMalloc");
     return MGL_SW_OK;
 }
 
@@ -627,8 +628,10 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed, bo
     t.n_units = cd.plan.n_units;
     t.score3 = (int *)ws.score3.p;
     t.work_count = (u32 *)ws.worklist.p;
-    t.worklist = (u32 *)ws.worklist.p + 4;
+    t.worklist = (u32 *)ws.worklist.p + MGLSW_WC_WORDS;
     t.startcell = (int4 *)ws.startcell.p;
+    t.wstate[0] = (uint4 *)ws.wstate.p;
+    t.wstate[1] = (uint4 *)ws.wstate.p + ((size_t)cd.plan.n_units * 2 + 1) * 3;
     if (score_only) {
         if ((e = launch_endpoints(t, pt)) != cudaSuccess) return cuda_fail(e, "endpoint launch");
         if ((e = cudaEventRecord(ws.ev_post, pt)) != cudaSuccess) return cuda_fail(e, "event record");
@@ -641,7 +644,9 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed, bo
         return MGL_SW_OK;
     }
     if ((e = launch_start(t, pt)) != cudaSuccess) return cuda_fail(e, "start-cell launch");
-    if ((e = launch_traceback(t, pipe_units > 0, pt)) != cudaSuccess) return cuda_fail(e, "traceback launch");
+    bool has_short = false, has_long = false;
+    for (const Launch &L : cd.plan.launches) { if (L.G == MGLSW_G_LONG) has_long = true; else has_short = true; }
+    if ((e = launch_traceback(t, has_short, has_long, pipe_units > 0, pt)) != cudaSuccess) return cuda_fail(e, "traceback launch");
     if (exact_shortcut) {
         if ((e = launch_exact_match(t, pt)) != cudaSuccess) return cuda_fail(e, "exact-match launch");
         bs.other_launches += 1;
@@ -662,7 +667,7 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed, bo
     }
     if (timed) cudaEventRecord(tev_[4], pt);
     if ((e = cudaEventRecord(ws.ev_post, pt)) != cudaSuccess) return cuda_fail(e, "event record");
-    bs.other_launches += 5;
+    bs.other_launches += 5 + (has_short ? MGLSW_TRACE_ROUNDS : 0) + (has_long ? 1 : 0) - (has_short ? 0 : 1);
     bs.chunks++;
     bs.cells += cd.plan.cells;
     bs.pairs += cd.n;

@@ -112,7 +112,7 @@ struct WorkSlot {
     cudaEvent_t ev_fork = nullptr, ev_side[MGLSW_SIDE] = {};
     cudaEvent_t ev_fill = nullptr, ev_post = nullptr, ev_counts = nullptr, ev_done = nullptr;
     DevBuf ckpt, carry, lastrow, colbest, scratch, offsets, n_ops, starts, tiles, ops, score3, n_chars;
-    DevBuf startcell, worklist;          /* launch_start -> launch_traceback: worklist[0] is the count, entries from word 4 on */
+    DevBuf startcell, worklist, wstate;  /* launch_start -> launch_traceback (TraceArgs): counters in the first MGLSW_WC_WORDS words of worklist */
     PinBuf h_n_ops, h_total;
     void release();
 };

@@ -27,10 +27,16 @@ struct TraceArgs {
     u32 *n_ops;               /* out, per pair                                  */
     int *score3;              /* out, score-only runs: per pair {score, end_ref, end_alt} */
     u32 n_units;              /* units of the chunk (padding units included)    */
-    /* launch_start -> launch_traceback: the pairs whose path has a gap, in the order the start kernel found them */
-    u32 *work_count;          /* entries in the worklist; zeroed by launch_start */
-    u32 *worklist;            /* 2 * n_units: pair slot (2 * unit + half) of entry k */
-    int4 *startcell;          /* 2 * n_units: {i, j, seg, score} of entry k (StartCell, sw_trace.h) */
+    /*
+     * launch_start -> launch_traceback: the pairs whose path has a gap.  worklist / startcell hold two lists: entries
+     * 0 .. work_count[0] - 1 the pairs of lane groups of 8, entries 2 n_units - 1 downwards (work_count[MGLSW_WC_LONG] of
+     * them) the pairs of whole-warp units.  work_count[r] = length of round r's list (sw_trace_round_kernel), whose
+     * entries are walks put away in wstate[r & 1] (three 16-byte words each: WalkState, sw_trace.h).
+     */
+    u32 *work_count;          /* MGLSW_WC_WORDS words, zeroed by launch_start    */
+    u32 *worklist;            /* 2 * n_units: pair slot (2 * unit + half)        */
+    int4 *startcell;          /* 2 * n_units: {i, j, seg, score} (StartCell, sw_trace.h) */
+    uint4 *wstate[2];         /* 2 * n_units * 3 each                            */
 };
 /*
  * The traceback's start cell of every pair (sw.cpp:116-127,155-170), found by a group of 8 lanes per pair reading the
@@ -38,8 +44,10 @@ struct TraceArgs {
  * here, the others are appended to the worklist launch_traceback walks.  Must precede launch_traceback on the stream.
  */
 cudaError_t launch_start(const TraceArgs &a, cudaStream_t stream);
-/* has_wide: some pair of the chunk has MGLSW_HOP_WIDE_MIN_STRIPS column strips or more (a pipelined fill launch): the kernel with the four-block hop */
-cudaError_t launch_traceback(const TraceArgs &a, bool has_wide, cudaStream_t stream);
+/* has_short / has_long: the chunk has units of lane groups of 8 / whole-warp units; has_wide: some pair has MGLSW_HOP_WIDE_MIN_STRIPS
+   column strips or more (a pipelined fill launch): the kernel with the four-block hop.  MGLSW_TRACE_ROUNDS + 1 launches for the
+   short pairs, one for the long ones */
+cudaError_t launch_traceback(const TraceArgs &a, bool has_short, bool has_long, bool has_wide, cudaStream_t stream);
 /* opt-in: SOFTCLIP / IGNORE pairs whose alt occurs verbatim in the ref take GATK's wrapper answer (last occurrence, all M);
    runs after launch_traceback on the same stream and overwrites offsets / n_ops / scratch of those pairs */
 cudaError_t launch_exact_match(const TraceArgs &a, cudaStream_t stream);

@@ -70,12 +70,34 @@ SW_HD W2 load_w2(const u32 *p)
  * 4-bit record per cell.  A block never extends below / right of the cell that asked for
  * it: the traceback only moves up and left.
  */
+/* n / d for n * d < 2^32 as one multiply: m = ceil(2^32 / d) (d >= 2; for d <= 1 the quotient is n itself and m is unused) */
+SW_HD u32 magic_u32(u32 d) { return d > 1u ? 0xffffffffu / d + 1u : 0u; }
+SW_HD u32 div_magic(u32 n, u32 d, u32 m)
+{
+#if SW_ON_DEVICE
+    return d > 1u ? __umulhi(n, m) : n;
+#else
+    return d > 1u ? (u32)(((u64)n * m) >> 32) : n;
+#endif
+}
+
 struct Replay {
     /* the unit's geometry, copied out of its descriptor once */
+
+    /* 0-based column -> (lane slot, register): sw_layout.h col_to_slot, the unit's divisors as multiplications */
+    SW_HD void slot_of(u32 col, u32 &slot, u32 &reg) const
+    {
+        const u32 wide = cr * (cb + 1);
+        if (col < wide) { slot = div_magic(col, cb + 1u, m_cb1); reg = col - slot * (cb + 1); }
+        else { const u32 c2 = col - wide; slot = cr + div_magic(c2, cb, m_cb); reg = c2 - (slot - cr) * cb; }
+    }
+
     const u32 *base;                     /* checkpoint regions of the warp, at this unit's lane group */
     const uint8_t *ref, *alt;            /* this pair's sequences */
     u32 G, K, KM, SC, LSW, RW, half, rbc; /* SC = sec_chunks(K), LSW / RW = words per lane slice / per region, rbc = row blocks per strip */
     u32 cb, cr;                          /* col_base, col_rem */
+    u32 m_cb1, m_cb, gsh;                /* column -> lane slot without a division: ceil(2^32 / (cb + 1)), ceil(2^32 / cb), log2(G) */
+    u32 swords;                          /* words of one strip's regions = rbc * RW */
     int match, mismatch, go, ge, bias, indel;
     u32 sh, msk;                         /* this pair's half of a checkpoint word: bits [sh, sh + 16) of a u16x2 unit, the whole word of an s32 unit */
     int ia, ib, ja, jb;
@@ -90,7 +112,9 @@ struct Replay {
         sh = s32 ? 0u : 16u * half_; msk = s32 ? 0xffffffffu : 0xffffu;
         G = G_; K = K_; KM = regs_mid(K_); SC = sec_chunks(K_); half = half_; rbc = u.rb_count;
         cb = u.col_base; cr = u.col_rem;
+        m_cb1 = magic_u32(cb + 1u); m_cb = magic_u32(cb); gsh = G_ == 32u ? 5u : 3u;
         LSW = lane_stride16(K_) * 4u; RW = region_words(K_);
+        swords = rbc * RW;
         base = ckpt + u.ckpt_off + (size_t)u.group * G_ * LSW;
         ref = arena + u.ref_off[half_]; alt = arena + u.alt_off[half_];
         match = c.s_match; mismatch = c.s_mismatch; go = c.s_go; ge = c.s_ge; bias = c.bias;
@@ -144,12 +168,8 @@ struct Replay {
             Lk[k] = 0; hv[k] = 0; ap[k] = nullptr;
             if (Ik > 0 && Jk > 0) {
                 u32 slot, reg;
-                {
-                    const u32 col = (u32)Jk - 1, wide = cr * (cb + 1);
-                    if (col < wide) { slot = col / (cb + 1); reg = col - slot * (cb + 1); }
-                    else { const u32 c2 = col - wide; slot = cr + c2 / cb; reg = c2 - (slot - cr) * cb; }
-                }
-                const u32 strip = slot / G, lane = slot - strip * G;
+                slot_of((u32)Jk - 1u, slot, reg);
+                const u32 strip = slot >> gsh, lane = slot - (strip << gsh);
                 const bool sub = reg >= KM;
                 const u32 k_lo = sub ? KM : 0u;
                 const int jc = (int)(slot < cr ? slot * (cb + 1) : cr * (cb + 1) + (slot - cr) * cb) + (int)k_lo;   /* = ja - 1 of Jk's block */
@@ -162,7 +182,7 @@ struct Replay {
                     u32 cs = strip, cl = lane, word = 0;
                     if (!sub) { word = 2; if (lane > 0) cl = lane - 1; else { cl = G - 1; cs = strip - 1; } }
                     const u32 tt = (u32)it + cl;                            /* the step at which lane cl worked on row it */
-                    ap[k] = base + (size_t)cs * rbc * RW + (size_t)cl * LSW + word + (size_t)(tt / MGLSW_RB) * RW + (tt % MGLSW_RB) * 4u;
+                    ap[k] = base + (size_t)cs * swords + (size_t)(cl * LSW + word + (tt % MGLSW_RB) * 4u) + (size_t)(tt / MGLSW_RB) * RW;
                 }
                 Lk[k] = L; S += L; Ik = it; Jk = jt;
             }
@@ -218,12 +238,8 @@ struct Replay {
     {
         /* (slot, register) of column J: sw_layout.h col_to_slot */
         u32 slot, reg;
-        {
-            const u32 col = (u32)J - 1, wide = cr * (cb + 1);
-            if (col < wide) { slot = col / (cb + 1); reg = col - slot * (cb + 1); }
-            else { const u32 c2 = col - wide; slot = cr + c2 / cb; reg = c2 - (slot - cr) * cb; }
-        }
-        const u32 strip = slot / G, lane = slot - strip * G;
+        slot_of((u32)J - 1u, slot, reg);
+        const u32 strip = slot >> gsh, lane = slot - (strip << gsh);
         const bool sub = reg >= KM;
         const u32 k_lo = sub ? KM : 0u;
         const int ja_ = (int)(slot < cr ? slot * (cb + 1) : cr * (cb + 1) + (slot - cr) * cb) + 1 + (int)k_lo;
@@ -238,7 +254,7 @@ struct Replay {
         if (!sub) { word = 2; if (lane > 0) cl = lane - 1; else { cl = G - 1; cs = strip - 1; } }
         const bool edge = ja_ == 1;                                /* matrix column 0: no checkpoint, sw.cpp:47-49 and :22-26,38 */
         /* slice of lane cl in region (cs, step / MGLSW_RB), entry step % MGLSW_RB, words word..word+1 */
-        const u32 *lp = base + (size_t)cs * rbc * RW + (size_t)cl * LSW + word;
+        const u32 *lp = base + (size_t)cs * swords + (size_t)(cl * LSW + word);
 
         /*
          * Every load of the block first, unconditional (indices clamped into the block, dead
@@ -540,6 +556,30 @@ struct Walker {
     }
 #undef SW_EMIT
 
+    /*
+     * Between two rebuilt blocks a walk is twelve words (WalkState): the unit's geometry is read again from its
+     * descriptor, the block's records are not needed once the walk has left it.  resume() = begin() with the saved
+     * scalars; what the walk has emitted so far is in the pair's scratch region already.
+     */
+    SW_HD void save(u32 sid, u32 out[12]) const
+    {
+        out[0] = sid; out[1] = (u32)I; out[2] = (u32)J; out[3] = (u32)run;
+        out[4] = state | (next << 8) | ((u32)mode << 16) | ((hk ? 1u : 0u) << 24);
+        out[5] = (u32)steplen; out[6] = (u32)cc; out[7] = (u32)r;
+        out[8] = (u32)hcur; out[9] = (u32)(ops_end - p); out[10] = hops; out[11] = (u32)start_score;
+    }
+    SW_HD void resume(const UnitDesc &u, u32 half, bool s32, u32 G, u32 K, const u32 *ckpt, const uint8_t *arena, const CellConsts &c,
+                      const u32 in[12], int strategy_, u32 *ops_end_, u64 *nib, u32 nstride)
+    {
+        rp.init(u, G, K, half, s32, ckpt, arena, c, nib, nstride);
+        strategy = strategy_; ops_end = ops_end_;
+        I = (int)in[1]; J = (int)in[2]; run = (int)in[3];
+        state = in[4] & 0xffu; next = (in[4] >> 8) & 0xffu; mode = (int)((in[4] >> 16) & 0xffu); hk = ((in[4] >> 24) & 1u) != 0;
+        steplen = (int)in[5]; cc = (int)in[6]; r = (int)in[7];
+        hcur = (int)in[8]; p = ops_end_ - in[9]; hops = in[10]; start_score = (int)in[11];
+        done = false;
+    }
+
     SW_HD PairResult finish()
     {
         PairResult res;
@@ -552,16 +592,27 @@ struct Walker {
 };
 
 /* one pair from start cell to CIGAR: what the emulator runs; the device drives Walkers itself (sw_traceback_kernel) */
+/* through_state: the walk is put away after every rebuilt block and taken up again by a fresh Walker, the way the
+   device's round kernels hand it from launch to launch (sw_trace_round_kernel) */
 SW_HD PairResult traceback_pair(const UnitDesc &u, u32 half, bool s32, u32 G, u32 K, const u32 *ckpt, const uint8_t *arena,
-                                const CellConsts &c, const StartCell &st, int strategy, u32 *ops_end, u64 *nib, u32 nstride)
+                                const CellConsts &c, const StartCell &st, int strategy, u32 *ops_end, u64 *nib, u32 nstride,
+                                bool through_state = false)
 {
     Walker w;
     w.begin(u, half, s32, G, K, ckpt, arena, c, st, strategy, ops_end, nib, nstride);
     const bool wide = u.nstrips >= MGLSW_HOP_WIDE_MIN_STRIPS;
-    for (;;) {
-        w.hop_phase(wide);
-        if (w.done) break;
+    w.hop_phase(wide);
+    while (!w.done) {
+        if (through_state) {
+            u32 rec[12];
+            w.save(0u, rec);
+            Walker v;
+            v.resume(u, half, s32, G, K, ckpt, arena, c, rec, strategy, ops_end, nib, nstride);
+            v.rp.builds = w.rp.builds;
+            w = v;
+        }
         w.build_phase();
+        w.hop_phase(wide);
     }
     return w.finish();
 }

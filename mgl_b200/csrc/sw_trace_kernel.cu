@@ -71,7 +71,7 @@ __global__ void __launch_bounds__(128) sw_start_kernel(const __grid_constant__ T
     const u32 sid = (blockIdx.x * 128u + threadIdx.x) >> 3;
     const u32 gl = threadIdx.x & 7u;
     const unsigned gmask = 0xffu << (threadIdx.x & 24u);
-    bool push = false;
+    bool push = false, is_long = false;
     StartCell sc;
     sc.i = sc.j = sc.seg = sc.score = 0;
     if (sid < 2u * a.n_units) {
@@ -81,6 +81,7 @@ __global__ void __launch_bounds__(128) sw_start_kernel(const __grid_constant__ T
         if ((u.flags & UNIT_ACTIVE) && p != NO_PAIR) {
             const bool s32 = (u.flags & UNIT_S32) != 0;
             const u32 G = (u.flags & UNIT_G32) ? MGLSW_G_LONG : MGLSW_G_SHORT;
+            is_long = (u.flags & UNIT_G32) != 0;
             const CellConsts &c = s32 ? a.c32 : a.c16;
             const int strategy = a.strategy[p];
             sc = start_cell_group(u, half, s32, G, u.regs, a.colbest + (size_t)(sid >> 1) * 4u, a.lastrow, strategy, gl, gmask);
@@ -112,73 +113,163 @@ __global__ void __launch_bounds__(128) sw_start_kernel(const __grid_constant__ T
         }
     }
     if (SCORE_ONLY) return;
-    /* one atomic per warp: its (at most four) pairs take consecutive worklist entries */
-    const unsigned pm = __ballot_sync(0xffffffffu, push);
-    if (pm == 0u) return;
+    /*
+     * Two lists in one array: pairs of lane groups of 8 from the front (they go through the round kernels), pairs of
+     * whole-warp units from the back (sw_traceback_kernel walks them from the start cell).  One atomic per warp and
+     * list: its (at most four) pairs take consecutive entries.
+     */
     const u32 wl = threadIdx.x & 31u;
-    u32 base = 0;
-    if (wl == (u32)(__ffs(pm) - 1)) base = atomicAdd(a.work_count, (u32)__popc(pm));
-    base = __shfl_sync(0xffffffffu, base, __ffs(pm) - 1);
-    if (push) {
-        const u32 k = base + (u32)__popc(pm & ((1u << wl) - 1u));
-        a.worklist[k] = sid;
-        a.startcell[k] = make_int4(sc.i, sc.j, sc.seg, sc.score);
+#pragma unroll
+    for (int which = 0; which < 2; which++) {
+        const unsigned pm = __ballot_sync(0xffffffffu, push && (int)is_long == which);
+        if (pm == 0u) continue;
+        u32 base = 0;
+        if (wl == (u32)(__ffs(pm) - 1)) base = atomicAdd(a.work_count + (which ? MGLSW_WC_LONG : 0), (u32)__popc(pm));
+        base = __shfl_sync(0xffffffffu, base, __ffs(pm) - 1);
+        if (push && (int)is_long == which) {
+            u32 k = base + (u32)__popc(pm & ((1u << wl) - 1u));
+            if (which) k = 2u * a.n_units - 1u - k;
+            a.worklist[k] = sid;
+            a.startcell[k] = make_int4(sc.i, sc.j, sc.seg, sc.score);
+        }
     }
 }
 
-/*
- * One lane per worklist entry: the pairs whose path has a gap, consecutive entries = neighbouring pair slots of one shape
- * bucket, whose checkpoints sit next to each other.  Each lane drives a Walker (sw_trace.h); once per round the warp
- * meets at a vote, so that the lanes that need a block rebuilt run the ONE replay site together.  Left to the hardware's
- * reconvergence the lanes drifted apart: the replay ran 19 times per warp with 4 lanes each where the slowest pair
- * needs 8 [B200, profiles/r19a]; which warps meet is decided below.  (Lanes that take the next entry off the list when their pair is done -- a grid of a
- * third or a quarter of the list -- keep the replay site fuller but were slower, alone and in the overlapped step:
- * profiles/r21a.)
- */
 #ifndef MGLSW_TRACE_THREADS
 #define MGLSW_TRACE_THREADS 128
 #endif
 #ifndef MGLSW_TRACE_MINB
 #define MGLSW_TRACE_MINB (512 / MGLSW_TRACE_THREADS)    /* 128 registers per thread */
 #endif
-template <bool HAS_WIDE>    /* false: the chunk has no pair of MGLSW_HOP_WIDE_MIN_STRIPS strips, the kernel carries no hopn code */
+
+/* one walk's identity from its pair slot, and the Walker set up on it: from the start cell, or from a saved state */
+struct WalkCtx { u32 p, flags, strips; };
+__device__ __forceinline__ WalkCtx walk_open(const TraceArgs &a, u32 sid, const int4 *start, const u32 *saved, Walker &w, u64 *nib)
+{
+    const UnitDesc &u = a.units[sid >> 1];
+    const u32 half = sid & 1u;
+    WalkCtx x;
+    x.p = u.pair[half]; x.flags = u.flags; x.strips = u.nstrips;
+    const bool s32 = (u.flags & UNIT_S32) != 0;
+    const u32 G = (u.flags & UNIT_G32) ? MGLSW_G_LONG : MGLSW_G_SHORT;
+    u32 *end = a.scratch + a.ops_end[x.p];
+    if (start) {
+        StartCell sc;
+        sc.i = start->x; sc.j = start->y; sc.seg = start->z; sc.score = start->w;
+        w.begin(u, half, s32, G, u.regs, a.ckpt, a.arena, s32 ? a.c32 : a.c16, sc, a.strategy[x.p], end, nib, (u32)MGLSW_TRACE_THREADS);
+    } else {
+        w.resume(u, half, s32, G, u.regs, a.ckpt, a.arena, s32 ? a.c32 : a.c16, saved, a.strategy[x.p], end, nib, (u32)MGLSW_TRACE_THREADS);
+    }
+    return x;
+}
+
+/*
+ * Round r of the pairs of lane groups of 8 (short paths: a few hops between two rebuilt blocks).  One lane per entry
+ * of round r's list; every entry needs exactly one block rebuilt now, so the replay site -- two thirds of the
+ * traceback's instructions -- runs with every live lane, where one launch that kept a pair on its lane until the end
+ * ran it with a third of them (the pairs of a warp need 1 to 10 rebuilds, 2.7 on average, and the warp waited for the
+ * slowest).  Then the walk hops on; a pair that reaches the matrix edge is written out, the others are put away
+ * (WalkState) on round r + 1's list, densely.  FIRST: entries come from sw_start_kernel (start cells); the walk
+ * begins with hops.
+ */
+template <bool FIRST>
+__global__ void __launch_bounds__(MGLSW_TRACE_THREADS, MGLSW_TRACE_MINB) sw_trace_round_kernel(const __grid_constant__ TraceArgs a, const u32 round)
+{
+    __shared__ u64 s_nib[MGLSW_TRACE_BUF * MGLSW_TRACE_THREADS];
+    const u32 k = blockIdx.x * blockDim.x + threadIdx.x;
+    const u32 count = __ldcg(a.work_count + round);
+    if ((k & ~31u) >= count) return;                /* whole warps leave; a lane past the end stays with its warp, idle */
+    const bool live = k < count;
+    const uint4 *in = a.wstate[round & 1u];
+    uint4 *out = a.wstate[(round + 1u) & 1u];
+    Walker w;
+    w.done = true;
+    WalkCtx x;
+    x.p = 0; x.flags = 0; x.strips = 0;
+    u32 sid = 0;
+    if (live) {
+        if (FIRST) {
+            sid = a.worklist[k];
+            const int4 s4 = a.startcell[k];
+            x = walk_open(a, sid, &s4, nullptr, w, s_nib + threadIdx.x);
+            w.hop_phase(false);
+        } else {
+            __align__(16) u32 rec[12];
+            *reinterpret_cast<uint4 *>(rec) = __ldcg(in + 3 * (size_t)k);
+            *reinterpret_cast<uint4 *>(rec + 4) = __ldcg(in + 3 * (size_t)k + 1);
+            *reinterpret_cast<uint4 *>(rec + 8) = __ldcg(in + 3 * (size_t)k + 2);
+            sid = rec[0];
+            x = walk_open(a, sid, nullptr, rec, w, s_nib + threadIdx.x);
+        }
+    }
+    __syncwarp();
+    if (!w.done) { w.build_phase(); w.hop_phase(false); }
+    if (live && w.done) {
+        const PairResult r = w.finish();
+        a.offsets[x.p] = r.offset;
+        a.n_ops[x.p] = r.n_ops;
+    }
+    const bool push = live && !w.done;
+    const unsigned pm = __ballot_sync(0xffffffffu, push);
+    if (pm == 0u) return;
+    const u32 wl = threadIdx.x & 31u;
+    u32 base = 0;
+    if (wl == (u32)(__ffs(pm) - 1)) base = atomicAdd(a.work_count + round + 1u, (u32)__popc(pm));
+    base = __shfl_sync(0xffffffffu, base, __ffs(pm) - 1);
+    if (push) {
+        const u32 q = base + (u32)__popc(pm & ((1u << wl) - 1u));
+        __align__(16) u32 rec[12];
+        w.save(sid, rec);
+        __stcg(out + 3 * (size_t)q, *reinterpret_cast<uint4 *>(rec));
+        __stcg(out + 3 * (size_t)q + 1, *reinterpret_cast<uint4 *>(rec + 4));
+        __stcg(out + 3 * (size_t)q + 2, *reinterpret_cast<uint4 *>(rec + 8));
+    }
+}
+
+/*
+ * One lane per pair until its walk ends: the pairs the round kernels have not finished after MGLSW_TRACE_ROUNDS
+ * rebuilds (RESUME: from their saved state; a few per cent of config 2's), and the pairs of whole-warp units (from their
+ * start cells, at the back of the worklist).  Each lane drives a Walker; two choices per warp, so that its lanes keep
+ * running the same code [B200, profiles/r22b, r22c; traceback alone, before the round kernels]:
+ * - lane groups of 8 meet at a vote once per round, so that the lanes that need a block rebuilt run the ONE replay site
+ *   together.  Left to the hardware's reconvergence the lanes drifted apart: the replay ran 19 times per warp with 4
+ *   lanes each where the slowest pair needs 8 (config 2: 5.6 -> 3.8 ms per 1 M pairs; profiles/r19a).  On long paths
+ *   every round lasts as long as the longest clean stretch among 32 lanes, so warps of whole-warp units let their
+ *   lanes run free, as the hardware reconverges them (config 3: 2.9 ms per 100 k pairs free, 5.1 ms met);
+ * - hops of MGLSW_HOP_BLOCKS blocks per round trip pay where the chain of round trips is what a pair waits for
+ *   (config 4's shapes; config 5 33 -> 29 ms per 1 M pairs); elsewhere their instructions cost more than the round
+ *   trips they save (config 3 2.9 -> 4.8 ms; config 2's overlapped step 15.8 -> 16.2 ms).
+ * (Lanes that take the next entry off the list when their pair is done -- a grid of a third or a quarter of the list --
+ * keep the replay site fuller but were slower, alone and in the overlapped step: profiles/r21a.)
+ */
+template <bool HAS_WIDE, bool RESUME>    /* HAS_WIDE false: no pair of MGLSW_HOP_WIDE_MIN_STRIPS strips in the chunk, the kernel carries no four-block hop */
 __global__ void __launch_bounds__(MGLSW_TRACE_THREADS, MGLSW_TRACE_MINB) sw_traceback_kernel(const __grid_constant__ TraceArgs a)
 {
     __shared__ u64 s_nib[MGLSW_TRACE_BUF * MGLSW_TRACE_THREADS];   /* the replayed block: records and boundary H values, one column per thread */
     const u32 k = blockIdx.x * blockDim.x + threadIdx.x;
-    const u32 count = __ldcg(a.work_count);
+    const u32 count = __ldcg(a.work_count + (RESUME ? MGLSW_TRACE_ROUNDS : MGLSW_WC_LONG));
     if ((k & ~31u) >= count) return;                /* whole warps leave; a lane past the end stays with its warp, idle */
     const bool live = k < count;
-    u32 p = 0, unit_flags = 0, strips = 0;
     Walker w;
     w.done = true;
+    WalkCtx x;
+    x.p = 0; x.flags = 0; x.strips = 0;
     if (live) {
-        const u32 sid = a.worklist[k];
-        const int4 s4 = a.startcell[k];
-        StartCell sc;
-        sc.i = s4.x; sc.j = s4.y; sc.seg = s4.z; sc.score = s4.w;
-        const UnitDesc &u = a.units[sid >> 1];
-        const u32 half = sid & 1u;
-        p = u.pair[half];
-        unit_flags = u.flags;
-        strips = u.nstrips;
-        const bool s32 = (u.flags & UNIT_S32) != 0;
-        const u32 G = (u.flags & UNIT_G32) ? MGLSW_G_LONG : MGLSW_G_SHORT;
-        w.begin(u, half, s32, G, u.regs, a.ckpt, a.arena, s32 ? a.c32 : a.c16, sc, a.strategy[p], a.scratch + a.ops_end[p],
-                s_nib + threadIdx.x, (u32)MGLSW_TRACE_THREADS);
+        if (RESUME) {
+            const uint4 *in = a.wstate[MGLSW_TRACE_ROUNDS & 1];
+            __align__(16) u32 rec[12];
+            *reinterpret_cast<uint4 *>(rec) = __ldcg(in + 3 * (size_t)k);
+            *reinterpret_cast<uint4 *>(rec + 4) = __ldcg(in + 3 * (size_t)k + 1);
+            *reinterpret_cast<uint4 *>(rec + 8) = __ldcg(in + 3 * (size_t)k + 2);
+            x = walk_open(a, rec[0], nullptr, rec, w, s_nib + threadIdx.x);
+        } else {
+            const u32 e = 2u * a.n_units - 1u - k;
+            const int4 s4 = a.startcell[e];
+            x = walk_open(a, a.worklist[e], &s4, nullptr, w, s_nib + threadIdx.x);
+        }
     }
-    /*
-     * Two choices per warp, so that its lanes keep running the same code [B200, profiles/r22b, r22c; traceback alone]:
-     * - the meeting point pays for short paths (lane groups of 8: at most 192 columns, a few hops between two rebuilt
-     *   blocks): config 2 5.6 -> 3.8 ms per 1 M pairs.  On long paths every round lasts as long as the longest clean
-     *   stretch among 32 lanes, so warps of whole-warp units let their lanes run free, as the hardware reconverges
-     *   them (config 3: 2.9 ms per 100 k pairs free, 5.1 ms met);
-     * - hops of MGLSW_HOP_BLOCKS blocks per round trip pay where the chain of round trips is what a pair waits for
-     *   (config 4's shapes; config 5 33 -> 29 ms per 1 M pairs); elsewhere their instructions cost more than the round
-     *   trips they save (config 3 2.9 -> 4.8 ms; config 2's overlapped step 15.8 -> 16.2 ms).
-     */
-    const bool meet = __all_sync(0xffffffffu, !live || !(unit_flags & UNIT_G32));
-    const bool wide = HAS_WIDE && __all_sync(0xffffffffu, !live || strips >= MGLSW_HOP_WIDE_MIN_STRIPS);
+    const bool meet = __all_sync(0xffffffffu, !live || !(x.flags & UNIT_G32));
+    const bool wide = HAS_WIDE && __all_sync(0xffffffffu, !live || x.strips >= MGLSW_HOP_WIDE_MIN_STRIPS);
     for (;;) {
         if (!w.done) w.hop_phase(wide);                                /* each lane on its own */
         if (meet) { if (__ballot_sync(0xffffffffu, !w.done) == 0u) break; }   /* leaves when every lane is done */
@@ -187,8 +278,8 @@ __global__ void __launch_bounds__(MGLSW_TRACE_THREADS, MGLSW_TRACE_MINB) sw_trac
     }
     if (!live) return;
     const PairResult r = w.finish();
-    a.offsets[p] = r.offset;
-    a.n_ops[p] = r.n_ops;
+    a.offsets[x.p] = r.offset;
+    a.n_ops[x.p] = r.n_ops;
 }
 
 /*
@@ -252,19 +343,27 @@ cudaError_t launch_endpoints(const TraceArgs &a, cudaStream_t stream)
 cudaError_t launch_start(const TraceArgs &a, cudaStream_t stream)
 {
     if (a.n_units == 0) return cudaSuccess;
-    cudaError_t e = cudaMemsetAsync(a.work_count, 0, sizeof(u32), stream);
+    cudaError_t e = cudaMemsetAsync(a.work_count, 0, MGLSW_WC_WORDS * sizeof(u32), stream);
     if (e != cudaSuccess) return e;
     sw_start_kernel<false><<<(2u * a.n_units * 8u + 127) / 128, 128, 0, stream>>>(a);
     return cudaGetLastError();
 }
 
-cudaError_t launch_traceback(const TraceArgs &a, bool has_wide, cudaStream_t stream)
+cudaError_t launch_traceback(const TraceArgs &a, bool has_short, bool has_long, bool has_wide, cudaStream_t stream)
 {
     if (a.n_units == 0) return cudaSuccess;
-    /* the worklist's length is on the device: the grid covers every pair slot, warps beyond the list leave at once */
+    /* the lists' lengths are on the device: every grid covers every pair slot, warps beyond a list leave at once */
     const u32 blocks = (2u * a.n_units + MGLSW_TRACE_THREADS - 1) / MGLSW_TRACE_THREADS;
-    if (has_wide) sw_traceback_kernel<true><<<blocks, MGLSW_TRACE_THREADS, 0, stream>>>(a);
-    else sw_traceback_kernel<false><<<blocks, MGLSW_TRACE_THREADS, 0, stream>>>(a);
+    if (has_short) {
+        sw_trace_round_kernel<true><<<blocks, MGLSW_TRACE_THREADS, 0, stream>>>(a, 0u);
+        for (u32 r = 1; r < MGLSW_TRACE_ROUNDS; r++) sw_trace_round_kernel<false><<<blocks, MGLSW_TRACE_THREADS, 0, stream>>>(a, r);
+        sw_traceback_kernel<false, true><<<blocks, MGLSW_TRACE_THREADS, 0, stream>>>(a);
+    }
+    if (has_long) {
+        const u32 lb = (a.n_units + MGLSW_TRACE_THREADS - 1) / MGLSW_TRACE_THREADS;      /* whole-warp units hold one pair each */
+        if (has_wide) sw_traceback_kernel<true, false><<<lb, MGLSW_TRACE_THREADS, 0, stream>>>(a);
+        else sw_traceback_kernel<false, false><<<lb, MGLSW_TRACE_THREADS, 0, stream>>>(a);
+    }
     return cudaGetLastError();
 }
 

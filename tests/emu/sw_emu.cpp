@@ -28,6 +28,7 @@ using namespace mglsw;
 namespace {
 
 int g_device_plan = 0;
+int g_through_state = 0;      /* 1: every walk is saved and resumed between two rebuilt blocks (Walker::save / resume) */
 int g_clean_shortcut = 1;      /* the whole-path shortcut of sw_start_kernel (sw_trace.h clean_path); 0: every pair is walked */
 
 /*
@@ -149,6 +150,7 @@ extern "C" {
 /* 1: plan with the device planner's stage bodies (sw_plan_dev.h) instead of the host planner (sw_plan.cpp) */
 void emu_use_device_plan(int on) { g_device_plan = on; }
 void emu_use_clean_shortcut(int on) { g_clean_shortcut = on; }
+void emu_use_through_state(int on) { g_through_state = on; }
 
 /*
  * Both planners on one chunk: sizes and bucket structure must agree exactly (the unit arrays may differ in the
@@ -259,7 +261,7 @@ int emu_align_batch(int n, const uint8_t *arena, const uint64_t *ref_off, const 
             if (clean && stats) stats[6]++;
         }
         if (!clean) {
-            r = traceback_pair(u, half, s32, G, u.regs, ckpt.data(), arena, cc, sc, strategies[p], end, nibbuf, 1u);
+            r = traceback_pair(u, half, s32, G, u.regs, ckpt.data(), arena, cc, sc, strategies[p], end, nibbuf, 1u, g_through_state != 0);
         }
         if (stats) { stats[4] += r.builds; stats[5] += r.hops; }
         if (const char *dump = std::getenv("EMU_DUMP")) {        /* developer aid: per-pair replay / hop counts in thread order */

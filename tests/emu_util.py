@@ -48,12 +48,13 @@ def pack_batch(pairs):
     return arena, offs[0::2].copy(), ref_len, offs[1::2].copy(), alt_len
 
 
-def emu_align(pairs, params, strategies, allow_s16=True, device_plan=False, clean_shortcut=True):
+def emu_align(pairs, params, strategies, allow_s16=True, device_plan=False, clean_shortcut=True, through_state=False):
     """-> list of (cigar text, offset), plus stats dict.  device_plan: the chunk is planned by the device planner's
     stage bodies (mgl_b200/csrc/sw_plan_dev.h) instead of the host planner (sw_plan.cpp)."""
     lib = _load()
     lib.emu_use_device_plan(1 if device_plan else 0)
     lib.emu_use_clean_shortcut(1 if clean_shortcut else 0)
+    lib.emu_use_through_state(1 if through_state else 0)
     n = len(pairs)
     arena, ro, rl, ao, al = pack_batch(pairs)
     st = np.asarray(strategies, dtype=np.int32)

@@ -17,10 +17,11 @@ def _by_params(golden):
     return by
 
 
-@pytest.mark.parametrize("allow_s16,clean_shortcut", [(True, True), (False, True), (True, False)])
-def test_emulated_kernels_match_golden(golden, allow_s16, clean_shortcut):
+@pytest.mark.parametrize("allow_s16,clean_shortcut,through_state", [(True, True, False), (False, True, False), (True, False, False), (True, False, True)])
+def test_emulated_kernels_match_golden(golden, allow_s16, clean_shortcut, through_state):
     """clean_shortcut: paths without a gap are written down from the start cell alone (sw_trace.h clean_path, what
-    sw_start_kernel does on the device); off: every pair is walked through hops and block replays"""
+    sw_start_kernel does on the device); off: every pair is walked through hops and block replays; through_state: the
+    walk is saved and resumed between two rebuilt blocks, as the device's round kernels hand it from launch to launch"""
     by = _by_params(golden)
     total = clean = 0
     # both arithmetics on the two BASELINE score sets; the 16-bit path additionally on every other score set
@@ -29,7 +30,7 @@ def test_emulated_kernels_match_golden(golden, allow_s16, clean_shortcut):
         cs = by[p]
         pairs = [(c["ref"].encode("latin1"), c["alt"].encode("latin1")) for c in cs]
         for si, s in enumerate(golden["strategies"]):
-            res, st = E.emu_align(pairs, p, s, allow_s16, clean_shortcut=clean_shortcut)
+            res, st = E.emu_align(pairs, p, s, allow_s16, clean_shortcut=clean_shortcut, through_state=through_state)
             assert (st["s16"] > 0) == allow_s16
             clean += st["clean"]
             bad = [(c["ref"], c["alt"], p, s, r, tuple(c["expect"][si])) for c, r in zip(cs, res) if r != tuple(c["expect"][si])]
