@@ -10,6 +10,7 @@
 #include <cstring>
 #include <mutex>
 #include <thread>
+#include <sched.h>
 
 #include "../../include/mgl_sw.h"
 #include "sw_cell.h"
@@ -232,11 +233,22 @@ void Engine::choose_slots(u64 total_est, int64_t n)
  * How many pairs the chunk starting at `first` takes: at most chunk_pairs, and as many as keep
  * the estimated checkpoints inside the budget.
  */
+/* CPUs this process may run on (a rank of an 8-GPU job is often confined to a few): sizes the short-lived scan threads */
+static unsigned allowed_cpus()
+{
+    cpu_set_t set;
+    CPU_ZERO(&set);
+    if (sched_getaffinity(0, sizeof set, &set) == 0) { const int c = CPU_COUNT(&set); if (c > 0) return (unsigned)c; }
+    return std::max(1u, std::thread::hardware_concurrency());
+}
+
 /* checkpoint bytes of one pair with the planner's geometry (sw_plan.cpp), as if it ran alone in 32-bit arithmetic */
 static inline u64 pair_ckpt_bytes(u32 tl, u32 ql)
 {
-    const u32 G = ql <= (u32)MGLSW_G_SHORT * MGLSW_KMAX ? MGLSW_G_SHORT : MGLSW_G_LONG;
-    const u32 ns = G == MGLSW_G_SHORT ? 1u : ceil_div_u32(ql, (u32)MGLSW_G_LONG * MGLSW_KMAX);
+    if (ql <= (u32)MGLSW_G_SHORT * MGLSW_KMAX)       /* one strip of 8 lanes: no division on the path every short pair of a 1 M-pair call takes */
+        return (u64)row_blocks(tl, MGLSW_G_SHORT) * lane_stride16((ql + MGLSW_G_SHORT - 1u) / MGLSW_G_SHORT) * 16u * MGLSW_G_SHORT;
+    const u32 G = MGLSW_G_LONG;
+    const u32 ns = ceil_div_u32(ql, (u32)MGLSW_G_LONG * MGLSW_KMAX);
     const u32 K = regs_per_lane(ql, ns * G);
     return (u64)ns * row_blocks(tl, G) * lane_stride16(K) * 16u * G;
 }
@@ -722,7 +734,7 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
     u64 total_len = 0, total_est = 0;
     u64 span_lo = ~0ull, span_hi = 0;                 /* the byte range of the caller's arena this batch touches (wrapped offsets are refused by plan_range) */
     estpre_.resize((size_t)in.n);                     /* per slice: inclusive prefix sums of the per-pair checkpoint estimate (bytes) */
-    const int T = in.n > 65536 ? (scan_threads > 0 ? scan_threads : (int)std::min<unsigned>(8u, std::max(1u, std::thread::hardware_concurrency() / 2))) : 1;
+    const int T = in.n > 65536 ? (scan_threads > 0 ? scan_threads : (int)std::min<unsigned>(16u, std::max(1u, allowed_cpus() / 2))) : 1;
     std::vector<u64> slice_off((size_t)T + 1, 0);
     {
         std::vector<u32> tmax((size_t)T, 0);
