@@ -15,6 +15,8 @@
 #ifndef MGLSW_TRACE_ROUNDS
 #define MGLSW_TRACE_ROUNDS 5        /* rebuilt blocks a short pair gets in the round kernels, one launch each, before a lane takes it to the end (sw_trace_kernel.cu) */
 #endif
+#define MGLSW_TRACE_ROUNDS_MIN_UNITS 1024   /* chunks of at most this many units skip the round kernels: one traceback launch */
+#define MGLSW_DEV_PLAN_MIN_PAIRS 1024   /* batches of at most this many pairs are planned on the host (sw_engine.cu) */
 #define MGLSW_WC_LONG 14           /* work_count word of the whole-warp units' list */
 #define MGLSW_WC_WORDS 16
 #define MGLSW_PIPE_MIN_STRIPS 4   /* pairs of at least this many strips run one per block, strips pipelined over its warps */

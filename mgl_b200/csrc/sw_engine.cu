@@ -642,6 +642,7 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed, bo
     t.work_count = (u32 *)ws.worklist.p;
     t.worklist = (u32 *)ws.worklist.p + MGLSW_WC_WORDS;
     t.startcell = (int4 *)ws.startcell.p;
+    t.no_rounds = cd.plan.n_units <= MGLSW_TRACE_ROUNDS_MIN_UNITS ? 1u : 0u;
     t.wstate[0] = (uint4 *)ws.wstate.p;
     t.wstate[1] = (uint4 *)ws.wstate.p + ((size_t)cd.plan.n_units * 2 + 1) * 3;
     if (score_only) {
@@ -658,6 +659,7 @@ int Engine::run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed, bo
     if ((e = launch_start(t, pt)) != cudaSuccess) return cuda_fail(e, "start-cell launch");
     bool has_short = false, has_long = false;
     for (const Launch &L : cd.plan.launches) { if (L.G == MGLSW_G_LONG) has_long = true; else has_short = true; }
+    if (t.no_rounds) { has_long = has_long || has_short; has_short = false; }
     if ((e = launch_traceback(t, has_short, has_long, pipe_units > 0, pt)) != cudaSuccess) return cuda_fail(e, "traceback launch");
     if (exact_shortcut) {
         if ((e = launch_exact_match(t, pt)) != cudaSuccess) return cuda_fail(e, "exact-match launch");
@@ -862,7 +864,9 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
      * fill kernel drains, about one plan per chunk time, so the look-ahead must cover several chunks), and this
      * thread reads back a summary per chunk.
      */
-    const bool dev_plan = host_plan == 0 && pack_arena == 0;
+    /* a batch of a few pairs (alignNative is a batch of one) is planned here, on the calling thread, in microseconds: the
+       planning kernel's grid barriers and the summary's way back cost 0.17 ms however small the chunk */
+    const bool dev_plan = host_plan == 0 && pack_arena == 0 && in.n > MGLSW_DEV_PLAN_MIN_PAIRS;
     const int DEV_AHEAD = 7;
     std::vector<std::pair<int64_t, int64_t>> bounds;
     int nthreads = plan_threads > 0 ? plan_threads : (int)std::min<unsigned>(8u, std::max(1u, std::thread::hardware_concurrency() / 2));

@@ -37,6 +37,8 @@ struct TraceArgs {
     u32 *worklist;            /* 2 * n_units: pair slot (2 * unit + half)        */
     int4 *startcell;          /* 2 * n_units: {i, j, seg, score} (StartCell, sw_trace.h) */
     uint4 *wstate[2];         /* 2 * n_units * 3 each                            */
+    u32 no_rounds;            /* a small chunk (one pair of alignNative, say): every pair goes on the back list and is walked by one
+                                 launch -- six more launches would cost more than the lanes they save */
 };
 /*
  * The traceback's start cell of every pair (sw.cpp:116-127,155-170), found by a group of 8 lanes per pair reading the

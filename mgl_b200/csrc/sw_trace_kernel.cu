@@ -81,7 +81,7 @@ __global__ void __launch_bounds__(128) sw_start_kernel(const __grid_constant__ T
         if ((u.flags & UNIT_ACTIVE) && p != NO_PAIR) {
             const bool s32 = (u.flags & UNIT_S32) != 0;
             const u32 G = (u.flags & UNIT_G32) ? MGLSW_G_LONG : MGLSW_G_SHORT;
-            is_long = (u.flags & UNIT_G32) != 0;
+            is_long = (u.flags & UNIT_G32) != 0 || a.no_rounds != 0u;
             const CellConsts &c = s32 ? a.c32 : a.c16;
             const int strategy = a.strategy[p];
             sc = start_cell_group(u, half, s32, G, u.regs, a.colbest + (size_t)(sid >> 1) * 4u, a.lastrow, strategy, gl, gmask);
@@ -360,7 +360,8 @@ cudaError_t launch_traceback(const TraceArgs &a, bool has_short, bool has_long, 
         sw_traceback_kernel<false, true><<<blocks, MGLSW_TRACE_THREADS, 0, stream>>>(a);
     }
     if (has_long) {
-        const u32 lb = (a.n_units + MGLSW_TRACE_THREADS - 1) / MGLSW_TRACE_THREADS;      /* whole-warp units hold one pair each */
+        /* whole-warp units hold one pair each; a small chunk has every pair slot on this list */
+        const u32 lb = ((a.no_rounds ? 2u : 1u) * a.n_units + MGLSW_TRACE_THREADS - 1) / MGLSW_TRACE_THREADS;
         if (has_wide) sw_traceback_kernel<true, false><<<lb, MGLSW_TRACE_THREADS, 0, stream>>>(a);
         else sw_traceback_kernel<false, false><<<lb, MGLSW_TRACE_THREADS, 0, stream>>>(a);
     }
