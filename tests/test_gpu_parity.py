@@ -108,6 +108,42 @@ def test_fuzz_vs_oracle(sw, oracle):
         _check(sw, oracle, pairs, params, strategies)
 
 
+@pytest.mark.parametrize("params", [(10, -15, -30, -5), (200, -150, -260, -11), (2, -3, -1, -4)])
+def test_fuzz_large_batches_through_the_round_kernels(sw, oracle, params):
+    """batches of more than MGLSW_TRACE_ROUNDS_MIN_UNITS units: the short pairs' walks go from launch to launch
+    (sw_trace_round_kernel, Walker::save / resume) -- all four strategies, degenerate alphabets, gaps at the edges,
+    in 16-bit and in 32-bit arithmetic, in one chunk and in several"""
+    rng = random.Random(hash(params) & 0xffff)
+    pairs = []
+    for k in range(7000):
+        alpha = rng.choice([b"A", b"AC", b"ACGT", b"ACGTN"])
+        ref = bytes(rng.choice(alpha) for _ in range(rng.randint(1, 220)))
+        kind = rng.random()
+        if kind < 0.6:
+            i = rng.randrange(len(ref)); j = rng.randint(i + 1, len(ref))
+            alt = bytearray(ref[i:j][:190])
+            for _ in range(rng.randint(0, 4)):
+                q = rng.randrange(len(alt))
+                what = rng.random()
+                if what < 0.4: alt[q] = rng.choice(alpha)
+                elif what < 0.7 and len(alt) < 190: alt[q:q] = bytes(rng.choice(alpha) for _ in range(rng.randint(1, 9)))
+                elif len(alt) > 12: del alt[q:q + rng.randint(1, 9)]
+            alt = bytes(alt) or b"A"
+        else:
+            alt = bytes(rng.choice(alpha) for _ in range(rng.randint(1, 190)))
+        pairs.append((ref, alt))
+    strategies = np.array([(1, 2, 4, 8)[k % 4] for k in range(len(pairs))], dtype=np.int32)
+    for chunk in (1 << 16, 3000):
+        sw.set_option("chunk_pairs", chunk)
+        try:
+            res = _check(sw, oracle, pairs, params, strategies)
+        finally:
+            sw.set_option("chunk_pairs", 1 << 16)
+        # the start kernel, five round launches and the final one on top of scan, scan, compact: per chunk (the last,
+        # partial chunk may be small enough for the single launch)
+        assert res.stats["other_launches"] >= 10 * max(1, res.stats["chunks"] - 1), res.stats
+
+
 def test_empty_and_invalid_inputs(sw):
     from mgl_b200 import native
     res = sw.align_batch([], (10, -15, -30, -5), 1)
