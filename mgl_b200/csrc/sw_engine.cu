@@ -91,7 +91,7 @@ void WorkSlot::release()
     ckpt.release(); carry.release(); lastrow.release(); colbest.release(); scratch.release();
     startcell.release(); worklist.release(); wstate.release();
     offsets.release(); n_ops.release(); starts.release(); tiles.release(); ops.release(); score3.release(); n_chars.release();
-    h_n_ops.release(); h_total.release();
+    h_n_ops.release(); h_total.release(); h_res.release(); h_ops.release();
     if (ev_counts) cudaEventDestroy(ev_counts);
     if (ev_done) cudaEventDestroy(ev_done);
     if (ev_fill) cudaEventDestroy(ev_fill);
@@ -777,6 +777,21 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         const cudaError_t pe = cudaPointerGetAttributes(&pa, in.arena);
         arena_pageable_ = pe != cudaSuccess || pa.type == cudaMemoryTypeUnregistered;
         if (pe != cudaSuccess) cudaGetLastError();
+        /*
+         * Result arrays in pageable memory (a JVM's buffers): a device-to-host copy into them is staged by the driver and
+         * only returns when the chunk's kernels have finished -- the thread that launches the chunks would wait for every one
+         * of them and nothing would overlap (config 2: 33.7 ms per 1 M pairs).  Such results come home into pinned buffers
+         * of the work slot and are copied out by this thread when the chunk is collected.
+         */
+        auto pageable = [](const void *p) {
+            if (!p) return false;
+            cudaPointerAttributes a;
+            const cudaError_t x = cudaPointerGetAttributes(&a, p);
+            if (x != cudaSuccess) { cudaGetLastError(); return true; }
+            return a.type == cudaMemoryTypeUnregistered;
+        };
+        res_pageable_ = pageable(so ? (const void *)out.score3 : (const void *)out.offsets);
+        ops_pageable_ = !so && pageable(tx ? (const void *)out.text : (const void *)out.ops);
     }
     /* checkpoint estimate of pairs [0, x) */
     auto est_before = [&](int64_t x) -> u64 {
@@ -830,13 +845,19 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         f.busy = false;
         cudaError_t ee;
         if ((ee = cudaEventSynchronize(ws.ev_counts)) != cudaSuccess) return cuda_fail(ee, "chunk execution");
-        if (so) return MGL_SW_OK;                         /* the three words per pair came home with ev_counts */
+        if (so) {                                         /* the three words per pair came home with ev_counts */
+            if (res_pageable_) std::memcpy(out.score3 + 3 * f.first, ws.h_res.p, (size_t)f.n * 3 * sizeof(int));
+            return MGL_SW_OK;
+        }
         const u32 *cnt = (const u32 *)ws.h_n_ops.p;
         const u64 total = cnt[f.n];
+        if (res_pageable_) std::memcpy(out.offsets + f.first, ws.h_res.p, (size_t)f.n * sizeof(int));   /* home since ev_counts */
+        void *dst = nullptr;
         if (!overflow && ops_running + total <= out_cap) {
             if (total) {
-                void *dst = tx ? (void *)(out.text + ops_running) : (void *)(out.ops + ops_running);
-                if ((ee = cudaMemcpyAsync(dst, ws.ops.p, total * esz, cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess)
+                dst = tx ? (void *)(out.text + ops_running) : (void *)(out.ops + ops_running);
+                if (ops_pageable_ && (ee = ws.h_ops.reserve(total * esz)) != cudaSuccess) return cuda_fail(ee, "pinned alloc");
+                if ((ee = cudaMemcpyAsync(ops_pageable_ ? ws.h_ops.p : dst, ws.ops.p, total * esz, cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess)
                     return cuda_fail(ee, "D2H ops");
                 bs.d2h_bytes += total * esz;
             }
@@ -847,6 +868,7 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         for (u32 k = 0; k < f.n; k++) { run += cnt[k]; out.cigar_start[f.first + k + 1] = run; }
         ops_running = run;
         if ((ee = cudaEventSynchronize(ws.ev_done)) != cudaSuccess) return cuda_fail(ee, "D2H ops");
+        if (ops_pageable_ && dst) std::memcpy(dst, ws.h_ops.p, total * esz);
         return MGL_SW_OK;
     };
 
@@ -974,7 +996,8 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         if ((rc = run_chunk(cd, ws, bs, false, so, tx)) != MGL_SW_OK) break;
         const u32 n = cd.n;
         if (so) {
-            if ((e = cudaMemcpyAsync(out.score3 + 3 * first, ws.score3.p, (size_t)n * 3 * sizeof(int), cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess) { rc = cuda_fail(e, "D2H scores"); break; }
+            if (res_pageable_ && (e = ws.h_res.reserve((size_t)n * 3 * sizeof(int))) != cudaSuccess) { rc = cuda_fail(e, "pinned alloc"); break; }
+            if ((e = cudaMemcpyAsync(res_pageable_ ? ws.h_res.p : (void *)(out.score3 + 3 * first), ws.score3.p, (size_t)n * 3 * sizeof(int), cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess) { rc = cuda_fail(e, "D2H scores"); break; }
             bs.d2h_bytes += (size_t)n * 12;
             cudaEventRecord(ws.ev_counts, ws.post);
             cudaEventRecord(ws.ev_post, ws.post);
@@ -983,7 +1006,8 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
             release_upto(c - NS + 2);
             continue;
         }
-        if ((e = cudaMemcpyAsync(out.offsets + first, ws.offsets.p, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess) { rc = cuda_fail(e, "D2H offsets"); break; }
+        if (res_pageable_ && (e = ws.h_res.reserve((size_t)n * sizeof(int))) != cudaSuccess) { rc = cuda_fail(e, "pinned alloc"); break; }
+        if ((e = cudaMemcpyAsync(res_pageable_ ? ws.h_res.p : (void *)(out.offsets + first), ws.offsets.p, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess) { rc = cuda_fail(e, "D2H offsets"); break; }
         if ((e = cudaMemcpyAsync(ws.h_n_ops.p, tx ? ws.n_chars.p : ws.n_ops.p, (size_t)n * sizeof(u32), cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess) { rc = cuda_fail(e, "D2H counts"); break; }
         if ((e = cudaMemcpyAsync((u32 *)ws.h_n_ops.p + n, (u32 *)ws.starts.p + n, sizeof(u32), cudaMemcpyDeviceToHost, ws.post)) != cudaSuccess) { rc = cuda_fail(e, "D2H total"); break; }
         bs.d2h_bytes += (size_t)n * 8 + 4;

@@ -114,6 +114,7 @@ struct WorkSlot {
     DevBuf ckpt, carry, lastrow, colbest, scratch, offsets, n_ops, starts, tiles, ops, score3, n_chars;
     DevBuf startcell, worklist, wstate;  /* launch_start -> launch_traceback (TraceArgs): counters in the first MGLSW_WC_WORDS words of worklist */
     PinBuf h_n_ops, h_total;
+    PinBuf h_res, h_ops;                 /* results on their way to PAGEABLE caller arrays: offsets / scores, and CIGAR elements / text */
     void release();
 };
 
@@ -179,6 +180,7 @@ private:
     DevBuf arena_;               /* device copy of bytes [arena_base_, ..) of the caller's arena, padded on both sides (sw_fill.h) */
     u64 arena_base_ = 0;
     bool arena_pageable_ = false;   /* the current batch's arena is ordinary (unregistered) host memory */
+    bool res_pageable_ = false, ops_pageable_ = false;   /* ... its offsets (or scores) / its CIGAR array are */
     /* where caller offset 0 would sit: device code adds the caller's own offsets (only [arena_base_, ..) is backed) */
     const uint8_t *arena_dev() const { return (const uint8_t *)((uintptr_t)arena_.p + MGLSW_ARENA_FRONT_PAD - (uintptr_t)arena_base_); }
     int reserve_arena(const BatchIn &in);
