@@ -365,6 +365,9 @@ struct PairResult {
  * last-column maximum (sw.cpp:100-104, kept by sw_fill.h) and the captured last row (scanned here as
  * sw.cpp:116-127 does).  `score` is H of that cell in the fill's representation (+ match + bias);
  * `seg` the reference's seg_length.  Also the whole result of the score-only entry point.
+ * select_start is the scan as the reference writes it, one thread per pair: what the emulator runs.  On the device a
+ * group of 8 lanes does the same selection (start_cell_group, sw_trace_kernel.cu), checked against the reference's
+ * results by the GPU parity tests.
  */
 struct StartCell { int i, j, seg, score; };
 
