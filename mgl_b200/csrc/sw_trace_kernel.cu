@@ -1,6 +1,7 @@
 /*
- * sw_trace_kernel.cu -- start cells (a lane group per pair; gap-free paths end there), checkpoint replay + traceback of
- * the others (one thread per pair), and the two small kernels that turn per-pair CIGAR scratch into one dense array.
+ * sw_trace_kernel.cu -- the traceback's kernels: start cells (a lane group per pair; gap-free paths end there), the walks
+ * of the other pairs (Walker, sw_trace.h: short pairs one rebuilt block per launch, the rest one lane per pair to the
+ * end), and the small kernels that turn per-pair CIGAR scratch into one dense array or into text.
  * Replaces calculateCigar / calculateCigar_avx (sw.cpp:149-255, sw_avx.cpp:324-430).
  */
 #include "sw_kernels.h"
