@@ -104,8 +104,9 @@ MGL_SW_API int mgl_sw_device_count(void);
 MGL_SW_API const char *mgl_sw_version(void);
 
 /* tuning knobs: "allow_s16" 0/1, "chunk_pairs", "trace_budget_mb", "plan_threads", "pack_arena" 0/1/2 (all-ACGT byte
-   ranges of the arena cross the host link at 2 bits per base and are expanded on the device: never / for chunks whose
-   planner thread is "pack_lead" chunks ahead of the upload / always; default 0: it pays only where the link, not the
+   ranges of the arena cross the host link at 2 bits per base and are expanded on the device: never / when it hides behind the
+   link (host planning: chunks whose planner thread is "pack_lead" chunks ahead of the upload; device planning: while uploads are queued
+   and chunks' bytes are late) / always; default 0: it pays only where the link, not the
    host's cores and memory, is the slower side), "pipe_wide" 0/1/2 (long-pair
    kernel on eight warps per pair: never / for launches of few pairs / always), "copy_threads" (threads that stage a PAGEABLE arena into pinned
    memory chunk by chunk; default 8 or half the hardware threads, 0 leaves it to the driver), "exact_match_shortcut" 0/1
@@ -113,7 +114,7 @@ MGL_SW_API const char *mgl_sw_version(void);
    what GATK's SWNativeAlignerWrapper returns without calling the binding -- offset = last occurrence, CIGAR all M --
    which the reference leaves to that wrapper, ...MicrosoftSmithWaterman.cpp:60), "slots" 0/2/3/4 (work slots, i.e. chunks
    in flight: 0 = two for batches of long pairs, four otherwise), "host_plan" 0/1 (chunks planned by
-   device kernels / by host threads; the 2-bit transport implies host planning), "overlap" 0/1 (resident_run: 1 = chunks
+   device kernels / by host threads), "pack_threads" (threads the 2-bit transport packs a chunk with under device planning; 0 = two), "overlap" 0/1 (resident_run: 1 = chunks
    alternate between two slots, whole-batch time only; 0 = one chunk at a time with per-kernel times) */
 MGL_SW_API int mgl_sw_set_option(mgl_sw_handle *h, const char *name, int64_t value);
 

@@ -361,6 +361,7 @@ int mgl_sw_set_option(mgl_sw_handle *h, const char *name, int64_t value)
         else if (!std::strcmp(name, "chunk_pairs")) { if (value < 1 || value > (1 << 22)) return MGL_SW_E_INVALID; e->chunk_pairs = (u32)value; }
         else if (!std::strcmp(name, "pipe_wide")) { if (value < 0 || value > 2) return MGL_SW_E_INVALID; e->pipe_wide = (int)value; }
         else if (!std::strcmp(name, "pack_arena")) { if (value < 0 || value > 2) return MGL_SW_E_INVALID; e->pack_arena = (int)value; }
+        else if (!std::strcmp(name, "pack_threads")) { if (value < 0 || value > 32) return MGL_SW_E_INVALID; e->pack_threads = (int)value; }
         else if (!std::strcmp(name, "pack_lead")) { if (value < 0 || value > 1024) return MGL_SW_E_INVALID; e->pack_lead = (int)value; }
         else if (!std::strcmp(name, "copy_threads")) { if (value < 0 || value > 32) return MGL_SW_E_INVALID; e->copy_threads = (int)value; }
         else if (!std::strcmp(name, "exact_match_shortcut")) e->exact_shortcut = value != 0;

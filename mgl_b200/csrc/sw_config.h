@@ -22,6 +22,8 @@
 #define MGLSW_PIPE_MIN_STRIPS 4   /* pairs of at least this many strips run one per block, strips pipelined over its warps */
 #define MGLSW_SPIN_MIN_CPUS_PER_GPU 0 /* below this many hardware threads per visible GPU the collecting thread sleeps on its events (0: always spin) */
 #define MGLSW_PACK_LEAD 6          /* chunks a planner must be ahead of the uploader to spend time packing its chunk */
+#define MGLSW_PACK_BACKLOG 2        /* device planning, pack_arena 1: uploads that must be waiting on the link before a chunk is packed */
+#define MGLSW_PACK_FIRST_CHUNK 3    /* ... and never one of the first chunks of a batch */
 #define MGLSW_PACK_MIN_BYTES 65536 /* a chunk's arena byte range below this is uploaded raw (one copy, no unpack launch) */
 
 /* X(kind_type, G, K) for every instantiated kernel */

@@ -357,6 +357,33 @@ int Engine::pack_chunk(const BatchIn &in, ChunkDev &cd, std::string &err) const
     return MGL_SW_OK;
 }
 
+/*
+ * The same on T short-lived threads (the staging thread of the device planner calls this for the chunks it decides to
+ * pack): the range is cut at multiples of 128 bytes, so every piece starts on a whole packed word.
+ */
+int Engine::pack_chunk_mt(const BatchIn &in, ChunkDev &cd, int T, std::string &err) const
+{
+    cd.packed_ok = false;
+    if (cd.arena_hi <= cd.arena_lo || cd.arena_hi - cd.arena_lo < MGLSW_PACK_MIN_BYTES) return MGL_SW_OK;
+    const u64 lo16 = cd.arena_lo & ~15ull, nb = cd.arena_hi - lo16;
+    const cudaError_t e = cd.h_packed.reserve(pack2_bytes(nb));
+    if (e != cudaSuccess) { err = std::string("pinned alloc: ") + cudaGetErrorString(e); return MGL_SW_E_CUDA; }
+    T = (int)std::min<u64>((u64)std::max(1, T), std::max<u64>(1, nb >> 20));
+    std::vector<char> ok((size_t)T, 0);
+    auto part = [&](int t) {
+        const u64 a = (nb * (u64)t / (u64)T) & ~127ull, b = t + 1 == T ? nb : (nb * (u64)(t + 1) / (u64)T) & ~127ull;
+        ok[(size_t)t] = b <= a || pack2(in.arena + lo16 + a, b - a, (uint8_t *)cd.h_packed.p + a / 4) ? 1 : 0;
+    };
+    std::vector<std::thread> th;
+    for (int t = 1; t < T; t++) th.emplace_back(part, t);
+    part(0);
+    for (std::thread &x : th) x.join();
+    bool all = true;
+    for (char c : ok) all = all && c;
+    cd.packed_ok = all;
+    return MGL_SW_OK;
+}
+
 int Engine::plan_next(const BatchIn &in, int64_t first, ChunkDev &cd)
 {
     std::string err;
@@ -371,7 +398,7 @@ int Engine::plan_next(const BatchIn &in, int64_t first, ChunkDev &cd)
  * kernel and the copy home of the summary.  The host touches each pair twice here (the memcpy, and one loop for the
  * min / max of its offsets and the scratch sum) and never again.
  */
-int Engine::issue_plan_dev(const BatchIn &in, int64_t first, int64_t take, ChunkDev &cd, BatchStats &bs, std::string &err, bool upload_arena) const
+int Engine::issue_plan_dev(const BatchIn &in, int64_t first, int64_t take, ChunkDev &cd, BatchStats &bs, std::string &err, bool upload_arena, bool want_pack)
 {
     auto cfail = [&](cudaError_t ce, const char *what) { err = std::string(what) + ": " + cudaGetErrorString(ce); cudaGetLastError(); return (int)MGL_SW_E_CUDA; };
     cudaError_t e;
@@ -445,7 +472,21 @@ int Engine::issue_plan_dev(const BatchIn &in, int64_t first, int64_t take, Chunk
     cd.arena_ahead = false;
     if (upload_arena) {
         if (!cd.ev_arena && (e = cudaEventCreateWithFlags(&cd.ev_arena, cudaEventDisableTiming)) != cudaSuccess) return cfail(e, "event create");
-        if (cd.arena_hi > cd.arena_lo) {
+        if (want_pack) {
+            /* the 2-bit transport from this thread: worth its CPU time when the link is what the step waits for (the caller decides) */
+            const int prc = pack_chunk_mt(in, cd, pack_threads > 0 ? pack_threads : 2, err);
+            if (prc != MGL_SW_OK) return prc;
+        }
+        if (cd.packed_ok) {
+            const u64 lo16 = cd.arena_lo & ~15ull, nb = cd.arena_hi - lo16;
+            const size_t pb = pack2_bytes(nb);
+            if ((e = cd.packed.reserve(pb)) != cudaSuccess) return cfail(e, "cudaMalloc packed arena");
+            if ((e = cudaMemcpyAsync(cd.packed.p, cd.h_packed.p, pb, cudaMemcpyHostToDevice, upload_stream_)) != cudaSuccess) return cfail(e, "H2D packed arena");
+            sw_unpack2_kernel<<<(unsigned)((nb / 16 + 256) / 256), 256, 0, upload_stream_>>>((const u32 *)cd.packed.p, (uint8_t *)arena_dev() + lo16, nb);
+            if ((e = cudaGetLastError()) != cudaSuccess) return cfail(e, "sw_unpack2_kernel");
+            bs.h2d_bytes += pb;
+            bs.other_launches++;
+        } else if (cd.arena_hi > cd.arena_lo) {
             const u64 nb = cd.arena_hi - cd.arena_lo;
             const uint8_t *src = in.arena + cd.arena_lo;
             /*
@@ -825,6 +866,7 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
      */
     const bool pack_batch = pack_arena != 0 && !whole;
     std::atomic<int> upload_cursor{0};
+    std::atomic<int> link_behind{0};                      /* 0 .. 4: how often, lately, a chunk's bytes were not on the device when its slot was free */
     if (whole) {
         if ((e = cudaMemcpyAsync((void *)(arena_dev() + span_lo), in.arena + span_lo, span, cudaMemcpyHostToDevice, slots_[0].stream)) != cudaSuccess)
             return cuda_fail(e, "H2D arena");
@@ -879,8 +921,8 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
      * collected; R = planners + slots + 1 keeps every planner busy without blocking the collector.
      */
     /*
-     * Who plans: device kernels (sw_plan_dev.cu) unless the caller asked for the host planner, or for the 2-bit
-     * transport, whose packing is done by the host planner threads.  With device planning ONE helper thread stages
+     * Who plans: device kernels (sw_plan_dev.cu) unless the caller asked for the host planner (whose threads then also do
+     * the packing of the 2-bit transport; with device planning the staging thread packs).  With device planning ONE helper thread stages
      * each chunk's slice of the pair table and queues its planning kernels, as far ahead as the ring allows
      * (DEV_AHEAD chunks beyond the slots: under load a plan's ~30 small dependent kernels get SM space mostly when a
      * fill kernel drains, about one plan per chunk time, so the look-ahead must cover several chunks), and this
@@ -888,7 +930,7 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
      */
     /* a batch of a few pairs (alignNative is a batch of one) is planned here, on the calling thread, in microseconds: the
        planning kernel's grid barriers and the summary's way back cost 0.17 ms however small the chunk */
-    const bool dev_plan = host_plan == 0 && pack_arena == 0 && in.n > MGLSW_DEV_PLAN_MIN_PAIRS;
+    const bool dev_plan = host_plan == 0 && in.n > MGLSW_DEV_PLAN_MIN_PAIRS;
     const int DEV_AHEAD = 7;
     std::vector<std::pair<int64_t, int64_t>> bounds;
     int nthreads = plan_threads > 0 ? plan_threads : (int)std::min<unsigned>(8u, std::max(1u, std::thread::hardware_concurrency() / 2));
@@ -943,9 +985,29 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
                 cv.wait(lk, [&] { return stop || k - collected < R; });
                 if (stop) return;
             }
-            int prc_k = dev_plan ? issue_plan_dev(in, bounds[(size_t)k].first, bounds[(size_t)k].second, *ring_[(size_t)(k % R)], bs_stage, perr[(size_t)k], !whole)
+            /*
+             * Device planning, pack_arena 1: this thread packs chunk k when the link is what the step waits for AND the
+             * packing hides behind it: the launching thread has lately found chunks' bytes still on their way when their
+             * slot was free (link_behind; eight GPUs sharing the host's memory path get 23 GB/s each), and at least
+             * MGLSW_PACK_BACKLOG of the uploads queued before chunk k have not finished, so the link has work while this
+             * thread packs.  Never one of the first chunks, which the GPU is waiting for.  On a link that keeps up (one GPU:
+             * 55 GB/s) the bytes are there long before their chunk's turn and nothing is packed.
+             */
+            bool want_pack = false;
+            if (dev_plan && pack_batch) {
+                if (pack_arena == 2) want_pack = true;
+                else if (k >= MGLSW_PACK_FIRST_CHUNK && link_behind.load(std::memory_order_relaxed) >= 2) {
+                    int backlog = 0;
+                    for (int d = 1; d <= 2 * MGLSW_PACK_BACKLOG && k - d >= 0; d++) {
+                        const ChunkDev &q = *ring_[(size_t)((k - d) % R)];
+                        if (q.arena_ahead && q.ev_arena && cudaEventQuery(q.ev_arena) == cudaErrorNotReady) backlog++;
+                    }
+                    want_pack = backlog >= MGLSW_PACK_BACKLOG;
+                }
+            }
+            int prc_k = dev_plan ? issue_plan_dev(in, bounds[(size_t)k].first, bounds[(size_t)k].second, *ring_[(size_t)(k % R)], bs_stage, perr[(size_t)k], !whole, want_pack)
                                  : plan_range(in, bounds[(size_t)k].first, bounds[(size_t)k].second, *ring_[(size_t)(k % R)], perr[(size_t)k]);
-            if (prc_k == MGL_SW_OK && pack_batch && (pack_arena == 2 || k - upload_cursor.load(std::memory_order_relaxed) >= pack_lead))
+            if (!dev_plan && prc_k == MGL_SW_OK && pack_batch && (pack_arena == 2 || k - upload_cursor.load(std::memory_order_relaxed) >= pack_lead))
                 prc_k = pack_chunk(in, *ring_[(size_t)(k % R)], perr[(size_t)k]);
             {
                 std::lock_guard<std::mutex> lk(mu);
@@ -975,7 +1037,7 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         upload_cursor.store(c, std::memory_order_relaxed);
         if (nchunks == 1) {
             std::string err;
-            rc = dev_plan ? issue_plan_dev(in, bounds[0].first, bounds[0].second, cd, bs_stage, err, !whole) : plan_range(in, bounds[0].first, bounds[0].second, cd, err);
+            rc = dev_plan ? issue_plan_dev(in, bounds[0].first, bounds[0].second, cd, bs_stage, err, !whole, pack_batch && pack_arena == 2) : plan_range(in, bounds[0].first, bounds[0].second, cd, err);
             if (rc != MGL_SW_OK) { fail(rc, err); break; }
         } else {
             std::unique_lock<std::mutex> lk(mu);
@@ -991,7 +1053,11 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
         if ((rc = ensure_slot(ws, cd.plan, cd.n, so, tx)) != MGL_SW_OK) break;
         if (dev_plan) {
             /* the staging thread sent the chunk's arena bytes ahead; its fill launches wait for them */
-            if (cd.arena_ahead && (e = cudaStreamWaitEvent(ws.stream, cd.ev_arena, 0)) != cudaSuccess) { rc = cuda_fail(e, "stream wait"); break; }
+            if (cd.arena_ahead) {
+                const int lb = link_behind.load(std::memory_order_relaxed);
+                link_behind.store(cudaEventQuery(cd.ev_arena) == cudaErrorNotReady ? std::min(lb + 1, 4) : std::max(lb - 1, 0), std::memory_order_relaxed);
+                if ((e = cudaStreamWaitEvent(ws.stream, cd.ev_arena, 0)) != cudaSuccess) { rc = cuda_fail(e, "stream wait"); break; }
+            }
         } else if ((rc = upload_chunk(in, cd, ws.stream, !whole, bs)) != MGL_SW_OK) break;
         if ((rc = run_chunk(cd, ws, bs, false, so, tx)) != MGL_SW_OK) break;
         const u32 n = cd.n;

@@ -152,6 +152,7 @@ public:
                                  /* Off by default: on this pool's boxes the host cores and memory, not the link, are the   */
                                  /* shared resource (profiles/r03c, r03e: 8 GPUs 8 640 GCUPS raw, 7 875 / 6 255 with 1 / 2)  */
     int pack_lead = MGLSW_PACK_LEAD;
+    int pack_threads = 0;        /* threads the device planner's staging thread packs a chunk with (0: two) */
 
 private:
     int fail(int code, const std::string &msg);
@@ -159,11 +160,12 @@ private:
     int plan_next(const BatchIn &in, int64_t first, ChunkDev &cd);
     /* device planner: stage + upload the pair-table slice and queue the planning kernels on plan_stream_;
        then (later) wait for the summary and turn it into cd.plan */
-    int issue_plan_dev(const BatchIn &in, int64_t first, int64_t take, ChunkDev &cd, BatchStats &bs, std::string &err, bool upload_arena) const;
+    int issue_plan_dev(const BatchIn &in, int64_t first, int64_t take, ChunkDev &cd, BatchStats &bs, std::string &err, bool upload_arena, bool want_pack);
     int collect_plan_dev(ChunkDev &cd);
     int64_t chunk_take(const BatchIn &in, int64_t first, u64 limit, u32 max_pairs, const u32 *est256) const;
     int plan_range(const BatchIn &in, int64_t first, int64_t take, ChunkDev &cd, std::string &err) const;
     int pack_chunk(const BatchIn &in, ChunkDev &cd, std::string &err) const;
+    int pack_chunk_mt(const BatchIn &in, ChunkDev &cd, int T, std::string &err) const;
     int upload_chunk(const BatchIn &in, ChunkDev &cd, cudaStream_t st, bool upload_arena, BatchStats &bs);
     int upload_arena_range(const BatchIn &in, ChunkDev &cd, cudaStream_t st, bool upload_arena, BatchStats &bs);
     int run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed, bool score_only = false, bool text = false);
