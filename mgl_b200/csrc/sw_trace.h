@@ -28,6 +28,9 @@
 
 #define MGLSW_KH ((MGLSW_KMAX + 1) / 2)      /* columns of a block: at most half a lane's registers */
 #define MGLSW_HOP_WIDE_MIN_STRIPS MGLSW_PIPE_MIN_STRIPS   /* pairs of at least this many column strips (= the pipelined fill launches) hop MGLSW_HOP_BLOCKS blocks at a time */
+#ifndef MGLSW_HOP_SHORT
+#define MGLSW_HOP_SHORT 2                     /* ... pairs of lane groups of 8 (the round kernels); other whole-warp units: 1 */
+#endif
 #ifndef MGLSW_HOP_BLOCKS
 #define MGLSW_HOP_BLOCKS 4                    /* blocks one diagonal hop tries to cross per memory round trip */
 #endif
@@ -507,16 +510,17 @@ struct Walker {
 
     /*
      * While H is known, cross blocks with diagonal hops (Replay::hop): a clean stretch of the alignment costs one
-     * memory round trip and a few byte compares per block or, `wide`, per MGLSW_HOP_BLOCKS blocks (Replay::hop<NB>; the
-     * caller's choice, the same for every lane of a warp so that they keep running the same code).  Returns when the
-     * pair is done or the block around (I, J) has to be rebuilt.
+     * memory round trip and a few byte compares per NB blocks (Replay::hop<NB>; the caller's choice, the same for every
+     * lane of a warp so that they keep running the same code).  Returns when the pair is done or the block around
+     * (I, J) has to be rebuilt.
      */
-    SW_HD void hop_phase(bool wide)
+    template <int NB>
+    SW_HD void hop_phase()
     {
         while (hk && !done) {
             int hn;
             bool blocked = false;
-            const int L = wide ? rp.hop<MGLSW_HOP_BLOCKS>(I, J, hcur, hn, blocked) : rp.hop<1>(I, J, hcur, hn, blocked);
+            const int L = rp.hop<NB>(I, J, hcur, hn, blocked);
             if (L == 0) break;
             if (state == OP_M) run += L;
             else { SW_EMIT(state, run); run = L; state = OP_M; }
@@ -603,8 +607,10 @@ SW_HD PairResult traceback_pair(const UnitDesc &u, u32 half, bool s32, u32 G, u3
 {
     Walker w;
     w.begin(u, half, s32, G, K, ckpt, arena, c, st, strategy, ops_end, nib, nstride);
-    const bool wide = u.nstrips >= MGLSW_HOP_WIDE_MIN_STRIPS;
-    w.hop_phase(wide);
+    /* the hop widths the device uses for this kind of unit (sw_trace_kernel.cu) */
+    const int nb = u.nstrips >= MGLSW_HOP_WIDE_MIN_STRIPS ? MGLSW_HOP_BLOCKS : (G == (u32)MGLSW_G_SHORT ? MGLSW_HOP_SHORT : 1);
+    auto hops = [&]() { if (nb == MGLSW_HOP_BLOCKS) w.hop_phase<MGLSW_HOP_BLOCKS>(); else if (nb == MGLSW_HOP_SHORT) w.hop_phase<MGLSW_HOP_SHORT>(); else w.hop_phase<1>(); };
+    hops();
     while (!w.done) {
         if (through_state) {
             u32 rec[12];
@@ -615,7 +621,7 @@ SW_HD PairResult traceback_pair(const UnitDesc &u, u32 half, bool s32, u32 G, u3
             w = v;
         }
         w.build_phase();
-        w.hop_phase(wide);
+        hops();
     }
     return w.finish();
 }

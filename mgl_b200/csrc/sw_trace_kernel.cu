@@ -193,7 +193,7 @@ __global__ void __launch_bounds__(MGLSW_TRACE_THREADS, MGLSW_TRACE_MINB) sw_trac
             sid = a.worklist[k];
             const int4 s4 = a.startcell[k];
             x = walk_open(a, sid, &s4, nullptr, w, s_nib + threadIdx.x);
-            w.hop_phase(false);
+            w.hop_phase<MGLSW_HOP_SHORT>();
         } else {
             __align__(16) u32 rec[12];
             *reinterpret_cast<uint4 *>(rec) = __ldcg(in + 3 * (size_t)k);
@@ -204,7 +204,7 @@ __global__ void __launch_bounds__(MGLSW_TRACE_THREADS, MGLSW_TRACE_MINB) sw_trac
         }
     }
     __syncwarp();
-    if (!w.done) { w.build_phase(); w.hop_phase(false); }
+    if (!w.done) { w.build_phase(); w.hop_phase<MGLSW_HOP_SHORT>(); }
     if (live && w.done) {
         const PairResult r = w.finish();
         a.offsets[x.p] = r.offset;
@@ -272,7 +272,12 @@ __global__ void __launch_bounds__(MGLSW_TRACE_THREADS, MGLSW_TRACE_MINB) sw_trac
     const bool meet = __all_sync(0xffffffffu, !live || !(x.flags & UNIT_G32));
     const bool wide = HAS_WIDE && __all_sync(0xffffffffu, !live || x.strips >= MGLSW_HOP_WIDE_MIN_STRIPS);
     for (;;) {
-        if (!w.done) w.hop_phase(wide);                                /* each lane on its own */
+        if (!w.done) {                                                 /* each lane on its own */
+            if (RESUME) w.hop_phase<MGLSW_HOP_SHORT>();                /* the round kernels' leftovers: lane groups of 8 */
+            else if (wide) w.hop_phase<MGLSW_HOP_BLOCKS>();
+            else if (meet) w.hop_phase<MGLSW_HOP_SHORT>();             /* a small chunk's lane groups of 8 */
+            else w.hop_phase<1>();
+        }
         if (meet) { if (__ballot_sync(0xffffffffu, !w.done) == 0u) break; }   /* leaves when every lane is done */
         else if (w.done) break;
         if (!w.done) w.build_phase();                                  /* met: the lanes that need it, together */
