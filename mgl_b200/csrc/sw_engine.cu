@@ -48,6 +48,46 @@ __global__ void __launch_bounds__(256) sw_unpack2_kernel(const u32 *__restrict__
     }
 }
 
+/* ---------------------------------------------------------------- helper threads */
+
+HelperPool::~HelperPool()
+{
+    { std::lock_guard<std::mutex> lk(mu_); stop_ = true; }
+    cv_.notify_all();
+    for (std::thread &t : th_) t.join();
+}
+
+void HelperPool::worker()
+{
+    std::unique_lock<std::mutex> lk(mu_);
+    for (;;) {
+        cv_.wait(lk, [&] { return stop_ || next_ < total_; });
+        if (stop_) return;
+        const int i = next_++;
+        const std::function<void(int)> *fn = task_;
+        lk.unlock();
+        (*fn)(i);
+        lk.lock();
+        if (--pending_ == 0) done_cv_.notify_all();
+    }
+}
+
+void HelperPool::run(int T, const std::function<void(int)> &fn)
+{
+    if (T <= 1) { fn(0); return; }
+    std::lock_guard<std::mutex> one(run_mu_);           /* one run at a time: the calling thread and the staging thread share the pool */
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        while ((int)th_.size() < T - 1) th_.emplace_back(&HelperPool::worker, this);
+        task_ = &fn; next_ = 1; total_ = T; pending_ = T - 1;
+    }
+    cv_.notify_all();
+    fn(0);
+    std::unique_lock<std::mutex> lk(mu_);
+    done_cv_.wait(lk, [&] { return pending_ == 0; });
+    task_ = nullptr; total_ = 0; next_ = 0;
+}
+
 /* ---------------------------------------------------------------- buffers */
 
 cudaError_t DevBuf::reserve(size_t bytes)
@@ -361,7 +401,7 @@ int Engine::pack_chunk(const BatchIn &in, ChunkDev &cd, std::string &err) const
  * The same on T short-lived threads (the staging thread of the device planner calls this for the chunks it decides to
  * pack): the range is cut at multiples of 128 bytes, so every piece starts on a whole packed word.
  */
-int Engine::pack_chunk_mt(const BatchIn &in, ChunkDev &cd, int T, std::string &err) const
+int Engine::pack_chunk_mt(const BatchIn &in, ChunkDev &cd, int T, std::string &err)
 {
     cd.packed_ok = false;
     if (cd.arena_hi <= cd.arena_lo || cd.arena_hi - cd.arena_lo < MGLSW_PACK_MIN_BYTES) return MGL_SW_OK;
@@ -374,10 +414,7 @@ int Engine::pack_chunk_mt(const BatchIn &in, ChunkDev &cd, int T, std::string &e
         const u64 a = (nb * (u64)t / (u64)T) & ~127ull, b = t + 1 == T ? nb : (nb * (u64)(t + 1) / (u64)T) & ~127ull;
         ok[(size_t)t] = b <= a || pack2(in.arena + lo16 + a, b - a, (uint8_t *)cd.h_packed.p + a / 4) ? 1 : 0;
     };
-    std::vector<std::thread> th;
-    for (int t = 1; t < T; t++) th.emplace_back(part, t);
-    part(0);
-    for (std::thread &x : th) x.join();
+    pool_.run(T, part);
     bool all = true;
     for (char c : ok) all = all && c;
     cd.packed_ok = all;
@@ -499,10 +536,7 @@ int Engine::issue_plan_dev(const BatchIn &in, int64_t first, int64_t take, Chunk
                 if ((e = cd.h_arena.reserve(nb)) != cudaSuccess) return cfail(e, "pinned alloc");
                 const int T = (int)std::min<u64>((u64)std::min<int>(copy_threads, std::max(1, (int)std::thread::hardware_concurrency() / 2)), std::max<u64>(1, nb >> 20));
                 auto part = [&](int t) { const u64 lo = nb * t / T, hi = nb * (t + 1) / T; std::memcpy((uint8_t *)cd.h_arena.p + lo, src + lo, hi - lo); };
-                std::vector<std::thread> th;
-                for (int t = 1; t < T; t++) th.emplace_back(part, t);
-                part(0);
-                for (std::thread &x : th) x.join();
+                pool_.run(T, part);
                 src = (const uint8_t *)cd.h_arena.p;
             }
             if ((e = cudaMemcpyAsync((uint8_t *)arena_dev() + cd.arena_lo, src, nb, cudaMemcpyHostToDevice, upload_stream_)) != cudaSuccess)
@@ -771,8 +805,8 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
     if (!so && !out.keep_first_start) out.cigar_start[0] = 0;
     if (in.n == 0) { if (stats) *stats = bs; return MGL_SW_OK; }
     /* one parallel pass over the pair table: longest ref, total length, per-pair checkpoint estimate (units of 256 B).
-       Short-lived std::threads, not OpenMP: an OpenMP team keeps spinning after the loop and takes the cores the
-       planner threads need in the next few milliseconds (measured: first chunks planned 3x slower). */
+       The engine's own sleeping helper threads (HelperPool), not OpenMP: an OpenMP team keeps spinning after the loop and
+       takes the cores the planner threads need in the next few milliseconds (measured: first chunks planned 3x slower). */
     u32 max_tl = 0;
     u64 total_len = 0, total_est = 0;
     u64 span_lo = ~0ull, span_hi = 0;                 /* the byte range of the caller's arena this batch touches (wrapped offsets are refused by plan_range) */
@@ -798,10 +832,7 @@ int Engine::align_batch(const BatchIn &in, BatchOut &out, BatchStats *stats)
             }
             tmax[(size_t)t] = m; tsum[(size_t)t] = sum; tes[(size_t)t] = es; tlo[(size_t)t] = alo; thi[(size_t)t] = ahi;
         };
-        std::vector<std::thread> th;
-        for (int t = 1; t < T; t++) th.emplace_back(scan, t);
-        scan(0);
-        for (std::thread &x : th) x.join();
+        pool_.run(T, scan);
         for (int t = 0; t < T; t++) {
             max_tl = std::max(max_tl, tmax[(size_t)t]); total_len += tsum[(size_t)t];
             slice_off[(size_t)t + 1] = slice_off[(size_t)t] + tes[(size_t)t];

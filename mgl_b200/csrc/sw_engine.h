@@ -14,7 +14,11 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "sw_fill.h"
@@ -118,6 +122,26 @@ struct WorkSlot {
     void release();
 };
 
+/*
+ * A few helper threads that stay: run(T, fn) calls fn(0) on the caller and fn(1) .. fn(T - 1) on them and returns when
+ * all are done.  Creating and joining fifteen std::threads costs 0.5 ms on these boxes -- as much as the work they were
+ * created for (the pair-table scan of a 1 M-pair batch) -- so the threads are created once and sleep in between (a
+ * condition variable: nothing spins after the call and takes a core from the planner, as an OpenMP team would).
+ */
+class HelperPool {
+public:
+    ~HelperPool();
+    void run(int T, const std::function<void(int)> &fn);
+private:
+    void worker();
+    std::vector<std::thread> th_;
+    std::mutex mu_, run_mu_;
+    std::condition_variable cv_, done_cv_;
+    const std::function<void(int)> *task_ = nullptr;
+    int next_ = 0, total_ = 0, pending_ = 0;
+    bool stop_ = false;
+};
+
 class Engine {
 public:
     explicit Engine(int device);
@@ -165,7 +189,7 @@ private:
     int64_t chunk_take(const BatchIn &in, int64_t first, u64 limit, u32 max_pairs, const u32 *est256) const;
     int plan_range(const BatchIn &in, int64_t first, int64_t take, ChunkDev &cd, std::string &err) const;
     int pack_chunk(const BatchIn &in, ChunkDev &cd, std::string &err) const;
-    int pack_chunk_mt(const BatchIn &in, ChunkDev &cd, int T, std::string &err) const;
+    int pack_chunk_mt(const BatchIn &in, ChunkDev &cd, int T, std::string &err);
     int upload_chunk(const BatchIn &in, ChunkDev &cd, cudaStream_t st, bool upload_arena, BatchStats &bs);
     int upload_arena_range(const BatchIn &in, ChunkDev &cd, cudaStream_t st, bool upload_arena, BatchStats &bs);
     int run_chunk(ChunkDev &cd, WorkSlot &ws, BatchStats &bs, bool timed, bool score_only = false, bool text = false);
@@ -181,6 +205,7 @@ private:
     std::string err_;
     DevBuf arena_;               /* device copy of bytes [arena_base_, ..) of the caller's arena, padded on both sides (sw_fill.h) */
     u64 arena_base_ = 0;
+    HelperPool pool_;               /* the scan of a batch's pair table; copies and packing of a chunk's arena bytes */
     bool arena_pageable_ = false;   /* the current batch's arena is ordinary (unregistered) host memory */
     bool res_pageable_ = false, ops_pageable_ = false;   /* ... its offsets (or scores) / its CIGAR array are */
     /* where caller offset 0 would sit: device code adds the caller's own offsets (only [arena_base_, ..) is backed) */
