@@ -243,7 +243,11 @@ __global__ void __launch_bounds__(MGLSW_TRACE_THREADS, MGLSW_TRACE_MINB) sw_trac
  * (Lanes that take the next entry off the list when their pair is done -- a grid of a third or a quarter of the list --
  * keep the replay site fuller but were slower, alone and in the overlapped step: profiles/r21a.)
  */
-template <bool HAS_WIDE, bool RESUME>    /* HAS_WIDE false: no pair of MGLSW_HOP_WIDE_MIN_STRIPS strips in the chunk, the kernel carries no four-block hop */
+/* HAS_WIDE false: no pair of MGLSW_HOP_WIDE_MIN_STRIPS strips in the chunk, the kernel carries no four-block hop; SMALL: a small
+   chunk's one launch, whose list holds lane groups of 8 as well (otherwise the back list is whole-warp units only, and the
+   kernel carries neither the meeting point nor the two-block hop: its lanes run apart, so every instruction it does not
+   hold is instruction cache they do not fight over) */
+template <bool HAS_WIDE, bool RESUME, bool SMALL>
 __global__ void __launch_bounds__(MGLSW_TRACE_THREADS, MGLSW_TRACE_MINB) sw_traceback_kernel(const __grid_constant__ TraceArgs a)
 {
     __shared__ u64 s_nib[MGLSW_TRACE_BUF * MGLSW_TRACE_THREADS];   /* the replayed block: records and boundary H values, one column per thread */
@@ -269,13 +273,13 @@ __global__ void __launch_bounds__(MGLSW_TRACE_THREADS, MGLSW_TRACE_MINB) sw_trac
             x = walk_open(a, a.worklist[e], &s4, nullptr, w, s_nib + threadIdx.x);
         }
     }
-    const bool meet = __all_sync(0xffffffffu, !live || !(x.flags & UNIT_G32));
+    const bool meet = RESUME || (SMALL && __all_sync(0xffffffffu, !live || !(x.flags & UNIT_G32)));
     const bool wide = HAS_WIDE && __all_sync(0xffffffffu, !live || x.strips >= MGLSW_HOP_WIDE_MIN_STRIPS);
     for (;;) {
         if (!w.done) {                                                 /* each lane on its own */
             if (RESUME) w.hop_phase<MGLSW_HOP_SHORT>();                /* the round kernels' leftovers: lane groups of 8 */
             else if (wide) w.hop_phase<MGLSW_HOP_BLOCKS>();
-            else if (meet) w.hop_phase<MGLSW_HOP_SHORT>();             /* a small chunk's lane groups of 8 */
+            else if (SMALL && meet) w.hop_phase<MGLSW_HOP_SHORT>();    /* a small chunk's lane groups of 8 */
             else w.hop_phase<1>();
         }
         if (meet) { if (__ballot_sync(0xffffffffu, !w.done) == 0u) break; }   /* leaves when every lane is done */
@@ -363,13 +367,16 @@ cudaError_t launch_traceback(const TraceArgs &a, bool has_short, bool has_long, 
     if (has_short) {
         sw_trace_round_kernel<true><<<blocks, MGLSW_TRACE_THREADS, 0, stream>>>(a, 0u);
         for (u32 r = 1; r < MGLSW_TRACE_ROUNDS; r++) sw_trace_round_kernel<false><<<blocks, MGLSW_TRACE_THREADS, 0, stream>>>(a, r);
-        sw_traceback_kernel<false, true><<<blocks, MGLSW_TRACE_THREADS, 0, stream>>>(a);
+        sw_traceback_kernel<false, true, false><<<blocks, MGLSW_TRACE_THREADS, 0, stream>>>(a);
     }
     if (has_long) {
         /* whole-warp units hold one pair each; a small chunk has every pair slot on this list */
         const u32 lb = ((a.no_rounds ? 2u : 1u) * a.n_units + MGLSW_TRACE_THREADS - 1) / MGLSW_TRACE_THREADS;
-        if (has_wide) sw_traceback_kernel<true, false><<<lb, MGLSW_TRACE_THREADS, 0, stream>>>(a);
-        else sw_traceback_kernel<false, false><<<lb, MGLSW_TRACE_THREADS, 0, stream>>>(a);
+        if (a.no_rounds) {
+            if (has_wide) sw_traceback_kernel<true, false, true><<<lb, MGLSW_TRACE_THREADS, 0, stream>>>(a);
+            else sw_traceback_kernel<false, false, true><<<lb, MGLSW_TRACE_THREADS, 0, stream>>>(a);
+        } else if (has_wide) sw_traceback_kernel<true, false, false><<<lb, MGLSW_TRACE_THREADS, 0, stream>>>(a);
+        else sw_traceback_kernel<false, false, false><<<lb, MGLSW_TRACE_THREADS, 0, stream>>>(a);
     }
     return cudaGetLastError();
 }
