@@ -237,6 +237,66 @@ struct Replay {
         return adv;
     }
 
+    /*
+     * Gap hops.  Inside a gap the walk only asks whether the gap was EXTENDED through each cell (sw.cpp:73-93), and the
+     * recurrence gives the same kind of inequality as for the diagonal: E[i+1][j] = max(E[i][j] - ge, H[i][j] - go)
+     * >= E[i][j] - ge, with equality exactly when the reference extends there (a tie extends, :75,:86).  Summed down a
+     * block's rows: E leaving the block == E entering it - rows * ge iff EVERY cell of the column extended -- and both
+     * values are row checkpoints (E of every register after each row block).  The same across a block's columns with
+     * F and the column checkpoints (F entering each half-lane block, every row).  Two 4-byte loads decide a whole
+     * block of a long deletion / insertion (the overhang gaps of INDEL alignments are hundreds of cells: config 3 rebuilt
+     * 17 blocks per pair, most of them along one gap), no block is recomputed.
+     * ehop: the walk stands at (r, J) inside a deletion, r the LAST row of a row block whose rows are all >= 2: true if
+     * the deletion runs through all MGLSW_RB rows of the block at column J.
+     */
+    SW_HD bool ehop(int r, int J) const
+    {
+        u32 slot, reg;
+        slot_of((u32)J - 1u, slot, reg);
+        const u32 strip = slot >> gsh, lane = slot - (strip << gsh);
+        const u32 t = (u32)r + lane;
+        if ((t % MGLSW_RB) != MGLSW_RB - 1u) return false;
+        const u32 rb = t / MGLSW_RB;
+        if (rb < 1u || (int)(rb * MGLSW_RB) - (int)lane < 2) return false;      /* needs the checkpoint above, and leaves r >= 1 */
+        const bool sub = reg >= KM;
+        const u32 kk = reg - (sub ? KM : 0u);
+        const u32 *ep = base + ((size_t)strip * rbc + rb) * RW + (size_t)(lane * LSW + MGLSW_RB * 4u + ((sub ? 2u * SC : 0u) + SC) * 4u + kk);
+#if SW_ON_DEVICE
+        const u32 bot = __ldcg(ep), top = __ldcg(ep - RW);
+#else
+        const u32 bot = ep[0], top = *(ep - RW);
+#endif
+        return (int)((top >> sh) & msk) - (int)((bot >> sh) & msk) == (int)MGLSW_RB * ge;
+    }
+    /* fhop: the walk stands at (I, cc) inside an insertion, cc the LAST column of a half-lane block that starts at column
+       >= 2: the block's width if the insertion runs through all of its columns in row I, else 0 */
+    SW_HD int fhop(int I, int cc) const
+    {
+        u32 slot, reg;
+        slot_of((u32)cc - 1u, slot, reg);
+        const u32 strip = slot >> gsh, lane = slot - (strip << gsh);
+        const u32 n = cb + (slot < cr ? 1u : 0u);
+        const bool sub = reg >= KM;
+        if (n < KM || reg != (sub ? n - 1u : KM - 1u)) return 0;                /* not the block's last column (or a lane too narrow to have a mid checkpoint) */
+        const u32 k_lo = sub ? KM : 0u;
+        const int ja_ = (int)(slot < cr ? slot * (cb + 1) : cr * (cb + 1) + (slot - cr) * cb) + 1 + (int)k_lo;
+        if (ja_ < 2) return 0;
+        /* F entering the block: the end checkpoint of the lane to the left (first half) or this lane's mid checkpoint (second half);
+           F leaving it: this lane's mid checkpoint (first half) or its end checkpoint (second half) */
+        u32 cs = strip, cl = lane, wl = 1u;
+        if (!sub) { wl = 3u; if (lane > 0) cl = lane - 1; else { cl = G - 1; cs = strip - 1; } }
+        const u32 tl_ = (u32)I + cl, tr_ = (u32)I + lane;
+        const u32 *lp = base + (size_t)cs * swords + (size_t)(cl * LSW + (tl_ % MGLSW_RB) * 4u + wl) + (size_t)(tl_ / MGLSW_RB) * RW;
+        const u32 *rp_ = base + (size_t)strip * swords + (size_t)(lane * LSW + (tr_ % MGLSW_RB) * 4u + (sub ? 3u : 1u)) + (size_t)(tr_ / MGLSW_RB) * RW;
+#if SW_ON_DEVICE
+        const u32 fl = __ldcg(lp), fr = __ldcg(rp_);
+#else
+        const u32 fl = *lp, fr = *rp_;
+#endif
+        const int width = (int)(reg - k_lo) + 1;
+        return (int)((fl >> sh) & msk) - (int)((fr >> sh) & msk) == width * ge ? width : 0;
+    }
+
     SW_HD void build(int I, int J)
     {
         /* (slot, register) of column J: sw_layout.h col_to_slot */
@@ -517,6 +577,9 @@ struct Walker {
     template <int NB>
     SW_HD void hop_phase()
     {
+        /* inside a gap: whole blocks of it, as long as the checkpoints say it runs through them (Replay::ehop / fhop) */
+        if (mode == 2) { while (rp.ehop(r, J)) { steplen += (int)MGLSW_RB; r -= (int)MGLSW_RB; hops++; } return; }
+        if (mode == 1) { for (int w; (w = rp.fhop(I, cc)) != 0;) { steplen += w; cc -= w; hops++; } return; }
         while (hk && !done) {
             int hn;
             bool blocked = false;
