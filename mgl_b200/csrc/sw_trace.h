@@ -27,7 +27,11 @@
 #include "sw_config.h"
 
 #define MGLSW_KH ((MGLSW_KMAX + 1) / 2)      /* columns of a block: at most half a lane's registers */
+#ifndef MGLSW_HOP_WIDE_MIN_STRIPS
 #define MGLSW_HOP_WIDE_MIN_STRIPS MGLSW_PIPE_MIN_STRIPS   /* pairs of at least this many column strips (= the pipelined fill launches) hop MGLSW_HOP_BLOCKS blocks at a time */
+#endif
+#define MGLSW_GAP_HOP_BLOCKS 8                 /* row blocks one deletion hop tries at once (Replay::ehop) */
+#define MGLSW_GAP_HOP_LANES 4                  /* lanes one insertion hop tries at once (Replay::fhop) */
 #ifndef MGLSW_HOP_SHORT
 #define MGLSW_HOP_SHORT 2                     /* ... pairs of lane groups of 8 (the round kernels); other whole-warp units: 1 */
 #endif
@@ -246,27 +250,34 @@ struct Replay {
      * F and the column checkpoints (F entering each half-lane block, every row).  Two 4-byte loads decide a whole
      * block of a long deletion / insertion (the overhang gaps of INDEL alignments are hundreds of cells: config 3 rebuilt
      * 17 blocks per pair, most of them along one gap), no block is recomputed.
-     * ehop: the walk stands at (r, J) inside a deletion, r the LAST row of a row block whose rows are all >= 2: true if
-     * the deletion runs through all MGLSW_RB rows of the block at column J.
+     * ehop: the walk stands at (r, J) inside a deletion, r the LAST row of a row block: the rows (a whole number of row
+     * blocks, up to MGLSW_GAP_HOP_BLOCKS of them, all of rows >= 2) the deletion runs through at column J, or 0.
      */
-    SW_HD bool ehop(int r, int J) const
+    SW_HD int ehop(int r, int J) const
     {
         u32 slot, reg;
         slot_of((u32)J - 1u, slot, reg);
         const u32 strip = slot >> gsh, lane = slot - (strip << gsh);
         const u32 t = (u32)r + lane;
-        if ((t % MGLSW_RB) != MGLSW_RB - 1u) return false;
+        if ((t % MGLSW_RB) != MGLSW_RB - 1u) return 0;
         const u32 rb = t / MGLSW_RB;
-        if (rb < 1u || (int)(rb * MGLSW_RB) - (int)lane < 2) return false;      /* needs the checkpoint above, and leaves r >= 1 */
+        /* the topmost block a hop may cross starts at row >= 2 (its checkpoint above exists, and the walk is left at r >= 1) */
+        const u32 rb_min = (lane + 2u + MGLSW_RB - 1u) / MGLSW_RB;
+        if (rb < rb_min || rb < 1u) return 0;
         const bool sub = reg >= KM;
         const u32 kk = reg - (sub ? KM : 0u);
         const u32 *ep = base + ((size_t)strip * rbc + rb) * RW + (size_t)(lane * LSW + MGLSW_RB * 4u + ((sub ? 2u * SC : 0u) + SC) * 4u + kk);
+        /* the sums telescope: m blocks at once need the same two values, m blocks apart; the far one first, one block as the fallback */
+        u32 m = rb - rb_min + 1u;
+        if (m > (u32)MGLSW_GAP_HOP_BLOCKS) m = MGLSW_GAP_HOP_BLOCKS;
 #if SW_ON_DEVICE
-        const u32 bot = __ldcg(ep), top = __ldcg(ep - RW);
+        const u32 bot = __ldcg(ep), far = __ldcg(ep - (size_t)m * RW), top = __ldcg(ep - RW);
 #else
-        const u32 bot = ep[0], top = *(ep - RW);
+        const u32 bot = ep[0], far = *(ep - (size_t)m * RW), top = *(ep - RW);
 #endif
-        return (int)((top >> sh) & msk) - (int)((bot >> sh) & msk) == (int)MGLSW_RB * ge;
+        const int vb = (int)((bot >> sh) & msk);
+        if ((int)((far >> sh) & msk) - vb == (int)(m * MGLSW_RB) * ge) return (int)(m * MGLSW_RB);
+        return (int)((top >> sh) & msk) - vb == (int)MGLSW_RB * ge ? (int)MGLSW_RB : 0;
     }
     /* fhop: the walk stands at (I, cc) inside an insertion, cc the LAST column of a half-lane block that starts at column
        >= 2: the block's width if the insertion runs through all of its columns in row I, else 0 */
@@ -293,8 +304,26 @@ struct Replay {
 #else
         const u32 fl = *lp, fr = *rp_;
 #endif
+        const int vr = (int)((fr >> sh) & msk);
+        /* the sums telescope here too: first the stretch back to the first column of the lane MGLSW_GAP_HOP_LANES to the left (F entering
+           it is the end checkpoint of the lane before that one), then this block alone */
+        const u32 nslot_row = slot - strip * G;                                  /* lanes to the left inside this strip */
+        if (nslot_row >= 2u) {
+            const u32 back = nslot_row - 1u < (u32)MGLSW_GAP_HOP_LANES ? nslot_row - 1u : (u32)MGLSW_GAP_HOP_LANES;
+            const u32 ts = slot - back, tcl = ts - 1u - strip * G;               /* target lane slot, and the lane whose end checkpoint holds F entering it */
+            const int tja = (int)(ts < cr ? ts * (cb + 1) : cr * (cb + 1) + (ts - cr) * cb) + 1;
+            const u32 tt_ = (u32)I + tcl;
+            const u32 *fp = base + (size_t)strip * swords + (size_t)(tcl * LSW + (tt_ % MGLSW_RB) * 4u + 3u) + (size_t)(tt_ / MGLSW_RB) * RW;
+#if SW_ON_DEVICE
+            const u32 ff = __ldcg(fp);
+#else
+            const u32 ff = *fp;
+#endif
+            const int wide = cc - tja + 1;
+            if (tja >= 2 && (int)((ff >> sh) & msk) - vr == wide * ge) return wide;
+        }
         const int width = (int)(reg - k_lo) + 1;
-        return (int)((fl >> sh) & msk) - (int)((fr >> sh) & msk) == width * ge ? width : 0;
+        return (int)((fl >> sh) & msk) - vr == width * ge ? width : 0;
     }
 
     SW_HD void build(int I, int J)
@@ -578,7 +607,7 @@ struct Walker {
     SW_HD void hop_phase()
     {
         /* inside a gap: whole blocks of it, as long as the checkpoints say it runs through them (Replay::ehop / fhop) */
-        if (mode == 2) { while (rp.ehop(r, J)) { steplen += (int)MGLSW_RB; r -= (int)MGLSW_RB; hops++; } return; }
+        if (mode == 2) { for (int h; (h = rp.ehop(r, J)) != 0;) { steplen += h; r -= h; hops++; } return; }
         if (mode == 1) { for (int w; (w = rp.fhop(I, cc)) != 0;) { steplen += w; cc -= w; hops++; } return; }
         while (hk && !done) {
             int hn;
