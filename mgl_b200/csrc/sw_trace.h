@@ -603,12 +603,14 @@ struct Walker {
      * lane of a warp so that they keep running the same code).  Returns when the pair is done or the block around
      * (I, J) has to be rebuilt.
      */
-    template <int NB>
+    template <int NB, bool GAPS = true>
     SW_HD void hop_phase()
     {
-        /* inside a gap: whole blocks of it, as long as the checkpoints say it runs through them (Replay::ehop / fhop) */
-        if (mode == 2) { for (int h; (h = rp.ehop(r, J)) != 0;) { steplen += h; r -= h; hops++; } return; }
-        if (mode == 1) { for (int w; (w = rp.fhop(I, cc)) != 0;) { steplen += w; cc -= w; hops++; } return; }
+        /* inside a gap: whole blocks of it, as long as the checkpoints say it runs through them (Replay::ehop / fhop).
+           GAPS false: the caller's pairs are short (lane groups of 8, at most 192 columns) and gaps of whole blocks rare: it
+           leaves the code out and rebuilds those blocks */
+        if (GAPS && mode == 2) { for (int h; (h = rp.ehop(r, J)) != 0;) { steplen += h; r -= h; hops++; } return; }
+        if (GAPS && mode == 1) { for (int w; (w = rp.fhop(I, cc)) != 0;) { steplen += w; cc -= w; hops++; } return; }
         while (hk && !done) {
             int hn;
             bool blocked = false;

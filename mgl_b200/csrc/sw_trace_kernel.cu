@@ -193,7 +193,7 @@ __global__ void __launch_bounds__(MGLSW_TRACE_THREADS, MGLSW_TRACE_MINB) sw_trac
             sid = a.worklist[k];
             const int4 s4 = a.startcell[k];
             x = walk_open(a, sid, &s4, nullptr, w, s_nib + threadIdx.x);
-            w.hop_phase<MGLSW_HOP_SHORT>();
+            w.hop_phase<MGLSW_HOP_SHORT, false>();
         } else {
             __align__(16) u32 rec[12];
             *reinterpret_cast<uint4 *>(rec) = __ldcg(in + 3 * (size_t)k);
@@ -204,7 +204,7 @@ __global__ void __launch_bounds__(MGLSW_TRACE_THREADS, MGLSW_TRACE_MINB) sw_trac
         }
     }
     __syncwarp();
-    if (!w.done) { w.build_phase(); w.hop_phase<MGLSW_HOP_SHORT>(); }
+    if (!w.done) { w.build_phase(); w.hop_phase<MGLSW_HOP_SHORT, false>(); }
     if (live && w.done) {
         const PairResult r = w.finish();
         a.offsets[x.p] = r.offset;
@@ -277,7 +277,7 @@ __global__ void __launch_bounds__(MGLSW_TRACE_THREADS, MGLSW_TRACE_MINB) sw_trac
     const bool wide = HAS_WIDE && __all_sync(0xffffffffu, !live || x.strips >= MGLSW_HOP_WIDE_MIN_STRIPS);
     for (;;) {
         if (!w.done) {                                                 /* each lane on its own */
-            if (RESUME) w.hop_phase<MGLSW_HOP_SHORT>();                /* the round kernels' leftovers: lane groups of 8 */
+            if (RESUME) w.hop_phase<MGLSW_HOP_SHORT, false>();         /* the round kernels' leftovers: lane groups of 8 */
             else if (wide) w.hop_phase<MGLSW_HOP_BLOCKS>();
             else if (SMALL && meet) w.hop_phase<MGLSW_HOP_SHORT>();    /* a small chunk's lane groups of 8 */
             else w.hop_phase<1>();
