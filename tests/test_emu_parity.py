@@ -74,22 +74,8 @@ def test_emulated_long_gaps_take_the_gap_hops(oracle):
     """deletions and insertions of 7 .. 200 cells starting and ending at every kind of offset against the 8-row / half-lane
     checkpoint grid, in lane groups of 8 and in whole-warp units: the walk crosses whole blocks of such a gap with two
     checkpoint loads (Replay::ehop / fhop) and must come out where the reference's cell-by-cell walk does"""
-    rng = random.Random(5)
-    pairs = []
-    for glen in (7, 8, 9, 15, 16, 17, 31, 33, 64, 65, 130, 200):
-        for pos in (1, 2, 7, 8, 9, 40, 77):
-            for long_alt in (False, True):
-                n = 420 if long_alt else 170
-                core = bytes(rng.choice(b"ACGT") for _ in range(n))
-                p = min(pos, n - 2)
-                cut = core[:p] + core[min(n, p + glen):]                    # the other sequence lacks glen bases at p
-                ins = core[:p] + bytes(rng.choice(b"ACGT") for _ in range(glen)) + core[p:]
-                if long_alt:
-                    pairs += [(cut, core), (core, cut), (ins, core), (core, ins)]
-                else:
-                    # alt (the second sequence) at most 192 columns: lane groups of 8
-                    pairs += [(core + core[:60], cut[:190]), (ins, core[:190]), (cut, core[:190])]
-    pairs = [(r, a) for r, a in pairs if len(r) and len(a)]
+    from gap_cases import long_gap_pairs
+    pairs = long_gap_pairs()
     for params in ((10, -15, -30, -5), (200, -150, -260, -11), (3, -1, -2, 0)):
         for s in oracle.STRATEGIES:
             res, st = E.emu_align(pairs, params, s)

@@ -144,6 +144,21 @@ def test_fuzz_large_batches_through_the_round_kernels(sw, oracle, params):
         assert res.stats["other_launches"] >= 10 * max(1, res.stats["chunks"] - 1), res.stats
 
 
+def test_long_gaps_take_the_gap_hops(sw, oracle):
+    """deletions and insertions of 7 .. 200 cells at every kind of offset against the checkpoint grid (tests/gap_cases.py):
+    the walk crosses whole blocks of such a gap with two checkpoint loads (Replay::ehop / fhop); as one small batch (one
+    traceback launch, lane groups of 8 and whole-warp units side by side) and repeated into a batch large enough for
+    the round kernels"""
+    from gap_cases import long_gap_pairs
+    pairs = long_gap_pairs()
+    for params in ((10, -15, -30, -5), (200, -150, -260, -11), (3, -1, -2, 0)):
+        strategies = np.array([(1, 2, 4, 8)[k % 4] for k in range(len(pairs))], dtype=np.int32)
+        _check(sw, oracle, pairs, params, strategies)
+        big = pairs * 8
+        res = _check(sw, oracle, big, params, np.array([(2, 8, 1, 4)[k % 4] for k in range(len(big))], dtype=np.int32))
+        assert res.stats["other_launches"] >= 10
+
+
 def test_empty_and_invalid_inputs(sw):
     from mgl_b200 import native
     res = sw.align_batch([], (10, -15, -30, -5), 1)
