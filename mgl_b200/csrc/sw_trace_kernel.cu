@@ -36,6 +36,18 @@ __device__ __forceinline__ StartCell start_cell_group(const UnitDesc &u, u32 hal
     } else {
         /* lane g takes lane slots g, g + 8, ...: K consecutive words each, columns ascending; the 8 lanes of a group read
            neighbouring 4 K-byte runs of one row, so the sectors are shared through L1 (the row was written by an earlier launch) */
+        /* first only the row's maximum (three instructions per word): a last row that stays below the last-column maximum --
+           a read that ends inside its haplotype -- cannot be where the walk starts, and the scan with the tie rules is skipped */
+        int rowmax = (int)0x80000000;
+        for (u32 slot = gl; slot < nslots; slot += 8u) {
+            const u32 cols = slot_cols(u, slot);
+            const u32 *wp = row + (size_t)slot * K;
+#pragma unroll 4
+            for (u32 reg = 0; reg < cols; reg++) { const int s = (int)((wp[reg] >> sh) & msk); rowmax = s > rowmax ? s : rowmax; }
+        }
+#pragma unroll
+        for (int m = 1; m < 8; m <<= 1) { const int o = __shfl_xor_sync(gmask, rowmax, m); rowmax = o > rowmax ? o : rowmax; }
+        if (rowmax < mqe) { sc.i = mqe_t; sc.j = ql; sc.seg = 0; sc.score = mqe; return sc; }
         int best = (int)0x80000000, bd = 0x7fffffff, bj = 0x7fffffff;
         for (u32 slot = gl; slot < nslots; slot += 8u) {
             const u32 cols = slot_cols(u, slot);
