@@ -83,6 +83,24 @@ def test_emulated_long_gaps_take_the_gap_hops(oracle):
             assert not bad, bad[:2]
 
 
+def test_emulated_long_gaps_across_strips(oracle):
+    """the same in strip-mined pairs (alt of 900 .. 2 400 columns: 2 to 4 strips, the last with four-block diagonal hops):
+    an insertion hop stays inside its strip, a deletion hop reads the row checkpoints of its own strip"""
+    rng = random.Random(9)
+    pairs = []
+    for n, glen, pos in ((900, 64, 10), (1700, 200, 770), (1700, 33, 1536), (2400, 130, 5), (2400, 300, 1500)):
+        core = bytes(rng.choice(b"ACGT") for _ in range(n))
+        cut = core[:pos] + core[pos + glen:]
+        ins = core[:pos] + bytes(rng.choice(b"ACGT") for _ in range(glen)) + core[pos:]
+        short = core[: n // 3]
+        pairs += [(cut, core), (core, ins), (short, core), (core[: n // 2], ins)]
+    for params in ((200, -150, -260, -11), (10, -15, -30, -5)):
+        for s in oracle.STRATEGIES:
+            res, st = E.emu_align(pairs, params, s)
+            bad = [(len(r), len(a), params, s) for (r, a), got in zip(pairs, res) if got != oracle.align(r, a, params, s)]
+            assert not bad, bad[:3]
+
+
 def test_planner_rejects_bad_input():
     with pytest.raises(RuntimeError):
         E.emu_align([(b"ACGT", b"")], (10, -15, -30, -5), 1)
